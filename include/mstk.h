@@ -1,0 +1,228 @@
+/*
+ * mstk.h -- C ABI of libmstk.so: the sm_100a kernels behind the spectrogram-latent
+ * denoising hot path (UNet eps-prediction, VAE encode/decode, DDIM loop, losses,
+ * mel front end).
+ *
+ * The reference (PrioteasaAndrei/music-style-transfer-ldm) has no FFI of its own: every
+ * device op is a torch.nn / ATen call made from models/model.py, models/loss.py and
+ * data/audio_processor.py.  Each entry point below therefore cites the reference
+ * call site (file:line under the reference tree) whose ATen/cuDNN/cuBLAS work it
+ * replaces.  The Python host layer (music_style_transfer_ldm_b200/) binds these with
+ * ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless said
+ *     otherwise; `stream` is a cudaStream_t / CUstream passed as void*.
+ *   - every call returns 0 (MSTK_OK) or a negative error code; the message is
+ *     available (thread-local) from mstk_last_error().  Nothing throws across the ABI.
+ *   - no allocation, no stream synchronisation, no host-visible side effects:
+ *     all work is enqueued on `stream` and is CUDA-graph capturable.
+ *   - activations are NHWC ("channels last"), dtype MSTK_F32 or MSTK_BF16;
+ *     parameters are packed once by the mstk_pack_* calls.
+ */
+#ifndef MSTK_H_
+#define MSTK_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSTK_ABI_VERSION 1
+
+enum { MSTK_OK = 0, MSTK_EINVAL = -1, MSTK_ECUDA = -2, MSTK_EUNSUPPORTED = -3 };
+enum { MSTK_F32 = 0, MSTK_BF16 = 1 };
+enum { MSTK_ACT_NONE = 0, MSTK_ACT_RELU = 1, MSTK_ACT_TANH = 2 };
+/* kernel family used for a contraction.  AUTO = tcgen05 implicit GEMM whenever the
+ * shape allows (bf16, Cin % 32 == 0, Cout % 16 == 0), else the CUDA-core kernel. */
+enum { MSTK_BACKEND_AUTO = 0, MSTK_BACKEND_SIMT = 1, MSTK_BACKEND_TCGEN05 = 2 };
+
+int mstk_version(void);
+const char* mstk_last_error(void);
+/* 1 when the tcgen05/TMA path could be initialised (driver entry point for
+ * cuTensorMapEncodeTiled resolved); it is an error, not a fallback, if it is 0. */
+int mstk_tcgen05_available(void);
+
+/* ------------------------------------------------------------------------------
+ * Fused DDIM update, applied in the epilogue of the last UNet conv (dec1) or
+ * stand-alone.  Replaces model.py:441-458 / 535-552 (7 elementwise ATen launches):
+ *   x0   = (x - s1m_t*eps) / sab_t
+ *   x'   = sab_n*x0 + s1m_n*eps + eta*(s1m_n*eps - s1m_t*eps)
+ * with sab = sqrt(alpha_bar), s1m = sqrt(1-alpha_bar) (host computes them in fp32
+ * exactly as torch does).  NOTE the reference's eta only rescales the predicted
+ * noise; no fresh noise is injected.
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_ddim_args {
+    const float* x_cur;   /* [N,H,W,C] fp32 current latent                       */
+    float* x_next;        /* [N,H,W,C] fp32 (may alias x_cur)                    */
+    void* x_next_lp;      /* optional bf16 copy of x_next (next step's conv input) */
+    float* x0_pred;       /* optional fp32 log of x0 (sampling_logs['pred_x0'])  */
+    float sab_t, s1m_t, sab_n, s1m_n, eta;
+} mstk_ddim_args;
+
+/* ------------------------------------------------------------------------------
+ * Convolution family: Conv2d k3 p1 (s1/s2), k1 (= nn.Linear over tokens),
+ * ConvTranspose2d k3 s2 p1 op1 and k4 s2 p1, all as one tap-gather implicit GEMM.
+ * Replaces F.conv2d / F.conv_transpose2d / F.linear + the elementwise ops that
+ * follow them in the reference:
+ *   UNet.forward            model.py:205-229 (bias, ReLU, +t_emb, +skip)
+ *   SpectrogramEncoder      model.py:16-25   (conv; BatchNorm statistics gathered here)
+ *   SpectrogramDecoder      model.py:37-46   (convT; tanh; (y+1)/2 of model.py:371)
+ *   StyleEncoder            model.py:70-79
+ *   MultiheadAttention in/out projections  model.py:155 (F.linear inside nn.MultiheadAttention)
+ *   VGGish features         thirdparty/torchvggish/vggish.py:108-118 driven by loss.py:78-90
+ * Epilogue order:  v = acc + bias ; stats += (v, v*v) ; v = act(v) ;
+ *                  v = v*out_scale + out_shift ; v += add_nc[n,c] ; v += add[n,h,w,c] ;
+ *                  store y (and/or DDIM update).
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_conv_args {
+    const void* x;        /* [n,h,w,cin] NHWC, `dtype`                              */
+    const void* wpacked;  /* [k*k][cout][cin], `dtype` (mstk_pack_conv_weight)      */
+    const float* bias;    /* [cout] fp32 or NULL                                    */
+    void* y;              /* [n,ho,wo,cout] NHWC, `out_dtype`; NULL allowed with ddim */
+    const void* add;      /* optional NHWC tensor shaped like y, `dtype`            */
+    const float* add_nc;  /* optional [n,cout] fp32 (time embedding, model.py:206)  */
+    double* stats;        /* optional [2*cout]: sum, sum of squares of v (BatchNorm
+                             batch statistics, model.py:18,21,24,39,42); accumulated
+                             with atomics, caller zeroes it                         */
+    const mstk_ddim_args* ddim; /* optional (HOST pointer)                          */
+    void* workspace;      /* split-K scratch, zero-initialised once by the caller;
+                             kernels leave it zeroed.  NULL = no split-K            */
+    size_t workspace_bytes;
+    int32_t n, h, w, cin, cout;
+    int32_t ksize;        /* 1, 3 or 4                                              */
+    int32_t stride;       /* 1 or 2                                                 */
+    int32_t transposed;   /* 0 conv (pad = ksize/2 for k3, 0 for k1);
+                             1 conv-transpose (k3 s2 p1 op1, or k4 s2 p1)           */
+    int32_t act;          /* MSTK_ACT_*                                             */
+    float out_scale, out_shift; /* applied after act; use 1,0 for identity          */
+    int32_t dtype;        /* dtype of x, wpacked, add                               */
+    int32_t out_dtype;    /* dtype of y                                             */
+    int32_t backend;      /* MSTK_BACKEND_*                                         */
+} mstk_conv_args;
+
+int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream);
+/* bytes of split-K workspace that lets the tcgen05 path spread this problem over
+ * the whole GPU (0 if split-K would not be used) */
+size_t mstk_conv2d_workspace_bytes(const mstk_conv_args* a);
+
+/* nn.Conv2d weight [cout,cin,k,k] fp32 -> [k*k][cout][cin] in `dtype`, optionally
+ * scaled per output channel (eval-mode BatchNorm folding, model.py:18-24). */
+int mstk_pack_conv_weight(const float* w_oihw, const float* scale_cout, void* dst,
+                          int cout, int cin, int k, int dtype, void* stream);
+/* nn.ConvTranspose2d weight [cin,cout,k,k] fp32 -> [k*k][cout][cin] in `dtype`. */
+int mstk_pack_convt_weight(const float* w_iohw, const float* scale_cout, void* dst,
+                           int cin, int cout, int k, int dtype, void* stream);
+
+/* layout changes at the nn.Module boundary (reference tensors are NCHW fp32) */
+int mstk_nchw_to_nhwc(const float* src, void* dst, int n, int c, int h, int w,
+                      int dst_dtype, void* stream);
+int mstk_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w,
+                      int src_dtype, void* stream);
+/* dtype cast of a flat buffer */
+int mstk_cast(const void* src, int src_dtype, void* dst, int dst_dtype, size_t count, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * BatchNorm2d: finalise batch statistics gathered by the producing conv and apply
+ * normalise + affine (+ReLU) in one 128-bit vectorised streaming pass.  Replaces
+ * nn.BatchNorm2d + nn.ReLU at model.py:18-19, 21-22, 24, 39-40, 42-43 (train mode:
+ * biased batch variance; running buffers updated with momentum and the unbiased
+ * variance).  Eval mode never reaches this call: it is folded into the conv.
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_bn_args {
+    const void* x;          /* [count, c] NHWC rows, `dtype`                        */
+    void* y;                /* same shape, `out_dtype` (may alias x if same dtype)  */
+    const double* stats;    /* [2*c] sum, sumsq over `count` rows                   */
+    const float* gamma;     /* [c]                                                  */
+    const float* beta;      /* [c]                                                  */
+    float* running_mean;    /* optional [c], updated in place                       */
+    float* running_var;     /* optional [c]                                         */
+    float* save_mean;       /* optional [c]: batch mean (for backward)              */
+    float* save_invstd;     /* optional [c]: 1/sqrt(var+eps)                        */
+    int64_t count;          /* rows = N*H*W (global count under data parallelism)   */
+    int32_t c;
+    float eps, momentum;
+    int32_t act;            /* MSTK_ACT_NONE or MSTK_ACT_RELU                       */
+    int32_t dtype, out_dtype;
+} mstk_bn_args;
+int mstk_bn_apply(const mstk_bn_args* a, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * UNet.time_mlp: sinusoidal embedding -> Linear -> GELU(erf) -> Linear.
+ * Replaces model.py:170-175, 203, 239-246.  t is fp32 (the reference accepts int64
+ * or float timesteps, models/tests.py:447); out is [b,128] fp32.
+ * ---------------------------------------------------------------------------- */
+int mstk_time_embed(const float* t, int b, const float* w1, const float* b1,
+                    const float* w2, const float* b2, float* out, int dim, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * Cross-attention core for nn.MultiheadAttention(E, heads) (model.py:155,
+ * SURVEY A.3) after the projections: per (sample, head) softmax(q k^T / sqrt(d)) v.
+ * q: [b, l, e]; k, v: [b, s, e] with row strides given in elements (k and v may be
+ * slices of one fused [b, s, 2e] projection); out: [b, l, e].  All `dtype`.
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_attn_args {
+    const void* q; const void* k; const void* v; void* out;
+    int32_t b, l, s, e, heads;
+    int32_t q_stride, k_stride, v_stride, out_stride;   /* elements between tokens */
+    int32_t dtype;
+} mstk_attn_args;
+int mstk_attention_fwd(const mstk_attn_args* a, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * Scheduler arithmetic (ForwardDiffusion, model.py:102-124), NHWC or NCHW agnostic:
+ * `inner` = elements per sample.
+ *   q_sample:   z_t = sqrt(ab[t_b])*x0 + sqrt(1-ab[t_b])*eps
+ *   predict_x0: x0  = (z_t - sqrt(1-ab[t_b])*eps_hat) / sqrt(ab[t_b])
+ * `z_lp` / `x0_lp`: optional bf16 copy for the next conv.
+ * ---------------------------------------------------------------------------- */
+int mstk_q_sample(const float* x0, const float* eps, const float* alpha_bar, const int64_t* t,
+                  float* z_t, void* z_lp, int b, int64_t inner, void* stream);
+int mstk_predict_x0(const float* z_t, const float* eps_hat, const float* alpha_bar, const int64_t* t,
+                    float* x0, void* x0_lp, int b, int64_t inner, void* stream);
+/* stand-alone DDIM update over `count` elements (same math as the fused epilogue);
+ * eps is fp32 */
+int mstk_ddim_step(const mstk_ddim_args* a, const float* eps, size_t count, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * Loss reductions (models/loss.py).  Each writes ONE fp32 scalar to `out` (device)
+ * using a double accumulator `scratch` ([4] doubles + [1] uint32 counter, zeroed by
+ * the caller once; kernels leave it zeroed).
+ *   mse:  mean((a-b)^2)                      loss.py:36,49
+ *   kl:   mean(0.5(z^2 - 1 - log(z^2+1e-8))) loss.py:31-32
+ * ---------------------------------------------------------------------------- */
+int mstk_mse(const void* a, const void* b, int dtype, size_t count, double* scratch, float* out, void* stream);
+int mstk_kl(const float* z, size_t count, double* scratch, float* out, void* stream);
+/* VGGish tap term (loss.py:94-99): per sample i, f/(std_unbiased(f_i)+1e-8) vs
+ * g/(std_unbiased(g_i)+1e-8), mean squared difference over all b*inner elements.
+ * tmp: [b*4 + 2] doubles scratch (zeroed by caller; left zeroed). Accumulates
+ * `weight * term` into out[0] (so the six taps can be summed with weight 1/6). */
+int mstk_feature_std_mse(const void* f, const void* g, int dtype, int b, int64_t inner,
+                         double* tmp, float weight, float* out, void* stream);
+/* 2x2/2 max pool on NHWC (vggish.py:113) */
+int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------
+ * Mel front end (data/audio_processor.py:44-73 -> librosa.feature.melspectrogram +
+ * power_to_db(ref=np.max) + the uint8 image quantisation):
+ * wave [b, len] fp32 -> frames (n_fft 2048, hop 512, periodic Hann, centre zero pad)
+ * -> |rFFT|^2 -> Slaney mel (n_mels) -> dB re per-clip max, floor -80 ->
+ * img = trunc(clip((S+80)*255/80,0,255)+0.5)/255 in [0,1], cropped to `crop_frames`.
+ * out: [b, n_mels, crop_frames] fp32 (row 0 = lowest band).  db_out optional
+ * [b, n_mels, frames] (the un-quantised dB values).  work: see mstk_mel_workspace_bytes.
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_mel_args {
+    const float* wave; float* out; float* db_out;
+    const float* mel_fb;     /* [n_mels, 1025] filterbank (host builds it, fp32)   */
+    void* work; size_t work_bytes;
+    int32_t b, len, n_mels, crop_frames;
+} mstk_mel_args;
+size_t mstk_mel_workspace_bytes(int b, int len, int n_mels);
+int mstk_mel_frontend(const mstk_mel_args* a, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSTK_H_ */

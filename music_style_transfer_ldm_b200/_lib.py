@@ -1,0 +1,111 @@
+"""ctypes binding of libmstk.so (the C ABI declared in include/mstk.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` /
+``python -m music_style_transfer_ldm_b200.build``.  There is NO fallback: if the
+shared object is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmstk.so")
+
+F32, BF16 = 0, 1
+ACT_NONE, ACT_RELU, ACT_TANH = 0, 1, 2
+BACKEND_AUTO, BACKEND_SIMT, BACKEND_TCGEN05 = 0, 1, 2
+
+c_void_p, c_int, c_float, c_size_t, c_int64 = C.c_void_p, C.c_int32, C.c_float, C.c_size_t, C.c_int64
+
+
+class MstkError(RuntimeError):
+    pass
+
+
+class DdimArgs(C.Structure):
+    _fields_ = [("x_cur", c_void_p), ("x_next", c_void_p), ("x_next_lp", c_void_p), ("x0_pred", c_void_p),
+                ("sab_t", c_float), ("s1m_t", c_float), ("sab_n", c_float), ("s1m_n", c_float), ("eta", c_float)]
+
+
+class ConvArgs(C.Structure):
+    _fields_ = [("x", c_void_p), ("wpacked", c_void_p), ("bias", c_void_p), ("y", c_void_p), ("add", c_void_p),
+                ("add_nc", c_void_p), ("stats", c_void_p), ("ddim", C.POINTER(DdimArgs)),
+                ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+                ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int),
+                ("ksize", c_int), ("stride", c_int), ("transposed", c_int), ("act", c_int),
+                ("out_scale", c_float), ("out_shift", c_float),
+                ("dtype", c_int), ("out_dtype", c_int), ("backend", c_int)]
+
+
+class BnArgs(C.Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p), ("stats", c_void_p), ("gamma", c_void_p), ("beta", c_void_p),
+                ("running_mean", c_void_p), ("running_var", c_void_p), ("save_mean", c_void_p),
+                ("save_invstd", c_void_p), ("count", c_int64), ("c", c_int), ("eps", c_float),
+                ("momentum", c_float), ("act", c_int), ("dtype", c_int), ("out_dtype", c_int)]
+
+
+class AttnArgs(C.Structure):
+    _fields_ = [("q", c_void_p), ("k", c_void_p), ("v", c_void_p), ("out", c_void_p),
+                ("b", c_int), ("l", c_int), ("s", c_int), ("e", c_int), ("heads", c_int),
+                ("q_stride", c_int), ("k_stride", c_int), ("v_stride", c_int), ("out_stride", c_int),
+                ("dtype", c_int)]
+
+
+class MelArgs(C.Structure):
+    _fields_ = [("wave", c_void_p), ("out", c_void_p), ("db_out", c_void_p), ("mel_fb", c_void_p),
+                ("work", c_void_p), ("work_bytes", c_size_t),
+                ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int)]
+
+
+# name -> (restype, argtypes); every symbol include/mstk.h declares
+SIGNATURES = {
+    "mstk_version": (c_int, []),
+    "mstk_last_error": (C.c_char_p, []),
+    "mstk_tcgen05_available": (c_int, []),
+    "mstk_conv2d_fwd": (c_int, [C.POINTER(ConvArgs), c_void_p]),
+    "mstk_conv2d_workspace_bytes": (c_size_t, [C.POINTER(ConvArgs)]),
+    "mstk_pack_conv_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_pack_convt_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_nchw_to_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_nhwc_to_nchw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_cast": (c_int, [c_void_p, c_int, c_void_p, c_int, c_size_t, c_void_p]),
+    "mstk_bn_apply": (c_int, [C.POINTER(BnArgs), c_void_p]),
+    "mstk_time_embed": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "mstk_attention_fwd": (c_int, [C.POINTER(AttnArgs), c_void_p]),
+    "mstk_q_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+    "mstk_predict_x0": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+    "mstk_ddim_step": (c_int, [C.POINTER(DdimArgs), c_void_p, c_size_t, c_void_p]),
+    "mstk_mse": (c_int, [c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_void_p]),
+    "mstk_kl": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
+    "mstk_feature_std_mse": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_float, c_void_p, c_void_p]),
+    "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_mel_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load libmstk.so and bind every declared symbol.  Raises if anything is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise MstkError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU or PyTorch fallback for the kernels.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().mstk_last_error()
+        raise MstkError(f"{what or 'mstk call'} failed (code {rc}): {msg.decode() if msg else '?'}")

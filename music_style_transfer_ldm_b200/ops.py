@@ -1,0 +1,312 @@
+"""Thin functional layer over the C ABI: torch tensors are only device-memory handles.
+
+Activations are NHWC (``[N, H, W, C]`` contiguous), fp32 or bf16.  Every function
+enqueues on torch's current CUDA stream (so the calls are CUDA-graph capturable) and
+raises ``MstkError`` on failure; nothing here computes with PyTorch ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (ACT_NONE, ACT_RELU, ACT_TANH, BACKEND_AUTO, BACKEND_SIMT, BACKEND_TCGEN05, BF16, F32,
+                   MstkError, check)
+
+TORCH_DTYPE = {F32: torch.float32, BF16: torch.bfloat16}
+
+
+def dtype_code(t_or_dtype) -> int:
+    d = t_or_dtype.dtype if isinstance(t_or_dtype, torch.Tensor) else t_or_dtype
+    if d == torch.float32:
+        return F32
+    if d == torch.bfloat16:
+        return BF16
+    raise MstkError(f"unsupported dtype {d}")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise MstkError(f"{name}: expected a CUDA tensor (the kernels have no CPU path)")
+    if not t.is_contiguous():
+        raise MstkError(f"{name}: expected a contiguous tensor")
+    return t
+
+
+_workspaces = {}
+WORKSPACE_BYTES = 32 << 20
+
+
+def workspace(device) -> torch.Tensor:
+    """Zero-initialised split-K scratch shared by all conv calls of a device (kernels
+    leave it zeroed; launches on one stream are ordered)."""
+    key = torch.device(device).index or 0
+    ws = _workspaces.get(key)
+    if ws is None:
+        ws = torch.zeros(WORKSPACE_BYTES, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+@dataclass
+class Ddim:
+    """Arguments of the fused DDIM update (include/mstk.h: mstk_ddim_args)."""
+    x_cur: torch.Tensor
+    x_next: torch.Tensor
+    sab_t: float
+    s1m_t: float
+    sab_n: float
+    s1m_n: float
+    eta: float
+    x_next_lp: Optional[torch.Tensor] = None
+    x0_pred: Optional[torch.Tensor] = None
+
+    def to_c(self) -> _lib.DdimArgs:
+        return _lib.DdimArgs(_p(self.x_cur), _p(self.x_next), _p(self.x_next_lp), _p(self.x0_pred),
+                             self.sab_t, self.s1m_t, self.sab_n, self.s1m_n, self.eta)
+
+
+def conv_out_hw(h, w, ksize, stride, transposed):
+    if transposed:
+        return 2 * h, 2 * w
+    pad = ksize // 2
+    return (h + 2 * pad - ksize) // stride + 1, (w + 2 * pad - ksize) // stride + 1
+
+
+def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *, ksize: int, stride: int = 1,
+         transposed: bool = False, act: int = ACT_NONE, add: Optional[torch.Tensor] = None,
+         add_nc: Optional[torch.Tensor] = None, stats: Optional[torch.Tensor] = None, ddim: Optional[Ddim] = None,
+         out_dtype: Optional[torch.dtype] = None, out_scale: float = 1.0, out_shift: float = 0.0,
+         out: Optional[torch.Tensor] = None, want_y: bool = True, backend: int = BACKEND_AUTO) -> Optional[torch.Tensor]:
+    """Conv2d / ConvTranspose2d / Linear with the fused epilogue (mstk_conv2d_fwd)."""
+    lib = _lib.load()
+    _dev(x, "conv.x"); _dev(wpacked, "conv.w")
+    n, h, w, cin = x.shape
+    kk, cout, cin_w = wpacked.shape
+    if cin_w != cin or kk != ksize * ksize:
+        raise MstkError(f"conv: packed weight {tuple(wpacked.shape)} does not match cin={cin} k={ksize}")
+    if wpacked.dtype != x.dtype:
+        raise MstkError(f"conv: weight dtype {wpacked.dtype} != activation dtype {x.dtype}")
+    ho, wo = conv_out_hw(h, w, ksize, stride, transposed)
+    out_dtype = out_dtype or x.dtype
+    y = None
+    if want_y:
+        y = out if out is not None else torch.empty((n, ho, wo, cout), dtype=out_dtype, device=x.device)
+        if tuple(y.shape) != (n, ho, wo, cout) or y.dtype != out_dtype:
+            raise MstkError("conv: bad `out` tensor")
+        _dev(y, "conv.out")
+    if add is not None:
+        _dev(add, "conv.add")
+        if tuple(add.shape) != (n, ho, wo, cout) or add.dtype != x.dtype:
+            raise MstkError(f"conv: add tensor {tuple(add.shape)}/{add.dtype} must match output shape and input dtype")
+    if add_nc is not None and (tuple(add_nc.shape) != (n, cout) or add_nc.dtype != torch.float32):
+        raise MstkError("conv: add_nc must be fp32 [n, cout]")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != cout):
+        raise MstkError("conv: bias must be fp32 [cout]")
+    if stats is not None and (stats.dtype != torch.float64 or stats.numel() != 2 * cout):
+        raise MstkError("conv: stats must be float64 [2*cout]")
+    ws = workspace(x.device)
+    dd = ddim.to_c() if ddim is not None else None
+    a = _lib.ConvArgs(_p(x), _p(wpacked), _p(bias), _p(y), _p(add), _p(add_nc), _p(stats),
+                      C.pointer(dd) if dd is not None else None, _p(ws), ws.numel(),
+                      n, h, w, cin, cout, ksize, stride, 1 if transposed else 0, act, out_scale, out_shift,
+                      dtype_code(x), dtype_code(out_dtype), backend)
+    check(lib.mstk_conv2d_fwd(C.byref(a), _stream()), "mstk_conv2d_fwd")
+    return y
+
+
+def pack_weight(w: torch.Tensor, dtype: torch.dtype, *, transposed: bool = False,
+                scale: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """nn.Conv2d [co,ci,k,k] / nn.ConvTranspose2d [ci,co,k,k] / nn.Linear [co,ci] fp32 -> [k*k, co, ci]."""
+    lib = _lib.load()
+    w = _dev(w.detach(), "pack.w")
+    if w.dtype != torch.float32:
+        raise MstkError("pack_weight: parameters must be fp32")
+    if w.dim() == 2:
+        co, ci, k = w.shape[0], w.shape[1], 1
+    elif transposed:
+        ci, co, k = w.shape[0], w.shape[1], w.shape[2]
+    else:
+        co, ci, k = w.shape[0], w.shape[1], w.shape[2]
+    dst = torch.empty((k * k, co, ci), dtype=dtype, device=w.device)
+    fn = lib.mstk_pack_convt_weight if (transposed and w.dim() == 4) else lib.mstk_pack_conv_weight
+    if transposed and w.dim() == 4:
+        check(fn(_p(w), _p(scale), _p(dst), ci, co, k, dtype_code(dtype), _stream()), "mstk_pack_convt_weight")
+    else:
+        check(fn(_p(w), _p(scale), _p(dst), co, ci, k, dtype_code(dtype), _stream()), "mstk_pack_conv_weight")
+    return dst
+
+
+def nchw_to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    lib = _lib.load()
+    x = _dev(x, "nchw_to_nhwc.x")
+    if x.dtype != torch.float32:
+        raise MstkError("nchw_to_nhwc: source must be fp32")
+    n, c, h, w = x.shape
+    dst = torch.empty((n, h, w, c), dtype=dtype, device=x.device)
+    check(lib.mstk_nchw_to_nhwc(_p(x), _p(dst), n, c, h, w, dtype_code(dtype), _stream()), "mstk_nchw_to_nhwc")
+    return dst
+
+
+def nhwc_to_nchw(x: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    x = _dev(x, "nhwc_to_nchw.x")
+    n, h, w, c = x.shape
+    dst = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
+    check(lib.mstk_nhwc_to_nchw(_p(x), _p(dst), n, c, h, w, dtype_code(x), _stream()), "mstk_nhwc_to_nchw")
+    return dst
+
+
+def cast(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    lib = _lib.load()
+    x = _dev(x, "cast.x")
+    if x.dtype == dtype:
+        return x
+    dst = torch.empty(x.shape, dtype=dtype, device=x.device)
+    check(lib.mstk_cast(_p(x), dtype_code(x), _p(dst), dtype_code(dtype), x.numel(), _stream()), "mstk_cast")
+    return dst
+
+
+def bn_apply(x: torch.Tensor, stats: torch.Tensor, gamma, beta, *, count: int, eps: float, momentum: float,
+             act: int, out_dtype: torch.dtype, running_mean=None, running_var=None, save_mean=None,
+             save_invstd=None) -> torch.Tensor:
+    lib = _lib.load()
+    x = _dev(x, "bn.x")
+    c = x.shape[-1]
+    y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    a = _lib.BnArgs(_p(x), _p(y), _p(stats), _p(gamma), _p(beta), _p(running_mean), _p(running_var), _p(save_mean),
+                    _p(save_invstd), count, c, eps, momentum, act, dtype_code(x), dtype_code(out_dtype))
+    check(lib.mstk_bn_apply(C.byref(a), _stream()), "mstk_bn_apply")
+    return y
+
+
+def time_embed(t: torch.Tensor, w1, b1, w2, b2) -> torch.Tensor:
+    lib = _lib.load()
+    t = _dev(t, "time_embed.t")
+    if t.dtype != torch.float32:
+        raise MstkError("time_embed: t must be fp32 (cast on the host side)")
+    dim = w1.shape[0]
+    out = torch.empty((t.numel(), dim), dtype=torch.float32, device=t.device)
+    check(lib.mstk_time_embed(_p(t), t.numel(), _p(w1), _p(b1), _p(w2), _p(b2), _p(out), dim, _stream()),
+          "mstk_time_embed")
+    return out
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> torch.Tensor:
+    """q [b,l,e]; k, v [b,s,e] (last-dim-contiguous views allowed) -> [b,l,e]."""
+    lib = _lib.load()
+    b, l, e = q.shape
+    s = k.shape[1]
+    for t, nm in ((q, "q"), (k, "k"), (v, "v")):
+        if not t.is_cuda or t.stride(-1) != 1 or t.stride(0) != t.shape[1] * t.stride(1):
+            raise MstkError(f"attention: {nm} must be a CUDA tensor with dense tokens")
+    out = torch.empty((b, l, e), dtype=q.dtype, device=q.device)
+    a = _lib.AttnArgs(_p(q), _p(k), _p(v), _p(out), b, l, s, e, heads, q.stride(1), k.stride(1), v.stride(1), e,
+                      dtype_code(q))
+    check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd")
+    return out
+
+
+def q_sample(x0, eps, alpha_bar, t, *, lp: bool = False):
+    lib = _lib.load()
+    _dev(x0, "q_sample.x0"); _dev(eps, "q_sample.eps")
+    b = x0.shape[0]
+    inner = x0.numel() // b
+    z = torch.empty_like(x0)
+    zlp = torch.empty(x0.shape, dtype=torch.bfloat16, device=x0.device) if lp else None
+    check(lib.mstk_q_sample(_p(x0), _p(eps), _p(alpha_bar), _p(t), _p(z), _p(zlp), b, inner, _stream()), "mstk_q_sample")
+    return z, zlp
+
+
+def predict_x0(z_t, eps_hat, alpha_bar, t, *, lp: bool = False):
+    lib = _lib.load()
+    _dev(z_t, "predict_x0.z_t"); _dev(eps_hat, "predict_x0.eps_hat")
+    b = z_t.shape[0]
+    inner = z_t.numel() // b
+    x0 = torch.empty_like(z_t)
+    xlp = torch.empty(z_t.shape, dtype=torch.bfloat16, device=z_t.device) if lp else None
+    check(lib.mstk_predict_x0(_p(z_t), _p(eps_hat), _p(alpha_bar), _p(t), _p(x0), _p(xlp), b, inner, _stream()),
+          "mstk_predict_x0")
+    return x0, xlp
+
+
+def ddim_step(d: Ddim, eps: torch.Tensor) -> None:
+    lib = _lib.load()
+    dd = d.to_c()
+    check(lib.mstk_ddim_step(C.byref(dd), _p(_dev(eps, "ddim.eps")), eps.numel(), _stream()), "mstk_ddim_step")
+
+
+_scratch = {}
+
+
+def _loss_scratch(device, n_doubles: int) -> torch.Tensor:
+    key = (torch.device(device).index or 0, n_doubles)
+    s = _scratch.get(key)
+    if s is None:
+        s = torch.zeros(n_doubles, dtype=torch.float64, device=device)
+        _scratch[key] = s
+    return s
+
+
+def mse(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    _dev(a, "mse.a"); _dev(b, "mse.b")
+    if a.dtype != b.dtype or a.numel() != b.numel():
+        raise MstkError("mse: operands must match")
+    out = torch.empty(1, dtype=torch.float32, device=a.device)
+    check(lib.mstk_mse(_p(a), _p(b), dtype_code(a), a.numel(), _p(_loss_scratch(a.device, 8)), _p(out), _stream()), "mstk_mse")
+    return out
+
+
+def kl(z: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    _dev(z, "kl.z")
+    out = torch.empty(1, dtype=torch.float32, device=z.device)
+    check(lib.mstk_kl(_p(z), z.numel(), _p(_loss_scratch(z.device, 8)), _p(out), _stream()), "mstk_kl")
+    return out
+
+
+def feature_std_mse(f: torch.Tensor, g: torch.Tensor, weight: float, out: torch.Tensor) -> None:
+    """Accumulates weight * mean((f/(std_i(f)+1e-8) - g/(std_i(g)+1e-8))^2) into out[0]."""
+    lib = _lib.load()
+    _dev(f, "feat.f"); _dev(g, "feat.g")
+    b = f.shape[0]
+    inner = f.numel() // b
+    tmp = _loss_scratch(f.device, 4 * b + 2)
+    check(lib.mstk_feature_std_mse(_p(f), _p(g), dtype_code(f), b, inner, _p(tmp), weight, _p(out), _stream()),
+          "mstk_feature_std_mse")
+
+
+def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    _dev(x, "maxpool.x")
+    n, h, w, c = x.shape
+    y = torch.empty((n, h // 2, w // 2, c), dtype=x.dtype, device=x.device)
+    check(lib.mstk_maxpool2x2(_p(x), _p(y), n, h, w, c, dtype_code(x), _stream()), "mstk_maxpool2x2")
+    return y
+
+
+def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, want_db: bool = False):
+    lib = _lib.load()
+    _dev(wave, "mel.wave"); _dev(mel_fb, "mel.fb")
+    b, ln = wave.shape
+    n_mels = mel_fb.shape[0]
+    frames = 1 + ln // 512
+    out = torch.empty((b, n_mels, crop_frames), dtype=torch.float32, device=wave.device)
+    db = torch.empty((b, n_mels, frames), dtype=torch.float32, device=wave.device) if want_db else None
+    nbytes = lib.mstk_mel_workspace_bytes(b, ln, n_mels)
+    work = torch.empty(nbytes, dtype=torch.uint8, device=wave.device)
+    a = _lib.MelArgs(_p(wave), _p(out), _p(db), _p(mel_fb), _p(work), nbytes, b, ln, n_mels, crop_frames)
+    check(lib.mstk_mel_frontend(C.byref(a), _stream()), "mstk_mel_frontend")
+    return out, db
