@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""Benchmark of the denoising hot path (BASELINE.json: "UNet denoise steps/s").
+
+    python bench.py --gpus N --steps K --warmup W            # CUDA path (libmstk)
+    python bench.py --impl reference --steps K --warmup W    # CPU arm: oracle port on the host cores
+
+Workload (BASELINE config 3): `LDM.content_style_transfer_wrapper(content, style,
+num_timesteps=50, eta=0)` at batch 64 per GPU, 128x128 spectrograms (latent 32x16x16):
+49 UNet eps-predictions each fused with its DDIM update, plus encoder, style encoder and two
+decoder passes.  One bench "step" = one such call.  `value` = UNet denoise steps per second
+over the whole job (49 * K * n_gpus / time); one denoise step = one batch-64 UNet evaluation +
+DDIM update.  Synthetic inputs, seeded random-init weights (no checkpoint is obtainable offline).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BATCH = 64
+NSTEPS = 50            # "50-step" => 49 UNet evaluations (reference model.py:525)
+SPEC = 128
+METRIC = "unet_denoise_steps_per_s"
+UNIT = "steps/s"
+
+
+def workload_config(extra=None):
+    c = {"workload": "config3: content_style_transfer_wrapper(num_timesteps=50, eta=0), batch 64/GPU, 1x128x128 spectrograms, "
+                     "latent 32x16x16, 49 UNet+DDIM steps + encoder + style encoder + 2 decoder passes",
+         "batch_per_gpu": BATCH, "num_timesteps": NSTEPS, "unet_evals_per_step": NSTEPS - 1,
+         "l2": "flushed between bench steps (256 MiB write); within a step the 13.7 MB of weights are L2 resident by design"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm (oracle port of the reference's algorithm; the reference tree itself is not on the box)
+# ------------------------------------------------------------------------------------------
+def cpu_transfer_timing(calls: int, warm_steps: int = 3):
+    """Times oracle.content_style_transfer (fp32, eval-mode BN) on the host cores.  Returns
+    (denoise steps/s, threads, description)."""
+    import torch
+    from oracle import ldm_oracle as O
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    threads = torch.get_num_threads()
+    sd = O.make_state_dict(1234)
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand((BATCH, 1, SPEC, SPEC), generator=g)
+    s = torch.rand((BATCH, 1, SPEC, SPEC), generator=g)
+    eps = torch.randn((BATCH, 32, SPEC // 8, SPEC // 8), generator=g)
+    with torch.no_grad():
+        O.content_style_transfer(sd, x, s, eps, num_timesteps=warm_steps + 1, eta=0.0, training=False)   # warm-up
+        t0 = time.perf_counter()
+        for _ in range(calls):
+            O.content_style_transfer(sd, x, s, eps, num_timesteps=NSTEPS, eta=0.0, training=False)
+        dt = time.perf_counter() - t0
+    return (NSTEPS - 1) * calls / dt, threads, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    calls = max(1, args.steps)
+    v, threads, dt = cpu_transfer_timing(calls, warm_steps=max(1, args.warmup))
+    sample = f"{calls} full config-3 call(s) (batch 64, 49 UNet+DDIM steps, enc + style enc + 2 dec), fp32, torch CPU kernels, {dt:.1f} s"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": calls, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / calls, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config({"arm": "oracle port of the reference algorithm (oracle/ldm_oracle.py) on host cores; "
+                                                               "the Python reference tree cannot travel to the GPU box"}),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------
+# roofline of the dominant kernel (conv_tc_kernel): per-layer timing of one UNet step
+# ------------------------------------------------------------------------------------------
+def conv_flops(rec):
+    """algorithmic FLOPs of one recorded conv call: 2 * output pixels * cout * cin * taps-per-output"""
+    n, h, w, cin, cout, k, s, tr = rec["n"], rec["h"], rec["w"], rec["cin"], rec["cout"], rec["ksize"], rec["stride"], rec["transposed"]
+    if tr:
+        # every input pixel meets every kernel tap exactly once
+        return 2.0 * n * h * w * cin * cout * k * k
+    ho, wo = (h + 2 * (k // 2) - k) // s + 1, (w + 2 * (k // 2) - k) // s + 1
+    return 2.0 * n * ho * wo * cin * cout * k * k
+
+
+def kernel_roofline(model, peaks, reps=20):
+    """Records the conv calls of ONE UNet+DDIM step, then replays each recorded call `reps` times
+    back to back inside a CUDA graph and times the graph with CUDA events on the launch stream.
+    Returns the roofline dict for the tcgen05 kernel and a per-layer table."""
+    import torch
+    from music_style_transfer_ldm_b200 import ops
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(1)
+    z = torch.randn((BATCH, 32, 16, 16), generator=g).to(dev)
+    st = {"s5": torch.rand((BATCH, 256, 4, 4), generator=g).to(dev), "s6": torch.rand((BATCH, 512, 2, 2), generator=g).to(dev)}
+    model.use_cuda_graphs = False
+    ops.RECORD = []
+    with torch.no_grad():
+        model.content_style_ddim_sample(z, st, timesteps=2, eta=0.0)     # exactly one UNet step
+    recs, ops.RECORD = ops.RECORD, None
+    model.use_cuda_graphs = True
+    torch.cuda.synchronize()
+    rows = []
+    stream = torch.cuda.Stream()
+    for rec in recs:
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                rec["replay"]()
+            stream.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=stream):
+                for _ in range(reps):
+                    rec["replay"]()
+            gr.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); gr.replay(); e1.record(stream)
+            stream.synchronize()
+            us = 1e3 * e0.elapsed_time(e1) / reps
+        rows.append({"layer": rec["tag"], "kernel": rec["kernel"], "us": us, "gflop": conv_flops(rec) / 1e9,
+                     "tflops": conv_flops(rec) / (us * 1e-6) / 1e12})
+    tc = [r for r in rows if r["kernel"] == "conv_tc_kernel"]
+    fl, us = sum(r["gflop"] for r in tc) * 1e9, sum(r["us"] for r in tc)
+    peak = peaks.get("bf16_tflops", 1590.0)
+    achieved = fl / (us * 1e-6) / 1e12 if us > 0 else 0.0
+    roof = {"bound": "tensor", "kernel": "conv_tc_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak, "traffic": None, "launches_per_unet_step": len(tc),
+            "flop_per_launch_avg": fl / max(1, len(tc)), "us_per_launch_avg": us / max(1, len(tc)),
+            "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1590 (B200_PROFILING.md)",
+            "note": "achieved = sum of algorithmic conv FLOPs of the tcgen05 launches of one batch-64 UNet step / sum of their "
+                    "isolated launch durations (each layer replayed 20x in a CUDA graph, CUDA events)"}
+    return roof, rows
+
+
+# ------------------------------------------------------------------------------------------
+# CUDA arm
+# ------------------------------------------------------------------------------------------
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200 import ops
+    from oracle import ldm_oracle as O      # only for the shared seeded weights and the cpu_baseline leg
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sd = O.make_state_dict(1234)
+    model = M.LDM(latent_dim=32, pretrained_path=None)
+    model.load_state_dict(sd, strict=True)
+    model.to(dev).eval().set_precision(args.precision)
+
+    g = torch.Generator().manual_seed(100 + rank)            # every rank: its own shard of the global batch
+    content_h = torch.rand((BATCH, 1, SPEC, SPEC), generator=g).pin_memory()
+    style_h = torch.rand((BATCH, 1, SPEC, SPEC), generator=g).pin_memory()
+    content_d, style_d = content_h.to(dev), style_h.to(dev)
+    out_h = [torch.empty((BATCH, 1, SPEC, SPEC)).pin_memory() for _ in range(2)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step_device():
+        return model.content_style_transfer_wrapper(content_d, style_d, num_timesteps=NSTEPS, eta=0.0)
+
+    def step_e2e():
+        c = content_h.to(dev, non_blocking=True)
+        s = style_h.to(dev, non_blocking=True)
+        dec, ztd = model.content_style_transfer_wrapper(c, s, num_timesteps=NSTEPS, eta=0.0)
+        out_h[0].copy_(dec, non_blocking=True)
+        out_h[1].copy_(ztd, non_blocking=True)
+
+    def timed(fn, k):
+        evs = []
+        for _ in range(k):
+            flush.fill_(1)                                   # L2 flush, outside the timed events
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)        # ms on the device
+
+    with torch.no_grad():
+        for _ in range(max(3, args.warmup)):
+            step_device()
+        step_e2e()
+        torch.cuda.synchronize()
+        ops.LAUNCHES = 0
+        step_device()
+        torch.cuda.synchronize()
+        launches_per_step = ops.LAUNCHES
+
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        barrier()
+        ms = timed(step_device, args.steps)
+        barrier()
+        ms_e2e = timed(step_e2e, args.steps)
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = t.tolist()
+    unet_steps = (NSTEPS - 1) * args.steps * world
+    value = unet_steps / (ms * 1e-3)
+    e2e_value = unet_steps / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        with torch.no_grad():
+            roof, rows = kernel_roofline(model, peaks)
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, threads, dt = cpu_transfer_timing(2)
+            cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": f"2 full config-3 calls (batch 64, 49 UNet+DDIM steps + VAE/style passes) of the oracle port, fp32, {dt:.1f} s"}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": workload_config({"precision": args.precision, "sharding": f"batch-sharded x{world}, no collective on the data path"}),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
+                    "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches_per_step * args.steps * 2),
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+            "samples_steps_per_s": value * BATCH,
+            "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
+            "layers": rows,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="mstk", choices=["mstk", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps is None:
+            args.steps = 2
+        args.steps = min(args.steps, 4)      # each step is ~5-10 s of CPU work: keep the run within minutes
+        run_reference(args)
+    else:
+        if args.steps is None:
+            args.steps = 20
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -607,9 +607,11 @@ class LDM(_Kernelised):
                 self._loop_body(ent["x"], ent["s5"], ent["s6"], times[:2], eta, None, ent["tt2"])
             torch.cuda.current_stream().wait_stream(side)
             g = torch.cuda.CUDAGraph()
+            n0 = ops.LAUNCHES
             with torch.cuda.graph(g):
                 self._loop_body(ent["x"], ent["s5"], ent["s6"], times, eta, logs, ent["tt"])
             ent["graph"] = g
+            ent["launches"], ops.LAUNCHES = ops.LAUNCHES - n0, n0      # capture enqueues nothing
             # the graph holds raw pointers to the packed weights: keep them alive with it
             ent["keep"] = [dict(m.__dict__.get("_mstk_cache", {})) for m in self.unet.modules()]
             if len(graphs) >= 8:
@@ -617,6 +619,7 @@ class LDM(_Kernelised):
             graphs[key] = ent
         ent["x"].copy_(z_t); ent["s5"].copy_(s5); ent["s6"].copy_(s6)
         ent["graph"].replay()
+        ops._count(ent["launches"])
         return ent["x"].clone(), ent["logs"]
 
     def _sample(self, z_t_nhwc, s5, s6, times, eta):

@@ -47,6 +47,25 @@ def _dev(t: torch.Tensor, name: str) -> torch.Tensor:
 _workspaces = {}
 WORKSPACE_BYTES = 32 << 20
 
+# bookkeeping for bench.py: kernels launched through this module (graph replays are added by
+# the caller that replays them) and, when RECORD is a list, a replayable record of conv calls
+LAUNCHES = 0
+RECORD = None
+
+
+def _count(n: int = 1) -> None:
+    global LAUNCHES
+    LAUNCHES += n
+
+
+def tc_eligible(dtype, cin: int, cout: int, stride: int, transposed: bool, h: int, w: int) -> bool:
+    """mirror of conv_tc_supported() in csrc/conv_tc.cu (which kernel AUTO picks)"""
+    if dtype != torch.bfloat16 or cin % 32 or cout % 16:
+        return False
+    if not transposed and stride == 2 and (h % 2 or w % 2):
+        return False
+    return True
+
 
 def workspace(device) -> torch.Tensor:
     """Zero-initialised split-K scratch shared by all conv calls of a device (kernels
@@ -123,6 +142,17 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
                       n, h, w, cin, cout, ksize, stride, 1 if transposed else 0, act, out_scale, out_shift,
                       dtype_code(x), dtype_code(out_dtype), backend)
     check(lib.mstk_conv2d_fwd(C.byref(a), _stream()), "mstk_conv2d_fwd")
+    _count()
+    if RECORD is not None:
+        use_tc = backend == BACKEND_TCGEN05 or (backend == BACKEND_AUTO and tc_eligible(x.dtype, cin, cout, stride, transposed, h, w))
+        keep = (x, wpacked, bias, y, add, add_nc, stats, ddim, dd, ws)
+
+        def replay(a=a, keep=keep):
+            check(lib.mstk_conv2d_fwd(C.byref(a), _stream()), "mstk_conv2d_fwd(replay)")
+
+        RECORD.append(dict(n=n, h=h, w=w, cin=cin, cout=cout, ksize=ksize, stride=stride, transposed=transposed,
+                           kernel="conv_tc_kernel" if use_tc else "conv_simt_kernel", replay=replay,
+                           tag=f"{'convT' if transposed else 'conv'}k{ksize}s{stride} {cin}->{cout} @{h}x{w} n{n}"))
     return y
 
 
@@ -156,6 +186,7 @@ def nchw_to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     n, c, h, w = x.shape
     dst = torch.empty((n, h, w, c), dtype=dtype, device=x.device)
     check(lib.mstk_nchw_to_nhwc(_p(x), _p(dst), n, c, h, w, dtype_code(dtype), _stream()), "mstk_nchw_to_nhwc")
+    _count(1)
     return dst
 
 
@@ -165,6 +196,7 @@ def nhwc_to_nchw(x: torch.Tensor) -> torch.Tensor:
     n, h, w, c = x.shape
     dst = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
     check(lib.mstk_nhwc_to_nchw(_p(x), _p(dst), n, c, h, w, dtype_code(x), _stream()), "mstk_nhwc_to_nchw")
+    _count(1)
     return dst
 
 
@@ -175,6 +207,7 @@ def cast(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
         return x
     dst = torch.empty(x.shape, dtype=dtype, device=x.device)
     check(lib.mstk_cast(_p(x), dtype_code(x), _p(dst), dtype_code(dtype), x.numel(), _stream()), "mstk_cast")
+    _count(1)
     return dst
 
 
@@ -188,6 +221,7 @@ def bn_apply(x: torch.Tensor, stats: torch.Tensor, gamma, beta, *, count: int, e
     a = _lib.BnArgs(_p(x), _p(y), _p(stats), _p(gamma), _p(beta), _p(running_mean), _p(running_var), _p(save_mean),
                     _p(save_invstd), count, c, eps, momentum, act, dtype_code(x), dtype_code(out_dtype))
     check(lib.mstk_bn_apply(C.byref(a), _stream()), "mstk_bn_apply")
+    _count(1)
     return y
 
 
@@ -200,6 +234,7 @@ def time_embed(t: torch.Tensor, w1, b1, w2, b2) -> torch.Tensor:
     out = torch.empty((t.numel(), dim), dtype=torch.float32, device=t.device)
     check(lib.mstk_time_embed(_p(t), t.numel(), _p(w1), _p(b1), _p(w2), _p(b2), _p(out), dim, _stream()),
           "mstk_time_embed")
+    _count(1)
     return out
 
 
@@ -215,6 +250,7 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
     a = _lib.AttnArgs(_p(q), _p(k), _p(v), _p(out), b, l, s, e, heads, q.stride(1), k.stride(1), v.stride(1), e,
                       dtype_code(q))
     check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd")
+    _count(1)
     return out
 
 
@@ -226,6 +262,7 @@ def q_sample(x0, eps, alpha_bar, t, *, lp: bool = False):
     z = torch.empty_like(x0)
     zlp = torch.empty(x0.shape, dtype=torch.bfloat16, device=x0.device) if lp else None
     check(lib.mstk_q_sample(_p(x0), _p(eps), _p(alpha_bar), _p(t), _p(z), _p(zlp), b, inner, _stream()), "mstk_q_sample")
+    _count(1)
     return z, zlp
 
 
@@ -238,6 +275,7 @@ def predict_x0(z_t, eps_hat, alpha_bar, t, *, lp: bool = False):
     xlp = torch.empty(z_t.shape, dtype=torch.bfloat16, device=z_t.device) if lp else None
     check(lib.mstk_predict_x0(_p(z_t), _p(eps_hat), _p(alpha_bar), _p(t), _p(x0), _p(xlp), b, inner, _stream()),
           "mstk_predict_x0")
+    _count(1)
     return x0, xlp
 
 
@@ -245,6 +283,7 @@ def ddim_step(d: Ddim, eps: torch.Tensor) -> None:
     lib = _lib.load()
     dd = d.to_c()
     check(lib.mstk_ddim_step(C.byref(dd), _p(_dev(eps, "ddim.eps")), eps.numel(), _stream()), "mstk_ddim_step")
+    _count(1)
 
 
 _scratch = {}
@@ -266,6 +305,7 @@ def mse(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
         raise MstkError("mse: operands must match")
     out = torch.empty(1, dtype=torch.float32, device=a.device)
     check(lib.mstk_mse(_p(a), _p(b), dtype_code(a), a.numel(), _p(_loss_scratch(a.device, 8)), _p(out), _stream()), "mstk_mse")
+    _count(1)
     return out
 
 
@@ -274,6 +314,7 @@ def kl(z: torch.Tensor) -> torch.Tensor:
     _dev(z, "kl.z")
     out = torch.empty(1, dtype=torch.float32, device=z.device)
     check(lib.mstk_kl(_p(z), z.numel(), _p(_loss_scratch(z.device, 8)), _p(out), _stream()), "mstk_kl")
+    _count(1)
     return out
 
 
@@ -286,6 +327,7 @@ def feature_std_mse(f: torch.Tensor, g: torch.Tensor, weight: float, out: torch.
     tmp = _loss_scratch(f.device, 4 * b + 2)
     check(lib.mstk_feature_std_mse(_p(f), _p(g), dtype_code(f), b, inner, _p(tmp), weight, _p(out), _stream()),
           "mstk_feature_std_mse")
+    _count(2)
 
 
 def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
@@ -294,6 +336,7 @@ def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     n, h, w, c = x.shape
     y = torch.empty((n, h // 2, w // 2, c), dtype=x.dtype, device=x.device)
     check(lib.mstk_maxpool2x2(_p(x), _p(y), n, h, w, c, dtype_code(x), _stream()), "mstk_maxpool2x2")
+    _count(1)
     return y
 
 
@@ -309,4 +352,5 @@ def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, wan
     work = torch.empty(nbytes, dtype=torch.uint8, device=wave.device)
     a = _lib.MelArgs(_p(wave), _p(out), _p(db), _p(mel_fb), _p(work), nbytes, b, ln, n_mels, crop_frames)
     check(lib.mstk_mel_frontend(C.byref(a), _stream()), "mstk_mel_frontend")
+    _count(3)
     return out, db
