@@ -90,6 +90,7 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
 bool conv_tc_supported(const ConvP& p);
 size_t conv_tc_workspace_bytes(const ConvP& p);
 bool tc_init();
+void tc_set_debug(long long* p);
 
 // ---------------------------------------------------------------------------
 // small device helpers

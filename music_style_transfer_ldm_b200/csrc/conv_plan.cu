@@ -95,6 +95,8 @@ extern "C" {
 int mstk_version(void) { return MSTK_ABI_VERSION; }
 const char* mstk_last_error(void) { return mstk::last_error(); }
 int mstk_tcgen05_available(void) { return mstk::tc_init() ? 1 : 0; }
+/* development aid (not in mstk.h): CTA (0,0,0) of every tcgen05 conv launch writes 8 clock64 stamps here */
+int mstk_debug_tc_timeline(long long* dev_buf) { mstk::tc_set_debug(dev_buf); return MSTK_OK; }
 
 int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     mstk::ConvP p;

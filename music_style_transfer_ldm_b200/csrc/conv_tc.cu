@@ -37,7 +37,9 @@ struct TcParams {
     int32_t tmem_cols;
     float* ws;                     // split-K workspace
     unsigned int* counters;        // split-K tile counters
+    long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
 };
+#define DBG_STAMP(i) do { if (q.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) q.dbg[i] = clock64(); } while (0)
 
 // ---------------------------------------------------------------------------
 // PTX wrappers
@@ -182,6 +184,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
 
     if (threadIdx.x == 0) {
+        DBG_STAMP(0);
         prefetch_tmap(&mapA0);
         prefetch_tmap(&mapB);
         for (int s = 0; s < q.stages; ++s) {
@@ -202,6 +205,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
+    if (threadIdx.x == 0) DBG_STAMP(1);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -228,6 +232,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                 }
                 tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
                 tma_load_2d(&mapB, &full_bar[s], sb, cb * q.KC, t.slice * p.Cout + co0);
+                if (it == 0) DBG_STAMP(2);
             }
         }
     } else if (warp == 1) {
@@ -238,6 +243,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                 const int s = it % q.stages;
                 const uint32_t par = (uint32_t)((it / q.stages) & 1);
                 mbar_wait(&full_bar[s], par);
+                if (it == 0) DBG_STAMP(3);
+                if (it == nkb - 1) DBG_STAMP(4);
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint32_t sb = sa + a_bytes;
@@ -264,6 +271,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
         const int et = threadIdx.x - 64;         // 0..127
 
         mbar_wait(&accum_bar, 0);
+        if (et == 0) DBG_STAMP(5);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
 
@@ -340,6 +348,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                 if (et == 0) *ctr = 0u;
             }
         }
+        if (et == 0) DBG_STAMP(6);
         tc_fence_before();
     }
 
@@ -347,6 +356,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)q.tmem_cols) : "memory");
+        if (lane == 0) DBG_STAMP(7);
     }
 }
 
@@ -356,6 +366,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
+static long long* g_dbg = nullptr;
+void tc_set_debug(long long* p) { g_dbg = p; }
 
 bool tc_init() {
     if (g_tc_state != 0) return g_tc_state > 0;
@@ -480,6 +492,7 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     }
     q.Wt = c.Wt; q.Ht = c.Ht; q.Nt = c.Nt;
     q.tiles_w = c.tiles_w; q.tiles_h = c.tiles_h; q.tiles_n = c.tiles_n;
+    q.dbg = g_dbg;
     q.KC = c.KC; q.BN = c.BN; q.kb_per_tap = c.kb_per_tap; q.splitk = c.splitk; q.stages = c.stages; q.tmem_cols = c.tmem_cols;
 
     const CUtensorMapSwizzle sw = (c.KC == 64) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
