@@ -1,0 +1,14 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, smoke, bench (both arms), ncu launch list, ncu --set full of the tcgen05 kernel.
+# Everything lands in gpurun_out/; numbers printed under ncu are never bench values.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,driver_version,clocks.sm,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+timeout 1500 python -m pytest tests -q -m gpu --timeout 600 > gpurun_out/t_gpu.log 2>&1; echo "pytest_gpu rc=$?" | tee gpurun_out/rc.txt
+timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/rc.txt
+timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?" | tee -a gpurun_out/rc.txt
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2> gpurun_out/bench_ref.err; echo "bench_ref rc=$?" | tee -a gpurun_out/rc.txt
+timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/b_short.log 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1; echo "ncu_list rc=$?" | tee -a gpurun_out/rc.txt
+timeout 300 python tools/profile_step.py 4 > gpurun_out/prof_plain.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"conv_tc_kernel|attention_kernel" -s 36 -c 17 -o gpurun_out/prof_step python tools/profile_step.py 4 > gpurun_out/prof_ncu.log 2>&1; echo "ncu_full rc=$?" | tee -a gpurun_out/rc.txt
+tail -n 5 gpurun_out/t_gpu.log; tail -n 4 gpurun_out/smoke.log; cut -c 1-1800 gpurun_out/bench.log; tail -n 5 gpurun_out/bench.err; cut -c 1-600 gpurun_out/bench_ref.log
