@@ -9,12 +9,25 @@
 //   columns = BN output channels; B operand = [BN x KC] box of the packed weights
 //             [tap][cout][cin] (K-major).
 //   K loop  = (tap, channel block) pairs, optionally split across gridDim.z (split-K) so
-//             that the small-M layers of the UNet still spread over all 148 SMs; partial
-//             tiles are reduced with fp32 RED into a zeroed workspace and the last CTA to
-//             arrive runs the epilogue and re-zeroes it.
+//             that the small-M layers of the UNet still spread over all 148 SMs.
+//
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer
-// (single thread issues tcgen05.mma, accumulator in TMEM), warps 2..5 = epilogue
-// (tcgen05.ld -> bias/act/adds/DDIM -> global).
+// (single thread issues tcgen05.mma, accumulator in TMEM), warps 2..5 = epilogue.
+//
+// Epilogue (v2, after the round-1a profile showed it was 60-80 % of the kernel):
+//   * everything the epilogue needs that does not depend on the accumulator is fetched
+//     WHILE the MMAs run: bias -> smem, residual tile (`add`) -> smem by TMA, x_cur of the
+//     fused DDIM update -> registers;
+//   * tcgen05.ld 32 columns at a time; the finished tile is staged in shared memory in the
+//     TMA swizzle layout (bank-conflict free 16-byte stores) and written with ONE TMA tensor
+//     store per 128-byte column chunk (coalescing is done by the copy engine; out-of-range
+//     rows are clipped by the tensor map);
+//   * split-K partials are reduced in L2 by the copy engine (cp.reduce.async.bulk .add.f32 of
+//     the whole contiguous fp32 tile) instead of per-lane REDs; the last CTA to arrive pulls
+//     the tile back with one bulk copy, runs the epilogue and re-zeroes the scratch.
+// Programmatic dependent launch: the prologue (barrier init, TMEM allocation, descriptor
+// prefetch) AND the weight (B operand) loads of the first pipeline stages are issued before
+// griddepcontrol.wait, i.e. they overlap the tail of the previous layer's kernel.
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include "common.cuh"
@@ -25,16 +38,31 @@ constexpr int TC_THREADS = 192;
 constexpr int TILE_M = 128;
 constexpr int MAX_STAGES = 8;
 
+struct TcMaps {
+    CUtensorMap a[4];     // input, one per stride-2 parity view (a[0] only for stride 1)
+    CUtensorMap b;        // packed weights [taps*cout][cin]
+    CUtensorMap out[4];   // output, one per conv-transpose phase (out[0] only for conv)
+    CUtensorMap add[4];   // residual tensor, same geometry as out
+};
+
 struct TcParams {
     ConvP p;
     int32_t Wt, Ht, Nt;            // tile box; Wt*Ht*Nt == 128
     int32_t tiles_w, tiles_h, tiles_n;
     int32_t KC;                    // channels per k-block: 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
-    int32_t BN;                    // output channels per CTA (16..256, multiple of 16)
+    int32_t BN;                    // output channels per CTA (16..128, multiple of 16)
     int32_t kb_per_tap;            // Cin / KC
     int32_t splitk;
     int32_t stages;
     int32_t tmem_cols;
+    int32_t out_esz;               // bytes per output element (2 or 4)
+    int32_t out_rowbytes;          // bytes per row of one output staging chunk (<= 128)
+    int32_t out_chunks;            // BN*out_esz / out_rowbytes
+    int32_t add_rowbytes, add_chunks;
+    int32_t use_tma_store;         // y written through the staging tile + TMA
+    int32_t use_tma_add;           // residual prefetched by TMA
+    uint32_t off_stage0;           // shared-memory carve-up (bytes from the 1024-aligned base)
+    uint32_t off_part, off_out, off_add, off_bias;
     float* ws;                     // split-K workspace
     unsigned int* counters;        // split-K tile counters
     long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
@@ -74,20 +102,40 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000ll) __trap();   // ~2 s at 2 GHz
     }
 }
-__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2, int c3) {
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, uint32_t dst, int c0, int c1, int c2, int c3) {
     asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
-            smem_u32(dst)),
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, uint32_t dst, int c0, int c1) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-            smem_u32(dst)),
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+                 "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, uint32_t src, uint32_t bytes) {
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst), "r"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(gsrc),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -130,7 +178,7 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
     uint32_t r[16];
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
@@ -143,17 +191,25 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// byte offset of 16-byte piece `j` of row `r` in a staging chunk with `rowbytes` bytes per row,
+// in the TMA swizzle layout of that row width (Swizzle<B,4,3>: 128 B rows -> B=3, 64 -> 2, 32 -> 1)
+__device__ __forceinline__ uint32_t swz_off(int r, int j, int rowbytes) {
+    const uint32_t o = (uint32_t)(r * rowbytes + j * 16);
+    const uint32_t mask = (uint32_t)(rowbytes >> 4) - 1u;       // 7, 3, 1
+    return o ^ (((o >> 7) & mask) << 4);
+}
+
 // ---------------------------------------------------------------------------
 // kernel
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(TC_THREADS, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
-               const __grid_constant__ CUtensorMap mapA2, const __grid_constant__ CUtensorMap mapA3,
-               const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TcParams q) {
+conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams q) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ __align__(8) uint64_t add_bar;
+    __shared__ __align__(8) uint64_t part_bar;
     __shared__ uint32_t tmem_base_smem;
     __shared__ uint32_t is_last_smem;
 
@@ -182,16 +238,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     const uint32_t b_bytes_al = (b_bytes + 1023u) & ~1023u;
     const uint32_t stage_bytes = a_bytes + b_bytes_al;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    float* sbias = reinterpret_cast<float*>(smem + q.off_bias);
 
     if (threadIdx.x == 0) {
         DBG_STAMP(0);
-        prefetch_tmap(&mapA0);
-        prefetch_tmap(&mapB);
+        prefetch_tmap(&maps.a[0]);
+        prefetch_tmap(&maps.b);
+        if (q.use_tma_store) prefetch_tmap(&maps.out[phase_idx]);
         for (int s = 0; s < q.stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&accum_bar, 1);
+        mbar_init(&add_bar, 1);
+        mbar_init(&part_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -210,29 +271,49 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
+            const int npre = nkb < q.stages ? nkb : q.stages;
+            // weights do not depend on the previous kernel: fetch them before the grid dependency resolves
+            for (int it = 0; it < npre; ++it) {
+                const int kb = kb_begin + it;
+                const int tap_i = kb / q.kb_per_tap;
+                const int cb = kb - tap_i * q.kb_per_tap;
+                mbar_expect_tx(&full_bar[it], a_bytes + b_bytes);
+                tma_load_2d(&maps.b, &full_bar[it], smem_base + q.off_stage0 + (uint32_t)it * stage_bytes + a_bytes, cb * q.KC,
+                            ph.taps[tap_i].slice * p.Cout + co0);
+            }
+            pdl_wait();
+            pdl_launch_dependents();
             for (int it = 0; it < nkb; ++it) {
                 const int s = it % q.stages;
                 const uint32_t par = (uint32_t)((it / q.stages) & 1);
-                mbar_wait(&empty_bar[s], par ^ 1u);
                 const int kb = kb_begin + it;
                 const int tap_i = kb / q.kb_per_tap;
                 const int cb = kb - tap_i * q.kb_per_tap;
                 const Tap t = ph.taps[tap_i];
-                uint8_t* sa = smem + (size_t)s * stage_bytes;
-                uint8_t* sb = sa + a_bytes;
-                mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
+                if (it >= npre) {
+                    mbar_wait(&empty_bar[s], par ^ 1u);
+                    mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+                    tma_load_2d(&maps.b, &full_bar[s], sa + a_bytes, cb * q.KC, t.slice * p.Cout + co0);
+                }
                 int dy = t.dy, dx = t.dx;
-                const CUtensorMap* mA = &mapA0;
+                const CUtensorMap* mA = &maps.a[0];
                 if (p.s_in == 2) {
                     const int py = dy & 1, px = dx & 1;        // parity view (works for negative offsets)
                     dy = (dy - py) / 2;
                     dx = (dx - px) / 2;
-                    const int v = py * 2 + px;
-                    mA = (v == 0) ? &mapA0 : (v == 1) ? &mapA1 : (v == 2) ? &mapA2 : &mapA3;
+                    mA = &maps.a[py * 2 + px];
                 }
                 tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
-                tma_load_2d(&mapB, &full_bar[s], sb, cb * q.KC, t.slice * p.Cout + co0);
                 if (it == 0) DBG_STAMP(2);
+                if (it == 0 && q.use_tma_add) {
+                    // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
+                    mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
+                    const int cpr = q.add_rowbytes >> 1;
+                    for (int ch = 0; ch < q.add_chunks; ++ch)
+                        tma_load_4d(&maps.add[phase_idx], &add_bar, smem_base + q.off_add + (uint32_t)(ch * TILE_M * q.add_rowbytes),
+                                    co0 + ch * cpr, w0, h0, n0);
+                }
             }
         }
     } else if (warp == 1) {
@@ -246,7 +327,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                 if (it == 0) DBG_STAMP(3);
                 if (it == nkb - 1) DBG_STAMP(4);
                 tc_fence_after();
-                const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
                 const uint32_t sb = sa + a_bytes;
                 const uint64_t adesc = make_smem_desc(sa, q.KC);
                 const uint64_t bdesc = make_smem_desc(sb, q.KC);
@@ -269,22 +350,118 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
         const int n_img = n0 + n_l, hg = h0 + h_l, wg = w0 + w_l;
         const bool row_ok = n_img < p.N;
         const int et = threadIdx.x - 64;         // 0..127
+        const int BN = q.BN;
+
+        // ---- work that does not need the accumulator: overlaps the main loop ----
+        if (et < BN) sbias[et] = p.bias ? __ldg(p.bias + co0 + et) : 0.f;   // parameters: safe before the grid dependency
+        pdl_wait();
+        const size_t pix_off = row_ok ? ((((size_t)n_img * p.Ho + (size_t)(hg * p.s_out + ph.oy)) * p.Wo + (size_t)(wg * p.s_out + ph.ox)) *
+                                         (size_t)p.Cout + (size_t)co0)
+                                      : 0;
+        float xc[16], anc[16];
+        const float* xcur_row = p.has_ddim ? p.ddim.x_cur + pix_off : nullptr;
+        const float* anc_row = p.add_nc ? p.add_nc + (size_t)(row_ok ? n_img : 0) * p.Cout + co0 : nullptr;
+        if (xcur_row && row_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                const float4 t = *reinterpret_cast<const float4*>(xcur_row + j);
+                xc[j] = t.x; xc[j + 1] = t.y; xc[j + 2] = t.z; xc[j + 3] = t.w;
+            }
+        }
+        if (anc_row) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + j));
+                anc[j] = t.x; anc[j + 1] = t.y; anc[j + 2] = t.z; anc[j + 3] = t.w;
+            }
+        }
+        epi_bar();                               // sbias visible to all epilogue threads
 
         mbar_wait(&accum_bar, 0);
         if (et == 0) DBG_STAMP(5);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
+        uint8_t* part = smem + q.off_part;
+        const int pm = (BN >= 32 ? 8 : BN / 4) - 1;       // XOR mask of the private partial-tile layout
+        bool finalize = true;
 
-        if (q.splitk == 1) {
-            for (int c = 0; c < q.BN; c += 16) {
+        if (q.splitk > 1) {
+            // ---- split-K: stage the fp32 partial tile, reduce it into L2 with the copy engine ----
+            for (int c = 0; c < BN; c += 16) {
                 float v[16];
                 tmem_ld16(taddr + (uint32_t)c, v);
-                const int cg = co0 + c;
-                if (p.bias) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] += __ldg(p.bias + cg + j);
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<float4*>(part + (size_t)row * BN * 4 + (size_t)(((c >> 2) + j) ^ (row & pm)) * 16) =
+                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+            fence_async_smem();
+            epi_bar();
+            const size_t tile_lin = ((size_t)phase_idx * gridDim.x + mt) * gridDim.y + blockIdx.y;
+            float* ws_tile = q.ws + tile_lin * (size_t)(TILE_M * BN);
+            const uint32_t tile_bytes = (uint32_t)(TILE_M * BN * 4);
+            if (et == 0) {
+                bulk_reduce_add_f32(ws_tile, smem_u32(part), tile_bytes);
+                bulk_commit();
+                bulk_wait_all();
+                __threadfence();
+                const unsigned int old = atomicAdd(q.counters + tile_lin, 1u);
+                const unsigned int last = (old == (unsigned int)(q.splitk - 1)) ? 1u : 0u;
+                if (last) {
+                    __threadfence();
+                    fence_async_all();
+                    mbar_expect_tx(&part_bar, tile_bytes);
+                    bulk_load(smem_u32(part), ws_tile, tile_bytes, &part_bar);
+                    q.counters[tile_lin] = 0u;
                 }
+                is_last_smem = last;
+            }
+            epi_bar();
+            finalize = is_last_smem != 0;
+            if (finalize) {
+                mbar_wait(&part_bar, 0);
+                // scratch back to zero for the next launch (the tile now lives in shared memory)
+                float4* z = reinterpret_cast<float4*>(ws_tile);
+                for (int i = et; i < TILE_M * BN / 4; i += 128) __stcg(z + i, make_float4(0.f, 0.f, 0.f, 0.f));
+            }
+        }
+
+        if (finalize) {
+            if (q.use_tma_add) mbar_wait(&add_bar, 0);
+            const int out_cpr = q.out_rowbytes / q.out_esz;
+            const int add_cpr = q.add_rowbytes >> 1;
+            for (int c = 0; c < BN; c += 16) {
+                float v[16];
+                if (q.splitk > 1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 t = *reinterpret_cast<const float4*>(part + (size_t)row * BN * 4 + (size_t)(((c >> 2) + j) ^ (row & pm)) * 16);
+                        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+                    }
+                } else {
+                    tmem_ld16(taddr + (uint32_t)c, v);
+                }
+                // prefetch the next chunk's per-row operands
+                float xn_[16], an_[16];
+                const bool more = c + 16 < BN;
+                if (more && xcur_row && row_ok) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const float4 t = *reinterpret_cast<const float4*>(xcur_row + c + 16 + j);
+                        xn_[j] = t.x; xn_[j + 1] = t.y; xn_[j + 2] = t.z; xn_[j + 3] = t.w;
+                    }
+                }
+                if (more && anc_row) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + c + 16 + j));
+                        an_[j] = t.x; an_[j + 1] = t.y; an_[j + 2] = t.z; an_[j + 3] = t.w;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] += sbias[c + j];
                 if (p.stats) {
+                    const int cg = co0 + c;
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         const float x = row_ok ? v[j] : 0.f;
@@ -296,56 +473,91 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
                         }
                     }
                 }
-                if (row_ok) epilogue_row<16>(p, ph, n_img, hg, wg, cg, 16, v);
-            }
-        } else {
-            // ---- split-K: RED partials into the workspace; last CTA finishes the tile ----
-            const size_t tile_rows = (size_t)(phase_idx * gridDim.x + mt) * TILE_M;
-            float* wrow = q.ws + (tile_rows + row) * (size_t)p.Cout + co0;
-            for (int c = 0; c < q.BN; c += 16) {
-                float v[16];
-                tmem_ld16(taddr + (uint32_t)c, v);
 #pragma unroll
-                for (int j = 0; j < 16; ++j) atomicAdd(wrow + c + j, v[j]);
-            }
-            __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            unsigned int* ctr = q.counters + ((size_t)phase_idx * gridDim.x + mt) * gridDim.y + blockIdx.y;
-            if (et == 0) {
-                const unsigned int old = atomicAdd(ctr, 1u);
-                is_last_smem = (old == (unsigned int)(q.splitk - 1)) ? 1u : 0u;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (is_last_smem) {
-                __threadfence();
-                for (int c = 0; c < q.BN; c += 16) {
-                    float v[16];
+                for (int j = 0; j < 16; ++j) {
+                    float x = apply_act(v[j], p.act);
+                    if (p.affine) x = x * p.out_scale + p.out_shift;
+                    v[j] = x;
+                }
+                if (anc_row) {
 #pragma unroll
-                    for (int j = 0; j < 16; j += 4) {
-                        const float4 t = __ldcg(reinterpret_cast<const float4*>(wrow + c + j));
-                        v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
-                        __stcg(reinterpret_cast<float4*>(wrow + c + j), make_float4(0.f, 0.f, 0.f, 0.f));
-                    }
-                    const int cg = co0 + c;
-                    if (p.bias) {
+                    for (int j = 0; j < 16; ++j) v[j] += anc[j];
+                }
+                if (q.use_tma_add) {
+                    const uint8_t* ab = smem + q.off_add + (size_t)(c / add_cpr) * TILE_M * q.add_rowbytes;
+                    const int j0 = ((c % add_cpr) * 2) >> 4;
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] += __ldg(p.bias + cg + j);
-                    }
-                    if (p.stats) {
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const uint4 t = *reinterpret_cast<const uint4*>(ab + swz_off(row, j0 + h2, q.add_rowbytes));
+                        const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&t);
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const float x = row_ok ? v[j] : 0.f;
-                            const float s1 = warp_sum(x);
-                            const float s2 = warp_sum(x * x);
-                            if (lane == j) {
-                                atomicAdd(p.stats + cg + j, (double)s1);
-                                atomicAdd(p.stats + p.Cout + cg + j, (double)s2);
-                            }
+                        for (int e = 0; e < 4; ++e) {
+                            const float2 f = __bfloat1622float2(hh[e]);
+                            v[8 * h2 + 2 * e] += f.x; v[8 * h2 + 2 * e + 1] += f.y;
                         }
                     }
-                    if (row_ok) epilogue_row<16>(p, ph, n_img, hg, wg, cg, 16, v);
                 }
-                if (et == 0) *ctr = 0u;
+                if (p.has_ddim && row_ok) {
+                    const DdimP& d = p.ddim;
+                    float xnew[16], x0v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float eps = v[j];
+                        const float dt = d.s1m_t * eps;
+                        const float x0 = (xc[j] - dt) / d.sab_t;
+                        const float dn = d.s1m_n * eps;
+                        xnew[j] = d.sab_n * x0 + dn + d.eta * (dn - dt);
+                        x0v[j] = x0;
+                    }
+                    float* xo = d.x_next + pix_off + c;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(xo + j) = make_float4(xnew[j], xnew[j + 1], xnew[j + 2], xnew[j + 3]);
+                    if (d.x0_pred) {
+                        float* po = d.x0_pred + pix_off + c;
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(po + j) = make_float4(x0v[j], x0v[j + 1], x0v[j + 2], x0v[j + 3]);
+                    }
+                    if (d.x_next_lp) {
+                        uint4 pk[2];
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(xnew[2 * e], xnew[2 * e + 1]);
+                        uint4* lo = reinterpret_cast<uint4*>(d.x_next_lp + pix_off + c);
+                        lo[0] = pk[0]; lo[1] = pk[1];
+                    }
+                }
+                if (q.use_tma_store) {
+                    uint8_t* ob = smem + q.off_out + (size_t)(c / out_cpr) * TILE_M * q.out_rowbytes;
+                    const int j0 = ((c % out_cpr) * q.out_esz) >> 4;
+                    if (q.out_esz == 4) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<float4*>(ob + swz_off(row, j0 + j, q.out_rowbytes)) =
+                                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    } else {
+                        uint4 pk[2];
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0, q.out_rowbytes)) = pk[0];
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, q.out_rowbytes)) = pk[1];
+                    }
+                }
+                if (more) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) { xc[j] = xn_[j]; anc[j] = an_[j]; }
+                }
+            }
+            if (q.use_tma_store) {
+                fence_async_smem();
+                epi_bar();
+                if (et == 0) {
+                    for (int ch = 0; ch < q.out_chunks; ++ch)
+                        tma_store_4d(&maps.out[phase_idx], smem_base + q.off_out + (uint32_t)(ch * TILE_M * q.out_rowbytes),
+                                     co0 + ch * out_cpr, w0, h0, n0);
+                    bulk_commit();
+                    bulk_wait_read();
+                }
             }
         }
         if (et == 0) DBG_STAMP(6);
@@ -366,6 +578,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant_
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
+static int g_pdl = 1;
+static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
 void tc_set_debug(long long* p) { g_dbg = p; }
 
@@ -385,6 +599,16 @@ bool tc_init() {
     if (cudaGetDevice(&dev) == cudaSuccess &&
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
         g_num_sms = sms;
+    // development knobs (tuning sweeps): MSTK_PDL=0 disables programmatic dependent launch,
+    // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
+    if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
+    if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages);
+    cudaError_t ea = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (ea != cudaSuccess) {
+        cuda_fail(ea, "cudaFuncSetAttribute(conv_tc_kernel)");
+        g_tc_state = -1;
+        return false;
+    }
     g_tc_state = 1;
     return true;
 }
@@ -400,16 +624,46 @@ bool conv_tc_supported(const ConvP& p) {
     if (p.Cin % 32 != 0 || p.Cout % 16 != 0) return false;
     if (p.s_in == 2 && ((p.H & 1) || (p.W & 1))) return false;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15)) return false;
+    if ((reinterpret_cast<uintptr_t>(p.y) & 15) || (reinterpret_cast<uintptr_t>(p.add) & 15)) return false;
+    if (p.has_ddim && ((reinterpret_cast<uintptr_t>(p.ddim.x_cur) & 15) || (reinterpret_cast<uintptr_t>(p.ddim.x_next) & 15) ||
+                       (reinterpret_cast<uintptr_t>(p.ddim.x_next_lp) & 15) || (reinterpret_cast<uintptr_t>(p.ddim.x0_pred) & 15)))
+        return false;
+    if (p.add_nc && (reinterpret_cast<uintptr_t>(p.add_nc) & 15)) return false;
     return true;
 }
 
 struct TcConfig {
     int Wt, Ht, Nt, tiles_w, tiles_h, tiles_n, KC, BN, kb_per_tap, splitk, stages, tmem_cols;
+    int out_esz, out_rowbytes, out_chunks, add_rowbytes, add_chunks;
+    uint32_t off_part, off_out, off_add, off_bias;
     size_t smem_bytes;
 };
 
+// shared-memory carve-up for a (BN, splitk, stages) choice; fills the offsets and smem_bytes
+static void layout_smem(const ConvP& p, TcConfig& c) {
+    const size_t a_bytes = (size_t)TILE_M * c.KC * 2;
+    const size_t b_bytes = (((size_t)c.BN * c.KC * 2) + 1023) & ~(size_t)1023;
+    const size_t pipe = (a_bytes + b_bytes) * c.stages;
+    c.out_esz = p.out_dtype == MSTK_F32 ? 4 : 2;
+    c.out_rowbytes = c.BN * c.out_esz >= 128 ? 128 : c.BN * c.out_esz;
+    c.out_chunks = c.BN * c.out_esz / c.out_rowbytes;
+    c.add_rowbytes = c.BN * 2 >= 128 ? 128 : c.BN * 2;
+    c.add_chunks = c.BN * 2 / c.add_rowbytes;
+    const size_t part = c.splitk > 1 ? (size_t)TILE_M * c.BN * 4 : 0;
+    const size_t outb = p.y ? (size_t)TILE_M * c.BN * c.out_esz : 0;
+    const size_t addb = p.add ? (size_t)TILE_M * c.BN * 2 : 0;
+    c.off_part = 0;
+    c.off_out = (uint32_t)part;                       // part and out tiles re-use the pipeline stages (main loop is over)
+    size_t main_bytes = pipe > part + outb ? pipe : part + outb;
+    main_bytes = (main_bytes + 1023) & ~(size_t)1023;
+    c.off_add = (uint32_t)main_bytes;
+    c.off_bias = (uint32_t)(main_bytes + addb);
+    c.smem_bytes = main_bytes + addb + (size_t)c.BN * 4 + 1024;   // + alignment slack
+}
+
 static TcConfig choose_config(const ConvP& p) {
     TcConfig c;
+    memset(&c, 0, sizeof(c));
     c.Wt = pow2_divisor(p.Wg, TILE_M);
     c.Ht = pow2_divisor(p.Hg, TILE_M / c.Wt);
     c.Nt = TILE_M / (c.Wt * c.Ht);
@@ -419,51 +673,80 @@ static TcConfig choose_config(const ConvP& p) {
     c.KC = (p.Cin % 64 == 0) ? 64 : 32;
     c.kb_per_tap = p.Cin / c.KC;
     const long long mtiles = (long long)c.tiles_w * c.tiles_h * c.tiles_n * p.nphases;
-    // widest N tile that still yields roughly one CTA per SM
-    int bn = 128;
-    while (bn > 32 && (p.Cout % bn != 0 || mtiles * (p.Cout / bn) < g_num_sms)) bn >>= 1;
-    while (p.Cout % bn != 0) bn >>= 1;       // cout is a multiple of 16
-    c.BN = bn;
-    long long ctas = mtiles * (p.Cout / bn);
-    int min_kb = 1 << 30;
+    int min_kb = 1 << 30, max_kb = 0;
     for (int i = 0; i < p.nphases; ++i) {
         const int kb = p.ph[i].ntaps * c.kb_per_tap;
         if (kb < min_kb) min_kb = kb;
+        if (kb > max_kb) max_kb = kb;
     }
-    int sk = 1;
-    // split K while the grid is under one wave and every split keeps >= 4 k-blocks
-    while (ctas * sk * 2 <= 2 * g_num_sms && min_kb / (sk * 2) >= 4 && sk < 16) sk *= 2;
-    c.splitk = sk;
-    const size_t a_bytes = (size_t)TILE_M * c.KC * 2;
-    const size_t b_bytes = (((size_t)c.BN * c.KC * 2) + 1023) & ~(size_t)1023;
-    const size_t stage = a_bytes + b_bytes;
-    int st = (int)((200 * 1024) / stage);
-    if (st > MAX_STAGES) st = MAX_STAGES;
-    if (st < 2) st = 2;
-    c.stages = st;
-    c.smem_bytes = stage * st + 1024;
+    // cost model (cycles) over (BN, splitk): L2-fed K loop vs MMA floor, wave quantisation, epilogue
+    double best = 1e30;
+    int best_bn = 16, best_sk = 1, best_st = 2;
+    for (int bn = 128; bn >= 16; bn >>= 1) {
+        if (p.Cout % bn != 0) continue;
+        if (g_force_bn && bn != g_force_bn && p.Cout % g_force_bn == 0) continue;
+        for (int sk = 1; sk <= 16; sk <<= 1) {
+            if (sk > min_kb) break;
+            if (g_force_sk && sk != g_force_sk && g_force_sk <= min_kb) continue;
+            if (sk > 1 && bn > 64) continue;          // keep the fp32 partial tile <= 32 KB
+            TcConfig t = c;
+            t.BN = bn; t.splitk = sk;
+            const int kb_cta = (max_kb + sk - 1) / sk;
+            int st = kb_cta < MAX_STAGES ? kb_cta : MAX_STAGES;
+            if (st < 2) st = 2;
+            t.stages = st;
+            layout_smem(p, t);
+            while (t.stages > 3 && t.smem_bytes > 100 * 1024) { --t.stages; layout_smem(p, t); }
+            if (t.smem_bytes > 220 * 1024) continue;
+            int occ = (int)((228 * 1024) / (t.smem_bytes + 1024));
+            if (occ > 4) occ = 4;
+            if (occ < 1) occ = 1;
+            const long long ctas = mtiles * (p.Cout / bn) * sk;
+            const long long slots = (long long)g_num_sms * occ;
+            const long long waves = (ctas + slots - 1) / slots;
+            const double conc = (double)(ctas < slots ? ctas : slots);
+            const double per_sm = conc / g_num_sms < 1.0 ? 1.0 : conc / g_num_sms;
+            double bw = 90.0 / per_sm;                               // bytes/cycle one CTA can pull through its SM
+            if (bw > 6000.0 / conc) bw = 6000.0 / conc;              // L2 cap shared by everyone streaming at once
+            const double stage_b = (double)TILE_M * c.KC * 2 + (double)bn * c.KC * 2;
+            const double t_load = kb_cta * stage_b / bw;
+            const double t_mma = (double)kb_cta * (c.KC / 16) * (bn / 2.0) * per_sm;
+            const double t_k = (t_load > t_mma ? t_load : t_mma) + 900.0;
+            const double t_epi = 500.0 + bn * 14.0 + (sk > 1 ? 1800.0 + bn * 10.0 : 0.0);
+            const double cost = waves * (t_k + t_epi) + 1200.0;
+            if (cost < best) { best = cost; best_bn = bn; best_sk = sk; best_st = t.stages; }
+        }
+    }
+    c.BN = best_bn; c.splitk = best_sk; c.stages = g_force_stages ? g_force_stages : best_st;
+    if (c.stages > MAX_STAGES) c.stages = MAX_STAGES;
+    if (c.stages < 2) c.stages = 2;
+    layout_smem(p, c);
     int cols = 32;
     while (cols < c.BN) cols <<= 1;
     c.tmem_cols = cols;
     return c;
 }
 
+static void ws_sizes(const ConvP& p, const TcConfig& c, size_t* ws, size_t* ctr) {
+    const size_t tiles = (size_t)c.tiles_w * c.tiles_h * c.tiles_n * p.nphases * (size_t)(p.Cout / c.BN);
+    *ws = tiles * TILE_M * (size_t)c.BN * sizeof(float);
+    *ctr = (tiles * sizeof(unsigned int) + 255) & ~(size_t)255;
+}
+
 size_t conv_tc_workspace_bytes(const ConvP& p) {
     if (!tc_init()) return 0;
     const TcConfig c = choose_config(p);
     if (c.splitk == 1) return 0;
-    const size_t mtiles = (size_t)c.tiles_w * c.tiles_h * c.tiles_n * p.nphases;
-    const size_t ws = mtiles * TILE_M * (size_t)p.Cout * sizeof(float);
-    const size_t ctr = mtiles * (size_t)(p.Cout / c.BN) * sizeof(unsigned int);
-    return ws + ((ctr + 255) & ~(size_t)255);
+    size_t ws, ctr;
+    ws_sizes(p, c, &ws, &ctr);
+    return ws + ctr;
 }
 
-static int encode_map(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_bytes,
-                      const cuuint32_t* box, CUtensorMapSwizzle sw) {
+static int encode_map(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
+                      const cuuint64_t* strides_bytes, const cuuint32_t* box, CUtensorMapSwizzle sw) {
     cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_bytes, box,
-                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = g_encode(m, dt, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]", (int)r, rank,
                   (unsigned long long)dims[0], (unsigned long long)dims[1], rank > 2 ? (unsigned long long)dims[2] : 0ull,
@@ -473,31 +756,56 @@ static int encode_map(CUtensorMap* m, const void* base, int rank, const cuuint64
     return MSTK_OK;
 }
 
+static CUtensorMapSwizzle swizzle_for(int rowbytes) {
+    return rowbytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : rowbytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
+// tensor maps of an output-shaped NHWC tensor (y or the residual): one per phase
+static int encode_out_maps(const ConvP& p, const TcConfig& c, const void* base, int esz, int rowbytes, CUtensorMap* maps) {
+    const CUtensorMapDataType dt = esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    for (int i = 0; i < p.nphases; ++i) {
+        const Phase& ph = p.ph[i];
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(base) + ((size_t)ph.oy * p.Wo + ph.ox) * p.Cout * esz;
+        const cuuint64_t s = (cuuint64_t)p.s_out;
+        cuuint64_t dims[4] = {(cuuint64_t)p.Cout, (cuuint64_t)p.Wg, (cuuint64_t)p.Hg, (cuuint64_t)p.N};
+        cuuint64_t strides[3] = {s * p.Cout * esz, s * p.Wo * p.Cout * esz, (cuuint64_t)p.Ho * p.Wo * p.Cout * esz};
+        cuuint32_t box[4] = {(cuuint32_t)(rowbytes / esz), (cuuint32_t)c.Wt, (cuuint32_t)c.Ht, (cuuint32_t)c.Nt};
+        int rc = encode_map(&maps[i], dt, b, 4, dims, strides, box, swizzle_for(rowbytes));
+        if (rc != MSTK_OK) return rc;
+    }
+    for (int i = p.nphases; i < 4; ++i) maps[i] = maps[0];
+    return MSTK_OK;
+}
+
 int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cudaStream_t st) {
     if (!tc_init()) return MSTK_EUNSUPPORTED;
     TcConfig c = choose_config(p);
     TcParams q;
     memset(&q, 0, sizeof(q));
     q.p = p;
-    const size_t mtiles = (size_t)c.tiles_w * c.tiles_h * c.tiles_n * p.nphases;
     if (c.splitk > 1) {
-        const size_t ws = mtiles * TILE_M * (size_t)p.Cout * sizeof(float);
-        const size_t ctr = mtiles * (size_t)(p.Cout / c.BN) * sizeof(unsigned int);
-        if (workspace == nullptr || workspace_bytes < ws + ctr) {
-            c.splitk = 1;   // caller gave no scratch: run un-split (still correct, fewer CTAs)
-        } else {
-            q.ws = reinterpret_cast<float*>(workspace);
-            q.counters = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(workspace) + ws);
-        }
+        size_t ws, ctr;
+        ws_sizes(p, c, &ws, &ctr);
+        MSTK_REQUIRE(workspace != nullptr && workspace_bytes >= ws + ctr,
+                     "conv(tcgen05): split-K needs %zu bytes of zero-initialised workspace (mstk_conv2d_workspace_bytes), got %zu",
+                     ws + ctr, workspace_bytes);
+        MSTK_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "conv(tcgen05): workspace must be 16-byte aligned");
+        q.ws = reinterpret_cast<float*>(workspace);
+        q.counters = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(workspace) + ws);
     }
     q.Wt = c.Wt; q.Ht = c.Ht; q.Nt = c.Nt;
     q.tiles_w = c.tiles_w; q.tiles_h = c.tiles_h; q.tiles_n = c.tiles_n;
     q.dbg = g_dbg;
     q.KC = c.KC; q.BN = c.BN; q.kb_per_tap = c.kb_per_tap; q.splitk = c.splitk; q.stages = c.stages; q.tmem_cols = c.tmem_cols;
+    q.out_esz = c.out_esz; q.out_rowbytes = c.out_rowbytes; q.out_chunks = c.out_chunks;
+    q.add_rowbytes = c.add_rowbytes; q.add_chunks = c.add_chunks;
+    q.use_tma_store = p.y ? 1 : 0;
+    q.use_tma_add = p.add ? 1 : 0;
+    q.off_stage0 = 0; q.off_part = c.off_part; q.off_out = c.off_out; q.off_add = c.off_add; q.off_bias = c.off_bias;
 
     const CUtensorMapSwizzle sw = (c.KC == 64) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    CUtensorMap mA[4], mB;
-    memset(mA, 0, sizeof(mA));
+    TcMaps maps;
+    memset(&maps, 0, sizeof(maps));
     const int s = p.s_in;
     const int nviews = (s == 2) ? 4 : 1;
     for (int v = 0; v < nviews; ++v) {
@@ -506,10 +814,10 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
         cuuint64_t dims[4] = {(cuuint64_t)p.Cin, (cuuint64_t)(p.W / s), (cuuint64_t)(p.H / s), (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)p.Cin * 2 * s, (cuuint64_t)p.W * p.Cin * 2 * s, (cuuint64_t)p.H * p.W * p.Cin * 2};
         cuuint32_t box[4] = {(cuuint32_t)c.KC, (cuuint32_t)c.Wt, (cuuint32_t)c.Ht, (cuuint32_t)c.Nt};
-        int rc = encode_map(&mA[v], base, 4, dims, strides, box, sw);
+        int rc = encode_map(&maps.a[v], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, 4, dims, strides, box, sw);
         if (rc != MSTK_OK) return rc;
     }
-    for (int v = nviews; v < 4; ++v) mA[v] = mA[0];
+    for (int v = nviews; v < 4; ++v) maps.a[v] = maps.a[0];
     {
         int nslices = 0;
         for (int i = 0; i < p.nphases; ++i)
@@ -518,18 +826,35 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
         cuuint64_t dims[2] = {(cuuint64_t)p.Cin, (cuuint64_t)nslices * p.Cout};
         cuuint64_t strides[1] = {(cuuint64_t)p.Cin * 2};
         cuuint32_t box[2] = {(cuuint32_t)c.KC, (cuuint32_t)c.BN};
-        int rc = encode_map(&mB, p.w, 2, dims, strides, box, sw);
+        int rc = encode_map(&maps.b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p.w, 2, dims, strides, box, sw);
         if (rc != MSTK_OK) return rc;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel)");
-        attr_set = true;
+    if (p.y) {
+        int rc = encode_out_maps(p, c, p.y, c.out_esz, c.out_rowbytes, maps.out);
+        if (rc != MSTK_OK) return rc;
+    } else {
+        for (int i = 0; i < 4; ++i) maps.out[i] = maps.a[0];
     }
-    dim3 grid((unsigned)(c.tiles_w * c.tiles_h * c.tiles_n), (unsigned)(p.Cout / c.BN), (unsigned)(p.nphases * c.splitk));
-    conv_tc_kernel<<<grid, TC_THREADS, c.smem_bytes, st>>>(mA[0], mA[1], mA[2], mA[3], mB, q);
-    MSTK_CHECK_LAUNCH("conv_tc launch");
+    if (p.add) {
+        int rc = encode_out_maps(p, c, p.add, 2, c.add_rowbytes, maps.add);
+        if (rc != MSTK_OK) return rc;
+    } else {
+        for (int i = 0; i < 4; ++i) maps.add[i] = maps.a[0];
+    }
+
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(c.tiles_w * c.tiles_h * c.tiles_n), (unsigned)(p.Cout / c.BN), (unsigned)(p.nphases * c.splitk));
+    cfg.blockDim = dim3(TC_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = c.smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_tc_kernel, maps, q);
+    if (e != cudaSuccess) return cuda_fail(e, "conv_tc launch");
     return MSTK_OK;
 }
 
