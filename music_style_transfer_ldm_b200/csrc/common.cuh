@@ -91,6 +91,8 @@ bool conv_tc_supported(const ConvP& p);
 size_t conv_tc_workspace_bytes(const ConvP& p);
 bool tc_init();
 void tc_set_debug(long long* p);
+void tc_set_force(int bn, int sk, int stages, int pdl);
+const int* tc_last_config();
 
 // ---------------------------------------------------------------------------
 // small device helpers

@@ -97,6 +97,10 @@ const char* mstk_last_error(void) { return mstk::last_error(); }
 int mstk_tcgen05_available(void) { return mstk::tc_init() ? 1 : 0; }
 /* development aid (not in mstk.h): CTA (0,0,0) of every tcgen05 conv launch writes 8 clock64 stamps here */
 int mstk_debug_tc_timeline(long long* dev_buf) { mstk::tc_set_debug(dev_buf); return MSTK_OK; }
+/* development aids (not in mstk.h): override the tile heuristic (0 = heuristic; pdl < 0 = keep) and read back
+ * {BN, splitk, stages, smem, grid.x, grid.y, grid.z, KC} of the most recent tcgen05 launch */
+int mstk_debug_tc_force(int bn, int sk, int stages, int pdl) { mstk::tc_set_force(bn, sk, stages, pdl); return MSTK_OK; }
+const int* mstk_debug_tc_last_config(void) { return mstk::tc_last_config(); }
 
 int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     mstk::ConvP p;

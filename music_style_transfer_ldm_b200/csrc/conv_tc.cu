@@ -202,8 +202,22 @@ __device__ __forceinline__ uint32_t swz_off(int r, int j, int rowbytes) {
 // ---------------------------------------------------------------------------
 // kernel
 // ---------------------------------------------------------------------------
+// Feature flags: the kernel is instantiated per feature set so that each instance's epilogue is a
+// few hundred instructions (the all-in-one version was ~4000 SASS instructions = 64 KB of code and
+// the epilogue ran at instruction-fetch speed).  A flag that is set still honours the run-time
+// argument; a flag that is clear compiles the feature out.
+enum : uint32_t { F_SPLITK = 1, F_STATS = 2, F_ADDNC = 4, F_ADD = 8, F_DDIM = 16, F_STORE = 32, F_ACTGEN = 64, F_ALL = 127 };
+
+template <uint32_t F>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams q) {
+    const bool f_split = (F & F_SPLITK) && q.splitk > 1;
+    const bool f_stats = (F & F_STATS) && q.p.stats != nullptr;
+    const bool f_addnc = (F & F_ADDNC) && q.p.add_nc != nullptr;
+    const bool f_add = (F & F_ADD) && q.use_tma_add;
+    const bool f_ddim = (F & F_DDIM) && q.p.has_ddim;
+    const bool f_store = (F & F_STORE) && q.use_tma_store;
+    const bool f_actgen = (F & F_ACTGEN) != 0;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
@@ -245,7 +259,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
         DBG_STAMP(0);
         prefetch_tmap(&maps.a[0]);
         prefetch_tmap(&maps.b);
-        if (q.use_tma_store) prefetch_tmap(&maps.out[phase_idx]);
+        if (f_store) prefetch_tmap(&maps.out[phase_idx]);
         for (int s = 0; s < q.stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -306,7 +320,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 }
                 tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
                 if (it == 0) DBG_STAMP(2);
-                if (it == 0 && q.use_tma_add) {
+                if (it == 0 && f_add) {
                     // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
                     mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
                     const int cpr = q.add_rowbytes >> 1;
@@ -359,8 +373,8 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                                          (size_t)p.Cout + (size_t)co0)
                                       : 0;
         float xc[16], anc[16];
-        const float* xcur_row = p.has_ddim ? p.ddim.x_cur + pix_off : nullptr;
-        const float* anc_row = p.add_nc ? p.add_nc + (size_t)(row_ok ? n_img : 0) * p.Cout + co0 : nullptr;
+        const float* xcur_row = f_ddim ? p.ddim.x_cur + pix_off : nullptr;
+        const float* anc_row = f_addnc ? p.add_nc + (size_t)(row_ok ? n_img : 0) * p.Cout + co0 : nullptr;
         if (xcur_row && row_ok) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
@@ -385,7 +399,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
         const int pm = (BN >= 32 ? 8 : BN / 4) - 1;       // XOR mask of the private partial-tile layout
         bool finalize = true;
 
-        if (q.splitk > 1) {
+        if (f_split) {
             // ---- split-K: stage the fp32 partial tile, reduce it into L2 with the copy engine ----
             for (int c = 0; c < BN; c += 16) {
                 float v[16];
@@ -397,6 +411,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
             }
             fence_async_smem();
             epi_bar();
+            if (et == 0) DBG_STAMP(8);
             const size_t tile_lin = ((size_t)phase_idx * gridDim.x + mt) * gridDim.y + blockIdx.y;
             float* ws_tile = q.ws + tile_lin * (size_t)(TILE_M * BN);
             const uint32_t tile_bytes = (uint32_t)(TILE_M * BN * 4);
@@ -415,6 +430,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                     q.counters[tile_lin] = 0u;
                 }
                 is_last_smem = last;
+                DBG_STAMP(9);
             }
             epi_bar();
             finalize = is_last_smem != 0;
@@ -423,16 +439,17 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 // scratch back to zero for the next launch (the tile now lives in shared memory)
                 float4* z = reinterpret_cast<float4*>(ws_tile);
                 for (int i = et; i < TILE_M * BN / 4; i += 128) __stcg(z + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                if (et == 0) DBG_STAMP(10);
             }
         }
 
         if (finalize) {
-            if (q.use_tma_add) mbar_wait(&add_bar, 0);
+            if (f_add) mbar_wait(&add_bar, 0);
             const int out_cpr = q.out_rowbytes / q.out_esz;
             const int add_cpr = q.add_rowbytes >> 1;
             for (int c = 0; c < BN; c += 16) {
                 float v[16];
-                if (q.splitk > 1) {
+                if (f_split) {
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const float4 t = *reinterpret_cast<const float4*>(part + (size_t)row * BN * 4 + (size_t)(((c >> 2) + j) ^ (row & pm)) * 16);
@@ -441,6 +458,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 } else {
                     tmem_ld16(taddr + (uint32_t)c, v);
                 }
+                if (c == 0 && et == 0) DBG_STAMP(13);
                 // prefetch the next chunk's per-row operands
                 float xn_[16], an_[16];
                 const bool more = c + 16 < BN;
@@ -460,7 +478,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 }
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] += sbias[c + j];
-                if (p.stats) {
+                if (f_stats) {
                     const int cg = co0 + c;
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
@@ -475,15 +493,21 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 }
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    float x = apply_act(v[j], p.act);
-                    if (p.affine) x = x * p.out_scale + p.out_shift;
+                    float x = v[j];
+                    if (f_actgen) {
+                        x = apply_act(x, p.act);
+                        if (p.affine) x = x * p.out_scale + p.out_shift;
+                    } else if (p.act == MSTK_ACT_RELU) {
+                        x = fmaxf(x, 0.f);
+                    }
                     v[j] = x;
                 }
+                if (c == 0 && et == 0) DBG_STAMP(14);
                 if (anc_row) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] += anc[j];
                 }
-                if (q.use_tma_add) {
+                if (f_add) {
                     const uint8_t* ab = smem + q.off_add + (size_t)(c / add_cpr) * TILE_M * q.add_rowbytes;
                     const int j0 = ((c % add_cpr) * 2) >> 4;
 #pragma unroll
@@ -497,7 +521,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                         }
                     }
                 }
-                if (p.has_ddim && row_ok) {
+                if (f_ddim && row_ok) {
                     const DdimP& d = p.ddim;
                     float xnew[16], x0v[16];
 #pragma unroll
@@ -526,7 +550,7 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                         lo[0] = pk[0]; lo[1] = pk[1];
                     }
                 }
-                if (q.use_tma_store) {
+                if (f_store) {
                     uint8_t* ob = smem + q.off_out + (size_t)(c / out_cpr) * TILE_M * q.out_rowbytes;
                     const int j0 = ((c % out_cpr) * q.out_esz) >> 4;
                     if (q.out_esz == 4) {
@@ -543,15 +567,18 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                         *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, q.out_rowbytes)) = pk[1];
                     }
                 }
+                if (c == 0 && et == 0) DBG_STAMP(15);
                 if (more) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) { xc[j] = xn_[j]; anc[j] = an_[j]; }
                 }
             }
-            if (q.use_tma_store) {
+            if (et == 0) DBG_STAMP(11);
+            if (f_store) {
                 fence_async_smem();
                 epi_bar();
                 if (et == 0) {
+                    DBG_STAMP(12);
                     for (int ch = 0; ch < q.out_chunks; ++ch)
                         tma_store_4d(&maps.out[phase_idx], smem_base + q.off_out + (uint32_t)(ch * TILE_M * q.out_rowbytes),
                                      co0 + ch * out_cpr, w0, h0, n0);
@@ -575,6 +602,20 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
+typedef void (*TcKernel)(const TcMaps, const TcParams);
+struct TcVariant { uint32_t flags; TcKernel fn; };
+#define TCV(f) {(f), conv_tc_kernel<(f)>}
+static const TcVariant kVariants[] = {
+    TCV(F_STORE), TCV(F_STORE | F_SPLITK),                                   // bias (+ReLU): most layers
+    TCV(F_STORE | F_ADDNC), TCV(F_STORE | F_ADDNC | F_SPLITK),               // + time embedding (UNet enc2)
+    TCV(F_STORE | F_ADD), TCV(F_STORE | F_ADD | F_SPLITK),                   // + skip connection (UNet dec2..4)
+    TCV(F_DDIM), TCV(F_DDIM | F_SPLITK), TCV(F_DDIM | F_STORE),              // fused DDIM update (UNet dec1)
+    TCV(F_STORE | F_STATS), TCV(F_STORE | F_STATS | F_SPLITK),               // BatchNorm statistics (VAE, train mode)
+    TCV(F_STORE | F_ACTGEN),                                                 // tanh / affine epilogues
+    TCV(F_ALL),                                                              // anything else
+};
+static const int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
+
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
@@ -582,6 +623,12 @@ static int g_pdl = 1;
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
 void tc_set_debug(long long* p) { g_dbg = p; }
+void tc_set_force(int bn, int sk, int stages, int pdl) {
+    g_force_bn = bn; g_force_sk = sk; g_force_stages = stages;
+    if (pdl >= 0) g_pdl = pdl;
+}
+static int g_last_cfg[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+const int* tc_last_config() { return g_last_cfg; }
 
 bool tc_init() {
     if (g_tc_state != 0) return g_tc_state > 0;
@@ -603,11 +650,13 @@ bool tc_init() {
     // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages);
-    cudaError_t ea = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    if (ea != cudaSuccess) {
-        cuda_fail(ea, "cudaFuncSetAttribute(conv_tc_kernel)");
-        g_tc_state = -1;
-        return false;
+    for (int i = 0; i < kNumVariants; ++i) {
+        cudaError_t ea = cudaFuncSetAttribute(kVariants[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        if (ea != cudaSuccess) {
+            cuda_fail(ea, "cudaFuncSetAttribute(conv_tc_kernel)");
+            g_tc_state = -1;
+            return false;
+        }
     }
     g_tc_state = 1;
     return true;
@@ -842,6 +891,8 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
         for (int i = 0; i < 4; ++i) maps.add[i] = maps.a[0];
     }
 
+    g_last_cfg[0] = c.BN; g_last_cfg[1] = c.splitk; g_last_cfg[2] = c.stages; g_last_cfg[3] = (int)c.smem_bytes;
+    g_last_cfg[4] = c.tiles_w * c.tiles_h * c.tiles_n; g_last_cfg[5] = p.Cout / c.BN; g_last_cfg[6] = p.nphases * c.splitk; g_last_cfg[7] = c.KC;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3((unsigned)(c.tiles_w * c.tiles_h * c.tiles_n), (unsigned)(p.Cout / c.BN), (unsigned)(p.nphases * c.splitk));
@@ -853,7 +904,18 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = g_pdl ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_tc_kernel, maps, q);
+    uint32_t need = 0;
+    if (c.splitk > 1) need |= F_SPLITK;
+    if (p.stats) need |= F_STATS;
+    if (p.add_nc) need |= F_ADDNC;
+    if (p.add) need |= F_ADD;
+    if (p.has_ddim) need |= F_DDIM;
+    if (p.y) need |= F_STORE;
+    if (p.affine || (p.act != MSTK_ACT_NONE && p.act != MSTK_ACT_RELU)) need |= F_ACTGEN;
+    TcKernel fn = kVariants[kNumVariants - 1].fn;
+    for (int i = 0; i < kNumVariants; ++i)
+        if (kVariants[i].flags == need) { fn = kVariants[i].fn; break; }
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fn, maps, q);
     if (e != cudaSuccess) return cuda_fail(e, "conv_tc launch");
     return MSTK_OK;
 }
