@@ -85,6 +85,9 @@ struct ConvP {
 int build_conv_plan(const mstk_conv_args* a, ConvP* p);
 
 int launch_conv_simt(const ConvP& p, cudaStream_t st);
+// HBM-streaming kernels for Cin == 1 (k3) and Cout == 1 (convT k4) layers
+bool conv_edge_supported(const ConvP& p);
+int launch_conv_edge(const ConvP& p, cudaStream_t st);
 // returns MSTK_EUNSUPPORTED when the shape is outside the tcgen05 kernel's domain
 int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cudaStream_t st);
 bool conv_tc_supported(const ConvP& p);

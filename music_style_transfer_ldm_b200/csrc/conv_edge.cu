@@ -1,0 +1,243 @@
+// HBM-streaming kernels for the two degenerate contractions of the hot path, which are
+// bandwidth problems, not MMA problems (the round-1a launch list showed the generic 64x64
+// CUDA-core GEMM tile spending 1.09 ms on a layer whose traffic is worth ~6 us):
+//
+//   conv_cin1_kernel      Conv2d k3 p1 (s1/s2) with Cin == 1: the first layer of the VAE
+//                         encoder (model.py:17), the style encoder (model.py:61) and the VGGish
+//                         stack (vggish.py:108-118).  9 input floats -> Cout outputs per pixel;
+//                         one thread owns 8 consecutive output channels of one pixel, so a warp
+//                         writes 512 contiguous bytes; BatchNorm statistics are reduced in
+//                         registers -> shared memory -> one double atomic per channel and CTA.
+//   convt4_cout1_kernel   ConvTranspose2d k4 s2 p1 with Cout == 1: the last decoder layer
+//                         (model.py:45) + tanh (+ the callers' (y+1)/2).  One thread owns one
+//                         input-grid position = a 2x2 block of output pixels and walks its 3x3
+//                         input neighbourhood with 128-bit loads (neighbouring threads share
+//                         them through L1); weights live in shared memory as fp32.
+#include "common.cuh"
+
+namespace mstk {
+
+struct EdgeP {
+    const void* x; const void* w; const float* bias; void* y; double* stats;
+    int N, H, W, Cin, Cout, Ho, Wo, stride, act, affine, dtype, out_dtype;
+    float out_scale, out_shift;
+};
+
+template <typename TO>
+__global__ void __launch_bounds__(256) conv_cin1_kernel(const EdgeP a) {
+    extern __shared__ float sm[];                 // w[9][Cout], bias[Cout], ssum[Cout], ssq[Cout]
+    float* sw = sm;
+    float* sb = sw + 9 * a.Cout;
+    float* ssum = sb + a.Cout;
+    float* ssq = ssum + a.Cout;
+    const float* __restrict__ wsrc = reinterpret_cast<const float*>(a.w);      // packed [9][Cout][1]
+    for (int i = threadIdx.x; i < 9 * a.Cout; i += blockDim.x) sw[i] = wsrc[i];
+    for (int i = threadIdx.x; i < a.Cout; i += blockDim.x) {
+        sb[i] = a.bias ? a.bias[i] : 0.f;
+        ssum[i] = 0.f; ssq[i] = 0.f;
+    }
+    __syncthreads();
+    const float* __restrict__ X = reinterpret_cast<const float*>(a.x);
+    TO* __restrict__ Y = reinterpret_cast<TO*>(a.y);
+    const int CG = a.Cout >> 3;
+    const size_t items = (size_t)a.N * a.Ho * a.Wo * CG;
+    float s1[8], s2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
+    int cg_prev = -1;
+    for (size_t it = blockIdx.x * (size_t)blockDim.x + threadIdx.x; it < items; it += (size_t)gridDim.x * blockDim.x) {
+        const int cg = (int)(it % CG);
+        size_t pix = it / CG;
+        const int ow = (int)(pix % a.Wo); pix /= a.Wo;
+        const int oh = (int)(pix % a.Ho);
+        const int n = (int)(pix / a.Ho);
+        if (a.stats && cg != cg_prev && cg_prev >= 0) {
+            // the channel group of this thread changed (only when gridDim*blockDim % CG != 0): flush
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                atomicAdd(&ssum[cg_prev * 8 + j], s1[j]); atomicAdd(&ssq[cg_prev * 8 + j], s2[j]);
+                s1[j] = 0.f; s2[j] = 0.f;
+            }
+        }
+        cg_prev = cg;
+        float xin[9];
+        const float* xb = X + (size_t)n * a.H * a.W;
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int ih = oh * a.stride + ky - 1, iw = ow * a.stride + kx - 1;
+                xin[ky * 3 + kx] = (ih >= 0 && ih < a.H && iw >= 0 && iw < a.W) ? __ldg(xb + (size_t)ih * a.W + iw) : 0.f;
+            }
+        float v[8];
+        const int c0 = cg * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = sb[c0 + j];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            const float4 w0 = *reinterpret_cast<const float4*>(sw + t * a.Cout + c0);
+            const float4 w1 = *reinterpret_cast<const float4*>(sw + t * a.Cout + c0 + 4);
+            v[0] = fmaf(xin[t], w0.x, v[0]); v[1] = fmaf(xin[t], w0.y, v[1]); v[2] = fmaf(xin[t], w0.z, v[2]); v[3] = fmaf(xin[t], w0.w, v[3]);
+            v[4] = fmaf(xin[t], w1.x, v[4]); v[5] = fmaf(xin[t], w1.y, v[5]); v[6] = fmaf(xin[t], w1.z, v[6]); v[7] = fmaf(xin[t], w1.w, v[7]);
+        }
+        if (a.stats) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { s1[j] += v[j]; s2[j] = fmaf(v[j], v[j], s2[j]); }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float x = apply_act(v[j], a.act);
+            if (a.affine) x = x * a.out_scale + a.out_shift;
+            v[j] = x;
+        }
+        const size_t off = ((((size_t)n * a.Ho + oh) * a.Wo + ow) * a.Cout) + c0;
+        if (sizeof(TO) == 4) {
+            float4* o = reinterpret_cast<float4*>(Y + off);
+            o[0] = make_float4(v[0], v[1], v[2], v[3]);
+            o[1] = make_float4(v[4], v[5], v[6], v[7]);
+        } else {
+            uint4 pk;
+            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            *reinterpret_cast<uint4*>(Y + off) = pk;
+        }
+    }
+    if (a.stats) {
+        if (cg_prev >= 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { atomicAdd(&ssum[cg_prev * 8 + j], s1[j]); atomicAdd(&ssq[cg_prev * 8 + j], s2[j]); }
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < a.Cout; c += blockDim.x) {
+            atomicAdd(a.stats + c, (double)ssum[c]);
+            atomicAdd(a.stats + a.Cout + c, (double)ssq[c]);
+        }
+    }
+}
+
+template <typename T> __device__ __forceinline__ void load8(const T* p, float (&o)[8]);
+template <> __device__ __forceinline__ void load8<float>(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&o)[8]) {
+    const uint4 q = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(h[e]); o[2 * e] = f.x; o[2 * e + 1] = f.y; }
+}
+
+// x [N,H,W,Cin] (T), w packed [16][1][Cin] (T), y [N,2H,2W,1] (TO)
+template <typename T, typename TO>
+__global__ void __launch_bounds__(128) convt4_cout1_kernel(const EdgeP a) {
+    extern __shared__ float sw[];                 // [16][Cin] fp32
+    const T* __restrict__ wsrc = reinterpret_cast<const T*>(a.w);
+    for (int i = threadIdx.x; i < 16 * a.Cin; i += blockDim.x) sw[i] = to_f(wsrc[i]);
+    __syncthreads();
+    const T* __restrict__ X = reinterpret_cast<const T*>(a.x);
+    TO* __restrict__ Y = reinterpret_cast<TO*>(a.y);
+    const float b0 = a.bias ? a.bias[0] : 0.f;
+    const size_t items = (size_t)a.N * a.H * a.W;
+    for (size_t it = blockIdx.x * (size_t)blockDim.x + threadIdx.x; it < items; it += (size_t)gridDim.x * blockDim.x) {
+        const int w = (int)(it % a.W);
+        const int h = (int)((it / a.W) % a.H);
+        const int n = (int)(it / ((size_t)a.W * a.H));
+        float acc[2][2] = {{b0, b0}, {b0, b0}};
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy) {
+            const int ih = h + dy;
+            if (ih < 0 || ih >= a.H) continue;
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+                const int iw = w + dx;
+                if (iw < 0 || iw >= a.W) continue;
+                const T* xp = X + (((size_t)n * a.H + ih) * a.W + iw) * a.Cin;
+                for (int c = 0; c < a.Cin; c += 8) {
+                    float xv[8];
+                    load8<T>(xp + c, xv);
+                    // phase py receives this row through kernel row ky = py + 1 - 2*dy (valid iff 0 <= ky < 4)
+#pragma unroll
+                    for (int py = 0; py < 2; ++py) {
+                        const int ky = py + 1 - 2 * dy;
+                        if (ky < 0 || ky > 3) continue;
+#pragma unroll
+                        for (int px = 0; px < 2; ++px) {
+                            const int kx = px + 1 - 2 * dx;
+                            if (kx < 0 || kx > 3) continue;
+                            const float* wr = sw + (ky * 4 + kx) * a.Cin + c;
+                            const float4 w0 = *reinterpret_cast<const float4*>(wr), w1 = *reinterpret_cast<const float4*>(wr + 4);
+                            float s = acc[py][px];
+                            s = fmaf(xv[0], w0.x, s); s = fmaf(xv[1], w0.y, s); s = fmaf(xv[2], w0.z, s); s = fmaf(xv[3], w0.w, s);
+                            s = fmaf(xv[4], w1.x, s); s = fmaf(xv[5], w1.y, s); s = fmaf(xv[6], w1.z, s); s = fmaf(xv[7], w1.w, s);
+                            acc[py][px] = s;
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int py = 0; py < 2; ++py) {
+            float o[2];
+#pragma unroll
+            for (int px = 0; px < 2; ++px) {
+                float x = apply_act(acc[py][px], a.act);
+                if (a.affine) x = x * a.out_scale + a.out_shift;
+                o[px] = x;
+            }
+            const size_t off = ((size_t)n * a.Ho + (2 * h + py)) * a.Wo + 2 * w;
+            if (sizeof(TO) == 4) *reinterpret_cast<float2*>(Y + off) = make_float2(o[0], o[1]);
+            else *reinterpret_cast<__nv_bfloat162*>(Y + off) = __floats2bfloat162_rn(o[0], o[1]);
+        }
+    }
+}
+
+static EdgeP make_edge(const ConvP& p) {
+    EdgeP a;
+    a.x = p.x; a.w = p.w; a.bias = p.bias; a.y = p.y; a.stats = p.stats;
+    a.N = p.N; a.H = p.H; a.W = p.W; a.Cin = p.Cin; a.Cout = p.Cout; a.Ho = p.Ho; a.Wo = p.Wo;
+    a.stride = p.s_in; a.act = p.act; a.affine = p.affine; a.dtype = p.dtype; a.out_dtype = p.out_dtype;
+    a.out_scale = p.out_scale; a.out_shift = p.out_shift;
+    return a;
+}
+
+bool conv_edge_supported(const ConvP& p) {
+    if (p.add || p.add_nc || p.has_ddim || !p.y) return false;
+    if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15)) return false;
+    if (p.nphases == 1 && p.Cin == 1 && p.ph[0].ntaps == 9 && p.dtype == MSTK_F32 && (p.Cout % 8) == 0 && p.Cout <= 1024) return true;
+    if (p.nphases == 4 && p.ph[3].ntaps == 4 && p.ph[0].ntaps == 4 && p.Cout == 1 && (p.Cin % 8) == 0 && p.Cin <= 512 && !p.stats) return true;
+    return false;
+}
+
+int launch_conv_edge(const ConvP& p, cudaStream_t st) {
+    const EdgeP a = make_edge(p);
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (p.nphases == 1) {
+        const size_t items = (size_t)p.N * p.Ho * p.Wo * (p.Cout / 8);
+        size_t blocks = (items + 255) / 256;
+        // 256 threads: a thread keeps its channel group across the grid-stride loop whenever Cout/8 divides 256
+        const size_t cap = (size_t)sms * 8;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        const size_t smem = (size_t)(9 + 3) * p.Cout * sizeof(float);
+        if (p.out_dtype == MSTK_F32) conv_cin1_kernel<float><<<(unsigned)blocks, 256, smem, st>>>(a);
+        else conv_cin1_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, smem, st>>>(a);
+        MSTK_CHECK_LAUNCH("conv_cin1 launch");
+    } else {
+        const size_t items = (size_t)p.N * p.H * p.W;
+        size_t blocks = (items + 127) / 128;
+        const size_t cap = (size_t)sms * 16;
+        if (blocks > cap) blocks = cap;
+        const size_t smem = (size_t)16 * p.Cin * sizeof(float);
+        const bool xf = p.dtype == MSTK_F32, of = p.out_dtype == MSTK_F32;
+        if (xf && of) convt4_cout1_kernel<float, float><<<(unsigned)blocks, 128, smem, st>>>(a);
+        else if (xf) convt4_cout1_kernel<float, __nv_bfloat16><<<(unsigned)blocks, 128, smem, st>>>(a);
+        else if (of) convt4_cout1_kernel<__nv_bfloat16, float><<<(unsigned)blocks, 128, smem, st>>>(a);
+        else convt4_cout1_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)blocks, 128, smem, st>>>(a);
+        MSTK_CHECK_LAUNCH("convt4_cout1 launch");
+    }
+    return MSTK_OK;
+}
+
+}  // namespace mstk

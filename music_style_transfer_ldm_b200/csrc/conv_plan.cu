@@ -108,8 +108,10 @@ int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     if (rc != MSTK_OK) return rc;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int backend = a->backend;
-    if (backend == MSTK_BACKEND_AUTO)
+    if (backend == MSTK_BACKEND_AUTO) {
+        if (mstk::conv_edge_supported(p)) return mstk::launch_conv_edge(p, st);
         backend = mstk::conv_tc_supported(p) ? MSTK_BACKEND_TCGEN05 : MSTK_BACKEND_SIMT;
+    }
     if (backend == MSTK_BACKEND_TCGEN05) {
         if (!mstk::conv_tc_supported(p)) {
             mstk::set_error("conv: tcgen05 backend requested but shape unsupported (dtype=%d cin=%d cout=%d hg=%d wg=%d)",

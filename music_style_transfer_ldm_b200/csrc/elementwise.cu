@@ -170,36 +170,61 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
 // ---------------------------------------------------------------------------
 // time embedding MLP: one CTA per sample, `dim` threads
 // ---------------------------------------------------------------------------
-__global__ void time_embed_kernel(const float* __restrict__ t, const float* __restrict__ w1, const float* __restrict__ b1,
+// TE_SPB samples per CTA; each Linear's weight matrix is staged once per CTA in shared memory
+// with coalesced reads ([dim][dim+1] padding: thread i then walks row i conflict-free).
+constexpr int TE_SPB = 16;
+__global__ void time_embed_kernel(const float* __restrict__ t, int nb, const float* __restrict__ w1, const float* __restrict__ b1,
                                   const float* __restrict__ w2, const float* __restrict__ b2, float* __restrict__ out, int dim) {
-    extern __shared__ float sm[];   // e[dim], h[dim]
-    float* e = sm;
-    float* h = sm + dim;
-    const int b = blockIdx.x, i = threadIdx.x;
+    extern __shared__ float sm[];   // ws[dim][dim+1], e[TE_SPB][dim], h[TE_SPB][dim]
+    float* ws = sm;
+    float* e = ws + (size_t)dim * (dim + 1);
+    float* h = e + TE_SPB * dim;
+    const int i = threadIdx.x;
+    const int s0 = blockIdx.x * TE_SPB;
+    const int ns = min(TE_SPB, nb - s0);
     const int half = dim / 2;
-    const float tv = t[b];
+    for (int idx = i; idx < dim * dim; idx += dim) ws[(idx / dim) * (dim + 1) + (idx % dim)] = w1[idx];
     {
         const int k = i < half ? i : i - half;
         // torch: exp(arange(half) * -(log(10000)/(half-1))) in fp32
         const float coef = -(float)(log(10000.0) / (double)(half - 1));
         const float fr = (float)exp((double)((float)k * coef));
-        const float arg = tv * fr;
-        e[i] = i < half ? sinf(arg) : cosf(arg);
+        for (int s = 0; s < ns; ++s) {
+            const float arg = t[s0 + s] * fr;
+            e[s * dim + i] = i < half ? sinf(arg) : cosf(arg);
+        }
     }
     __syncthreads();
     {
-        float acc = b1[i];
-        const float* wr = w1 + (size_t)i * dim;
-        for (int k = 0; k < dim; ++k) acc = fmaf(e[k], wr[k], acc);
+        float acc[TE_SPB];
+        const float bb = b1[i];
+#pragma unroll
+        for (int s = 0; s < TE_SPB; ++s) acc[s] = bb;
+        const float* wr = ws + (size_t)i * (dim + 1);
+        for (int k = 0; k < dim; ++k) {
+            const float w = wr[k];
+#pragma unroll
+            for (int s = 0; s < TE_SPB; ++s) acc[s] = fmaf(e[s * dim + k], w, acc[s]);
+        }
         // exact GELU (nn.GELU default): 0.5 x (1 + erf(x / sqrt(2)))
-        h[i] = 0.5f * acc * (1.f + erff(acc * 0.70710678118654752440f));
+#pragma unroll
+        for (int s = 0; s < TE_SPB; ++s) h[s * dim + i] = 0.5f * acc[s] * (1.f + erff(acc[s] * 0.70710678118654752440f));
     }
     __syncthreads();
+    for (int idx = i; idx < dim * dim; idx += dim) ws[(idx / dim) * (dim + 1) + (idx % dim)] = w2[idx];
+    __syncthreads();
     {
-        float acc = b2[i];
-        const float* wr = w2 + (size_t)i * dim;
-        for (int k = 0; k < dim; ++k) acc = fmaf(h[k], wr[k], acc);
-        out[(size_t)b * dim + i] = acc;
+        float acc[TE_SPB];
+        const float bb = b2[i];
+#pragma unroll
+        for (int s = 0; s < TE_SPB; ++s) acc[s] = bb;
+        const float* wr = ws + (size_t)i * (dim + 1);
+        for (int k = 0; k < dim; ++k) {
+            const float w = wr[k];
+#pragma unroll
+            for (int s = 0; s < TE_SPB; ++s) acc[s] = fmaf(h[s * dim + k], w, acc[s]);
+        }
+        for (int s = 0; s < ns; ++s) out[(size_t)(s0 + s) * dim + i] = acc[s];
     }
 }
 
@@ -497,7 +522,15 @@ int mstk_time_embed(const float* t, int b, const float* w1, const float* b1, con
                     void* stream) {
     MSTK_REQUIRE(t && w1 && b1 && w2 && b2 && out && b > 0, "time_embed: null");
     MSTK_REQUIRE(dim >= 4 && dim <= 1024 && (dim % 2) == 0, "time_embed: bad dim");
-    time_embed_kernel<<<b, dim, 2 * dim * sizeof(float), (cudaStream_t)stream>>>(t, w1, b1, w2, b2, out, dim);
+    MSTK_REQUIRE(dim <= 192, "time_embed: dim %d too large for the shared-memory weight tile", dim);
+    const size_t smem = ((size_t)dim * (dim + 1) + 2 * TE_SPB * dim) * sizeof(float);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(time_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return cuda_fail(e, "time_embed smem attr");
+        smem_set = smem;
+    }
+    time_embed_kernel<<<(b + TE_SPB - 1) / TE_SPB, dim, smem, (cudaStream_t)stream>>>(t, b, w1, b1, w2, b2, out, dim);
     MSTK_CHECK_LAUNCH("time_embed");
     return MSTK_OK;
 }
