@@ -222,6 +222,95 @@ typedef struct mstk_mel_args {
 size_t mstk_mel_workspace_bytes(int b, int len, int n_mels);
 int mstk_mel_frontend(const mstk_mel_args* a, void* stream);
 
+/* ==============================================================================
+ * Backward pass and optimizer of the training step (models/train.py:163-208).  The
+ * reference gets these from autograd + torch.optim.Adam; here every gradient op is an
+ * explicit kernel so that the whole step is one graph-capturable stream of launches.
+ * Data gradients of the contractions re-use mstk_conv2d_fwd on a re-packed weight
+ * (conv s2 <-> conv-transpose s2; stride-1 convs and nn.Linear through the dgrad pack).
+ * ============================================================================== */
+
+/* Conv2d / Linear weight [cout,cin,k,k] fp32 -> [k*k][cin][cout] in `dtype`, taps flipped:
+ * the packed weight of the stride-1 convolution (k3 p1, or k1) that maps dL/dy to dL/dx. */
+int mstk_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int cout, int cin, int k, int dtype, void* stream);
+
+/* Weight gradient of the convolution family: for every kernel tap,
+ *   dW[tap][co][ci] += sum over pixels of dy[out pixel, co] * x[in pixel shifted by tap, ci],
+ * accumulated (atomically, fp32) straight into the gradient tensor in the PARAMETER's own
+ * layout: [cout][cin][k][k] for Conv2d / Linear, [cin][cout][k][k] for ConvTranspose2d.
+ * Geometry arguments are those of the FORWARD call (mstk_conv_args). */
+typedef struct mstk_wgrad_args {
+    const void* x;        /* [n,h,w,cin] forward input, x_dtype                          */
+    const void* dy;       /* [n,ho,wo,cout] gradient w.r.t. the conv output, dy_dtype    */
+    float* dw;            /* fp32 parameter-layout gradient, caller zeroes it per step   */
+    int32_t n, h, w, cin, cout, ksize, stride, transposed;
+    int32_t x_dtype, dy_dtype;
+} mstk_wgrad_args;
+int mstk_conv2d_wgrad(const mstk_wgrad_args* a, void* stream);
+
+/* Activation backward + bias gradient in one streaming pass over [rows, c]:
+ *   g = (dy [+ dy2]) * act'(.) * y_scale ;  dbias[c] += column sums of g
+ * act' comes from the saved forward OUTPUT y: ReLU -> (y > 0); tanh -> 1 - t^2 with
+ * t = (y - y_shift) / y_scale (the forward's fused out_scale/out_shift); NONE -> 1. */
+typedef struct mstk_act_bwd_args {
+    const void* dy; const void* dy2;   /* dy2 optional (skip-connection gradient), same dtype */
+    const void* y;                      /* forward output (ignored for MSTK_ACT_NONE)          */
+    void* g;                            /* may be NULL when only dbias is wanted               */
+    float* dbias;                       /* optional [c], accumulated                           */
+    int64_t rows; int32_t c;
+    int32_t act; float y_scale, y_shift;
+    int32_t dy_dtype, y_dtype, g_dtype;
+} mstk_act_bwd_args;
+int mstk_act_bwd(const mstk_act_bwd_args* a, void* stream);
+
+/* BatchNorm2d (training mode) backward, two passes over v = the conv output that fed the
+ * norm: (1) sums[0:c] = sum g, sums[c:2c] = sum g*xhat with g = dy * (relu mask of the
+ * recomputed output); all-reduce `sums` across ranks here under data parallelism;
+ * (2) dv = gamma*invstd*(g - sums0/count - xhat*sums1/count), dgamma += sums1, dbeta += sums0. */
+typedef struct mstk_bn_bwd_args {
+    const void* dy; const void* v; void* dv;
+    const float* mean; const float* invstd; const float* gamma; const float* beta;
+    double* sums;            /* [2*c], zeroed by the caller before pass 1 */
+    float* dgamma; float* dbeta;
+    int64_t rows;            /* local rows */
+    int64_t count;           /* global rows (= rows * world size) */
+    int32_t c, act, dy_dtype, v_dtype, dv_dtype;
+} mstk_bn_bwd_args;
+int mstk_bn_bwd_reduce(const mstk_bn_bwd_args* a, void* stream);
+int mstk_bn_bwd_apply(const mstk_bn_bwd_args* a, void* stream);
+
+/* Cross-attention core backward (recomputes the probabilities): given d_out [b,l,e],
+ * writes dq [b,l,e], dk and dv [b,s,e] (strides as in mstk_attn_args; dk/dv may be the two
+ * halves of one [b,s,2e] buffer). */
+typedef struct mstk_attn_bwd_args {
+    const void* q; const void* k; const void* v; const void* d_out;
+    void* dq; void* dk; void* dv;
+    int32_t b, l, s, e, heads;
+    int32_t q_stride, k_stride, v_stride, do_stride, dq_stride, dk_stride, dv_stride;
+    int32_t dtype;
+} mstk_attn_bwd_args;
+int mstk_attention_bwd(const mstk_attn_bwd_args* a, void* stream);
+
+/* time MLP with the intermediates the backward needs (e = sinusoid, pre = Linear1 output) */
+int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2,
+                          float* out, float* e_out, float* pre_out, int dim, void* stream);
+/* dpre = dh * gelu'(pre) (exact erf GELU), fp32 */
+int mstk_gelu_bwd(const float* dh, const float* pre, float* dpre, size_t count, void* stream);
+/* out[b, c] = sum over hw of (a[b,hw,c] + a2[b,hw,c]) ; a2 optional; fp32 out */
+int mstk_sum_hw(const void* a, const void* a2, int dtype, int b, int64_t hw, int c, float* out, void* stream);
+/* out = y + add (same shape, optional) + add_nc[n, c] (optional): the un-fused form of the conv epilogue adds,
+ * used in training where the pre-add ReLU output must be kept for the mask */
+int mstk_add_bcast(const void* y, const void* add, const float* add_nc, void* out, int n, int64_t hw, int c, int dtype, void* stream);
+/* g = scale * (a - b), a and b fp32, g in g_dtype: gradient of mean((a-b)^2) with scale = 2*w/count */
+int mstk_mse_grad(const float* a, const float* b, float scale, void* g, int g_dtype, size_t count, void* stream);
+/* gradient w.r.t. eps_hat of  w_d*mean((eps_hat-eps)^2) + L(x0_pred(eps_hat)):
+ *   g = scale_d*(eps_hat - eps) - sqrt(1-ab[t])/sqrt(ab[t]) * dx0      (model.py:117-124, loss.py:48) */
+int mstk_eps_grad(const void* dx0, int dx0_dtype, const float* eps_hat, const float* eps, const float* alpha_bar, const int64_t* t,
+                  float scale_d, void* g, int g_dtype, int b, int64_t inner, void* stream);
+/* torch.optim.Adam (no amsgrad, no weight decay) over a flat fp32 arena; `step` is the 1-based step count */
+int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
+                   int64_t step, float grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

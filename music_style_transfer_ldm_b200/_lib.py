@@ -58,6 +58,32 @@ class MelArgs(C.Structure):
                 ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int)]
 
 
+class WgradArgs(C.Structure):
+    _fields_ = [("x", c_void_p), ("dy", c_void_p), ("dw", c_void_p),
+                ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int), ("ksize", c_int),
+                ("stride", c_int), ("transposed", c_int), ("x_dtype", c_int), ("dy_dtype", c_int)]
+
+
+class ActBwdArgs(C.Structure):
+    _fields_ = [("dy", c_void_p), ("dy2", c_void_p), ("y", c_void_p), ("g", c_void_p), ("dbias", c_void_p),
+                ("rows", c_int64), ("c", c_int), ("act", c_int), ("y_scale", c_float), ("y_shift", c_float),
+                ("dy_dtype", c_int), ("y_dtype", c_int), ("g_dtype", c_int)]
+
+
+class BnBwdArgs(C.Structure):
+    _fields_ = [("dy", c_void_p), ("v", c_void_p), ("dv", c_void_p), ("mean", c_void_p), ("invstd", c_void_p),
+                ("gamma", c_void_p), ("beta", c_void_p), ("sums", c_void_p), ("dgamma", c_void_p), ("dbeta", c_void_p),
+                ("rows", c_int64), ("count", c_int64), ("c", c_int), ("act", c_int), ("dy_dtype", c_int),
+                ("v_dtype", c_int), ("dv_dtype", c_int)]
+
+
+class AttnBwdArgs(C.Structure):
+    _fields_ = [("q", c_void_p), ("k", c_void_p), ("v", c_void_p), ("d_out", c_void_p), ("dq", c_void_p), ("dk", c_void_p),
+                ("dv", c_void_p), ("b", c_int), ("l", c_int), ("s", c_int), ("e", c_int), ("heads", c_int),
+                ("q_stride", c_int), ("k_stride", c_int), ("v_stride", c_int), ("do_stride", c_int), ("dq_stride", c_int),
+                ("dk_stride", c_int), ("dv_stride", c_int), ("dtype", c_int)]
+
+
 # name -> (restype, argtypes); every symbol include/mstk.h declares
 SIGNATURES = {
     "mstk_version": (c_int, []),
@@ -80,6 +106,19 @@ SIGNATURES = {
     "mstk_kl": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "mstk_feature_std_mse": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_float, c_void_p, c_void_p]),
     "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_pack_conv_weight_dgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
+    "mstk_act_bwd": (c_int, [C.POINTER(ActBwdArgs), c_void_p]),
+    "mstk_bn_bwd_reduce": (c_int, [C.POINTER(BnBwdArgs), c_void_p]),
+    "mstk_bn_bwd_apply": (c_int, [C.POINTER(BnBwdArgs), c_void_p]),
+    "mstk_attention_bwd": (c_int, [C.POINTER(AttnBwdArgs), c_void_p]),
+    "mstk_time_embed_train": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "mstk_gelu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "mstk_sum_hw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_void_p]),
+    "mstk_add_bcast": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_void_p]),
+    "mstk_mse_grad": (c_int, [c_void_p, c_void_p, c_float, c_void_p, c_int, c_size_t, c_void_p]),
+    "mstk_eps_grad": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int64, c_void_p]),
+    "mstk_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p]),
     "mstk_mel_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),
 }

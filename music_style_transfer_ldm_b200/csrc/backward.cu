@@ -1,0 +1,652 @@
+// Backward pass and optimizer kernels of the training step (reference: autograd over
+// models/model.py + torch.optim.Adam at models/train.py:156-201).
+//
+//   wgrad_simt_kernel     weight gradient of the whole convolution family as a tap-gather
+//                         GEMM with K = pixels, CUDA cores, fp32 accumulate, split over pixel
+//                         ranges, atomically accumulated in the parameter's own layout
+//   act_bwd_kernel        ReLU / tanh backward (+ skip-gradient sum) + bias gradient
+//   bn_bwd_*              BatchNorm2d training-mode backward (reduce, apply)
+//   attention_bwd_kernel  softmax-attention backward per (sample, head)
+//   small streaming ops   sum over pixels, GELU', broadcast add, loss gradients, Adam
+#include "common.cuh"
+
+namespace mstk {
+
+static int bw_sms() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) sms = v;
+        else sms = 148;
+    }
+    return sms;
+}
+static unsigned bw_grid(size_t items, int threads, int per_sm = 8) {
+    size_t blocks = (items + threads - 1) / threads;
+    const size_t cap = (size_t)bw_sms() * per_sm;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (unsigned)blocks;
+}
+
+__device__ __forceinline__ void load4_rt(const void* p, int dtype, size_t idx, float (&o)[4]) {
+    if (dtype == MSTK_F32) {
+        const float4 q = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + idx);
+        o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w;
+    } else {
+        const uint2 q = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p) + idx);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+        const float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]);
+        o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// weight gradient
+// ---------------------------------------------------------------------------
+struct WgradP {
+    ConvP p;              // forward plan; p.x = forward input, p.y = dy (Ho x Wo x Cout)
+    float* dw;
+    int x_dtype, dy_dtype;
+    long long s_co, s_ci; // strides of (co, ci) in the parameter layout; the tap index is innermost
+    int ksplit;
+    int npt;              // number of (phase, tap) pairs
+};
+
+constexpr int WG_BM = 64, WG_BN = 64, WG_BK = 16, WG_LD = 68;
+
+__global__ void __launch_bounds__(256) wgrad_simt_kernel(const WgradP q) {
+    __shared__ __align__(16) float As[WG_BK][WG_LD];   // dy rows  [pixel][co]
+    __shared__ __align__(16) float Bs[WG_BK][WG_LD];   // x rows   [pixel][ci]
+    const ConvP& p = q.p;
+    int pt = blockIdx.z / q.ksplit;
+    const int ks = blockIdx.z - pt * q.ksplit;
+    int phase_idx = 0;
+    while (pt >= p.ph[phase_idx].ntaps) { pt -= p.ph[phase_idx].ntaps; ++phase_idx; }
+    const Phase& ph = p.ph[phase_idx];
+    const Tap tap = ph.taps[pt];
+    const long long K = (long long)p.N * p.Hg * p.Wg;
+    const long long k_begin = K * ks / q.ksplit, k_end = K * (ks + 1) / q.ksplit;
+    const int co0 = blockIdx.x * WG_BM, ci0 = blockIdx.y * WG_BN;
+    const int tid = threadIdx.x;
+    const int lrow = tid >> 4;            // pixel row of the k-chunk this thread loads
+    const int lc = (tid & 15) * 4;        // first of its 4 channels inside the 64-wide tile
+    const bool vec_a = (p.Cout & 3) == 0, vec_b = (p.Cin & 3) == 0;
+    const int ty = tid >> 4, tx = tid & 15;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (long long k0 = k_begin; k0 < k_end; k0 += WG_BK) {
+        float av[4] = {0.f, 0.f, 0.f, 0.f}, bv[4] = {0.f, 0.f, 0.f, 0.f};
+        const long long kp = k0 + lrow;
+        if (kp < k_end) {
+            const int n = (int)(kp / ((long long)p.Hg * p.Wg));
+            const int r = (int)(kp - (long long)n * p.Hg * p.Wg);
+            const int hg = r / p.Wg, wg = r - hg * p.Wg;
+            const int oh = hg * p.s_out + ph.oy, ow = wg * p.s_out + ph.ox;
+            const int ih = hg * p.s_in + tap.dy, iw = wg * p.s_in + tap.dx;
+            const size_t yo = (((size_t)n * p.Ho + oh) * p.Wo + ow) * (size_t)p.Cout;
+            const int ca = co0 + lc;
+            if (vec_a) {
+                if (ca < p.Cout) load4_rt(p.y, q.dy_dtype, yo + ca, av);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (ca + j < p.Cout) av[j] = load_as_f(p.y, q.dy_dtype, yo + ca + j);
+            }
+            if (ih >= 0 && ih < p.H && iw >= 0 && iw < p.W) {
+                const size_t xo = (((size_t)n * p.H + ih) * p.W + iw) * (size_t)p.Cin;
+                const int cb = ci0 + lc;
+                if (vec_b) {
+                    if (cb < p.Cin) load4_rt(p.x, q.x_dtype, xo + cb, bv);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (cb + j < p.Cin) bv[j] = load_as_f(p.x, q.x_dtype, xo + cb + j);
+                }
+            }
+        }
+        *reinterpret_cast<float4*>(&As[lrow][lc]) = make_float4(av[0], av[1], av[2], av[3]);
+        *reinterpret_cast<float4*>(&Bs[lrow][lc]) = make_float4(bv[0], bv[1], bv[2], bv[3]);
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < WG_BK; ++k) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+            const float ar[4] = {a.x, a.y, a.z, a.w};
+            const float br[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(ar[i], br[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int co = co0 + ty * 4 + i;
+        if (co >= p.Cout) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int ci = ci0 + tx * 4 + j;
+            if (ci < p.Cin) atomicAdd(q.dw + (long long)co * q.s_co + (long long)ci * q.s_ci + tap.slice, acc[i][j]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// vector helpers: 8 consecutive elements of a runtime-typed tensor
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void load8_rt(const void* p, int dtype, size_t i8, float (&v)[8]) {
+    if (dtype == MSTK_F32) {
+        const float4 a = reinterpret_cast<const float4*>(p)[2 * i8], b = reinterpret_cast<const float4*>(p)[2 * i8 + 1];
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+        const uint4 q = reinterpret_cast<const uint4*>(p)[i8];
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
+    }
+}
+__device__ __forceinline__ void store8_rt(void* p, int dtype, size_t i8, const float (&v)[8]) {
+    if (dtype == MSTK_F32) {
+        reinterpret_cast<float4*>(p)[2 * i8] = make_float4(v[0], v[1], v[2], v[3]);
+        reinterpret_cast<float4*>(p)[2 * i8 + 1] = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+        uint4 q;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+        reinterpret_cast<uint4*>(p)[i8] = q;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// activation backward + bias gradient
+// ---------------------------------------------------------------------------
+struct ActBwdP {
+    const void* dy; const void* dy2; const void* y; void* g; float* dbias;
+    long long rows; int c, act; float y_scale, y_shift; int dy_dtype, y_dtype, g_dtype;
+};
+__device__ __forceinline__ float act_deriv(float y, int act, float y_scale, float y_shift) {
+    if (act == MSTK_ACT_RELU) return y > 0.f ? y_scale : 0.f;
+    if (act == MSTK_ACT_TANH) { const float t = (y - y_shift) / y_scale; return (1.f - t * t) * y_scale; }
+    return y_scale;
+}
+// vector path: c % 8 == 0; per-thread column sums are flushed through shared memory
+__global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
+    extern __shared__ float scol[];     // [c] when dbias
+    if (a.dbias) {
+        for (int i = threadIdx.x; i < a.c; i += blockDim.x) scol[i] = 0.f;
+        __syncthreads();
+    }
+    const size_t total = (size_t)a.rows * a.c;
+    if ((a.c & 7) == 0) {
+        const size_t nvec = total >> 3;
+        float s[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s[k] = 0.f;
+        int ch_prev = -1;
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+            const int ch = (int)((i << 3) % (size_t)a.c);
+            float d[8], d2[8], y[8];
+            load8_rt(a.dy, a.dy_dtype, i, d);
+            if (a.dy2) {
+                load8_rt(a.dy2, a.dy_dtype, i, d2);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] += d2[k];
+            }
+            if (a.act != MSTK_ACT_NONE) {
+                load8_rt(a.y, a.y_dtype, i, y);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] *= act_deriv(y[k], a.act, a.y_scale, a.y_shift);
+            } else if (a.y_scale != 1.f) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] *= a.y_scale;
+            }
+            if (a.g) store8_rt(a.g, a.g_dtype, i, d);
+            if (a.dbias) {
+                if (ch != ch_prev && ch_prev >= 0) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { atomicAdd(&scol[ch_prev + k], s[k]); s[k] = 0.f; }
+                }
+                ch_prev = ch;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += d[k];
+            }
+        }
+        if (a.dbias && ch_prev >= 0) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(&scol[ch_prev + k], s[k]);
+        }
+    } else {
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+            float d = load_as_f(a.dy, a.dy_dtype, i);
+            if (a.dy2) d += load_as_f(a.dy2, a.dy_dtype, i);
+            const float yv = a.act != MSTK_ACT_NONE ? load_as_f(a.y, a.y_dtype, i) : 0.f;
+            d *= act_deriv(yv, a.act, a.y_scale, a.y_shift);
+            if (a.g) store_from_f(a.g, a.g_dtype, i, d);
+            if (a.dbias) atomicAdd(&scol[(int)(i % (size_t)a.c)], d);
+        }
+    }
+    if (a.dbias) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.c; i += blockDim.x) atomicAdd(a.dbias + i, scol[i]);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// BatchNorm backward
+// ---------------------------------------------------------------------------
+struct BnBwdP {
+    const void* dy; const void* v; void* dv; const float* mean; const float* invstd; const float* gamma; const float* beta;
+    double* sums; float* dgamma; float* dbeta; long long rows, count; int c, act, dy_dtype, v_dtype, dv_dtype;
+};
+// g = dy * relu-mask(gamma*xhat+beta); requires c % 8 == 0
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdP a) {
+    extern __shared__ float sm[];        // s0[c], s1[c]
+    float* s0 = sm; float* s1 = sm + a.c;
+    for (int i = threadIdx.x; i < 2 * a.c; i += blockDim.x) sm[i] = 0.f;
+    __syncthreads();
+    const size_t nvec = ((size_t)a.rows * a.c) >> 3;
+    float p0[8], p1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { p0[k] = 0.f; p1[k] = 0.f; }
+    int ch_prev = -1;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+        const int ch = (int)((i << 3) % (size_t)a.c);
+        if (ch != ch_prev && ch_prev >= 0) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { atomicAdd(&s0[ch_prev + k], p0[k]); atomicAdd(&s1[ch_prev + k], p1[k]); p0[k] = 0.f; p1[k] = 0.f; }
+        }
+        ch_prev = ch;
+        float d[8], v[8];
+        load8_rt(a.dy, a.dy_dtype, i, d);
+        load8_rt(a.v, a.v_dtype, i, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xh = (v[k] - a.mean[ch + k]) * a.invstd[ch + k];
+            float g = d[k];
+            if (a.act == MSTK_ACT_RELU && !(a.gamma[ch + k] * xh + a.beta[ch + k] > 0.f)) g = 0.f;
+            p0[k] += g; p1[k] = fmaf(g, xh, p1[k]);
+        }
+    }
+    if (ch_prev >= 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { atomicAdd(&s0[ch_prev + k], p0[k]); atomicAdd(&s1[ch_prev + k], p1[k]); }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.c; i += blockDim.x) {
+        atomicAdd(a.sums + i, (double)s0[i]);
+        atomicAdd(a.sums + a.c + i, (double)s1[i]);
+    }
+}
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdP a) {
+    extern __shared__ float sm[];        // m0[c] = sum g / count, m1[c] = sum g*xhat / count
+    float* m0 = sm; float* m1 = sm + a.c;
+    for (int i = threadIdx.x; i < a.c; i += blockDim.x) {
+        m0[i] = (float)(a.sums[i] / (double)a.count);
+        m1[i] = (float)(a.sums[a.c + i] / (double)a.count);
+        if (blockIdx.x == 0) {
+            if (a.dbeta) a.dbeta[i] += (float)a.sums[i];
+            if (a.dgamma) a.dgamma[i] += (float)a.sums[a.c + i];
+        }
+    }
+    __syncthreads();
+    const size_t nvec = ((size_t)a.rows * a.c) >> 3;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+        const int ch = (int)((i << 3) % (size_t)a.c);
+        float d[8], v[8];
+        load8_rt(a.dy, a.dy_dtype, i, d);
+        load8_rt(a.v, a.v_dtype, i, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float is = a.invstd[ch + k];
+            const float xh = (v[k] - a.mean[ch + k]) * is;
+            float g = d[k];
+            if (a.act == MSTK_ACT_RELU && !(a.gamma[ch + k] * xh + a.beta[ch + k] > 0.f)) g = 0.f;
+            d[k] = a.gamma[ch + k] * is * (g - m0[ch + k] - xh * m1[ch + k]);
+        }
+        store8_rt(a.dv, a.dv_dtype, i, d);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// attention backward: one CTA per (sample, head); K, V staged as fp32, dK / dV accumulated
+// in shared memory, one warp per query row (probabilities recomputed).
+// ---------------------------------------------------------------------------
+struct AttnBwdP {
+    const void* q; const void* k; const void* v; const void* d_out; void* dq; void* dk; void* dv;
+    int b, l, s, e, heads, qs, ks, vs, dos, dqs, dks, dvs, dtype;
+};
+constexpr int AB_WARPS = 8;
+__global__ void __launch_bounds__(AB_WARPS * 32) attention_bwd_kernel(const AttnBwdP a) {
+    extern __shared__ float sm[];
+    const int d = a.e / a.heads;
+    float* Ks = sm;                                  // [s][d+1]
+    float* Vs = Ks + (size_t)a.s * (d + 1);          // [s][d+1]
+    float* dKs = Vs + (size_t)a.s * (d + 1);         // [s][d]
+    float* dVs = dKs + (size_t)a.s * d;              // [s][d]
+    float* Ps = dVs + (size_t)a.s * d;               // [warps][s]  probabilities, then dS
+    float* Qs = Ps + AB_WARPS * a.s;                 // [warps][d]  scaled q
+    float* Os = Qs + AB_WARPS * d;                   // [warps][d]  d_out row
+    const int b = blockIdx.x / a.heads, hd = blockIdx.x - b * a.heads;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < a.s * d; i += blockDim.x) {
+        const int si = i / d, di = i - si * d;
+        Ks[si * (d + 1) + di] = load_as_f(a.k, a.dtype, ((size_t)b * a.s + si) * a.ks + hd * d + di);
+        Vs[si * (d + 1) + di] = load_as_f(a.v, a.dtype, ((size_t)b * a.s + si) * a.vs + hd * d + di);
+        dKs[i] = 0.f; dVs[i] = 0.f;
+    }
+    __syncthreads();
+    const float scaling = 1.0f / sqrtf((float)d);
+    float* pw = Ps + warp * a.s;
+    float* qw = Qs + warp * d;
+    float* ow = Os + warp * d;
+    for (int qi = warp; qi < a.l; qi += AB_WARPS) {
+        for (int di = lane; di < d; di += 32) {
+            qw[di] = load_as_f(a.q, a.dtype, ((size_t)b * a.l + qi) * a.qs + hd * d + di) * scaling;
+            ow[di] = load_as_f(a.d_out, a.dtype, ((size_t)b * a.l + qi) * a.dos + hd * d + di);
+        }
+        __syncwarp();
+        // probabilities
+        float mx = -INFINITY;
+        for (int si = lane; si < a.s; si += 32) {
+            float acc = 0.f;
+            const float* kr = Ks + si * (d + 1);
+            for (int di = 0; di < d; ++di) acc = fmaf(qw[di], kr[di], acc);
+            pw[si] = acc;
+            mx = fmaxf(mx, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.f;
+        for (int si = lane; si < a.s; si += 32) { const float ev = expf(pw[si] - mx); pw[si] = ev; sum += ev; }
+        sum = warp_sum(sum);
+        const float inv = 1.f / sum;
+        // dP = d_out . V^T ; rowdot = sum p*dP ; dS = p*(dP - rowdot)
+        float rowdot = 0.f;
+        float dp_local[4];                           // s <= 128 -> at most 4 keys per lane
+        int cnt = 0;
+        for (int si = lane; si < a.s; si += 32, ++cnt) {
+            const float pr = pw[si] * inv;
+            float acc = 0.f;
+            const float* vr = Vs + si * (d + 1);
+            for (int di = 0; di < d; ++di) acc = fmaf(ow[di], vr[di], acc);
+            dp_local[cnt] = acc;
+            rowdot = fmaf(pr, acc, rowdot);
+            // dV[s] += p * d_out
+            for (int di = 0; di < d; ++di) atomicAdd(&dVs[si * d + di], pr * ow[di]);
+            pw[si] = pr;
+        }
+        rowdot = warp_sum(rowdot);
+        cnt = 0;
+        for (int si = lane; si < a.s; si += 32, ++cnt) {
+            const float ds = pw[si] * (dp_local[cnt] - rowdot);
+            pw[si] = ds;
+            // dK[s] += dS * (scaled q)   (scores = (q*scaling) . k)
+            for (int di = 0; di < d; ++di) atomicAdd(&dKs[si * d + di], ds * qw[di]);
+        }
+        __syncwarp();
+        // dq = scaling * sum_s dS[s] * k[s]
+        for (int di = lane; di < d; di += 32) {
+            float acc = 0.f;
+            for (int si = 0; si < a.s; ++si) acc = fmaf(pw[si], Ks[si * (d + 1) + di], acc);
+            store_from_f(a.dq, a.dtype, ((size_t)b * a.l + qi) * a.dqs + hd * d + di, acc * scaling);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.s * d; i += blockDim.x) {
+        const int si = i / d, di = i - si * d;
+        store_from_f(a.dk, a.dtype, ((size_t)b * a.s + si) * a.dks + hd * d + di, dKs[i]);
+        store_from_f(a.dv, a.dtype, ((size_t)b * a.s + si) * a.dvs + hd * d + di, dVs[i]);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// small streaming ops
+// ---------------------------------------------------------------------------
+__global__ void sum_hw_kernel(const void* __restrict__ a, const void* __restrict__ a2, int dtype, long long hw, int c, float* __restrict__ out) {
+    // grid (ceil(c/blockDim.x), b); thread = channel, loop over pixels (coalesced across channels)
+    const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ch >= c) return;
+    const size_t base = (size_t)blockIdx.y * hw * c + ch;
+    float acc = 0.f;
+    for (long long p = 0; p < hw; ++p) {
+        acc += load_as_f(a, dtype, base + (size_t)p * c);
+        if (a2) acc += load_as_f(a2, dtype, base + (size_t)p * c);
+    }
+    out[(size_t)blockIdx.y * c + ch] = acc;
+}
+__global__ void gelu_bwd_kernel(const float* __restrict__ dh, const float* __restrict__ pre, float* __restrict__ dpre, size_t count) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        const float x = pre[i];
+        const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752440f));
+        const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+        dpre[i] = dh[i] * (cdf + x * pdf);
+    }
+}
+__global__ void add_bcast_kernel(const void* __restrict__ y, const void* __restrict__ add, const float* __restrict__ add_nc, void* out,
+                                 long long hw, int c, int dtype, size_t total) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        float v = load_as_f(y, dtype, i);
+        if (add) v += load_as_f(add, dtype, i);
+        if (add_nc) v += add_nc[(i / ((size_t)hw * c)) * c + (i % c)];
+        store_from_f(out, dtype, i, v);
+    }
+}
+__global__ void mse_grad_kernel(const float* __restrict__ a, const float* __restrict__ b, float scale, void* g, int g_dtype, size_t count) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x)
+        store_from_f(g, g_dtype, i, scale * (a[i] - b[i]));
+}
+__global__ void eps_grad_kernel(const void* __restrict__ dx0, int dx0_dtype, const float* __restrict__ eh, const float* __restrict__ eps,
+                                const float* __restrict__ ab, const long long* __restrict__ t, float scale_d, void* g, int g_dtype,
+                                long long inner, size_t total) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const float abv = ab[t[i / (size_t)inner]];
+        const float coef = -sqrtf(1.f - abv) / sqrtf(abv);
+        store_from_f(g, g_dtype, i, scale_d * (eh[i] - eps[i]) + coef * load_as_f(dx0, dx0_dtype, i));
+    }
+}
+// torch.optim.Adam single-tensor semantics: exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2*v + (1-b2) g^2;
+// denom = sqrt(v)/sqrt(bc2) + eps; p -= (lr/bc1) * m/denom
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                                   size_t count, float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, float gs) {
+    const size_t nvec = count >> 2;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+        float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+        const float4 gg = reinterpret_cast<const float4*>(g)[i];
+        float* pe = reinterpret_cast<float*>(&pp); float* me = reinterpret_cast<float*>(&mm); float* ve = reinterpret_cast<float*>(&vv);
+        const float* ge = reinterpret_cast<const float*>(&gg);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float gr = ge[k] * gs;
+            me[k] = me[k] + (gr - me[k]) * (1.f - b1);
+            ve[k] = ve[k] * b2 + (1.f - b2) * gr * gr;
+            const float denom = sqrtf(ve[k]) / bc2_sqrt + eps;
+            pe[k] = pe[k] - (lr / bc1) * (me[k] / denom);
+        }
+        reinterpret_cast<float4*>(p)[i] = pp; reinterpret_cast<float4*>(m)[i] = mm; reinterpret_cast<float4*>(v)[i] = vv;
+    }
+    for (size_t i = (nvec << 2) + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        const float gr = g[i] * gs;
+        const float mn = m[i] + (gr - m[i]) * (1.f - b1);
+        const float vn = v[i] * b2 + (1.f - b2) * gr * gr;
+        m[i] = mn; v[i] = vn;
+        p[i] = p[i] - (lr / bc1) * (mn / (sqrtf(vn) / bc2_sqrt + eps));
+    }
+}
+// dst [k*k][cin][cout] = w[cout][cin][k-1-ky][k-1-kx]
+__global__ void pack_dgrad_kernel(const float* __restrict__ src, void* dst, int cout, int cin, int k, int dtype) {
+    const int kk = k * k;
+    const size_t total = (size_t)kk * cout * cin;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int co = (int)(i % cout);
+        const int ci = (int)((i / cout) % cin);
+        const int s = (int)(i / ((size_t)cin * cout));
+        store_from_f(dst, dtype, i, src[((size_t)co * cin + ci) * kk + (kk - 1 - s)]);
+    }
+}
+
+}  // namespace mstk
+
+using namespace mstk;
+
+extern "C" {
+
+int mstk_pack_conv_weight_dgrad(const float* w, void* dst, int cout, int cin, int k, int dtype, void* stream) {
+    MSTK_REQUIRE(w && dst && cout > 0 && cin > 0 && (k == 1 || k == 3), "pack_conv_weight_dgrad: bad args");
+    const size_t total = (size_t)k * k * cout * cin;
+    pack_dgrad_kernel<<<bw_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(w, dst, cout, cin, k, dtype);
+    MSTK_CHECK_LAUNCH("pack_conv_weight_dgrad");
+    return MSTK_OK;
+}
+
+int mstk_conv2d_wgrad(const mstk_wgrad_args* a, void* stream) {
+    MSTK_REQUIRE(a && a->x && a->dy && a->dw, "wgrad: null");
+    // build the FORWARD plan (taps / phases); x stays the input, "y" is dy
+    mstk_conv_args f;
+    memset(&f, 0, sizeof(f));
+    f.x = a->x; f.wpacked = a->x /* unused */; f.y = const_cast<void*>(a->dy);
+    f.n = a->n; f.h = a->h; f.w = a->w; f.cin = a->cin; f.cout = a->cout; f.ksize = a->ksize; f.stride = a->stride;
+    f.transposed = a->transposed; f.act = MSTK_ACT_NONE; f.out_scale = 1.f; f.out_shift = 0.f;
+    f.dtype = a->x_dtype; f.out_dtype = a->dy_dtype;
+    WgradP q;
+    int rc = build_conv_plan(&f, &q.p);
+    if (rc != MSTK_OK) return rc;
+    MSTK_REQUIRE((reinterpret_cast<uintptr_t>(a->x) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->dy) & 15) == 0, "wgrad: operands must be 16-byte aligned");
+    q.dw = a->dw; q.x_dtype = a->x_dtype; q.dy_dtype = a->dy_dtype;
+    const int kk = a->ksize * a->ksize;
+    if (a->transposed) { q.s_ci = (long long)a->cout * kk; q.s_co = kk; }
+    else { q.s_co = (long long)a->cin * kk; q.s_ci = kk; }
+    q.npt = 0;
+    for (int i = 0; i < q.p.nphases; ++i) q.npt += q.p.ph[i].ntaps;
+    const long long K = (long long)q.p.N * q.p.Hg * q.p.Wg;
+    const long long tiles = (long long)((a->cout + WG_BM - 1) / WG_BM) * ((a->cin + WG_BN - 1) / WG_BN) * q.npt;
+    long long ks = (4LL * bw_sms() + tiles - 1) / tiles;          // aim at ~4 CTAs per SM
+    const long long ks_max = (K + 4 * WG_BK - 1) / (4 * WG_BK);    // at least 4 k-chunks per split
+    if (ks > ks_max) ks = ks_max;
+    if (ks < 1) ks = 1;
+    MSTK_REQUIRE((long long)q.npt * ks <= 65535, "wgrad: grid too large");
+    q.ksplit = (int)ks;
+    dim3 grid((a->cout + WG_BM - 1) / WG_BM, (a->cin + WG_BN - 1) / WG_BN, (unsigned)(q.npt * ks));
+    wgrad_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(q);
+    MSTK_CHECK_LAUNCH("wgrad");
+    return MSTK_OK;
+}
+
+int mstk_act_bwd(const mstk_act_bwd_args* a, void* stream) {
+    MSTK_REQUIRE(a && a->dy && (a->g || a->dbias), "act_bwd: null");
+    MSTK_REQUIRE(a->act == MSTK_ACT_NONE || a->y, "act_bwd: y needed for the activation derivative");
+    MSTK_REQUIRE(a->rows > 0 && a->c > 0 && a->c <= 8192, "act_bwd: bad dims");
+    MSTK_REQUIRE(a->y_scale != 0.f, "act_bwd: y_scale must be non-zero");
+    ActBwdP p;
+    p.dy = a->dy; p.dy2 = a->dy2; p.y = a->y; p.g = a->g; p.dbias = a->dbias; p.rows = a->rows; p.c = a->c; p.act = a->act;
+    p.y_scale = a->y_scale; p.y_shift = a->y_shift; p.dy_dtype = a->dy_dtype; p.y_dtype = a->y_dtype; p.g_dtype = a->g_dtype;
+    const size_t total = (size_t)a->rows * a->c;
+    const size_t items = (a->c & 7) == 0 ? total / 8 : total;
+    act_bwd_kernel<<<bw_grid(items, 256, 4), 256, a->dbias ? a->c * sizeof(float) : 0, (cudaStream_t)stream>>>(p);
+    MSTK_CHECK_LAUNCH("act_bwd");
+    return MSTK_OK;
+}
+
+static int bn_bwd_common(const mstk_bn_bwd_args* a, BnBwdP* p) {
+    MSTK_REQUIRE(a && a->dy && a->v && a->mean && a->invstd && a->gamma && a->beta && a->sums, "bn_bwd: null");
+    MSTK_REQUIRE(a->c > 0 && (a->c & 7) == 0 && a->c <= 4096 && a->rows > 0 && a->count >= a->rows, "bn_bwd: bad dims (c must be a multiple of 8)");
+    p->dy = a->dy; p->v = a->v; p->dv = a->dv; p->mean = a->mean; p->invstd = a->invstd; p->gamma = a->gamma; p->beta = a->beta;
+    p->sums = a->sums; p->dgamma = a->dgamma; p->dbeta = a->dbeta; p->rows = a->rows; p->count = a->count; p->c = a->c; p->act = a->act;
+    p->dy_dtype = a->dy_dtype; p->v_dtype = a->v_dtype; p->dv_dtype = a->dv_dtype;
+    return MSTK_OK;
+}
+int mstk_bn_bwd_reduce(const mstk_bn_bwd_args* a, void* stream) {
+    BnBwdP p;
+    int rc = bn_bwd_common(a, &p);
+    if (rc != MSTK_OK) return rc;
+    bn_bwd_reduce_kernel<<<bw_grid((size_t)a->rows * a->c / 8, 256, 4), 256, 2 * a->c * sizeof(float), (cudaStream_t)stream>>>(p);
+    MSTK_CHECK_LAUNCH("bn_bwd_reduce");
+    return MSTK_OK;
+}
+int mstk_bn_bwd_apply(const mstk_bn_bwd_args* a, void* stream) {
+    BnBwdP p;
+    int rc = bn_bwd_common(a, &p);
+    if (rc != MSTK_OK) return rc;
+    MSTK_REQUIRE(a->dv, "bn_bwd_apply: dv is null");
+    bn_bwd_apply_kernel<<<bw_grid((size_t)a->rows * a->c / 8, 256, 8), 256, 2 * a->c * sizeof(float), (cudaStream_t)stream>>>(p);
+    MSTK_CHECK_LAUNCH("bn_bwd_apply");
+    return MSTK_OK;
+}
+
+int mstk_attention_bwd(const mstk_attn_bwd_args* a, void* stream) {
+    MSTK_REQUIRE(a && a->q && a->k && a->v && a->d_out && a->dq && a->dk && a->dv, "attention_bwd: null");
+    MSTK_REQUIRE(a->b > 0 && a->l > 0 && a->s > 0 && a->s <= 128 && a->heads > 0 && a->e % a->heads == 0, "attention_bwd: bad dims (s <= 128)");
+    AttnBwdP p;
+    p.q = a->q; p.k = a->k; p.v = a->v; p.d_out = a->d_out; p.dq = a->dq; p.dk = a->dk; p.dv = a->dv;
+    p.b = a->b; p.l = a->l; p.s = a->s; p.e = a->e; p.heads = a->heads; p.qs = a->q_stride; p.ks = a->k_stride; p.vs = a->v_stride;
+    p.dos = a->do_stride; p.dqs = a->dq_stride; p.dks = a->dk_stride; p.dvs = a->dv_stride; p.dtype = a->dtype;
+    const int d = a->e / a->heads;
+    const size_t smem = ((size_t)2 * a->s * (d + 1) + (size_t)2 * a->s * d + AB_WARPS * a->s + 2 * AB_WARPS * d) * sizeof(float);
+    MSTK_REQUIRE(smem <= 200 * 1024, "attention_bwd: s*d too large (s=%d d=%d)", a->s, d);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "attention_bwd smem attr");
+        smem_set = 200 * 1024;
+    }
+    attention_bwd_kernel<<<a->b * a->heads, AB_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    MSTK_CHECK_LAUNCH("attention_bwd");
+    return MSTK_OK;
+}
+
+int mstk_gelu_bwd(const float* dh, const float* pre, float* dpre, size_t count, void* stream) {
+    MSTK_REQUIRE(dh && pre && dpre && count > 0, "gelu_bwd: bad args");
+    gelu_bwd_kernel<<<bw_grid(count, 256), 256, 0, (cudaStream_t)stream>>>(dh, pre, dpre, count);
+    MSTK_CHECK_LAUNCH("gelu_bwd");
+    return MSTK_OK;
+}
+int mstk_sum_hw(const void* a, const void* a2, int dtype, int b, int64_t hw, int c, float* out, void* stream) {
+    MSTK_REQUIRE(a && out && b > 0 && b <= 65535 && hw > 0 && c > 0, "sum_hw: bad args");
+    dim3 grid((c + 127) / 128, b);
+    sum_hw_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(a, a2, dtype, hw, c, out);
+    MSTK_CHECK_LAUNCH("sum_hw");
+    return MSTK_OK;
+}
+int mstk_add_bcast(const void* y, const void* add, const float* add_nc, void* out, int n, int64_t hw, int c, int dtype, void* stream) {
+    MSTK_REQUIRE(y && out && n > 0 && hw > 0 && c > 0, "add_bcast: bad args");
+    const size_t total = (size_t)n * hw * c;
+    add_bcast_kernel<<<bw_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(y, add, add_nc, out, hw, c, dtype, total);
+    MSTK_CHECK_LAUNCH("add_bcast");
+    return MSTK_OK;
+}
+int mstk_mse_grad(const float* a, const float* b, float scale, void* g, int g_dtype, size_t count, void* stream) {
+    MSTK_REQUIRE(a && b && g && count > 0, "mse_grad: bad args");
+    mse_grad_kernel<<<bw_grid(count, 256), 256, 0, (cudaStream_t)stream>>>(a, b, scale, g, g_dtype, count);
+    MSTK_CHECK_LAUNCH("mse_grad");
+    return MSTK_OK;
+}
+int mstk_eps_grad(const void* dx0, int dx0_dtype, const float* eps_hat, const float* eps, const float* alpha_bar, const int64_t* t,
+                  float scale_d, void* g, int g_dtype, int b, int64_t inner, void* stream) {
+    MSTK_REQUIRE(dx0 && eps_hat && eps && alpha_bar && t && g && b > 0 && inner > 0, "eps_grad: bad args");
+    const size_t total = (size_t)b * inner;
+    eps_grad_kernel<<<bw_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(dx0, dx0_dtype, eps_hat, eps, alpha_bar, (const long long*)t, scale_d,
+                                                                         g, g_dtype, inner, total);
+    MSTK_CHECK_LAUNCH("eps_grad");
+    return MSTK_OK;
+}
+int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps, int64_t step,
+                   float grad_scale, void* stream) {
+    MSTK_REQUIRE(p && g && m && v && count > 0 && step >= 1, "adam: bad args");
+    MSTK_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+                 "adam: arenas must be 16-byte aligned");
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, (float)bc1,
+                                                                               (float)sqrt(bc2), grad_scale);
+    MSTK_CHECK_LAUNCH("adam");
+    return MSTK_OK;
+}
+
+}  // extern "C"

@@ -45,10 +45,11 @@ int build_conv_plan(const mstk_conv_args* a, ConvP* p) {
     }
     const int k = a->ksize, s = a->stride;
     if (!a->transposed) {
-        MSTK_REQUIRE(k == 1 || k == 3, "conv: ksize %d unsupported (1 or 3)", k);
+        MSTK_REQUIRE(k == 1 || k == 3 || k == 4, "conv: ksize %d unsupported (1, 3 or 4)", k);
         MSTK_REQUIRE(s == 1 || s == 2, "conv: stride %d unsupported", s);
-        MSTK_REQUIRE(k == 3 || s == 1, "conv: k1 needs stride 1");
-        const int pad = k / 2;
+        MSTK_REQUIRE(k != 1 || s == 1, "conv: k1 needs stride 1");
+        MSTK_REQUIRE(k != 4 || s == 2, "conv: k4 needs stride 2 (data gradient of ConvTranspose2d k4 s2 p1)");
+        const int pad = k == 4 ? 1 : k / 2;
         p->Ho = (a->h + 2 * pad - k) / s + 1;
         p->Wo = (a->w + 2 * pad - k) / s + 1;
         p->Hg = p->Ho; p->Wg = p->Wo;

@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
 // with coalesced reads ([dim][dim+1] padding: thread i then walks row i conflict-free).
 constexpr int TE_SPB = 16;
 __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const float* __restrict__ w1, const float* __restrict__ b1,
-                                  const float* __restrict__ w2, const float* __restrict__ b2, float* __restrict__ out, int dim) {
+                                  const float* __restrict__ w2, const float* __restrict__ b2, float* __restrict__ out,
+                                  float* __restrict__ e_out, float* __restrict__ pre_out, int dim) {
     extern __shared__ float sm[];   // ws[dim][dim+1], e[TE_SPB][dim], h[TE_SPB][dim]
     float* ws = sm;
     float* e = ws + (size_t)dim * (dim + 1);
@@ -192,6 +193,7 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const flo
         for (int s = 0; s < ns; ++s) {
             const float arg = t[s0 + s] * fr;
             e[s * dim + i] = i < half ? sinf(arg) : cosf(arg);
+            if (e_out) e_out[(size_t)(s0 + s) * dim + i] = e[s * dim + i];
         }
     }
     __syncthreads();
@@ -209,6 +211,8 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const flo
         // exact GELU (nn.GELU default): 0.5 x (1 + erf(x / sqrt(2)))
 #pragma unroll
         for (int s = 0; s < TE_SPB; ++s) h[s * dim + i] = 0.5f * acc[s] * (1.f + erff(acc[s] * 0.70710678118654752440f));
+        if (pre_out)
+            for (int s = 0; s < ns; ++s) pre_out[(size_t)(s0 + s) * dim + i] = acc[s];
     }
     __syncthreads();
     for (int idx = i; idx < dim * dim; idx += dim) ws[(idx / dim) * (dim + 1) + (idx % dim)] = w2[idx];
@@ -518,8 +522,14 @@ int mstk_bn_apply(const mstk_bn_args* a, void* stream) {
     return MSTK_OK;
 }
 
+int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out,
+                          float* e_out, float* pre_out, int dim, void* stream);
 int mstk_time_embed(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out, int dim,
                     void* stream) {
+    return mstk_time_embed_train(t, b, w1, b1, w2, b2, out, nullptr, nullptr, dim, stream);
+}
+int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out,
+                          float* e_out, float* pre_out, int dim, void* stream) {
     MSTK_REQUIRE(t && w1 && b1 && w2 && b2 && out && b > 0, "time_embed: null");
     MSTK_REQUIRE(dim >= 4 && dim <= 1024 && (dim % 2) == 0, "time_embed: bad dim");
     MSTK_REQUIRE(dim <= 192, "time_embed: dim %d too large for the shared-memory weight tile", dim);
@@ -530,7 +540,7 @@ int mstk_time_embed(const float* t, int b, const float* w1, const float* b1, con
         if (e != cudaSuccess) return cuda_fail(e, "time_embed smem attr");
         smem_set = smem;
     }
-    time_embed_kernel<<<(b + TE_SPB - 1) / TE_SPB, dim, smem, (cudaStream_t)stream>>>(t, b, w1, b1, w2, b2, out, dim);
+    time_embed_kernel<<<(b + TE_SPB - 1) / TE_SPB, dim, smem, (cudaStream_t)stream>>>(t, b, w1, b1, w2, b2, out, e_out, pre_out, dim);
     MSTK_CHECK_LAUNCH("time_embed");
     return MSTK_OK;
 }

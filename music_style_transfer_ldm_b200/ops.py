@@ -99,7 +99,7 @@ class Ddim:
 def conv_out_hw(h, w, ksize, stride, transposed):
     if transposed:
         return 2 * h, 2 * w
-    pad = ksize // 2
+    pad = 1 if ksize == 4 else ksize // 2
     return (h + 2 * pad - ksize) // stride + 1, (w + 2 * pad - ksize) // stride + 1
 
 
@@ -354,3 +354,149 @@ def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, wan
     check(lib.mstk_mel_frontend(C.byref(a), _stream()), "mstk_mel_frontend")
     _count(3)
     return out, db
+
+
+# ------------------------------------------------------------------------------------------
+# backward pass / optimizer (include/mstk.h, "Backward pass and optimizer" section)
+# ------------------------------------------------------------------------------------------
+def pack_weight_dgrad(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """Conv2d [co,ci,k,k] / Linear [co,ci] fp32 -> [k*k, ci, co] with flipped taps: the packed weight of the
+    stride-1 conv that maps dL/dy to dL/dx."""
+    lib = _lib.load()
+    w = _dev(w.detach(), "pack_dgrad.w")
+    co, ci = w.shape[0], w.shape[1]
+    k = 1 if w.dim() == 2 else w.shape[2]
+    dst = torch.empty((k * k, ci, co), dtype=dtype, device=w.device)
+    check(lib.mstk_pack_conv_weight_dgrad(_p(w), _p(dst), co, ci, k, dtype_code(dtype), _stream()), "mstk_pack_conv_weight_dgrad")
+    return dst
+
+
+def wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, *, ksize: int, stride: int = 1, transposed: bool = False) -> None:
+    """dw (fp32, the parameter's own layout) += weight gradient of the forward conv that mapped x -> y."""
+    lib = _lib.load()
+    _dev(x, "wgrad.x"); _dev(dy, "wgrad.dy"); _dev(dw, "wgrad.dw")
+    n, h, w, cin = x.shape
+    cout = dy.shape[-1]
+    ho, wo = conv_out_hw(h, w, ksize, stride, transposed)
+    if tuple(dy.shape) != (n, ho, wo, cout):
+        raise MstkError(f"wgrad: dy {tuple(dy.shape)} does not match the forward output {(n, ho, wo, cout)}")
+    if dw.dtype != torch.float32 or dw.numel() != cin * cout * ksize * ksize:
+        raise MstkError("wgrad: dw must be the fp32 parameter-shaped gradient")
+    a = _lib.WgradArgs(_p(x), _p(dy), _p(dw), n, h, w, cin, cout, ksize, stride, 1 if transposed else 0, dtype_code(x), dtype_code(dy))
+    check(lib.mstk_conv2d_wgrad(C.byref(a), _stream()), "mstk_conv2d_wgrad")
+    _count()
+
+
+def act_bwd(dy: torch.Tensor, y: Optional[torch.Tensor], *, act: int, dy2: Optional[torch.Tensor] = None,
+            dbias: Optional[torch.Tensor] = None, g_dtype: Optional[torch.dtype] = None, want_g: bool = True,
+            y_scale: float = 1.0, y_shift: float = 0.0) -> Optional[torch.Tensor]:
+    lib = _lib.load()
+    _dev(dy, "act_bwd.dy")
+    c = dy.shape[-1]
+    rows = dy.numel() // c
+    g = torch.empty(dy.shape, dtype=g_dtype or dy.dtype, device=dy.device) if want_g else None
+    if dy2 is not None and (dy2.dtype != dy.dtype or dy2.shape != dy.shape):
+        raise MstkError("act_bwd: dy2 must match dy")
+    if y is not None and y.numel() != dy.numel():
+        raise MstkError("act_bwd: y must match dy")
+    a = _lib.ActBwdArgs(_p(dy), _p(dy2), _p(y), _p(g), _p(dbias), rows, c, act, y_scale, y_shift, dtype_code(dy),
+                        dtype_code(y) if y is not None else 0, dtype_code(g) if g is not None else 0)
+    check(lib.mstk_act_bwd(C.byref(a), _stream()), "mstk_act_bwd")
+    _count()
+    return g
+
+
+def bn_bwd(dy: torch.Tensor, v: torch.Tensor, mean, invstd, gamma, beta, *, act: int, dgamma, dbeta, world: int = 1,
+           sync=None, dv_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """training-mode BatchNorm2d backward (two passes; `sync(sums)` all-reduces the two per-channel sums)"""
+    lib = _lib.load()
+    c = v.shape[-1]
+    rows = v.numel() // c
+    sums = torch.zeros(2 * c, dtype=torch.float64, device=v.device)
+    dv = torch.empty(v.shape, dtype=dv_dtype or dy.dtype, device=v.device)
+    a = _lib.BnBwdArgs(_p(dy), _p(v), _p(dv), _p(mean), _p(invstd), _p(gamma), _p(beta), _p(sums), _p(dgamma), _p(dbeta),
+                       rows, rows * world, c, act, dtype_code(dy), dtype_code(v), dtype_code(dv))
+    check(lib.mstk_bn_bwd_reduce(C.byref(a), _stream()), "mstk_bn_bwd_reduce")
+    if sync is not None:
+        sync(sums)
+    check(lib.mstk_bn_bwd_apply(C.byref(a), _stream()), "mstk_bn_bwd_apply")
+    _count(2)
+    return dv
+
+
+def attention_bwd(q, k, v, d_out, heads: int):
+    """q, d_out [b,l,e]; k, v [b,s,e] views -> dq [b,l,e], dkv [b,s,2e] (dk = [..., :e], dv = [..., e:])"""
+    lib = _lib.load()
+    b, l, e = q.shape
+    s = k.shape[1]
+    dq = torch.empty((b, l, e), dtype=q.dtype, device=q.device)
+    dkv = torch.empty((b, s, 2 * e), dtype=q.dtype, device=q.device)
+    a = _lib.AttnBwdArgs(_p(q), _p(k), _p(v), _p(d_out), _p(dq), dkv.data_ptr(), dkv.data_ptr() + e * dkv.element_size(),
+                         b, l, s, e, heads, q.stride(1), k.stride(1), v.stride(1), d_out.stride(1), e, 2 * e, 2 * e, dtype_code(q))
+    check(lib.mstk_attention_bwd(C.byref(a), _stream()), "mstk_attention_bwd")
+    _count()
+    return dq, dkv
+
+
+def time_embed_train(t, w1, b1, w2, b2):
+    lib = _lib.load()
+    dim = w1.shape[0]
+    n = t.numel()
+    out, e, pre = (torch.empty((n, dim), dtype=torch.float32, device=t.device) for _ in range(3))
+    check(lib.mstk_time_embed_train(_p(t), n, _p(w1), _p(b1), _p(w2), _p(b2), _p(out), _p(e), _p(pre), dim, _stream()),
+          "mstk_time_embed_train")
+    _count()
+    return out, e, pre
+
+
+def gelu_bwd(dh, pre):
+    lib = _lib.load()
+    out = torch.empty_like(pre)
+    check(lib.mstk_gelu_bwd(_p(dh), _p(pre), _p(out), pre.numel(), _stream()), "mstk_gelu_bwd")
+    _count()
+    return out
+
+
+def sum_hw(a: torch.Tensor, a2: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[b,h,w,c] -> fp32 [b,c] (sum of a + a2 over the pixels)"""
+    lib = _lib.load()
+    b, c = a.shape[0], a.shape[-1]
+    hw = a.numel() // (b * c)
+    out = torch.empty((b, c), dtype=torch.float32, device=a.device)
+    check(lib.mstk_sum_hw(_p(a), _p(a2), dtype_code(a), b, hw, c, _p(out), _stream()), "mstk_sum_hw")
+    _count()
+    return out
+
+
+def add_bcast(y: torch.Tensor, add: Optional[torch.Tensor] = None, add_nc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    lib = _lib.load()
+    n, c = y.shape[0], y.shape[-1]
+    hw = y.numel() // (n * c)
+    out = torch.empty_like(y)
+    check(lib.mstk_add_bcast(_p(y), _p(add), _p(add_nc), _p(out), n, hw, c, dtype_code(y), _stream()), "mstk_add_bcast")
+    _count()
+    return out
+
+
+def mse_grad(a: torch.Tensor, b: torch.Tensor, scale: float, g_dtype: torch.dtype) -> torch.Tensor:
+    lib = _lib.load()
+    g = torch.empty(a.shape, dtype=g_dtype, device=a.device)
+    check(lib.mstk_mse_grad(_p(a), _p(b), scale, _p(g), dtype_code(g_dtype), a.numel(), _stream()), "mstk_mse_grad")
+    _count()
+    return g
+
+
+def eps_grad(dx0: torch.Tensor, eps_hat, eps, alpha_bar, t, scale_d: float, g_dtype: torch.dtype) -> torch.Tensor:
+    lib = _lib.load()
+    b = eps_hat.shape[0]
+    g = torch.empty(eps_hat.shape, dtype=g_dtype, device=eps_hat.device)
+    check(lib.mstk_eps_grad(_p(dx0), dtype_code(dx0), _p(eps_hat), _p(eps), _p(alpha_bar), _p(t), scale_d, _p(g), dtype_code(g_dtype),
+                            b, eps_hat.numel() // b, _stream()), "mstk_eps_grad")
+    _count()
+    return g
+
+
+def adam_step(p, g, m, v, *, lr: float, beta1: float, beta2: float, eps: float, step: int, grad_scale: float = 1.0) -> None:
+    lib = _lib.load()
+    check(lib.mstk_adam_step(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, step, grad_scale, _stream()), "mstk_adam_step")
+    _count()

@@ -1,10 +1,2 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -q -m gpu --timeout 300 -x > gpurun_out/t_gpu.log 2>&1; echo "gpu tests rc=$?"; tail -n 15 gpurun_out/t_gpu.log
-timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/b_short.log 2>gpurun_out/b_short.err; echo "bench rc=$?"; tail -n 3 gpurun_out/b_short.err
-python - <<'PY'
-import json
-try:
-    d=json.loads(open('gpurun_out/b_short.log').read().strip().splitlines()[-1])
-    print("steps/s", d['value'], "e2e", d['e2e']['value'], "unet_step_us", d['unet_step_us'], "roof", d['roofline']['achieved'])
-except Exception as e: print("no bench", e)
-PY
+timeout 900 python -m pytest tests/test_gpu_backward_ops.py -q -m gpu --timeout 300 > gpurun_out/t_bwd.log 2>&1; echo "bwd tests rc=$?"; tail -n 40 gpurun_out/t_bwd.log
