@@ -291,9 +291,9 @@ typedef struct mstk_attn_bwd_args {
 } mstk_attn_bwd_args;
 int mstk_attention_bwd(const mstk_attn_bwd_args* a, void* stream);
 
-/* time MLP with the intermediates the backward needs (e = sinusoid, pre = Linear1 output) */
+/* time MLP with the intermediates the backward needs (e = sinusoid, pre = Linear1 output, h = GELU(pre)) */
 int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2,
-                          float* out, float* e_out, float* pre_out, int dim, void* stream);
+                          float* out, float* e_out, float* pre_out, float* h_out, int dim, void* stream);
 /* dpre = dh * gelu'(pre) (exact erf GELU), fp32 */
 int mstk_gelu_bwd(const float* dh, const float* pre, float* dpre, size_t count, void* stream);
 /* out[b, c] = sum over hw of (a[b,hw,c] + a2[b,hw,c]) ; a2 optional; fp32 out */

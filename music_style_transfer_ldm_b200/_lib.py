@@ -112,7 +112,7 @@ SIGNATURES = {
     "mstk_bn_bwd_reduce": (c_int, [C.POINTER(BnBwdArgs), c_void_p]),
     "mstk_bn_bwd_apply": (c_int, [C.POINTER(BnBwdArgs), c_void_p]),
     "mstk_attention_bwd": (c_int, [C.POINTER(AttnBwdArgs), c_void_p]),
-    "mstk_time_embed_train": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "mstk_time_embed_train": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "mstk_gelu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "mstk_sum_hw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "mstk_add_bcast": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_void_p]),

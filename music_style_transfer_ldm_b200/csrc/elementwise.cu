@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
 constexpr int TE_SPB = 16;
 __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const float* __restrict__ w1, const float* __restrict__ b1,
                                   const float* __restrict__ w2, const float* __restrict__ b2, float* __restrict__ out,
-                                  float* __restrict__ e_out, float* __restrict__ pre_out, int dim) {
+                                  float* __restrict__ e_out, float* __restrict__ pre_out, float* __restrict__ h_out, int dim) {
     extern __shared__ float sm[];   // ws[dim][dim+1], e[TE_SPB][dim], h[TE_SPB][dim]
     float* ws = sm;
     float* e = ws + (size_t)dim * (dim + 1);
@@ -213,6 +213,8 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const flo
         for (int s = 0; s < TE_SPB; ++s) h[s * dim + i] = 0.5f * acc[s] * (1.f + erff(acc[s] * 0.70710678118654752440f));
         if (pre_out)
             for (int s = 0; s < ns; ++s) pre_out[(size_t)(s0 + s) * dim + i] = acc[s];
+        if (h_out)
+            for (int s = 0; s < ns; ++s) h_out[(size_t)(s0 + s) * dim + i] = h[s * dim + i];
     }
     __syncthreads();
     for (int idx = i; idx < dim * dim; idx += dim) ws[(idx / dim) * (dim + 1) + (idx % dim)] = w2[idx];
@@ -523,13 +525,13 @@ int mstk_bn_apply(const mstk_bn_args* a, void* stream) {
 }
 
 int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out,
-                          float* e_out, float* pre_out, int dim, void* stream);
+                          float* e_out, float* pre_out, float* h_out, int dim, void* stream);
 int mstk_time_embed(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out, int dim,
                     void* stream) {
-    return mstk_time_embed_train(t, b, w1, b1, w2, b2, out, nullptr, nullptr, dim, stream);
+    return mstk_time_embed_train(t, b, w1, b1, w2, b2, out, nullptr, nullptr, nullptr, dim, stream);
 }
 int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b1, const float* w2, const float* b2, float* out,
-                          float* e_out, float* pre_out, int dim, void* stream) {
+                          float* e_out, float* pre_out, float* h_out, int dim, void* stream) {
     MSTK_REQUIRE(t && w1 && b1 && w2 && b2 && out && b > 0, "time_embed: null");
     MSTK_REQUIRE(dim >= 4 && dim <= 1024 && (dim % 2) == 0, "time_embed: bad dim");
     MSTK_REQUIRE(dim <= 192, "time_embed: dim %d too large for the shared-memory weight tile", dim);
@@ -540,7 +542,7 @@ int mstk_time_embed_train(const float* t, int b, const float* w1, const float* b
         if (e != cudaSuccess) return cuda_fail(e, "time_embed smem attr");
         smem_set = smem;
     }
-    time_embed_kernel<<<(b + TE_SPB - 1) / TE_SPB, dim, smem, (cudaStream_t)stream>>>(t, b, w1, b1, w2, b2, out, e_out, pre_out, dim);
+    time_embed_kernel<<<(b + TE_SPB - 1) / TE_SPB, dim, smem, (cudaStream_t)stream>>>(t, b, w1, b1, w2, b2, out, e_out, pre_out, h_out, dim);
     MSTK_CHECK_LAUNCH("time_embed");
     return MSTK_OK;
 }

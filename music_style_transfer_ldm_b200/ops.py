@@ -442,11 +442,11 @@ def time_embed_train(t, w1, b1, w2, b2):
     lib = _lib.load()
     dim = w1.shape[0]
     n = t.numel()
-    out, e, pre = (torch.empty((n, dim), dtype=torch.float32, device=t.device) for _ in range(3))
-    check(lib.mstk_time_embed_train(_p(t), n, _p(w1), _p(b1), _p(w2), _p(b2), _p(out), _p(e), _p(pre), dim, _stream()),
+    out, e, pre, h = (torch.empty((n, dim), dtype=torch.float32, device=t.device) for _ in range(4))
+    check(lib.mstk_time_embed_train(_p(t), n, _p(w1), _p(b1), _p(w2), _p(b2), _p(out), _p(e), _p(pre), _p(h), dim, _stream()),
           "mstk_time_embed_train")
     _count()
-    return out, e, pre
+    return out, e, pre, h
 
 
 def gelu_bwd(dh, pre):

@@ -1,0 +1,342 @@
+"""Drop-in surface of the reference's models/train.py training step on libmstk kernels.
+
+    LDMTrainer(model, train_loader, device, lr=1e-4, style_loss_weight=0.1)      train.py:141-161
+        .train_step(content_spec, style_spec) -> dict of 4 floats                 train.py:163-208
+        .train_step_device(content, style, t=None, noise=None) -> dict of 0-dim CUDA tensors (no host sync)
+
+The reference gets its gradients from autograd and its update from torch.optim.Adam under fp16
+autocast + GradScaler.  Here forward, backward and update are one explicit stream of C-ABI kernel
+launches (no autograd tape, no torch compute op on the path):
+
+  * forward = LDM.forward's kernels with the intermediates kept (conv inputs, pre-add ReLU outputs,
+    BatchNorm batch statistics, attention q / kv, the time MLP's e / pre / h);
+  * gradient reaches the decoder, the UNet and the style encoder through MSE(recon, x) and
+    MSE(eps_hat, eps) only: the encoder is frozen (model.py:340-341), the two VGGish terms are
+    evaluated under torch.no_grad() in the reference (loss.py:78) and the KL term sees only the
+    frozen encoder's output -- so those three are forward-only here too;
+  * data gradients of the contractions run on the forward kernels with re-packed weights, weight
+    gradients accumulate in a flat fp32 gradient arena in the parameters' own layouts, and the
+    update is ONE fused Adam kernel over the flat parameter / gradient / moment arenas;
+  * bf16 mode needs no loss scaling, so GradScaler is omitted (documented deviation; fp32 master
+    weights and fp32 weight gradients as under autocast).
+
+Data parallelism (one process per GPU): pass ``process_group`` / ``world_size``.  The batch is sharded;
+the gradient arena is all-reduced in buckets (NCCL, side stream) as soon as the backward sweep has
+finished the layers of a bucket, and the BatchNorm forward/backward statistics are all-reduced so every
+rank normalises with the GLOBAL batch statistics (single-process parity).
+Epoch bookkeeping, plotting, tqdm and checkpoint writing (train.py:210-293) are outside the hot path.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import loss as L
+from . import model as Mo
+from . import ops
+from .ops import ACT_NONE, ACT_RELU, ACT_TANH, MstkError
+
+
+class _Arena:
+    """Flat fp32 storage for the trainable parameters (in backward-completion order), their gradients and
+    the two Adam moments.  ``param.data`` / ``param.grad`` become views, so ``state_dict`` is unchanged."""
+
+    def __init__(self, params: List[nn.Parameter], device):
+        self.params = params
+        self.offsets, off = [], 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + 3) // 4 * 4             # keep every view 16-byte aligned
+        self.size = off
+        self.p = torch.zeros(off, dtype=torch.float32, device=device)
+        self.g = torch.zeros(off, dtype=torch.float32, device=device)
+        self.m = torch.zeros(off, dtype=torch.float32, device=device)
+        self.v = torch.zeros(off, dtype=torch.float32, device=device)
+        for p, o in zip(params, self.offsets):
+            view = self.p[o:o + p.numel()].view(p.shape)
+            view.copy_(p.data)
+            p.data = view
+            p.grad = self.g[o:o + p.numel()].view(p.shape)
+
+    def span(self, first: nn.Parameter, last: nn.Parameter):
+        i0 = next(i for i, p in enumerate(self.params) if p is first)
+        i1 = next(i for i, p in enumerate(self.params) if p is last)
+        return self.offsets[i0], self.offsets[i1] + (self.params[i1].numel() + 3) // 4 * 4
+
+
+def _backward_order(model) -> List[nn.Parameter]:
+    """trainable parameters in the order the backward sweep finishes them (decoder, UNet top-down, style encoder)"""
+    d, u, s = model.decoder.decoder, model.unet, model.style_encoder
+    mods = [d[6], d[4], d[3], d[1], d[0], u.dec1, u.dec2, u.dec3, u.dec4, u.bottleneck,
+            u.cross_attention1.multihead_attn, u.enc4, u.cross_attention2.multihead_attn, u.enc3, u.enc2, u.time_mlp[3],
+            u.time_mlp[1], u.enc1, s.enc6, s.enc5, s.enc4, s.enc3, s.enc2, s.enc1]
+    out, seen = [], set()
+    for m in mods:
+        for p in m.parameters():
+            if id(p) not in seen:
+                seen.add(id(p))
+                out.append(p)
+    return out
+
+
+class LDMTrainer:
+    def __init__(self, model, train_loader, device, lr=1e-4, style_loss_weight=0.1, process_group=None, world_size: int = 1,
+                 num_buckets: int = 3):
+        self.model = model.to(device)
+        self.train_loader = train_loader
+        self.device = torch.device(device)
+        self.style_loss_weight = style_loss_weight
+        self.lr = float(lr)
+        self.betas, self.eps = (0.9, 0.999), 1e-8          # torch.optim.Adam defaults (train.py:156)
+        self.step_count = 0
+        self.group, self.world = process_group, int(world_size)
+        if self.device.type != "cuda":
+            raise MstkError("LDMTrainer: the training step runs on sm_100a kernels only (no CPU fallback)")
+        order = _backward_order(self.model)
+        trainable = [p for p in self.model.parameters() if p.requires_grad]
+        if {id(p) for p in trainable} != {id(p) for p in order}:
+            raise MstkError("LDMTrainer: expected exactly decoder + unet + style_encoder to be trainable (the reference freezes the "
+                            "encoder, model.py:340-341, and VGGishFeatureLoss is frozen); call model._freeze_encoder() first")
+        self.arena = _Arena(order, self.device)
+        for m in self.model.modules():                        # packed-weight caches point at the old storages
+            m.__dict__.pop("_mstk_cache", None)
+        # gradient buckets for the data-parallel all-reduce, in backward-completion order
+        u, s, d = self.model.unet, self.model.style_encoder, self.model.decoder.decoder
+        cuts = [(d[6].weight, u.dec4.bias), (u.bottleneck.weight, u.enc1.bias), (s.enc6.weight, s.enc1.bias)]
+        self.buckets = [self.arena.span(a, b) for a, b in cuts][:max(1, num_buckets)]
+        if len(self.buckets) < 3:
+            self.buckets[-1] = (self.buckets[-1][0], self.arena.size)
+        self.comm_stream = torch.cuda.Stream(device=self.device) if self.world > 1 else None
+        if self.world > 1:
+            Mo.set_bn_sync_group(self.group, self.world)
+            import torch.distributed as dist
+            dist.broadcast(self.arena.p, src=0, group=self.group)        # identical replicas (buffers: see sync_buffers)
+
+    # -- reference API ----------------------------------------------------------------------
+    def train_step(self, content_spec, style_spec):
+        out = self.train_step_device(content_spec, style_spec)
+        vals = torch.stack([out[k] for k in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]).tolist()   # ONE host sync
+        return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), vals))
+
+    def _sync_sums(self, sums):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(sums, group=self.group)
+
+    def _reduce_bucket(self, i: int):
+        """all-reduce bucket i of the gradient arena on the side stream, behind everything enqueued so far"""
+        if self.world <= 1 or i >= len(self.buckets):
+            return
+        import torch.distributed as dist
+        lo, hi = self.buckets[i]
+        ev = torch.cuda.Event()
+        ev.record()
+        self.comm_stream.wait_event(ev)
+        with torch.cuda.stream(self.comm_stream):
+            dist.all_reduce(self.arena.g[lo:hi], group=self.group)
+
+    # -- helpers ------------------------------------------------------------------------------
+    @staticmethod
+    def _dgrad(mod, name, conv, dy, *, w=None, out_dtype=None):
+        """data gradient of `conv` (Conv2d / ConvTranspose2d / Linear) w.r.t. its input, on the forward kernels"""
+        w = conv.weight if w is None else w
+        dt = dy.dtype
+        if isinstance(conv, nn.ConvTranspose2d):        # convT s2 -> conv s2, weight read as [co = cin_T][ci = cout_T]
+            wp = mod._cached((name, "dg", dt), (conv.weight,), lambda: ops.pack_weight(w, dt))
+            return ops.conv(dy, wp, None, ksize=conv.kernel_size[0], stride=2, out_dtype=out_dtype)
+        if isinstance(conv, nn.Conv2d) and conv.stride[0] == 2:   # conv s2 -> convT s2, weight read as [cin_T = co][cout_T = ci]
+            wp = mod._cached((name, "dg", dt), (conv.weight,), lambda: ops.pack_weight(w, dt, transposed=True))
+            return ops.conv(dy, wp, None, ksize=3, stride=2, transposed=True, out_dtype=out_dtype)
+        k = 1 if w.dim() == 2 else w.shape[2]           # stride-1 conv / Linear: flipped-tap, transposed pack
+        wp = mod._cached((name, "dg", dt), (conv.weight if hasattr(conv, "weight") else w,), lambda: ops.pack_weight_dgrad(w, dt))
+        return ops.conv(dy, wp, None, ksize=k, stride=1, out_dtype=out_dtype)
+
+    def _dec_layer(self, name, conv, bn, x, adt):
+        dec = self.model.decoder
+        c = bn.num_features
+        stats = torch.zeros(2 * c, dtype=torch.float64, device=x.device)
+        v = ops.conv(x, dec._packed(name, conv.weight, adt, True), dec._f32(name + ".b", conv.bias), ksize=4, stride=2, transposed=True,
+                     act=ACT_NONE, stats=stats, out_dtype=adt)
+        Mo._sync_bn_stats(stats)
+        mean, invstd = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+        rows = v.numel() // c
+        h = ops.bn_apply(v, stats, bn.weight.detach(), bn.bias.detach(), count=rows * self.world, eps=bn.eps,
+                         momentum=bn.momentum if bn.momentum is not None else 0.1, act=ACT_RELU, out_dtype=adt,
+                         running_mean=bn.running_mean, running_var=bn.running_var, save_mean=mean, save_invstd=invstd)
+        bn.num_batches_tracked.add_(1)
+        return v, h, mean, invstd
+
+    def _attn_fwd(self, ca, feat, style):
+        e, m, adt = ca.embed_dim, ca.multihead_attn, feat.dtype
+        b, h, w, _ = feat.shape
+        kv = ca._project_style(style)
+        wq = ca._cached(("wq", adt), (m.in_proj_weight,), lambda: ops.pack_weight(m.in_proj_weight.detach()[:e], adt))
+        bq = ca._cached(("bq",), (m.in_proj_bias,), lambda: m.in_proj_bias.detach()[:e].float().contiguous())
+        q = ops.conv(feat, wq, bq, ksize=1)
+        kv2 = kv.view(b, kv.shape[1] * kv.shape[2], 2 * e)
+        o = ops.attention(q.view(b, h * w, e), kv2[:, :, :e], kv2[:, :, e:], ca.num_heads)
+        out = ops.conv(o.view(b, h, w, e), ca._packed("wo", m.out_proj.weight, adt), ca._f32("bo", m.out_proj.bias), ksize=1)
+        return out, dict(feat=feat, style=style, q=q, kv=kv2, o=o)
+
+    def _attn_bwd(self, ca, sv, d_out):
+        """d_out: gradient w.r.t. the attention output [b,h,w,e] -> (d_feat, d_style); parameter grads accumulated"""
+        e, m = ca.embed_dim, ca.multihead_attn
+        b, h, w, _ = d_out.shape
+        feat, style, q, kv, o = sv["feat"], sv["style"], sv["q"], sv["kv"], sv["o"]
+        ops.act_bwd(d_out, None, act=ACT_NONE, dbias=m.out_proj.bias.grad, want_g=False)
+        ops.wgrad(o.view(b, h, w, e), d_out, m.out_proj.weight.grad, ksize=1)
+        d_o = self._dgrad(ca, "wo", m.out_proj, d_out)
+        dq, dkv = ops.attention_bwd(q.view(b, h * w, e), kv[:, :, :e], kv[:, :, e:], d_o.view(b, h * w, e), ca.num_heads)
+        dq4, dkv4 = dq.view(b, h, w, e), dkv.view(b, style.shape[1], style.shape[2], 2 * e)
+        gw, gb = m.in_proj_weight.grad, m.in_proj_bias.grad
+        ops.act_bwd(dq4, None, act=ACT_NONE, dbias=gb[:e], want_g=False)
+        ops.act_bwd(dkv4, None, act=ACT_NONE, dbias=gb[e:], want_g=False)
+        ops.wgrad(feat, dq4, gw[:e], ksize=1)
+        ops.wgrad(style, dkv4, gw[e:], ksize=1)
+        wq_, wkv_ = m.in_proj_weight.detach()[:e], m.in_proj_weight.detach()[e:]
+        d_feat = ops.conv(dq4, ca._cached(("wq", "dg", dq.dtype), (m.in_proj_weight,), lambda: ops.pack_weight_dgrad(wq_, dq.dtype)), None, ksize=1)
+        d_style = ops.conv(dkv4, ca._cached(("wkv", "dg", dq.dtype), (m.in_proj_weight,), lambda: ops.pack_weight_dgrad(wkv_, dq.dtype)), None, ksize=1)
+        return d_feat, d_style
+
+    def _relu_conv_bwd(self, mod, name, conv, x_in, y_relu, dy, dy2=None, need_dx=True):
+        """backward of y = ReLU(conv(x) + b): bias / weight gradients accumulated, returns dL/dx"""
+        g = ops.act_bwd(dy, y_relu, act=ACT_RELU, dy2=dy2, dbias=conv.bias.grad)
+        tr = isinstance(conv, nn.ConvTranspose2d)
+        ops.wgrad(x_in, g, conv.weight.grad, ksize=conv.kernel_size[0], stride=conv.stride[0], transposed=tr)
+        return self._dgrad(mod, name, conv, g) if need_dx else None
+
+    # -- the step ---------------------------------------------------------------------------
+    def train_step_device(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """One optimisation step on this rank's shard.  ``t`` [B] int64 and ``noise`` [B,C,h,w] (NCHW, the reference's
+        randn_like shape) may be passed in (parity tests, data-parallel sharding of a globally drawn batch); otherwise
+        they are drawn as the reference does (train.py:172, model.py:110).  Returns the four losses as 0-dim tensors."""
+        model = self.model
+        u, dec, sty = model.unet, model.decoder, model.style_encoder
+        d = dec.decoder
+        if not d[1].training:
+            raise MstkError("LDMTrainer: call model.train() first (train.py:212); the step back-propagates through train-mode BatchNorm")
+        adt = Mo._act_dtype(model._precision())
+        lp = adt == torch.bfloat16
+        xs = model._spec_nhwc(content_spec, "train_step")
+        ss = model._spec_nhwc(style_spec, "train_step")
+        dev, B = xs.device, xs.shape[0]
+        ab = model.noise_scheduler.alpha_bar_t
+        self.arena.g.zero_()                                                     # optimizer.zero_grad()
+        if t is None:
+            t = torch.randint(0, model.num_timesteps, (B,), device=dev)
+        t = t.to(device=dev, dtype=torch.int64).contiguous()
+
+        # ================= forward (LDM.forward, model.py:355-379), intermediates kept =================
+        z0 = model.encoder._forward_nhwc(xs)                                     # frozen; BatchNorm in train mode (train.py:212)
+        _, h, w, c = z0.shape
+        S = sty._forward_nhwc(ss)                                                # six post-ReLU maps
+        if noise is None:
+            noise = torch.randn((B, c, h, w), dtype=torch.float32, device=dev)
+        noise_l = ops.nchw_to_nhwc(noise.to(dev).float().contiguous(), torch.float32)
+        z_t, z_t_lp = ops.q_sample(z0, noise_l, ab, t, lp=lp)
+        zin = z_t_lp if lp else z_t
+        l1, l2 = u.time_mlp[1], u.time_mlp[3]
+        temb, te_e, te_pre, te_h = ops.time_embed_train(t.to(torch.float32), l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach())
+        z1 = u._conv("enc1", zin, act=ACT_RELU)
+        r2 = u._conv("enc2", z1, act=ACT_RELU)
+        z2 = ops.add_bcast(r2, add_nc=temb)
+        z3 = u._conv("enc3", z2, act=ACT_RELU)
+        a3, sv2 = self._attn_fwd(u.cross_attention2, z3, S[4])
+        z4 = u._conv("enc4", a3, act=ACT_RELU)
+        a4, sv1 = self._attn_fwd(u.cross_attention1, z4, S[5])
+        bt = u._conv("bottleneck", a4, act=ACT_RELU)
+        r_d4 = u._conv("dec4", bt, act=ACT_RELU); d4 = ops.add_bcast(r_d4, add=z3)
+        r_d3 = u._conv("dec3", d4, act=ACT_RELU); d3 = ops.add_bcast(r_d3, add=z2)
+        r_d2 = u._conv("dec2", d3, act=ACT_RELU); d2 = ops.add_bcast(r_d2, add=z1)
+        eps_hat = u._conv("dec1", d2, act=ACT_NONE, out_dtype=torch.float32)
+        z0p, z0p_lp = ops.predict_x0(z_t, eps_hat, ab, t, lp=lp)
+        dec_in = z0p_lp if lp else z0p
+        v1, h1, mean1, inv1 = self._dec_layer("d0", d[0], d[1], dec_in, adt)
+        v2, h2, mean2, inv2 = self._dec_layer("d3", d[3], d[4], h1, adt)
+        rec = ops.conv(h2, dec._packed("d6", d[6].weight, adt, True), dec._f32("d6.b", d[6].bias), ksize=4, stride=2, transposed=True,
+                       act=ACT_TANH, out_dtype=torch.float32, out_scale=0.5, out_shift=0.5)      # reconstructed = (tanh + 1) / 2
+
+        # ================= losses (train.py:182-186) =================
+        den = ops.mse(eps_hat, noise_l).squeeze(0)
+        mse_rec = ops.mse(rec, xs).squeeze(0)
+        kl = ops.kl(z0).squeeze(0)
+        fl = model.feature_loss_net
+        H, W = xs.shape[1], xs.shape[2]
+        three = torch.empty((3 * B, H, W, 1), dtype=torch.float32, device=dev)
+        three[:B].copy_(xs); three[B:2 * B].copy_(rec); three[2 * B:].copy_(ss)
+        taps = fl._taps(three)                                                   # one pass of the frozen stack for all three images
+        perc = torch.zeros(1, dtype=torch.float32, device=dev)
+        styl = torch.zeros(1, dtype=torch.float32, device=dev)
+        for f in taps:
+            ops.feature_std_mse(f[:B], f[B:2 * B], 1.0 / len(taps), perc)         # compression_loss's perceptual term (loss.py:40)
+            ops.feature_std_mse(f[B:2 * B], f[2 * B:], 1.0 / len(taps), styl)     # style_loss (loss.py:104-106)
+        comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
+        total = comp + den + self.style_loss_weight * styl.squeeze(0)
+
+        # ================= backward =================
+        # reconstruction path: d/drec of mean((rec - x)^2); tanh and the (y+1)/2 folded into act_bwd
+        g_rec = ops.mse_grad(rec, xs, 2.0 / rec.numel(), torch.float32)
+        g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=d[6].bias.grad, y_scale=0.5, y_shift=0.5)
+        ops.wgrad(h2, g6, d[6].weight.grad, ksize=4, stride=2, transposed=True)
+        w6 = dec._cached(("d6", "dg32"), (d[6].weight,), lambda: ops.pack_weight(d[6].weight, torch.float32))
+        dh2 = ops.conv(g6, w6, None, ksize=4, stride=2, out_dtype=adt)
+        dv2 = ops.bn_bwd(dh2, v2, mean2, inv2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=d[4].weight.grad,
+                         dbeta=d[4].bias.grad, world=self.world, sync=self._sync_sums)
+        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=d[3].bias.grad, want_g=False)
+        ops.wgrad(h1, dv2, d[3].weight.grad, ksize=4, stride=2, transposed=True)
+        dh1 = self._dgrad(dec, "d3", d[3], dv2)
+        dv1 = ops.bn_bwd(dh1, v1, mean1, inv1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=d[1].weight.grad,
+                         dbeta=d[1].bias.grad, world=self.world, sync=self._sync_sums)
+        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=d[0].bias.grad, want_g=False)
+        ops.wgrad(dec_in, dv1, d[0].weight.grad, ksize=4, stride=2, transposed=True)
+        dz0p = self._dgrad(dec, "d0", d[0], dv1)
+        # eps_hat gathers the denoising loss and the reconstruction path through x0_pred (model.py:117-124)
+        g_eps = ops.eps_grad(dz0p, eps_hat, noise_l, ab, t, 2.0 / eps_hat.numel(), adt)
+        # ---- UNet, top-down ----
+        ops.act_bwd(g_eps, None, act=ACT_NONE, dbias=u.dec1.bias.grad, want_g=False)
+        ops.wgrad(d2, g_eps, u.dec1.weight.grad, ksize=3)
+        dd2 = self._dgrad(u, "dec1", u.dec1, g_eps)
+        dd3 = self._relu_conv_bwd(u, "dec2", u.dec2, d3, r_d2, dd2)
+        dd4 = self._relu_conv_bwd(u, "dec3", u.dec3, d4, r_d3, dd3)
+        dbt = self._relu_conv_bwd(u, "dec4", u.dec4, bt, r_d4, dd4)
+        self._reduce_bucket(0)
+        da4 = self._relu_conv_bwd(u, "bottleneck", u.bottleneck, a4, bt, dbt)
+        dz4, ds6_attn = self._attn_bwd(u.cross_attention1, sv1, da4)
+        da3 = self._relu_conv_bwd(u, "enc4", u.enc4, a3, z4, dz4)
+        dz3a, ds5_attn = self._attn_bwd(u.cross_attention2, sv2, da3)
+        dz2c = self._relu_conv_bwd(u, "enc3", u.enc3, z2, z3, dz3a, dy2=dd4)        # + skip gradient of dec4's add
+        # z2 = ReLU(enc2(z1)) + t_emb: its gradient is dz2c + dd3 (skip of dec3's add)
+        dtemb = ops.sum_hw(dz2c, dd3)
+        dz1c = self._relu_conv_bwd(u, "enc2", u.enc2, z1, r2, dz2c, dy2=dd3)
+        self._relu_conv_bwd(u, "enc1", u.enc1, zin, z1, dz1c, dy2=dd2, need_dx=False)
+        # time MLP (model.py:170-175): Linear2 <- GELU <- Linear1 <- sinusoid
+        nb = dtemb.shape[0]
+        dt4 = dtemb.view(nb, 1, 1, -1)
+        ops.act_bwd(dt4, None, act=ACT_NONE, dbias=l2.bias.grad, want_g=False)
+        ops.wgrad(te_h.view(nb, 1, 1, -1), dt4, l2.weight.grad, ksize=1)
+        dh = self._dgrad(u, "t2", l2, dt4)
+        dpre = ops.gelu_bwd(dh.view(nb, -1), te_pre).view(nb, 1, 1, -1)
+        ops.act_bwd(dpre, None, act=ACT_NONE, dbias=l1.bias.grad, want_g=False)
+        ops.wgrad(te_e.view(nb, 1, 1, -1), dpre, l1.weight.grad, ksize=1)
+        self._reduce_bucket(1)
+        # ---- style encoder: s6 feeds attention1, s5 feeds attention2 and enc6 ----
+        ds5c = self._relu_conv_bwd(sty, "enc6", sty.enc6, S[4], S[5], ds6_attn)
+        dsk = self._relu_conv_bwd(sty, "enc5", sty.enc5, S[3], S[4], ds5c, dy2=ds5_attn)
+        dsk = self._relu_conv_bwd(sty, "enc4", sty.enc4, S[2], S[3], dsk)
+        dsk = self._relu_conv_bwd(sty, "enc3", sty.enc3, S[1], S[2], dsk)
+        dsk = self._relu_conv_bwd(sty, "enc2", sty.enc2, S[0], S[1], dsk)
+        self._relu_conv_bwd(sty, "enc1", sty.enc1, ss, S[0], dsk, need_dx=False)
+        self._reduce_bucket(2)
+
+        # ================= update (torch.optim.Adam, train.py:156, 200) =================
+        if self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.step_count += 1
+        ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
+                      eps=self.eps, step=self.step_count, grad_scale=1.0 / self.world)
+        for m in model.modules():                       # parameters changed under the packed copies
+            if m is not fl:
+                m.__dict__.pop("_mstk_cache", None)
+        return {"compression_loss": comp, "denoisinsg_loss": den, "style_loss": styl.squeeze(0), "total_loss": total}

@@ -125,8 +125,9 @@ def test_time_mlp_pieces_and_small_ops():
     e_ref = O.sinusoidal_embedding(t, 128)
     pre_ref = F.linear(e_ref, w1, b1).requires_grad_(True)
     out_ref = F.linear(F.gelu(pre_ref), w2, b2)
-    out, e, pre = ops.time_embed_train(t.to(DEV), w1.to(DEV), b1.to(DEV), w2.to(DEV), b2.to(DEV))
+    out, e, pre, hh = ops.time_embed_train(t.to(DEV), w1.to(DEV), b1.to(DEV), w2.to(DEV), b2.to(DEV))
     assert_close(e, e_ref, 1e-5, "sinusoid"); assert_close(pre, pre_ref, 1e-5, "pre"); assert_close(out, out_ref, 1e-5, "out")
+    assert_close(hh, F.gelu(pre_ref.detach()), 1e-5, "gelu(pre)")
     dh = torch.randn(pre_ref.shape, generator=g)
     F.gelu(pre_ref).backward(dh)
     assert_close(ops.gelu_bwd(dh.to(DEV), pre_ref.detach().to(DEV)), pre_ref.grad, 1e-5, "gelu'")
