@@ -27,7 +27,7 @@ STEPS, B, LR, W = 3, 2, 5e-4, 3.0
 # Adam turns into full +-lr steps, so their values are not reproducible across summation orders (nor do they matter).
 SAVE_KEYS = ["decoder.decoder.6.weight", "decoder.decoder.4.weight", "decoder.decoder.1.weight", "unet.dec1.bias", "unet.enc2.bias",
              "unet.time_mlp.1.bias", "unet.cross_attention2.multihead_attn.in_proj_bias", "style_encoder.enc1.weight",
-             "decoder.decoder.1.running_mean", "encoder.encoder.1.running_var"]
+             "decoder.decoder.1.running_var", "encoder.encoder.1.running_var"]
 
 
 def step_inputs(i):

@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_backward_ops.py -q -m gpu --timeout 300 > gpurun_out/t_bwd.log 2>&1; echo "bwd tests rc=$?"; tail -n 40 gpurun_out/t_bwd.log
+timeout 1200 python -m pytest tests/test_gpu_train.py -q -m gpu --timeout 600 -s > gpurun_out/t_train.log 2>&1; echo "train tests rc=$?"; tail -n 40 gpurun_out/t_train.log
