@@ -81,6 +81,57 @@ def _backward_order(model) -> List[nn.Parameter]:
     return out
 
 
+class GradReducer:
+    """Data-parallel exchange of the training step: bucketed all-reduce (sum) of the flat gradient arena, issued per
+    bucket behind the backward kernels that fill it and overlapped with the rest of the sweep on a side stream, plus
+    the small all-reduces of BatchNorm statistics.  Works on CPU tensors too (gloo, synchronous) for the host-logic tests."""
+
+    def __init__(self, grads: torch.Tensor, buckets, group=None, world_size: int = 1):
+        self.g, self.buckets, self.group, self.world = grads, list(buckets), group, int(world_size)
+        self.stream = torch.cuda.Stream(device=grads.device) if (self.world > 1 and grads.is_cuda) else None
+        lo = 0
+        for a, b in self.buckets:
+            if a != lo or b <= a:
+                raise MstkError(f"GradReducer: buckets must tile the arena contiguously, got {self.buckets}")
+            lo = b
+        if lo != grads.numel():
+            raise MstkError("GradReducer: buckets do not cover the arena")
+
+    def all_reduce_small(self, t: torch.Tensor) -> None:
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, group=self.group)
+
+    def reduce_bucket(self, i: int) -> None:
+        if self.world <= 1 or i >= len(self.buckets):
+            return
+        import torch.distributed as dist
+        lo, hi = self.buckets[i]
+        if self.stream is None:
+            dist.all_reduce(self.g[lo:hi], group=self.group)
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            dist.all_reduce(self.g[lo:hi], group=self.group)
+
+    def wait(self) -> None:
+        if self.stream is not None:
+            torch.cuda.current_stream().wait_stream(self.stream)
+
+
+def bucket_spans(model, arena: "_Arena", num_buckets: int = 3):
+    """contiguous [lo, hi) slices of the arena in backward-completion order: decoder + UNet decoder half,
+    UNet bottleneck/attention/encoder half + time MLP, style encoder"""
+    u, s, d = model.unet, model.style_encoder, model.decoder.decoder
+    cuts = [(d[6].weight, u.dec4.bias), (u.bottleneck.weight, u.enc1.bias), (s.enc6.weight, s.enc1.bias)]
+    spans = [arena.span(a, b) for a, b in cuts]
+    n = max(1, min(3, num_buckets))
+    merged = spans[:n - 1] + [(spans[n - 1][0], arena.size)]
+    return merged
+
+
 class LDMTrainer:
     def __init__(self, model, train_loader, device, lr=1e-4, style_loss_weight=0.1, process_group=None, world_size: int = 1,
                  num_buckets: int = 3):
@@ -103,16 +154,15 @@ class LDMTrainer:
         for m in self.model.modules():                        # packed-weight caches point at the old storages
             m.__dict__.pop("_mstk_cache", None)
         # gradient buckets for the data-parallel all-reduce, in backward-completion order
-        u, s, d = self.model.unet, self.model.style_encoder, self.model.decoder.decoder
-        cuts = [(d[6].weight, u.dec4.bias), (u.bottleneck.weight, u.enc1.bias), (s.enc6.weight, s.enc1.bias)]
-        self.buckets = [self.arena.span(a, b) for a, b in cuts][:max(1, num_buckets)]
-        if len(self.buckets) < 3:
-            self.buckets[-1] = (self.buckets[-1][0], self.arena.size)
-        self.comm_stream = torch.cuda.Stream(device=self.device) if self.world > 1 else None
+        self.buckets = bucket_spans(self.model, self.arena, num_buckets)
+        self.reducer = GradReducer(self.arena.g, self.buckets, self.group, self.world)
         if self.world > 1:
             Mo.set_bn_sync_group(self.group, self.world)
             import torch.distributed as dist
-            dist.broadcast(self.arena.p, src=0, group=self.group)        # identical replicas (buffers: see sync_buffers)
+            dist.broadcast(self.arena.p, src=0, group=self.group)        # identical replicas
+            for b in self.model.buffers():                                # BatchNorm running buffers
+                if b.dtype.is_floating_point:
+                    dist.broadcast(b, src=0, group=self.group)
 
     # -- reference API ----------------------------------------------------------------------
     def train_step(self, content_spec, style_spec):
@@ -121,21 +171,15 @@ class LDMTrainer:
         return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), vals))
 
     def _sync_sums(self, sums):
-        if self.world > 1:
-            import torch.distributed as dist
-            dist.all_reduce(sums, group=self.group)
+        self.reducer.all_reduce_small(sums)
 
-    def _reduce_bucket(self, i: int):
-        """all-reduce bucket i of the gradient arena on the side stream, behind everything enqueued so far"""
-        if self.world <= 1 or i >= len(self.buckets):
-            return
-        import torch.distributed as dist
-        lo, hi = self.buckets[i]
-        ev = torch.cuda.Event()
-        ev.record()
-        self.comm_stream.wait_event(ev)
-        with torch.cuda.stream(self.comm_stream):
-            dist.all_reduce(self.arena.g[lo:hi], group=self.group)
+    def _reduce_bucket(self, stage: int):
+        """the backward sweep finished stage 0 (decoder + UNet decoder half), 1 (rest of the UNet) or 2 (style encoder):
+        launch the all-reduce of every bucket that is complete now (the last bucket always ends with stage 2)"""
+        n = len(self.buckets)
+        for b in range(n):
+            if (b if b < n - 1 else 2) == stage:
+                self.reducer.reduce_bucket(b)
 
     # -- helpers ------------------------------------------------------------------------------
     @staticmethod
@@ -331,12 +375,15 @@ class LDMTrainer:
         self._reduce_bucket(2)
 
         # ================= update (torch.optim.Adam, train.py:156, 200) =================
-        if self.world > 1:
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.reducer.wait()
         self.step_count += 1
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
                       eps=self.eps, step=self.step_count, grad_scale=1.0 / self.world)
         for m in model.modules():                       # parameters changed under the packed copies
             if m is not fl:
                 m.__dict__.pop("_mstk_cache", None)
-        return {"compression_loss": comp, "denoisinsg_loss": den, "style_loss": styl.squeeze(0), "total_loss": total}
+        losses = torch.stack([comp, den, styl.squeeze(0), total])
+        if self.world > 1:                              # report the GLOBAL batch's losses (equal shards: mean of the ranks' means)
+            self.reducer.all_reduce_small(losses)
+            losses = losses / self.world
+        return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), losses.unbind(0)))
