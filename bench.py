@@ -187,6 +187,84 @@ def kernel_roofline(model, peaks, reps=20):
 
 
 # ------------------------------------------------------------------------------------------
+# training leg (BASELINE config 4): LDMTrainer.train_step, bf16, GLOBAL batch 256 sharded over the ranks
+# ------------------------------------------------------------------------------------------
+TRAIN_GLOBAL_BATCH = 256
+
+
+def train_leg(args, rank, world, dev, barrier):
+    """Returns a dict for the JSON line (rank 0) with train samples/s: device-resident and end-to-end
+    (pinned host batch -> device inside the timed region, 4 loss scalars read back every step)."""
+    import torch
+    import torch.distributed as dist
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200 import ops
+    from music_style_transfer_ldm_b200.train import LDMTrainer
+    from oracle import ldm_oracle as O
+    if TRAIN_GLOBAL_BATCH % world:
+        return {"skipped": f"global batch {TRAIN_GLOBAL_BATCH} not divisible by {world} ranks"}
+    per = TRAIN_GLOBAL_BATCH // world
+    model = M.LDM(latent_dim=32, pretrained_path=None)
+    model.load_state_dict(O.make_state_dict(1234), strict=True)
+    model._freeze_encoder()
+    model.to(dev).set_precision(args.precision)
+    tr = LDMTrainer(model, None, dev, lr=5e-4, style_loss_weight=3.0, process_group=None, world_size=world)
+    model.train()
+    g = torch.Generator().manual_seed(500 + rank)
+    xh = torch.rand((per, 1, SPEC, SPEC), generator=g).pin_memory()
+    sh = torch.rand((per, 1, SPEC, SPEC), generator=g).pin_memory()
+    xd, sd_ = xh.to(dev), sh.to(dev)
+    loss_h = torch.empty(4).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    steps = max(2, min(args.steps, 8))
+
+    def step_device():
+        return tr.train_step_device(xd, sd_)
+
+    def step_e2e():
+        out = tr.train_step_device(xh.to(dev, non_blocking=True), sh.to(dev, non_blocking=True))
+        loss_h.copy_(torch.stack([out[k] for k in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]), non_blocking=True)
+
+    def timed(fn, k):
+        evs = []
+        for _ in range(k):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)
+
+    for _ in range(3):
+        step_device()
+    step_e2e()
+    torch.cuda.synchronize()
+    n0 = ops.LAUNCHES
+    step_device()
+    torch.cuda.synchronize()
+    launches = ops.LAUNCHES - n0
+    barrier()
+    ms = timed(step_device, steps)
+    barrier()
+    ms_e2e = timed(step_e2e, steps)
+    barrier()
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = t.tolist()
+    final = [float(v) for v in loss_h.tolist()]
+    del tr, model
+    torch.cuda.empty_cache()
+    return {"metric": "train_samples_per_s", "value": TRAIN_GLOBAL_BATCH * steps / (ms * 1e-3), "unit": "samples/s",
+            "ms_per_step": ms / steps, "steps": steps, "global_batch": TRAIN_GLOBAL_BATCH, "batch_per_gpu": per, "scaling": "strong",
+            "e2e": {"value": TRAIN_GLOBAL_BATCH * steps / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / steps,
+                    "h2d_bytes_per_step": 2 * xh.numel() * 4, "d2h_bytes_per_step": 16},
+            "gpu_launches_per_step": int(launches), "last_losses": final,
+            "workload": "config4: LDMTrainer.train_step (fwd + 4 losses incl. 2 VGGish feature losses + bwd + Adam), bf16, "
+                        "1x128x128 spectrograms, encoder frozen, style_loss_weight 3.0, DDP gradient + BatchNorm-stat all-reduce"}
+
+
+# ------------------------------------------------------------------------------------------
 # CUDA arm
 # ------------------------------------------------------------------------------------------
 def run_cuda(args):
@@ -267,6 +345,14 @@ def run_cuda(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = t.tolist()
+    train = None
+    if not args.no_train:
+        del model
+        torch.cuda.empty_cache()
+        train = train_leg(args, rank, world, dev, barrier)
+        model = M.LDM(latent_dim=32, pretrained_path=None)          # fresh sampler model for the roofline leg
+        model.load_state_dict(sd, strict=True)
+        model.to(dev).eval().set_precision(args.precision)
     unet_steps = (NSTEPS - 1) * args.steps * world
     value = unet_steps / (ms * 1e-3)
     e2e_value = unet_steps / (ms_e2e * 1e-3)
@@ -293,7 +379,7 @@ def run_cuda(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
-            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train,
             "samples_steps_per_s": value * BATCH,
             "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
             "layers": rows,
@@ -311,6 +397,7 @@ def main():
     ap.add_argument("--impl", default="mstk", choices=["mstk", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step leg")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps is None:
