@@ -141,7 +141,8 @@ typedef struct mstk_bn_args {
     float* running_var;     /* optional [c]                                         */
     float* save_mean;       /* optional [c]: batch mean (for backward)              */
     float* save_invstd;     /* optional [c]: 1/sqrt(var+eps)                        */
-    int64_t count;          /* rows = N*H*W (global count under data parallelism)   */
+    int64_t count;          /* statistics count = N*H*W over ALL ranks (what `stats` sums over) */
+    int64_t rows;           /* rows of x / y held by THIS rank (0 = same as count)      */
     int32_t c;
     float eps, momentum;
     int32_t act;            /* MSTK_ACT_NONE or MSTK_ACT_RELU                       */

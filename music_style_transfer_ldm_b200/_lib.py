@@ -41,7 +41,7 @@ class ConvArgs(C.Structure):
 class BnArgs(C.Structure):
     _fields_ = [("x", c_void_p), ("y", c_void_p), ("stats", c_void_p), ("gamma", c_void_p), ("beta", c_void_p),
                 ("running_mean", c_void_p), ("running_var", c_void_p), ("save_mean", c_void_p),
-                ("save_invstd", c_void_p), ("count", c_int64), ("c", c_int), ("eps", c_float),
+                ("save_invstd", c_void_p), ("count", c_int64), ("rows", c_int64), ("c", c_int), ("eps", c_float),
                 ("momentum", c_float), ("act", c_int), ("dtype", c_int), ("out_dtype", c_int)]
 
 

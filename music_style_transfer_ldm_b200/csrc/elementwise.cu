@@ -90,7 +90,7 @@ __global__ void cast_kernel(const void* __restrict__ src, int sd, void* dst, int
 struct BnP {
     const void* x; void* y; const double* stats; const float* gamma; const float* beta;
     float* running_mean; float* running_var; float* save_mean; float* save_invstd;
-    long long count; int c; float eps, momentum; int act, dtype, out_dtype;
+    long long count, rows; int c; float eps, momentum; int act, dtype, out_dtype;
 };
 
 // one thread handles 8 consecutive channels of one row (requires c % 8 == 0) or falls
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
         }
     }
     __syncthreads();
-    const size_t total = (size_t)a.count * a.c;
+    const size_t total = (size_t)a.rows * a.c;
     if ((a.c & 7) == 0) {
         const size_t nvec = total >> 3;
         for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
@@ -512,12 +512,12 @@ int mstk_cast(const void* src, int sd, void* dst, int dd, size_t count, void* st
 
 int mstk_bn_apply(const mstk_bn_args* a, void* stream) {
     MSTK_REQUIRE(a && a->x && a->y && a->stats, "bn_apply: null");
-    MSTK_REQUIRE(a->c > 0 && a->c <= 4096 && a->count > 0, "bn_apply: bad dims");
+    MSTK_REQUIRE(a->c > 0 && a->c <= 4096 && a->count > 0 && a->rows >= 0 && a->rows <= a->count, "bn_apply: bad dims");
     BnP p;
     p.x = a->x; p.y = a->y; p.stats = a->stats; p.gamma = a->gamma; p.beta = a->beta;
     p.running_mean = a->running_mean; p.running_var = a->running_var; p.save_mean = a->save_mean; p.save_invstd = a->save_invstd;
-    p.count = a->count; p.c = a->c; p.eps = a->eps; p.momentum = a->momentum; p.act = a->act; p.dtype = a->dtype; p.out_dtype = a->out_dtype;
-    const size_t total = (size_t)a->count * a->c;
+    p.count = a->count; p.rows = a->rows > 0 ? a->rows : a->count; p.c = a->c; p.eps = a->eps; p.momentum = a->momentum; p.act = a->act; p.dtype = a->dtype; p.out_dtype = a->out_dtype;
+    const size_t total = (size_t)p.rows * a->c;
     const size_t items = (a->c & 7) == 0 ? total / 8 : total;
     bn_apply_kernel<<<grid_for(items, 256), 256, 2 * a->c * sizeof(float), (cudaStream_t)stream>>>(p);
     MSTK_CHECK_LAUNCH("bn_apply");

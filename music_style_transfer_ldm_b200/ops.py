@@ -219,7 +219,7 @@ def bn_apply(x: torch.Tensor, stats: torch.Tensor, gamma, beta, *, count: int, e
     c = x.shape[-1]
     y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
     a = _lib.BnArgs(_p(x), _p(y), _p(stats), _p(gamma), _p(beta), _p(running_mean), _p(running_var), _p(save_mean),
-                    _p(save_invstd), count, c, eps, momentum, act, dtype_code(x), dtype_code(out_dtype))
+                    _p(save_invstd), count, x.numel() // c, c, eps, momentum, act, dtype_code(x), dtype_code(out_dtype))
     check(lib.mstk_bn_apply(C.byref(a), _stream()), "mstk_bn_apply")
     _count(1)
     return y
