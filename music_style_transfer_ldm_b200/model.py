@@ -45,7 +45,7 @@ class _Kernelised(nn.Module):
         if p not in (None, "fp32", "bf16"):
             raise ValueError("precision must be 'fp32', 'bf16' or None (inherit default)")
         for m in self.modules():
-            if isinstance(m, _Kernelised):
+            if isinstance(m, _Kernelised) or hasattr(m, "_taps"):      # _taps: the VGGishFeatureLoss stack (loss.py)
                 m.precision = p
         return self
 
