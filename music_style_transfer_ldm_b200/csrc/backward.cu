@@ -523,6 +523,7 @@ int mstk_conv2d_wgrad(const mstk_wgrad_args* a, void* stream) {
     const int kk = a->ksize * a->ksize;
     if (a->transposed) { q.s_ci = (long long)a->cout * kk; q.s_co = kk; }
     else { q.s_co = (long long)a->cin * kk; q.s_ci = kk; }
+    if (wgrad_tc_supported(q.p, a->x_dtype, a->dy_dtype)) return launch_wgrad_tc(q.p, a->dw, q.s_co, q.s_ci, (cudaStream_t)stream);
     q.npt = 0;
     for (int i = 0; i < q.p.nphases; ++i) q.npt += q.p.ph[i].ntaps;
     const long long K = (long long)q.p.N * q.p.Hg * q.p.Wg;

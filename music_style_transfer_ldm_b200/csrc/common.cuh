@@ -93,6 +93,9 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
 bool conv_tc_supported(const ConvP& p);
 size_t conv_tc_workspace_bytes(const ConvP& p);
 bool tc_init();
+// tcgen05 weight gradient (wgrad_tc.cu); `p` = forward plan with p.x = input, p.y = dy
+bool wgrad_tc_supported(const ConvP& p, int x_dtype, int dy_dtype);
+int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, cudaStream_t st);
 void tc_set_debug(long long* p);
 void tc_set_force(int bn, int sk, int stages, int pdl);
 const int* tc_last_config();

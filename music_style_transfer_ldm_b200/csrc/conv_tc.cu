@@ -31,11 +31,11 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace mstk {
 
 constexpr int TC_THREADS = 192;
-constexpr int TILE_M = 128;
 constexpr int MAX_STAGES = 8;
 
 struct TcMaps {
@@ -68,136 +68,6 @@ struct TcParams {
     long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
 };
 #define DBG_STAMP(i) do { if (q.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) q.dbg[i] = clock64(); } while (0)
-
-// ---------------------------------------------------------------------------
-// PTX wrappers
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}\n"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return ok;
-}
-// Bounded wait: a pipeline bug must surface as a launch failure (trap), never as a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t a = smem_u32(bar);
-    if (mbar_try_wait(a, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(a, parity)) {
-        if (clock64() - t0 > 4000000000ll) __trap();   // ~2 s at 2 GHz
-    }
-}
-__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, uint32_t dst, int c0, int c1, int c2, int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
-        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, uint32_t dst, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
-    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map), "r"(src), "r"(c0),
-                 "r"(c1), "r"(c2), "r"(c3)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, uint32_t src, uint32_t bytes) {
-    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gdst), "r"(src), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(gsrc),
-                 "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// K-major operand tile in shared memory, rows of KC bf16 (64 -> 128 B rows / SWIZZLE_128B,
-// 32 -> 64 B rows / SWIZZLE_64B), 8-row groups SBO bytes apart.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, int kc) {
-    const uint32_t sbo = (uint32_t)(8 * kc * 2);                 // 1024 or 512
-    const uint64_t layout = (kc == 64) ? 2ull : 4ull;            // SWIZZLE_128B : SWIZZLE_64B
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);                    // start address
-    d |= (uint64_t)0 << 16;                                      // LBO (unused for swizzled K-major)
-    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;                  // SBO
-    d |= 1ull << 46;                                             // descriptor version (sm_100)
-    d |= layout << 61;
-    return d;
-}
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=n
-__device__ __forceinline__ uint32_t make_idesc(int n) {
-    uint32_t d = 0;
-    d |= 1u << 4;                       // D format f32
-    d |= 1u << 7;                       // A format bf16
-    d |= 1u << 10;                      // B format bf16
-    d |= (uint32_t)(n >> 3) << 17;      // N >> 3
-    d |= (uint32_t)(TILE_M >> 4) << 24; // M >> 4
-    return d;
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// byte offset of 16-byte piece `j` of row `r` in a staging chunk with `rowbytes` bytes per row,
-// in the TMA swizzle layout of that row width (Swizzle<B,4,3>: 128 B rows -> B=3, 64 -> 2, 32 -> 1)
-__device__ __forceinline__ uint32_t swz_off(int r, int j, int rowbytes) {
-    const uint32_t o = (uint32_t)(r * rowbytes + j * 16);
-    const uint32_t mask = (uint32_t)(rowbytes >> 4) - 1u;       // 7, 3, 1
-    return o ^ (((o >> 7) & mask) << 4);
-}
 
 // ---------------------------------------------------------------------------
 // kernel
@@ -804,6 +674,18 @@ static int encode_map(CUtensorMap* m, CUtensorMapDataType dt, const void* base, 
     }
     return MSTK_OK;
 }
+
+// exported to wgrad_tc.cu: encode a bf16/f32 tiled map with the swizzle that matches `rowbytes`
+int tc_encode_map(CUtensorMap* m, int is_f32, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box, int rowbytes) {
+    cuuint64_t d[5], s[5];
+    cuuint32_t b[5];
+    for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; }
+    for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+    const CUtensorMapSwizzle sw = rowbytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : rowbytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+    return encode_map(m, is_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, d, s, b, sw);
+}
+int tc_num_sms() { return g_num_sms; }
 
 static CUtensorMapSwizzle swizzle_for(int rowbytes) {
     return rowbytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : rowbytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;

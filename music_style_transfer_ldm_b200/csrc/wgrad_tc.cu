@@ -1,0 +1,376 @@
+// tcgen05 / TMEM / TMA weight gradient of the convolution family (bf16 in, fp32 accumulate).
+//
+//   dW[tap][co][ci] = sum over GEMM pixels of dy[out pixel, co] * x[in pixel shifted by tap, ci]
+//
+// is a GEMM whose K dimension is the PIXEL index.  Both operands are NHWC, i.e. channel-contiguous:
+// they are "MN-major" UMMA operands, so no transposition is needed -- a 4-D TMA box
+// {64 channels, Wt, Ht, Nt} (128-byte rows, SWIZZLE_128B) of dy or of the tap-shifted x lands in
+// shared memory exactly in the canonical MN-major SW128 layout (8-pixel groups 1024 B apart = SBO,
+// 64-channel chunks KP*128 B apart = LBO).  Padding halos and ragged batch tiles are zero-filled by
+// TMA and contribute nothing.
+//
+// One CTA owns a 128-channel slice of the M side, a BNt-channel slice of the N side, a GROUP of up
+// to `tpc` taps of one phase (one TMEM accumulator per tap, so the tap-independent operand is loaded
+// once per group) and a range of pixel tiles (split-K).  M side = dy (Cout) unless only Cin is a
+// multiple of 128 ("swap": the accumulator is then [ci][co]).  The epilogue adds the fp32
+// accumulators into the gradient tensor in the parameter's own layout with RED.ADD.F32.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue.
+#include <cuda.h>
+#include <stdlib.h>
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace mstk {
+
+constexpr int WG_THREADS = 192;
+constexpr int WG_KP = 64;            // pixels per k-block
+constexpr int WG_MAX_STAGES = 8;
+constexpr int WG_MAX_GROUPS = 32;
+
+struct WgMaps {
+    CUtensorMap dy[4];   // per phase (strided views of dy for conv-transpose)
+    CUtensorMap x[4];    // per stride-2 parity view of x
+};
+
+struct WgGroup { int16_t phase, tap0, ntaps, pad; };
+
+struct WgParams {
+    ConvP p;                       // forward plan (phases / taps / geometry)
+    float* dw;
+    long long s_m, s_n;            // dw strides (elements) of the M-side / N-side channel
+    int32_t swap;                  // 0: M = dy channels (cout), N = x channels (cin); 1: the other way round
+    int32_t BNt;                   // N-side channels per CTA (32, 64, 128 or 256)
+    int32_t n_cc;                  // channels per N-side TMA chunk (64 -> SW128, 32 -> SW64)
+    int32_t n_chunks;              // BNt / n_cc
+    int32_t m_tiles, n_tiles, ngroups, tpc;
+    int32_t Wt, Ht, Nt, tiles_w, tiles_h, ptiles;
+    int32_t ksplit, stages, tmem_cols;
+    uint32_t m_tile_bytes, n_tile_bytes, stage_bytes;
+    WgGroup groups[WG_MAX_GROUPS];
+};
+
+// MN-major operand tile: rows of `rowbytes` (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B) per pixel,
+// 8-pixel groups `8*rowbytes` apart (SBO), channel chunks `lbo` bytes apart (LBO).
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr, int rowbytes, uint32_t lbo) {
+    const uint32_t sbo = (uint32_t)(8 * rowbytes);
+    const uint64_t layout = (rowbytes == 128) ? 2ull : 4ull;
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= 1ull << 46;
+    d |= layout << 61;
+    return d;
+}
+// kind::f16 instruction descriptor, D = f32, A = B = bf16, BOTH MN-major, M = 128, N = n
+__device__ __forceinline__ uint32_t make_idesc_mn(int n) {
+    uint32_t d = 0;
+    d |= 1u << 4;
+    d |= 1u << 7;
+    d |= 1u << 10;
+    d |= 1u << 15;                      // A MN-major
+    d |= 1u << 16;                      // B MN-major
+    d |= (uint32_t)(n >> 3) << 17;
+    d |= (uint32_t)(TILE_M >> 4) << 24;
+    return d;
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgParams q) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[WG_MAX_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[WG_MAX_STAGES];
+    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ uint32_t tmem_base_smem;
+
+    const ConvP& p = q.p;
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // work decomposition: blockIdx.x = group + ngroups * (m_tile + m_tiles * n_tile)  (taps of the same
+    // pixel range are neighbours in launch order, so the shared operand is an L2 hit), blockIdx.y = k-split
+    const int g_idx = blockIdx.x % q.ngroups;
+    const int rest = blockIdx.x / q.ngroups;
+    const int mt = rest % q.m_tiles;
+    const int nt = rest / q.m_tiles;
+    const WgGroup grp = q.groups[g_idx];
+    const Phase& ph = p.ph[grp.phase];
+    const int ntaps = grp.ntaps;
+    const int m0 = mt * TILE_M;
+    const int n0c = nt * q.BNt;
+    const int pt_begin = (int)(((long long)blockIdx.y * q.ptiles) / q.ksplit);
+    const int pt_end = (int)(((long long)(blockIdx.y + 1) * q.ptiles) / q.ksplit);
+    const int nkb = pt_end - pt_begin;
+
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int n_rowbytes = q.n_cc * 2;
+    const uint32_t m_chunk_bytes = (uint32_t)(WG_KP * 128);
+    const uint32_t n_chunk_bytes = (uint32_t)(WG_KP * n_rowbytes);
+    // stage layout: [M tiles][N tiles]; the tap-dependent side (x) holds `tpc` tiles, the other one tile
+    const uint32_t off_n = (q.swap ? (uint32_t)q.tpc : 1u) * q.m_tile_bytes;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&maps.dy[grp.phase]);
+        prefetch_tmap(&maps.x[0]);
+        for (int s = 0; s < q.stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)),
+                     "r"((uint32_t)q.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0 && nkb > 0) {
+            const uint32_t tx_bytes = (q.swap ? (uint32_t)ntaps : 1u) * q.m_tile_bytes + (q.swap ? 1u : (uint32_t)ntaps) * q.n_tile_bytes;
+            const int dy_c0 = q.swap ? n0c : m0;        // first dy channel of this CTA
+            const int x_c0 = q.swap ? m0 : n0c;         // first x channel
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % q.stages;
+                const uint32_t par = (uint32_t)((it / q.stages) & 1);
+                if (it >= q.stages) mbar_wait(&empty_bar[s], par ^ 1u);
+                const int pt = pt_begin + it;
+                const int tw = pt % q.tiles_w;
+                const int th = (pt / q.tiles_w) % q.tiles_h;
+                const int tn = pt / (q.tiles_w * q.tiles_h);
+                const int w0 = tw * q.Wt, h0 = th * q.Ht, n0 = tn * q.Nt;
+                const uint32_t st = smem_base + (uint32_t)s * q.stage_bytes;
+                mbar_expect_tx(&full_bar[s], tx_bytes);
+                // dy tile (tap independent)
+                if (!q.swap) {
+                    for (int j = 0; j < 2; ++j)
+                        tma_load_4d(&maps.dy[grp.phase], &full_bar[s], st + (uint32_t)j * m_chunk_bytes, dy_c0 + 64 * j, w0, h0, n0);
+                } else {
+                    for (int j = 0; j < q.n_chunks; ++j)
+                        tma_load_4d(&maps.dy[grp.phase], &full_bar[s], st + off_n + (uint32_t)j * n_chunk_bytes, dy_c0 + q.n_cc * j, w0, h0, n0);
+                }
+                // x tiles, one per tap of the group
+                for (int t = 0; t < ntaps; ++t) {
+                    const Tap tap = ph.taps[grp.tap0 + t];
+                    int dy = tap.dy, dx = tap.dx;
+                    const CUtensorMap* mX = &maps.x[0];
+                    if (p.s_in == 2) {
+                        const int py = dy & 1, px = dx & 1;
+                        dy = (dy - py) / 2;
+                        dx = (dx - px) / 2;
+                        mX = &maps.x[py * 2 + px];
+                    }
+                    if (q.swap) {
+                        for (int j = 0; j < 2; ++j)
+                            tma_load_4d(mX, &full_bar[s], st + (uint32_t)t * q.m_tile_bytes + (uint32_t)j * m_chunk_bytes, x_c0 + 64 * j,
+                                        w0 + dx, h0 + dy, n0);
+                    } else {
+                        for (int j = 0; j < q.n_chunks; ++j)
+                            tma_load_4d(mX, &full_bar[s], st + off_n + (uint32_t)t * q.n_tile_bytes + (uint32_t)j * n_chunk_bytes,
+                                        x_c0 + q.n_cc * j, w0 + dx, h0 + dy, n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0 && nkb > 0) {
+            const uint32_t idesc = make_idesc_mn(q.BNt);
+            const uint32_t kstep_a = (uint32_t)(16 * 128) >> 4;            // 16 pixels further along K
+            const uint32_t kstep_b = (uint32_t)(16 * n_rowbytes) >> 4;
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % q.stages;
+                const uint32_t par = (uint32_t)((it / q.stages) & 1);
+                mbar_wait(&full_bar[s], par);
+                tc_fence_after();
+                const uint32_t st = smem_base + (uint32_t)s * q.stage_bytes;
+                for (int t = 0; t < ntaps; ++t) {
+                    const uint32_t sa = st + (q.swap ? (uint32_t)t * q.m_tile_bytes : 0u);
+                    const uint32_t sb = st + off_n + (q.swap ? 0u : (uint32_t)t * q.n_tile_bytes);
+                    const uint64_t adesc = make_desc_mn(sa, 128, m_chunk_bytes);
+                    const uint64_t bdesc = make_desc_mn(sb, n_rowbytes, n_chunk_bytes);
+                    const uint32_t tacc = tmem_base + (uint32_t)(t * q.BNt);
+#pragma unroll
+                    for (int k = 0; k < WG_KP / 16; ++k)
+                        umma_bf16(tacc, adesc + (uint64_t)(k * kstep_a), bdesc + (uint64_t)(k * kstep_b), idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(&accum_bar);
+        }
+    } else if (nkb > 0) {
+        // ===================== epilogue (warps 2..5) =====================
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;
+        mbar_wait(&accum_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
+        float* drow = q.dw + (long long)(m0 + row) * q.s_m + (long long)n0c * q.s_n;
+        for (int t = 0; t < ntaps; ++t) {
+            float* dt = drow + ph.taps[grp.tap0 + t].slice;
+            for (int c = 0; c < q.BNt; c += 16) {
+                float v[16];
+                tmem_ld16(taddr + (uint32_t)(t * q.BNt + c), v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) atomicAdd(dt + (long long)(c + j) * q.s_n, v[j]);
+            }
+        }
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)q.tmem_cols) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+static int g_wg_state = 0;     // 0 unknown, 1 ok, -1 failed / disabled
+
+static bool wgrad_tc_init() {
+    if (g_wg_state != 0) return g_wg_state > 0;
+    if (const char* s = getenv("MSTK_WGRAD_TC")) {
+        if (atoi(s) == 0) { g_wg_state = -1; return false; }
+    }
+    if (!tc_init()) { g_wg_state = -1; return false; }
+    cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); g_wg_state = -1; return false; }
+    g_wg_state = 1;
+    return true;
+}
+
+static int wg_pow2_divisor(int x, int cap) {
+    int d = 1;
+    while (d * 2 <= cap && (x % (d * 2)) == 0) d *= 2;
+    return d;
+}
+
+// `p` is the FORWARD plan with p.x = forward input and p.y = dy.
+bool wgrad_tc_supported(const ConvP& p, int x_dtype, int dy_dtype) {
+    if (x_dtype != MSTK_BF16 || dy_dtype != MSTK_BF16) return false;
+    const bool m_is_cout = (p.Cout % 128) == 0;
+    const bool m_is_cin = (p.Cin % 128) == 0;
+    if (!m_is_cout && !m_is_cin) return false;
+    const int cn = m_is_cout ? p.Cin : p.Cout;
+    if (!(cn % 64 == 0 || cn == 32)) return false;
+    if (p.s_in == 2 && ((p.H & 1) || (p.W & 1))) return false;
+    if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return false;
+    int groups = 0;
+    for (int i = 0; i < p.nphases; ++i) groups += p.ph[i].ntaps;     // worst case tpc = 1
+    if (groups > WG_MAX_GROUPS) return false;
+    return wgrad_tc_init();
+}
+
+int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, cudaStream_t st) {
+    if (!wgrad_tc_init()) return MSTK_EUNSUPPORTED;
+    WgParams q;
+    memset(&q, 0, sizeof(q));
+    q.p = p;
+    q.dw = dw;
+    q.swap = (p.Cout % 128) == 0 ? 0 : 1;
+    const int CM = q.swap ? p.Cin : p.Cout;
+    const int CN = q.swap ? p.Cout : p.Cin;
+    q.s_m = q.swap ? s_ci : s_co;
+    q.s_n = q.swap ? s_co : s_ci;
+    if (CN == 32) { q.BNt = 32; q.n_cc = 32; }
+    else { q.n_cc = 64; q.BNt = (CN % 256 == 0) ? 256 : (CN % 128 == 0) ? 128 : 64; }
+    q.n_chunks = q.BNt / q.n_cc;
+    q.m_tiles = CM / TILE_M;
+    q.n_tiles = CN / q.BNt;
+    q.m_tile_bytes = (uint32_t)(TILE_M * WG_KP * 2);
+    q.n_tile_bytes = (uint32_t)(q.BNt * WG_KP * 2);
+    // taps per CTA: bounded by TMEM columns (512) and a 64 KB stage
+    const uint32_t budget = 64 * 1024;
+    int tmax = 512 / q.BNt;
+    if (tmax > 4) tmax = 4;
+    {
+        const uint32_t dep = q.swap ? q.m_tile_bytes : q.n_tile_bytes;
+        const uint32_t fix = q.swap ? q.n_tile_bytes : q.m_tile_bytes;
+        const int fit = (int)((budget - fix) / dep);
+        if (tmax > fit) tmax = fit;
+        if (tmax < 1) tmax = 1;
+    }
+    q.ngroups = 0;
+    q.tpc = 1;
+    for (int i = 0; i < p.nphases; ++i) {
+        const int nt = p.ph[i].ntaps;
+        const int ng = (nt + tmax - 1) / tmax;
+        const int t = (nt + ng - 1) / ng;                 // balanced group size
+        if (t > q.tpc) q.tpc = t;
+        for (int t0 = 0; t0 < nt; t0 += t) {
+            if (q.ngroups >= WG_MAX_GROUPS) { set_error("wgrad(tcgen05): too many tap groups"); return MSTK_EUNSUPPORTED; }
+            WgGroup& g = q.groups[q.ngroups++];
+            g.phase = (int16_t)i; g.tap0 = (int16_t)t0; g.ntaps = (int16_t)((nt - t0) < t ? (nt - t0) : t); g.pad = 0;
+        }
+    }
+    q.stage_bytes = (q.swap ? (uint32_t)q.tpc : 1u) * q.m_tile_bytes + (q.swap ? 1u : (uint32_t)q.tpc) * q.n_tile_bytes;
+    q.stages = (int)((200u * 1024u) / q.stage_bytes);
+    if (q.stages > WG_MAX_STAGES) q.stages = WG_MAX_STAGES;
+    if (q.stages < 2) q.stages = 2;
+    int cols = 32;
+    while (cols < q.tpc * q.BNt) cols <<= 1;
+    q.tmem_cols = cols;
+    // pixel tiles
+    q.Wt = wg_pow2_divisor(p.Wg, WG_KP);
+    q.Ht = wg_pow2_divisor(p.Hg, WG_KP / q.Wt);
+    q.Nt = WG_KP / (q.Wt * q.Ht);
+    q.tiles_w = p.Wg / q.Wt;
+    q.tiles_h = p.Hg / q.Ht;
+    const int tiles_n = (p.N + q.Nt - 1) / q.Nt;
+    q.ptiles = q.tiles_w * q.tiles_h * tiles_n;
+    const long long base = (long long)q.ngroups * q.m_tiles * q.n_tiles;
+    long long ks = (2LL * tc_num_sms() + base - 1) / base;
+    const long long ks_max = (q.ptiles + 3) / 4;          // at least ~4 k-blocks per CTA
+    if (ks > ks_max) ks = ks_max;
+    if (ks < 1) ks = 1;
+    if (ks > 65535) ks = 65535;
+    q.ksplit = (int)ks;
+
+    WgMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    const int dy_cc = q.swap ? q.n_cc : 64;
+    const int x_cc = q.swap ? 64 : q.n_cc;
+    for (int i = 0; i < p.nphases; ++i) {
+        const Phase& ph = p.ph[i];
+        const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.y) + ((size_t)ph.oy * p.Wo + ph.ox) * p.Cout;
+        const uint64_t s = (uint64_t)p.s_out;
+        uint64_t dims[4] = {(uint64_t)p.Cout, (uint64_t)p.Wg, (uint64_t)p.Hg, (uint64_t)p.N};
+        uint64_t strides[3] = {s * p.Cout * 2, s * p.Wo * p.Cout * 2, (uint64_t)p.Ho * p.Wo * p.Cout * 2};
+        uint32_t box[4] = {(uint32_t)dy_cc, (uint32_t)q.Wt, (uint32_t)q.Ht, (uint32_t)q.Nt};
+        int rc = tc_encode_map(&maps.dy[i], 0, b, 4, dims, strides, box, dy_cc * 2);
+        if (rc != MSTK_OK) return rc;
+    }
+    for (int i = p.nphases; i < 4; ++i) maps.dy[i] = maps.dy[0];
+    const int s = p.s_in;
+    const int nviews = (s == 2) ? 4 : 1;
+    for (int v = 0; v < nviews; ++v) {
+        const int py = v >> 1, px = v & 1;
+        const __nv_bfloat16* b = reinterpret_cast<const __nv_bfloat16*>(p.x) + ((size_t)py * p.W + px) * p.Cin;
+        uint64_t dims[4] = {(uint64_t)p.Cin, (uint64_t)(p.W / s), (uint64_t)(p.H / s), (uint64_t)p.N};
+        uint64_t strides[3] = {(uint64_t)p.Cin * 2 * s, (uint64_t)p.W * p.Cin * 2 * s, (uint64_t)p.H * p.W * p.Cin * 2};
+        uint32_t box[4] = {(uint32_t)x_cc, (uint32_t)q.Wt, (uint32_t)q.Ht, (uint32_t)q.Nt};
+        int rc = tc_encode_map(&maps.x[v], 0, b, 4, dims, strides, box, x_cc * 2);
+        if (rc != MSTK_OK) return rc;
+    }
+    for (int v = nviews; v < 4; ++v) maps.x[v] = maps.x[0];
+
+    dim3 grid((unsigned)base, (unsigned)q.ksplit, 1);
+    const size_t smem = (size_t)q.stages * q.stage_bytes + 1024;
+    wgrad_tc_kernel<<<grid, WG_THREADS, smem, st>>>(maps, q);
+    MSTK_CHECK_LAUNCH("wgrad_tc launch");
+    return MSTK_OK;
+}
+
+}  // namespace mstk
