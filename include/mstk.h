@@ -198,10 +198,22 @@ int mstk_mse(const void* a, const void* b, int dtype, size_t count, double* scra
 int mstk_kl(const float* z, size_t count, double* scratch, float* out, void* stream);
 /* VGGish tap term (loss.py:94-99): per sample i, f/(std_unbiased(f_i)+1e-8) vs
  * g/(std_unbiased(g_i)+1e-8), mean squared difference over all b*inner elements.
- * tmp: [b*4 + 2] doubles scratch (zeroed by caller; left zeroed). Accumulates
+ * tmp: [b*4 + 3] doubles scratch (zeroed by caller; left zeroed). Accumulates
  * `weight * term` into out[0] (so the six taps can be summed with weight 1/6). */
 int mstk_feature_std_mse(const void* f, const void* g, int dtype, int b, int64_t inner,
                          double* tmp, float weight, float* out, void* stream);
+/* The same term for the training step, which evaluates it on the pairs (f0,f1) and (f1,f2)
+ * (compression_loss's perceptual term loss.py:40 and style_loss loss.py:104-106 share the
+ * reconstruction's features): per-sample statistics in one pass, both pair terms in one pass.
+ *   mstk_sample_stats : stats[s*2 + {0,1}] += sum, sum of squares of f[s, 0..inner)
+ *   mstk_feature_mse3 : out_a += weight * mean((f0/(std0+1e-8) - f1/(std1+1e-8))^2),
+ *                       out_c += weight * mean((f1/(std1+1e-8) - f2/(std2+1e-8))^2)  (f2 may be NULL)
+ * st0/st1/st2: [2*b] doubles from mstk_sample_stats; scratch: 3 doubles.  Statistics and scratch
+ * are zeroed by the caller once and left zeroed.  inner % 8 == 0 (bf16) / 4 (fp32). */
+int mstk_sample_stats(const void* f, int dtype, int samples, int64_t inner, double* stats, void* stream);
+int mstk_feature_mse3(const void* f0, const void* f1, const void* f2, int dtype, int b, int64_t inner,
+                      double* st0, double* st1, double* st2, double* scratch, float weight,
+                      float* out_a, float* out_c, void* stream);
 /* 2x2/2 max pool on NHWC (vggish.py:113) */
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
 

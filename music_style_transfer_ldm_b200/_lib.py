@@ -105,6 +105,9 @@ SIGNATURES = {
     "mstk_mse": (c_int, [c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_void_p]),
     "mstk_kl": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "mstk_feature_std_mse": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_float, c_void_p, c_void_p]),
+    "mstk_sample_stats": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
+    "mstk_feature_mse3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                  c_void_p, c_void_p, c_void_p]),
     "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_pack_conv_weight_dgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),

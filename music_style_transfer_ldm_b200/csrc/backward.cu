@@ -492,6 +492,113 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ src, void* dst, int 
     }
 }
 
+// ---------------------------------------------------------------------------
+// weight gradient of the single-channel edge layers (HBM-streaming, CUDA cores):
+//   Conv2d(1, C, k3, stride s, p1):          V = dy [N,Hv,Wv,C], S = x  [N,Hs,Ws]
+//   ConvTranspose2d(C, 1, k4, s2, p1):       V = x  [N,Hv,Wv,C], S = dy [N,Hs,Ws]
+// Both are  dw[c][ky][kx] += sum_{n,vh,vw} V[n,vh,vw,c] * S[n, vh*ss + ky - 1, vw*ss + kx - 1]  (zero outside S).
+// The vector operand is read exactly once (CH channels = one 8/16-byte load per thread and pixel), the
+// scalar window comes from L1; K*K*CH accumulators per thread, shared-memory then global RED at the end.
+// ---------------------------------------------------------------------------
+struct EdgeWgradP {
+    const __nv_bfloat16* v;
+    const void* s;
+    float* dw;
+    int s_dtype;
+    int N, Hv, Wv, C, Hs, Ws, ss;
+};
+
+template <int K, int CH>
+__global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
+    extern __shared__ float acc_s[];                  // [C][K*K]
+    const int tpp = q.C / CH;                         // threads per pixel
+    const int ppb = 256 / tpp;                        // pixels per block iteration
+    const int cg = threadIdx.x % tpp;                 // channel group
+    const int slot = threadIdx.x / tpp;
+    for (int i = threadIdx.x; i < q.C * K * K; i += 256) acc_s[i] = 0.f;
+    __syncthreads();
+    float acc[K * K][CH];
+#pragma unroll
+    for (int t = 0; t < K * K; ++t)
+#pragma unroll
+        for (int c = 0; c < CH; ++c) acc[t][c] = 0.f;
+    const long long npix = (long long)q.N * q.Hv * q.Wv;
+    if (slot < ppb) {
+        for (long long pix = (long long)blockIdx.x * ppb + slot; pix < npix; pix += (long long)gridDim.x * ppb) {
+            const int n = (int)(pix / ((long long)q.Hv * q.Wv));
+            const int r = (int)(pix - (long long)n * q.Hv * q.Wv);
+            const int vh = r / q.Wv, vw = r - vh * q.Wv;
+            float vv[CH];
+            const __nv_bfloat16* vp = q.v + pix * q.C + cg * CH;
+            if (CH == 8) {
+                const uint4 u = *reinterpret_cast<const uint4*>(vp);
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(h[e]); vv[2 * e] = f.x; vv[2 * e + 1] = f.y; }
+            } else {
+                const uint2 u = *reinterpret_cast<const uint2*>(vp);
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int e = 0; e < 2; ++e) { const float2 f = __bfloat1622float2(h[e]); vv[2 * e] = f.x; vv[2 * e + 1] = f.y; }
+            }
+            const int sh0 = vh * q.ss - 1, sw0 = vw * q.ss - 1;
+            const size_t sbase = (size_t)n * q.Hs * q.Ws;
+#pragma unroll
+            for (int ky = 0; ky < K; ++ky) {
+                const int sh = sh0 + ky;
+                const bool okh = sh >= 0 && sh < q.Hs;
+#pragma unroll
+                for (int kx = 0; kx < K; ++kx) {
+                    const int sw = sw0 + kx;
+                    float sv = 0.f;
+                    if (okh && sw >= 0 && sw < q.Ws) sv = load_as_f(q.s, q.s_dtype, sbase + (size_t)sh * q.Ws + sw);
+#pragma unroll
+                    for (int c = 0; c < CH; ++c) acc[ky * K + kx][c] = fmaf(vv[c], sv, acc[ky * K + kx][c]);
+                }
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < K * K; ++t)
+#pragma unroll
+            for (int c = 0; c < CH; ++c) atomicAdd(&acc_s[(cg * CH + c) * K * K + t], acc[t][c]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < q.C * K * K; i += 256) atomicAdd(q.dw + i, acc_s[i]);
+}
+
+// returns MSTK_EUNSUPPORTED when the layer is not one of the two edge shapes
+static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
+    EdgeWgradP q;
+    memset(&q, 0, sizeof(q));
+    q.dw = a->dw; q.N = a->n;
+    if (!a->transposed && a->cin == 1 && a->ksize == 3 && a->dy_dtype == MSTK_BF16 && (a->cout % 8) == 0 && a->cout <= 256 &&
+        (256 % (a->cout / 8)) == 0) {
+        q.v = reinterpret_cast<const __nv_bfloat16*>(a->dy); q.s = a->x; q.s_dtype = a->x_dtype;
+        q.Hv = (a->h + 2 - 3) / a->stride + 1; q.Wv = (a->w + 2 - 3) / a->stride + 1; q.C = a->cout;
+        q.Hs = a->h; q.Ws = a->w; q.ss = a->stride;
+        const long long npix = (long long)q.N * q.Hv * q.Wv;
+        const int ppb = 256 / (q.C / 8);
+        long long blocks = (npix + ppb - 1) / ppb;
+        if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();
+        wgrad_edge_kernel<3, 8><<<(unsigned)blocks, 256, (size_t)q.C * 9 * sizeof(float), st>>>(q);
+        MSTK_CHECK_LAUNCH("wgrad_edge(cin=1)");
+        return MSTK_OK;
+    }
+    if (a->transposed && a->cout == 1 && a->ksize == 4 && a->stride == 2 && a->x_dtype == MSTK_BF16 && (a->cin % 4) == 0 &&
+        a->cin <= 512 && (256 % (a->cin / 4)) == 0) {
+        q.v = reinterpret_cast<const __nv_bfloat16*>(a->x); q.s = a->dy; q.s_dtype = a->dy_dtype;
+        q.Hv = a->h; q.Wv = a->w; q.C = a->cin; q.Hs = 2 * a->h; q.Ws = 2 * a->w; q.ss = 2;
+        const long long npix = (long long)q.N * q.Hv * q.Wv;
+        const int ppb = 256 / (q.C / 4);
+        long long blocks = (npix + ppb - 1) / ppb;
+        if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();
+        wgrad_edge_kernel<4, 4><<<(unsigned)blocks, 256, (size_t)q.C * 16 * sizeof(float), st>>>(q);
+        MSTK_CHECK_LAUNCH("wgrad_edge(cout=1)");
+        return MSTK_OK;
+    }
+    return MSTK_EUNSUPPORTED;
+}
+
 }  // namespace mstk
 
 using namespace mstk;
@@ -515,6 +622,10 @@ int mstk_conv2d_wgrad(const mstk_wgrad_args* a, void* stream) {
     f.n = a->n; f.h = a->h; f.w = a->w; f.cin = a->cin; f.cout = a->cout; f.ksize = a->ksize; f.stride = a->stride;
     f.transposed = a->transposed; f.act = MSTK_ACT_NONE; f.out_scale = 1.f; f.out_shift = 0.f;
     f.dtype = a->x_dtype; f.out_dtype = a->dy_dtype;
+    {
+        const int rce = launch_wgrad_edge(a, (cudaStream_t)stream);
+        if (rce != MSTK_EUNSUPPORTED) return rce;
+    }
     WgradP q;
     int rc = build_conv_plan(&f, &q.p);
     if (rc != MSTK_OK) return rc;

@@ -45,12 +45,25 @@ __global__ void __launch_bounds__(256) conv_cin1_kernel(const EdgeP a) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
     int cg_prev = -1;
+    const unsigned per_img = (unsigned)(a.Ho * a.Wo);
     for (size_t it = blockIdx.x * (size_t)blockDim.x + threadIdx.x; it < items; it += (size_t)gridDim.x * blockDim.x) {
-        const int cg = (int)(it % CG);
-        size_t pix = it / CG;
-        const int ow = (int)(pix % a.Wo); pix /= a.Wo;
-        const int oh = (int)(pix % a.Ho);
-        const int n = (int)(pix / a.Ho);
+        // 32-bit index arithmetic (64-bit div/mod cost more than the 72 FMAs of the item); CG is a power of two
+        // for every layer of the model, but stay generic
+        int cg, n;
+        unsigned r;
+        if (items <= 0xFFFFFFFFull) {
+            const unsigned i32 = (unsigned)it, pix = i32 / (unsigned)CG;
+            cg = (int)(i32 - pix * (unsigned)CG);
+            n = (int)(pix / per_img);
+            r = pix - (unsigned)n * per_img;
+        } else {
+            const size_t pix64 = it / (unsigned)CG;
+            cg = (int)(it - pix64 * (unsigned)CG);
+            n = (int)(pix64 / per_img);
+            r = (unsigned)(pix64 - (size_t)n * per_img);
+        }
+        const int oh = (int)(r / (unsigned)a.Wo);
+        const int ow = (int)(r - (unsigned)oh * (unsigned)a.Wo);
         if (a.stats && cg != cg_prev && cg_prev >= 0) {
             // the channel group of this thread changed (only when gridDim*blockDim % CG != 0): flush
 #pragma unroll

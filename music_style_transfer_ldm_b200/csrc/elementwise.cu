@@ -613,6 +613,15 @@ int mstk_feature_std_mse(const void* f, const void* g, int dtype, int b, int64_t
                          void* stream) {
     MSTK_REQUIRE(f && g && tmp && out && b > 0 && inner > 1, "feature_std_mse: bad args");
     MSTK_REQUIRE(b <= 65535, "feature_std_mse: batch too large");
+    if (feat_vec_ok(f, dtype, inner) && feat_vec_ok(g, dtype, inner)) {
+        // vectorised path: per-sample statistics of both maps, then one fused normalise + MSE pass
+        cudaStream_t st = (cudaStream_t)stream;
+        int rc = launch_sample_stats(f, dtype, b, inner, tmp, st);
+        if (rc != MSTK_OK) return rc;
+        rc = launch_sample_stats(g, dtype, b, inner, tmp + 2 * (size_t)b, st);
+        if (rc != MSTK_OK) return rc;
+        return launch_feat_mse3(f, g, nullptr, dtype, b, inner, tmp, tmp + 2 * (size_t)b, nullptr, tmp + 4 * (size_t)b, weight, out, nullptr, st);
+    }
     unsigned gx = grid_for((size_t)inner, 256, 4);
     const unsigned cap = (unsigned)((num_sms() * 8 + b - 1) / b);
     if (gx > cap) gx = cap < 1 ? 1 : cap;
@@ -623,8 +632,26 @@ int mstk_feature_std_mse(const void* f, const void* g, int dtype, int b, int64_t
     MSTK_CHECK_LAUNCH("feature_std_mse(mse)");
     return MSTK_OK;
 }
+int mstk_sample_stats(const void* f, int dtype, int samples, int64_t inner, double* stats, void* stream) {
+    MSTK_REQUIRE(f && stats && samples > 0 && samples <= 65535 && inner > 1, "sample_stats: bad args");
+    MSTK_REQUIRE(feat_vec_ok(f, dtype, inner), "sample_stats: inner must be a multiple of 8 (bf16) / 4 (fp32) and f 16-byte aligned");
+    return launch_sample_stats(f, dtype, samples, inner, stats, (cudaStream_t)stream);
+}
+int mstk_feature_mse3(const void* f0, const void* f1, const void* f2, int dtype, int b, int64_t inner, double* st0, double* st1,
+                      double* st2, double* scratch, float weight, float* out_a, float* out_c, void* stream) {
+    MSTK_REQUIRE(f0 && f1 && st0 && st1 && scratch && out_a && b > 0 && b <= 65535 && inner > 1, "feature_mse3: bad args");
+    MSTK_REQUIRE(!f2 || (st2 && out_c), "feature_mse3: the third map needs its statistics and an output");
+    MSTK_REQUIRE(feat_vec_ok(f0, dtype, inner) && feat_vec_ok(f1, dtype, inner) && (!f2 || feat_vec_ok(f2, dtype, inner)),
+                 "feature_mse3: inner must be a multiple of 8 (bf16) / 4 (fp32) and the maps 16-byte aligned");
+    return launch_feat_mse3(f0, f1, f2, dtype, b, inner, st0, st1, st2, scratch, weight, out_a, out_c, (cudaStream_t)stream);
+}
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream) {
     MSTK_REQUIRE(x && y && n > 0 && h > 1 && w > 1 && c > 0, "maxpool: bad args");
+    {
+        const int v = dtype == MSTK_BF16 ? 8 : 4;
+        if ((c % v) == 0 && !(h & 1) && !(w & 1) && n <= 65535 && !(reinterpret_cast<uintptr_t>(x) & 15) && !(reinterpret_cast<uintptr_t>(y) & 15))
+            return launch_maxpool_vec(x, y, n, h, w, c, dtype, (cudaStream_t)stream);
+    }
     const size_t total = (size_t)n * (h / 2) * (w / 2) * c;
     maxpool2x2_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, h, w, c, dtype);
     MSTK_CHECK_LAUNCH("maxpool");

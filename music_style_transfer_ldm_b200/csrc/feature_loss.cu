@@ -1,0 +1,232 @@
+// HBM-streaming kernels of the VGGish feature loss (reference models/loss.py:64-101):
+//
+//   sample_stats_kernel   per-sample sum / sum of squares of a feature map [S, inner]
+//   feat_mse3_kernel      ONE pass over up to three feature maps f0, f1, f2 [B, inner] that
+//                         accumulates  A = sum (f0/(std0+1e-8) - f1/(std1+1e-8))^2   (perceptual pair)
+//                                      C = sum (f1/(std1+1e-8) - f2/(std2+1e-8))^2   (style pair)
+//                         the training step evaluates both terms on (x, recon) and (recon, style), so
+//                         recon's features are read once instead of twice.
+//   maxpool2x2_vec_kernel 2x2/2 max pool on NHWC, 8 channels per thread
+//
+// All of them move 16 bytes per thread and load (8 bf16 / 4 fp32), keep fp32 partial sums over short
+// runs and fold them into doubles, use 32-bit index arithmetic inside a sample, and end in one double
+// atomic per CTA and quantity.
+#include "common.cuh"
+
+namespace mstk {
+
+template <int DT> struct VecT;
+template <> struct VecT<MSTK_BF16> { static constexpr int N = 8; };
+template <> struct VecT<MSTK_F32> { static constexpr int N = 4; };
+
+template <int DT>
+__device__ __forceinline__ void load_vec(const void* p, size_t vec_idx, float (&o)[VecT<DT>::N]) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(p) + vec_idx);
+    if (DT == MSTK_BF16) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(h[e]);
+            o[2 * e] = f.x; o[2 * e + 1] = f.y;
+        }
+    } else {
+        o[0] = __uint_as_float(q.x); o[1] = __uint_as_float(q.y); o[2] = __uint_as_float(q.z); o[3] = __uint_as_float(q.w);
+    }
+}
+
+__device__ __forceinline__ double block_sum_d(double v, double* red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (warp == 0) {
+        r = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.0;
+        r = warp_sum(r);
+    }
+    return r;   // valid in thread 0
+}
+
+// stats[s*2 + {0,1}] += sum, sum of squares of f[s, :]   (grid: x = chunks of a sample, y = sample)
+template <int DT>
+__global__ void __launch_bounds__(256) sample_stats_kernel(const void* __restrict__ f, long long inner, double* stats) {
+    __shared__ double red[32];
+    constexpr int V = VecT<DT>::N;
+    const int s = blockIdx.y;
+    const size_t vbase = (size_t)s * (size_t)(inner / V);
+    const unsigned nvec = (unsigned)(inner / V);
+    double ds = 0.0, dq = 0.0;
+    float ls = 0.f, lq = 0.f;
+    int run = 0;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < nvec; i += gridDim.x * 256u) {
+        float v[V];
+        load_vec<DT>(f, vbase + i, v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) { ls += v[j]; lq = fmaf(v[j], v[j], lq); }
+        if (++run == 16) { ds += ls; dq += lq; ls = lq = 0.f; run = 0; }
+    }
+    ds += ls; dq += lq;
+    ds = block_sum_d(ds, red);
+    dq = block_sum_d(dq, red);
+    if (threadIdx.x == 0) {
+        atomicAdd(stats + 2 * s, ds);
+        atomicAdd(stats + 2 * s + 1, dq);
+    }
+}
+
+__device__ __forceinline__ float inv_std(const double* st, int b, double n) {
+    const double m = st[2 * b] / n;
+    double var = (st[2 * b + 1] - n * m * m) / (n - 1.0);      // unbiased, as torch.std (loss.py:94)
+    if (var < 0) var = 0;
+    return 1.f / ((float)sqrt(var) + 1e-8f);
+}
+
+// scratch: [acc_a, acc_c, counter]; the last CTA finalises, adds the weighted means into out_a / out_c and
+// re-zeroes scratch and the three statistics arrays.
+template <int DT>
+__global__ void __launch_bounds__(256) feat_mse3_kernel(const void* __restrict__ f0, const void* __restrict__ f1, const void* __restrict__ f2,
+                                                       int nb, long long inner, double* st0, double* st1, double* st2, double* scratch,
+                                                       float weight, float* out_a, float* out_c) {
+    __shared__ double red[32];
+    constexpr int V = VecT<DT>::N;
+    const int b = blockIdx.y;
+    const double n = (double)inner;
+    const float r0 = inv_std(st0, b, n), r1 = inv_std(st1, b, n);
+    const float r2 = f2 ? inv_std(st2, b, n) : 0.f;
+    const size_t vbase = (size_t)b * (size_t)(inner / V);
+    const unsigned nvec = (unsigned)(inner / V);
+    double da = 0.0, dc = 0.0;
+    float la = 0.f, lc = 0.f;
+    int run = 0;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < nvec; i += gridDim.x * 256u) {
+        float a[V], m[V];
+        load_vec<DT>(f0, vbase + i, a);
+        load_vec<DT>(f1, vbase + i, m);
+        if (f2) {
+            float c[V];
+            load_vec<DT>(f2, vbase + i, c);
+#pragma unroll
+            for (int j = 0; j < V; ++j) { const float d = m[j] * r1 - c[j] * r2; lc = fmaf(d, d, lc); }
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) { const float d = a[j] * r0 - m[j] * r1; la = fmaf(d, d, la); }
+        if (++run == 16) { da += la; dc += lc; la = lc = 0.f; run = 0; }
+    }
+    da += la; dc += lc;
+    da = block_sum_d(da, red);
+    dc = block_sum_d(dc, red);
+    if (threadIdx.x == 0) {
+        atomicAdd(scratch, da);
+        if (f2) atomicAdd(scratch + 1, dc);
+        __threadfence();
+        unsigned int* ctr = reinterpret_cast<unsigned int*>(scratch + 2);
+        const unsigned int old = atomicAdd(ctr, 1u);
+        if (old == gridDim.x * gridDim.y - 1) {
+            __threadfence();
+            const double sa = atomicAdd(scratch, 0.0), sc = atomicAdd(scratch + 1, 0.0);
+            const double den = (double)nb * n;
+            atomicAdd(out_a, weight * (float)(sa / den));
+            if (f2) atomicAdd(out_c, weight * (float)(sc / den));
+            scratch[0] = 0.0; scratch[1] = 0.0;
+            *ctr = 0u;
+            for (int i = 0; i < 2 * nb; ++i) {
+                st0[i] = 0.0; st1[i] = 0.0;
+                if (f2) st2[i] = 0.0;
+            }
+        }
+    }
+}
+
+// x [n,h,w,c] -> y [n,h/2,w/2,c]; one thread = 8 (bf16) or 4 (fp32) channels of one output pixel
+template <int DT>
+__global__ void __launch_bounds__(256) maxpool2x2_vec_kernel(const void* __restrict__ x, void* y, int n, int h, int w, int c) {
+    constexpr int V = VecT<DT>::N;
+    const int ho = h / 2, wo = w / 2, cv = c / V;
+    const unsigned per_img = (unsigned)ho * wo * cv;
+    const int img = blockIdx.y;
+    const size_t in_base = (size_t)img * h * w * cv;      // in vectors
+    const size_t out_base = (size_t)img * per_img;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < per_img; i += gridDim.x * 256u) {
+        const unsigned ch = i % cv;
+        const unsigned r = i / cv;
+        const unsigned ox = r % wo, oy = r / wo;
+        const size_t b00 = in_base + ((size_t)(2 * oy) * w + 2 * ox) * cv + ch;
+        float a[V], b[V], d[V], e[V];
+        load_vec<DT>(x, b00, a);
+        load_vec<DT>(x, b00 + cv, b);
+        load_vec<DT>(x, b00 + (size_t)w * cv, d);
+        load_vec<DT>(x, b00 + (size_t)w * cv + cv, e);
+        uint4 o;
+        if (DT == MSTK_BF16) {
+            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                hh[j] = __floats2bfloat162_rn(fmaxf(fmaxf(a[2 * j], b[2 * j]), fmaxf(d[2 * j], e[2 * j])),
+                                              fmaxf(fmaxf(a[2 * j + 1], b[2 * j + 1]), fmaxf(d[2 * j + 1], e[2 * j + 1])));
+        } else {
+            o.x = __float_as_uint(fmaxf(fmaxf(a[0], b[0]), fmaxf(d[0], e[0])));
+            o.y = __float_as_uint(fmaxf(fmaxf(a[1], b[1]), fmaxf(d[1], e[1])));
+            o.z = __float_as_uint(fmaxf(fmaxf(a[2 % V], b[2 % V]), fmaxf(d[2 % V], e[2 % V])));
+            o.w = __float_as_uint(fmaxf(fmaxf(a[3 % V], b[3 % V]), fmaxf(d[3 % V], e[3 % V])));
+        }
+        reinterpret_cast<uint4*>(y)[out_base + i] = o;
+    }
+}
+
+static int fl_sms() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) sms = v;
+        else sms = 148;
+    }
+    return sms;
+}
+// grid.x so that grid.x * samples ~ 8 CTAs per SM, at most one CTA per 256 vectors
+static unsigned fl_grid_x(long long nvec, int samples) {
+    long long gx = (nvec + 255) / 256;
+    long long cap = ((long long)fl_sms() * 8 + samples - 1) / samples;
+    if (cap < 1) cap = 1;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    return (unsigned)gx;
+}
+
+bool feat_vec_ok(const void* f, int dtype, long long inner) {
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    return (inner % v) == 0 && (reinterpret_cast<uintptr_t>(f) & 15) == 0 && inner / v < (1ll << 31);
+}
+
+int launch_sample_stats(const void* f, int dtype, int samples, long long inner, double* stats, cudaStream_t st) {
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    dim3 grid(fl_grid_x(inner / v, samples), (unsigned)samples);
+    if (dtype == MSTK_BF16) sample_stats_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(f, inner, stats);
+    else sample_stats_kernel<MSTK_F32><<<grid, 256, 0, st>>>(f, inner, stats);
+    MSTK_CHECK_LAUNCH("sample_stats");
+    return MSTK_OK;
+}
+
+int launch_feat_mse3(const void* f0, const void* f1, const void* f2, int dtype, int b, long long inner, double* st0, double* st1,
+                     double* st2, double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st) {
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    dim3 grid(fl_grid_x(inner / v, b), (unsigned)b);
+    if (dtype == MSTK_BF16)
+        feat_mse3_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(f0, f1, f2, b, inner, st0, st1, st2, scratch, weight, out_a, out_c);
+    else
+        feat_mse3_kernel<MSTK_F32><<<grid, 256, 0, st>>>(f0, f1, f2, b, inner, st0, st1, st2, scratch, weight, out_a, out_c);
+    MSTK_CHECK_LAUNCH("feature_mse3");
+    return MSTK_OK;
+}
+
+int launch_maxpool_vec(const void* x, void* y, int n, int h, int w, int c, int dtype, cudaStream_t st) {
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    const long long per_img = (long long)(h / 2) * (w / 2) * (c / v);
+    dim3 grid(fl_grid_x(per_img, n), (unsigned)n);
+    if (dtype == MSTK_BF16) maxpool2x2_vec_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(x, y, n, h, w, c);
+    else maxpool2x2_vec_kernel<MSTK_F32><<<grid, 256, 0, st>>>(x, y, n, h, w, c);
+    MSTK_CHECK_LAUNCH("maxpool(vec)");
+    return MSTK_OK;
+}
+
+}  // namespace mstk

@@ -324,9 +324,28 @@ def feature_std_mse(f: torch.Tensor, g: torch.Tensor, weight: float, out: torch.
     _dev(f, "feat.f"); _dev(g, "feat.g")
     b = f.shape[0]
     inner = f.numel() // b
-    tmp = _loss_scratch(f.device, 4 * b + 2)
+    tmp = _loss_scratch(f.device, 4 * b + 4)
     check(lib.mstk_feature_std_mse(_p(f), _p(g), dtype_code(f), b, inner, _p(tmp), weight, _p(out), _stream()),
           "mstk_feature_std_mse")
+    _count(2)
+
+
+def feature_mse3(f_all: torch.Tensor, b: int, weight: float, out_a: torch.Tensor, out_c: torch.Tensor) -> None:
+    """f_all: [3b, ...] features of three image batches stacked along dim 0.  Accumulates the VGGish tap term
+    (loss.py:94-99) of the pair (f_all[:b], f_all[b:2b]) into out_a and of (f_all[b:2b], f_all[2b:]) into out_c."""
+    lib = _lib.load()
+    _dev(f_all, "feat3.f")
+    if f_all.shape[0] != 3 * b or not f_all.is_contiguous():
+        raise MstkError("feature_mse3: expected a contiguous [3b, ...] tensor")
+    inner = f_all.numel() // (3 * b)
+    esz = f_all.element_size()
+    tmp = _loss_scratch(f_all.device, 6 * b + 4)
+    dt = dtype_code(f_all)
+    base = f_all.data_ptr()
+    check(lib.mstk_sample_stats(base, dt, 3 * b, inner, _p(tmp), _stream()), "mstk_sample_stats")
+    d0 = tmp.data_ptr()
+    check(lib.mstk_feature_mse3(base, base + b * inner * esz, base + 2 * b * inner * esz, dt, b, inner, d0, d0 + 16 * b, d0 + 32 * b,
+                                d0 + 48 * b, weight, _p(out_a), _p(out_c), _stream()), "mstk_feature_mse3")
     _count(2)
 
 

@@ -314,8 +314,8 @@ class LDMTrainer:
         perc = torch.zeros(1, dtype=torch.float32, device=dev)
         styl = torch.zeros(1, dtype=torch.float32, device=dev)
         for f in taps:
-            ops.feature_std_mse(f[:B], f[B:2 * B], 1.0 / len(taps), perc)         # compression_loss's perceptual term (loss.py:40)
-            ops.feature_std_mse(f[B:2 * B], f[2 * B:], 1.0 / len(taps), styl)     # style_loss (loss.py:104-106)
+            # perc: compression_loss's perceptual term (loss.py:40); styl: style_loss (loss.py:104-106); one fused pass
+            ops.feature_mse3(f, B, 1.0 / len(taps), perc, styl)
         comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
         total = comp + den + self.style_loss_weight * styl.squeeze(0)
 

@@ -1,0 +1,55 @@
+"""-m gpu: the vectorised VGGish feature-loss kernels (csrc/feature_loss.cu) against the reference formula
+(models/loss.py:94-99: x / (std over (C,H,W), unbiased, + 1e-8), MSE) computed with torch on the CPU."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from gpu_util import assert_close, gen, nchw, nhwc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _term(f, h):
+    fn = f / (f.std(dim=[1, 2, 3], keepdim=True) + 1e-8)
+    hn = h / (h.std(dim=[1, 2, 3], keepdim=True) + 1e-8)
+    return ((fn - hn) ** 2).mean().reshape(1)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(3, 64, 16, 16), (5, 40, 9, 8), (2, 512, 8, 8)])
+def test_feature_mse3(shape, dt):
+    from music_style_transfer_ldm_b200 import ops
+    g = gen(sum(shape))
+    b = shape[0]
+    maps = [(torch.relu(torch.randn(shape, generator=g)) * s).to(dt).float() for s in (1.0, 3.0, 0.25)]
+    ref_a, ref_c = _term(maps[0], maps[1]), _term(maps[1], maps[2])
+    f_all = torch.cat([nhwc(m, dt) for m in maps], dim=0).to(DEV)
+    for _ in range(2):      # twice: statistics and scratch must come back zeroed
+        out_a, out_c = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+        ops.feature_mse3(f_all, b, 0.5, out_a, out_c)
+        ops.feature_mse3(f_all, b, 0.5, out_a, out_c)
+        assert_close(out_a, ref_a, 2e-5, "feature_mse3 pair (0,1)")
+        assert_close(out_c, ref_c, 2e-5, "feature_mse3 pair (1,2)")
+    # the two-map entry point goes through the same kernels
+    out = torch.zeros(1, device=DEV)
+    ops.feature_std_mse(f_all[:b], f_all[b:2 * b], 1.0, out)
+    assert_close(out, ref_a, 2e-5, "feature_std_mse (vector path)")
+
+
+def test_feature_std_mse_scalar_fallback():
+    from music_style_transfer_ldm_b200 import ops
+    g = gen(3)
+    f, h = torch.relu(torch.randn((3, 5, 3, 7), generator=g)), torch.relu(torch.randn((3, 5, 3, 7), generator=g)) * 2    # inner = 105: odd
+    out = torch.zeros(1, device=DEV)
+    ops.feature_std_mse(nhwc(f).to(DEV), nhwc(h).to(DEV), 1.0, out)
+    assert_close(out, _term(f, h), 1e-5, "feature_std_mse (scalar path)")
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(3, 64, 16, 32), (2, 24, 8, 12), (2, 20, 6, 10)])
+def test_maxpool_vec(shape, dt):
+    from music_style_transfer_ldm_b200 import ops
+    x = torch.randn(shape, generator=gen(shape[1])).to(dt).float()
+    got = nchw(ops.maxpool2x2(nhwc(x, dt).to(DEV))).cpu()
+    assert torch.equal(got, F.max_pool2d(x, 2, 2))
