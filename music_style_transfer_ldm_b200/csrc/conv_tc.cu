@@ -78,6 +78,39 @@ struct TcParams {
 // argument; a flag that is clear compiles the feature out.
 enum : uint32_t { F_SPLITK = 1, F_STATS = 2, F_ADDNC = 4, F_ADD = 8, F_DDIM = 16, F_STORE = 32, F_ACTGEN = 64, F_ALL = 127 };
 
+// Column sums over the 32 rows held by a warp (one row per lane, 16 columns per lane): halving butterfly,
+// 16 shuffles instead of 16 x 5.  Returns the sum of column ((lane >> 1) & 15 bit-reversed as below) in every
+// lane; lanes l and l^1 hold the same column.  Column index of a lane: colsum_index(lane).
+__device__ __forceinline__ float colsum16(float (&a)[16], int lane) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const bool up = (lane & 16) != 0;
+        const float send = up ? a[i] : a[i + 8], mine = up ? a[i + 8] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const bool up = (lane & 8) != 0;
+        const float send = up ? a[i] : a[i + 4], mine = up ? a[i + 4] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const bool up = (lane & 4) != 0;
+        const float send = up ? a[i] : a[i + 2], mine = up ? a[i + 2] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    {
+        const bool up = (lane & 2) != 0;
+        const float send = up ? a[0] : a[1], mine = up ? a[1] : a[0];
+        a[0] = mine + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    return a[0] + __shfl_xor_sync(0xffffffffu, a[0], 1);
+}
+__device__ __forceinline__ int colsum_index(int lane) {
+    return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+}
+
 template <uint32_t F>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams q) {
@@ -238,6 +271,8 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
 
         // ---- work that does not need the accumulator: overlaps the main loop ----
         if (et < BN) sbias[et] = p.bias ? __ldg(p.bias + co0 + et) : 0.f;   // parameters: safe before the grid dependency
+        float* sstat = sbias + BN;                // [2][BN] per-CTA column sums of the BatchNorm statistics
+        if (f_stats) { for (int i = et; i < 2 * BN; i += 128) sstat[i] = 0.f; }
         pdl_wait();
         const size_t pix_off = row_ok ? ((((size_t)n_img * p.Ho + (size_t)(hg * p.s_out + ph.oy)) * p.Wo + (size_t)(wg * p.s_out + ph.ox)) *
                                          (size_t)p.Cout + (size_t)co0)
@@ -349,16 +384,17 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] += sbias[c + j];
                 if (f_stats) {
-                    const int cg = co0 + c;
+                    float a1[16], a2[16];
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         const float x = row_ok ? v[j] : 0.f;
-                        const float s1 = warp_sum(x);
-                        const float s2 = warp_sum(x * x);
-                        if (lane == j) {
-                            atomicAdd(p.stats + cg + j, (double)s1);
-                            atomicAdd(p.stats + p.Cout + cg + j, (double)s2);
-                        }
+                        a1[j] = x; a2[j] = x * x;
+                    }
+                    const float s1 = colsum16(a1, lane), s2 = colsum16(a2, lane);
+                    if (!(lane & 1)) {
+                        const int ci = c + colsum_index(lane);
+                        atomicAdd(&sstat[ci], s1);
+                        atomicAdd(&sstat[BN + ci], s2);
                     }
                 }
 #pragma unroll
@@ -444,6 +480,13 @@ conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcPa
                 }
             }
             if (et == 0) DBG_STAMP(11);
+            if (f_stats) {
+                epi_bar();
+                if (et < BN) {
+                    atomicAdd(p.stats + co0 + et, (double)sstat[et]);
+                    atomicAdd(p.stats + p.Cout + co0 + et, (double)sstat[BN + et]);
+                }
+            }
             if (f_store) {
                 fence_async_smem();
                 epi_bar();
@@ -577,7 +620,7 @@ static void layout_smem(const ConvP& p, TcConfig& c) {
     main_bytes = (main_bytes + 1023) & ~(size_t)1023;
     c.off_add = (uint32_t)main_bytes;
     c.off_bias = (uint32_t)(main_bytes + addb);
-    c.smem_bytes = main_bytes + addb + (size_t)c.BN * 4 + 1024;   // + alignment slack
+    c.smem_bytes = main_bytes + addb + (size_t)c.BN * 4 * 3 + 1024;   // bias + 2 x BN stat sums + alignment slack
 }
 
 static TcConfig choose_config(const ConvP& p) {

@@ -41,6 +41,7 @@ struct WgParams {
     float* dw;
     long long s_m, s_n;            // dw strides (elements) of the M-side / N-side channel
     int32_t swap;                  // 0: M = dy channels (cout), N = x channels (cin); 1: the other way round
+    int32_t CM;                    // channels on the M side (rows >= CM of the last tile are zero padding)
     int32_t BNt;                   // N-side channels per CTA (32, 64, 128 or 256)
     int32_t n_cc;                  // channels per N-side TMA chunk (64 -> SW128, 32 -> SW64)
     int32_t n_chunks;              // BNt / n_cc
@@ -215,7 +216,7 @@ wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgP
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
         float* drow = q.dw + (long long)(m0 + row) * q.s_m + (long long)n0c * q.s_n;
-        for (int t = 0; t < ntaps; ++t) {
+        for (int t = 0; t < ntaps && m0 + row < q.CM; ++t) {
             float* dt = drow + ph.taps[grp.tap0 + t].slice;
             for (int c = 0; c < q.BNt; c += 16) {
                 float v[16];
@@ -257,13 +258,22 @@ static int wg_pow2_divisor(int x, int cap) {
     return d;
 }
 
+// M side (128 TMEM lanes): a channel count that is a multiple of 128, else a multiple of 64 (the upper 64 rows
+// are then an out-of-range TMA chunk = zeros).  0: M = cout, 1: M = cin ("swap"), -1: unsupported.
+static int wg_pick_swap(const ConvP& p) {
+    if ((p.Cout % 128) == 0) return 0;
+    if ((p.Cin % 128) == 0) return 1;
+    if ((p.Cout % 64) == 0) return 0;
+    if ((p.Cin % 64) == 0) return 1;
+    return -1;
+}
+
 // `p` is the FORWARD plan with p.x = forward input and p.y = dy.
 bool wgrad_tc_supported(const ConvP& p, int x_dtype, int dy_dtype) {
     if (x_dtype != MSTK_BF16 || dy_dtype != MSTK_BF16) return false;
-    const bool m_is_cout = (p.Cout % 128) == 0;
-    const bool m_is_cin = (p.Cin % 128) == 0;
-    if (!m_is_cout && !m_is_cin) return false;
-    const int cn = m_is_cout ? p.Cin : p.Cout;
+    const int sw = wg_pick_swap(p);
+    if (sw < 0) return false;
+    const int cn = sw ? p.Cout : p.Cin;
     if (!(cn % 64 == 0 || cn == 32)) return false;
     if (p.s_in == 2 && ((p.H & 1) || (p.W & 1))) return false;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return false;
@@ -279,7 +289,8 @@ int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, c
     memset(&q, 0, sizeof(q));
     q.p = p;
     q.dw = dw;
-    q.swap = (p.Cout % 128) == 0 ? 0 : 1;
+    q.swap = wg_pick_swap(p);
+    if (q.swap < 0) return MSTK_EUNSUPPORTED;
     const int CM = q.swap ? p.Cin : p.Cout;
     const int CN = q.swap ? p.Cout : p.Cin;
     q.s_m = q.swap ? s_ci : s_co;
@@ -287,7 +298,8 @@ int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, c
     if (CN == 32) { q.BNt = 32; q.n_cc = 32; }
     else { q.n_cc = 64; q.BNt = (CN % 256 == 0) ? 256 : (CN % 128 == 0) ? 128 : 64; }
     q.n_chunks = q.BNt / q.n_cc;
-    q.m_tiles = CM / TILE_M;
+    q.m_tiles = (CM + TILE_M - 1) / TILE_M;
+    q.CM = CM;
     q.n_tiles = CN / q.BNt;
     q.m_tile_bytes = (uint32_t)(TILE_M * WG_KP * 2);
     q.n_tile_bytes = (uint32_t)(q.BNt * WG_KP * 2);

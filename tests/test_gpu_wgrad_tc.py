@@ -23,6 +23,8 @@ CASES = [
     (37, 1, 1, 128, 128, 1, 1, False),    # Linear (time MLP)
     (9, 4, 4, 256, 512, 1, 1, False),     # attention projection as k1 conv
     (40, 16, 16, 64, 128, 3, 1, False),   # many pixel tiles -> split-K > 1
+    (4, 16, 16, 32, 64, 3, 1, False),     # M side of 64 channels (upper half of the tile = out-of-range chunk), N = 32 (unet.enc1)
+    (4, 16, 16, 64, 32, 3, 1, False),     # swap with a 64-channel M side (unet.dec1)
 ]
 
 
