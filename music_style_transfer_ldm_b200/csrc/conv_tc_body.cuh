@@ -1,0 +1,512 @@
+// Body of the tcgen05 tap-gather implicit-GEMM convolution (see conv_tc.cu for the design notes), shared by the
+// stand-alone kernel (conv_tc.cu) and the persistent layer-program kernel (program.cu).
+#pragma once
+#include <cuda.h>
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace mstk {
+
+constexpr int TC_THREADS = 192;
+constexpr int MAX_STAGES = 8;
+
+struct TcMaps {
+    CUtensorMap a[4];     // input, one per stride-2 parity view (a[0] only for stride 1)
+    CUtensorMap b;        // packed weights [taps*cout][cin]
+    CUtensorMap out[4];   // output, one per conv-transpose phase (out[0] only for conv)
+    CUtensorMap add[4];   // residual tensor, same geometry as out
+};
+
+struct TcParams {
+    ConvP p;
+    int32_t Wt, Ht, Nt;            // tile box; Wt*Ht*Nt == 128
+    int32_t tiles_w, tiles_h, tiles_n;
+    int32_t KC;                    // channels per k-block: 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
+    int32_t BN;                    // output channels per CTA (16..128, multiple of 16)
+    int32_t kb_per_tap;            // Cin / KC
+    int32_t splitk;
+    int32_t stages;
+    int32_t tmem_cols;
+    int32_t out_esz;               // bytes per output element (2 or 4)
+    int32_t out_rowbytes;          // bytes per row of one output staging chunk (<= 128)
+    int32_t out_chunks;            // BN*out_esz / out_rowbytes
+    int32_t add_rowbytes, add_chunks;
+    int32_t use_tma_store;         // y written through the staging tile + TMA
+    int32_t use_tma_add;           // residual prefetched by TMA
+    uint32_t off_stage0;           // shared-memory carve-up (bytes from the 1024-aligned base)
+    uint32_t off_part, off_out, off_add, off_bias;
+    int32_t krot;                  // rotate the K loop per CTA (see the producer)
+    float* ws;                     // split-K workspace
+    unsigned int* counters;        // split-K tile counters
+    long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
+};
+#define DBG_STAMP(i) do { if (q.dbg && (PROG ? blockIdx.x == 0 : (bx == 0 && by == 0 && bz == 0))) q.dbg[i] = clock64(); } while (0)
+
+// ---------------------------------------------------------------------------
+// kernel
+// ---------------------------------------------------------------------------
+// Feature flags: the kernel is instantiated per feature set so that each instance's epilogue is a
+// few hundred instructions (the all-in-one version was ~4000 SASS instructions = 64 KB of code and
+// the epilogue ran at instruction-fetch speed).  A flag that is set still honours the run-time
+// argument; a flag that is clear compiles the feature out.
+enum : uint32_t { F_SPLITK = 1, F_STATS = 2, F_ADDNC = 4, F_ADD = 8, F_DDIM = 16, F_STORE = 32, F_ACTGEN = 64, F_ALL = 127 };
+
+// Column sums over the 32 rows held by a warp (one row per lane, 16 columns per lane): halving butterfly,
+// 16 shuffles instead of 16 x 5.  Returns the sum of column ((lane >> 1) & 15 bit-reversed as below) in every
+// lane; lanes l and l^1 hold the same column.  Column index of a lane: colsum_index(lane).
+__device__ __forceinline__ float colsum16(float (&a)[16], int lane) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const bool up = (lane & 16) != 0;
+        const float send = up ? a[i] : a[i + 8], mine = up ? a[i + 8] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const bool up = (lane & 8) != 0;
+        const float send = up ? a[i] : a[i + 4], mine = up ? a[i + 4] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const bool up = (lane & 4) != 0;
+        const float send = up ? a[i] : a[i + 2], mine = up ? a[i + 2] : a[i];
+        a[i] = mine + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    {
+        const bool up = (lane & 2) != 0;
+        const float send = up ? a[0] : a[1], mine = up ? a[1] : a[0];
+        a[0] = mine + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    return a[0] + __shfl_xor_sync(0xffffffffu, a[0], 1);
+}
+__device__ __forceinline__ int colsum_index(int lane) {
+    return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+}
+
+// Per-CTA resources that outlive one tile (static shared memory of the calling kernel).
+struct TcShared {
+    uint64_t full_bar[MAX_STAGES];
+    uint64_t empty_bar[MAX_STAGES];
+    uint64_t accum_bar, add_bar, part_bar;
+    uint32_t tmem_base;
+    uint32_t is_last;
+};
+
+// One output tile (bx, by, bz) of a launch whose grid would be (gx, gy, *).  PROG = false: the body of the
+// stand-alone kernel (allocates and frees its TMEM columns, fresh mbarriers).  PROG = true: called in a loop by the
+// persistent program kernel (program.cu): TMEM is allocated once by the caller (sh.tmem_base), the mbarriers are
+// invalidated and re-initialised per tile, all 192 threads must call it.
+template <uint32_t F, bool PROG>
+__device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams& q, const int bx, const int by, const int bz,
+                                             const int gx, const int gy, TcShared& sh, uint8_t* smem_raw) {
+    const bool f_split = (F & F_SPLITK) && q.splitk > 1;
+    const bool f_stats = (F & F_STATS) && q.p.stats != nullptr;
+    const bool f_addnc = (F & F_ADDNC) && q.p.add_nc != nullptr;
+    const bool f_add = (F & F_ADD) && q.use_tma_add;
+    const bool f_ddim = (F & F_DDIM) && q.p.has_ddim;
+    const bool f_store = (F & F_STORE) && q.use_tma_store;
+    const bool f_actgen = (F & F_ACTGEN) != 0;
+    uint64_t* const full_bar = sh.full_bar;
+    uint64_t* const empty_bar = sh.empty_bar;
+    uint64_t& accum_bar = sh.accum_bar;
+    uint64_t& add_bar = sh.add_bar;
+    uint64_t& part_bar = sh.part_bar;
+    uint32_t& tmem_base_smem = sh.tmem_base;
+    uint32_t& is_last_smem = sh.is_last;
+
+    const ConvP& p = q.p;
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // tile coordinates
+    const int mt = bx;
+    const int tw = mt % q.tiles_w;
+    const int th = (mt / q.tiles_w) % q.tiles_h;
+    const int tn = mt / (q.tiles_w * q.tiles_h);
+    const int w0 = tw * q.Wt, h0 = th * q.Ht, n0 = tn * q.Nt;
+    const int co0 = by * q.BN;
+    const int phase_idx = bz / q.splitk;
+    const int ks = bz - phase_idx * q.splitk;
+    const Phase& ph = p.ph[phase_idx];
+    const int total_kb = ph.ntaps * q.kb_per_tap;
+    const int kb_begin = (int)(((long long)ks * total_kb) / q.splitk);
+    const int kb_end = (int)(((long long)(ks + 1) * total_kb) / q.splitk);
+    const int nkb = kb_end - kb_begin;
+
+    // shared-memory carve-up (1024-byte aligned for the 128B swizzle atom)
+    const uint32_t a_bytes = TILE_M * q.KC * 2;
+    const uint32_t b_bytes = q.BN * q.KC * 2;
+    const uint32_t b_bytes_al = (b_bytes + 1023u) & ~1023u;
+    const uint32_t stage_bytes = a_bytes + b_bytes_al;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    float* sbias = reinterpret_cast<float*>(smem + q.off_bias);
+
+    if (threadIdx.x == 0) {
+        DBG_STAMP(0);
+        prefetch_tmap(&maps.a[0]);
+        prefetch_tmap(&maps.b);
+        if (f_store) prefetch_tmap(&maps.out[phase_idx]);
+        if (PROG) {
+            // the previous tile's barriers are quiescent (the body ends in __syncthreads): invalidate, then re-arm
+            for (int s = 0; s < MAX_STAGES; ++s) { mbar_inval(&full_bar[s]); mbar_inval(&empty_bar[s]); }
+            mbar_inval(&accum_bar); mbar_inval(&add_bar); mbar_inval(&part_bar);
+        }
+        for (int s = 0; s < (PROG ? MAX_STAGES : q.stages); ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&accum_bar, 1);
+        mbar_init(&add_bar, 1);
+        mbar_init(&part_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (!PROG && warp == 1) {
+        // TMEM allocation (whole warp), base address lands in shared memory
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)),
+                     "r"((uint32_t)q.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+    if (threadIdx.x == 0) DBG_STAMP(1);
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const int npre = nkb < q.stages ? nkb : q.stages;
+            // optional K-loop rotation (tuning knob, off by default): CTAs that share a weight tile start at different
+            // k-blocks so that they pull different B tiles at any instant.  Measured on B200: no effect (the ~0.9 k
+            // cycles per k-block of the small UNet layers is not an L2 hot-spot).
+            const int rot = q.krot ? (int)(((unsigned)bx * 5u + (unsigned)bz) % (unsigned)nkb) : 0;
+            // weights do not depend on the previous kernel: fetch them before the grid dependency resolves
+            for (int it = 0; it < npre; ++it) {
+                const int kb = kb_begin + (it + rot < nkb ? it + rot : it + rot - nkb);
+                const int tap_i = kb / q.kb_per_tap;
+                const int cb = kb - tap_i * q.kb_per_tap;
+                mbar_expect_tx(&full_bar[it], a_bytes + b_bytes);
+                tma_load_2d(&maps.b, &full_bar[it], smem_base + q.off_stage0 + (uint32_t)it * stage_bytes + a_bytes, cb * q.KC,
+                            ph.taps[tap_i].slice * p.Cout + co0);
+            }
+            pdl_wait();
+            pdl_launch_dependents();
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % q.stages;
+                const uint32_t par = (uint32_t)((it / q.stages) & 1);
+                const int kb = kb_begin + (it + rot < nkb ? it + rot : it + rot - nkb);
+                const int tap_i = kb / q.kb_per_tap;
+                const int cb = kb - tap_i * q.kb_per_tap;
+                const Tap t = ph.taps[tap_i];
+                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
+                if (it >= npre) {
+                    mbar_wait(&empty_bar[s], par ^ 1u);
+                    mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
+                    tma_load_2d(&maps.b, &full_bar[s], sa + a_bytes, cb * q.KC, t.slice * p.Cout + co0);
+                }
+                int dy = t.dy, dx = t.dx;
+                const CUtensorMap* mA = &maps.a[0];
+                if (p.s_in == 2) {
+                    const int py = dy & 1, px = dx & 1;        // parity view (works for negative offsets)
+                    dy = (dy - py) / 2;
+                    dx = (dx - px) / 2;
+                    mA = &maps.a[py * 2 + px];
+                }
+                tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
+                if (it == 0) DBG_STAMP(2);
+                if (it == 0 && f_add) {
+                    // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
+                    mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
+                    const int cpr = q.add_rowbytes >> 1;
+                    for (int ch = 0; ch < q.add_chunks; ++ch)
+                        tma_load_4d(&maps.add[phase_idx], &add_bar, smem_base + q.off_add + (uint32_t)(ch * TILE_M * q.add_rowbytes),
+                                    co0 + ch * cpr, w0, h0, n0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(q.BN);
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % q.stages;
+                const uint32_t par = (uint32_t)((it / q.stages) & 1);
+                mbar_wait(&full_bar[s], par);
+                if (it == 0) DBG_STAMP(3);
+                if (it == nkb - 1) DBG_STAMP(4);
+                tc_fence_after();
+                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
+                const uint32_t sb = sa + a_bytes;
+                const uint64_t adesc = make_smem_desc(sa, q.KC);
+                const uint64_t bdesc = make_smem_desc(sb, q.KC);
+                const int ksteps = q.KC / 16;
+                for (int k = 0; k < ksteps; ++k) {
+                    // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
+                    umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);     // frees the smem slot when these MMAs retire
+            }
+            umma_commit(&accum_bar);            // accumulator complete
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int qd = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = qd * 32 + lane;          // GEMM row inside the tile
+        const int w_l = row % q.Wt;
+        const int h_l = (row / q.Wt) % q.Ht;
+        const int n_l = row / (q.Wt * q.Ht);
+        const int n_img = n0 + n_l, hg = h0 + h_l, wg = w0 + w_l;
+        const bool row_ok = n_img < p.N;
+        const int et = threadIdx.x - 64;         // 0..127
+        const int BN = q.BN;
+
+        // ---- work that does not need the accumulator: overlaps the main loop ----
+        if (et < BN) sbias[et] = p.bias ? __ldg(p.bias + co0 + et) : 0.f;   // parameters: safe before the grid dependency
+        float* sstat = sbias + BN;                // [2][BN] per-CTA column sums of the BatchNorm statistics
+        if (f_stats) { for (int i = et; i < 2 * BN; i += 128) sstat[i] = 0.f; }
+        pdl_wait();
+        const size_t pix_off = row_ok ? ((((size_t)n_img * p.Ho + (size_t)(hg * p.s_out + ph.oy)) * p.Wo + (size_t)(wg * p.s_out + ph.ox)) *
+                                         (size_t)p.Cout + (size_t)co0)
+                                      : 0;
+        float xc[16], anc[16];
+        const float* xcur_row = f_ddim ? p.ddim.x_cur + pix_off : nullptr;
+        const float* anc_row = f_addnc ? p.add_nc + (size_t)(row_ok ? n_img : 0) * p.Cout + co0 : nullptr;
+        if (xcur_row && row_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                const float4 t = *reinterpret_cast<const float4*>(xcur_row + j);
+                xc[j] = t.x; xc[j + 1] = t.y; xc[j + 2] = t.z; xc[j + 3] = t.w;
+            }
+        }
+        if (anc_row) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + j));
+                anc[j] = t.x; anc[j + 1] = t.y; anc[j + 2] = t.z; anc[j + 3] = t.w;
+            }
+        }
+        epi_bar();                               // sbias visible to all epilogue threads
+
+        mbar_wait(&accum_bar, 0);
+        if (et == 0) DBG_STAMP(5);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);
+        uint8_t* part = smem + q.off_part;
+        const int pm = (BN >= 32 ? 8 : BN / 4) - 1;       // XOR mask of the private partial-tile layout
+        bool finalize = true;
+
+        if (f_split) {
+            // ---- split-K: stage the fp32 partial tile, reduce it into L2 with the copy engine ----
+            for (int c = 0; c < BN; c += 16) {
+                float v[16];
+                tmem_ld16(taddr + (uint32_t)c, v);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<float4*>(part + (size_t)row * BN * 4 + (size_t)(((c >> 2) + j) ^ (row & pm)) * 16) =
+                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+            fence_async_smem();
+            epi_bar();
+            if (et == 0) DBG_STAMP(8);
+            const size_t tile_lin = ((size_t)phase_idx * gx + mt) * gy + by;
+            float* ws_tile = q.ws + tile_lin * (size_t)(TILE_M * BN);
+            const uint32_t tile_bytes = (uint32_t)(TILE_M * BN * 4);
+            if (et == 0) {
+                bulk_reduce_add_f32(ws_tile, smem_u32(part), tile_bytes);
+                bulk_commit();
+                bulk_wait_all();
+                __threadfence();
+                const unsigned int old = atomicAdd(q.counters + tile_lin, 1u);
+                const unsigned int last = (old == (unsigned int)(q.splitk - 1)) ? 1u : 0u;
+                if (last) {
+                    __threadfence();
+                    fence_async_all();
+                    mbar_expect_tx(&part_bar, tile_bytes);
+                    bulk_load(smem_u32(part), ws_tile, tile_bytes, &part_bar);
+                    q.counters[tile_lin] = 0u;
+                }
+                is_last_smem = last;
+                DBG_STAMP(9);
+            }
+            epi_bar();
+            finalize = is_last_smem != 0;
+            if (finalize) {
+                mbar_wait(&part_bar, 0);
+                // scratch back to zero for the next launch (the tile now lives in shared memory)
+                float4* z = reinterpret_cast<float4*>(ws_tile);
+                for (int i = et; i < TILE_M * BN / 4; i += 128) __stcg(z + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                if (et == 0) DBG_STAMP(10);
+            }
+        }
+
+        if (finalize) {
+            if (f_add) mbar_wait(&add_bar, 0);
+            const int out_cpr = q.out_rowbytes / q.out_esz;
+            const int add_cpr = q.add_rowbytes >> 1;
+            for (int c = 0; c < BN; c += 16) {
+                float v[16];
+                if (f_split) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 t = *reinterpret_cast<const float4*>(part + (size_t)row * BN * 4 + (size_t)(((c >> 2) + j) ^ (row & pm)) * 16);
+                        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+                    }
+                } else {
+                    tmem_ld16(taddr + (uint32_t)c, v);
+                }
+                if (c == 0 && et == 0) DBG_STAMP(13);
+                // prefetch the next chunk's per-row operands
+                float xn_[16], an_[16];
+                const bool more = c + 16 < BN;
+                if (more && xcur_row && row_ok) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const float4 t = *reinterpret_cast<const float4*>(xcur_row + c + 16 + j);
+                        xn_[j] = t.x; xn_[j + 1] = t.y; xn_[j + 2] = t.z; xn_[j + 3] = t.w;
+                    }
+                }
+                if (more && anc_row) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + c + 16 + j));
+                        an_[j] = t.x; an_[j + 1] = t.y; an_[j + 2] = t.z; an_[j + 3] = t.w;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] += sbias[c + j];
+                if (f_stats) {
+                    float a1[16], a2[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float x = row_ok ? v[j] : 0.f;
+                        a1[j] = x; a2[j] = x * x;
+                    }
+                    const float s1 = colsum16(a1, lane), s2 = colsum16(a2, lane);
+                    if (!(lane & 1)) {
+                        const int ci = c + colsum_index(lane);
+                        atomicAdd(&sstat[ci], s1);
+                        atomicAdd(&sstat[BN + ci], s2);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    float x = v[j];
+                    if (f_actgen) {
+                        x = apply_act(x, p.act);
+                        if (p.affine) x = x * p.out_scale + p.out_shift;
+                    } else if (p.act == MSTK_ACT_RELU) {
+                        x = fmaxf(x, 0.f);
+                    }
+                    v[j] = x;
+                }
+                if (c == 0 && et == 0) DBG_STAMP(14);
+                if (anc_row) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] += anc[j];
+                }
+                if (f_add) {
+                    const uint8_t* ab = smem + q.off_add + (size_t)(c / add_cpr) * TILE_M * q.add_rowbytes;
+                    const int j0 = ((c % add_cpr) * 2) >> 4;
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const uint4 t = *reinterpret_cast<const uint4*>(ab + swz_off(row, j0 + h2, q.add_rowbytes));
+                        const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float2 f = __bfloat1622float2(hh[e]);
+                            v[8 * h2 + 2 * e] += f.x; v[8 * h2 + 2 * e + 1] += f.y;
+                        }
+                    }
+                }
+                if (f_ddim && row_ok) {
+                    const DdimP& d = p.ddim;
+                    float xnew[16], x0v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float eps = v[j];
+                        const float dt = d.s1m_t * eps;
+                        const float x0 = (xc[j] - dt) / d.sab_t;
+                        const float dn = d.s1m_n * eps;
+                        xnew[j] = d.sab_n * x0 + dn + d.eta * (dn - dt);
+                        x0v[j] = x0;
+                    }
+                    float* xo = d.x_next + pix_off + c;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(xo + j) = make_float4(xnew[j], xnew[j + 1], xnew[j + 2], xnew[j + 3]);
+                    if (d.x0_pred) {
+                        float* po = d.x0_pred + pix_off + c;
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(po + j) = make_float4(x0v[j], x0v[j + 1], x0v[j + 2], x0v[j + 3]);
+                    }
+                    if (d.x_next_lp) {
+                        uint4 pk[2];
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(xnew[2 * e], xnew[2 * e + 1]);
+                        uint4* lo = reinterpret_cast<uint4*>(d.x_next_lp + pix_off + c);
+                        lo[0] = pk[0]; lo[1] = pk[1];
+                    }
+                }
+                if (f_store) {
+                    uint8_t* ob = smem + q.off_out + (size_t)(c / out_cpr) * TILE_M * q.out_rowbytes;
+                    const int j0 = ((c % out_cpr) * q.out_esz) >> 4;
+                    if (q.out_esz == 4) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<float4*>(ob + swz_off(row, j0 + j, q.out_rowbytes)) =
+                                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    } else {
+                        uint4 pk[2];
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0, q.out_rowbytes)) = pk[0];
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, q.out_rowbytes)) = pk[1];
+                    }
+                }
+                if (c == 0 && et == 0) DBG_STAMP(15);
+                if (more) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) { xc[j] = xn_[j]; anc[j] = an_[j]; }
+                }
+            }
+            if (et == 0) DBG_STAMP(11);
+            if (f_stats) {
+                epi_bar();
+                if (et < BN) {
+                    atomicAdd(p.stats + co0 + et, (double)sstat[et]);
+                    atomicAdd(p.stats + p.Cout + co0 + et, (double)sstat[BN + et]);
+                }
+            }
+            if (f_store) {
+                fence_async_smem();
+                epi_bar();
+                if (et == 0) {
+                    DBG_STAMP(12);
+                    for (int ch = 0; ch < q.out_chunks; ++ch)
+                        tma_store_4d(&maps.out[phase_idx], smem_base + q.off_out + (uint32_t)(ch * TILE_M * q.out_rowbytes),
+                                     co0 + ch * out_cpr, w0, h0, n0);
+                    bulk_commit();
+                    bulk_wait_read();
+                }
+            }
+        }
+        if (et == 0) DBG_STAMP(6);
+        tc_fence_before();
+    }
+
+    __syncthreads();
+    if (!PROG && warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)q.tmem_cols) : "memory");
+        if (lane == 0) DBG_STAMP(7);
+    }
+}
+
+// program.cu: append a fully resolved launch to the program being recorded
+int prog_record_conv(const TcMaps& maps, const TcParams& q, uint32_t flags, int gx, int gy, int gz, size_t smem_bytes);
+
+}  // namespace mstk

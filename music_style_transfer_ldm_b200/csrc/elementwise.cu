@@ -2,6 +2,7 @@
 // arithmetic, loss reductions, pooling.  128-bit vectorised where alignment allows,
 // warp-shuffle reductions, grids sized in multiples of the SM count.
 #include "common.cuh"
+#include "attention_body.cuh"
 
 namespace mstk {
 
@@ -235,67 +236,11 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const flo
 }
 
 // ---------------------------------------------------------------------------
-// attention core: grid (b*heads, ceil(l / QPB)); K_h and V_h staged in shared memory
-// as fp32; one warp per query row.
+// attention core (body in attention_body.cuh): grid (b*heads, ceil(l / QPB))
 // ---------------------------------------------------------------------------
-struct AttnP {
-    const void* q; const void* k; const void* v; void* out;
-    int b, l, s, e, heads, qs, ks, vs, os, dtype;
-};
-constexpr int ATTN_WARPS = 4;
-constexpr int ATTN_QPB = 16;   // queries per CTA
-
 __global__ void __launch_bounds__(ATTN_WARPS * 32) attention_kernel(const AttnP a) {
     extern __shared__ float sm[];
-    const int d = a.e / a.heads;
-    float* Ks = sm;                         // [s][d+1]
-    float* Vs = Ks + (size_t)a.s * (d + 1); // [s][d]
-    float* Ps = Vs + (size_t)a.s * d;       // [ATTN_WARPS][s]
-    float* Qs = Ps + ATTN_WARPS * a.s;      // [ATTN_WARPS][d]
-    const int bh = blockIdx.x;
-    const int b = bh / a.heads, hd = bh - b * a.heads;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < a.s * d; i += blockDim.x) {
-        const int si = i / d, di = i - si * d;
-        Ks[si * (d + 1) + di] = load_as_f(a.k, a.dtype, ((size_t)b * a.s + si) * a.ks + hd * d + di);
-        Vs[si * d + di] = load_as_f(a.v, a.dtype, ((size_t)b * a.s + si) * a.vs + hd * d + di);
-    }
-    __syncthreads();
-    const float scaling = 1.0f / sqrtf((float)d);
-    const int q_begin = blockIdx.y * ATTN_QPB;
-    const int q_end = min(a.l, q_begin + ATTN_QPB);
-    float* pw = Ps + warp * a.s;
-    float* qw = Qs + warp * d;
-    for (int qi = q_begin + warp; qi < q_end; qi += ATTN_WARPS) {
-        for (int di = lane; di < d; di += 32)
-            qw[di] = load_as_f(a.q, a.dtype, ((size_t)b * a.l + qi) * a.qs + hd * d + di) * scaling;
-        __syncwarp();
-        float mx = -INFINITY;
-        for (int si = lane; si < a.s; si += 32) {
-            float acc = 0.f;
-            const float* kr = Ks + si * (d + 1);
-            for (int di = 0; di < d; ++di) acc = fmaf(qw[di], kr[di], acc);
-            pw[si] = acc;
-            mx = fmaxf(mx, acc);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        float sum = 0.f;
-        for (int si = lane; si < a.s; si += 32) {
-            const float ev = expf(pw[si] - mx);
-            pw[si] = ev;
-            sum += ev;
-        }
-        sum = warp_sum(sum);
-        const float inv = 1.f / sum;
-        __syncwarp();
-        for (int di = lane; di < d; di += 32) {
-            float acc = 0.f;
-            for (int si = 0; si < a.s; ++si) acc = fmaf(pw[si], Vs[si * d + di], acc);
-            store_from_f(a.out, a.dtype, ((size_t)b * a.l + qi) * a.os + hd * d + di, acc * inv);
-        }
-        __syncwarp();
-    }
+    attention_unit(a, (int)blockIdx.x, (int)blockIdx.y, sm, ATTN_WARPS);
 }
 
 // ---------------------------------------------------------------------------
@@ -553,6 +498,7 @@ int mstk_attention_fwd(const mstk_attn_args* a, void* stream) {
     AttnP p;
     p.q = a->q; p.k = a->k; p.v = a->v; p.out = a->out; p.b = a->b; p.l = a->l; p.s = a->s; p.e = a->e; p.heads = a->heads;
     p.qs = a->q_stride; p.ks = a->k_stride; p.vs = a->v_stride; p.os = a->out_stride; p.dtype = a->dtype;
+    if (prog_recording()) return prog_record_attn(p);
     const int d = a->e / a->heads;
     const size_t smem = ((size_t)a->s * (d + 1) + (size_t)a->s * d + ATTN_WARPS * a->s + ATTN_WARPS * d) * sizeof(float);
     MSTK_REQUIRE(smem <= 200 * 1024, "attention: s*d too large for the shared-memory kernel (s=%d d=%d)", a->s, d);
