@@ -253,15 +253,90 @@ def train_leg(args, rank, world, dev, barrier):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = t.tolist()
     final = [float(v) for v in loss_h.tolist()]
+    extra = {}
+    if rank == 0:
+        extra = train_rooflines(model, per, dev)
     del tr, model
     torch.cuda.empty_cache()
     return {"metric": "train_samples_per_s", "value": TRAIN_GLOBAL_BATCH * steps / (ms * 1e-3), "unit": "samples/s",
             "ms_per_step": ms / steps, "steps": steps, "global_batch": TRAIN_GLOBAL_BATCH, "batch_per_gpu": per, "scaling": "strong",
             "e2e": {"value": TRAIN_GLOBAL_BATCH * steps / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / steps,
                     "h2d_bytes_per_step": 2 * xh.numel() * 4, "d2h_bytes_per_step": 16},
-            "gpu_launches_per_step": int(launches), "last_losses": final,
+            "gpu_launches_per_step": int(launches), "last_losses": final, **extra,
             "workload": "config4: LDMTrainer.train_step (fwd + 4 losses incl. 2 VGGish feature losses + bwd + Adam), bf16, "
                         "1x128x128 spectrograms, encoder frozen, style_loss_weight 3.0, DDP gradient + BatchNorm-stat all-reduce"}
+
+
+def _time_us(fn, reps=10):
+    import torch
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return 1e3 * e0.elapsed_time(e1) / reps
+
+
+def train_rooflines(model, per, dev):
+    """Rooflines of the training step's two kernel families, measured live (CUDA events, each call repeated
+    back to back, inputs far larger than L2 for the big layers):
+      * tensor: the tcgen05 convolutions of the VGGish feature stack (17 of the step's 19.6 GFLOP/sample), per layer
+        and in aggregate, against the measured bf16 peak;
+      * hbm: the streaming kernels of the feature loss on the first (largest) tap, against the measured copy bandwidth.
+    Algorithmic work: conv = 2*pixels*cout*cin*9 FLOP; sample_stats = one read of the map; feature_mse3 = one read of
+    the three maps; maxpool = one read + a quarter-size write."""
+    import torch
+    from music_style_transfer_ldm_b200 import ops
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    g = torch.Generator().manual_seed(3)
+    three = torch.rand((3 * per, SPEC, SPEC, 1), generator=g).to(dev)
+    fl = model.feature_loss_net
+    ops.RECORD = []
+    with torch.no_grad():
+        taps = fl._taps(three)
+    recs, ops.RECORD = ops.RECORD, None
+    rows = []
+    for rec in recs:
+        if rec["kernel"] != "conv_tc_kernel":
+            continue
+        us = _time_us(rec["replay"], 5)
+        rows.append({"layer": rec["tag"], "us": us, "gflop": conv_flops(rec) / 1e9, "tflops": conv_flops(rec) / (us * 1e-6) / 1e12})
+    fl_sum, us_sum = sum(r["gflop"] for r in rows) * 1e9, sum(r["us"] for r in rows)
+    peak_t = peaks.get("bf16_tflops", 1590.0)
+    tensor = {"bound": "tensor", "kernel": "conv_tc_kernel (VGGish stack, 3 x %d images)" % per, "achieved": fl_sum / (us_sum * 1e-6) / 1e12,
+              "peak": peak_t, "unit": "TFLOP/s", "frac": fl_sum / (us_sum * 1e-6) / 1e12 / peak_t, "layers": rows,
+              "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1590"}
+    f0 = taps[0]
+    nbytes = f0.numel() * f0.element_size()
+    peak_h = peaks.get("hbm_gbs", 6500.0)
+    stats = torch.zeros(6 * per + 4, dtype=torch.float64, device=dev)
+    oa, oc = torch.zeros(1, device=dev), torch.zeros(1, device=dev)
+    lib = ops._lib.load()
+
+    def k_stats():
+        lib.mstk_sample_stats(f0.data_ptr(), ops.dtype_code(f0), 3 * per, f0.numel() // (3 * per), stats.data_ptr(), ops._stream())
+
+    us_stats = _time_us(k_stats)
+    stats.zero_()
+    us_mse = _time_us(lambda: ops.feature_mse3(f0, per, 1.0, oa, oc)) - us_stats          # feature_mse3 = stats + mse kernels
+    us_pool = _time_us(lambda: ops.maxpool2x2(f0))
+    hbm = [{"kernel": "sample_stats_kernel", "bytes": nbytes, "us": us_stats},
+           {"kernel": "feat_mse3_kernel", "bytes": nbytes, "us": us_mse},
+           {"kernel": "maxpool2x2_vec_kernel", "bytes": nbytes * 1.25, "us": us_pool}]
+    for h in hbm:
+        h["achieved_gbs"] = h["bytes"] / (h["us"] * 1e-6) / 1e9
+        h["frac"] = h["achieved_gbs"] / peak_h
+    return {"roofline": tensor, "roofline_hbm": {"bound": "hbm", "peak": peak_h, "unit": "GB/s", "tap": "VGGish tap 1: [%d,128,128,64] bf16" % (3 * per),
+                                                 "kernels": hbm}}
 
 
 # ------------------------------------------------------------------------------------------

@@ -214,6 +214,13 @@ int mstk_sample_stats(const void* f, int dtype, int samples, int64_t inner, doub
 int mstk_feature_mse3(const void* f0, const void* f1, const void* f2, int dtype, int b, int64_t inner,
                       double* st0, double* st1, double* st2, double* scratch, float weight,
                       float* out_a, float* out_c, void* stream);
+/* One-pass form of the same two terms for a whole tap: f = [3*b, h, w, c] (x, reconstruction, style stacked);
+ * per-sample sums and cross terms in one read of f, the terms follow algebraically
+ * (sum (x r_x - y r_y)^2 = r_x^2 Sxx - 2 r_x r_y Sxy + r_y^2 Syy); `pooled` (optional, [3*b, h/2, w/2, c])
+ * receives the 2x2/2 max pool of f (the next VGGish conv's input, vggish.py:113) from the same read.
+ * acc: [8*b] doubles, scratch: 1 double; zeroed by the caller once, left zeroed. */
+int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc,
+                        double* scratch, float weight, float* out_a, float* out_c, void* stream);
 /* 2x2/2 max pool on NHWC (vggish.py:113) */
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
 

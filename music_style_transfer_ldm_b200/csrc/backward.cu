@@ -222,6 +222,44 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) atomicAdd(&scol[ch_prev + k], s[k]);
         }
+    } else if (a.c == 1 && (total & 3) == 0) {
+        // single channel (the decoder's output layer): 4 elements per thread, the bias gradient is ONE sum --
+        // registers -> warp shuffle -> one shared-memory atomic per warp (the generic path below would issue one
+        // shared-memory atomic per ELEMENT on the same address)
+        const size_t nvec = total >> 2;
+        float s = 0.f;
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+            float d[4], d2[4], y[4];
+            load4_rt(a.dy, a.dy_dtype, i << 2, d);
+            if (a.dy2) {
+                load4_rt(a.dy2, a.dy_dtype, i << 2, d2);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) d[k] += d2[k];
+            }
+            if (a.act != MSTK_ACT_NONE) {
+                load4_rt(a.y, a.y_dtype, i << 2, y);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) d[k] *= act_deriv(y[k], a.act, a.y_scale, a.y_shift);
+            } else if (a.y_scale != 1.f) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) d[k] *= a.y_scale;
+            }
+            if (a.g) {
+                if (a.g_dtype == MSTK_F32) {
+                    *reinterpret_cast<float4*>(reinterpret_cast<float*>(a.g) + (i << 2)) = make_float4(d[0], d[1], d[2], d[3]);
+                } else {
+                    uint2 pk;
+                    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+                    h[0] = __floats2bfloat162_rn(d[0], d[1]); h[1] = __floats2bfloat162_rn(d[2], d[3]);
+                    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(a.g) + (i << 2)) = pk;
+                }
+            }
+            s += (d[0] + d[1]) + (d[2] + d[3]);
+        }
+        if (a.dbias) {
+            s = warp_sum(s);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&scol[0], s);
+        }
     } else {
         for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
             float d = load_as_f(a.dy, a.dy_dtype, i);

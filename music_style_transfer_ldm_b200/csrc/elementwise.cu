@@ -591,6 +591,16 @@ int mstk_feature_mse3(const void* f0, const void* f1, const void* f2, int dtype,
                  "feature_mse3: inner must be a multiple of 8 (bf16) / 4 (fp32) and the maps 16-byte aligned");
     return launch_feat_mse3(f0, f1, f2, dtype, b, inner, st0, st1, st2, scratch, weight, out_a, out_c, (cudaStream_t)stream);
 }
+int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc, double* scratch, float weight,
+                        float* out_a, float* out_c, void* stream) {
+    MSTK_REQUIRE(f && acc && scratch && out_a && out_c && b > 0 && b <= 65535 && h > 0 && w > 0 && c > 0, "feature_fused3: bad args");
+    MSTK_REQUIRE(dtype == MSTK_BF16 || dtype == MSTK_F32, "feature_fused3: bad dtype");
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    MSTK_REQUIRE((c % v) == 0 && (long long)h * w * (c / v) < (1ll << 31), "feature_fused3: c must be a multiple of %d", v);
+    MSTK_REQUIRE(!(reinterpret_cast<uintptr_t>(f) & 15) && !(reinterpret_cast<uintptr_t>(pooled) & 15), "feature_fused3: 16-byte alignment");
+    MSTK_REQUIRE(!pooled || (!(h & 1) && !(w & 1)), "feature_fused3: pooling needs even h, w");
+    return launch_feat_fused3(f, pooled, dtype, b, h, w, c, acc, scratch, weight, out_a, out_c, (cudaStream_t)stream);
+}
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream) {
     MSTK_REQUIRE(x && y && n > 0 && h > 1 && w > 1 && c > 0, "maxpool: bad args");
     {

@@ -193,6 +193,159 @@ static unsigned fl_grid_x(long long nvec, int samples) {
     return (unsigned)gx;
 }
 
+// ---------------------------------------------------------------------------
+// The whole VGGish tap of the training step in ONE pass over the feature map of the three image batches
+// x (0), recon (1), style (2), stacked as f[3*nb, h, w, c]:
+//   per sample b: sums  Sx, Sxx, Sr, Srr, Ss, Sss  and the cross terms  Sxr, Srs   -> acc[b][8] (double)
+//   optionally the 2x2/2 max-pooled map (the next conv's input) for all three batches.
+// With r_i = 1/(std_i + 1e-8) the tap terms of loss.py:94-99 follow algebraically, with no second pass:
+//   sum (x r_x - r r_r)^2 = r_x^2 Sxx - 2 r_x r_r Sxr + r_r^2 Srr      (likewise for the (recon, style) pair)
+// The last CTA to finish evaluates them for every sample, adds weight * mean into out_a / out_c and re-zeroes
+// acc and the counter.  Traffic: one read of f (+ a quarter-size write) instead of three reads (+ the write).
+// ---------------------------------------------------------------------------
+template <int DT, bool POOL>
+__global__ void __launch_bounds__(256) feat_fused3_kernel(const void* __restrict__ f, void* pooled, int nb, int h, int w, int c, double* acc,
+                                                         double* scratch, float weight, float* out_a, float* out_c) {
+    __shared__ double red[32];
+    constexpr int V = VecT<DT>::N;
+    const int b = blockIdx.y;
+    const int cv = c / V;
+    const size_t img_vecs = (size_t)h * w * cv;                    // vectors per image
+    float l[8];
+    double d[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { l[k] = 0.f; d[k] = 0.0; }
+    int run = 0;
+    if (POOL) {
+        const int ho = h / 2, wo = w / 2;
+        const unsigned items = (unsigned)ho * wo * cv;
+        for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < items; i += gridDim.x * 256u) {
+            const unsigned ch = i % cv;
+            const unsigned r = i / cv;
+            const unsigned ox = r % wo, oy = r / wo;
+            const size_t q00 = ((size_t)(2 * oy) * w + 2 * ox) * cv + ch;
+            float m[3][V];
+#pragma unroll
+            for (int im = 0; im < 3; ++im)
+#pragma unroll
+                for (int j = 0; j < V; ++j) m[im][j] = -INFINITY;
+#pragma unroll
+            for (int p4 = 0; p4 < 4; ++p4) {
+                const size_t off = q00 + (size_t)(p4 >> 1) * w * cv + (size_t)(p4 & 1) * cv;
+                float x[V], rr[V], s[V];
+                load_vec<DT>(f, (size_t)b * img_vecs + off, x);
+                load_vec<DT>(f, (size_t)(nb + b) * img_vecs + off, rr);
+                load_vec<DT>(f, (size_t)(2 * nb + b) * img_vecs + off, s);
+#pragma unroll
+                for (int j = 0; j < V; ++j) {
+                    l[0] += x[j]; l[1] = fmaf(x[j], x[j], l[1]);
+                    l[2] += rr[j]; l[3] = fmaf(rr[j], rr[j], l[3]);
+                    l[4] += s[j]; l[5] = fmaf(s[j], s[j], l[5]);
+                    l[6] = fmaf(x[j], rr[j], l[6]); l[7] = fmaf(rr[j], s[j], l[7]);
+                    m[0][j] = fmaxf(m[0][j], x[j]); m[1][j] = fmaxf(m[1][j], rr[j]); m[2][j] = fmaxf(m[2][j], s[j]);
+                }
+            }
+            const size_t out_img = (size_t)ho * wo * cv;
+#pragma unroll
+            for (int im = 0; im < 3; ++im) {
+                uint4 o;
+                if (DT == MSTK_BF16) {
+                    __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(m[im][(2 * j) % V], m[im][(2 * j + 1) % V]);
+                } else {
+                    o.x = __float_as_uint(m[im][0]); o.y = __float_as_uint(m[im][1]); o.z = __float_as_uint(m[im][2 % V]); o.w = __float_as_uint(m[im][3 % V]);
+                }
+                reinterpret_cast<uint4*>(pooled)[(size_t)(im * nb + b) * out_img + i] = o;
+            }
+            if (++run == 4) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { d[k] += l[k]; l[k] = 0.f; }
+                run = 0;
+            }
+        }
+    } else {
+        const unsigned nvec = (unsigned)img_vecs;
+        for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < nvec; i += gridDim.x * 256u) {
+            float x[V], rr[V], s[V];
+            load_vec<DT>(f, (size_t)b * img_vecs + i, x);
+            load_vec<DT>(f, (size_t)(nb + b) * img_vecs + i, rr);
+            load_vec<DT>(f, (size_t)(2 * nb + b) * img_vecs + i, s);
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                l[0] += x[j]; l[1] = fmaf(x[j], x[j], l[1]);
+                l[2] += rr[j]; l[3] = fmaf(rr[j], rr[j], l[3]);
+                l[4] += s[j]; l[5] = fmaf(s[j], s[j], l[5]);
+                l[6] = fmaf(x[j], rr[j], l[6]); l[7] = fmaf(rr[j], s[j], l[7]);
+            }
+            if (++run == 16) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { d[k] += l[k]; l[k] = 0.f; }
+                run = 0;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        d[k] += l[k];
+        d[k] = block_sum_d(d[k], red);
+    }
+    __shared__ unsigned int s_last;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(acc + (size_t)b * 8 + k, d[k]);
+        __threadfence();
+        unsigned int* ctr = reinterpret_cast<unsigned int*>(scratch);
+        s_last = (atomicAdd(ctr, 1u) == gridDim.x * gridDim.y - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        const double n = (double)h * w * c;
+        double ta = 0.0, tc = 0.0;
+        for (int s = threadIdx.x; s < nb; s += 256) {
+            double* a = acc + (size_t)s * 8;
+            double v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v[k] = __ldcg(a + k); a[k] = 0.0; }
+            double r3[3];
+#pragma unroll
+            for (int im = 0; im < 3; ++im) {
+                const double mean = v[2 * im] / n;
+                double var = (v[2 * im + 1] - n * mean * mean) / (n - 1.0);
+                if (var < 0) var = 0;
+                r3[im] = 1.0 / ((double)((float)sqrt(var)) + 1e-8);
+            }
+            ta += r3[0] * r3[0] * v[1] - 2.0 * r3[0] * r3[1] * v[6] + r3[1] * r3[1] * v[3];
+            tc += r3[1] * r3[1] * v[3] - 2.0 * r3[1] * r3[2] * v[7] + r3[2] * r3[2] * v[5];
+        }
+        ta = block_sum_d(ta, red);
+        tc = block_sum_d(tc, red);
+        if (threadIdx.x == 0) {
+            const double den = (double)nb * n;
+            atomicAdd(out_a, weight * (float)(ta / den));
+            atomicAdd(out_c, weight * (float)(tc / den));
+            *reinterpret_cast<unsigned int*>(scratch) = 0u;
+        }
+    }
+}
+
+int launch_feat_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc, double* scratch, float weight,
+                       float* out_a, float* out_c, cudaStream_t st) {
+    const int v = dtype == MSTK_BF16 ? 8 : 4;
+    const long long items = pooled ? (long long)(h / 2) * (w / 2) * (c / v) : (long long)h * w * (c / v);
+    dim3 grid(fl_grid_x(items, b), (unsigned)b);
+    if (dtype == MSTK_BF16) {
+        if (pooled) feat_fused3_kernel<MSTK_BF16, true><<<grid, 256, 0, st>>>(f, pooled, b, h, w, c, acc, scratch, weight, out_a, out_c);
+        else feat_fused3_kernel<MSTK_BF16, false><<<grid, 256, 0, st>>>(f, pooled, b, h, w, c, acc, scratch, weight, out_a, out_c);
+    } else {
+        if (pooled) feat_fused3_kernel<MSTK_F32, true><<<grid, 256, 0, st>>>(f, pooled, b, h, w, c, acc, scratch, weight, out_a, out_c);
+        else feat_fused3_kernel<MSTK_F32, false><<<grid, 256, 0, st>>>(f, pooled, b, h, w, c, acc, scratch, weight, out_a, out_c);
+    }
+    MSTK_CHECK_LAUNCH("feature_fused3");
+    return MSTK_OK;
+}
+
 bool feat_vec_ok(const void* f, int dtype, long long inner) {
     const int v = dtype == MSTK_BF16 ? 8 : 4;
     return (inner % v) == 0 && (reinterpret_cast<uintptr_t>(f) & 15) == 0 && inner / v < (1ll << 31);

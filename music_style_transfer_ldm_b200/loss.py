@@ -87,6 +87,31 @@ class VGGishFeatureLoss(nn.Module):
                 h = ops.maxpool2x2(h)
         return taps
 
+    def _loss3(self, three_nhwc_f32: torch.Tensor, b: int, out_a: torch.Tensor, out_c: torch.Tensor) -> None:
+        """Training-step form (train.py:182-186 evaluates the loss on (x, recon) and on (recon, style)): ``three`` =
+        [x; recon; style] stacked, one pass of the frozen stack; every tap is ONE streaming kernel that yields both
+        pair terms and the pooled input of the next conv."""
+        from .model import _DEFAULT_PRECISION, _act_dtype
+        adt = _act_dtype(self.precision or _DEFAULT_PRECISION)
+        layers = list(self.features)
+        convs = [i for i, l in enumerate(layers) if isinstance(l, nn.Conv2d)]
+        h = three_nhwc_f32
+        for ci, idx in enumerate(convs):
+            layer = layers[idx]
+            first = layer.in_channels == 1
+            wp, bias = self._packed(idx, torch.float32 if first else adt)
+            h = ops.conv(h, wp, bias, ksize=3, stride=1, act=ACT_RELU, out_dtype=adt)
+            last = ci == len(convs) - 1
+            pool = (not last) and idx + 2 < len(layers) and isinstance(layers[idx + 2], nn.MaxPool2d)
+            vec = 8 if adt == torch.bfloat16 else 4
+            if h.shape[3] % vec == 0 and h.shape[1] % 2 == 0 and h.shape[2] % 2 == 0:
+                pooled = ops.feature_fused3(h, b, 1.0 / len(convs), out_a, out_c, pool)
+            else:       # odd shapes: the separate kernels
+                ops.feature_mse3(h, b, 1.0 / len(convs), out_a, out_c)
+                pooled = ops.maxpool2x2(h) if pool else None
+            if pool:
+                h = pooled
+
     def forward(self, predicted, target):
         p = _as_cuda_f32(predicted, "VGGishFeatureLoss")
         t = _as_cuda_f32(target, "VGGishFeatureLoss")

@@ -418,6 +418,22 @@ def feature_mse3(f_all: torch.Tensor, b: int, weight: float, out_a: torch.Tensor
     _count(2)
 
 
+def feature_fused3(f_all: torch.Tensor, b: int, weight: float, out_a: torch.Tensor, out_c: torch.Tensor, pool: bool):
+    """One pass over a VGGish tap f_all [3b,h,w,c]: accumulates the tap terms of (f[:b], f[b:2b]) into out_a and of
+    (f[b:2b], f[2b:]) into out_c; returns the 2x2 max-pooled map when ``pool`` (else None)."""
+    lib = _lib.load()
+    _dev(f_all, "feat_fused3.f")
+    n3, h, w, c = f_all.shape
+    if n3 != 3 * b:
+        raise MstkError("feature_fused3: expected a [3b,h,w,c] tensor")
+    pooled = torch.empty((n3, h // 2, w // 2, c), dtype=f_all.dtype, device=f_all.device) if pool else None
+    tmp = _loss_scratch(f_all.device, 8 * b + 2)
+    check(lib.mstk_feature_fused3(_p(f_all), _p(pooled), dtype_code(f_all), b, h, w, c, tmp.data_ptr(), tmp.data_ptr() + 64 * b, weight,
+                                  _p(out_a), _p(out_c), _stream()), "mstk_feature_fused3")
+    _count(1)
+    return pooled
+
+
 def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     _dev(x, "maxpool.x")

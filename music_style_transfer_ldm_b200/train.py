@@ -310,12 +310,11 @@ class LDMTrainer:
         H, W = xs.shape[1], xs.shape[2]
         three = torch.empty((3 * B, H, W, 1), dtype=torch.float32, device=dev)
         three[:B].copy_(xs); three[B:2 * B].copy_(rec); three[2 * B:].copy_(ss)
-        taps = fl._taps(three)                                                   # one pass of the frozen stack for all three images
         perc = torch.zeros(1, dtype=torch.float32, device=dev)
         styl = torch.zeros(1, dtype=torch.float32, device=dev)
-        for f in taps:
-            # perc: compression_loss's perceptual term (loss.py:40); styl: style_loss (loss.py:104-106); one fused pass
-            ops.feature_mse3(f, B, 1.0 / len(taps), perc, styl)
+        # one pass of the frozen stack for all three images; perc: compression_loss's perceptual term (loss.py:40),
+        # styl: style_loss (loss.py:104-106); each tap = one conv + one fused streaming kernel
+        fl._loss3(three, B, perc, styl)
         comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
         total = comp + den + self.style_loss_weight * styl.squeeze(0)
 

@@ -53,3 +53,27 @@ def test_maxpool_vec(shape, dt):
     x = torch.randn(shape, generator=gen(shape[1])).to(dt).float()
     got = nchw(ops.maxpool2x2(nhwc(x, dt).to(DEV))).cpu()
     assert torch.equal(got, F.max_pool2d(x, 2, 2))
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape,pool", [((3, 64, 16, 16), True), ((2, 128, 8, 12), False), ((4, 8, 6, 10), True)])
+def test_feature_fused3(shape, pool, dt):
+    """one-pass tap (sums + cross terms + max pool) vs the two-pass reference formula"""
+    from music_style_transfer_ldm_b200 import ops
+    g = gen(sum(shape) + 1)
+    b = shape[0]
+    maps = [(torch.relu(torch.randn(shape, generator=g)) * s).to(dt).float() for s in (1.0, 3.0, 0.25)]
+    # make the first pair strongly correlated: the algebraic form must survive the cancellation
+    maps[1] = (maps[0] * 2.0 + 0.05 * torch.relu(torch.randn(shape, generator=g))).to(dt).float()
+    ref_a, ref_c = _term(maps[0], maps[1]), _term(maps[1], maps[2])
+    f_all = torch.cat([nhwc(m, dt) for m in maps], dim=0).to(DEV)
+    for _ in range(2):      # accumulators and counter must come back zeroed
+        out_a, out_c = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+        pooled = ops.feature_fused3(f_all, b, 1.0, out_a, out_c, pool)
+        assert_close(out_a, ref_a, 1e-3, "feature_fused3 pair (0,1)")
+        assert_close(out_c, ref_c, 1e-4, "feature_fused3 pair (1,2)")
+        if pool:
+            want = F.max_pool2d(torch.cat(maps, dim=0), 2, 2)
+            assert torch.equal(nchw(pooled).cpu(), want)
+        else:
+            assert pooled is None

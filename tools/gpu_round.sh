@@ -14,3 +14,12 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:"con
 tail -n 5 gpurun_out/t_gpu.log; tail -n 4 gpurun_out/smoke.log; cut -c 1-1800 gpurun_out/bench.log; tail -n 5 gpurun_out/bench.err; cut -c 1-600 gpurun_out/bench_ref.log
 timeout 300 python tools/profile_train.py 256 3 > gpurun_out/pt_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/train_launches.csv python tools/profile_train.py 256 3 > gpurun_out/pt_ncu.log 2>&1; echo "ncu_train rc=$?" | tee -a gpurun_out/rc.txt
+timeout 900 ncu --set full --clock-control none -k regex:"conv_tc_kernel|wgrad_tc_kernel|feat_fused3_kernel|conv_cin1_row|wgrad_edge" --launch-skip 70 --launch-count 36 -o gpurun_out/prof_train python tools/profile_train.py 256 3 > gpurun_out/prof_train_ncu.log 2>&1; echo "ncu_full_train rc=$?" | tee -a gpurun_out/rc.txt
+# keep the raw pages as CSV; drop reports that would push gpurun_out over the 64 MiB merge limit
+for r in prof_step prof_train; do
+  if [ -f gpurun_out/$r.ncu-rep ]; then
+    ncu -i gpurun_out/$r.ncu-rep --page raw --csv > gpurun_out/${r}_raw.csv 2>/dev/null
+    sz=$(stat -c %s gpurun_out/$r.ncu-rep); if [ "$sz" -gt 25000000 ]; then rm -f gpurun_out/$r.ncu-rep; fi
+  fi
+done
+du -sh gpurun_out | tee -a gpurun_out/rc.txt
