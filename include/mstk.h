@@ -352,6 +352,10 @@ int mstk_eps_grad(const void* dx0, int dx0_dtype, const float* eps_hat, const fl
 /* torch.optim.Adam (no amsgrad, no weight decay) over a flat fp32 arena; `step` is the 1-based step count */
 int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
                    int64_t step, float grad_scale, void* stream);
+/* The same update with the step count (>= 1) read from device memory, so that a CUDA graph of the whole training
+ * step can be replayed (the caller increments *step_dev on the stream before this call). */
+int mstk_adam_step_dev(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
+                       const int64_t* step_dev, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

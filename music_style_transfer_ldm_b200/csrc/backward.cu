@@ -493,7 +493,14 @@ __global__ void eps_grad_kernel(const void* __restrict__ dx0, int dx0_dtype, con
 // torch.optim.Adam single-tensor semantics: exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2*v + (1-b2) g^2;
 // denom = sqrt(v)/sqrt(bc2) + eps; p -= (lr/bc1) * m/denom
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                                                   size_t count, float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, float gs) {
+                                                   size_t count, float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, float gs,
+                                                   const long long* __restrict__ step_dev) {
+    if (step_dev) {
+        // step counter in device memory (CUDA-graph replays): bias corrections computed here, in double as on the host
+        const double s = (double)step_dev[0];
+        bc1 = (float)(1.0 - pow((double)b1, s));
+        bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, s));
+    }
     const size_t nvec = count >> 2;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
         float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
@@ -794,7 +801,18 @@ int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, f
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
     adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, (float)bc1,
-                                                                               (float)sqrt(bc2), grad_scale);
+                                                                               (float)sqrt(bc2), grad_scale, nullptr);
+    MSTK_CHECK_LAUNCH("adam");
+    return MSTK_OK;
+}
+
+int mstk_adam_step_dev(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
+                       const int64_t* step_dev, float grad_scale, void* stream) {
+    MSTK_REQUIRE(p && g && m && v && count > 0 && step_dev, "adam: bad args");
+    MSTK_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+                 "adam: arenas must be 16-byte aligned");
+    adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, 1.f, 1.f, grad_scale,
+                                                                               reinterpret_cast<const long long*>(step_dev));
     MSTK_CHECK_LAUNCH("adam");
     return MSTK_OK;
 }

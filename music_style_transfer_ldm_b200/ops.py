@@ -600,7 +600,15 @@ def eps_grad(dx0: torch.Tensor, eps_hat, eps, alpha_bar, t, scale_d: float, g_dt
     return g
 
 
-def adam_step(p, g, m, v, *, lr: float, beta1: float, beta2: float, eps: float, step: int, grad_scale: float = 1.0) -> None:
+def adam_step(p, g, m, v, *, lr: float, beta1: float, beta2: float, eps: float, step, grad_scale: float = 1.0) -> None:
+    """``step``: python int, or a 1-element int64 CUDA tensor holding the step count (graph-replayable)."""
     lib = _lib.load()
+    if isinstance(step, torch.Tensor):
+        if step.dtype != torch.int64 or not step.is_cuda:
+            raise MstkError("adam_step: a device step counter must be an int64 CUDA tensor")
+        check(lib.mstk_adam_step_dev(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, _p(step), grad_scale, _stream()),
+              "mstk_adam_step_dev")
+        _count()
+        return
     check(lib.mstk_adam_step(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, step, grad_scale, _stream()), "mstk_adam_step")
     _count()

@@ -142,6 +142,14 @@ class LDMTrainer:
         self.lr = float(lr)
         self.betas, self.eps = (0.9, 0.999), 1e-8          # torch.optim.Adam defaults (train.py:156)
         self.step_count = 0
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=device)
+        # Whole-step CUDA graph: after `graph_warmup` eager steps the step (forward, losses, backward, bucketed all-reduce,
+        # Adam) is captured once per input shape and replayed; t and the noise come from torch's graph-safe CUDA
+        # generator exactly as in eager mode.  Only used when t / noise are not passed in.
+        self.use_cuda_graph = True
+        self.graph_warmup = 2
+        self._graph = None
+        self._eager_steps = 0
         self.group, self.world = process_group, int(world_size)
         if self.device.type != "cuda":
             raise MstkError("LDMTrainer: the training step runs on sm_100a kernels only (no CPU fallback)")
@@ -253,6 +261,41 @@ class LDMTrainer:
 
     # -- the step ---------------------------------------------------------------------------
     def train_step_device(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """Public device-side step: eager for the first steps / explicit t, noise; afterwards a CUDA-graph replay."""
+        if (not self.use_cuda_graph or t is not None or noise is not None or not content_spec.is_cuda
+                or torch.cuda.is_current_stream_capturing()):
+            return self._step_impl(content_spec, style_spec, t, noise)
+        key = (tuple(content_spec.shape), tuple(style_spec.shape), self.model._precision())
+        if self._graph is not None and self._graph["key"] != key:
+            self._graph = None
+            self._eager_steps = 0
+        if self._graph is None:
+            if self._eager_steps < self.graph_warmup:
+                self._eager_steps += 1
+                return self._step_impl(content_spec, style_spec, None, None)
+            ent = {"key": key, "x": content_spec.detach().float().contiguous().clone(),
+                   "s": style_spec.detach().float().contiguous().clone()}
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0, c0 = ops.LAUNCHES, self.step_count
+            with torch.cuda.graph(g):
+                ent["out"] = self._step_impl(ent["x"], ent["s"], None, None)
+            ent["launches"] = ops.LAUNCHES - n0
+            ops.LAUNCHES, self.step_count = n0, c0          # capture enqueued nothing
+            ent["graph"] = g
+            self._graph = ent
+        ent = self._graph
+        ent["x"].copy_(content_spec)
+        ent["s"].copy_(style_spec)
+        ent["graph"].replay()
+        self.step_count += 1
+        ops._count(ent["launches"])
+        for m in self.model.modules():                       # parameters changed under any packed copies made outside the graph
+            if m is not self.model.feature_loss_net:
+                m.__dict__.pop("_mstk_cache", None)
+        return ent["out"]
+
+    def _step_impl(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         """One optimisation step on this rank's shard.  ``t`` [B] int64 and ``noise`` [B,C,h,w] (NCHW, the reference's
         randn_like shape) may be passed in (parity tests, data-parallel sharding of a globally drawn batch); otherwise
         they are drawn as the reference does (train.py:172, model.py:110).  Returns the four losses as 0-dim tensors."""
@@ -376,8 +419,9 @@ class LDMTrainer:
         # ================= update (torch.optim.Adam, train.py:156, 200) =================
         self.reducer.wait()
         self.step_count += 1
+        self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
-                      eps=self.eps, step=self.step_count, grad_scale=1.0 / self.world)
+                      eps=self.eps, step=self.step_dev, grad_scale=1.0 / self.world)
         for m in model.modules():                       # parameters changed under the packed copies
             if m is not fl:
                 m.__dict__.pop("_mstk_cache", None)

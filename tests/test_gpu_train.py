@@ -92,3 +92,26 @@ def test_reference_api_and_errors(sd):
     m2 = M.LDM(latent_dim=32, pretrained_path=None).to(DEV)      # encoder not frozen -> not the reference's LDM stage
     with pytest.raises(MstkError):
         LDMTrainer(m2, None, torch.device(DEV))
+
+
+def test_graph_replayed_step_matches_eager(sd):
+    """The whole-step CUDA graph (captured after two eager steps) must reproduce the eager step: same seeds ->
+    same t / noise from torch's CUDA generator -> same losses (up to the split-K / atomic summation order)."""
+    g = torch.Generator().manual_seed(3)
+    x = torch.rand((8, 1, 128, 128), generator=g).to(DEV)
+    s = torch.rand((8, 1, 128, 128), generator=g).to(DEV)
+    curves = {}
+    for mode in ("eager", "graph"):
+        m, tr = _trainer(sd, "bf16", 5e-4, 3.0)
+        tr.use_cuda_graph = mode == "graph"
+        rows = []
+        for i in range(6):
+            torch.cuda.manual_seed(1000 + i)
+            out = tr.train_step(x, s)
+            rows.append([out[k] for k in KEYS])
+        if mode == "graph":
+            assert tr._graph is not None and tr._graph["launches"] > 100, "the step was not captured"
+            assert tr.step_count == 6 and int(tr.step_dev.item()) == 6
+        curves[mode] = np.asarray(rows)
+    assert np.isfinite(curves["graph"]).all()
+    np.testing.assert_allclose(curves["graph"], curves["eager"], rtol=2e-2, err_msg="graph-replayed steps vs eager steps")
