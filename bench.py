@@ -192,7 +192,7 @@ def kernel_roofline(model, peaks, reps=20):
 TRAIN_GLOBAL_BATCH = 256
 
 
-def train_leg(args, rank, world, dev, barrier):
+def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True):
     """Returns a dict for the JSON line (rank 0) with train samples/s: device-resident and end-to-end
     (pinned host batch -> device inside the timed region, 4 loss scalars read back every step)."""
     import torch
@@ -201,9 +201,10 @@ def train_leg(args, rank, world, dev, barrier):
     from music_style_transfer_ldm_b200 import ops
     from music_style_transfer_ldm_b200.train import LDMTrainer
     from oracle import ldm_oracle as O
-    if TRAIN_GLOBAL_BATCH % world:
-        return {"skipped": f"global batch {TRAIN_GLOBAL_BATCH} not divisible by {world} ranks"}
-    per = TRAIN_GLOBAL_BATCH // world
+    gb = global_batch or TRAIN_GLOBAL_BATCH
+    if gb % world:
+        return {"skipped": f"global batch {gb} not divisible by {world} ranks"}
+    per = gb // world
     model = M.LDM(latent_dim=32, pretrained_path=None)
     model.load_state_dict(O.make_state_dict(1234), strict=True)
     model._freeze_encoder()
@@ -254,13 +255,14 @@ def train_leg(args, rank, world, dev, barrier):
     ms, ms_e2e = t.tolist()
     final = [float(v) for v in loss_h.tolist()]
     extra = {}
-    if rank == 0:
+    if rank == 0 and rooflines:
         extra = train_rooflines(model, per, dev)
     del tr, model
     torch.cuda.empty_cache()
-    return {"metric": "train_samples_per_s", "value": TRAIN_GLOBAL_BATCH * steps / (ms * 1e-3), "unit": "samples/s",
-            "ms_per_step": ms / steps, "steps": steps, "global_batch": TRAIN_GLOBAL_BATCH, "batch_per_gpu": per, "scaling": "strong",
-            "e2e": {"value": TRAIN_GLOBAL_BATCH * steps / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / steps,
+    return {"metric": "train_samples_per_s", "value": gb * steps / (ms * 1e-3), "unit": "samples/s",
+            "ms_per_step": ms / steps, "steps": steps, "global_batch": gb, "batch_per_gpu": per,
+            "scaling": "strong" if gb == TRAIN_GLOBAL_BATCH else "weak",
+            "e2e": {"value": gb * steps / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / steps,
                     "h2d_bytes_per_step": 2 * xh.numel() * 4, "d2h_bytes_per_step": 16},
             "gpu_launches_per_step": int(launches), "last_losses": final, **extra,
             "workload": "config4: LDMTrainer.train_step (fwd + 4 losses incl. 2 VGGish feature losses + bwd + Adam), bf16, "
@@ -420,11 +422,14 @@ def run_cuda(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = t.tolist()
-    train = None
+    train = train_weak = None
     if not args.no_train:
         del model
         torch.cuda.empty_cache()
         train = train_leg(args, rank, world, dev, barrier)
+        if world > 1:
+            # supplementary: the same step with the PER-GPU batch held at 256 (weak scaling of the training step)
+            train_weak = train_leg(args, rank, world, dev, barrier, global_batch=TRAIN_GLOBAL_BATCH * world, rooflines=False)
         model = M.LDM(latent_dim=32, pretrained_path=None)          # fresh sampler model for the roofline leg
         model.load_state_dict(sd, strict=True)
         model.to(dev).eval().set_precision(args.precision)
@@ -454,7 +459,7 @@ def run_cuda(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
-            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train,
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak,
             "samples_steps_per_s": value * BATCH,
             "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
             "layers": rows,

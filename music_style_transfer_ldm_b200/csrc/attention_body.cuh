@@ -13,7 +13,8 @@ struct AttnP {
     int b, l, s, e, heads, qs, ks, vs, os, dtype;
 };
 constexpr int ATTN_WARPS = 4;
-constexpr int ATTN_QPB = 16;   // queries per CTA
+constexpr int ATTN_QPB = 4;    // queries per CTA = one per warp: the UNet's L = 16 / 4 token maps are latency bound, so every
+                               // query row gets its own warp (K/V staging is repeated per CTA from L2, 4 KB)
 
 // One (batch*head, query block) unit, executed by all `nwarps` warps of the calling CTA; `sm` needs
 // attn_smem_floats(a, nwarps) floats.  Ends with the CTA's threads past their last shared-memory access only after

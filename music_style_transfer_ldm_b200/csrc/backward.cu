@@ -190,8 +190,9 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) s[k] = 0.f;
         int ch_prev = -1;
-        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
-            const int ch = (int)((i << 3) % (size_t)a.c);
+        ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
+            const int ch = cw.ch;
             float d[8], d2[8], y[8];
             load8_rt(a.dy, a.dy_dtype, i, d);
             if (a.dy2) {
@@ -294,8 +295,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdP a) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) { p0[k] = 0.f; p1[k] = 0.f; }
     int ch_prev = -1;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
-        const int ch = (int)((i << 3) % (size_t)a.c);
+    ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
+        const int ch = cw.ch;
         if (ch != ch_prev && ch_prev >= 0) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) { atomicAdd(&s0[ch_prev + k], p0[k]); atomicAdd(&s1[ch_prev + k], p1[k]); p0[k] = 0.f; p1[k] = 0.f; }
@@ -335,8 +337,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdP a) {
     }
     __syncthreads();
     const size_t nvec = ((size_t)a.rows * a.c) >> 3;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
-        const int ch = (int)((i << 3) % (size_t)a.c);
+    ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
+        const int ch = cw.ch;
         float d[8], v[8];
         load8_rt(a.dy, a.dy_dtype, i, d);
         load8_rt(a.v, a.v_dtype, i, v);
@@ -473,7 +476,14 @@ __global__ void add_bcast_kernel(const void* __restrict__ y, const void* __restr
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         float v = load_as_f(y, dtype, i);
         if (add) v += load_as_f(add, dtype, i);
-        if (add_nc) v += add_nc[(i / ((size_t)hw * c)) * c + (i % c)];
+        if (add_nc) {
+            if (total < (1ull << 32)) {
+                const unsigned i32 = (unsigned)i, per = (unsigned)(hw * c);
+                v += add_nc[(i32 / per) * (unsigned)c + (i32 % (unsigned)c)];
+            } else {
+                v += add_nc[(i / ((size_t)hw * c)) * c + (i % c)];
+            }
+        }
         store_from_f(out, dtype, i, v);
     }
 }
@@ -553,7 +563,7 @@ struct EdgeWgradP {
     int N, Hv, Wv, C, Hs, Ws, ss;
 };
 
-template <int K, int CH>
+template <int K, int CH, bool SF32>
 __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
     extern __shared__ float acc_s[];                  // [C][K*K]
     const int tpp = q.C / CH;                         // threads per pixel
@@ -570,9 +580,16 @@ __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
     const long long npix = (long long)q.N * q.Hv * q.Wv;
     if (slot < ppb) {
         for (long long pix = (long long)blockIdx.x * ppb + slot; pix < npix; pix += (long long)gridDim.x * ppb) {
-            const int n = (int)(pix / ((long long)q.Hv * q.Wv));
-            const int r = (int)(pix - (long long)n * q.Hv * q.Wv);
-            const int vh = r / q.Wv, vw = r - vh * q.Wv;
+            int n, r;
+            if (npix < (1ll << 31)) {          // 32-bit index arithmetic whenever it fits (a 64-bit division is ~100 instructions)
+                const unsigned p32 = (unsigned)pix, hw = (unsigned)(q.Hv * q.Wv);
+                n = (int)(p32 / hw);
+                r = (int)(p32 - (unsigned)n * hw);
+            } else {
+                n = (int)(pix / ((long long)q.Hv * q.Wv));
+                r = (int)(pix - (long long)n * q.Hv * q.Wv);
+            }
+            const int vh = (int)((unsigned)r / (unsigned)q.Wv), vw = r - vh * q.Wv;
             float vv[CH];
             const __nv_bfloat16* vp = q.v + pix * q.C + cg * CH;
             if (CH == 8) {
@@ -588,19 +605,27 @@ __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
             }
             const int sh0 = vh * q.ss - 1, sw0 = vw * q.ss - 1;
             const size_t sbase = (size_t)n * q.Hs * q.Ws;
+            // the K*K scalar window FIRST, as independent branch-free loads (clamped address, zero by select): with a
+            // branch per tap the compiler kept load -> FMA -> load order and every tap paid a serial L2 round trip
+            float sv[K * K];
 #pragma unroll
             for (int ky = 0; ky < K; ++ky) {
                 const int sh = sh0 + ky;
-                const bool okh = sh >= 0 && sh < q.Hs;
+                const int shc = min(max(sh, 0), q.Hs - 1);
 #pragma unroll
                 for (int kx = 0; kx < K; ++kx) {
                     const int sw = sw0 + kx;
-                    float sv = 0.f;
-                    if (okh && sw >= 0 && sw < q.Ws) sv = load_as_f(q.s, q.s_dtype, sbase + (size_t)sh * q.Ws + sw);
-#pragma unroll
-                    for (int c = 0; c < CH; ++c) acc[ky * K + kx][c] = fmaf(vv[c], sv, acc[ky * K + kx][c]);
+                    const int swc = min(max(sw, 0), q.Ws - 1);
+                    const size_t si = sbase + (size_t)shc * q.Ws + swc;
+                    const float raw = SF32 ? __ldg(reinterpret_cast<const float*>(q.s) + si)
+                                           : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(q.s)[si]);
+                    sv[ky * K + kx] = (sh == shc && sw == swc) ? raw : 0.f;
                 }
             }
+#pragma unroll
+            for (int t = 0; t < K * K; ++t)
+#pragma unroll
+                for (int c = 0; c < CH; ++c) acc[t][c] = fmaf(vv[c], sv[t], acc[t][c]);
         }
 #pragma unroll
         for (int t = 0; t < K * K; ++t)
@@ -625,7 +650,8 @@ static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
         const int ppb = 256 / (q.C / 8);
         long long blocks = (npix + ppb - 1) / ppb;
         if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();
-        wgrad_edge_kernel<3, 8><<<(unsigned)blocks, 256, (size_t)q.C * 9 * sizeof(float), st>>>(q);
+        if (q.s_dtype == MSTK_F32) wgrad_edge_kernel<3, 8, true><<<(unsigned)blocks, 256, (size_t)q.C * 9 * sizeof(float), st>>>(q);
+        else wgrad_edge_kernel<3, 8, false><<<(unsigned)blocks, 256, (size_t)q.C * 9 * sizeof(float), st>>>(q);
         MSTK_CHECK_LAUNCH("wgrad_edge(cin=1)");
         return MSTK_OK;
     }
@@ -637,7 +663,8 @@ static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
         const int ppb = 256 / (q.C / 4);
         long long blocks = (npix + ppb - 1) / ppb;
         if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();
-        wgrad_edge_kernel<4, 4><<<(unsigned)blocks, 256, (size_t)q.C * 16 * sizeof(float), st>>>(q);
+        if (q.s_dtype == MSTK_F32) wgrad_edge_kernel<4, 4, true><<<(unsigned)blocks, 256, (size_t)q.C * 16 * sizeof(float), st>>>(q);
+        else wgrad_edge_kernel<4, 4, false><<<(unsigned)blocks, 256, (size_t)q.C * 16 * sizeof(float), st>>>(q);
         MSTK_CHECK_LAUNCH("wgrad_edge(cout=1)");
         return MSTK_OK;
     }

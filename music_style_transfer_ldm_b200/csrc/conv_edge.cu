@@ -266,8 +266,11 @@ template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bflo
 }
 
 // x [N,H,W,Cin] (T), w packed [16][1][Cin] (T), y [N,2H,2W,1] (TO)
+// One thread = 8 channels of one input-grid position (Cin/8 consecutive lanes share a position, so a warp reads
+// whole 128-byte pixel rows); it loads its 3x3 neighbourhood as nine independent 16-byte loads, accumulates the
+// four output phases over its 8 channels and the lanes of a position are summed with shuffles.
 template <typename T, typename TO>
-__global__ void __launch_bounds__(128) convt4_cout1_kernel(const EdgeP a) {
+__global__ void __launch_bounds__(192, 2) convt4_cout1_kernel(const EdgeP a) {
     extern __shared__ float sw[];                 // [16][Cin] fp32
     const T* __restrict__ wsrc = reinterpret_cast<const T*>(a.w);
     for (int i = threadIdx.x; i < 16 * a.Cin; i += blockDim.x) sw[i] = to_f(wsrc[i]);
@@ -275,56 +278,81 @@ __global__ void __launch_bounds__(128) convt4_cout1_kernel(const EdgeP a) {
     const T* __restrict__ X = reinterpret_cast<const T*>(a.x);
     TO* __restrict__ Y = reinterpret_cast<TO*>(a.y);
     const float b0 = a.bias ? a.bias[0] : 0.f;
-    const size_t items = (size_t)a.N * a.H * a.W;
-    for (size_t it = blockIdx.x * (size_t)blockDim.x + threadIdx.x; it < items; it += (size_t)gridDim.x * blockDim.x) {
-        const int w = (int)(it % a.W);
-        const int h = (int)((it / a.W) % a.H);
-        const int n = (int)(it / ((size_t)a.W * a.H));
-        float acc[2][2] = {{b0, b0}, {b0, b0}};
+    const int tpp = a.Cin >> 3;                   // lanes per position: 1, 2, 4, 8, 16 or 32 (host guarantees a power of two)
+    const int cg = threadIdx.x & (tpp - 1);
+    const int c0 = cg << 3;
+    const unsigned ppb = blockDim.x / tpp;
+    const unsigned slot = threadIdx.x / tpp;
+    const unsigned hw = (unsigned)(a.W * a.H);
+    const unsigned long long items = (unsigned long long)a.N * hw;
+    // all lanes of a warp run the same number of iterations (positions are padded per warp), so the shuffles are safe
+    const unsigned long long iters = (items + (unsigned long long)gridDim.x * ppb - 1) / ((unsigned long long)gridDim.x * ppb);
+    for (unsigned long long k = 0; k < iters; ++k) {
+        const unsigned long long it = (k * gridDim.x + blockIdx.x) * ppb + slot;
+        const bool live = it < items;
+        const unsigned long long itc = live ? it : 0;
+        const int n = (int)(itc / hw);
+        const unsigned r = (unsigned)(itc - (unsigned long long)n * hw);
+        const int h = (int)(r / (unsigned)a.W);
+        const int w = (int)(r - (unsigned)h * (unsigned)a.W);
+        float xv[9][8];
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy) {
-            const int ih = h + dy;
-            if (ih < 0 || ih >= a.H) continue;
+        for (int dy = -1; dy <= 1; ++dy)
 #pragma unroll
             for (int dx = -1; dx <= 1; ++dx) {
-                const int iw = w + dx;
-                if (iw < 0 || iw >= a.W) continue;
-                const T* xp = X + (((size_t)n * a.H + ih) * a.W + iw) * a.Cin;
-                for (int c = 0; c < a.Cin; c += 8) {
-                    float xv[8];
-                    load8<T>(xp + c, xv);
-                    // phase py receives this row through kernel row ky = py + 1 - 2*dy (valid iff 0 <= ky < 4)
+                const int ih = h + dy, iw = w + dx;
+                const int ihc = min(max(ih, 0), a.H - 1), iwc = min(max(iw, 0), a.W - 1);
+                load8<T>(X + (((size_t)n * a.H + ihc) * a.W + iwc) * a.Cin + c0, xv[(dy + 1) * 3 + dx + 1]);
+                if (ih != ihc || iw != iwc) {
 #pragma unroll
-                    for (int py = 0; py < 2; ++py) {
-                        const int ky = py + 1 - 2 * dy;
-                        if (ky < 0 || ky > 3) continue;
+                    for (int j = 0; j < 8; ++j) xv[(dy + 1) * 3 + dx + 1][j] = 0.f;
+                }
+            }
+        float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
 #pragma unroll
-                        for (int px = 0; px < 2; ++px) {
-                            const int kx = px + 1 - 2 * dx;
-                            if (kx < 0 || kx > 3) continue;
-                            const float* wr = sw + (ky * 4 + kx) * a.Cin + c;
-                            const float4 w0 = *reinterpret_cast<const float4*>(wr), w1 = *reinterpret_cast<const float4*>(wr + 4);
-                            float s = acc[py][px];
-                            s = fmaf(xv[0], w0.x, s); s = fmaf(xv[1], w0.y, s); s = fmaf(xv[2], w0.z, s); s = fmaf(xv[3], w0.w, s);
-                            s = fmaf(xv[4], w1.x, s); s = fmaf(xv[5], w1.y, s); s = fmaf(xv[6], w1.z, s); s = fmaf(xv[7], w1.w, s);
-                            acc[py][px] = s;
-                        }
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+                const float* xr = xv[(dy + 1) * 3 + dx + 1];
+                // phase py receives this row through kernel row ky = py + 1 - 2*dy (valid iff 0 <= ky < 4)
+#pragma unroll
+                for (int py = 0; py < 2; ++py) {
+                    const int ky = py + 1 - 2 * dy;
+                    if (ky < 0 || ky > 3) continue;
+#pragma unroll
+                    for (int px = 0; px < 2; ++px) {
+                        const int kx = px + 1 - 2 * dx;
+                        if (kx < 0 || kx > 3) continue;
+                        const float* wr = sw + (ky * 4 + kx) * a.Cin + c0;
+                        const float4 w0 = *reinterpret_cast<const float4*>(wr), w1 = *reinterpret_cast<const float4*>(wr + 4);
+                        float s = acc[py][px];
+                        s = fmaf(xr[0], w0.x, s); s = fmaf(xr[1], w0.y, s); s = fmaf(xr[2], w0.z, s); s = fmaf(xr[3], w0.w, s);
+                        s = fmaf(xr[4], w1.x, s); s = fmaf(xr[5], w1.y, s); s = fmaf(xr[6], w1.z, s); s = fmaf(xr[7], w1.w, s);
+                        acc[py][px] = s;
                     }
                 }
             }
+        // sum over the tpp lanes of this position (tpp is a power of two <= 32 and positions are tpp-aligned in the warp)
+        for (int o = tpp >> 1; o > 0; o >>= 1) {
+#pragma unroll
+            for (int py = 0; py < 2; ++py)
+#pragma unroll
+                for (int px = 0; px < 2; ++px) acc[py][px] += __shfl_xor_sync(0xffffffffu, acc[py][px], o);
         }
+        if (live && cg == 0) {
 #pragma unroll
-        for (int py = 0; py < 2; ++py) {
-            float o[2];
+            for (int py = 0; py < 2; ++py) {
+                float o[2];
 #pragma unroll
-            for (int px = 0; px < 2; ++px) {
-                float x = apply_act(acc[py][px], a.act);
-                if (a.affine) x = x * a.out_scale + a.out_shift;
-                o[px] = x;
+                for (int px = 0; px < 2; ++px) {
+                    float x = apply_act(acc[py][px] + b0, a.act);
+                    if (a.affine) x = x * a.out_scale + a.out_shift;
+                    o[px] = x;
+                }
+                const size_t off = ((size_t)n * a.Ho + (2 * h + py)) * a.Wo + 2 * w;
+                if (sizeof(TO) == 4) *reinterpret_cast<float2*>(Y + off) = make_float2(o[0], o[1]);
+                else *reinterpret_cast<__nv_bfloat162*>(Y + off) = __floats2bfloat162_rn(o[0], o[1]);
             }
-            const size_t off = ((size_t)n * a.Ho + (2 * h + py)) * a.Wo + 2 * w;
-            if (sizeof(TO) == 4) *reinterpret_cast<float2*>(Y + off) = make_float2(o[0], o[1]);
-            else *reinterpret_cast<__nv_bfloat162*>(Y + off) = __floats2bfloat162_rn(o[0], o[1]);
         }
     }
 }
@@ -342,7 +370,8 @@ bool conv_edge_supported(const ConvP& p) {
     if (p.add || p.add_nc || p.has_ddim || !p.y) return false;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15)) return false;
     if (p.nphases == 1 && p.Cin == 1 && p.ph[0].ntaps == 9 && p.dtype == MSTK_F32 && (p.Cout % 8) == 0 && p.Cout <= 1024) return true;
-    if (p.nphases == 4 && p.ph[3].ntaps == 4 && p.ph[0].ntaps == 4 && p.Cout == 1 && (p.Cin % 8) == 0 && p.Cin <= 512 && !p.stats) return true;
+    if (p.nphases == 4 && p.ph[3].ntaps == 4 && p.ph[0].ntaps == 4 && p.Cout == 1 && (p.Cin % 8) == 0 && p.Cin <= 256 &&
+        ((p.Cin / 8) & (p.Cin / 8 - 1)) == 0 && !p.stats) return true;      // Cin/8 lanes per position: a power of two <= 32
     return false;
 }
 
@@ -383,15 +412,16 @@ int launch_conv_edge(const ConvP& p, cudaStream_t st) {
         MSTK_CHECK_LAUNCH("conv_cin1 launch");
     } else {
         const size_t items = (size_t)p.N * p.H * p.W;
-        size_t blocks = (items + 127) / 128;
-        const size_t cap = (size_t)sms * 16;
+        const size_t ppb = 192 / (p.Cin / 8);
+        size_t blocks = (items + ppb - 1) / ppb;
+        const size_t cap = (size_t)sms * 6;
         if (blocks > cap) blocks = cap;
         const size_t smem = (size_t)16 * p.Cin * sizeof(float);
         const bool xf = p.dtype == MSTK_F32, of = p.out_dtype == MSTK_F32;
-        if (xf && of) convt4_cout1_kernel<float, float><<<(unsigned)blocks, 128, smem, st>>>(a);
-        else if (xf) convt4_cout1_kernel<float, __nv_bfloat16><<<(unsigned)blocks, 128, smem, st>>>(a);
-        else if (of) convt4_cout1_kernel<__nv_bfloat16, float><<<(unsigned)blocks, 128, smem, st>>>(a);
-        else convt4_cout1_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)blocks, 128, smem, st>>>(a);
+        if (xf && of) convt4_cout1_kernel<float, float><<<(unsigned)blocks, 192, smem, st>>>(a);
+        else if (xf) convt4_cout1_kernel<float, __nv_bfloat16><<<(unsigned)blocks, 192, smem, st>>>(a);
+        else if (of) convt4_cout1_kernel<__nv_bfloat16, float><<<(unsigned)blocks, 192, smem, st>>>(a);
+        else convt4_cout1_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)blocks, 192, smem, st>>>(a);
         MSTK_CHECK_LAUNCH("convt4_cout1 launch");
     }
     return MSTK_OK;

@@ -124,9 +124,9 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
     const size_t total = (size_t)a.rows * a.c;
     if ((a.c & 7) == 0) {
         const size_t nvec = total >> 3;
-        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
-            const size_t e = i << 3;
-            const int ch = (int)(e % a.c);
+        ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
+            const int ch = cw.ch;
             float v[8];
             if (a.dtype == MSTK_F32) {
                 const float4 q0 = reinterpret_cast<const float4*>(a.x)[2 * i];

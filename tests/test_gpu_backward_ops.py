@@ -71,7 +71,7 @@ def test_act_bwd(c, act):
     got2 = ops.act_bwd(dy.bfloat16().to(DEV), y.detach().to(DEV), act=act, g_dtype=torch.float32,
                        y_scale=0.5 if act == 2 else 1.0, y_shift=0.5 if act == 2 else 0.0)
     assert rel_l2(got2, v.grad * 0 + torch.autograd.grad(
-        (F.relu(v) if act == 1 else (torch.tanh(v) * 0.5 + 0.5 if act == 2 else v * 1.0)), v, dy.bfloat16().float())[0]) < 1e-5
+        (F.relu(v) if act == 1 else (torch.tanh(v) * 0.5 + 0.5 if act == 2 else v * 1.0)), v, dy.bfloat16().float())[0]) < 3e-5   # fp32: 1 - t*t cancels near |t| = 1
 
 
 @pytest.mark.parametrize("c,relu", [(64, True), (32, False)])
