@@ -11,7 +11,8 @@
 //   K loop  = (tap, channel block) pairs, optionally split across gridDim.z (split-K) so
 //             that the small-M layers of the UNet still spread over all 148 SMs.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer
+// Warp roles (224 threads): warp 0 = A (activation) TMA producer, warp 6 = B (weight) TMA producer -- one issuing LANE per
+// pipeline stage, because loads issued by a single thread do not overlap (tools/tma_probe.cu) --, warp 1 = TMEM allocator + MMA issuer
 // (single thread issues tcgen05.mma, accumulator in TMEM), warps 2..5 = epilogue.
 //
 // Epilogue (v2, after the round-1a profile showed it was 60-80 % of the kernel):
@@ -66,7 +67,7 @@ static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
 static int g_pdl = 1;
-static int g_krot = 0;   // K-loop rotation (MSTK_KROT=1): measured no effect on B200 (round 1c), kept as a tuning knob
+static int g_force_group = 0, g_trace = 0;
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
 void tc_set_debug(long long* p) { g_dbg = p; }
@@ -95,9 +96,9 @@ bool tc_init() {
         g_num_sms = sms;
     // development knobs (tuning sweeps): MSTK_PDL=0 disables programmatic dependent launch,
     // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
+    if (const char* s = getenv("MSTK_TC_TRACE")) g_trace = atoi(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
-    if (const char* s = getenv("MSTK_KROT")) g_krot = atoi(s) != 0;
-    if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages);
+    if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
     for (int i = 0; i < kNumVariants; ++i) {
         cudaError_t ea = cudaFuncSetAttribute(kVariants[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (ea != cudaSuccess) {
@@ -130,7 +131,7 @@ bool conv_tc_supported(const ConvP& p) {
 }
 
 struct TcConfig {
-    int Wt, Ht, Nt, tiles_w, tiles_h, tiles_n, KC, BN, kb_per_tap, splitk, stages, tmem_cols;
+    int Wt, Ht, Nt, tiles_w, tiles_h, tiles_n, KC, BN, kb_per_tap, splitk, stages, kgroup, tmem_cols;
     int out_esz, out_rowbytes, out_chunks, add_rowbytes, add_chunks;
     uint32_t off_part, off_out, off_add, off_bias;
     size_t smem_bytes;
@@ -140,7 +141,7 @@ struct TcConfig {
 static void layout_smem(const ConvP& p, TcConfig& c) {
     const size_t a_bytes = (size_t)TILE_M * c.KC * 2;
     const size_t b_bytes = (((size_t)c.BN * c.KC * 2) + 1023) & ~(size_t)1023;
-    const size_t pipe = (a_bytes + b_bytes) * c.stages;
+    const size_t pipe = (a_bytes + b_bytes) * c.stages * c.kgroup;
     c.out_esz = p.out_dtype == MSTK_F32 ? 4 : 2;
     c.out_rowbytes = c.BN * c.out_esz >= 128 ? 128 : c.BN * c.out_esz;
     c.out_chunks = c.BN * c.out_esz / c.out_rowbytes;
@@ -178,7 +179,7 @@ static TcConfig choose_config(const ConvP& p) {
     }
     // cost model (cycles) over (BN, splitk): L2-fed K loop vs MMA floor, wave quantisation, epilogue
     double best = 1e30;
-    int best_bn = 16, best_sk = 1, best_st = 2;
+    int best_bn = 16, best_sk = 1, best_st = 2, best_grp = 1;
     for (int bn = 128; bn >= 16; bn >>= 1) {
         if (p.Cout % bn != 0) continue;
         if (g_force_bn && bn != g_force_bn && p.Cout % g_force_bn == 0) continue;
@@ -186,37 +187,50 @@ static TcConfig choose_config(const ConvP& p) {
             if (sk > min_kb) break;
             if (g_force_sk && sk != g_force_sk && g_force_sk <= min_kb) continue;
             if (sk > 1 && bn > 64) continue;          // keep the fp32 partial tile <= 32 KB
-            TcConfig t = c;
-            t.BN = bn; t.splitk = sk;
             const int kb_cta = (max_kb + sk - 1) / sk;
-            int st = kb_cta < MAX_STAGES ? kb_cta : MAX_STAGES;
-            if (st < 2) st = 2;
-            t.stages = st;
-            layout_smem(p, t);
-            while (t.stages > 3 && t.smem_bytes > 100 * 1024) { --t.stages; layout_smem(p, t); }
-            if (t.smem_bytes > 220 * 1024) continue;
-            int occ = (int)((228 * 1024) / (t.smem_bytes + 1024));
-            if (occ > 4) occ = 4;
-            if (occ < 1) occ = 1;
-            const long long ctas = mtiles * (p.Cout / bn) * sk;
-            const long long slots = (long long)g_num_sms * occ;
-            const long long waves = (ctas + slots - 1) / slots;
-            const double conc = (double)(ctas < slots ? ctas : slots);
-            const double per_sm = conc / g_num_sms < 1.0 ? 1.0 : conc / g_num_sms;
-            double bw = 90.0 / per_sm;                               // bytes/cycle one CTA can pull through its SM
-            if (bw > 6000.0 / conc) bw = 6000.0 / conc;              // L2 cap shared by everyone streaming at once
-            const double stage_b = (double)TILE_M * c.KC * 2 + (double)bn * c.KC * 2;
-            const double t_load = kb_cta * stage_b / bw;
-            const double t_mma = (double)kb_cta * (c.KC / 16) * (bn / 2.0) * per_sm;
-            const double t_k = (t_load > t_mma ? t_load : t_mma) + 900.0;
-            const double t_epi = 500.0 + bn * 14.0 + (sk > 1 ? 1800.0 + bn * 10.0 : 0.0);
-            const double cost = waves * (t_k + t_epi) + 1200.0;
-            if (cost < best) { best = cost; best_bn = bn; best_sk = sk; best_st = t.stages; }
+            // k-blocks per stage: one issuer round (wait, MMAs, commit) costs ~600 cycles whatever it carries, so
+            // short K loops want few, fat rounds; at most 16 MMAs per round and 30 producer lanes
+            for (int grp = 1; grp <= 4; ++grp) {
+                if (grp > 1 && (grp * (c.KC / 16) > 16 || grp > kb_cta)) break;
+                if (g_force_group && grp != g_force_group && g_force_group <= kb_cta) continue;
+                TcConfig t = c;
+                t.BN = bn; t.splitk = sk; t.kgroup = grp;
+                const int ngroups = (kb_cta + grp - 1) / grp;
+                int st = ngroups < MAX_STAGES ? ngroups : MAX_STAGES;
+                if (st < 2) st = 2;
+                while (st * grp > 30) --st;
+                t.stages = st;
+                layout_smem(p, t);
+                const int min_st = grp > 1 ? 2 : 3;
+                while (t.stages > min_st && t.smem_bytes > 100 * 1024) { --t.stages; layout_smem(p, t); }
+                if (t.smem_bytes > 220 * 1024) continue;
+                int occ = (int)((228 * 1024) / (t.smem_bytes + 1024));
+                if (occ > 4) occ = 4;
+                if (occ < 1) occ = 1;
+                const long long ctas = mtiles * (p.Cout / bn) * sk;
+                const long long slots = (long long)g_num_sms * occ;
+                const long long waves = (ctas + slots - 1) / slots;
+                const double conc = (double)(ctas < slots ? ctas : slots);
+                const double per_sm = conc / g_num_sms < 1.0 ? 1.0 : conc / g_num_sms;
+                double bw = 90.0 / per_sm;                               // bytes/cycle one CTA can pull through its SM
+                if (bw > 6000.0 / conc) bw = 6000.0 / conc;              // L2 cap shared by everyone streaming at once
+                const double stage_b = (double)TILE_M * c.KC * 2 + (double)bn * c.KC * 2;
+                const double t_load = kb_cta * stage_b / bw;
+                const double t_mma = (double)kb_cta * (c.KC / 16) * (bn / 2.0) * per_sm;
+                const double t_issue = ngroups * 600.0 + (double)kb_cta * (c.KC / 16) * 15.0;
+                double t_k = t_load > t_mma ? t_load : t_mma;
+                if (t_issue > t_k) t_k = t_issue;
+                t_k += 600.0 + (t.stages * grp < kb_cta ? 0.0 : 0.0);
+                const double t_epi = 500.0 + bn * 14.0 + (sk > 1 ? 1800.0 + bn * 10.0 : 0.0);
+                const double cost = waves * (t_k + t_epi) + 1200.0;
+                if (cost < best) { best = cost; best_bn = bn; best_sk = sk; best_st = t.stages; best_grp = grp; }
+            }
         }
     }
-    c.BN = best_bn; c.splitk = best_sk; c.stages = g_force_stages ? g_force_stages : best_st;
+    c.BN = best_bn; c.splitk = best_sk; c.kgroup = best_grp; c.stages = g_force_stages ? g_force_stages : best_st;
     if (c.stages > MAX_STAGES) c.stages = MAX_STAGES;
     if (c.stages < 2) c.stages = 2;
+    while (c.stages * c.kgroup > 30) --c.stages;
     layout_smem(p, c);
     int cols = 32;
     while (cols < c.BN) cols <<= 1;
@@ -305,12 +319,14 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     q.Wt = c.Wt; q.Ht = c.Ht; q.Nt = c.Nt;
     q.tiles_w = c.tiles_w; q.tiles_h = c.tiles_h; q.tiles_n = c.tiles_n;
     q.dbg = g_dbg;
-    q.krot = g_krot;
-    q.KC = c.KC; q.BN = c.BN; q.kb_per_tap = c.kb_per_tap; q.splitk = c.splitk; q.stages = c.stages; q.tmem_cols = c.tmem_cols;
+    q.KC = c.KC; q.BN = c.BN; q.kb_per_tap = c.kb_per_tap; q.splitk = c.splitk; q.stages = c.stages; q.kgroup = c.kgroup; q.tmem_cols = c.tmem_cols;
     q.out_esz = c.out_esz; q.out_rowbytes = c.out_rowbytes; q.out_chunks = c.out_chunks;
     q.add_rowbytes = c.add_rowbytes; q.add_chunks = c.add_chunks;
     q.use_tma_store = p.y ? 1 : 0;
     q.use_tma_add = p.add ? 1 : 0;
+    if (g_trace)
+        fprintf(stderr, "[mstk conv_tc] N%d %dx%d Cin%d Cout%d k%d: BN %d KC %d splitk %d stages %d kgroup %d smem %zu\n", p.N, p.H, p.W, p.Cin,
+                p.Cout, p.nphases, c.BN, c.KC, c.splitk, c.stages, c.kgroup, c.smem_bytes);
     q.off_stage0 = 0; q.off_part = c.off_part; q.off_out = c.off_out; q.off_add = c.off_add; q.off_bias = c.off_bias;
 
     const CUtensorMapSwizzle sw = (c.KC == 64) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;

@@ -7,7 +7,7 @@
 
 namespace mstk {
 
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 224;     // warps: 0 A producer, 1 MMA issuer, 2..5 epilogue, 6 B producer
 constexpr int MAX_STAGES = 8;
 
 struct TcMaps {
@@ -35,7 +35,7 @@ struct TcParams {
     int32_t use_tma_add;           // residual prefetched by TMA
     uint32_t off_stage0;           // shared-memory carve-up (bytes from the 1024-aligned base)
     uint32_t off_part, off_out, off_add, off_bias;
-    int32_t krot;                  // rotate the K loop per CTA (see the producer)
+    int32_t kgroup;                // k-blocks per pipeline stage (one barrier round trip and one commit per group)
     float* ws;                     // split-K workspace
     unsigned int* counters;        // split-K tile counters
     long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
@@ -96,7 +96,7 @@ struct TcShared {
 // One output tile (bx, by, bz) of a launch whose grid would be (gx, gy, *).  PROG = false: the body of the
 // stand-alone kernel (allocates and frees its TMEM columns, fresh mbarriers).  PROG = true: called in a loop by the
 // persistent program kernel (program.cu): TMEM is allocated once by the caller (sh.tmem_base), the mbarriers are
-// invalidated and re-initialised per tile, all 192 threads must call it.
+// invalidated and re-initialised per tile, all TC_THREADS threads must call it.
 template <uint32_t F, bool PROG>
 __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams& q, const int bx, const int by, const int bz,
                                              const int gx, const int gy, TcShared& sh, uint8_t* smem_raw) {
@@ -138,7 +138,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     const uint32_t a_bytes = TILE_M * q.KC * 2;
     const uint32_t b_bytes = q.BN * q.KC * 2;
     const uint32_t b_bytes_al = (b_bytes + 1023u) & ~1023u;
-    const uint32_t stage_bytes = a_bytes + b_bytes_al;
+    const uint32_t sub_bytes = a_bytes + b_bytes_al;        // one k-block: A tile + B tile
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t smem_base = smem_u32(smem);
     float* sbias = reinterpret_cast<float*>(smem + q.off_bias);
@@ -154,7 +154,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
             mbar_inval(&accum_bar); mbar_inval(&add_bar); mbar_inval(&part_bar);
         }
         for (int s = 0; s < (PROG ? MAX_STAGES : q.stages); ++s) {
-            mbar_init(&full_bar[s], 1);
+            mbar_init(&full_bar[s], 2);          // one arrive.expect_tx from each of the two producers
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&accum_bar, 1);
@@ -175,38 +175,31 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     const uint32_t tmem_base = tmem_base_smem;
     if (threadIdx.x == 0) DBG_STAMP(1);
 
+    // K loop.  Two measurements on B200 shape it (tools/tma_probe.cu and the clock64 stamps, tools/tc_timeline.py):
+    //  * TMA loads issued from one instruction stream (a single thread, or a warp running the loop in lock-step)
+    //    complete a full latency (~600 cycles) apart however many stages are open; loads issued by divergent lanes
+    //    that each run their own loop overlap.  So every sub-slot of the pipeline belongs to one producer lane.
+    //  * One round of the MMA issuer (barrier wait, tcgen05.mma x n, commit) costs ~600 cycles + ~15 per MMA even
+    //    with every operand already in shared memory, so the round must carry many MMAs: a pipeline stage holds
+    //    `kgroup` consecutive k-blocks (each its own A box + B box) behind ONE full/empty barrier pair.
+    // Sub-slot j = stage * kgroup + g lives at off_stage0 + j * sub_bytes (A tile, then the B tile).
+    const int G = q.kgroup;
+    const int ngroups = (nkb + G - 1) / G;
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            const int npre = nkb < q.stages ? nkb : q.stages;
-            // optional K-loop rotation (tuning knob, off by default): CTAs that share a weight tile start at different
-            // k-blocks so that they pull different B tiles at any instant.  Measured on B200: no effect (the ~0.9 k
-            // cycles per k-block of the small UNet layers is not an L2 hot-spot).
-            const int rot = q.krot ? (int)(((unsigned)bx * 5u + (unsigned)bz) % (unsigned)nkb) : 0;
-            // weights do not depend on the previous kernel: fetch them before the grid dependency resolves
-            for (int it = 0; it < npre; ++it) {
-                const int kb = kb_begin + (it + rot < nkb ? it + rot : it + rot - nkb);
-                const int tap_i = kb / q.kb_per_tap;
-                const int cb = kb - tap_i * q.kb_per_tap;
-                mbar_expect_tx(&full_bar[it], a_bytes + b_bytes);
-                tma_load_2d(&maps.b, &full_bar[it], smem_base + q.off_stage0 + (uint32_t)it * stage_bytes + a_bytes, cb * q.KC,
-                            ph.taps[tap_i].slice * p.Cout + co0);
-            }
-            pdl_wait();
-            pdl_launch_dependents();
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % q.stages;
-                const uint32_t par = (uint32_t)((it / q.stages) & 1);
-                const int kb = kb_begin + (it + rot < nkb ? it + rot : it + rot - nkb);
+        // ===================== A producer (activations: after the grid dependency) =====================
+        pdl_wait();
+        if (lane == 0) pdl_launch_dependents();
+        if (lane < q.stages * G) {
+            const int s = lane / G, g = lane - s * G;
+            const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)lane * sub_bytes;
+            int use = 0;
+            for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
+                const int cnt = nkb - grp * G < G ? nkb - grp * G : G;     // k-blocks in this group (the last may be short)
+                if (g >= cnt) break;
+                const int kb = kb_begin + grp * G + g;
                 const int tap_i = kb / q.kb_per_tap;
                 const int cb = kb - tap_i * q.kb_per_tap;
                 const Tap t = ph.taps[tap_i];
-                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
-                if (it >= npre) {
-                    mbar_wait(&empty_bar[s], par ^ 1u);
-                    mbar_expect_tx(&full_bar[s], a_bytes + b_bytes);
-                    tma_load_2d(&maps.b, &full_bar[s], sa + a_bytes, cb * q.KC, t.slice * p.Cout + co0);
-                }
                 int dy = t.dy, dx = t.dx;
                 const CUtensorMap* mA = &maps.a[0];
                 if (p.s_in == 2) {
@@ -215,41 +208,99 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     dx = (dx - px) / 2;
                     mA = &maps.a[py * 2 + px];
                 }
+                if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
+                // lane g == 0 posts the group's byte count; its siblings' complete_tx may land first (the transaction
+                // count goes transiently negative, the phase cannot complete before both producers have arrived)
+                if (g == 0) mbar_expect_tx(&full_bar[s], a_bytes * (uint32_t)cnt);
                 tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
-                if (it == 0) DBG_STAMP(2);
-                if (it == 0 && f_add) {
-                    // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
-                    mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
-                    const int cpr = q.add_rowbytes >> 1;
-                    for (int ch = 0; ch < q.add_chunks; ++ch)
-                        tma_load_4d(&maps.add[phase_idx], &add_bar, smem_base + q.off_add + (uint32_t)(ch * TILE_M * q.add_rowbytes),
-                                    co0 + ch * cpr, w0, h0, n0);
-                }
+                if (grp == 0 && g == 0) DBG_STAMP(2);
+            }
+        } else if (lane == 31 && f_add) {
+            // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
+            mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
+            const int cpr = q.add_rowbytes >> 1;
+            for (int ch = 0; ch < q.add_chunks; ++ch)
+                tma_load_4d(&maps.add[phase_idx], &add_bar, smem_base + q.off_add + (uint32_t)(ch * TILE_M * q.add_rowbytes),
+                            co0 + ch * cpr, w0, h0, n0);
+        }
+    } else if (warp == 6) {
+        // ===================== B producer (weights: never depend on the previous kernel, no grid-dependency wait) =====
+        if (lane < q.stages * G) {
+            const int s = lane / G, g = lane - s * G;
+            const uint32_t sb = smem_base + q.off_stage0 + (uint32_t)lane * sub_bytes + a_bytes;
+            int use = 0;
+            for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
+                const int cnt = nkb - grp * G < G ? nkb - grp * G : G;
+                if (g >= cnt) break;
+                const int kb = kb_begin + grp * G + g;
+                const int tap_i = kb / q.kb_per_tap;
+                const int cb = kb - tap_i * q.kb_per_tap;
+                if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
+                if (g == 0) mbar_expect_tx(&full_bar[s], b_bytes * (uint32_t)cnt);
+                tma_load_2d(&maps.b, &full_bar[s], sb, cb * q.KC, ph.taps[tap_i].slice * p.Cout + co0);
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc(q.BN);
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % q.stages;
-                const uint32_t par = (uint32_t)((it / q.stages) & 1);
-                mbar_wait(&full_bar[s], par);
-                if (it == 0) DBG_STAMP(3);
-                if (it == nkb - 1) DBG_STAMP(4);
+        // The whole warp runs the loop converged (all lanes wait on the stage barrier) and one elected lane issues:
+        // under an ordinary `lane == 0` branch every tcgen05 instruction is wrapped in a serialisation loop.  Loop
+        // invariants are pinned in registers and the barriers addressed by their shared-space address, so the loop
+        // body is the wait, the MMAs and the commit and nothing else.
+        {
+            const uint32_t idesc = keep_reg(make_idesc(q.BN));
+            const int ksteps = keep_reg(q.KC / 16);
+            const int stages = keep_reg(q.stages);
+            const int ng = keep_reg(ngroups);
+            const int gsz = keep_reg(G);
+            const uint32_t tm = keep_reg(tmem_base);
+            const uint64_t adesc0 = make_smem_desc(smem_base + q.off_stage0, q.KC);
+            const uint64_t bdesc0 = make_smem_desc(smem_base + q.off_stage0 + a_bytes, q.KC);
+            // both descriptors advance together; only the 14-bit start-address field (>>4) changes and it cannot carry
+            const uint32_t alo0 = keep_reg((uint32_t)adesc0), blo0 = keep_reg((uint32_t)bdesc0);
+            const uint32_t ahi = keep_reg((uint32_t)(adesc0 >> 32)), bhi = keep_reg((uint32_t)(bdesc0 >> 32));
+            const uint32_t dsub = keep_reg(sub_bytes >> 4);
+            const uint32_t dstage = keep_reg((sub_bytes >> 4) * (uint32_t)G);
+            const uint32_t full0 = keep_reg(smem_u32(&full_bar[0])), empty0 = keep_reg(smem_u32(&empty_bar[0]));
+            const uint32_t accum_a = keep_reg(smem_u32(&accum_bar));
+            const bool dbg_on = q.dbg && (PROG ? blockIdx.x == 0 : (bx == 0 && by == 0 && bz == 0)) && lane == 0;
+            int s = 0, left = keep_reg(nkb);
+            uint32_t par = 0, soff = 0, acc = 0;
+            for (int grp = 0; grp < ng; ++grp) {
+                mbar_wait_addr(full0 + 8u * (uint32_t)s, par);
                 tc_fence_after();
-                const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)s * stage_bytes;
-                const uint32_t sb = sa + a_bytes;
-                const uint64_t adesc = make_smem_desc(sa, q.KC);
-                const uint64_t bdesc = make_smem_desc(sb, q.KC);
-                const int ksteps = q.KC / 16;
-                for (int k = 0; k < ksteps; ++k) {
-                    // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
-                    umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (it > 0 || k > 0) ? 1u : 0u);
+                if (dbg_on) {
+                    if (grp == 0) q.dbg[3] = clock64();
+                    if (grp == ng - 1) q.dbg[4] = clock64();
+                    if (grp < 8) q.dbg[16 + grp * 8] = clock64();
                 }
-                umma_commit(&empty_bar[s]);     // frees the smem slot when these MMAs retire
+                const int cnt = left < gsz ? left : gsz;
+                left -= cnt;
+                if (elect_one()) {
+                    uint32_t alo = alo0 + soff, blo = blo0 + soff;
+                    for (int g = 0; g < cnt; ++g) {
+                        // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
+                        if (ksteps == 4) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                umma_bf16(tm, ((uint64_t)ahi << 32) | (alo + 2u * k), ((uint64_t)bhi << 32) | (blo + 2u * k), idesc, acc);
+                                acc = 1u;
+                            }
+                        } else {
+                            for (int k = 0; k < ksteps; ++k) {
+                                umma_bf16(tm, ((uint64_t)ahi << 32) | (alo + 2u * k), ((uint64_t)bhi << 32) | (blo + 2u * k), idesc, acc);
+                                acc = 1u;
+                            }
+                        }
+                        alo += dsub; blo += dsub;
+                    }
+                    umma_commit_addr(empty0 + 8u * (uint32_t)s);     // frees the stage when these MMAs retire
+                    if (grp == ng - 1) umma_commit_addr(accum_a);     // accumulator complete
+                }
+                acc = 1u;
+                __syncwarp();
+                if (++s == stages) { s = 0; par ^= 1u; soff = 0; }
+                else soff += dstage;
             }
-            umma_commit(&accum_bar);            // accumulator complete
         }
     } else {
         // ===================== epilogue (warps 2..5) =====================
@@ -290,7 +341,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         }
         epi_bar();                               // sbias visible to all epilogue threads
 
-        mbar_wait(&accum_bar, 0);
+        mbar_wait_backoff(&accum_bar, 0, 64);
         if (et == 0) DBG_STAMP(5);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);

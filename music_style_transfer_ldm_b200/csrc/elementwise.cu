@@ -240,6 +240,10 @@ __global__ void time_embed_kernel(const float* __restrict__ t, int nb, const flo
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(ATTN_WARPS * 32) attention_kernel(const AttnP a) {
     extern __shared__ float sm[];
+    // programmatic dependent launch: wait for the producer of q (the projection conv), then let the next kernel (the
+    // output projection, which prefetches its weights before ITS wait) start its prologue under this one
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     attention_unit(a, (int)blockIdx.x, (int)blockIdx.y, sm, ATTN_WARPS);
 }
 
@@ -509,8 +513,19 @@ int mstk_attention_fwd(const mstk_attn_args* a, void* stream) {
         smem_set = 200 * 1024;
     }
     dim3 grid(a->b * a->heads, (a->l + ATTN_QPB - 1) / ATTN_QPB);
-    attention_kernel<<<grid, ATTN_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
-    MSTK_CHECK_LAUNCH("attention");
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(ATTN_WARPS * 32, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, attention_kernel, p);
+    if (le != cudaSuccess) return cuda_fail(le, "attention launch");
     return MSTK_OK;
 }
 

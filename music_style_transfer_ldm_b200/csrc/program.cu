@@ -63,7 +63,7 @@ program_kernel(const ProgOp* __restrict__ ops, const int nops, unsigned int* syn
     const int warp = threadIdx.x >> 5;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&sh.full_bar[s], 1); mbar_init(&sh.empty_bar[s], 1); }
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&sh.full_bar[s], 2); mbar_init(&sh.empty_bar[s], 1); }
         mbar_init(&sh.accum_bar, 1); mbar_init(&sh.add_bar, 1); mbar_init(&sh.part_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }

@@ -47,6 +47,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000ll) __trap();   // ~2 s at 2 GHz
     }
 }
+// Long wait (the epilogue warps waiting for the whole K loop): back off between polls so the polling does not sit in
+// the shared-memory/mbarrier pipe in front of the MMA issuer's and the producers' barrier operations.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    const uint32_t a = smem_u32(bar);
+    if (mbar_try_wait(a, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(a, parity)) {
+        __nanosleep(ns);
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
 __device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, uint32_t dst, int c0, int c1, int c2, int c3) {
     asm volatile(
         "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
@@ -85,6 +96,36 @@ __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+// Pin a loop invariant in a register.  Kernel parameters are otherwise re-read from the constant bank (LDC/LDCU) at
+// every use inside a loop whose body holds `asm volatile(... "memory")`, and those loads sit on the issuer's
+// dependent chain.
+__device__ __forceinline__ uint32_t keep_reg(uint32_t v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ int keep_reg(int v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ void mbar_wait_addr(uint32_t a, uint32_t parity) {
+    if (mbar_try_wait(a, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(a, parity)) {
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// One lane of a CONVERGED warp (elect.sync).  The compiler treats the guarded region as single-threaded and uniform,
+// so tcgen05.mma / tcgen05.commit inside it compile to bare UTCHMMA / UTCBAR; under an ordinary `lane == 0` branch
+// each of them is wrapped in an ELECT + BRA.U.ANY serialisation loop fed by R2UR moves (cuobjdump), which made the
+// issuer thread the bound of the K loop (~740 cycles per k-block with every stage already landed, B200).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // K-major operand tile in shared memory, rows of KC bf16 (64 -> 128 B rows / SWIZZLE_128B,

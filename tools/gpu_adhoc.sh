@@ -1,8 +1,13 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -q -m gpu --timeout 600 -x > gpurun_out/t_gpu.log 2>&1; echo "tests rc=$?"; tail -n 3 gpurun_out/t_gpu.log
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-train > gpurun_out/b_short.log 2>gpurun_out/b_short.err; echo "bench rc=$?"; tail -n 5 gpurun_out/b_short.err
-python - <<'PY'
+MSTK_TC_TRACE=1 timeout 300 python tools/tc_timeline.py > gpurun_out/tc_timeline2.txt 2>&1; grep -B1 -A1 "^conv" gpurun_out/tc_timeline2.txt | grep -v "^--" | awk '!seen[$0]++' | cut -c 1-200
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for f in "" "0,0,0,1"; do
+MSTK_TC_FORCE=$f timeout 600 python bench.py > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
 import json
-d=json.loads(open('gpurun_out/b_short.log').read().strip().splitlines()[-1])
-print("steps/s", d['value'], "e2e", d['e2e']['value'], "us/step", d['unet_step_us'])
+d=json.loads(open('gpurun_out/bench_adhoc.json').read().strip().splitlines()[-1])
+print('sampling', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'])
+t=d.get('train',{})
+print('train', t.get('value'), t.get('ms_per_step'))
+for r in t.get('rooflines',[])[:12]: print('  ', r)
 PY
+done

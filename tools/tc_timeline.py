@@ -8,7 +8,7 @@ import torch
 from music_style_transfer_ldm_b200 import ops, _lib
 lib = _lib.load()
 lib.mstk_debug_tc_timeline.argtypes = [ctypes.c_void_p]
-dbg = torch.zeros(8, dtype=torch.int64, device="cuda")
+dbg = torch.zeros(96, dtype=torch.int64, device="cuda")
 lib.mstk_debug_tc_timeline(dbg.data_ptr())
 CASES = [(64, 16, 16, 32, 64, 3, 1, False), (64, 16, 16, 64, 128, 3, 2, False), (64, 8, 8, 128, 256, 3, 2, False),
          (64, 4, 4, 256, 256, 1, 1, False), (64, 4, 4, 256, 512, 3, 2, False), (64, 2, 2, 512, 512, 3, 1, False),
@@ -25,4 +25,8 @@ for (n, h, w, cin, cout, k, s, tr) in CASES:
     torch.cuda.synchronize()
     t = dbg.cpu().tolist()
     rel = [v - t[0] for v in t]
-    print(f"{'convT' if tr else 'conv'} k{k}s{s} {cin}->{cout} @{h}x{w}: event {1e3*e0.elapsed_time(e1):7.1f} us | cycles since entry: {rel[1:]}")
+    print(f"{'convT' if tr else 'conv'} k{k}s{s} {cin}->{cout} @{h}x{w}: event {1e3*e0.elapsed_time(e1):7.1f} us | cycles since entry: {rel[1:8]}")
+    tops = [rel[16 + it * 8] for it in range(8) if t[16 + it * 8]]
+    print(f"    epilogue: accumulator ready {rel[5]}, first tmem_ld {rel[13]}, first chunk math {rel[14]}, first chunk staged {rel[15]}, all staged {rel[11]}, store issued {rel[12]}, done {rel[6]}")
+    print("    k-block start (after its wait), deltas:", [b - a for a, b in zip(tops, tops[1:])])
+    dbg.zero_()
