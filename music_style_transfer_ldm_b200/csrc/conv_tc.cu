@@ -202,12 +202,14 @@ static TcConfig choose_config(const ConvP& p) {
                 t.stages = st;
                 layout_smem(p, t);
                 const int min_st = grp > 1 ? 2 : 3;
-                while (t.stages > min_st && t.smem_bytes > 100 * 1024) { --t.stages; layout_smem(p, t); }
+                const long long ctas = mtiles * (p.Cout / bn) * sk;
+                // a grid of at most one CTA per SM may as well hold its whole K loop in flight
+                const size_t budget = ctas <= g_num_sms ? 200 * 1024 : 100 * 1024;
+                while (t.stages > min_st && t.smem_bytes > budget) { --t.stages; layout_smem(p, t); }
                 if (t.smem_bytes > 220 * 1024) continue;
                 int occ = (int)((228 * 1024) / (t.smem_bytes + 1024));
                 if (occ > 4) occ = 4;
                 if (occ < 1) occ = 1;
-                const long long ctas = mtiles * (p.Cout / bn) * sk;
                 const long long slots = (long long)g_num_sms * occ;
                 const long long waves = (ctas + slots - 1) / slots;
                 const double conc = (double)(ctas < slots ? ctas : slots);

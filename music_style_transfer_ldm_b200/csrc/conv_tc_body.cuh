@@ -139,7 +139,9 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     const uint32_t b_bytes = q.BN * q.KC * 2;
     const uint32_t b_bytes_al = (b_bytes + 1023u) & ~1023u;
     const uint32_t sub_bytes = a_bytes + b_bytes_al;        // one k-block: A tile + B tile
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // pointer arithmetic (not an integer round trip) so that the compiler keeps the shared address space: LDS/STS/ATOMS
+    // instead of generic LD/ST/ATOM in the epilogue
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
     float* sbias = reinterpret_cast<float*>(smem + q.off_bias);
 
@@ -183,18 +185,47 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     //    with every operand already in shared memory, so the round must carry many MMAs: a pipeline stage holds
     //    `kgroup` consecutive k-blocks (each its own A box + B box) behind ONE full/empty barrier pair.
     // Sub-slot j = stage * kgroup + g lives at off_stage0 + j * sub_bytes (A tile, then the B tile).
+    //  * Issuing one TMA load occupies its warp for ~200 cycles and the loads of one warp's lanes are issued one after
+    //    the other, so the producer jobs are spread over all six non-MMA warps: weights (B, no grid dependency) on
+    //    warps 6, 2, 3 and activations (A, after the grid dependency) on warps 0, 4, 5; the epilogue warps go on to
+    //    their own work when their producer lanes have issued their last load.
     const int G = q.kgroup;
     const int ngroups = (nkb + G - 1) / G;
-    if (warp == 0) {
-        // ===================== A producer (activations: after the grid dependency) =====================
-        pdl_wait();
-        if (lane == 0) pdl_launch_dependents();
-        if (lane < q.stages * G) {
-            const int s = lane / G, g = lane - s * G;
-            const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)lane * sub_bytes;
+    const int nsub = q.stages * G;
+    const int b_idx = warp == 6 ? 0 : warp == 2 ? 1 : warp == 3 ? 2 : -1;
+    const int a_idx = warp == 0 ? 0 : warp == 4 ? 1 : warp == 5 ? 2 : -1;
+    if (b_idx >= 0) {
+        // ===================== B producers (weights) =====================
+        const int j = lane * 3 + b_idx;
+        if (j < nsub) {
+            const int s = j / G, g = j - s * G;
+            const uint32_t sb = smem_base + q.off_stage0 + (uint32_t)j * sub_bytes + a_bytes;
             int use = 0;
             for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
                 const int cnt = nkb - grp * G < G ? nkb - grp * G : G;     // k-blocks in this group (the last may be short)
+                if (g >= cnt) break;
+                const int kb = kb_begin + grp * G + g;
+                const int tap_i = kb / q.kb_per_tap;
+                const int cb = kb - tap_i * q.kb_per_tap;
+                if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
+                // lane g == 0 posts the group's byte count; its siblings' complete_tx may land first (the transaction
+                // count goes transiently negative, the phase cannot complete before both operands' counts are posted)
+                if (g == 0) mbar_expect_tx(&full_bar[s], b_bytes * (uint32_t)cnt);
+                tma_load_2d(&maps.b, &full_bar[s], sb, cb * q.KC, ph.taps[tap_i].slice * p.Cout + co0);
+            }
+        }
+    }
+    if (a_idx >= 0) {
+        // ===================== A producers (activations) =====================
+        pdl_wait();
+        if (warp == 0 && lane == 0) pdl_launch_dependents();
+        const int j = lane * 3 + a_idx;
+        if (j < nsub) {
+            const int s = j / G, g = j - s * G;
+            const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)j * sub_bytes;
+            int use = 0;
+            for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
+                const int cnt = nkb - grp * G < G ? nkb - grp * G : G;
                 if (g >= cnt) break;
                 const int kb = kb_begin + grp * G + g;
                 const int tap_i = kb / q.kb_per_tap;
@@ -209,13 +240,11 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     mA = &maps.a[py * 2 + px];
                 }
                 if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
-                // lane g == 0 posts the group's byte count; its siblings' complete_tx may land first (the transaction
-                // count goes transiently negative, the phase cannot complete before both producers have arrived)
                 if (g == 0) mbar_expect_tx(&full_bar[s], a_bytes * (uint32_t)cnt);
                 tma_load_4d(mA, &full_bar[s], sa, cb * q.KC, w0 + dx, h0 + dy, n0);
-                if (grp == 0 && g == 0) DBG_STAMP(2);
+                if (j == 0 && use == 0) DBG_STAMP(2);
             }
-        } else if (lane == 31 && f_add) {
+        } else if (warp == 0 && lane == 31 && f_add) {
             // residual tile for the epilogue (with split-K any CTA can be the one that finalises)
             mbar_expect_tx(&add_bar, (uint32_t)(TILE_M * q.BN * 2));
             const int cpr = q.add_rowbytes >> 1;
@@ -223,24 +252,8 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                 tma_load_4d(&maps.add[phase_idx], &add_bar, smem_base + q.off_add + (uint32_t)(ch * TILE_M * q.add_rowbytes),
                             co0 + ch * cpr, w0, h0, n0);
         }
-    } else if (warp == 6) {
-        // ===================== B producer (weights: never depend on the previous kernel, no grid-dependency wait) =====
-        if (lane < q.stages * G) {
-            const int s = lane / G, g = lane - s * G;
-            const uint32_t sb = smem_base + q.off_stage0 + (uint32_t)lane * sub_bytes + a_bytes;
-            int use = 0;
-            for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
-                const int cnt = nkb - grp * G < G ? nkb - grp * G : G;
-                if (g >= cnt) break;
-                const int kb = kb_begin + grp * G + g;
-                const int tap_i = kb / q.kb_per_tap;
-                const int cb = kb - tap_i * q.kb_per_tap;
-                if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
-                if (g == 0) mbar_expect_tx(&full_bar[s], b_bytes * (uint32_t)cnt);
-                tma_load_2d(&maps.b, &full_bar[s], sb, cb * q.KC, ph.taps[tap_i].slice * p.Cout + co0);
-            }
-        }
-    } else if (warp == 1) {
+    }
+    if (warp == 1) {
         // ===================== MMA issuer =====================
         // The whole warp runs the loop converged (all lanes wait on the stage barrier) and one elected lane issues:
         // under an ordinary `lane == 0` branch every tcgen05 instruction is wrapped in a serialisation loop.  Loop
@@ -302,7 +315,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                 else soff += dstage;
             }
         }
-    } else {
+    } else if (warp >= 2 && warp <= 5) {
         // ===================== epilogue (warps 2..5) =====================
         const int qd = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = qd * 32 + lane;          // GEMM row inside the tile
@@ -397,6 +410,14 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
             if (f_add) mbar_wait(&add_bar, 0);
             const int out_cpr = q.out_rowbytes / q.out_esz;
             const int add_cpr = q.add_rowbytes >> 1;
+            // columns per staging chunk are powers of two (row bytes 32/64/128): shifts, not divisions, in the loop
+            const int out_sh = 31 - __clz(out_cpr), add_sh = 31 - __clz(add_cpr);
+            const int out_esz = q.out_esz, out_rowbytes = q.out_rowbytes, add_rowbytes = q.add_rowbytes;
+            uint8_t* const out_stage = smem + q.off_out;
+            const uint8_t* const add_stage = smem + q.off_add;
+            const int act = p.act;
+            float vnext[16];
+            if (!f_split) tmem_ld16_issue(taddr, vnext);
             for (int c = 0; c < BN; c += 16) {
                 float v[16];
                 if (f_split) {
@@ -406,7 +427,11 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                         v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
                     }
                 } else {
-                    tmem_ld16(taddr + (uint32_t)c, v);
+                    // the next chunk's TMEM load is in flight while this one is processed
+                    tmem_ld_wait(vnext);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = vnext[j];
+                    if (c + 16 < BN) tmem_ld16_issue(taddr + (uint32_t)(c + 16), vnext);
                 }
                 if (c == 0 && et == 0) DBG_STAMP(13);
                 // prefetch the next chunk's per-row operands
@@ -446,9 +471,9 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                 for (int j = 0; j < 16; ++j) {
                     float x = v[j];
                     if (f_actgen) {
-                        x = apply_act(x, p.act);
+                        x = apply_act(x, act);
                         if (p.affine) x = x * p.out_scale + p.out_shift;
-                    } else if (p.act == MSTK_ACT_RELU) {
+                    } else if (act == MSTK_ACT_RELU) {
                         x = fmaxf(x, 0.f);
                     }
                     v[j] = x;
@@ -459,11 +484,11 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     for (int j = 0; j < 16; ++j) v[j] += anc[j];
                 }
                 if (f_add) {
-                    const uint8_t* ab = smem + q.off_add + (size_t)(c / add_cpr) * TILE_M * q.add_rowbytes;
-                    const int j0 = ((c % add_cpr) * 2) >> 4;
+                    const uint8_t* ab = add_stage + (size_t)(c >> add_sh) * TILE_M * add_rowbytes;
+                    const int j0 = ((c & (add_cpr - 1)) * 2) >> 4;
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
-                        const uint4 t = *reinterpret_cast<const uint4*>(ab + swz_off(row, j0 + h2, q.add_rowbytes));
+                        const uint4 t = *reinterpret_cast<const uint4*>(ab + swz_off(row, j0 + h2, add_rowbytes));
                         const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&t);
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
@@ -502,20 +527,20 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     }
                 }
                 if (f_store) {
-                    uint8_t* ob = smem + q.off_out + (size_t)(c / out_cpr) * TILE_M * q.out_rowbytes;
-                    const int j0 = ((c % out_cpr) * q.out_esz) >> 4;
-                    if (q.out_esz == 4) {
+                    uint8_t* ob = out_stage + (size_t)(c >> out_sh) * TILE_M * out_rowbytes;
+                    const int j0 = ((c & (out_cpr - 1)) * out_esz) >> 4;
+                    if (out_esz == 4) {
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
-                            *reinterpret_cast<float4*>(ob + swz_off(row, j0 + j, q.out_rowbytes)) =
+                            *reinterpret_cast<float4*>(ob + swz_off(row, j0 + j, out_rowbytes)) =
                                 make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                     } else {
                         uint4 pk[2];
                         __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
 #pragma unroll
                         for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
-                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0, q.out_rowbytes)) = pk[0];
-                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, q.out_rowbytes)) = pk[1];
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0, out_rowbytes)) = pk[0];
+                        *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, out_rowbytes)) = pk[1];
                     }
                 }
                 if (c == 0 && et == 0) DBG_STAMP(15);

@@ -105,7 +105,9 @@ wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgP
     const int pt_end = (int)(((long long)(blockIdx.y + 1) * q.ptiles) / q.ksplit);
     const int nkb = pt_end - pt_begin;
 
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // pointer arithmetic (not an integer round trip) so that the compiler keeps the shared address space: LDS/STS/ATOMS
+    // instead of generic LD/ST/ATOM in the epilogue
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
     const int n_rowbytes = q.n_cc * 2;
     const uint32_t m_chunk_bytes = (uint32_t)(WG_KP * 128);

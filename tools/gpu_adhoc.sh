@@ -1,13 +1,10 @@
 mkdir -p gpurun_out
-MSTK_TC_TRACE=1 timeout 300 python tools/tc_timeline.py > gpurun_out/tc_timeline2.txt 2>&1; grep -B1 -A1 "^conv" gpurun_out/tc_timeline2.txt | grep -v "^--" | awk '!seen[$0]++' | cut -c 1-200
+timeout 300 python tools/tc_timeline.py > gpurun_out/tc_timeline2.txt 2>&1; grep -A1 "^conv" gpurun_out/tc_timeline2.txt | grep -v "^--" | cut -c 1-200 | head -8
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-for f in "" "0,0,0,1"; do
-MSTK_TC_FORCE=$f timeout 600 python bench.py > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
+timeout 600 python bench.py > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
 import json
 d=json.loads(open('gpurun_out/bench_adhoc.json').read().strip().splitlines()[-1])
 print('sampling', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'])
 t=d.get('train',{})
-print('train', t.get('value'), t.get('ms_per_step'))
-for r in t.get('rooflines',[])[:12]: print('  ', r)
+print('train', t.get('value'), t.get('ms_per_step'), t['roofline']['frac'], [round(l['tflops']) for l in t['roofline']['layers']])
 PY
-done
