@@ -354,7 +354,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         }
         epi_bar();                               // sbias visible to all epilogue threads
 
-        mbar_wait_backoff(&accum_bar, 0, 64);
+        mbar_wait(&accum_bar, 0);
         if (et == 0) DBG_STAMP(5);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16);

@@ -136,81 +136,99 @@ wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgP
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
 
-    if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0 && nkb > 0) {
+    // ===================== TMA producers =====================
+    // One stage takes n_dy + ntaps * n_x box loads.  Issuing a TMA load occupies its warp for ~200 cycles (measured,
+    // tools/tma_probe.cu), so each load of the stage is a job owned by one lane, jobs dealt round-robin over the five
+    // non-MMA warps (the epilogue warps have nothing else to do until the accumulators are complete); every job lane
+    // walks all k-blocks, waiting on the stage's empty barrier itself; job 0 posts the stage's byte count.
+    if (warp != 1 && nkb > 0) {
+        const int n_dy = q.swap ? q.n_chunks : 2;
+        const int n_x = q.swap ? 2 : q.n_chunks;
+        const int njobs = n_dy + ntaps * n_x;
+        const int slot = warp == 0 ? 0 : warp - 1;                 // warps 0,2,3,4,5 -> 0..4
+        const int j = lane * 5 + slot;
+        if (j < njobs) {
             const uint32_t tx_bytes = (q.swap ? (uint32_t)ntaps : 1u) * q.m_tile_bytes + (q.swap ? 1u : (uint32_t)ntaps) * q.n_tile_bytes;
             const int dy_c0 = q.swap ? n0c : m0;        // first dy channel of this CTA
             const int x_c0 = q.swap ? m0 : n0c;         // first x channel
+            const CUtensorMap* map;
+            uint32_t dst;
+            int c0, dx = 0, dy = 0;
+            if (j < n_dy) {
+                map = &maps.dy[grp.phase];
+                dst = q.swap ? off_n + (uint32_t)j * n_chunk_bytes : (uint32_t)j * m_chunk_bytes;
+                c0 = q.swap ? dy_c0 + q.n_cc * j : dy_c0 + 64 * j;
+            } else {
+                const int tj = (j - n_dy) / n_x, cj = (j - n_dy) - tj * n_x;
+                const Tap tap = ph.taps[grp.tap0 + tj];
+                dy = tap.dy; dx = tap.dx;
+                map = &maps.x[0];
+                if (p.s_in == 2) {
+                    const int py = dy & 1, px = dx & 1;
+                    dy = (dy - py) / 2;
+                    dx = (dx - px) / 2;
+                    map = &maps.x[py * 2 + px];
+                }
+                dst = q.swap ? (uint32_t)tj * q.m_tile_bytes + (uint32_t)cj * m_chunk_bytes
+                             : off_n + (uint32_t)tj * q.n_tile_bytes + (uint32_t)cj * n_chunk_bytes;
+                c0 = q.swap ? x_c0 + 64 * cj : x_c0 + q.n_cc * cj;
+            }
+            int s = 0;
+            uint32_t par = 1;                            // parity of the empty barrier's PREVIOUS phase use
             for (int it = 0; it < nkb; ++it) {
-                const int s = it % q.stages;
-                const uint32_t par = (uint32_t)((it / q.stages) & 1);
-                if (it >= q.stages) mbar_wait(&empty_bar[s], par ^ 1u);
+                if (it >= q.stages) mbar_wait(&empty_bar[s], par);
                 const int pt = pt_begin + it;
                 const int tw = pt % q.tiles_w;
                 const int th = (pt / q.tiles_w) % q.tiles_h;
                 const int tn = pt / (q.tiles_w * q.tiles_h);
-                const int w0 = tw * q.Wt, h0 = th * q.Ht, n0 = tn * q.Nt;
-                const uint32_t st = smem_base + (uint32_t)s * q.stage_bytes;
-                mbar_expect_tx(&full_bar[s], tx_bytes);
-                // dy tile (tap independent)
-                if (!q.swap) {
-                    for (int j = 0; j < 2; ++j)
-                        tma_load_4d(&maps.dy[grp.phase], &full_bar[s], st + (uint32_t)j * m_chunk_bytes, dy_c0 + 64 * j, w0, h0, n0);
-                } else {
-                    for (int j = 0; j < q.n_chunks; ++j)
-                        tma_load_4d(&maps.dy[grp.phase], &full_bar[s], st + off_n + (uint32_t)j * n_chunk_bytes, dy_c0 + q.n_cc * j, w0, h0, n0);
-                }
-                // x tiles, one per tap of the group
-                for (int t = 0; t < ntaps; ++t) {
-                    const Tap tap = ph.taps[grp.tap0 + t];
-                    int dy = tap.dy, dx = tap.dx;
-                    const CUtensorMap* mX = &maps.x[0];
-                    if (p.s_in == 2) {
-                        const int py = dy & 1, px = dx & 1;
-                        dy = (dy - py) / 2;
-                        dx = (dx - px) / 2;
-                        mX = &maps.x[py * 2 + px];
-                    }
-                    if (q.swap) {
-                        for (int j = 0; j < 2; ++j)
-                            tma_load_4d(mX, &full_bar[s], st + (uint32_t)t * q.m_tile_bytes + (uint32_t)j * m_chunk_bytes, x_c0 + 64 * j,
-                                        w0 + dx, h0 + dy, n0);
-                    } else {
-                        for (int j = 0; j < q.n_chunks; ++j)
-                            tma_load_4d(mX, &full_bar[s], st + off_n + (uint32_t)t * q.n_tile_bytes + (uint32_t)j * n_chunk_bytes,
-                                        x_c0 + q.n_cc * j, w0 + dx, h0 + dy, n0);
-                    }
-                }
+                if (j == 0) mbar_expect_tx(&full_bar[s], tx_bytes);
+                tma_load_4d(map, &full_bar[s], smem_base + (uint32_t)s * q.stage_bytes + dst, c0, tw * q.Wt + dx, th * q.Ht + dy, tn * q.Nt);
+                if (++s == q.stages) { s = 0; par ^= 1u; }
             }
         }
-    } else if (warp == 1) {
+    }
+    if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0 && nkb > 0) {
-            const uint32_t idesc = make_idesc_mn(q.BNt);
+        // whole warp converged, one elected lane issues (see conv_tc_body.cuh); invariants pinned in registers
+        if (nkb > 0) {
+            const uint32_t idesc = keep_reg(make_idesc_mn(q.BNt));
             const uint32_t kstep_a = (uint32_t)(16 * 128) >> 4;            // 16 pixels further along K
-            const uint32_t kstep_b = (uint32_t)(16 * n_rowbytes) >> 4;
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % q.stages;
-                const uint32_t par = (uint32_t)((it / q.stages) & 1);
-                mbar_wait(&full_bar[s], par);
+            const uint32_t kstep_b = keep_reg((uint32_t)(16 * n_rowbytes) >> 4);
+            const int stages = keep_reg(q.stages), nk = keep_reg(nkb), nt_ = keep_reg(ntaps);
+            const uint32_t full0 = keep_reg(smem_u32(&full_bar[0])), empty0 = keep_reg(smem_u32(&empty_bar[0]));
+            const uint32_t accum_a = keep_reg(smem_u32(&accum_bar));
+            const uint32_t a_tap = keep_reg(q.swap ? q.m_tile_bytes >> 4 : 0u), b_tap = keep_reg(q.swap ? 0u : q.n_tile_bytes >> 4);
+            const uint64_t adesc0 = make_desc_mn(smem_base, 128, m_chunk_bytes);
+            const uint64_t bdesc0 = make_desc_mn(smem_base + off_n, n_rowbytes, n_chunk_bytes);
+            const uint32_t alo0 = keep_reg((uint32_t)adesc0), blo0 = keep_reg((uint32_t)bdesc0);
+            const uint32_t ahi = keep_reg((uint32_t)(adesc0 >> 32)), bhi = keep_reg((uint32_t)(bdesc0 >> 32));
+            const uint32_t dstage = keep_reg(q.stage_bytes >> 4);
+            const uint32_t bnt = keep_reg((uint32_t)q.BNt), tm = keep_reg(tmem_base);
+            int s = 0;
+            uint32_t par = 0, soff = 0, acc = 0;
+            for (int it = 0; it < nk; ++it) {
+                mbar_wait_addr(full0 + 8u * (uint32_t)s, par);
                 tc_fence_after();
-                const uint32_t st = smem_base + (uint32_t)s * q.stage_bytes;
-                for (int t = 0; t < ntaps; ++t) {
-                    const uint32_t sa = st + (q.swap ? (uint32_t)t * q.m_tile_bytes : 0u);
-                    const uint32_t sb = st + off_n + (q.swap ? 0u : (uint32_t)t * q.n_tile_bytes);
-                    const uint64_t adesc = make_desc_mn(sa, 128, m_chunk_bytes);
-                    const uint64_t bdesc = make_desc_mn(sb, n_rowbytes, n_chunk_bytes);
-                    const uint32_t tacc = tmem_base + (uint32_t)(t * q.BNt);
+                if (elect_one()) {
+                    uint32_t alo = alo0 + soff, blo = blo0 + soff, tacc = tm;
+                    for (int t = 0; t < nt_; ++t) {
 #pragma unroll
-                    for (int k = 0; k < WG_KP / 16; ++k)
-                        umma_bf16(tacc, adesc + (uint64_t)(k * kstep_a), bdesc + (uint64_t)(k * kstep_b), idesc, (it > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < WG_KP / 16; ++k)
+                            umma_bf16(tacc, ((uint64_t)ahi << 32) | (alo + k * kstep_a), ((uint64_t)bhi << 32) | (blo + k * kstep_b), idesc,
+                                      (acc | (uint32_t)k) ? 1u : 0u);
+                        alo += a_tap; blo += b_tap; tacc += bnt;
+                    }
+                    umma_commit_addr(empty0 + 8u * (uint32_t)s);
+                    if (it == nk - 1) umma_commit_addr(accum_a);
                 }
-                umma_commit(&empty_bar[s]);
+                acc = 1u;
+                __syncwarp();
+                if (++s == stages) { s = 0; par ^= 1u; soff = 0; }
+                else soff += dstage;
             }
-            umma_commit(&accum_bar);
         }
-    } else if (nkb > 0) {
+    }
+    if (warp >= 2 && nkb > 0) {
         // ===================== epilogue (warps 2..5) =====================
         const int qd = warp & 3;
         const int row = qd * 32 + lane;

@@ -1,7 +1,6 @@
 mkdir -p gpurun_out
-timeout 300 python tools/tc_timeline.py > gpurun_out/tc_timeline2.txt 2>&1; grep -A1 "^conv" gpurun_out/tc_timeline2.txt | grep -v "^--" | cut -c 1-200 | head -8
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 600 python bench.py > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
 import json
 d=json.loads(open('gpurun_out/bench_adhoc.json').read().strip().splitlines()[-1])
 print('sampling', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'])
