@@ -38,7 +38,7 @@
 namespace mstk {
 
 template <uint32_t F>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TC_THREADS, (F & F_DDIM) ? 1 : TC_MIN_CTAS)
 conv_tc_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams q) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) TcShared sh;

@@ -7,7 +7,9 @@
 
 namespace mstk {
 
-constexpr int TC_THREADS = 224;     // warps: 0 A producer, 1 MMA issuer, 2..5 epilogue, 6 B producer
+constexpr int TC_THREADS = 352;     // warps: 0 A producer, 1 MMA issuer, 2..5 + 7..10 epilogue (column halves), 6 B producer
+constexpr int EPI_THREADS = 256;
+constexpr int TC_MIN_CTAS = 2;      // registers capped at 65536 / (2 * 352) = 93 so that two CTAs fit an SM
 constexpr int MAX_STAGES = 8;
 
 struct TcMaps {
@@ -315,8 +317,10 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                 else soff += dstage;
             }
         }
-    } else if (warp >= 2 && warp <= 5) {
-        // ===================== epilogue (warps 2..5) =====================
+    } else if (warp >= 2 && warp != 6) {
+        // ===================== epilogue (warps 2..5: lower half of the columns, 7..10: upper half) =====================
+        // one warp per scheduler leaves the epilogue bound by its own instruction latencies; two warps per TMEM lane
+        // quarter, each taking half of the BN columns, halve it
         const int qd = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = qd * 32 + lane;          // GEMM row inside the tile
         const int w_l = row % q.Wt;
@@ -324,13 +328,16 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         const int n_l = row / (q.Wt * q.Ht);
         const int n_img = n0 + n_l, hg = h0 + h_l, wg = w0 + w_l;
         const bool row_ok = n_img < p.N;
-        const int et = threadIdx.x - 64;         // 0..127
+        const int half = warp >= 7 ? 1 : 0;
+        const int et = half ? (int)threadIdx.x - 96 : (int)threadIdx.x - 64;         // 0..255
         const int BN = q.BN;
+        const int cbeg = BN >= 32 ? half * (BN >> 1) : 0;             // this warp's columns [cbeg, cend)
+        const int cend = BN >= 32 ? cbeg + (BN >> 1) : (half ? 0 : BN);
 
         // ---- work that does not need the accumulator: overlaps the main loop ----
         if (et < BN) sbias[et] = p.bias ? __ldg(p.bias + co0 + et) : 0.f;   // parameters: safe before the grid dependency
         float* sstat = sbias + BN;                // [2][BN] per-CTA column sums of the BatchNorm statistics
-        if (f_stats) { for (int i = et; i < 2 * BN; i += 128) sstat[i] = 0.f; }
+        if (f_stats) { for (int i = et; i < 2 * BN; i += EPI_THREADS) sstat[i] = 0.f; }
         pdl_wait();
         const size_t pix_off = row_ok ? ((((size_t)n_img * p.Ho + (size_t)(hg * p.s_out + ph.oy)) * p.Wo + (size_t)(wg * p.s_out + ph.ox)) *
                                          (size_t)p.Cout + (size_t)co0)
@@ -338,17 +345,17 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         float xc[16], anc[16];
         const float* xcur_row = f_ddim ? p.ddim.x_cur + pix_off : nullptr;
         const float* anc_row = f_addnc ? p.add_nc + (size_t)(row_ok ? n_img : 0) * p.Cout + co0 : nullptr;
-        if (xcur_row && row_ok) {
+        if (xcur_row && row_ok && cbeg < cend) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
-                const float4 t = *reinterpret_cast<const float4*>(xcur_row + j);
+                const float4 t = *reinterpret_cast<const float4*>(xcur_row + cbeg + j);
                 xc[j] = t.x; xc[j + 1] = t.y; xc[j + 2] = t.z; xc[j + 3] = t.w;
             }
         }
-        if (anc_row) {
+        if (anc_row && cbeg < cend) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + j));
+                const float4 t = __ldg(reinterpret_cast<const float4*>(anc_row + cbeg + j));
                 anc[j] = t.x; anc[j + 1] = t.y; anc[j + 2] = t.z; anc[j + 3] = t.w;
             }
         }
@@ -364,7 +371,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
 
         if (f_split) {
             // ---- split-K: stage the fp32 partial tile, reduce it into L2 with the copy engine ----
-            for (int c = 0; c < BN; c += 16) {
+            for (int c = cbeg; c < cend; c += 16) {
                 float v[16];
                 tmem_ld16(taddr + (uint32_t)c, v);
 #pragma unroll
@@ -401,7 +408,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                 mbar_wait(&part_bar, 0);
                 // scratch back to zero for the next launch (the tile now lives in shared memory)
                 float4* z = reinterpret_cast<float4*>(ws_tile);
-                for (int i = et; i < TILE_M * BN / 4; i += 128) __stcg(z + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                for (int i = et; i < TILE_M * BN / 4; i += EPI_THREADS) __stcg(z + i, make_float4(0.f, 0.f, 0.f, 0.f));
                 if (et == 0) DBG_STAMP(10);
             }
         }
@@ -417,8 +424,8 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
             const uint8_t* const add_stage = smem + q.off_add;
             const int act = p.act;
             float vnext[16];
-            if (!f_split) tmem_ld16_issue(taddr, vnext);
-            for (int c = 0; c < BN; c += 16) {
+            if (!f_split && cbeg < cend) tmem_ld16_issue(taddr + (uint32_t)cbeg, vnext);
+            for (int c = cbeg; c < cend; c += 16) {
                 float v[16];
                 if (f_split) {
 #pragma unroll
@@ -431,12 +438,12 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     tmem_ld_wait(vnext);
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] = vnext[j];
-                    if (c + 16 < BN) tmem_ld16_issue(taddr + (uint32_t)(c + 16), vnext);
+                    if (c + 16 < cend) tmem_ld16_issue(taddr + (uint32_t)(c + 16), vnext);
                 }
-                if (c == 0 && et == 0) DBG_STAMP(13);
+                if (c == cbeg && et == 0) DBG_STAMP(13);
                 // prefetch the next chunk's per-row operands
                 float xn_[16], an_[16];
-                const bool more = c + 16 < BN;
+                const bool more = c + 16 < cend;
                 if (more && xcur_row && row_ok) {
 #pragma unroll
                     for (int j = 0; j < 16; j += 4) {
@@ -478,7 +485,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     }
                     v[j] = x;
                 }
-                if (c == 0 && et == 0) DBG_STAMP(14);
+                if (c == cbeg && et == 0) DBG_STAMP(14);
                 if (anc_row) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] += anc[j];
@@ -543,7 +550,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                         *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, out_rowbytes)) = pk[1];
                     }
                 }
-                if (c == 0 && et == 0) DBG_STAMP(15);
+                if (c == cbeg && et == 0) DBG_STAMP(15);
                 if (more) {
 #pragma unroll
                     for (int j = 0; j < 16; ++j) { xc[j] = xn_[j]; anc[j] = an_[j]; }
