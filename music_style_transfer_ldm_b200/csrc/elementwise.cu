@@ -247,6 +247,111 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attention_kernel(const AttnP 
     attention_unit(a, (int)blockIdx.x, (int)blockIdx.y, sm, ATTN_WARPS);
 }
 
+// The UNet's cross-attention is tiny (L = 16 or 4 latent tokens against S = 16 or 4 style tokens, d = 64 / 128) and
+// purely latency bound, so: one CTA per (batch, head, block of ATTN2_QPB queries) stages Q, K and V ONCE with 16-byte
+// loads that are all in flight together, one thread per (query, key) pair for the scores, one warp per softmax row,
+// one thread per output element for P V.  Same arithmetic order per dot product as attention_unit (q pre-scaled,
+// ascending d, ascending s), so both paths agree to rounding of the softmax sum.
+constexpr int ATTN2_THREADS = 256;
+constexpr int ATTN2_QPB = 16;
+template <typename T>
+__device__ __forceinline__ void stage8(float* dst, const T* src);
+template <>
+__device__ __forceinline__ void stage8<__nv_bfloat16>(float* dst, const __nv_bfloat16* src) {
+    const uint4 r = __ldg(reinterpret_cast<const uint4*>(src));
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        dst[2 * e] = f.x; dst[2 * e + 1] = f.y;
+    }
+}
+template <>
+__device__ __forceinline__ void stage8<float>(float* dst, const float* src) {
+    const float4 r0 = __ldg(reinterpret_cast<const float4*>(src)), r1 = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    dst[0] = r0.x; dst[1] = r0.y; dst[2] = r0.z; dst[3] = r0.w;
+    dst[4] = r1.x; dst[5] = r1.y; dst[6] = r1.z; dst[7] = r1.w;
+}
+template <typename T>
+__global__ void __launch_bounds__(ATTN2_THREADS) attention_block_kernel(const AttnP a) {
+    extern __shared__ float sm[];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int d = a.e / a.heads, d8 = d >> 3;
+    const int bh = (int)blockIdx.x, b = bh / a.heads, hd = bh - b * a.heads;
+    const int q0 = (int)blockIdx.y * ATTN2_QPB;
+    const int lq = min(ATTN2_QPB, a.l - q0);
+    float* Ks = sm;                                  // [s][d+1]
+    float* Vs = Ks + (size_t)a.s * (d + 1);          // [s][d]
+    float* Qs = Vs + (size_t)a.s * d;                // [lq][d+1] (pre-scaled)
+    float* Ps = Qs + (size_t)ATTN2_QPB * (d + 1);    // [lq][s+1]
+    const float scaling = 1.0f / sqrtf((float)d);
+    const T* kp = reinterpret_cast<const T*>(a.k) + (size_t)b * a.s * a.ks + hd * d;
+    const T* vp = reinterpret_cast<const T*>(a.v) + (size_t)b * a.s * a.vs + hd * d;
+    const T* qp = reinterpret_cast<const T*>(a.q) + ((size_t)b * a.l + q0) * a.qs + hd * d;
+    const int nk = a.s * d8, nq = lq * d8;
+    for (int i = threadIdx.x; i < 2 * nk + nq; i += ATTN2_THREADS) {
+        float f[8];
+        if (i < nk) {
+            const int r = i / d8, c = (i - r * d8) * 8;
+            stage8<T>(f, kp + (size_t)r * a.ks + c);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) Ks[r * (d + 1) + c + e] = f[e];
+        } else if (i < 2 * nk) {
+            const int ii = i - nk, r = ii / d8, c = (ii - r * d8) * 8;
+            stage8<T>(f, vp + (size_t)r * a.vs + c);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) Vs[r * d + c + e] = f[e];
+        } else {
+            const int ii = i - 2 * nk, r = ii / d8, c = (ii - r * d8) * 8;
+            stage8<T>(f, qp + (size_t)r * a.qs + c);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) Qs[r * (d + 1) + c + e] = f[e] * scaling;
+        }
+    }
+    __syncthreads();
+    for (int pr = threadIdx.x; pr < lq * a.s; pr += ATTN2_THREADS) {
+        const int qi = pr / a.s, si = pr - qi * a.s;
+        const float* qr = Qs + qi * (d + 1);
+        const float* kr = Ks + si * (d + 1);
+        float acc = 0.f;
+#pragma unroll 8
+        for (int di = 0; di < d; ++di) acc = fmaf(qr[di], kr[di], acc);
+        Ps[qi * (a.s + 1) + si] = acc;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int qi = warp; qi < lq; qi += ATTN2_THREADS / 32) {
+        float* pw = Ps + qi * (a.s + 1);
+        float mx = -INFINITY;
+        for (int si = lane; si < a.s; si += 32) mx = fmaxf(mx, pw[si]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.f;
+        for (int si = lane; si < a.s; si += 32) {
+            const float ev = expf(pw[si] - mx);
+            pw[si] = ev;
+            sum += ev;
+        }
+        sum = warp_sum(sum);
+        if (lane == 0) pw[a.s] = 1.f / sum;
+    }
+    __syncthreads();
+    T* op = reinterpret_cast<T*>(a.out) + ((size_t)b * a.l + q0) * a.os + hd * d;
+    for (int o = threadIdx.x; o < lq * d; o += ATTN2_THREADS) {
+        const int qi = o / d, di = o - qi * d;
+        const float* pw = Ps + qi * (a.s + 1);
+        float acc = 0.f;
+        for (int si = 0; si < a.s; ++si) acc = fmaf(pw[si], Vs[si * d + di], acc);
+        const float r = acc * pw[a.s];
+        if (sizeof(T) == 4) reinterpret_cast<float*>(op)[(size_t)qi * a.os + di] = r;
+        else reinterpret_cast<__nv_bfloat16*>(op)[(size_t)qi * a.os + di] = __float2bfloat16_rn(r);
+    }
+}
+__host__ __device__ inline size_t attn2_smem_floats(int s, int d) {
+    return (size_t)s * (d + 1) + (size_t)s * d + (size_t)ATTN2_QPB * (d + 1) + (size_t)ATTN2_QPB * (s + 1);
+}
+
 // ---------------------------------------------------------------------------
 // scheduler arithmetic
 // ---------------------------------------------------------------------------
@@ -504,6 +609,30 @@ int mstk_attention_fwd(const mstk_attn_args* a, void* stream) {
     p.qs = a->q_stride; p.ks = a->k_stride; p.vs = a->v_stride; p.os = a->out_stride; p.dtype = a->dtype;
     if (prog_recording()) return prog_record_attn(p);
     const int d = a->e / a->heads;
+    {
+        // block kernel: 16-byte staging loads need aligned rows; everything else takes the warp-per-query kernel below
+        const int esz = a->dtype == MSTK_F32 ? 4 : 2, per16 = 16 / esz;
+        const size_t smem2 = attn2_smem_floats(a->s, d) * sizeof(float);
+        const bool aligned = (d % 8) == 0 && (a->q_stride % per16) == 0 && (a->k_stride % per16) == 0 && (a->v_stride % per16) == 0 &&
+                             ((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->k) | reinterpret_cast<uintptr_t>(a->v)) & 15) == 0;
+        if (aligned && smem2 <= 48 * 1024) {
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3(a->b * a->heads, (a->l + ATTN2_QPB - 1) / ATTN2_QPB);
+            cfg.blockDim = dim3(ATTN2_THREADS, 1, 1);
+            cfg.dynamicSmemBytes = smem2;
+            cfg.stream = (cudaStream_t)stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            cudaError_t le = a->dtype == MSTK_F32 ? cudaLaunchKernelEx(&cfg, attention_block_kernel<float>, p)
+                                                  : cudaLaunchKernelEx(&cfg, attention_block_kernel<__nv_bfloat16>, p);
+            if (le != cudaSuccess) return cuda_fail(le, "attention launch");
+            return MSTK_OK;
+        }
+    }
     const size_t smem = ((size_t)a->s * (d + 1) + (size_t)a->s * d + ATTN_WARPS * a->s + ATTN_WARPS * d) * sizeof(float);
     MSTK_REQUIRE(smem <= 200 * 1024, "attention: s*d too large for the shared-memory kernel (s=%d d=%d)", a->s, d);
     static size_t smem_set = 0;
