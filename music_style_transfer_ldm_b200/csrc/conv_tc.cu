@@ -329,6 +329,17 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     if (g_trace)
         fprintf(stderr, "[mstk conv_tc] N%d %dx%d Cin%d Cout%d k%d: BN %d KC %d splitk %d stages %d kgroup %d smem %zu\n", p.N, p.H, p.W, p.Cin,
                 p.Cout, p.nphases, c.BN, c.KC, c.splitk, c.stages, c.kgroup, c.smem_bytes);
+    {
+        auto inv = [](int d) -> uint32_t { return d <= 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); };
+        auto lg2 = [](int v) { int s = 0; while ((1 << s) < v) ++s; return s; };
+        q.inv_tiles_w = inv(c.tiles_w); q.inv_tiles_h = inv(c.tiles_h); q.inv_tiles_wh = inv(c.tiles_w * c.tiles_h);
+        q.inv_kb_per_tap = inv(c.kb_per_tap); q.inv_kgroup = inv(c.kgroup);
+        q.wt_shift = lg2(c.Wt); q.ht_shift = lg2(c.Ht); q.splitk_shift = lg2(c.splitk);
+        const long long mt_max = (long long)c.tiles_w * c.tiles_h * c.tiles_n;
+        MSTK_REQUIRE(mt_max * c.tiles_w * c.tiles_h < (1ll << 32) && (1 << q.splitk_shift) == c.splitk && (1 << q.wt_shift) == c.Wt &&
+                         (1 << q.ht_shift) == c.Ht,
+                     "conv(tcgen05): tile grid outside the range of the division-free index math");
+    }
     q.off_stage0 = 0; q.off_part = c.off_part; q.off_out = c.off_out; q.off_add = c.off_add; q.off_bias = c.off_bias;
 
     const CUtensorMapSwizzle sw = (c.KC == 64) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;

@@ -38,6 +38,10 @@ struct TcParams {
     uint32_t off_stage0;           // shared-memory carve-up (bytes from the 1024-aligned base)
     uint32_t off_part, off_out, off_add, off_bias;
     int32_t kgroup;                // k-blocks per pipeline stage (one barrier round trip and one commit per group)
+    // division-free index math on the prologue's critical path: ceil(2^32 / d) multipliers (0 for d == 1, see fdiv)
+    // and shifts for the power-of-two tile box and split-K factor; filled by launch_conv_tc
+    uint32_t inv_tiles_w, inv_tiles_h, inv_tiles_wh, inv_kb_per_tap, inv_kgroup;
+    int32_t wt_shift, ht_shift, splitk_shift;
     float* ws;                     // split-K workspace
     unsigned int* counters;        // split-K tile counters
     long long* dbg;                // optional timeline of CTA (0,0,0): 8 clock64 stamps
@@ -86,6 +90,9 @@ __device__ __forceinline__ int colsum_index(int lane) {
     return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
 }
 
+// n / d for small non-negative n with inv = ceil(2^32 / d) (exact while n * d < 2^32; inv == 0 encodes d == 1)
+__device__ __forceinline__ int fdiv(int n, uint32_t inv) { return inv ? (int)__umulhi((uint32_t)n, inv) : n; }
+
 // Per-CTA resources that outlive one tile (static shared memory of the calling kernel).
 struct TcShared {
     uint64_t full_bar[MAX_STAGES];
@@ -121,19 +128,20 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    // tile coordinates
+    // tile coordinates (no integer divisions: each is a ~100-cycle dependent chain in front of the first TMA)
     const int mt = bx;
-    const int tw = mt % q.tiles_w;
-    const int th = (mt / q.tiles_w) % q.tiles_h;
-    const int tn = mt / (q.tiles_w * q.tiles_h);
+    const int mrow = fdiv(mt, q.inv_tiles_w);                 // mt / tiles_w
+    const int tw = mt - mrow * q.tiles_w;
+    const int tn = fdiv(mt, q.inv_tiles_wh);                  // mt / (tiles_w * tiles_h)
+    const int th = mrow - tn * q.tiles_h;
     const int w0 = tw * q.Wt, h0 = th * q.Ht, n0 = tn * q.Nt;
     const int co0 = by * q.BN;
-    const int phase_idx = bz / q.splitk;
-    const int ks = bz - phase_idx * q.splitk;
+    const int phase_idx = bz >> q.splitk_shift;
+    const int ks = bz - (phase_idx << q.splitk_shift);
     const Phase& ph = p.ph[phase_idx];
     const int total_kb = ph.ntaps * q.kb_per_tap;
-    const int kb_begin = (int)(((long long)ks * total_kb) / q.splitk);
-    const int kb_end = (int)(((long long)(ks + 1) * total_kb) / q.splitk);
+    const int kb_begin = (ks * total_kb) >> q.splitk_shift;
+    const int kb_end = ((ks + 1) * total_kb) >> q.splitk_shift;
     const int nkb = kb_end - kb_begin;
 
     // shared-memory carve-up (1024-byte aligned for the 128B swizzle atom)
@@ -192,7 +200,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     //    warps 6, 2, 3 and activations (A, after the grid dependency) on warps 0, 4, 5; the epilogue warps go on to
     //    their own work when their producer lanes have issued their last load.
     const int G = q.kgroup;
-    const int ngroups = (nkb + G - 1) / G;
+    const int ngroups = fdiv(nkb + G - 1, q.inv_kgroup);
     const int nsub = q.stages * G;
     const int b_idx = warp == 6 ? 0 : warp == 2 ? 1 : warp == 3 ? 2 : -1;
     const int a_idx = warp == 0 ? 0 : warp == 4 ? 1 : warp == 5 ? 2 : -1;
@@ -200,14 +208,14 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         // ===================== B producers (weights) =====================
         const int j = lane * 3 + b_idx;
         if (j < nsub) {
-            const int s = j / G, g = j - s * G;
+            const int s = fdiv(j, q.inv_kgroup), g = j - s * G;
             const uint32_t sb = smem_base + q.off_stage0 + (uint32_t)j * sub_bytes + a_bytes;
             int use = 0;
             for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
                 const int cnt = nkb - grp * G < G ? nkb - grp * G : G;     // k-blocks in this group (the last may be short)
                 if (g >= cnt) break;
                 const int kb = kb_begin + grp * G + g;
-                const int tap_i = kb / q.kb_per_tap;
+                const int tap_i = fdiv(kb, q.inv_kb_per_tap);
                 const int cb = kb - tap_i * q.kb_per_tap;
                 if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
                 // lane g == 0 posts the group's byte count; its siblings' complete_tx may land first (the transaction
@@ -223,14 +231,14 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         if (warp == 0 && lane == 0) pdl_launch_dependents();
         const int j = lane * 3 + a_idx;
         if (j < nsub) {
-            const int s = j / G, g = j - s * G;
+            const int s = fdiv(j, q.inv_kgroup), g = j - s * G;
             const uint32_t sa = smem_base + q.off_stage0 + (uint32_t)j * sub_bytes;
             int use = 0;
             for (int grp = s; grp < ngroups; grp += q.stages, ++use) {
                 const int cnt = nkb - grp * G < G ? nkb - grp * G : G;
                 if (g >= cnt) break;
                 const int kb = kb_begin + grp * G + g;
-                const int tap_i = kb / q.kb_per_tap;
+                const int tap_i = fdiv(kb, q.inv_kb_per_tap);
                 const int cb = kb - tap_i * q.kb_per_tap;
                 const Tap t = ph.taps[tap_i];
                 int dy = t.dy, dx = t.dx;
@@ -323,9 +331,9 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
         // quarter, each taking half of the BN columns, halve it
         const int qd = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = qd * 32 + lane;          // GEMM row inside the tile
-        const int w_l = row % q.Wt;
-        const int h_l = (row / q.Wt) % q.Ht;
-        const int n_l = row / (q.Wt * q.Ht);
+        const int w_l = row & (q.Wt - 1);                        // the tile box sides are powers of two
+        const int h_l = (row >> q.wt_shift) & (q.Ht - 1);
+        const int n_l = row >> (q.wt_shift + q.ht_shift);
         const int n_img = n0 + n_l, hg = h0 + h_l, wg = w0 + w_l;
         const bool row_ok = n_img < p.N;
         const int half = warp >= 7 ? 1 : 0;
