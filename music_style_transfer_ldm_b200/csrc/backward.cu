@@ -448,6 +448,129 @@ __global__ void __launch_bounds__(AB_WARPS * 32) attention_bwd_kernel(const Attn
     }
 }
 
+// Block form for the UNet's tiny cross-attention (L, S <= 16 tokens, d = 64 / 128): one CTA per (sample, head) holds Q,
+// K, V and dO in shared memory (16-byte staging loads), one thread per (query, key) pair for the scores and dP, one warp
+// per softmax row, one thread per element of dV = P^T dO, dK = dS^T Qs and dQ = scaling * dS K: no atomics, nothing
+// serialised over the head dimension.  The warp-per-query kernel above stays for shapes that do not fit.
+constexpr int AB2_THREADS = 256;
+template <typename T>
+__device__ __forceinline__ void ab_stage8(float* dst, const T* src, float scale);
+template <>
+__device__ __forceinline__ void ab_stage8<__nv_bfloat16>(float* dst, const __nv_bfloat16* src, float scale) {
+    const uint4 r = __ldg(reinterpret_cast<const uint4*>(src));
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        dst[2 * e] = f.x * scale; dst[2 * e + 1] = f.y * scale;
+    }
+}
+template <>
+__device__ __forceinline__ void ab_stage8<float>(float* dst, const float* src, float scale) {
+    const float4 r0 = __ldg(reinterpret_cast<const float4*>(src)), r1 = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    dst[0] = r0.x * scale; dst[1] = r0.y * scale; dst[2] = r0.z * scale; dst[3] = r0.w * scale;
+    dst[4] = r1.x * scale; dst[5] = r1.y * scale; dst[6] = r1.z * scale; dst[7] = r1.w * scale;
+}
+template <typename T>
+__device__ __forceinline__ void ab_store(T* p, float v);
+template <> __device__ __forceinline__ void ab_store<float>(float* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void ab_store<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+__host__ __device__ inline size_t ab2_smem_floats(int l, int s, int d) {
+    return (size_t)2 * s * (d + 1) + (size_t)2 * l * (d + 1) + (size_t)2 * l * (s + 1);
+}
+template <typename T>
+__global__ void __launch_bounds__(AB2_THREADS) attention_bwd_block_kernel(const AttnBwdP a) {
+    extern __shared__ float sm[];
+    const int d = a.e / a.heads, d8 = d >> 3, l = a.l, s = a.s;
+    float* Ks = sm;                                  // [s][d+1]
+    float* Vs = Ks + (size_t)s * (d + 1);            // [s][d+1]
+    float* Qs = Vs + (size_t)s * (d + 1);            // [l][d+1]  scaled q
+    float* Os = Qs + (size_t)l * (d + 1);            // [l][d+1]  d_out
+    float* Ps = Os + (size_t)l * (d + 1);            // [l][s+1]  scores -> probabilities
+    float* Ds = Ps + (size_t)l * (s + 1);            // [l][s+1]  dP -> dS
+    const int b = blockIdx.x / a.heads, hd = blockIdx.x - b * a.heads;
+    const float scaling = 1.0f / sqrtf((float)d);
+    const T* kp = reinterpret_cast<const T*>(a.k) + (size_t)b * s * a.ks + hd * d;
+    const T* vp = reinterpret_cast<const T*>(a.v) + (size_t)b * s * a.vs + hd * d;
+    const T* qp = reinterpret_cast<const T*>(a.q) + (size_t)b * l * a.qs + hd * d;
+    const T* op = reinterpret_cast<const T*>(a.d_out) + (size_t)b * l * a.dos + hd * d;
+    const int nk = s * d8, nq = l * d8;
+    for (int i = threadIdx.x; i < 2 * nk + 2 * nq; i += AB2_THREADS) {
+        float f[8];
+        float* dst;
+        if (i < nk) {
+            const int r = i / d8, c = (i - r * d8) * 8;
+            ab_stage8<T>(f, kp + (size_t)r * a.ks + c, 1.f); dst = Ks + r * (d + 1) + c;
+        } else if (i < 2 * nk) {
+            const int ii = i - nk, r = ii / d8, c = (ii - r * d8) * 8;
+            ab_stage8<T>(f, vp + (size_t)r * a.vs + c, 1.f); dst = Vs + r * (d + 1) + c;
+        } else if (i < 2 * nk + nq) {
+            const int ii = i - 2 * nk, r = ii / d8, c = (ii - r * d8) * 8;
+            ab_stage8<T>(f, qp + (size_t)r * a.qs + c, scaling); dst = Qs + r * (d + 1) + c;
+        } else {
+            const int ii = i - 2 * nk - nq, r = ii / d8, c = (ii - r * d8) * 8;
+            ab_stage8<T>(f, op + (size_t)r * a.dos + c, 1.f); dst = Os + r * (d + 1) + c;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dst[e] = f[e];
+    }
+    __syncthreads();
+    // scores and dP = dO V^T
+    for (int pr = threadIdx.x; pr < l * s; pr += AB2_THREADS) {
+        const int qi = pr / s, si = pr - qi * s;
+        const float* qr = Qs + qi * (d + 1);
+        const float* orow = Os + qi * (d + 1);
+        const float* kr = Ks + si * (d + 1);
+        const float* vr = Vs + si * (d + 1);
+        float a1 = 0.f, a2 = 0.f;
+#pragma unroll 8
+        for (int di = 0; di < d; ++di) { a1 = fmaf(qr[di], kr[di], a1); a2 = fmaf(orow[di], vr[di], a2); }
+        Ps[qi * (s + 1) + si] = a1;
+        Ds[qi * (s + 1) + si] = a2;
+    }
+    __syncthreads();
+    // softmax rows, rowdot = sum p dP, dS = p (dP - rowdot)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int qi = warp; qi < l; qi += AB2_THREADS / 32) {
+        float* pw = Ps + qi * (s + 1);
+        float* dw = Ds + qi * (s + 1);
+        float mx = -INFINITY;
+        for (int si = lane; si < s; si += 32) mx = fmaxf(mx, pw[si]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.f;
+        for (int si = lane; si < s; si += 32) { const float ev = expf(pw[si] - mx); pw[si] = ev; sum += ev; }
+        sum = warp_sum(sum);
+        const float inv = 1.f / sum;
+        float rowdot = 0.f;
+        for (int si = lane; si < s; si += 32) { const float pr = pw[si] * inv; pw[si] = pr; rowdot = fmaf(pr, dw[si], rowdot); }
+        rowdot = warp_sum(rowdot);
+        for (int si = lane; si < s; si += 32) dw[si] = pw[si] * (dw[si] - rowdot);
+    }
+    __syncthreads();
+    T* dkp = reinterpret_cast<T*>(a.dk) + (size_t)b * s * a.dks + hd * d;
+    T* dvp = reinterpret_cast<T*>(a.dv) + (size_t)b * s * a.dvs + hd * d;
+    T* dqp = reinterpret_cast<T*>(a.dq) + (size_t)b * l * a.dqs + hd * d;
+    const int nkv = s * d, nqd = l * d;
+    for (int o = threadIdx.x; o < 2 * nkv + nqd; o += AB2_THREADS) {
+        float acc = 0.f;
+        if (o < nkv) {                       // dV[si][di] = sum_q P[q][si] dO[q][di]
+            const int si = o / d, di = o - si * d;
+            for (int qi = 0; qi < l; ++qi) acc = fmaf(Ps[qi * (s + 1) + si], Os[qi * (d + 1) + di], acc);
+            ab_store<T>(dvp + (size_t)si * a.dvs + di, acc);
+        } else if (o < 2 * nkv) {            // dK[si][di] = sum_q dS[q][si] Qs[q][di]   (scores = (q*scaling) . k)
+            const int oo = o - nkv, si = oo / d, di = oo - si * d;
+            for (int qi = 0; qi < l; ++qi) acc = fmaf(Ds[qi * (s + 1) + si], Qs[qi * (d + 1) + di], acc);
+            ab_store<T>(dkp + (size_t)si * a.dks + di, acc);
+        } else {                             // dQ[qi][di] = scaling * sum_s dS[qi][s] K[s][di]
+            const int oo = o - 2 * nkv, qi = oo / d, di = oo - qi * d;
+            for (int si = 0; si < s; ++si) acc = fmaf(Ds[qi * (s + 1) + si], Ks[si * (d + 1) + di], acc);
+            ab_store<T>(dqp + (size_t)qi * a.dqs + di, acc * scaling);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------
 // small streaming ops
 // ---------------------------------------------------------------------------
@@ -772,6 +895,20 @@ int mstk_attention_bwd(const mstk_attn_bwd_args* a, void* stream) {
     p.b = a->b; p.l = a->l; p.s = a->s; p.e = a->e; p.heads = a->heads; p.qs = a->q_stride; p.ks = a->k_stride; p.vs = a->v_stride;
     p.dos = a->do_stride; p.dqs = a->dq_stride; p.dks = a->dk_stride; p.dvs = a->dv_stride; p.dtype = a->dtype;
     const int d = a->e / a->heads;
+    {
+        const int per16 = a->dtype == MSTK_F32 ? 4 : 8;
+        const size_t smem2 = ab2_smem_floats(a->l, a->s, d) * sizeof(float);
+        const bool aligned = (d % 8) == 0 && (a->q_stride % per16) == 0 && (a->k_stride % per16) == 0 && (a->v_stride % per16) == 0 &&
+                             (a->do_stride % per16) == 0 &&
+                             ((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->k) | reinterpret_cast<uintptr_t>(a->v) |
+                               reinterpret_cast<uintptr_t>(a->d_out)) & 15) == 0;
+        if (aligned && smem2 <= 48 * 1024 && a->l * a->s <= 4096) {
+            if (a->dtype == MSTK_F32) attention_bwd_block_kernel<float><<<a->b * a->heads, AB2_THREADS, smem2, (cudaStream_t)stream>>>(p);
+            else attention_bwd_block_kernel<__nv_bfloat16><<<a->b * a->heads, AB2_THREADS, smem2, (cudaStream_t)stream>>>(p);
+            MSTK_CHECK_LAUNCH("attention_bwd");
+            return MSTK_OK;
+        }
+    }
     const size_t smem = ((size_t)2 * a->s * (d + 1) + (size_t)2 * a->s * d + AB_WARPS * a->s + 2 * AB_WARPS * d) * sizeof(float);
     MSTK_REQUIRE(smem <= 200 * 1024, "attention_bwd: s*d too large (s=%d d=%d)", a->s, d);
     static size_t smem_set = 0;

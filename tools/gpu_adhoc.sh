@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
-timeout 300 python tools/tc_timeline.py > gpurun_out/tc_timeline2.txt 2>&1; grep -A2 "^conv" gpurun_out/tc_timeline2.txt | grep -v "^--" | cut -c 1-200 | head -6
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
 import json
