@@ -10,7 +10,7 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/b
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/b_short.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1; echo "ncu_list rc=$?" | tee -a gpurun_out/rc.txt
 timeout 300 python tools/profile_step.py 4 > gpurun_out/prof_plain.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"conv_tc_kernel|attention_kernel" -s 36 -c 17 -o gpurun_out/prof_step python tools/profile_step.py 4 > gpurun_out/prof_ncu.log 2>&1; echo "ncu_full rc=$?" | tee -a gpurun_out/rc.txt
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"conv_tc_kernel|attention" -s 36 -c 17 -o gpurun_out/prof_step python tools/profile_step.py 4 > gpurun_out/prof_ncu.log 2>&1; echo "ncu_full rc=$?" | tee -a gpurun_out/rc.txt
 tail -n 5 gpurun_out/t_gpu.log; tail -n 4 gpurun_out/smoke.log; cut -c 1-1800 gpurun_out/bench.log; tail -n 5 gpurun_out/bench.err; cut -c 1-600 gpurun_out/bench_ref.log
 timeout 300 python tools/profile_train.py 256 3 > gpurun_out/pt_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/train_launches.csv python tools/profile_train.py 256 3 > gpurun_out/pt_ncu.log 2>&1; echo "ncu_train rc=$?" | tee -a gpurun_out/rc.txt

@@ -13,6 +13,8 @@ lib.mstk_debug_tc_timeline(dbg.data_ptr())
 CASES = [(64, 16, 16, 32, 64, 3, 1, False), (64, 16, 16, 64, 128, 3, 2, False), (64, 8, 8, 128, 256, 3, 2, False),
          (64, 4, 4, 256, 256, 1, 1, False), (64, 4, 4, 256, 512, 3, 2, False), (64, 2, 2, 512, 512, 3, 1, False),
          (64, 2, 2, 512, 256, 3, 2, True), (64, 8, 8, 128, 64, 3, 2, True), (64, 16, 16, 64, 32, 3, 1, False)]
+if os.environ.get('TCVGG'):
+    CASES = [(768, 64, 64, 64, 128, 3, 1, False), (768, 32, 32, 128, 256, 3, 1, False), (768, 16, 16, 512, 512, 3, 1, False)]
 for (n, h, w, cin, cout, k, s, tr) in CASES:
     x = torch.randn((n, h, w, cin), device="cuda").bfloat16()
     wp = torch.randn((k * k, cout, cin), device="cuda").bfloat16()
