@@ -477,17 +477,28 @@ template <> __device__ __forceinline__ void ab_store<float>(float* p, float v) {
 template <> __device__ __forceinline__ void ab_store<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
 __host__ __device__ inline size_t ab2_smem_floats(int l, int s, int d) {
-    return (size_t)2 * s * (d + 1) + (size_t)2 * l * (d + 1) + (size_t)2 * l * (s + 1);
+    return (size_t)2 * s * (d + 4) + (size_t)2 * l * (d + 4) + (size_t)2 * l * (s + 1);
+}
+template <typename T>
+__device__ __forceinline__ void ab_store4(T* p, float4 v);
+template <> __device__ __forceinline__ void ab_store4<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <> __device__ __forceinline__ void ab_store4<__nv_bfloat16>(__nv_bfloat16* p, float4 v) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo); pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(p) = pk;
 }
 template <typename T>
 __global__ void __launch_bounds__(AB2_THREADS) attention_bwd_block_kernel(const AttnBwdP a) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float smv[];
+    float* sm = smv;
     const int d = a.e / a.heads, d8 = d >> 3, l = a.l, s = a.s;
-    float* Ks = sm;                                  // [s][d+1]
-    float* Vs = Ks + (size_t)s * (d + 1);            // [s][d+1]
-    float* Qs = Vs + (size_t)s * (d + 1);            // [l][d+1]  scaled q
-    float* Os = Qs + (size_t)l * (d + 1);            // [l][d+1]  d_out
-    float* Ps = Os + (size_t)l * (d + 1);            // [l][s+1]  scores -> probabilities
+    const int dp = d + 4;                            // 16-byte aligned rows, 8 consecutive rows on distinct banks
+    float* Ks = sm;                                  // [s][dp]
+    float* Vs = Ks + (size_t)s * dp;                 // [s][dp]
+    float* Qs = Vs + (size_t)s * dp;                 // [l][dp]  scaled q
+    float* Os = Qs + (size_t)l * dp;                 // [l][dp]  d_out
+    float* Ps = Os + (size_t)l * dp;                 // [l][s+1]  scores -> probabilities
     float* Ds = Ps + (size_t)l * (s + 1);            // [l][s+1]  dP -> dS
     const int b = blockIdx.x / a.heads, hd = blockIdx.x - b * a.heads;
     const float scaling = 1.0f / sqrtf((float)d);
@@ -501,31 +512,35 @@ __global__ void __launch_bounds__(AB2_THREADS) attention_bwd_block_kernel(const 
         float* dst;
         if (i < nk) {
             const int r = i / d8, c = (i - r * d8) * 8;
-            ab_stage8<T>(f, kp + (size_t)r * a.ks + c, 1.f); dst = Ks + r * (d + 1) + c;
+            ab_stage8<T>(f, kp + (size_t)r * a.ks + c, 1.f); dst = Ks + r * dp + c;
         } else if (i < 2 * nk) {
             const int ii = i - nk, r = ii / d8, c = (ii - r * d8) * 8;
-            ab_stage8<T>(f, vp + (size_t)r * a.vs + c, 1.f); dst = Vs + r * (d + 1) + c;
+            ab_stage8<T>(f, vp + (size_t)r * a.vs + c, 1.f); dst = Vs + r * dp + c;
         } else if (i < 2 * nk + nq) {
             const int ii = i - 2 * nk, r = ii / d8, c = (ii - r * d8) * 8;
-            ab_stage8<T>(f, qp + (size_t)r * a.qs + c, scaling); dst = Qs + r * (d + 1) + c;
+            ab_stage8<T>(f, qp + (size_t)r * a.qs + c, scaling); dst = Qs + r * dp + c;
         } else {
             const int ii = i - 2 * nk - nq, r = ii / d8, c = (ii - r * d8) * 8;
-            ab_stage8<T>(f, op + (size_t)r * a.dos + c, 1.f); dst = Os + r * (d + 1) + c;
+            ab_stage8<T>(f, op + (size_t)r * a.dos + c, 1.f); dst = Os + r * dp + c;
         }
-#pragma unroll
-        for (int e = 0; e < 8; ++e) dst[e] = f[e];
+        *reinterpret_cast<float4*>(dst) = make_float4(f[0], f[1], f[2], f[3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(f[4], f[5], f[6], f[7]);
     }
     __syncthreads();
-    // scores and dP = dO V^T
+    // scores and dP = dO V^T (128-bit shared-memory reads: the kernel is bound by LDS instructions)
     for (int pr = threadIdx.x; pr < l * s; pr += AB2_THREADS) {
         const int qi = pr / s, si = pr - qi * s;
-        const float* qr = Qs + qi * (d + 1);
-        const float* orow = Os + qi * (d + 1);
-        const float* kr = Ks + si * (d + 1);
-        const float* vr = Vs + si * (d + 1);
+        const float4* qr = reinterpret_cast<const float4*>(Qs + qi * dp);
+        const float4* orow = reinterpret_cast<const float4*>(Os + qi * dp);
+        const float4* kr = reinterpret_cast<const float4*>(Ks + si * dp);
+        const float4* vr = reinterpret_cast<const float4*>(Vs + si * dp);
         float a1 = 0.f, a2 = 0.f;
-#pragma unroll 8
-        for (int di = 0; di < d; ++di) { a1 = fmaf(qr[di], kr[di], a1); a2 = fmaf(orow[di], vr[di], a2); }
+#pragma unroll 4
+        for (int c = 0; c < (d >> 2); ++c) {
+            const float4 qv = qr[c], kv = kr[c], ov = orow[c], vv = vr[c];
+            a1 = fmaf(qv.x, kv.x, a1); a1 = fmaf(qv.y, kv.y, a1); a1 = fmaf(qv.z, kv.z, a1); a1 = fmaf(qv.w, kv.w, a1);
+            a2 = fmaf(ov.x, vv.x, a2); a2 = fmaf(ov.y, vv.y, a2); a2 = fmaf(ov.z, vv.z, a2); a2 = fmaf(ov.w, vv.w, a2);
+        }
         Ps[qi * (s + 1) + si] = a1;
         Ds[qi * (s + 1) + si] = a2;
     }
@@ -552,21 +567,33 @@ __global__ void __launch_bounds__(AB2_THREADS) attention_bwd_block_kernel(const 
     T* dkp = reinterpret_cast<T*>(a.dk) + (size_t)b * s * a.dks + hd * d;
     T* dvp = reinterpret_cast<T*>(a.dv) + (size_t)b * s * a.dvs + hd * d;
     T* dqp = reinterpret_cast<T*>(a.dq) + (size_t)b * l * a.dqs + hd * d;
-    const int nkv = s * d, nqd = l * d;
+    const int d4 = d >> 2, nkv = s * d4, nqd = l * d4;
     for (int o = threadIdx.x; o < 2 * nkv + nqd; o += AB2_THREADS) {
-        float acc = 0.f;
-        if (o < nkv) {                       // dV[si][di] = sum_q P[q][si] dO[q][di]
-            const int si = o / d, di = o - si * d;
-            for (int qi = 0; qi < l; ++qi) acc = fmaf(Ps[qi * (s + 1) + si], Os[qi * (d + 1) + di], acc);
-            ab_store<T>(dvp + (size_t)si * a.dvs + di, acc);
-        } else if (o < 2 * nkv) {            // dK[si][di] = sum_q dS[q][si] Qs[q][di]   (scores = (q*scaling) . k)
-            const int oo = o - nkv, si = oo / d, di = oo - si * d;
-            for (int qi = 0; qi < l; ++qi) acc = fmaf(Ds[qi * (s + 1) + si], Qs[qi * (d + 1) + di], acc);
-            ab_store<T>(dkp + (size_t)si * a.dks + di, acc);
-        } else {                             // dQ[qi][di] = scaling * sum_s dS[qi][s] K[s][di]
-            const int oo = o - 2 * nkv, qi = oo / d, di = oo - qi * d;
-            for (int si = 0; si < s; ++si) acc = fmaf(Ds[qi * (s + 1) + si], Ks[si * (d + 1) + di], acc);
-            ab_store<T>(dqp + (size_t)qi * a.dqs + di, acc * scaling);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (o < nkv) {                       // dV[si][di..] = sum_q P[q][si] dO[q][di..]
+            const int si = o / d4, di = (o - si * d4) * 4;
+            for (int qi = 0; qi < l; ++qi) {
+                const float w = Ps[qi * (s + 1) + si];
+                const float4 x = *reinterpret_cast<const float4*>(Os + qi * dp + di);
+                acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
+            }
+            ab_store4<T>(dvp + (size_t)si * a.dvs + di, acc);
+        } else if (o < 2 * nkv) {            // dK[si][di..] = sum_q dS[q][si] Qs[q][di..]   (scores = (q*scaling) . k)
+            const int oo = o - nkv, si = oo / d4, di = (oo - si * d4) * 4;
+            for (int qi = 0; qi < l; ++qi) {
+                const float w = Ds[qi * (s + 1) + si];
+                const float4 x = *reinterpret_cast<const float4*>(Qs + qi * dp + di);
+                acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
+            }
+            ab_store4<T>(dkp + (size_t)si * a.dks + di, acc);
+        } else {                             // dQ[qi][di..] = scaling * sum_s dS[qi][s] K[s][di..]
+            const int oo = o - 2 * nkv, qi = oo / d4, di = (oo - qi * d4) * 4;
+            for (int si = 0; si < s; ++si) {
+                const float w = Ds[qi * (s + 1) + si];
+                const float4 x = *reinterpret_cast<const float4*>(Ks + si * dp + di);
+                acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
+            }
+            ab_store4<T>(dqp + (size_t)qi * a.dqs + di, make_float4(acc.x * scaling, acc.y * scaling, acc.z * scaling, acc.w * scaling));
         }
     }
 }
@@ -899,7 +926,9 @@ int mstk_attention_bwd(const mstk_attn_bwd_args* a, void* stream) {
         const int per16 = a->dtype == MSTK_F32 ? 4 : 8;
         const size_t smem2 = ab2_smem_floats(a->l, a->s, d) * sizeof(float);
         const bool aligned = (d % 8) == 0 && (a->q_stride % per16) == 0 && (a->k_stride % per16) == 0 && (a->v_stride % per16) == 0 &&
-                             (a->do_stride % per16) == 0 &&
+                             (a->do_stride % per16) == 0 && (a->dq_stride % per16) == 0 && (a->dk_stride % per16) == 0 &&
+                             (a->dv_stride % per16) == 0 &&
+                             ((reinterpret_cast<uintptr_t>(a->dq) | reinterpret_cast<uintptr_t>(a->dk) | reinterpret_cast<uintptr_t>(a->dv)) & 15) == 0 &&
                              ((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->k) | reinterpret_cast<uintptr_t>(a->v) |
                                reinterpret_cast<uintptr_t>(a->d_out)) & 15) == 0;
         if (aligned && smem2 <= 48 * 1024 && a->l * a->s <= 4096) {

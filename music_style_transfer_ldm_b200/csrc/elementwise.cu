@@ -274,17 +274,18 @@ __device__ __forceinline__ void stage8<float>(float* dst, const float* src) {
 }
 template <typename T>
 __global__ void __launch_bounds__(ATTN2_THREADS) attention_block_kernel(const AttnP a) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int d = a.e / a.heads, d8 = d >> 3;
+    const int dp = d + 4;                            // row pitch: 16-byte aligned rows, 8 consecutive rows on distinct banks
     const int bh = (int)blockIdx.x, b = bh / a.heads, hd = bh - b * a.heads;
     const int q0 = (int)blockIdx.y * ATTN2_QPB;
     const int lq = min(ATTN2_QPB, a.l - q0);
-    float* Ks = sm;                                  // [s][d+1]
-    float* Vs = Ks + (size_t)a.s * (d + 1);          // [s][d]
-    float* Qs = Vs + (size_t)a.s * d;                // [lq][d+1] (pre-scaled)
-    float* Ps = Qs + (size_t)ATTN2_QPB * (d + 1);    // [lq][s+1]
+    float* Ks = sm;                                  // [s][dp]
+    float* Vs = Ks + (size_t)a.s * dp;               // [s][dp]
+    float* Qs = Vs + (size_t)a.s * dp;               // [lq][dp] (pre-scaled)
+    float* Ps = Qs + (size_t)ATTN2_QPB * dp;         // [lq][s+1]
     const float scaling = 1.0f / sqrtf((float)d);
     const T* kp = reinterpret_cast<const T*>(a.k) + (size_t)b * a.s * a.ks + hd * d;
     const T* vp = reinterpret_cast<const T*>(a.v) + (size_t)b * a.s * a.vs + hd * d;
@@ -292,31 +293,34 @@ __global__ void __launch_bounds__(ATTN2_THREADS) attention_block_kernel(const At
     const int nk = a.s * d8, nq = lq * d8;
     for (int i = threadIdx.x; i < 2 * nk + nq; i += ATTN2_THREADS) {
         float f[8];
+        float* dst;
+        float sc = 1.f;
         if (i < nk) {
             const int r = i / d8, c = (i - r * d8) * 8;
-            stage8<T>(f, kp + (size_t)r * a.ks + c);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) Ks[r * (d + 1) + c + e] = f[e];
+            stage8<T>(f, kp + (size_t)r * a.ks + c); dst = Ks + r * dp + c;
         } else if (i < 2 * nk) {
             const int ii = i - nk, r = ii / d8, c = (ii - r * d8) * 8;
-            stage8<T>(f, vp + (size_t)r * a.vs + c);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) Vs[r * d + c + e] = f[e];
+            stage8<T>(f, vp + (size_t)r * a.vs + c); dst = Vs + r * dp + c;
         } else {
             const int ii = i - 2 * nk, r = ii / d8, c = (ii - r * d8) * 8;
-            stage8<T>(f, qp + (size_t)r * a.qs + c);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) Qs[r * (d + 1) + c + e] = f[e] * scaling;
+            stage8<T>(f, qp + (size_t)r * a.qs + c); dst = Qs + r * dp + c; sc = scaling;
         }
+        *reinterpret_cast<float4*>(dst) = make_float4(f[0] * sc, f[1] * sc, f[2] * sc, f[3] * sc);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(f[4] * sc, f[5] * sc, f[6] * sc, f[7] * sc);
     }
     __syncthreads();
+    // scores: one thread per (query, key); the kernel is bound by shared-memory instructions, so 128-bit reads
+    // (same ascending-d fma order as the scalar form)
     for (int pr = threadIdx.x; pr < lq * a.s; pr += ATTN2_THREADS) {
         const int qi = pr / a.s, si = pr - qi * a.s;
-        const float* qr = Qs + qi * (d + 1);
-        const float* kr = Ks + si * (d + 1);
+        const float4* qr = reinterpret_cast<const float4*>(Qs + qi * dp);
+        const float4* kr = reinterpret_cast<const float4*>(Ks + si * dp);
         float acc = 0.f;
-#pragma unroll 8
-        for (int di = 0; di < d; ++di) acc = fmaf(qr[di], kr[di], acc);
+#pragma unroll 4
+        for (int c = 0; c < (d >> 2); ++c) {
+            const float4 qv = qr[c], kv = kr[c];
+            acc = fmaf(qv.x, kv.x, acc); acc = fmaf(qv.y, kv.y, acc); acc = fmaf(qv.z, kv.z, acc); acc = fmaf(qv.w, kv.w, acc);
+        }
         Ps[qi * (a.s + 1) + si] = acc;
     }
     __syncthreads();
@@ -337,19 +341,32 @@ __global__ void __launch_bounds__(ATTN2_THREADS) attention_block_kernel(const At
         if (lane == 0) pw[a.s] = 1.f / sum;
     }
     __syncthreads();
+    // P V: one thread per (query, 4 consecutive channels)
     T* op = reinterpret_cast<T*>(a.out) + ((size_t)b * a.l + q0) * a.os + hd * d;
-    for (int o = threadIdx.x; o < lq * d; o += ATTN2_THREADS) {
-        const int qi = o / d, di = o - qi * d;
+    const int d4 = d >> 2;
+    for (int o = threadIdx.x; o < lq * d4; o += ATTN2_THREADS) {
+        const int qi = o / d4, di = (o - qi * d4) * 4;
         const float* pw = Ps + qi * (a.s + 1);
-        float acc = 0.f;
-        for (int si = 0; si < a.s; ++si) acc = fmaf(pw[si], Vs[si * d + di], acc);
-        const float r = acc * pw[a.s];
-        if (sizeof(T) == 4) reinterpret_cast<float*>(op)[(size_t)qi * a.os + di] = r;
-        else reinterpret_cast<__nv_bfloat16*>(op)[(size_t)qi * a.os + di] = __float2bfloat16_rn(r);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int si = 0; si < a.s; ++si) {
+            const float pv = pw[si];
+            const float4 vv = *reinterpret_cast<const float4*>(Vs + si * dp + di);
+            acc.x = fmaf(pv, vv.x, acc.x); acc.y = fmaf(pv, vv.y, acc.y); acc.z = fmaf(pv, vv.z, acc.z); acc.w = fmaf(pv, vv.w, acc.w);
+        }
+        const float inv = pw[a.s];
+        T* dst = op + (size_t)qi * a.os + di;
+        if (sizeof(T) == 4) {
+            *reinterpret_cast<float4*>(dst) = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+        } else {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x * inv, acc.y * inv), hi = __floats2bfloat162_rn(acc.z * inv, acc.w * inv);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo); pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst) = pk;
+        }
     }
 }
 __host__ __device__ inline size_t attn2_smem_floats(int s, int d) {
-    return (size_t)s * (d + 1) + (size_t)s * d + (size_t)ATTN2_QPB * (d + 1) + (size_t)ATTN2_QPB * (s + 1);
+    return (size_t)2 * s * (d + 4) + (size_t)ATTN2_QPB * (d + 4) + (size_t)ATTN2_QPB * (s + 1);
 }
 
 // ---------------------------------------------------------------------------
@@ -614,7 +631,9 @@ int mstk_attention_fwd(const mstk_attn_args* a, void* stream) {
         const int esz = a->dtype == MSTK_F32 ? 4 : 2, per16 = 16 / esz;
         const size_t smem2 = attn2_smem_floats(a->s, d) * sizeof(float);
         const bool aligned = (d % 8) == 0 && (a->q_stride % per16) == 0 && (a->k_stride % per16) == 0 && (a->v_stride % per16) == 0 &&
-                             ((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->k) | reinterpret_cast<uintptr_t>(a->v)) & 15) == 0;
+                             (a->out_stride % per16) == 0 &&
+                             ((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->k) | reinterpret_cast<uintptr_t>(a->v) |
+                               reinterpret_cast<uintptr_t>(a->out)) & 15) == 0;
         if (aligned && smem2 <= 48 * 1024) {
             cudaLaunchConfig_t cfg;
             memset(&cfg, 0, sizeof(cfg));
