@@ -68,6 +68,11 @@ static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
 static int g_pdl = 1;
 static int g_force_group = 0, g_trace = 0;
+// Split-K partners as a thread-block cluster reducing through DSMEM (MSTK_TC_CLUSTER=1).  Measured on B200: the
+// reduction itself is faster (6.6 k -> 4.4 k cycles per tile) but the sampling loop is SLOWER (10 607 -> 10 323
+// steps/s): a cluster needs 4-8 free SMs of one GPC at once, which stalls the programmatic-dependent-launch overlap
+// of consecutive layers.  Off by default.
+static int g_cluster = 0;
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
 void tc_set_debug(long long* p) { g_dbg = p; }
@@ -97,6 +102,7 @@ bool tc_init() {
     // development knobs (tuning sweeps): MSTK_PDL=0 disables programmatic dependent launch,
     // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
     if (const char* s = getenv("MSTK_TC_TRACE")) g_trace = atoi(s);
+    if (const char* s = getenv("MSTK_TC_CLUSTER")) g_cluster = atoi(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
     for (int i = 0; i < kNumVariants; ++i) {
@@ -308,7 +314,9 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     TcParams q;
     memset(&q, 0, sizeof(q));
     q.p = p;
-    if (c.splitk > 1) {
+    // opt-in: split-K partners as one thread-block cluster (portable size <= 8); never in recorded layer programs
+    q.cluster = (c.splitk > 1 && c.splitk <= 8 && g_cluster && !prog_recording()) ? 1 : 0;
+    if (c.splitk > 1 && !q.cluster) {
         size_t ws, ctr;
         ws_sizes(p, c, &ws, &ctr);
         MSTK_REQUIRE(workspace != nullptr && workspace_bytes >= ws + ctr,
@@ -389,11 +397,20 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     cfg.blockDim = dim3(TC_THREADS, 1, 1);
     cfg.dynamicSmemBytes = c.smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int nattr = 0;
+    if (g_pdl) {
+        attr[nattr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[nattr].val.programmaticStreamSerializationAllowed = 1;
+        ++nattr;
+    }
+    if (q.cluster) {
+        attr[nattr].id = cudaLaunchAttributeClusterDimension;
+        attr[nattr].val.clusterDim.x = 1; attr[nattr].val.clusterDim.y = 1; attr[nattr].val.clusterDim.z = (unsigned)c.splitk;
+        ++nattr;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = g_pdl ? 1 : 0;
+    cfg.numAttrs = nattr;
     uint32_t need = 0;
     if (c.splitk > 1) need |= F_SPLITK;
     if (p.stats) need |= F_STATS;

@@ -111,6 +111,25 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t a, uint32_t parity) {
 __device__ __forceinline__ void umma_commit_addr(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// Thread-block clusters (split-K partners of one output tile reduce through distributed shared memory).
+// barrier.cluster counts EVERY non-exited thread of every CTA of the cluster, warp-converged (.aligned).
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_map(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ float4 ld_cluster_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_cluster_f4(uint32_t addr, float4 v) {
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 // One lane of a CONVERGED warp (elect.sync).  The compiler treats the guarded region as single-threaded and uniform,
 // so tcgen05.mma / tcgen05.commit inside it compile to bare UTCHMMA / UTCBAR; under an ordinary `lane == 0` branch
 // each of them is wrapped in an ELECT + BRA.U.ANY serialisation loop fed by R2UR moves (cuobjdump), which made the

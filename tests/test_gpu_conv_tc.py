@@ -105,3 +105,15 @@ def test_conv_tcgen05_ddim():
     assert_close(nchw(y), eps, 1e-5, "eps")
     assert_close(nchw(xc), xn_ref, 1e-5, "x_next")
     assert_close(nchw(xlp), xn_ref, 5e-3, "x_next bf16")
+
+
+def test_conv_tcgen05_cluster_splitk():
+    """opt-in MSTK_TC_CLUSTER=1 path (split-K partners reduce through distributed shared memory): the environment is
+    read once per process, so the split-K cases run in a child interpreter"""
+    import os, subprocess, sys
+    env = dict(os.environ, MSTK_TC_CLUSTER="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_conv_tc.py"), "-q", "-x",
+                        "-k", "2x4x4x256x512 or 2x2x2x512x512 or 2x2x2x512x256 or 65x2x2 or epilogue or ddim"],
+                       env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -1,3 +1,7 @@
 mkdir -p gpurun_out
-{ echo "# tools/tc_timeline.py: clock64 stamps of CTA (0,0,0), cycles since kernel entry: [setup done, first TMA issued, first stage landed, last stage landed, accumulator ready, epilogue done, TMEM freed]"; echo "## UNet layers, batch 64"; timeout 300 python tools/tc_timeline.py 2>&1 | grep -v Warning; echo "## VGGish layers, 768 images"; TCVGG=1 timeout 300 python tools/tc_timeline.py 2>&1 | grep -v Warning; } > gpurun_out/tc_timeline_r1d.txt
-cat gpurun_out/tc_timeline_r1d.txt | cut -c 1-230
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout 600 python bench.py --no-cpu-baseline --no-train > gpurun_out/bench_adhoc.json 2> gpurun_out/bench_adhoc.err; python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_adhoc.json').read().strip().splitlines()[-1])
+print('sampling', d['value'], 'e2e', d['e2e']['value'], 'roof', d['roofline']['frac'])
+PY
