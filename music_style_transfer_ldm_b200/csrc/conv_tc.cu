@@ -73,6 +73,7 @@ static int g_force_group = 0, g_trace = 0;
 // steps/s): a cluster needs 4-8 free SMs of one GPC at once, which stalls the programmatic-dependent-launch overlap
 // of consecutive layers.  Off by default.
 static int g_cluster = 0;
+static double g_split_cost = 1800.0;   // cost-model cycles charged to a split-K tile (MSTK_TC_SPLIT_COST)
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
 void tc_set_debug(long long* p) { g_dbg = p; }
@@ -103,6 +104,7 @@ bool tc_init() {
     // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
     if (const char* s = getenv("MSTK_TC_TRACE")) g_trace = atoi(s);
     if (const char* s = getenv("MSTK_TC_CLUSTER")) g_cluster = atoi(s);
+    if (const char* s = getenv("MSTK_TC_SPLIT_COST")) g_split_cost = atof(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
     for (int i = 0; i < kNumVariants; ++i) {
@@ -229,7 +231,7 @@ static TcConfig choose_config(const ConvP& p) {
                 double t_k = t_load > t_mma ? t_load : t_mma;
                 if (t_issue > t_k) t_k = t_issue;
                 t_k += 600.0 + (t.stages * grp < kb_cta ? 0.0 : 0.0);
-                const double t_epi = 500.0 + bn * 14.0 + (sk > 1 ? 1800.0 + bn * 10.0 : 0.0);
+                const double t_epi = 500.0 + bn * 14.0 + (sk > 1 ? g_split_cost + bn * 10.0 : 0.0);
                 const double cost = waves * (t_k + t_epi) + 1200.0;
                 if (cost < best) { best = cost; best_bn = bn; best_sk = sk; best_st = t.stages; best_grp = grp; }
             }
