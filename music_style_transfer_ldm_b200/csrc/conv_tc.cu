@@ -73,6 +73,7 @@ static int g_force_group = 0, g_trace = 0;
 // steps/s): a cluster needs 4-8 free SMs of one GPC at once, which stalls the programmatic-dependent-launch overlap
 // of consecutive layers.  Off by default.
 static int g_cluster = 0;
+static int g_direct = 0;      // MSTK_TC_DIRECT=1: register -> global output stores instead of staging + TMA store
 static double g_split_cost = 1800.0;   // cost-model cycles charged to a split-K tile (MSTK_TC_SPLIT_COST)
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
 static long long* g_dbg = nullptr;
@@ -104,6 +105,7 @@ bool tc_init() {
     // MSTK_TC_FORCE="BN,splitk,stages" overrides the tile heuristic (0 = keep heuristic value)
     if (const char* s = getenv("MSTK_TC_TRACE")) g_trace = atoi(s);
     if (const char* s = getenv("MSTK_TC_CLUSTER")) g_cluster = atoi(s);
+    if (const char* s = getenv("MSTK_TC_DIRECT")) g_direct = atoi(s);
     if (const char* s = getenv("MSTK_TC_SPLIT_COST")) g_split_cost = atof(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
@@ -335,6 +337,7 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     q.out_esz = c.out_esz; q.out_rowbytes = c.out_rowbytes; q.out_chunks = c.out_chunks;
     q.add_rowbytes = c.add_rowbytes; q.add_chunks = c.add_chunks;
     q.use_tma_store = p.y ? 1 : 0;
+    q.direct_store = g_direct;
     q.use_tma_add = p.add ? 1 : 0;
     if (g_trace)
         fprintf(stderr, "[mstk conv_tc] N%d %dx%d Cin%d Cout%d k%d: BN %d KC %d splitk %d stages %d kgroup %d smem %zu\n", p.N, p.H, p.W, p.Cin,

@@ -42,6 +42,7 @@ struct TcParams {
     // and shifts for the power-of-two tile box and split-K factor; filled by launch_conv_tc
     uint32_t inv_tiles_w, inv_tiles_h, inv_tiles_wh, inv_kb_per_tap, inv_kgroup;
     int32_t wt_shift, ht_shift, splitk_shift;
+    int32_t direct_store;          // epilogue writes y from registers instead of staging + TMA store
     int32_t cluster;               // split-K partners are one thread-block cluster (1,1,splitk): reduce through DSMEM, no scratch
     float* ws;                     // split-K workspace
     unsigned int* counters;        // split-K tile counters
@@ -460,6 +461,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
             uint8_t* const out_stage = smem + q.off_out;
             const uint8_t* const add_stage = smem + q.off_add;
             const int act = p.act;
+            const bool direct = q.direct_store != 0;
             float vnext[16];
             if (!f_split && cbeg < cend) tmem_ld16_issue(taddr + (uint32_t)cbeg, vnext);
             for (int c = cbeg; c < cend; c += 16) {
@@ -570,7 +572,24 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                         lo[0] = pk[0]; lo[1] = pk[1];
                     }
                 }
-                if (f_store) {
+                if (f_store && direct) {
+                    // straight from registers: 32 (bf16) / 64 (fp32) contiguous bytes per row and chunk, whole sectors;
+                    // nothing to stage, no bulk store to wait for at the end of the CTA
+                    if (row_ok) {
+                        if (out_esz == 4) {
+                            float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.y) + pix_off + c);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) o4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        } else {
+                            uint4 pk[2];
+                            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+                            uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.y) + pix_off + c);
+                            o4[0] = pk[0]; o4[1] = pk[1];
+                        }
+                    }
+                } else if (f_store) {
                     uint8_t* ob = out_stage + (size_t)(c >> out_sh) * TILE_M * out_rowbytes;
                     const int j0 = ((c & (out_cpr - 1)) * out_esz) >> 4;
                     if (out_esz == 4) {
@@ -601,7 +620,7 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
                     atomicAdd(p.stats + p.Cout + co0 + et, (double)sstat[BN + et]);
                 }
             }
-            if (f_store) {
+            if (f_store && !direct) {
                 fence_async_smem();
                 epi_bar();
                 if (et == 0) {
