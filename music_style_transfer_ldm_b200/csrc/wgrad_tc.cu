@@ -363,7 +363,8 @@ int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, c
     const int tiles_n = (p.N + q.Nt - 1) / q.Nt;
     q.ptiles = q.tiles_w * q.tiles_h * tiles_n;
     const long long base = (long long)q.ngroups * q.m_tiles * q.n_tiles;
-    long long ks = (2LL * tc_num_sms() + base - 1) / base;
+    // one CTA per SM (the stages take ~200 KB): aim at two FULL waves, never a third one holding a handful of CTAs
+    long long ks = (2LL * tc_num_sms()) / base;
     const long long ks_max = (q.ptiles + 3) / 4;          // at least ~4 k-blocks per CTA
     if (ks > ks_max) ks = ks_max;
     if (ks < 1) ks = 1;
