@@ -24,7 +24,12 @@ Data parallelism (one process per GPU): pass ``process_group`` / ``world_size``.
 the gradient arena is all-reduced in buckets (NCCL, side stream) as soon as the backward sweep has
 finished the layers of a bucket, and the BatchNorm forward/backward statistics are all-reduced so every
 rank normalises with the GLOBAL batch statistics (single-process parity).
-Epoch bookkeeping, plotting, tqdm and checkpoint writing (train.py:210-293) are outside the hot path.
+        .train_epoch(epoch) -> (avg total, avg compression, avg denoising, avg style)   train.py:209-243
+        .train(num_epochs)                                                         train.py:245-293
+The epoch loop keeps the reference's contract (loader element layout, the ``training_iteration_noise``
+factor in the averages, ReduceLROnPlateau(factor 0.5, patience 10) on the epoch loss, a checkpoint every
+100 epochs) but accumulates the losses on the device -- one host read per epoch instead of one per step.
+Plotting (matplotlib) and tqdm are outside the hot path.
 """
 from __future__ import annotations
 
@@ -34,6 +39,7 @@ import torch
 import torch.nn as nn
 
 from . import loss as L
+from .config import config
 from . import model as Mo
 from . import ops
 from .ops import ACT_NONE, ACT_RELU, ACT_TANH, MstkError
@@ -132,6 +138,33 @@ def bucket_spans(model, arena: "_Arena", num_buckets: int = 3):
     return merged
 
 
+class PlateauScheduler:
+    """torch.optim.lr_scheduler.ReduceLROnPlateau(mode='min', threshold=1e-4 'rel', cooldown=0, eps=1e-8) restated on a
+    plain ``.lr`` attribute (the trainers here own a flat arena and one fused Adam launch, not a torch optimizer):
+    train.py:159-161 (factor 0.5, patience 10, min_lr 0) and train.py:48 (config-driven, min_lr 1e-6)."""
+
+    def __init__(self, owner, mode_factor: float = 0.5, patience: int = 10, min_lr: float = 0.0, threshold: float = 1e-4,
+                 eps: float = 1e-8):
+        if mode_factor >= 1.0:
+            raise ValueError("Factor should be < 1.0.")
+        self.owner, self.factor, self.patience, self.min_lr = owner, float(mode_factor), int(patience), float(min_lr)
+        self.threshold, self.eps = float(threshold), float(eps)
+        self.best, self.num_bad_epochs, self.last_epoch = float("inf"), 0, 0
+
+    def step(self, metric) -> None:
+        current = float(metric)
+        self.last_epoch += 1
+        if current < self.best * (1.0 - self.threshold):
+            self.best, self.num_bad_epochs = current, 0
+        else:
+            self.num_bad_epochs += 1
+        if self.num_bad_epochs > self.patience:
+            new_lr = max(self.owner.lr * self.factor, self.min_lr)
+            if self.owner.lr - new_lr > self.eps:
+                self.owner.lr = new_lr
+            self.num_bad_epochs = 0
+
+
 class LDMTrainer:
     def __init__(self, model, train_loader, device, lr=1e-4, style_loss_weight=0.1, process_group=None, world_size: int = 1,
                  num_buckets: int = 3):
@@ -139,7 +172,9 @@ class LDMTrainer:
         self.train_loader = train_loader
         self.device = torch.device(device)
         self.style_loss_weight = style_loss_weight
-        self.lr = float(lr)
+        self._lr = float(lr)
+        self.scheduler = PlateauScheduler(self, mode_factor=0.5, patience=10)      # train.py:159-161
+        self.checkpoint_dir = "models/pretrained"                                # train.py:266
         self.betas, self.eps = (0.9, 0.999), 1e-8          # torch.optim.Adam defaults (train.py:156)
         self.step_count = 0
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=device)
@@ -172,7 +207,53 @@ class LDMTrainer:
                 if b.dtype.is_floating_point:
                     dist.broadcast(b, src=0, group=self.group)
 
+    @property
+    def lr(self) -> float:
+        return self._lr
+
+    @lr.setter
+    def lr(self, value: float) -> None:
+        """the learning rate is a launch parameter of the Adam kernel: a captured step is re-captured when it changes"""
+        if float(value) != self._lr:
+            self._lr = float(value)
+            if self._graph is not None:
+                self._graph = None
+                self._eager_steps = self.graph_warmup
+
     # -- reference API ----------------------------------------------------------------------
+    def train_epoch(self, epoch):
+        """train.py:209-243: one pass over ``train_loader`` whose elements are ((content, label), (style, label));
+        returns the four epoch averages (total, compression, denoising, style), each multiplied by
+        config['training_iteration_noise'] as the reference does.  Losses are summed on the device."""
+        self.model.train()
+        num_batches = len(self.train_loader)
+        acc = torch.zeros(4, dtype=torch.float64, device=self.device)
+        for element in self.train_loader:
+            (content_spec, _), (style_spec, _) = element
+            out = self.train_step_device(content_spec.to(self.device, non_blocking=True), style_spec.to(self.device, non_blocking=True))
+            acc += torch.stack([out["total_loss"], out["compression_loss"], out["denoisinsg_loss"], out["style_loss"]]).double()
+        k = config["training_iteration_noise"]
+        return tuple(v / num_batches * k for v in acc.tolist())                  # ONE host sync per epoch
+
+    def train(self, num_epochs):
+        """train.py:245-293 without the matplotlib plots: epochs, ReduceLROnPlateau on the epoch's total loss,
+        a state_dict checkpoint every 100 epochs into ``self.checkpoint_dir`` (reference: models/pretrained/;
+        None skips the write).  Returns the per-epoch (total, compression, denoising, style) history."""
+        history = []
+        for epoch in range(num_epochs):
+            losses = self.train_epoch(epoch)
+            print(f"Epoch {epoch}: Train Loss = {losses[0]:.4f}")
+            self.scheduler.step(losses[0])
+            history.append(losses)
+            print(f"Compression Loss: {losses[1]:.4f}")
+            print(f"Denoisinsg Loss: {losses[2]:.4f}")
+            print(f"Style Loss: {losses[3]:.4f}")
+            if epoch % 100 == 0 and self.checkpoint_dir is not None:
+                import os
+                os.makedirs(self.checkpoint_dir, exist_ok=True)
+                torch.save(self.model.state_dict(), os.path.join(self.checkpoint_dir, f"ldm_{epoch}.pth"))
+        return history
+
     def train_step(self, content_spec, style_spec):
         out = self.train_step_device(content_spec, style_spec)
         vals = torch.stack([out[k] for k in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]).tolist()   # ONE host sync

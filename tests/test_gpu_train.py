@@ -115,3 +115,35 @@ def test_graph_replayed_step_matches_eager(sd):
         curves[mode] = np.asarray(rows)
     assert np.isfinite(curves["graph"]).all()
     np.testing.assert_allclose(curves["graph"], curves["eager"], rtol=2e-2, err_msg="graph-replayed steps vs eager steps")
+
+
+def test_train_epoch_and_train_follow_reference_contract(sd, tmp_path, capsys):
+    """train.py:209-293: loader elements ((content, label), (style, label)); epoch averages x training_iteration_noise;
+    the device-side accumulation equals a loop of train_step; ReduceLROnPlateau halves lr and the captured step follows."""
+    from music_style_transfer_ldm_b200.config import config
+    g = torch.Generator().manual_seed(5)
+    loader = [((torch.rand((4, 1, 128, 128), generator=g), torch.zeros(4)), (torch.rand((4, 1, 128, 128), generator=g), torch.ones(4)))
+              for _ in range(4)]
+    m1, tr1 = _trainer(sd, "fp32", 1e-4, 3.0)
+    tr1.train_loader = loader
+    torch.manual_seed(11); torch.cuda.manual_seed(11)
+    avg = tr1.train_epoch(0)
+    m2, tr2 = _trainer(sd, "fp32", 1e-4, 3.0)
+    torch.manual_seed(11); torch.cuda.manual_seed(11)
+    tot = np.zeros(4)
+    for (c, _), (s, _) in loader:
+        out = tr2.train_step(c.to(DEV), s.to(DEV))
+        tot += [out["total_loss"], out["compression_loss"], out["denoisinsg_loss"], out["style_loss"]]
+    np.testing.assert_allclose(avg, tot / len(loader) * config["training_iteration_noise"], rtol=1e-4)   # split-K / atomic summation order
+    assert tr1.step_count == 4 and tr1._graph is not None                  # steps 3-4 were graph replays
+    # train(): scheduler + checkpoint; force a plateau so the learning rate is halved and the graph re-captured
+    tr1.checkpoint_dir = str(tmp_path)
+    tr1.scheduler.patience = 0
+    tr1.scheduler.best = -1.0
+    hist = tr1.train(2)
+    assert len(hist) == 2 and all(len(h) == 4 and np.isfinite(h).all() for h in hist)
+    assert tr1.lr == pytest.approx(1e-4 * 0.25)
+    assert (tmp_path / "ldm_0.pth").is_file()
+    back = torch.load(tmp_path / "ldm_0.pth", map_location="cpu")
+    assert set(back) == set(sd)
+    assert "Epoch 1: Train Loss" in capsys.readouterr().out
