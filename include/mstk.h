@@ -356,6 +356,13 @@ int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, f
  * step can be replayed (the caller increments *step_dev on the stream before this call). */
 int mstk_adam_step_dev(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
                        const int64_t* step_dev, float grad_scale, void* stream);
+/* torch.optim.AdamW (decoupled weight decay: p *= 1 - lr*weight_decay before the Adam update), the optimizer of the
+ * reference's autoencoder stage (models/train.py:47, default weight_decay 0.01); step count in device memory. */
+int mstk_adamw_step_dev(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
+                        float weight_decay, const int64_t* step_dev, float grad_scale, void* stream);
+/* g = dz (optional, dz_dtype) + scale * (z - z/(z^2 + 1e-8)): gradient of scale*count * kl_regularization_loss(z)
+ * (models/loss.py:31-32) added to the gradient arriving from the decoder; z and g fp32 */
+int mstk_kl_grad(const float* z, const void* dz, int dz_dtype, float scale, float* g, size_t count, void* stream);
 
 #ifdef __cplusplus
 }

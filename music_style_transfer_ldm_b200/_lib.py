@@ -132,6 +132,8 @@ SIGNATURES = {
     "mstk_mse_grad": (c_int, [c_void_p, c_void_p, c_float, c_void_p, c_int, c_size_t, c_void_p]),
     "mstk_eps_grad": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int64, c_void_p]),
     "mstk_adam_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_void_p, c_float, c_void_p]),
+    "mstk_adamw_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_float, c_void_p, c_float, c_void_p]),
+    "mstk_kl_grad": (c_int, [c_void_p, c_void_p, c_int, c_float, c_void_p, c_size_t, c_void_p]),
     "mstk_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p]),
     "mstk_mel_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),

@@ -641,6 +641,16 @@ __global__ void mse_grad_kernel(const float* __restrict__ a, const float* __rest
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x)
         store_from_f(g, g_dtype, i, scale * (a[i] - b[i]));
 }
+// d/dz of w * mean(0.5 (z^2 - 1 - log(z^2 + 1e-8)))  (loss.py:31-32) = scale * (z - z / (z^2 + 1e-8)), scale = w / count;
+// added to the gradient arriving from the decoder (optional)
+__global__ void kl_grad_kernel(const float* __restrict__ z, const void* __restrict__ dz, int dz_dtype, float scale, float* __restrict__ g,
+                               size_t count) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        const float zz = z[i];
+        const float k = scale * (zz - zz / (zz * zz + 1e-8f));
+        g[i] = dz ? load_as_f(dz, dz_dtype, i) + k : k;
+    }
+}
 __global__ void eps_grad_kernel(const void* __restrict__ dx0, int dx0_dtype, const float* __restrict__ eh, const float* __restrict__ eps,
                                 const float* __restrict__ ab, const long long* __restrict__ t, float scale_d, void* g, int g_dtype,
                                 long long inner, size_t total) {
@@ -654,7 +664,7 @@ __global__ void eps_grad_kernel(const void* __restrict__ dx0, int dx0_dtype, con
 // denom = sqrt(v)/sqrt(bc2) + eps; p -= (lr/bc1) * m/denom
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                                                    size_t count, float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt, float gs,
-                                                   const long long* __restrict__ step_dev) {
+                                                   const long long* __restrict__ step_dev, float decay) {
     if (step_dev) {
         // step counter in device memory (CUDA-graph replays): bias corrections computed here, in double as on the host
         const double s = (double)step_dev[0];
@@ -673,7 +683,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
             me[k] = me[k] + (gr - me[k]) * (1.f - b1);
             ve[k] = ve[k] * b2 + (1.f - b2) * gr * gr;
             const float denom = sqrtf(ve[k]) / bc2_sqrt + eps;
-            pe[k] = pe[k] - (lr / bc1) * (me[k] / denom);
+            pe[k] = pe[k] * decay - (lr / bc1) * (me[k] / denom);
         }
         reinterpret_cast<float4*>(p)[i] = pp; reinterpret_cast<float4*>(m)[i] = mm; reinterpret_cast<float4*>(v)[i] = vv;
     }
@@ -682,7 +692,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
         const float mn = m[i] + (gr - m[i]) * (1.f - b1);
         const float vn = v[i] * b2 + (1.f - b2) * gr * gr;
         m[i] = mn; v[i] = vn;
-        p[i] = p[i] - (lr / bc1) * (mn / (sqrtf(vn) / bc2_sqrt + eps));
+        p[i] = p[i] * decay - (lr / bc1) * (mn / (sqrtf(vn) / bc2_sqrt + eps));
     }
 }
 // dst [k*k][cin][cout] = w[cout][cin][k-1-ky][k-1-kx]
@@ -994,7 +1004,7 @@ int mstk_adam_step(float* p, const float* g, float* m, float* v, size_t count, f
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
     adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, (float)bc1,
-                                                                               (float)sqrt(bc2), grad_scale, nullptr);
+                                                                               (float)sqrt(bc2), grad_scale, nullptr, 1.f);
     MSTK_CHECK_LAUNCH("adam");
     return MSTK_OK;
 }
@@ -1005,8 +1015,27 @@ int mstk_adam_step_dev(float* p, const float* g, float* m, float* v, size_t coun
     MSTK_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
                  "adam: arenas must be 16-byte aligned");
     adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, 1.f, 1.f, grad_scale,
-                                                                               reinterpret_cast<const long long*>(step_dev));
+                                                                               reinterpret_cast<const long long*>(step_dev), 1.f);
     MSTK_CHECK_LAUNCH("adam");
+    return MSTK_OK;
+}
+
+int mstk_adamw_step_dev(float* p, const float* g, float* m, float* v, size_t count, float lr, float beta1, float beta2, float eps,
+                        float weight_decay, const int64_t* step_dev, float grad_scale, void* stream) {
+    MSTK_REQUIRE(p && g && m && v && count > 0 && step_dev && weight_decay >= 0.f, "adamw: bad args");
+    MSTK_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+                 "adamw: arenas must be 16-byte aligned");
+    adam_kernel<<<bw_grid(count / 4 + 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, beta1, beta2, eps, 1.f, 1.f, grad_scale,
+                                                                               reinterpret_cast<const long long*>(step_dev),
+                                                                               1.f - lr * weight_decay);
+    MSTK_CHECK_LAUNCH("adamw");
+    return MSTK_OK;
+}
+
+int mstk_kl_grad(const float* z, const void* dz, int dz_dtype, float scale, float* g, size_t count, void* stream) {
+    MSTK_REQUIRE(z && g && count > 0, "kl_grad: bad args");
+    kl_grad_kernel<<<bw_grid(count, 256), 256, 0, (cudaStream_t)stream>>>(z, dz, dz_dtype, scale, g, count);
+    MSTK_CHECK_LAUNCH("kl_grad");
     return MSTK_OK;
 }
 

@@ -600,9 +600,30 @@ def eps_grad(dx0: torch.Tensor, eps_hat, eps, alpha_bar, t, scale_d: float, g_dt
     return g
 
 
-def adam_step(p, g, m, v, *, lr: float, beta1: float, beta2: float, eps: float, step, grad_scale: float = 1.0) -> None:
-    """``step``: python int, or a 1-element int64 CUDA tensor holding the step count (graph-replayable)."""
+def kl_grad(z: torch.Tensor, dz: Optional[torch.Tensor], scale: float) -> torch.Tensor:
+    """fp32 g = dz + scale * (z - z/(z^2 + 1e-8)); scale = weight / z.numel() for weight * kl_regularization_loss(z)"""
     lib = _lib.load()
+    _dev(z, "kl_grad.z")
+    if z.dtype != torch.float32 or (dz is not None and dz.shape != z.shape):
+        raise MstkError("kl_grad: z must be fp32 and dz must match it")
+    g = torch.empty_like(z)
+    check(lib.mstk_kl_grad(_p(z), _p(dz), dtype_code(dz) if dz is not None else 0, scale, _p(g), z.numel(), _stream()), "mstk_kl_grad")
+    _count()
+    return g
+
+
+def adam_step(p, g, m, v, *, lr: float, beta1: float, beta2: float, eps: float, step, grad_scale: float = 1.0,
+              weight_decay: Optional[float] = None) -> None:
+    """``step``: python int, or a 1-element int64 CUDA tensor holding the step count (graph-replayable).
+    ``weight_decay`` not None selects torch.optim.AdamW's decoupled decay (device step counter only)."""
+    lib = _lib.load()
+    if weight_decay is not None:
+        if not isinstance(step, torch.Tensor) or step.dtype != torch.int64 or not step.is_cuda:
+            raise MstkError("adam_step: AdamW needs an int64 CUDA step counter")
+        check(lib.mstk_adamw_step_dev(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, weight_decay, _p(step), grad_scale,
+                                      _stream()), "mstk_adamw_step_dev")
+        _count()
+        return
     if isinstance(step, torch.Tensor):
         if step.dtype != torch.int64 or not step.is_cuda:
             raise MstkError("adam_step: a device step counter must be an int64 CUDA tensor")

@@ -511,3 +511,176 @@ class LDMTrainer:
             self.reducer.all_reduce_small(losses)
             losses = losses / self.world
         return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), losses.unbind(0)))
+
+
+# =====================================================================================================
+# Autoencoder stage: models/train.py:28-138
+# =====================================================================================================
+def _conv_bn_train(mod, name, conv, bn, x, *, transposed: bool, ksize: int, act: int, mid_dtype, out_dtype, first: bool = False):
+    """conv / convT (stride 2) with the batch sums in its epilogue, then the normalise(+ReLU) pass; keeps what the
+    backward sweep needs: the pre-BatchNorm map v and the batch mean / inverse std."""
+    c = bn.num_features
+    stats = torch.zeros(2 * c, dtype=torch.float64, device=x.device)
+    wp = mod._packed(name, conv.weight, torch.float32 if first else x.dtype, transposed)
+    v = ops.conv(x, wp, mod._f32(name + ".b", conv.bias), ksize=ksize, stride=2, transposed=transposed, act=ACT_NONE, stats=stats,
+                 out_dtype=mid_dtype)
+    mean, invstd = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+    h = ops.bn_apply(v, stats, bn.weight.detach(), bn.bias.detach(), count=v.numel() // c, eps=bn.eps,
+                     momentum=bn.momentum if bn.momentum is not None else 0.1, act=act, out_dtype=out_dtype,
+                     running_mean=bn.running_mean, running_var=bn.running_var, save_mean=mean, save_invstd=invstd)
+    bn.num_batches_tracked.add_(1)
+    return v, h, mean, invstd
+
+
+class AutoencoderTrainer:
+    """One optimisation step of the reference's autoencoder stage (train.py:47, 68-83) on libmstk kernels:
+    latent = encoder(x); recon = decoder(latent) (tanh range, NOT rescaled -- train.py:71-75 compares it with the
+    spectrogram directly); loss = compression_loss(x, recon, latent, feature_extractor); AdamW over encoder + decoder.
+
+    Gradient reaches the parameters through MSE(recon, x) and through 0.01 * KL(latent) (encoder only); the feature
+    stack of the perceptual term runs under torch.no_grad() in the reference (loss.py:78) and is forward-only here.
+    Forward, backward and update are an explicit stream of C-ABI launches, as in LDMTrainer.  Single process."""
+
+    def __init__(self, encoder, decoder, feature_extractor, device, lr=5e-4, weight_decay=1e-2):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise MstkError("AutoencoderTrainer: the training step runs on sm_100a kernels only (no CPU fallback)")
+        self.encoder, self.decoder = encoder.to(device), decoder.to(device)
+        self.feature_extractor = feature_extractor.to(device) if feature_extractor is not None else None
+        self.lr, self.weight_decay = float(lr), float(weight_decay)        # torch.optim.AdamW defaults (train.py:47)
+        self.betas, self.eps = (0.9, 0.999), 1e-8
+        self.step_count = 0
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=device)
+        e, d = self.encoder.encoder, self.decoder.decoder
+        # backward-completion order: decoder top-down, then the encoder top-down
+        order = [d[6].weight, d[6].bias, d[4].weight, d[4].bias, d[3].weight, d[3].bias, d[1].weight, d[1].bias, d[0].weight, d[0].bias,
+                 e[7].weight, e[7].bias, e[6].weight, e[6].bias, e[4].weight, e[4].bias, e[3].weight, e[3].bias, e[1].weight, e[1].bias,
+                 e[0].weight, e[0].bias]
+        if not all(p.requires_grad for p in order):
+            raise MstkError("AutoencoderTrainer: every encoder / decoder parameter must require grad (train.py:47)")
+        self.arena = _Arena(order, self.device)
+        for m in list(self.encoder.modules()) + list(self.decoder.modules()):
+            m.__dict__.pop("_mstk_cache", None)
+
+    def train_step(self, spectrogram) -> float:
+        return float(self.train_step_device(spectrogram))
+
+    def train_step_device(self, spectrogram) -> torch.Tensor:
+        enc, dec = self.encoder, self.decoder
+        e, d = enc.encoder, dec.decoder
+        if not (e[1].training and d[1].training):
+            raise MstkError("AutoencoderTrainer: call encoder.train() and decoder.train() first (train.py:60-61)")
+        Mo._need_cuda(spectrogram, "AutoencoderTrainer")
+        x = spectrogram.detach().float().contiguous()
+        if x.dim() != 4 or x.shape[1] != 1 or x.shape[2] % 8 or x.shape[3] % 8:
+            raise MstkError(f"AutoencoderTrainer: expected a [B,1,H,W] spectrogram with H, W multiples of 8, got {tuple(x.shape)}")
+        B, _, H, W = x.shape
+        xs = x.view(B, H, W, 1)
+        adt = Mo._act_dtype(enc._precision())
+        self.arena.g.zero_()                                                     # optimizer.zero_grad()
+
+        # ---- forward (model.py:16-28, 37-49), intermediates kept ----
+        v0, h0, m0, i0 = _conv_bn_train(enc, "c0", e[0], e[1], xs, transposed=False, ksize=3, act=ACT_RELU, mid_dtype=adt, out_dtype=adt, first=True)
+        v1, h1, m1, i1 = _conv_bn_train(enc, "c3", e[3], e[4], h0, transposed=False, ksize=3, act=ACT_RELU, mid_dtype=adt, out_dtype=adt)
+        v2, z, m2, i2 = _conv_bn_train(enc, "c6", e[6], e[7], h1, transposed=False, ksize=3, act=ACT_NONE, mid_dtype=torch.float32,
+                                       out_dtype=torch.float32)
+        dec_in = z if adt == torch.float32 else ops.cast(z, adt)
+        u1, g1, n1, j1 = _conv_bn_train(dec, "d0", d[0], d[1], dec_in, transposed=True, ksize=4, act=ACT_RELU, mid_dtype=adt, out_dtype=adt)
+        u2, g2, n2, j2 = _conv_bn_train(dec, "d3", d[3], d[4], g1, transposed=True, ksize=4, act=ACT_RELU, mid_dtype=adt, out_dtype=adt)
+        rec = ops.conv(g2, dec._packed("d6", d[6].weight, adt, True), dec._f32("d6.b", d[6].bias), ksize=4, stride=2, transposed=True,
+                       act=ACT_TANH, out_dtype=torch.float32)
+
+        # ---- compression_loss (loss.py:34-45) ----
+        loss = ops.mse(rec, xs).squeeze(0) + 0.01 * ops.kl(z).squeeze(0)
+        if self.feature_extractor is not None:
+            loss = loss + 0.1 * L.perceptual_loss(x, rec.view(B, 1, H, W), config["compression_feature_extractor"],
+                                                  feature_extractor=self.feature_extractor)
+
+        # ---- backward: decoder ----
+        g_rec = ops.mse_grad(rec, xs, 2.0 / rec.numel(), torch.float32)
+        g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=d[6].bias.grad)
+        ops.wgrad(g2, g6, d[6].weight.grad, ksize=4, stride=2, transposed=True)
+        w6 = dec._cached(("d6", "dg32"), (d[6].weight,), lambda: ops.pack_weight(d[6].weight, torch.float32))
+        dg2 = ops.conv(g6, w6, None, ksize=4, stride=2, out_dtype=adt)
+        du2 = ops.bn_bwd(dg2, u2, n2, j2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=d[4].weight.grad, dbeta=d[4].bias.grad)
+        ops.act_bwd(du2, None, act=ACT_NONE, dbias=d[3].bias.grad, want_g=False)
+        ops.wgrad(g1, du2, d[3].weight.grad, ksize=4, stride=2, transposed=True)
+        dg1 = LDMTrainer._dgrad(dec, "d3", d[3], du2)
+        du1 = ops.bn_bwd(dg1, u1, n1, j1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=d[1].weight.grad, dbeta=d[1].bias.grad)
+        ops.act_bwd(du1, None, act=ACT_NONE, dbias=d[0].bias.grad, want_g=False)
+        ops.wgrad(dec_in, du1, d[0].weight.grad, ksize=4, stride=2, transposed=True)
+        dz = LDMTrainer._dgrad(dec, "d0", d[0], du1)
+        # ---- backward: encoder; the latent also carries 0.01 * KL ----
+        gz = ops.kl_grad(z, dz, 0.01 / z.numel())
+        dv2 = ops.bn_bwd(gz, v2, m2, i2, e[7].weight.detach(), e[7].bias.detach(), act=ACT_NONE, dgamma=e[7].weight.grad, dbeta=e[7].bias.grad,
+                         dv_dtype=adt)
+        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=e[6].bias.grad, want_g=False)
+        ops.wgrad(h1, dv2, e[6].weight.grad, ksize=3, stride=2)
+        dh1 = LDMTrainer._dgrad(enc, "c6", e[6], dv2)
+        dv1 = ops.bn_bwd(dh1, v1, m1, i1, e[4].weight.detach(), e[4].bias.detach(), act=ACT_RELU, dgamma=e[4].weight.grad, dbeta=e[4].bias.grad)
+        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=e[3].bias.grad, want_g=False)
+        ops.wgrad(h0, dv1, e[3].weight.grad, ksize=3, stride=2)
+        dh0 = LDMTrainer._dgrad(enc, "c3", e[3], dv1)
+        dv0 = ops.bn_bwd(dh0, v0, m0, i0, e[1].weight.detach(), e[1].bias.detach(), act=ACT_RELU, dgamma=e[1].weight.grad, dbeta=e[1].bias.grad)
+        ops.act_bwd(dv0, None, act=ACT_NONE, dbias=e[0].bias.grad, want_g=False)
+        ops.wgrad(xs, dv0, e[0].weight.grad, ksize=3, stride=2)
+
+        # ---- update (torch.optim.AdamW, train.py:47, 81-83) ----
+        self.step_count += 1
+        self.step_dev.add_(1)
+        ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
+                      eps=self.eps, step=self.step_dev, weight_decay=self.weight_decay)
+        for m in list(enc.modules()) + list(dec.modules()):       # parameters changed under the packed copies
+            m.__dict__.pop("_mstk_cache", None)
+        return loss
+
+
+def train_autoencoder(config, train_loader=None, test_loader=None, checkpoint_dir="models/pretrained"):
+    """models/train.py:28-138 without dataset preparation and plotting: ``train_loader`` / ``test_loader`` yield
+    elements whose [0] is a [B,1,H,W] spectrogram batch (the reference builds them with prepare_dataset(config),
+    which is dataset I/O outside the path).  AdamW + ReduceLROnPlateau on the validation loss, best-validation and
+    final checkpoints of encoder.pth / decoder.pth.  Returns (encoder, decoder, train_losses, val_losses)."""
+    import os
+    if not torch.cuda.is_available():
+        raise RuntimeError("GPU not available, please check your setup.")           # train.py:32-36
+    if train_loader is None or test_loader is None:
+        raise MstkError("train_autoencoder: pass train_loader and test_loader (dataset preparation is outside the hot path)")
+    device = torch.device("cuda")
+    encoder = Mo.SpectrogramEncoder(config["latent_dim_encoder"]).to(device)
+    decoder = Mo.SpectrogramDecoder(config["latent_dim_encoder"]).to(device)
+    feature_extractor = L.VGGishFeatureLoss().to(device)
+    tr = AutoencoderTrainer(encoder, decoder, feature_extractor, device, lr=config["learning_rate"])
+    scheduler = PlateauScheduler(tr, mode_factor=config["learning_rate_factor"], patience=config["learning_rate_patience"],
+                                 min_lr=config["learning_rate_min"])
+
+    def save():
+        if checkpoint_dir is not None:
+            os.makedirs(checkpoint_dir, exist_ok=True)
+            torch.save(encoder.state_dict(), os.path.join(checkpoint_dir, "encoder.pth"))
+            torch.save(decoder.state_dict(), os.path.join(checkpoint_dir, "decoder.pth"))
+
+    train_losses, val_losses, best_val = [], [], float("inf")
+    for epoch in range(config["num_epochs"]):
+        encoder.train(); decoder.train()
+        acc = torch.zeros((), dtype=torch.float64, device=device)
+        for element in train_loader:
+            acc += tr.train_step_device(element[0].to(device, non_blocking=True)).double()
+        train_losses.append(float(acc) / len(train_loader))
+        encoder.eval(); decoder.eval()
+        acc = torch.zeros((), dtype=torch.float64, device=device)
+        with torch.no_grad():
+            for element in test_loader:
+                spec = element[0].to(device, non_blocking=True)
+                latent = encoder(spec)
+                acc += L.compression_loss(spec, decoder(latent), latent, feature_extractor).double()
+        val_losses.append(float(acc) / len(test_loader))
+        scheduler.step(val_losses[-1])
+        if val_losses[-1] < best_val:
+            best_val = val_losses[-1]
+            save()
+        print(f"Epoch: {epoch}")
+        print(f"Average Train Loss: {train_losses[-1]:.6f}")
+        print(f"Average Val Loss: {val_losses[-1]:.6f}")
+        print(f"Learning Rate: {tr.lr:.6f}")
+    save()
+    return encoder, decoder, train_losses, val_losses

@@ -60,3 +60,44 @@ class OracleTrainer:
 
     def state_dict(self) -> O.SD:
         return {k: v.detach().clone() for k, v in self.sd.items()}
+
+
+AE_PREFIXES = ("encoder.", "decoder.")
+
+
+class OracleAutoencoderTrainer:
+    """models/train.py:47, 68-83 (the autoencoder stage's loop body): latent = encoder(x); recon = decoder(latent)
+    (tanh range, not rescaled); loss = compression_loss(x, recon, latent, VGGish) (loss.py:34-45, 'vggish' branch);
+    torch.optim.AdamW over encoder + decoder parameters (default betas / eps / weight_decay 0.01).  Train-mode BatchNorm.
+
+    Parity: PINNED by tests/golden/ae_steps.npz (tests/golden/make_golden_ae.py drives the unmodified reference
+    SpectrogramEncoder / SpectrogramDecoder / compression_loss / VGGishFeatureLoss with the reference's optimizer):
+    losses of three steps and the step-0 gradients.  The KL term's -1/z gradient at BatchNorm outputs near zero makes the
+    encoder gradient ill-conditioned in the reference itself (see make_golden_ae.py), hence the looser encoder tolerances."""
+
+    def __init__(self, sd: O.SD, lr: float = 5e-4):
+        self.sd = {k: v.clone() for k, v in sd.items()}
+        self.keys = [k for k in self.sd if k.startswith(AE_PREFIXES)
+                     and not k.endswith(("running_mean", "running_var", "num_batches_tracked"))]
+        for k in self.keys:
+            self.sd[k].requires_grad_(True)
+        self.opt = torch.optim.AdamW([self.sd[k] for k in self.keys], lr=lr)
+
+    def train_step(self, x: torch.Tensor) -> float:
+        sd = self.sd
+        self.opt.zero_grad()
+        upd: O.SD = {}
+        z = O.encoder_fwd(sd, x.float(), True, update=upd)
+        rec = O.decoder_fwd(sd, z, True, update=upd)
+        with torch.no_grad():                      # loss.py:78
+            perc = O.vggish_feature_loss(sd, x, rec)
+        loss = torch.mean((rec - x) ** 2) + 0.1 * perc + 0.01 * O.kl_regularization_loss(z)
+        loss.backward()
+        self.opt.step()
+        with torch.no_grad():
+            for k, v in upd.items():
+                sd[k] = v.detach().clone() if isinstance(v, torch.Tensor) else v
+        return float(loss.detach())
+
+    def state_dict(self) -> O.SD:
+        return {k: v.detach().clone() for k, v in self.sd.items()}

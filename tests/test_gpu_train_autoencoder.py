@@ -1,0 +1,133 @@
+"""-m gpu: the autoencoder stage (models/train.py:28-138) on libmstk kernels.
+  * AutoencoderTrainer.train_step against tests/golden/ae_steps.npz (unmodified reference modules + AdamW): fp32 mode,
+    losses of 3 consecutive steps within 1e-4 relative, updated parameters against the oracle trainer;
+  * bf16 mode: 20-step loss curve within 1 % of the fp32 oracle;
+  * train_autoencoder(config, loaders): epoch loop, validation pass, scheduler, checkpoints.
+"""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import make_golden_ae as GA
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+# mathematically zero gradients: conv biases feeding a train-mode BatchNorm (see make_golden_ae.py)
+NOISE = ("encoder.encoder.0.bias", "encoder.encoder.3.bias", "encoder.encoder.6.bias", "decoder.decoder.0.bias", "decoder.decoder.3.bias",
+         "running_mean")
+
+
+def _sub(sd, prefix):
+    return {k[len(prefix):]: v.clone() for k, v in sd.items() if k.startswith(prefix)}
+
+
+def _trainer(sd, precision, lr):
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200.loss import VGGishFeatureLoss
+    from music_style_transfer_ldm_b200.train import AutoencoderTrainer
+    enc, dec, fl = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32), VGGishFeatureLoss()
+    enc.load_state_dict(_sub(sd, "encoder."), strict=True)
+    dec.load_state_dict(_sub(sd, "decoder."), strict=True)
+    fl.load_state_dict(_sub(sd, "feature_loss_net."), strict=True)
+    for m in (enc, dec, fl):
+        m.to(DEV).set_precision(precision) if hasattr(m, "set_precision") else m.to(DEV)
+    fl.precision = precision
+    tr = AutoencoderTrainer(enc, dec, fl, torch.device(DEV), lr=lr)
+    enc.train(); dec.train()
+    return enc, dec, tr
+
+
+def test_fp32_steps_match_reference_fixture(sd):
+    """losses of three steps and the step-0 gradients (read from the gradient arena) against the reference fixture;
+    tolerances of the KL-conditioned encoder gradient as in tests/test_oracle_golden_train.py"""
+    from test_oracle_golden_train import AE_LOSS_RTOL, ae_grad_tol
+    g = cases.load("ae_steps")
+    enc, dec, tr = _trainer(sd, "fp32", GA.LR)
+    named = {**{"encoder." + k: p for k, p in enc.named_parameters()}, **{"decoder." + k: p for k, p in dec.named_parameters()}}
+    for i in range(GA.STEPS):
+        got = tr.train_step(GA.step_input(i).to(DEV))
+        np.testing.assert_allclose(got, g["losses"][i], rtol=max(AE_LOSS_RTOL[i], 1e-4), err_msg=f"step {i} loss vs reference modules + AdamW")
+        if i == 0:
+            checked = 0
+            for k in GA.SAVE_KEYS:
+                if "g0:" + k in g:
+                    want, have = g["g0:" + k], named[k].grad.detach().cpu().numpy()
+                    assert np.abs(have - want).max() <= ae_grad_tol(k) * np.abs(want).max(), f"{k}: {np.abs(have - want).max()} of {np.abs(want).max()}"
+                    checked += 1
+            assert checked >= 8
+    after = {k: p.detach().cpu() for k, p in named.items()}
+    for k in GA.SAVE_KEYS:
+        if k in after:                  # three Adam steps move a weight by at most ~3 lr
+            np.testing.assert_allclose(after[k].numpy(), g["p:" + k], rtol=1e-3, atol=4 * GA.LR, err_msg=k)
+    np.testing.assert_allclose(enc.encoder[7].running_var.cpu().numpy(), g["p:encoder.encoder.7.running_var"], rtol=2e-3)
+    assert int(enc.encoder[1].num_batches_tracked) == GA.STEPS and tr.step_count == GA.STEPS
+
+
+def test_adamw_and_kl_grad_kernels():
+    """mstk_adamw_step_dev against torch.optim.AdamW, mstk_kl_grad against autograd of loss.py:31-32"""
+    from music_style_transfer_ldm_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    p0, gr = torch.randn(1003, generator=g), torch.randn(1003, generator=g)
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([ref], lr=1e-2, weight_decay=0.05)
+    n = (1003 + 3) // 4 * 4
+    p, gg, m, v = (torch.zeros(n, device=DEV) for _ in range(4))
+    p[:1003] = p0.to(DEV)
+    step = torch.zeros(1, dtype=torch.int64, device=DEV)
+    for s in range(3):
+        ref.grad = gr * (s + 1)
+        opt.step()
+        gg[:1003] = (gr * (s + 1)).to(DEV)
+        step.add_(1)
+        ops.adam_step(p, gg, m, v, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, step=step, weight_decay=0.05)
+    np.testing.assert_allclose(p[:1003].cpu().numpy(), ref.detach().numpy(), rtol=2e-6, atol=1e-7)
+    z = torch.randn((2, 16, 16, 32), generator=g)
+    dz = torch.randn((2, 16, 16, 32), generator=g)
+    zr = z.clone().requires_grad_(True)
+    (0.01 * torch.mean(0.5 * (zr * zr - 1 - torch.log(zr * zr + 1e-8)))).backward()
+    got = ops.kl_grad(z.to(DEV), dz.to(DEV), 0.01 / z.numel()).cpu()
+    np.testing.assert_allclose(got.numpy(), (zr.grad + dz).numpy(), rtol=1e-5, atol=1e-7)
+    got = ops.kl_grad(z.to(DEV), None, 0.01 / z.numel()).cpu()
+    np.testing.assert_allclose(got.numpy(), zr.grad.numpy(), rtol=1e-5, atol=1e-9)
+
+
+def test_bf16_loss_curve_within_one_percent(sd):
+    from oracle import train_oracle as T
+    enc, dec, tr = _trainer(sd, "bf16", GA.LR)
+    ot = T.OracleAutoencoderTrainer(sd, lr=GA.LR)
+    for i in range(20):
+        x = torch.rand((4, 1, 128, 128), generator=torch.Generator().manual_seed(9100 + i))
+        got, want = tr.train_step(x.to(DEV)), ot.train_step(x)
+        assert abs(got - want) <= 0.01 * abs(want), f"step {i}: {got} vs oracle {want}"
+
+
+def test_errors(sd):
+    from music_style_transfer_ldm_b200.ops import MstkError
+    enc, dec, tr = _trainer(sd, "fp32", 1e-3)
+    with pytest.raises(MstkError):
+        tr.train_step(torch.rand(2, 1, 128, 128))                   # CPU tensor: no fallback
+    with pytest.raises(MstkError):
+        tr.train_step(torch.rand(2, 1, 100, 128, device=DEV))
+    enc.eval()
+    with pytest.raises(MstkError):
+        tr.train_step(torch.rand(2, 1, 128, 128, device=DEV))
+
+
+def test_train_autoencoder_loop(tmp_path, capsys):
+    from music_style_transfer_ldm_b200.config import config
+    from music_style_transfer_ldm_b200.train import train_autoencoder
+    g = torch.Generator().manual_seed(1)
+    base = torch.rand((8, 1, 128, 128), generator=g)
+    train_loader = [(base[:4],), (base[4:],)] * 3
+    test_loader = [(base[:4],)]
+    cfg = dict(config, num_epochs=3, learning_rate=2e-3)
+    torch.manual_seed(0)
+    enc, dec, tl, vl = train_autoencoder(cfg, train_loader, test_loader, checkpoint_dir=str(tmp_path))
+    assert len(tl) == 3 and len(vl) == 3 and np.isfinite(tl + vl).all()
+    assert tl[-1] < tl[0]                                           # it learns the 8 fixed images
+    assert (tmp_path / "encoder.pth").is_file() and (tmp_path / "decoder.pth").is_file()
+    assert set(torch.load(tmp_path / "encoder.pth", map_location="cpu")) == set(enc.state_dict())
+    assert "Average Val Loss" in capsys.readouterr().out
+    with pytest.raises(Exception):
+        train_autoencoder(cfg)
