@@ -187,6 +187,54 @@ def kernel_roofline(model, peaks, reps=20):
 
 
 # ------------------------------------------------------------------------------------------
+# VAE leg (BASELINE config 2): encode -> decode round trip of 16 spectrograms of 128 mel x 1024 frames; HBM bound
+# ------------------------------------------------------------------------------------------
+VAE_BATCH, VAE_H, VAE_W = 16, 128, 1024
+VAE_ELEMS_PER_SAMPLE = 12.98e6        # input + every inter-layer activation written once and read once + output
+
+
+def vae_leg(sd, dev, peaks, precision, reps=20):
+    """SpectrogramEncoder -> SpectrogramDecoder through the public modules (NCHW fp32 in / out), captured once in a
+    CUDA graph and replayed; eval mode (BatchNorm folded into the convs) and train mode (batch statistics in the conv
+    epilogue + one normalise pass).  achieved = SURVEY 8(d)'s minimal traffic / device time."""
+    import torch
+    import music_style_transfer_ldm_b200 as M
+    enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
+    enc.to(dev).set_precision(precision); dec.to(dev).set_precision(precision)
+    x = torch.rand((VAE_BATCH, 1, VAE_H, VAE_W), generator=torch.Generator().manual_seed(3)).to(dev)
+    bytes_min = VAE_ELEMS_PER_SAMPLE * VAE_BATCH * (2 if precision == "bf16" else 4)
+    peak = peaks.get("hbm_gbs", 6550.0)
+    out = {"workload": f"config2: decoder(encoder(x)), x [16,1,128,1024] fp32 NCHW, {precision} activations, latent [16,32,16,128]",
+           "bound": "hbm", "peak": peak, "unit": "GB/s", "algorithmic_bytes_per_round_trip": bytes_min,
+           "l2": "working set of one round trip (>= 415 MB bf16) exceeds the 126 MB L2",
+           "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6550 (B200_PROFILING.md)"}
+    with torch.no_grad():
+        for mode in ("eval", "train"):
+            enc.train(mode == "train"); dec.train(mode == "train")
+            stream = torch.cuda.Stream()
+            with torch.cuda.stream(stream):
+                for _ in range(3):
+                    y = dec(enc(x))
+                stream.synchronize()
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=stream):
+                    y = dec(enc(x))
+                gr.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(reps):
+                    gr.replay()
+                e1.record(stream)
+                stream.synchronize()
+            us = 1e3 * e0.elapsed_time(e1) / reps
+            out[mode] = {"us_per_round_trip": us, "spectrograms_per_s": VAE_BATCH / (us * 1e-6), "achieved": bytes_min / (us * 1e-6) / 1e9,
+                         "frac": bytes_min / (us * 1e-6) / 1e9 / peak, "finite": bool(torch.isfinite(y).all())}
+    return out
+
+
+# ------------------------------------------------------------------------------------------
 # training leg (BASELINE config 4): LDMTrainer.train_step, bf16, GLOBAL batch 256 sharded over the ranks
 # ------------------------------------------------------------------------------------------
 TRAIN_GLOBAL_BATCH = 256
@@ -446,6 +494,7 @@ def run_cuda(args):
             pass
         with torch.no_grad():
             roof, rows = kernel_roofline(model, peaks)
+        vae = None if args.no_vae else vae_leg(sd, dev, peaks, args.precision)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             v, threads, dt = cpu_transfer_timing(2)
@@ -459,7 +508,7 @@ def run_cuda(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
-            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak,
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak, "vae": vae,
             "samples_steps_per_s": value * BATCH,
             "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
             "layers": rows,
@@ -478,6 +527,7 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg")
+    ap.add_argument("--no-vae", action="store_true", help="skip the config-2 VAE round-trip leg")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps is None:

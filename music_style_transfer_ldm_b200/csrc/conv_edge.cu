@@ -13,6 +13,7 @@
 //                         input-grid position = a 2x2 block of output pixels and walks its 3x3
 //                         input neighbourhood with 128-bit loads (neighbouring threads share
 //                         them through L1); weights live in shared memory as fp32.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace mstk {
@@ -357,6 +358,101 @@ __global__ void __launch_bounds__(192, 2) convt4_cout1_kernel(const EdgeP a) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// convt4_cout1_mma_kernel: the same layer for bf16 activations with Cin == 64 (the decoder's last layer in bf16 mode)
+// as a skinny GEMM + col2im, so that x is read ONCE from HBM (the walking kernel above re-reads every pixel row
+// through nine 16-byte loads per position and 32 LDS.128 of weights: 143 us for 16 x 64 x 512 x 64, 0.5 TB/s).
+//   P[pos][tap] = sum_c x[pos][c] * w[tap][c]        M = positions of an 8 x 32 tile + 1-pixel halo (340), N = 16 taps, K = 64
+//   y[2h+py][2w+px] = sum over the 2 x 2 (dy, dx) neighbours whose tap (ky, kx) = (py+1-2dy, px+1-2dx) exists of P[h+dy][w+dx][ky*4+kx]
+// The GEMM runs on mma.sync m16n8k16 (bf16 x bf16 -> fp32) straight from global memory: the contraction does not care
+// about the order of the channels, so lane q of a quad owns the 16 CONSECUTIVE channels [16q, 16q+16) of its two rows
+// (two 16-byte loads per row) and the weight fragments use the same permutation (16 registers, loaded once).
+// P lives in shared memory as [tap][pos] (pos stride 340 = 4 mod 16: the fragment stores and the col2im reads are
+// conflict-free).  HBM bound: 128 B read per position + 16 B (fp32) written.
+constexpr int CT_TH = 8, CT_TW = 32, CT_PW = CT_TW + 2, CT_NP = (CT_TH + 2) * CT_PW, CT_MT = (CT_NP + 15) / 16;
+
+template <typename TO>
+__global__ void __launch_bounds__(256) convt4_cout1_mma_kernel(const EdgeP a, int tiles_w, int tiles_h) {
+    __shared__ float P[16 * CT_NP];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, q = lane & 3;
+    unsigned bid = blockIdx.x;
+    const int twi = (int)(bid % (unsigned)tiles_w); bid /= (unsigned)tiles_w;
+    const int thi = (int)(bid % (unsigned)tiles_h);
+    const int n = (int)(bid / (unsigned)tiles_h);
+    const int h0 = thi * CT_TH, w0 = twi * CT_TW;
+    const __nv_bfloat16* __restrict__ X = reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)n * a.H * a.W * 64;
+    // weight fragments: tap = nt*8 + g, channels [16q, 16q+16)
+    uint4 wv[2][2];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+        const uint4* wp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(a.w) + (nt * 8 + g) * 64 + 16 * q);
+        wv[nt][0] = __ldg(wp); wv[nt][1] = __ldg(wp + 1);
+    }
+    for (int mt = warp; mt < CT_MT; mt += 8) {
+        uint4 r[2][2];
+        int tpos[2];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int t = mt * 16 + g + 8 * half;
+            tpos[half] = t;
+            const int ty = t / CT_PW, tx = t - ty * CT_PW;
+            const int gh = h0 - 1 + ty, gw = w0 - 1 + tx;
+            if (t < CT_NP && gh >= 0 && gh < a.H && gw >= 0 && gw < a.W) {
+                const uint4* xp = reinterpret_cast<const uint4*>(X + ((size_t)gh * a.W + gw) * 64 + 16 * q);
+                r[half][0] = __ldg(xp); r[half][1] = __ldg(xp + 1);
+            } else {
+                r[half][0] = make_uint4(0u, 0u, 0u, 0u); r[half][1] = r[half][0];
+            }
+        }
+        float c[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+        const unsigned* r0 = reinterpret_cast<const unsigned*>(&r[0][0]);
+        const unsigned* r1 = reinterpret_cast<const unsigned*>(&r[1][0]);
+#pragma unroll
+        for (int s4 = 0; s4 < 4; ++s4) {
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                const unsigned* wr = reinterpret_cast<const unsigned*>(&wv[nt][0]);
+                asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+f"(c[nt][0]), "+f"(c[nt][1]), "+f"(c[nt][2]), "+f"(c[nt][3])
+                             : "r"(r0[2 * s4]), "r"(r1[2 * s4]), "r"(r0[2 * s4 + 1]), "r"(r1[2 * s4 + 1]), "r"(wr[2 * s4]), "r"(wr[2 * s4 + 1]));
+            }
+        }
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int half = 0; half < 2; ++half)
+                if (tpos[half] < CT_NP) {
+                    P[(nt * 8 + 2 * q) * CT_NP + tpos[half]] = c[nt][2 * half];
+                    P[(nt * 8 + 2 * q + 1) * CT_NP + tpos[half]] = c[nt][2 * half + 1];
+                }
+    }
+    __syncthreads();
+    const int iy = threadIdx.x >> 5, ix = threadIdx.x & 31;
+    const int h = h0 + iy, w = w0 + ix;
+    if (h >= a.H || w >= a.W) return;
+    const float b0 = a.bias ? a.bias[0] : 0.f;
+    const int tc = (iy + 1) * CT_PW + ix + 1;
+    TO* __restrict__ Y = reinterpret_cast<TO*>(a.y);
+#pragma unroll
+    for (int py = 0; py < 2; ++py) {
+        // (dy, ky) pairs of this output row: (0, py + 1) and (py ? +1 : -1, py ? 0 : 3)
+        const int dyb = py ? 1 : -1, kyb = py ? 0 : 3, kya = py + 1;
+        float o[2];
+#pragma unroll
+        for (int px = 0; px < 2; ++px) {
+            const int dxb = px ? 1 : -1, kxb = px ? 0 : 3, kxa = px + 1;
+            float v = P[(kya * 4 + kxa) * CT_NP + tc] + P[(kya * 4 + kxb) * CT_NP + tc + dxb] +
+                      P[(kyb * 4 + kxa) * CT_NP + tc + dyb * CT_PW] + P[(kyb * 4 + kxb) * CT_NP + tc + dyb * CT_PW + dxb];
+            v = apply_act(v + b0, a.act);
+            if (a.affine) v = v * a.out_scale + a.out_shift;
+            o[px] = v;
+        }
+        const size_t off = ((size_t)n * a.Ho + (2 * h + py)) * a.Wo + 2 * w;
+        if (sizeof(TO) == 4) *reinterpret_cast<float2*>(Y + off) = make_float2(o[0], o[1]);
+        else *reinterpret_cast<__nv_bfloat162*>(Y + off) = __floats2bfloat162_rn(o[0], o[1]);
+    }
+}
+
 static EdgeP make_edge(const ConvP& p) {
     EdgeP a;
     a.x = p.x; a.w = p.w; a.bias = p.bias; a.y = p.y; a.stats = p.stats;
@@ -418,6 +514,15 @@ int launch_conv_edge(const ConvP& p, cudaStream_t st) {
         if (blocks > cap) blocks = cap;
         const size_t smem = (size_t)16 * p.Cin * sizeof(float);
         const bool xf = p.dtype == MSTK_F32, of = p.out_dtype == MSTK_F32;
+        const size_t tw = (p.W + CT_TW - 1) / CT_TW, th = (p.H + CT_TH - 1) / CT_TH;
+        static const bool no_mma = getenv("MSTK_CONVT_WALK") != nullptr;      // A/B switch: the walking kernel for every shape
+        if (!xf && p.Cin == 64 && !no_mma && (size_t)p.N * tw * th < 0x7FFFFFFFull) {
+            const unsigned tiles = (unsigned)((size_t)p.N * tw * th);
+            if (of) convt4_cout1_mma_kernel<float><<<tiles, 256, 0, st>>>(a, (int)tw, (int)th);
+            else convt4_cout1_mma_kernel<__nv_bfloat16><<<tiles, 256, 0, st>>>(a, (int)tw, (int)th);
+            MSTK_CHECK_LAUNCH("convt4_cout1_mma launch");
+            return MSTK_OK;
+        }
         if (xf && of) convt4_cout1_kernel<float, float><<<(unsigned)blocks, 192, smem, st>>>(a);
         else if (xf) convt4_cout1_kernel<float, __nv_bfloat16><<<(unsigned)blocks, 192, smem, st>>>(a);
         else if (of) convt4_cout1_kernel<__nv_bfloat16, float><<<(unsigned)blocks, 192, smem, st>>>(a);

@@ -40,7 +40,8 @@ def test_conv_cin1(n, h, w, cout, stride, odt):
 
 
 @pytest.mark.parametrize("n,h,w,cin,dt", [(3, 64, 64, 64, torch.bfloat16), (2, 16, 24, 64, torch.float32), (1, 5, 7, 8, torch.float32),
-                                          (1, 64, 512, 64, torch.bfloat16)])
+                                          (1, 64, 512, 64, torch.bfloat16), (2, 5, 7, 64, torch.bfloat16), (1, 13, 70, 64, torch.bfloat16),
+                                          (1, 9, 33, 32, torch.bfloat16)])     # bf16 Cin=64: the mma + col2im kernel, ragged tiles too
 def test_convt4_cout1(n, h, w, cin, dt):
     ops = _ops()
     g = gen(n * 11 + cin)
