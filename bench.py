@@ -317,6 +317,58 @@ def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True
                         "1x128x128 spectrograms, encoder frozen, style_loss_weight 3.0, DDP gradient + BatchNorm-stat all-reduce"}
 
 
+def ae_leg(sd, dev, precision, batch=256, steps=6):
+    """one optimisation step of the autoencoder stage (train.py:68-83): encoder + decoder forward with
+    train-mode BatchNorm, compression_loss (MSE + 0.1 VGGish + 0.01 KL), backward through both, fused AdamW; CUDA-graph replay."""
+    import torch
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200 import ops
+    from music_style_transfer_ldm_b200.loss import VGGishFeatureLoss
+    from music_style_transfer_ldm_b200.train import AutoencoderTrainer
+    enc, dec, fl = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32), VGGishFeatureLoss()
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
+    fl.load_state_dict({k[len("feature_loss_net."):]: v for k, v in sd.items() if k.startswith("feature_loss_net.")})
+    enc.to(dev).set_precision(precision); dec.to(dev).set_precision(precision); fl.to(dev); fl.precision = precision
+    tr = AutoencoderTrainer(enc, dec, fl, dev, lr=5e-4)
+    enc.train(); dec.train()
+    xh = torch.rand((batch, 1, SPEC, SPEC), generator=torch.Generator().manual_seed(77)).pin_memory()
+    xd = xh.to(dev)
+    loss_h = torch.empty(1).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step_device():
+        return tr.train_step_device(xd)
+
+    def step_e2e():
+        loss_h.copy_(tr.train_step_device(xh.to(dev, non_blocking=True)).reshape(1), non_blocking=True)
+
+    def timed(fn, k):
+        evs = []
+        for _ in range(k):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)
+
+    for _ in range(4):
+        step_device()
+    step_e2e()
+    torch.cuda.synchronize()
+    n0 = ops.LAUNCHES
+    step_device()
+    torch.cuda.synchronize()
+    launches = ops.LAUNCHES - n0
+    ms, ms_e2e = timed(step_device, steps), timed(step_e2e, steps)
+    return {"metric": "autoencoder_train_samples_per_s", "value": batch * steps / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / steps,
+            "steps": steps, "batch": batch, "e2e": {"value": batch * steps / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / steps,
+                                                    "h2d_bytes_per_step": xh.numel() * 4, "d2h_bytes_per_step": 4},
+            "gpu_launches_per_step": int(launches), "last_loss": float(loss_h[0]),
+            "workload": f"train_autoencoder step (models/train.py:68-83), {precision}, batch {batch}, 1x128x128 spectrograms, 'vggish' perceptual branch"}
+
+
 def _time_us(fn, reps=10):
     import torch
     for _ in range(3):
@@ -495,6 +547,7 @@ def run_cuda(args):
         with torch.no_grad():
             roof, rows = kernel_roofline(model, peaks)
         vae = None if args.no_vae else vae_leg(sd, dev, peaks, args.precision)
+        ae = None if (args.no_train or world > 1) else ae_leg(sd, dev, args.precision)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             v, threads, dt = cpu_transfer_timing(2)
@@ -508,7 +561,7 @@ def run_cuda(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
-            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak, "vae": vae,
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak, "vae": vae, "train_autoencoder": ae,
             "samples_steps_per_s": value * BATCH,
             "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
             "layers": rows,

@@ -539,7 +539,8 @@ class AutoencoderTrainer:
 
     Gradient reaches the parameters through MSE(recon, x) and through 0.01 * KL(latent) (encoder only); the feature
     stack of the perceptual term runs under torch.no_grad() in the reference (loss.py:78) and is forward-only here.
-    Forward, backward and update are an explicit stream of C-ABI launches, as in LDMTrainer.  Single process."""
+    Forward, backward and update are an explicit stream of C-ABI launches, as in LDMTrainer, replayed as one CUDA graph
+    after two eager steps.  Single process."""
 
     def __init__(self, encoder, decoder, feature_extractor, device, lr=5e-4, weight_decay=1e-2):
         self.device = torch.device(device)
@@ -547,10 +548,14 @@ class AutoencoderTrainer:
             raise MstkError("AutoencoderTrainer: the training step runs on sm_100a kernels only (no CPU fallback)")
         self.encoder, self.decoder = encoder.to(device), decoder.to(device)
         self.feature_extractor = feature_extractor.to(device) if feature_extractor is not None else None
-        self.lr, self.weight_decay = float(lr), float(weight_decay)        # torch.optim.AdamW defaults (train.py:47)
+        self._lr, self.weight_decay = float(lr), float(weight_decay)       # torch.optim.AdamW defaults (train.py:47)
         self.betas, self.eps = (0.9, 0.999), 1e-8
         self.step_count = 0
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=device)
+        # whole-step CUDA graph after `graph_warmup` eager steps, re-captured when the input shape, the precision or
+        # the learning rate (a launch parameter of the AdamW kernel) changes
+        self.use_cuda_graph, self.graph_warmup = True, 2
+        self._graph, self._eager_steps = None, 0
         e, d = self.encoder.encoder, self.decoder.decoder
         # backward-completion order: decoder top-down, then the encoder top-down
         order = [d[6].weight, d[6].bias, d[4].weight, d[4].bias, d[3].weight, d[3].bias, d[1].weight, d[1].bias, d[0].weight, d[0].bias,
@@ -562,10 +567,51 @@ class AutoencoderTrainer:
         for m in list(self.encoder.modules()) + list(self.decoder.modules()):
             m.__dict__.pop("_mstk_cache", None)
 
+    @property
+    def lr(self) -> float:
+        return self._lr
+
+    @lr.setter
+    def lr(self, value: float) -> None:
+        if float(value) != self._lr:
+            self._lr = float(value)
+            if self._graph is not None:
+                self._graph, self._eager_steps = None, self.graph_warmup
+
     def train_step(self, spectrogram) -> float:
         return float(self.train_step_device(spectrogram))
 
     def train_step_device(self, spectrogram) -> torch.Tensor:
+        """eager for the first steps, afterwards a replay of the captured step; returns the loss as a 0-dim CUDA tensor"""
+        if not self.use_cuda_graph or not spectrogram.is_cuda or torch.cuda.is_current_stream_capturing():
+            return self._step_impl(spectrogram)
+        key = (tuple(spectrogram.shape), self.encoder._precision(), self.feature_extractor is not None)
+        if self._graph is not None and self._graph["key"] != key:
+            self._graph, self._eager_steps = None, 0
+        if self._graph is None:
+            if self._eager_steps < self.graph_warmup:
+                self._eager_steps += 1
+                return self._step_impl(spectrogram)
+            ent = {"key": key, "x": spectrogram.detach().float().contiguous().clone()}
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0, c0 = ops.LAUNCHES, self.step_count
+            with torch.cuda.graph(g):
+                ent["out"] = self._step_impl(ent["x"])
+            ent["launches"] = ops.LAUNCHES - n0
+            ops.LAUNCHES, self.step_count = n0, c0          # capture enqueued nothing
+            ent["graph"] = g
+            self._graph = ent
+        ent = self._graph
+        ent["x"].copy_(spectrogram)
+        ent["graph"].replay()
+        self.step_count += 1
+        ops._count(ent["launches"])
+        for m in list(self.encoder.modules()) + list(self.decoder.modules()):
+            m.__dict__.pop("_mstk_cache", None)
+        return ent["out"]
+
+    def _step_impl(self, spectrogram) -> torch.Tensor:
         enc, dec = self.encoder, self.decoder
         e, d = enc.encoder, dec.decoder
         if not (e[1].training and d[1].training):
