@@ -194,18 +194,8 @@ __global__ void __launch_bounds__(192, 2) conv_cin1_row_kernel(const EdgeP a) {
         }
         TO* yrow = Y + (((size_t)n * a.Ho + oh) * a.Wo + ow0) * a.Cout + c0;
         const int npx = a.Wo - ow0 < SEG ? a.Wo - ow0 : SEG;
-#pragma unroll 2
-        for (int i = 0; i < npx; ++i) {
-            const int iw = (ow0 + i) * STRIDE - 1;
-#pragma unroll
-            for (int ky = 0; ky < 3; ++ky) {
-                if (STRIDE == 1) {
-                    win[ky][2] = (rok[ky] && iw + 2 < a.W) ? __ldg(rowp[ky] + iw + 2) : 0.f;
-                } else {
-                    win[ky][1] = rok[ky] ? __ldg(rowp[ky] + iw + 1) : 0.f;            // iw + 1 = 2*ow < W always
-                    win[ky][2] = (rok[ky] && iw + 2 < a.W) ? __ldg(rowp[ky] + iw + 2) : 0.f;
-                }
-            }
+        // one output pixel from the 3x3 window: 72 FMA, statistics, activation, one 16-byte store, window shift
+        auto emit = [&](int i) {
             float v[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = bias[j];
@@ -225,7 +215,7 @@ __global__ void __launch_bounds__(192, 2) conv_cin1_row_kernel(const EdgeP a) {
                 if (a.affine) x = x * a.out_scale + a.out_shift;
                 v[j] = x;
             }
-            TO* o = yrow + (size_t)i * a.Cout;
+            TO* o = yrow + (unsigned)i * (unsigned)a.Cout;
             if (sizeof(TO) == 4) {
                 reinterpret_cast<float4*>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
                 reinterpret_cast<float4*>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
@@ -241,6 +231,54 @@ __global__ void __launch_bounds__(192, 2) conv_cin1_row_kernel(const EdgeP a) {
                 if (STRIDE == 1) { win[ky][0] = win[ky][1]; win[ky][1] = win[ky][2]; }
                 else win[ky][0] = win[ky][2];
             }
+        };
+        // interior runs (all three input rows exist, no load of the run crosses the right edge): loads through
+        // three walking pointers with compile-time offsets, no predicates; stride 2 fetches its two new columns
+        // as ONE 8-byte load per row (2*ow is even and W is even, so the pair is 8-byte aligned)
+        // (stride 1: only the LAST pixel of an image row reads past the right edge, so its load alone is predicated --
+        // the last segment of a row shares its warp with interior segments and must not diverge from them)
+        const bool interior = rok[0] && rok[1] && rok[2] && npx == SEG && (STRIDE == 2 ? (a.W & 1) == 0 : true);
+        if (interior) {
+            if (STRIDE == 2) {
+                const float2* q0 = reinterpret_cast<const float2*>(rowp[0] + 2 * ow0);
+                const float2* q1 = reinterpret_cast<const float2*>(rowp[1] + 2 * ow0);
+                const float2* q2 = reinterpret_cast<const float2*>(rowp[2] + 2 * ow0);
+#pragma unroll 4
+                for (int i = 0; i < SEG; ++i) {
+                    const float2 t0 = __ldg(q0 + i), t1 = __ldg(q1 + i), t2 = __ldg(q2 + i);
+                    win[0][1] = t0.x; win[0][2] = t0.y; win[1][1] = t1.x; win[1][2] = t1.y; win[2][1] = t2.x; win[2][2] = t2.y;
+                    emit(i);
+                }
+            } else {
+                const float* q0 = rowp[0] + ow0 + 1;
+                const float* q1 = rowp[1] + ow0 + 1;
+                const float* q2 = rowp[2] + ow0 + 1;
+#pragma unroll 5
+                for (int i = 0; i < SEG - 1; ++i) {
+                    win[0][2] = __ldg(q0 + i); win[1][2] = __ldg(q1 + i); win[2][2] = __ldg(q2 + i);
+                    emit(i);
+                }
+                const bool more = ow0 + SEG < a.W;
+                win[0][2] = more ? __ldg(q0 + SEG - 1) : 0.f;
+                win[1][2] = more ? __ldg(q1 + SEG - 1) : 0.f;
+                win[2][2] = more ? __ldg(q2 + SEG - 1) : 0.f;
+                emit(SEG - 1);
+            }
+            continue;
+        }
+#pragma unroll 2
+        for (int i = 0; i < npx; ++i) {
+            const int iw = (ow0 + i) * STRIDE - 1;
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+                if (STRIDE == 1) {
+                    win[ky][2] = (rok[ky] && iw + 2 < a.W) ? __ldg(rowp[ky] + iw + 2) : 0.f;
+                } else {
+                    win[ky][1] = rok[ky] ? __ldg(rowp[ky] + iw + 1) : 0.f;            // iw + 1 = 2*ow < W always
+                    win[ky][2] = (rok[ky] && iw + 2 < a.W) ? __ldg(rowp[ky] + iw + 2) : 0.f;
+                }
+            }
+            emit(i);
         }
     }
     if (a.stats) {
