@@ -8,6 +8,7 @@
 //   bn_bwd_*              BatchNorm2d training-mode backward (reduce, apply)
 //   attention_bwd_kernel  softmax-attention backward per (sample, head)
 //   small streaming ops   sum over pixels, GELU', broadcast add, loss gradients, Adam
+#include <cstdlib>
 #include "common.cuh"
 
 namespace mstk {
@@ -796,6 +797,101 @@ __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
     for (int i = threadIdx.x; i < q.C * K * K; i += 256) atomicAdd(q.dw + i, acc_s[i]);
 }
 
+// ---------------------------------------------------------------------------
+// The ConvTranspose2d(64, 1, k4, s2, p1) weight gradient (decoder last layer) as a skinny GEMM on mma.sync m16n8k16:
+//   dw^T[tap][c] = sum_pix S_tap[pix] * V[pix][c]          M = 16 taps, N = 64 channels, K = pixels
+// The CUDA-core kernel above spends ~200 instructions per (pixel, 4 channels) on window addressing that all 16 threads
+// of a pixel repeat (337 us for 256 x 64 x 64 x 64, 0.4 TB/s).  Here a warp takes 16 consecutive pixels of a row per step:
+//   B (V, bf16): lane (g, q) loads the 8 CONSECUTIVE channels [8g, 8g+8) of pixels 2q, 2q+1, 2q+8, 2q+9 (four 16-byte loads,
+//      a quad-row of lanes covers whole 128-byte pixels) and interleaves pixel pairs with PRMT; n-tile j, column g <-> channel 8g+j
+//   A (S = dy, fp32 or bf16): 8 gathered scalars per lane, split into bf16 hi + lo parts (two MMAs) so fp32 dy keeps ~16 bits
+// 32 fp32 accumulators per lane; warps -> shared memory -> one global RED per weight and CTA.  V is read exactly once.
+// ---------------------------------------------------------------------------
+template <bool SF32>
+__global__ void __launch_bounds__(256) wgrad_convt4_cout1_mma_kernel(const EdgeWgradP q) {
+    __shared__ float acc_s[64 * 16];                  // [c][tap] = the parameter's own layout
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) acc_s[i] = 0.f;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, g = lane >> 2, qd = lane & 3;
+    const int segs = q.Wv >> 4;
+    const long long steps = (long long)q.N * q.Hv * segs;
+    const long long wstride = (long long)gridDim.x * 8;
+    float c[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { c[j][0] = 0.f; c[j][1] = 0.f; c[j][2] = 0.f; c[j][3] = 0.f; }
+    const int ky0 = g >> 2, kx = g & 3;                // taps g (ky0, kx) and g + 8 (ky0 + 2, kx)
+    for (long long st = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); st < steps; st += wstride) {
+        const int seg = (int)(st % segs);
+        const long long row = st / segs;
+        const int vh = (int)(row % q.Hv), n = (int)(row / q.Hv);
+        const int vw0 = seg << 4;
+        // ---- V: four pixels x 8 channels ----
+        const __nv_bfloat16* vp = q.v + ((row * q.Wv + vw0) * 64 + 8 * g);
+        const uint4 p0 = *reinterpret_cast<const uint4*>(vp + (2 * qd) * 64);
+        const uint4 p1 = *reinterpret_cast<const uint4*>(vp + (2 * qd + 1) * 64);
+        const uint4 p2 = *reinterpret_cast<const uint4*>(vp + (2 * qd + 8) * 64);
+        const uint4 p3 = *reinterpret_cast<const uint4*>(vp + (2 * qd + 9) * 64);
+        // ---- S: taps (g, g+8) at pixels 2q, 2q+1, 2q+8, 2q+9 ----
+        float sv[2][4];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int sh = 2 * vh + ky0 + 2 * half - 1;
+            const bool rok = sh >= 0 && sh < q.Hs;
+            const size_t rbase = ((size_t)n * q.Hs + (rok ? sh : 0)) * q.Ws;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int k = 2 * qd + (e & 1) + 8 * (e >> 1);
+                const int sw = 2 * (vw0 + k) + kx - 1;
+                const bool ok = rok && sw >= 0 && sw < q.Ws;
+                const size_t si = rbase + (ok ? sw : 0);
+                const float raw = SF32 ? __ldg(reinterpret_cast<const float*>(q.s) + si)
+                                       : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(q.s)[si]);
+                sv[half][e] = ok ? raw : 0.f;
+            }
+        }
+        unsigned ah[4], al[4];                          // a0: (tap g, k 2q..), a1: (tap g+8, k 2q..), a2: (tap g, k 2q+8..), a3: (tap g+8, k 2q+8..)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int half = r & 1, e0 = (r >> 1) * 2;
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(sv[half][e0], sv[half][e0 + 1]);
+            ah[r] = *reinterpret_cast<const unsigned*>(&hi);
+            if (SF32) {
+                const float2 hf = __bfloat1622float2(hi);
+                const __nv_bfloat162 lo = __floats2bfloat162_rn(sv[half][e0] - hf.x, sv[half][e0 + 1] - hf.y);
+                al[r] = *reinterpret_cast<const unsigned*>(&lo);
+            }
+        }
+        const unsigned* w0 = reinterpret_cast<const unsigned*>(&p0);
+        const unsigned* w1 = reinterpret_cast<const unsigned*>(&p1);
+        const unsigned* w2 = reinterpret_cast<const unsigned*>(&p2);
+        const unsigned* w3 = reinterpret_cast<const unsigned*>(&p3);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            // channel 8g + j of the pixel pairs: low halves for even j, high halves for odd j
+            const unsigned sel = (j & 1) ? 0x7632u : 0x5410u;
+            const unsigned b0 = __byte_perm(w0[j >> 1], w1[j >> 1], sel);
+            const unsigned b1 = __byte_perm(w2[j >> 1], w3[j >> 1], sel);
+            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(c[j][0]), "+f"(c[j][1]), "+f"(c[j][2]), "+f"(c[j][3])
+                         : "r"(ah[0]), "r"(ah[1]), "r"(ah[2]), "r"(ah[3]), "r"(b0), "r"(b1));
+            if (SF32)
+                asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+f"(c[j][0]), "+f"(c[j][1]), "+f"(c[j][2]), "+f"(c[j][3])
+                             : "r"(al[0]), "r"(al[1]), "r"(al[2]), "r"(al[3]), "r"(b0), "r"(b1));
+        }
+    }
+    // c[j][0..1]: tap g, columns 2q, 2q+1 of n-tile j -> channels 8*(2q) + j, 8*(2q+1) + j; c[j][2..3]: tap g + 8
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        atomicAdd(&acc_s[(16 * qd + j) * 16 + g], c[j][0]);
+        atomicAdd(&acc_s[(16 * qd + 8 + j) * 16 + g], c[j][1]);
+        atomicAdd(&acc_s[(16 * qd + j) * 16 + g + 8], c[j][2]);
+        atomicAdd(&acc_s[(16 * qd + 8 + j) * 16 + g + 8], c[j][3]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) atomicAdd(q.dw + i, acc_s[i]);
+}
+
 // returns MSTK_EUNSUPPORTED when the layer is not one of the two edge shapes
 static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
     EdgeWgradP q;
@@ -820,6 +916,15 @@ static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
         q.v = reinterpret_cast<const __nv_bfloat16*>(a->x); q.s = a->dy; q.s_dtype = a->dy_dtype;
         q.Hv = a->h; q.Wv = a->w; q.C = a->cin; q.Hs = 2 * a->h; q.Ws = 2 * a->w; q.ss = 2;
         const long long npix = (long long)q.N * q.Hv * q.Wv;
+        static const bool no_mma = getenv("MSTK_WGRAD_EDGE_WALK") != nullptr;      // A/B switch: the CUDA-core kernel for every shape
+        if (q.C == 64 && (q.Wv & 15) == 0 && !no_mma && (reinterpret_cast<uintptr_t>(q.v) & 15) == 0) {
+            long long mb = (npix / 16 + 7) / 8;
+            if (mb > 4LL * bw_sms()) mb = 4LL * bw_sms();
+            if (q.s_dtype == MSTK_F32) wgrad_convt4_cout1_mma_kernel<true><<<(unsigned)mb, 256, 0, st>>>(q);
+            else wgrad_convt4_cout1_mma_kernel<false><<<(unsigned)mb, 256, 0, st>>>(q);
+            MSTK_CHECK_LAUNCH("wgrad_convt4_cout1_mma");
+            return MSTK_OK;
+        }
         const int ppb = 256 / (q.C / 4);
         long long blocks = (npix + ppb - 1) / ppb;
         if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();

@@ -53,6 +53,22 @@ def test_wgrad_and_dgrad(case, dt):
     assert_close(nchw(dx), x.grad, tol * 10, "dgrad")
 
 
+@pytest.mark.parametrize("n,h,w,dy_dt,tol", [(2, 16, 32, torch.float32, 2e-4), (3, 5, 16, torch.bfloat16, 1e-4), (1, 64, 64, torch.float32, 2e-4)])
+def test_wgrad_convt4_cout1_mma(n, h, w, dy_dt, tol):
+    """the decoder's last layer (ConvTranspose2d(64, 1, 4, 2, 1)): mma.sync skinny-GEMM weight gradient, bf16 x with an fp32
+    (hi + lo bf16 split) or bf16 dy, against autograd; accumulation into dw checked by calling twice"""
+    ops = _ops()
+    g = gen(n * 7 + h)
+    x = torch.randn((n, 64, h, w), generator=g).bfloat16().float()
+    wt = (torch.randn((64, 1, 4, 4), generator=g) / 32).requires_grad_(True)
+    dy = torch.randn((n, 1, 2 * h, 2 * w), generator=g).to(dy_dt).float()
+    F.conv_transpose2d(x, wt, None, stride=2, padding=1).backward(dy)
+    dw = torch.zeros(wt.shape, device=DEV)
+    for _ in range(2):
+        ops.wgrad(nhwc(x, torch.bfloat16).to(DEV), nhwc(dy, dy_dt).to(DEV), dw, ksize=4, stride=2, transposed=True)
+    assert_close(dw.cpu() / 2, wt.grad, tol, "wgrad convT k4 cout1 (mma)")
+
+
 @pytest.mark.parametrize("c,act", [(64, 1), (32, 2), (1, 2), (24, 0), (12, 1)])
 def test_act_bwd(c, act):
     ops = _ops()
