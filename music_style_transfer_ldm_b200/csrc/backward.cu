@@ -798,7 +798,7 @@ __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
 }
 
 // ---------------------------------------------------------------------------
-// The ConvTranspose2d(64, 1, k4, s2, p1) weight gradient (decoder last layer) as a skinny GEMM on mma.sync m16n8k16:
+// wgrad_edge_mma_kernel: the ConvTranspose2d(64, 1, k4, s2, p1) weight gradient (decoder last layer) as a skinny GEMM on mma.sync m16n8k16:
 //   dw^T[tap][c] = sum_pix S_tap[pix] * V[pix][c]          M = 16 taps, N = 64 channels, K = pixels
 // The CUDA-core kernel above spends ~200 instructions per (pixel, 4 channels) on window addressing that all 16 threads
 // of a pixel repeat (337 us for 256 x 64 x 64 x 64, 0.4 TB/s).  Here a warp takes 16 consecutive pixels of a row per step:
@@ -807,10 +807,13 @@ __global__ void __launch_bounds__(256) wgrad_edge_kernel(const EdgeWgradP q) {
 //   A (S = dy, fp32 or bf16): 8 gathered scalars per lane, split into bf16 hi + lo parts (two MMAs) so fp32 dy keeps ~16 bits
 // 32 fp32 accumulators per lane; warps -> shared memory -> one global RED per weight and CTA.  V is read exactly once.
 // ---------------------------------------------------------------------------
-template <bool SF32>
-__global__ void __launch_bounds__(256) wgrad_convt4_cout1_mma_kernel(const EdgeWgradP q) {
-    __shared__ float acc_s[64 * 16];                  // [c][tap] = the parameter's own layout
-    for (int i = threadIdx.x; i < 64 * 16; i += 256) acc_s[i] = 0.f;
+// The same kernel serves Conv2d(1, 64, k3, stride s, p1) (first layer of the style encoder / VAE encoder): K = 3, nine taps in
+// the 16-row A tile (rows 9..15 are zero), V = dy, S = x.
+template <int K, bool SF32>
+__global__ void __launch_bounds__(256) wgrad_edge_mma_kernel(const EdgeWgradP q) {
+    constexpr int KK = K * K;
+    __shared__ float acc_s[64 * KK];                  // [c][tap] = the parameter's own layout
+    for (int i = threadIdx.x; i < 64 * KK; i += 256) acc_s[i] = 0.f;
     __syncthreads();
     const int lane = threadIdx.x & 31, g = lane >> 2, qd = lane & 3;
     const int segs = q.Wv >> 4;
@@ -819,7 +822,9 @@ __global__ void __launch_bounds__(256) wgrad_convt4_cout1_mma_kernel(const EdgeW
     float c[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { c[j][0] = 0.f; c[j][1] = 0.f; c[j][2] = 0.f; c[j][3] = 0.f; }
-    const int ky0 = g >> 2, kx = g & 3;                // taps g (ky0, kx) and g + 8 (ky0 + 2, kx)
+    // taps g and g + 8 of the A tile
+    const int tky[2] = {g / K, (g + 8) / K}, tkx[2] = {g % K, (g + 8) % K};
+    const bool tok[2] = {g < KK, g + 8 < KK};
     for (long long st = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); st < steps; st += wstride) {
         const int seg = (int)(st % segs);
         const long long row = st / segs;
@@ -835,13 +840,13 @@ __global__ void __launch_bounds__(256) wgrad_convt4_cout1_mma_kernel(const EdgeW
         float sv[2][4];
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
-            const int sh = 2 * vh + ky0 + 2 * half - 1;
-            const bool rok = sh >= 0 && sh < q.Hs;
+            const int sh = q.ss * vh + tky[half] - 1;
+            const bool rok = tok[half] && sh >= 0 && sh < q.Hs;
             const size_t rbase = ((size_t)n * q.Hs + (rok ? sh : 0)) * q.Ws;
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int k = 2 * qd + (e & 1) + 8 * (e >> 1);
-                const int sw = 2 * (vw0 + k) + kx - 1;
+                const int sw = q.ss * (vw0 + k) + tkx[half] - 1;
                 const bool ok = rok && sw >= 0 && sw < q.Ws;
                 const size_t si = rbase + (ok ? sw : 0);
                 const float raw = SF32 ? __ldg(reinterpret_cast<const float*>(q.s) + si)
@@ -883,13 +888,17 @@ __global__ void __launch_bounds__(256) wgrad_convt4_cout1_mma_kernel(const EdgeW
     // c[j][0..1]: tap g, columns 2q, 2q+1 of n-tile j -> channels 8*(2q) + j, 8*(2q+1) + j; c[j][2..3]: tap g + 8
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        atomicAdd(&acc_s[(16 * qd + j) * 16 + g], c[j][0]);
-        atomicAdd(&acc_s[(16 * qd + 8 + j) * 16 + g], c[j][1]);
-        atomicAdd(&acc_s[(16 * qd + j) * 16 + g + 8], c[j][2]);
-        atomicAdd(&acc_s[(16 * qd + 8 + j) * 16 + g + 8], c[j][3]);
+        if (tok[0]) {
+            atomicAdd(&acc_s[(16 * qd + j) * KK + g], c[j][0]);
+            atomicAdd(&acc_s[(16 * qd + 8 + j) * KK + g], c[j][1]);
+        }
+        if (tok[1]) {
+            atomicAdd(&acc_s[(16 * qd + j) * KK + g + 8], c[j][2]);
+            atomicAdd(&acc_s[(16 * qd + 8 + j) * KK + g + 8], c[j][3]);
+        }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 64 * 16; i += 256) atomicAdd(q.dw + i, acc_s[i]);
+    for (int i = threadIdx.x; i < 64 * KK; i += 256) atomicAdd(q.dw + i, acc_s[i]);
 }
 
 // returns MSTK_EUNSUPPORTED when the layer is not one of the two edge shapes
@@ -903,6 +912,15 @@ static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
         q.Hv = (a->h + 2 - 3) / a->stride + 1; q.Wv = (a->w + 2 - 3) / a->stride + 1; q.C = a->cout;
         q.Hs = a->h; q.Ws = a->w; q.ss = a->stride;
         const long long npix = (long long)q.N * q.Hv * q.Wv;
+        static const bool no_mma3 = getenv("MSTK_WGRAD_EDGE_WALK") != nullptr;
+        if (q.C == 64 && (q.Wv & 15) == 0 && !no_mma3 && (reinterpret_cast<uintptr_t>(q.v) & 15) == 0) {
+            long long mb = (npix / 16 + 7) / 8;
+            if (mb > 4LL * bw_sms()) mb = 4LL * bw_sms();
+            if (q.s_dtype == MSTK_F32) wgrad_edge_mma_kernel<3, true><<<(unsigned)mb, 256, 0, st>>>(q);
+            else wgrad_edge_mma_kernel<3, false><<<(unsigned)mb, 256, 0, st>>>(q);
+            MSTK_CHECK_LAUNCH("wgrad_edge_mma(cin=1)");
+            return MSTK_OK;
+        }
         const int ppb = 256 / (q.C / 8);
         long long blocks = (npix + ppb - 1) / ppb;
         if (blocks > 4LL * bw_sms()) blocks = 4LL * bw_sms();
@@ -920,9 +938,9 @@ static int launch_wgrad_edge(const mstk_wgrad_args* a, cudaStream_t st) {
         if (q.C == 64 && (q.Wv & 15) == 0 && !no_mma && (reinterpret_cast<uintptr_t>(q.v) & 15) == 0) {
             long long mb = (npix / 16 + 7) / 8;
             if (mb > 4LL * bw_sms()) mb = 4LL * bw_sms();
-            if (q.s_dtype == MSTK_F32) wgrad_convt4_cout1_mma_kernel<true><<<(unsigned)mb, 256, 0, st>>>(q);
-            else wgrad_convt4_cout1_mma_kernel<false><<<(unsigned)mb, 256, 0, st>>>(q);
-            MSTK_CHECK_LAUNCH("wgrad_convt4_cout1_mma");
+            if (q.s_dtype == MSTK_F32) wgrad_edge_mma_kernel<4, true><<<(unsigned)mb, 256, 0, st>>>(q);
+            else wgrad_edge_mma_kernel<4, false><<<(unsigned)mb, 256, 0, st>>>(q);
+            MSTK_CHECK_LAUNCH("wgrad_edge_mma(cout=1)");
             return MSTK_OK;
         }
         const int ppb = 256 / (q.C / 4);

@@ -69,6 +69,23 @@ def test_wgrad_convt4_cout1_mma(n, h, w, dy_dt, tol):
     assert_close(dw.cpu() / 2, wt.grad, tol, "wgrad convT k4 cout1 (mma)")
 
 
+@pytest.mark.parametrize("n,h,w,stride,x_dt,tol", [(2, 32, 64, 2, torch.float32, 2e-4), (3, 10, 32, 2, torch.bfloat16, 1e-4),
+                                                   (2, 6, 16, 1, torch.float32, 2e-4), (1, 128, 128, 2, torch.float32, 2e-4)])
+def test_wgrad_conv_cin1_mma(n, h, w, stride, x_dt, tol):
+    """Conv2d(1, 64, 3, stride, 1) (style encoder / VAE encoder first layer): the nine-tap form of the mma.sync edge wgrad"""
+    ops = _ops()
+    g = gen(n * 5 + h + stride)
+    x = torch.rand((n, 1, h, w), generator=g).to(x_dt).float()
+    wt = (torch.randn((64, 1, 3, 3), generator=g) / 3).requires_grad_(True)
+    y = F.conv2d(x, wt, None, stride=stride, padding=1)
+    dy = torch.randn(y.shape, generator=g).bfloat16().float()
+    y.backward(dy)
+    dw = torch.zeros(wt.shape, device=DEV)
+    for _ in range(2):
+        ops.wgrad(nhwc(x, x_dt).to(DEV), nhwc(dy, torch.bfloat16).to(DEV), dw, ksize=3, stride=stride)
+    assert_close(dw.cpu() / 2, wt.grad, tol, "wgrad conv k3 cin1 (mma)")
+
+
 @pytest.mark.parametrize("c,act", [(64, 1), (32, 2), (1, 2), (24, 0), (12, 1)])
 def test_act_bwd(c, act):
     ops = _ops()
