@@ -177,8 +177,15 @@ def kernel_roofline(model, peaks, reps=20):
     fl, us = sum(r["gflop"] for r in tc) * 1e9, sum(r["us"] for r in tc)
     peak = peaks.get("bf16_tflops", 1590.0)
     achieved = fl / (us * 1e-6) / 1e12 if us > 0 else 0.0
+    traffic, traffic_src = None, None
+    try:        # dram bytes per launch from the committed ncu --set full capture (tools/traffic_from_ncu.py)
+        with open(os.path.join(ROOT, "profiles", "conv_tc_traffic.json")) as f:
+            tj = json.load(f)
+        traffic, traffic_src = tj["bytes_per_launch"], f"profiles/conv_tc_traffic.json ({tj['launches']} launches of one UNet step, {tj['metric']})"
+    except (OSError, KeyError, ValueError):
+        pass
     roof = {"bound": "tensor", "kernel": "conv_tc_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-            "frac": achieved / peak, "traffic": None, "launches_per_unet_step": len(tc),
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_unet_step": len(tc),
             "flop_per_launch_avg": fl / max(1, len(tc)), "us_per_launch_avg": us / max(1, len(tc)),
             "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1590 (B200_PROFILING.md)",
             "note": "achieved = sum of algorithmic conv FLOPs of the tcgen05 launches of one batch-64 UNet step / sum of their "

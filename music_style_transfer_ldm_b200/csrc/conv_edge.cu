@@ -491,6 +491,114 @@ __global__ void __launch_bounds__(256) convt4_cout1_mma_kernel(const EdgeP a, in
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// conv_cin1_k4s2_mma_kernel: Conv2d(1, 64, k4, s2, p1) with bf16 output -- the data gradient of the decoder's last
+// layer (ConvTranspose2d(64, 1, 4, 2, 1) read backwards: dh[pix][c] = sum_tap dy[2oh+ky-1][2ow+kx-1] * w[tap][c]).  It ran on
+// the generic CUDA-core tile (114 us at batch 256 for 134 MB of output).  One k16 step of mma.sync per 16 output pixels:
+// A = the 16 gathered taps of each pixel, B = the [16 taps][64 channels] weight (n-tile j, column g <-> channel 8g+j, so a
+// lane ends up with 2 x 8 consecutive output channels = 16-byte stores, a quad with a whole 128-byte pixel).
+// fp32 operands are split into bf16 hi + lo and three MMAs (hi*hi + lo*hi + hi*lo) keep ~16 mantissa bits.
+// HBM bound: 128 B written per output pixel, the scalar input stays in L1/L2.
+template <typename TO>
+__global__ void __launch_bounds__(256) conv_cin1_k4s2_mma_kernel(const EdgeP a) {
+    const int lane = threadIdx.x & 31, g = lane >> 2, qd = lane & 3;
+    const float* __restrict__ Wt = reinterpret_cast<const float*>(a.w);       // packed [16][64][1]
+    unsigned bh[8][2], bl[8][2];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int k = 2 * qd + 8 * r;
+            const float w0 = Wt[k * 64 + 8 * g + j], w1 = Wt[(k + 1) * 64 + 8 * g + j];
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(w0, w1);
+            const float2 hf = __bfloat1622float2(hi);
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(w0 - hf.x, w1 - hf.y);
+            bh[j][r] = *reinterpret_cast<const unsigned*>(&hi);
+            bl[j][r] = *reinterpret_cast<const unsigned*>(&lo);
+        }
+    float bias0[8], bias1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        bias0[j] = a.bias ? a.bias[16 * qd + j] : 0.f;
+        bias1[j] = a.bias ? a.bias[16 * qd + 8 + j] : 0.f;
+    }
+    const float* __restrict__ X = reinterpret_cast<const float*>(a.x);
+    TO* __restrict__ Y = reinterpret_cast<TO*>(a.y);
+    const int segs = a.Wo >> 4;
+    const long long steps = (long long)a.N * a.Ho * segs;
+    const int kyb = qd >> 1, kxb = 2 * (qd & 1);            // taps 2q, 2q+1: (kyb, kxb), (kyb, kxb+1); taps 2q+8, 2q+9: ky + 2
+    for (long long st = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); st < steps; st += (long long)gridDim.x * 8) {
+        const int seg = (int)(st % segs);
+        const long long row = st / segs;
+        const int oh = (int)(row % a.Ho), n = (int)(row / a.Ho);
+        const int ow0 = seg << 4;
+        float sv[4][2];                                      // [a-register r: (pixel g | g+8, ky | ky+2)][column pair]
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int ow = ow0 + g + 8 * (r & 1);
+            const int ih = 2 * oh + kyb + 2 * (r >> 1) - 1;
+            const bool rok = ih >= 0 && ih < a.H;
+            const float* xr = X + ((size_t)n * a.H + (rok ? ih : 0)) * a.W;
+            const int iw = 2 * ow + kxb - 1;
+            sv[r][0] = (rok && iw >= 0) ? __ldg(xr + (iw >= 0 ? iw : 0)) : 0.f;
+            sv[r][1] = (rok && iw + 1 < a.W) ? __ldg(xr + (iw + 1 < a.W ? iw + 1 : 0)) : 0.f;
+        }
+        unsigned ah[4], al[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(sv[r][0], sv[r][1]);
+            const float2 hf = __bfloat1622float2(hi);
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(sv[r][0] - hf.x, sv[r][1] - hf.y);
+            ah[r] = *reinterpret_cast<const unsigned*>(&hi);
+            al[r] = *reinterpret_cast<const unsigned*>(&lo);
+        }
+        float c[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            c[j][0] = bias0[j]; c[j][1] = bias1[j]; c[j][2] = bias0[j]; c[j][3] = bias1[j];
+#define MSTK_MMA(A, B)                                                                                                      \
+            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" \
+                         : "+f"(c[j][0]), "+f"(c[j][1]), "+f"(c[j][2]), "+f"(c[j][3])                                        \
+                         : "r"(A[0]), "r"(A[1]), "r"(A[2]), "r"(A[3]), "r"(B[j][0]), "r"(B[j][1]))
+            MSTK_MMA(al, bh); MSTK_MMA(ah, bl); MSTK_MMA(ah, bh);
+#undef MSTK_MMA
+        }
+        // c[j][0]: pixel g, channel 16q+j; c[j][1]: pixel g, channel 16q+8+j; c[j][2], c[j][3]: pixel g+8
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            TO* o = Y + (((size_t)row * a.Wo + ow0 + g + 8 * half) * 64 + 16 * qd);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                float v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float x = apply_act(c[j][2 * half + e], a.act);
+                    if (a.affine) x = x * a.out_scale + a.out_shift;
+                    v[j] = x;
+                }
+                if (sizeof(TO) == 4) {
+                    reinterpret_cast<float4*>(o + 8 * e)[0] = make_float4(v[0], v[1], v[2], v[3]);
+                    reinterpret_cast<float4*>(o + 8 * e)[1] = make_float4(v[4], v[5], v[6], v[7]);
+                } else {
+                    uint4 pk;
+                    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) h[t] = __floats2bfloat162_rn(v[2 * t], v[2 * t + 1]);
+                    *reinterpret_cast<uint4*>(o + 8 * e) = pk;
+                }
+            }
+        }
+    }
+}
+
+static bool cin1_k4s2_plan(const ConvP& p) {
+    if (!(p.nphases == 1 && p.Cin == 1 && p.Cout == 64 && p.ph[0].ntaps == 16 && p.s_in == 2 && p.dtype == MSTK_F32 && !p.stats &&
+          p.out_dtype == MSTK_BF16 && (p.Wo & 15) == 0 && p.Ho * 2 == p.H && p.Wo * 2 == p.W)) return false;
+    for (int t = 0; t < 16; ++t)
+        if (p.ph[0].taps[t].slice != t || p.ph[0].taps[t].dy != t / 4 - 1 || p.ph[0].taps[t].dx != t % 4 - 1) return false;
+    return getenv("MSTK_CIN1_K4_SIMT") == nullptr;
+}
+
 static EdgeP make_edge(const ConvP& p) {
     EdgeP a;
     a.x = p.x; a.w = p.w; a.bias = p.bias; a.y = p.y; a.stats = p.stats;
@@ -504,6 +612,7 @@ bool conv_edge_supported(const ConvP& p) {
     if (p.add || p.add_nc || p.has_ddim || !p.y) return false;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15)) return false;
     if (p.nphases == 1 && p.Cin == 1 && p.ph[0].ntaps == 9 && p.dtype == MSTK_F32 && (p.Cout % 8) == 0 && p.Cout <= 1024) return true;
+    if (cin1_k4s2_plan(p)) return true;
     if (p.nphases == 4 && p.ph[3].ntaps == 4 && p.ph[0].ntaps == 4 && p.Cout == 1 && (p.Cin % 8) == 0 && p.Cin <= 256 &&
         ((p.Cin / 8) & (p.Cin / 8 - 1)) == 0 && !p.stats) return true;      // Cin/8 lanes per position: a power of two <= 32
     return false;
@@ -513,6 +622,14 @@ int launch_conv_edge(const ConvP& p, cudaStream_t st) {
     const EdgeP a = make_edge(p);
     int sms = 148, dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (p.nphases == 1 && p.ph[0].ntaps == 16) {
+        const long long steps = (long long)p.N * p.Ho * (p.Wo / 16);
+        long long blocks = (steps + 7) / 8;
+        if (blocks > 4LL * sms) blocks = 4LL * sms;
+        conv_cin1_k4s2_mma_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(a);
+        MSTK_CHECK_LAUNCH("conv_cin1_k4s2_mma launch");
+        return MSTK_OK;
+    }
     if (p.nphases == 1) {
         const size_t items = (size_t)p.N * p.Ho * p.Wo * (p.Cout / 8);
         size_t blocks = (items + 255) / 256;

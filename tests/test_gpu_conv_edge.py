@@ -54,3 +54,22 @@ def test_convt4_cout1(n, h, w, cin, dt):
                  out_scale=0.5, out_shift=0.5)
     assert tuple(y.shape) == (n, 2 * h, 2 * w, 1)
     assert_close(nchw(y), ref, 2e-5, "convT k4 cout1")
+
+
+@pytest.mark.parametrize("n,h,w", [(2, 16, 32), (1, 128, 128), (3, 6, 64)])
+def test_conv_cin1_k4s2_mma(n, h, w):
+    """Conv2d(1, 64, 4, 2, 1), fp32 in -> bf16 out (data gradient of the decoder's last layer): mma.sync kernel with hi/lo
+    bf16 operand split, against F.conv2d; tolerance = bf16 rounding of the output"""
+    ops = _ops()
+    g = gen(n * 3 + h)
+    x = torch.randn((n, 1, h, w), generator=g)
+    wt = torch.randn((64, 1, 4, 4), generator=g) / 4
+    b = torch.randn((64,), generator=g) * 0.1
+    ref = F.conv2d(x, wt, b, stride=2, padding=1)
+    wp = ops.pack_weight(wt.to(DEV), torch.float32)
+    y = ops.conv(nhwc(x, torch.float32).to(DEV), wp, b.to(DEV), ksize=4, stride=2, out_dtype=torch.bfloat16)
+    assert tuple(y.shape) == (n, h // 2, w // 2, 64)
+    assert_close(nchw(y.float()), ref, 8e-3, "conv k4 s2 cin1 (mma)")
+    y0 = ops.conv(nhwc(x, torch.float32).to(DEV), wp, None, ksize=4, stride=2, out_dtype=torch.float32, backend=ops.BACKEND_SIMT)
+    yb = ops.conv(nhwc(x, torch.float32).to(DEV), wp, None, ksize=4, stride=2, out_dtype=torch.bfloat16)
+    assert (yb.float() - y0.bfloat16().float()).abs().max().item() <= 2e-2 * y0.abs().max().item() / 2      # within an ulp or two of the fp32 path

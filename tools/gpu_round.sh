@@ -22,4 +22,12 @@ for r in prof_step prof_train; do
     sz=$(stat -c %s gpurun_out/$r.ncu-rep); if [ "$sz" -gt 25000000 ]; then rm -f gpurun_out/$r.ncu-rep; fi
   fi
 done
+[ -f gpurun_out/prof_step_raw.csv ] && python tools/traffic_from_ncu.py gpurun_out/prof_step_raw.csv conv_tc_kernel gpurun_out/conv_tc_traffic.json \
+  "ncu --set full --clock-control none -k regex:conv_tc_kernel|attention -s 36 -c 17 python tools/profile_step.py 4"
+# config-2 VAE round trip: launch list with DRAM bytes (eval and train mode)
+for m in eval train; do
+  timeout 300 python tools/profile_vae.py $m 3 > /dev/null 2>&1 && \
+  timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
+    --log-file gpurun_out/vae_${m}_launches.csv python tools/profile_vae.py $m 3 > /dev/null 2>&1
+done
 du -sh gpurun_out | tee -a gpurun_out/rc.txt
