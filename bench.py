@@ -557,9 +557,9 @@ def run_cuda(args):
         ae = None if (args.no_train or world > 1) else ae_leg(sd, dev, args.precision)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, threads, dt = cpu_transfer_timing(2)
+            v, threads, dt = cpu_transfer_timing(10)
             cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                   "sample": f"2 full config-3 calls (batch 64, 49 UNet+DDIM steps + VAE/style passes) of the oracle port, fp32, {dt:.1f} s"}
+                   "sample": f"10 full config-3 calls (batch 64, 49 UNet+DDIM steps + VAE/style passes) of the oracle port, fp32, {dt:.1f} s"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -591,8 +591,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps is None:
-            args.steps = 2
-        args.steps = min(args.steps, 4)      # each step is ~5-10 s of CPU work: keep the run within minutes
+            args.steps = 10
+        args.steps = min(args.steps, 20)     # each step (one full config-3 call) is ~1 s on 16 host cores: 10-20 s of CPU work
         run_reference(args)
     else:
         if args.steps is None:
