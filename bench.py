@@ -206,6 +206,8 @@ def vae_leg(sd, dev, peaks, precision, reps=20):
     epilogue + one normalise pass).  achieved = SURVEY 8(d)'s minimal traffic / device time."""
     import torch
     import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200 import model as Mo
+    Mo.set_bn_sync_group(None, 1)        # this leg runs on rank 0 alone: train-mode BatchNorm must not all-reduce its statistics
     enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
     enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
     dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
@@ -314,6 +316,8 @@ def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True
         extra = train_rooflines(model, per, dev)
     del tr, model
     torch.cuda.empty_cache()
+    from music_style_transfer_ldm_b200 import model as Mo
+    Mo.set_bn_sync_group(None, 1)        # the trainer switched BatchNorm to global-batch statistics; later legs are per rank
     return {"metric": "train_samples_per_s", "value": gb * steps / (ms * 1e-3), "unit": "samples/s",
             "ms_per_step": ms / steps, "steps": steps, "global_batch": gb, "batch_per_gpu": per,
             "scaling": "strong" if gb == TRAIN_GLOBAL_BATCH else "weak",
