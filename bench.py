@@ -557,7 +557,8 @@ def run_cuda(args):
             pass
         with torch.no_grad():
             roof, rows = kernel_roofline(model, peaks)
-        vae = None if args.no_vae else vae_leg(sd, dev, peaks, args.precision)
+        # single-GPU measurements (config 2 and the autoencoder stage do not shard): skipped in the N > 1 scaling runs
+        vae = None if (args.no_vae or world > 1) else vae_leg(sd, dev, peaks, args.precision)
         ae = None if (args.no_train or world > 1) else ae_leg(sd, dev, args.precision)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
