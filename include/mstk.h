@@ -225,28 +225,6 @@ int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, in
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------
- * Layer programs: the 49 x 17 dependent layers of a sampling loop (models/model.py:503-559)
- * as ONE persistent cooperative kernel (one CTA per SM, device-wide barrier between layers)
- * instead of 833 launches.  Between mstk_program_begin and mstk_program_end the calling
- * thread's mstk_conv2d_fwd (tcgen05 path only) and mstk_attention_fwd calls are RECORDED
- * into the caller's host table (mstk_program_op_bytes() bytes per op, 128-byte aligned)
- * instead of launched; any other entry point still launches.  The caller copies the table
- * to device memory and runs a contiguous op range with mstk_program_run.  dev_sync: two
- * zero-initialised uint32 in device memory (barrier state, left reusable).  All tensors
- * named by recorded ops must stay alive and in place while the program is in use.
- * ------------------------------------------------------------------------------ */
-typedef struct mstk_program_info {
-    int32_t nops;        /* ops recorded                                   */
-    int32_t smem_bytes;  /* dynamic shared memory the program kernel needs */
-    int32_t tmem_cols;   /* TMEM columns it allocates                      */
-} mstk_program_info;
-size_t mstk_program_op_bytes(void);
-int mstk_program_begin(void* host_ops, int max_ops);
-int mstk_program_end(mstk_program_info* info);
-int mstk_program_run(const void* dev_ops, const mstk_program_info* info, int first_op, int nops,
-                     unsigned int* dev_sync, void* stream);
-
-/* ------------------------------------------------------------------------------
  * Mel front end (data/audio_processor.py:44-73 -> librosa.feature.melspectrogram +
  * power_to_db(ref=np.max) + the uint8 image quantisation):
  * wave [b, len] fp32 -> frames (n_fft 2048, hop 512, periodic Hann, centre zero pad)

@@ -58,10 +58,6 @@ class MelArgs(C.Structure):
                 ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int)]
 
 
-class ProgramInfo(C.Structure):
-    _fields_ = [("nops", c_int), ("smem_bytes", c_int), ("tmem_cols", c_int)]
-
-
 class WgradArgs(C.Structure):
     _fields_ = [("x", c_void_p), ("dy", c_void_p), ("dw", c_void_p),
                 ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int), ("ksize", c_int),
@@ -109,10 +105,6 @@ SIGNATURES = {
     "mstk_mse": (c_int, [c_void_p, c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_void_p]),
     "mstk_kl": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "mstk_feature_std_mse": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_float, c_void_p, c_void_p]),
-    "mstk_program_op_bytes": (c_size_t, []),
-    "mstk_program_begin": (c_int, [c_void_p, c_int]),
-    "mstk_program_end": (c_int, [C.POINTER(ProgramInfo)]),
-    "mstk_program_run": (c_int, [c_void_p, C.POINTER(ProgramInfo), c_int, c_int, c_void_p, c_void_p]),
     "mstk_sample_stats": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "mstk_feature_mse3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
                                   c_void_p, c_void_p, c_void_p]),

@@ -1,6 +1,9 @@
 """In-tree build of libmstk.so for sm_100a (nvcc cross-compiles without a GPU).
 
-    python -m music_style_transfer_ldm_b200.build [--force]
+    python -m music_style_transfer_ldm_b200.build [--force] [-v]
+
+Every csrc/*.cu is compiled to its own object (in parallel, re-compiled only when it or a header
+it can include changed) under csrc/_obj/, then linked into libmstk.so next to this file.
 """
 from __future__ import annotations
 
@@ -8,36 +11,62 @@ import glob
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(CSRC, "_obj")
 OUT = os.path.join(HERE, "libmstk.so")
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-cudart", "static",
-              "-Xcompiler", "-fPIC", "-shared"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+LINK_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static", "-shared", "-Xcompiler", "-fPIC"]
 
 
 def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+def headers():
+    return sorted(glob.glob(os.path.join(CSRC, "*.cuh"))) + [os.path.join(HERE, "..", "include", "mstk.h")]
+
+
+def _obj_of(src: str) -> str:
+    return os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
+
+
+def _stale(target: str, deps) -> bool:
+    if not os.path.isfile(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
 def up_to_date() -> bool:
-    if not os.path.isfile(OUT):
-        return False
-    t = os.path.getmtime(OUT)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(HERE, "..", "include", "mstk.h")]
-    return all(os.path.getmtime(d) <= t for d in deps)
+    return not _stale(OUT, sources() + headers())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return OUT
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + sources()
+    os.makedirs(OBJ, exist_ok=True)
+    hdrs = headers()
+    todo = [s for s in sources() if force or _stale(_obj_of(s), [s] + hdrs)]
+
+    def compile_one(src):
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", _obj_of(src), src]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        return src, cmd, r
+
+    with ThreadPoolExecutor(max_workers=min(len(todo) or 1, os.cpu_count() or 4)) as ex:
+        for src, cmd, r in ex.map(compile_one, todo):
+            if r.returncode != 0:
+                raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+            if verbose:
+                print(r.stderr)
+    cmd = [nvcc] + LINK_FLAGS + ["-o", OUT] + [_obj_of(s) for s in sources()]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("link failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     return OUT
 
 

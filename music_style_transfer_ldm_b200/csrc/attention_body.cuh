@@ -1,4 +1,4 @@
-// Softmax attention core shared by the stand-alone kernel (elementwise.cu) and the layer-program kernel (program.cu).
+// Softmax attention core of the stand-alone attention kernel (elementwise.cu).
 #pragma once
 #include "common.cuh"
 
@@ -70,8 +70,6 @@ __device__ __forceinline__ void attention_unit(const AttnP& a, const int bh, con
     }
 }
 
-
-int prog_record_attn(const AttnP& a);
 
 __host__ __device__ inline size_t attn_smem_floats(int s, int d, int nwarps) {
     return (size_t)s * (d + 1) + (size_t)s * d + (size_t)nwarps * s + (size_t)nwarps * d;

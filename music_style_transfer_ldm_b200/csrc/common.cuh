@@ -93,8 +93,6 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
 bool conv_tc_supported(const ConvP& p);
 size_t conv_tc_workspace_bytes(const ConvP& p);
 bool tc_init();
-// layer-program recorder (program.cu): true while the calling thread records instead of launching
-bool prog_recording();
 // vectorised feature-loss kernels (feature_loss.cu)
 bool feat_vec_ok(const void* f, int dtype, long long inner);
 int launch_sample_stats(const void* f, int dtype, int samples, long long inner, double* stats, cudaStream_t st);

@@ -109,10 +109,6 @@ int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     if (rc != MSTK_OK) return rc;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int backend = a->backend;
-    if (mstk::prog_recording() && !(backend != MSTK_BACKEND_SIMT && mstk::conv_tc_supported(p) && !(backend == MSTK_BACKEND_AUTO && mstk::conv_edge_supported(p)))) {
-        mstk::set_error("conv: only tcgen05 convolutions can be recorded into a layer program (dtype=%d cin=%d cout=%d)", p.dtype, p.Cin, p.Cout);
-        return MSTK_EUNSUPPORTED;
-    }
     if (backend == MSTK_BACKEND_AUTO) {
         if (mstk::conv_edge_supported(p)) return mstk::launch_conv_edge(p, st);
         backend = mstk::conv_tc_supported(p) ? MSTK_BACKEND_TCGEN05 : MSTK_BACKEND_SIMT;

@@ -318,8 +318,8 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     TcParams q;
     memset(&q, 0, sizeof(q));
     q.p = p;
-    // opt-in: split-K partners as one thread-block cluster (portable size <= 8); never in recorded layer programs
-    q.cluster = (c.splitk > 1 && c.splitk <= 8 && g_cluster && !prog_recording()) ? 1 : 0;
+    // opt-in: split-K partners as one thread-block cluster (portable size <= 8)
+    q.cluster = (c.splitk > 1 && c.splitk <= 8 && g_cluster) ? 1 : 0;
     if (c.splitk > 1 && !q.cluster) {
         size_t ws, ctr;
         ws_sizes(p, c, &ws, &ctr);
@@ -428,8 +428,7 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
     uint32_t picked = F_ALL;
     for (int i = 0; i < kNumVariants; ++i)
         if (kVariants[i].flags == need) { fn = kVariants[i].fn; picked = need; break; }
-    if (prog_recording())
-        return prog_record_conv(maps, q, picked, (int)cfg.gridDim.x, (int)cfg.gridDim.y, (int)cfg.gridDim.z, c.smem_bytes);
+    (void)picked;
     cudaError_t e = cudaLaunchKernelEx(&cfg, fn, maps, q);
     if (e != cudaSuccess) return cuda_fail(e, "conv_tc launch");
     return MSTK_OK;

@@ -651,7 +651,4 @@ __device__ __forceinline__ void conv_tc_body(const TcMaps& maps, const TcParams&
     }
 }
 
-// program.cu: append a fully resolved launch to the program being recorded
-int prog_record_conv(const TcMaps& maps, const TcParams& q, uint32_t flags, int gx, int gy, int gz, size_t smem_bytes);
-
 }  // namespace mstk

@@ -624,7 +624,6 @@ int mstk_attention_fwd(const mstk_attn_args* a, void* stream) {
     AttnP p;
     p.q = a->q; p.k = a->k; p.v = a->v; p.out = a->out; p.b = a->b; p.l = a->l; p.s = a->s; p.e = a->e; p.heads = a->heads;
     p.qs = a->q_stride; p.ks = a->k_stride; p.vs = a->v_stride; p.os = a->out_stride; p.dtype = a->dtype;
-    if (prog_recording()) return prog_record_attn(p);
     const int d = a->e / a->heads;
     {
         // block kernel: 16-byte staging loads need aligned rows; everything else takes the warp-per-query kernel below

@@ -468,8 +468,6 @@ class LDM(_Kernelised):
         self.num_timesteps = num_timesteps
         self.feature_loss_net = VGGishFeatureLoss()
         self.use_cuda_graphs = True
-        self.use_programs = False         # sampling loop as ONE persistent layer-program kernel (ops.Program): correct, but
-                                          # measured slower than the PDL-chained CUDA graph, so opt-in
         self.collect_sampling_logs = False
 
         if pretrained_path:
@@ -583,36 +581,6 @@ class LDM(_Kernelised):
             self.unet._forward_nhwc(x_lp if x_lp is not None else x, temb[i], kv2, kv1, ddim=d, want_eps=logs is not None,
                                     eps_out=logs["noise_pred"][i] if logs is not None else None)
 
-    def _run_loop_program(self, z_t, s5, s6, times: List[int], eta: float, logs):
-        """The N-1 UNet + DDIM steps as ONE persistent kernel launch (ops.Program): the per-step layers are recorded
-        once per (shapes, schedule, weights) and replayed; style K/V projections, the bf16 shadow of x and the
-        time-embedding table are refreshed by a handful of ordinary launches before it."""
-        adt = _act_dtype(self._precision())
-        nsteps = len(times) - 1
-        b = z_t.shape[0]
-        key = (tuple(z_t.shape), tuple(s5.shape), tuple(s6.shape), s5.dtype, tuple(times), float(eta), logs is not None)
-        progs = self.__dict__.setdefault("_programs", {})
-        sig = self._weights_sig()
-        ent = progs.get(key)
-        if ent is None or ent["sig"] != sig:
-            x = z_t.clone()
-            x_lp = torch.empty(x.shape, dtype=adt, device=x.device)
-            kv2, kv1 = self.unet._project_style(s5, s6)
-            temb = self.unet._time_embedding(self._step_times(times, b, z_t.device)).view(nsteps, b, -1)
-            with ops.Program(z_t.device, nsteps * 20 + 8) as prog:
-                self._loop_steps(x, x_lp, temb, kv2, kv1, times, eta, logs)
-            ent = {"sig": sig, "x": x, "x_lp": x_lp, "kv2": kv2, "kv1": kv1, "temb": temb, "logs": logs, "prog": prog}
-            if len(progs) >= 4:
-                progs.clear()
-            progs[key] = ent
-        else:
-            kv2, kv1 = self.unet._project_style(s5, s6)
-            ent["kv2"].copy_(kv2); ent["kv1"].copy_(kv1)
-        ent["x"].copy_(z_t)
-        ops.cast(ent["x"], adt, out=ent["x_lp"])
-        ent["prog"].run()
-        return ent["x"].clone(), ent["logs"]
-
     def _weights_sig(self):
         return tuple((p.data_ptr(), p._version) for p in list(self.unet.parameters()) + [self.noise_scheduler.alpha_bar_t])
 
@@ -627,9 +595,6 @@ class LDM(_Kernelised):
                     "noise_pred": torch.empty((nsteps,) + tuple(z_t.shape), dtype=torch.float32, device=z_t.device)}
         if nsteps <= 0:
             return z_t.clone(), logs
-        if (self.use_programs and self.use_cuda_graphs and self._precision() == "bf16"
-                and not torch.cuda.is_current_stream_capturing()):
-            return self._run_loop_program(z_t, s5, s6, times, eta, logs)
         if not self.use_cuda_graphs or torch.cuda.is_current_stream_capturing():
             return self._loop_body(z_t.clone(), s5, s6, times, eta, logs, self._step_times(times, b, z_t.device)), logs
         key = (tuple(z_t.shape), tuple(s5.shape), tuple(s6.shape), s5.dtype, tuple(times), float(eta), self._precision(),

@@ -55,72 +55,7 @@ RECORD = None
 
 def _count(n: int = 1) -> None:
     global LAUNCHES
-    if _PROGRAM is not None:        # recorded into a layer program, not launched
-        return
     LAUNCHES += n
-
-
-# ------------------------------------------------------------------------------------------
-# layer programs (include/mstk.h "Layer programs"): record conv / attention calls, run them as ONE
-# persistent cooperative kernel
-# ------------------------------------------------------------------------------------------
-_PROGRAM = None
-
-
-class Program:
-    """with Program(device, max_ops) as prog: <ops.conv / ops.attention calls are recorded, not launched>
-    prog.run() then executes the recorded ops in order inside one kernel launch.  Every tensor touched by a
-    recorded op is kept alive by the program (the ops hold raw pointers)."""
-
-    def __init__(self, device, max_ops: int):
-        self.lib = _lib.load()
-        self.device = torch.device(device)
-        self.max_ops = int(max_ops)
-        self.op_bytes = int(self.lib.mstk_program_op_bytes())
-        raw = torch.empty(self.max_ops * self.op_bytes + 128, dtype=torch.uint8)
-        off = (-raw.data_ptr()) % 128
-        self._host = raw[off:off + self.max_ops * self.op_bytes]
-        self.info = _lib.ProgramInfo()
-        self.keep = []
-        self.dev_ops = None
-        self.sync = None
-
-    def __enter__(self):
-        global _PROGRAM
-        if _PROGRAM is not None:
-            raise MstkError("Program: already recording")
-        check(self.lib.mstk_program_begin(self._host.data_ptr(), self.max_ops), "mstk_program_begin")
-        _PROGRAM = self
-        return self
-
-    def __exit__(self, et, ev, tb):
-        global _PROGRAM
-        _PROGRAM = None
-        rc = self.lib.mstk_program_end(C.byref(self.info))
-        if et is None:
-            check(rc, "mstk_program_end")
-            n = self.info.nops * self.op_bytes
-            self.dev_ops = self._host[:n].to(self.device)
-            if self.dev_ops.data_ptr() % 128:
-                raise MstkError("Program: device table is not 128-byte aligned")
-            self.sync = torch.zeros(2, dtype=torch.int32, device=self.device)
-        self._host = None
-        return False
-
-    @property
-    def nops(self) -> int:
-        return int(self.info.nops)
-
-    def run(self, first: int = 0, n: Optional[int] = None) -> None:
-        global LAUNCHES
-        n = self.nops - first if n is None else n
-        check(self.lib.mstk_program_run(_p(self.dev_ops), C.byref(self.info), first, n, _p(self.sync), _stream()), "mstk_program_run")
-        LAUNCHES += 1
-
-
-def _keep(*tensors) -> None:
-    if _PROGRAM is not None:
-        _PROGRAM.keep.extend(t for t in tensors if t is not None)
 
 
 def tc_eligible(dtype, cin: int, cout: int, stride: int, transposed: bool, h: int, w: int) -> bool:
@@ -208,7 +143,6 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
                       dtype_code(x), dtype_code(out_dtype), backend)
     check(lib.mstk_conv2d_fwd(C.byref(a), _stream()), "mstk_conv2d_fwd")
     _count()
-    _keep(x, wpacked, bias, y, add, add_nc, stats, ws, *( (ddim.x_cur, ddim.x_next, ddim.x_next_lp, ddim.x0_pred) if ddim is not None else ()))
     if RECORD is not None:
         use_tc = backend == BACKEND_TCGEN05 or (backend == BACKEND_AUTO and tc_eligible(x.dtype, cin, cout, stride, transposed, h, w))
         keep = (x, wpacked, bias, y, add, add_nc, stats, ddim, dd, ws)
@@ -319,7 +253,6 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
                       dtype_code(q))
     check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd")
     _count(1)
-    _keep(q, k, v, out)
     return out
 
 
