@@ -105,6 +105,14 @@ class _BnFold:
         return mod._cached((name, "fold", dtype), deps, build)
 
 
+def _drop_fold(mod: _Kernelised, name: str) -> None:
+    """a train-mode pass moves running_mean / running_var through raw pointers: the eval fold is stale"""
+    cache = mod.__dict__.get("_mstk_cache")
+    if cache:
+        for k in [k for k in cache if isinstance(k, tuple) and len(k) == 3 and k[0] == name and k[1] == "fold"]:
+            del cache[k]
+
+
 def _conv_bn(mod: _Kernelised, name: str, conv, bn: nn.BatchNorm2d, x: torch.Tensor, *, w_dtype, mid_dtype, out_dtype,
              act, transposed: bool, ksize: int, first_layer: bool = False) -> torch.Tensor:
     """conv (or convT) + BatchNorm2d (+ReLU).  Train mode: batch statistics gathered in the
@@ -114,6 +122,7 @@ def _conv_bn(mod: _Kernelised, name: str, conv, bn: nn.BatchNorm2d, x: torch.Ten
         wp, bias = _BnFold.get(mod, name, conv, bn, w_dtype, transposed)
         return ops.conv(x, wp, bias, ksize=ksize, stride=2, transposed=transposed, act=act, out_dtype=out_dtype)
     cout = bn.num_features
+    _drop_fold(mod, name)
     stats = torch.zeros(2 * cout, dtype=torch.float64, device=x.device)
     wp = mod._packed(name, conv.weight, w_dtype, transposed)
     y = ops.conv(x, wp, mod._f32(name + ".b", conv.bias), ksize=ksize, stride=2, transposed=transposed, act=ACT_NONE,
@@ -130,13 +139,36 @@ def _conv_bn(mod: _Kernelised, name: str, conv, bn: nn.BatchNorm2d, x: torch.Ten
     return out
 
 
-# data-parallel hook: when a process group is active the per-channel (sum, sumsq) are
-# all-reduced so that every rank normalises with the GLOBAL batch statistics.
+# data-parallel hook: inside ``with bn_sync_group(group, world)`` the per-channel (sum, sumsq) of every
+# train-mode BatchNorm are all-reduced so that each rank normalises with the GLOBAL batch statistics
+# (SURVEY 8e).  The trainers open the scope around their own step only: a module forward outside a
+# training step (a rank-0-only sample or validation pass) never issues a collective.
 _BN_GROUP = {"group": None, "world": 1}
 
 
-def set_bn_sync_group(group, world_size: int) -> None:
-    _BN_GROUP["group"], _BN_GROUP["world"] = group, int(world_size)
+class bn_sync_group:
+    def __init__(self, group, world_size: int):
+        self.new = (group, int(world_size))
+
+    def __enter__(self):
+        self.old = (_BN_GROUP["group"], _BN_GROUP["world"])
+        _BN_GROUP["group"], _BN_GROUP["world"] = self.new
+        return self
+
+    def __exit__(self, *exc):
+        _BN_GROUP["group"], _BN_GROUP["world"] = self.old
+        return False
+
+
+def invalidate_packed(root: nn.Module, keep=()) -> None:
+    """Parameters / buffers under ``root`` were rewritten through raw pointers (the trainers' fused Adam, a
+    train-mode BatchNorm's running buffers), which torch's version counters do not see: drop every packed
+    copy and every captured sampling graph that holds one."""
+    for m in root.modules():
+        if any(m is k for k in keep):
+            continue
+        m.__dict__.pop("_mstk_cache", None)
+        m.__dict__.pop("_graphs", None)
 
 
 def _bn_world() -> int:
@@ -166,6 +198,7 @@ class SpectrogramEncoder(_Kernelised):
         adt = _act_dtype(self._precision())
         if e[1].training:
             cout = e[1].num_features
+            _drop_fold(self, "c0")
             stats = torch.zeros(2 * cout, dtype=torch.float64, device=x.device)
             y = _first_layer_conv(self, "c0", e[0], x, adt, ACT_NONE, stats=stats)
             stats = _sync_bn_stats(stats)

@@ -253,6 +253,14 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
                       dtype_code(q))
     check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd")
     _count(1)
+    if RECORD is not None:
+        keep = (q, k, v, out)
+
+        def replay(a=a, keep=keep):
+            check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd(replay)")
+
+        RECORD.append(dict(kernel="attention_block_kernel", replay=replay, flops=4.0 * b * l * s * e,
+                           tag=f"attention core b{b} l{l} s{s} e{e} h{heads}"))
     return out
 
 

@@ -186,6 +186,7 @@ class LDMTrainer:
         self._graph = None
         self._eager_steps = 0
         self.group, self.world = process_group, int(world_size)
+        self._gen = None
         if self.device.type != "cuda":
             raise MstkError("LDMTrainer: the training step runs on sm_100a kernels only (no CPU fallback)")
         order = _backward_order(self.model)
@@ -194,13 +195,11 @@ class LDMTrainer:
             raise MstkError("LDMTrainer: expected exactly decoder + unet + style_encoder to be trainable (the reference freezes the "
                             "encoder, model.py:340-341, and VGGishFeatureLoss is frozen); call model._freeze_encoder() first")
         self.arena = _Arena(order, self.device)
-        for m in self.model.modules():                        # packed-weight caches point at the old storages
-            m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(self.model)                      # packed-weight caches point at the old storages
         # gradient buckets for the data-parallel all-reduce, in backward-completion order
         self.buckets = bucket_spans(self.model, self.arena, num_buckets)
         self.reducer = GradReducer(self.arena.g, self.buckets, self.group, self.world)
         if self.world > 1:
-            Mo.set_bn_sync_group(self.group, self.world)
             import torch.distributed as dist
             dist.broadcast(self.arena.p, src=0, group=self.group)        # identical replicas
             for b in self.model.buffers():                                # BatchNorm running buffers
@@ -248,7 +247,11 @@ class LDMTrainer:
             print(f"Compression Loss: {losses[1]:.4f}")
             print(f"Denoisinsg Loss: {losses[2]:.4f}")
             print(f"Style Loss: {losses[3]:.4f}")
-            if epoch % 100 == 0 and self.checkpoint_dir is not None:
+            rank0 = True
+            if self.world > 1:
+                import torch.distributed as dist
+                rank0 = dist.get_rank(self.group) == 0                  # identical replicas: one writer
+            if epoch % 100 == 0 and self.checkpoint_dir is not None and rank0:
                 import os
                 os.makedirs(self.checkpoint_dir, exist_ok=True)
                 torch.save(self.model.state_dict(), os.path.join(self.checkpoint_dir, f"ldm_{epoch}.pth"))
@@ -342,9 +345,10 @@ class LDMTrainer:
 
     # -- the step ---------------------------------------------------------------------------
     def train_step_device(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
-        """Public device-side step: eager for the first steps / explicit t, noise; afterwards a CUDA-graph replay."""
-        if (not self.use_cuda_graph or t is not None or noise is not None or not content_spec.is_cuda
-                or torch.cuda.is_current_stream_capturing()):
+        """Public device-side step: eager for the first ``graph_warmup`` steps, afterwards a CUDA-graph replay.  The
+        captured step reads t and the noise from static buffers: they are drawn (or, when passed in, copied) outside
+        the graph, so the replayed step is the same function of (content, style, t, noise) as the eager one."""
+        if not self.use_cuda_graph or not content_spec.is_cuda or torch.cuda.is_current_stream_capturing():
             return self._step_impl(content_spec, style_spec, t, noise)
         key = (tuple(content_spec.shape), tuple(style_spec.shape), self.model._precision())
         if self._graph is not None and self._graph["key"] != key:
@@ -353,14 +357,18 @@ class LDMTrainer:
         if self._graph is None:
             if self._eager_steps < self.graph_warmup:
                 self._eager_steps += 1
-                return self._step_impl(content_spec, style_spec, None, None)
+                return self._step_impl(content_spec, style_spec, t, noise)
+            B, H, W = content_spec.shape[0], content_spec.shape[2], content_spec.shape[3]
+            lat = self.model.encoder.encoder[6].out_channels
             ent = {"key": key, "x": content_spec.detach().float().contiguous().clone(),
-                   "s": style_spec.detach().float().contiguous().clone()}
+                   "s": style_spec.detach().float().contiguous().clone(),
+                   "t": torch.zeros((B,), dtype=torch.int64, device=self.device),
+                   "noise": torch.zeros((B, lat, H // 8, W // 8), dtype=torch.float32, device=self.device)}
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             n0, c0 = ops.LAUNCHES, self.step_count
             with torch.cuda.graph(g):
-                ent["out"] = self._step_impl(ent["x"], ent["s"], None, None)
+                ent["out"] = self._step_impl(ent["x"], ent["s"], ent["t"], ent["noise"])
             ent["launches"] = ops.LAUNCHES - n0
             ops.LAUNCHES, self.step_count = n0, c0          # capture enqueued nothing
             ent["graph"] = g
@@ -368,15 +376,40 @@ class LDMTrainer:
         ent = self._graph
         ent["x"].copy_(content_spec)
         ent["s"].copy_(style_spec)
+        if t is None or noise is None:
+            t_d, noise_d = self._draw(*ent["noise"].shape)
+            t = t_d if t is None else t
+            noise = noise_d if noise is None else noise
+        ent["t"].copy_(t)
+        ent["noise"].copy_(noise)
         ent["graph"].replay()
         self.step_count += 1
         ops._count(ent["launches"])
-        for m in self.model.modules():                       # parameters changed under any packed copies made outside the graph
-            if m is not self.model.feature_loss_net:
-                m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(self.model, keep=(self.model.feature_loss_net,))   # parameters changed under packed copies / captured sampling graphs
         return ent["out"]
 
     def _step_impl(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        # BatchNorm statistics are global-batch statistics INSIDE the step only (Mo.bn_sync_group): module forwards
+        # outside a training step never all-reduce
+        with Mo.bn_sync_group(self.group, self.world):
+            return self._step_body(content_spec, style_spec, t, noise)
+
+    def _draw(self, B: int, c: int, h: int, w: int):
+        """t ~ randint(0, T) (train.py:172) and eps ~ randn (model.py:110) for this rank's shard.  Single process: torch's
+        default CUDA generator, as the reference.  Data parallel: a per-rank generator (seed = initial seed + 1 + rank), so
+        that the shards of one global batch do not repeat the same timesteps / noise."""
+        gen = None
+        if self.world > 1:
+            if self._gen is None:
+                import torch.distributed as dist
+                self._gen = torch.Generator(device=self.device)
+                self._gen.manual_seed(torch.initial_seed() + 1 + dist.get_rank(self.group))
+            gen = self._gen
+        t = torch.randint(0, self.model.num_timesteps, (B,), device=self.device, generator=gen)
+        noise = torch.randn((B, c, h, w), dtype=torch.float32, device=self.device, generator=gen)
+        return t, noise
+
+    def _step_body(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         """One optimisation step on this rank's shard.  ``t`` [B] int64 and ``noise`` [B,C,h,w] (NCHW, the reference's
         randn_like shape) may be passed in (parity tests, data-parallel sharding of a globally drawn batch); otherwise
         they are drawn as the reference does (train.py:172, model.py:110).  Returns the four losses as 0-dim tensors."""
@@ -392,16 +425,17 @@ class LDMTrainer:
         dev, B = xs.device, xs.shape[0]
         ab = model.noise_scheduler.alpha_bar_t
         self.arena.g.zero_()                                                     # optimizer.zero_grad()
-        if t is None:
-            t = torch.randint(0, model.num_timesteps, (B,), device=dev)
+        if t is None or noise is None:
+            lat = model.encoder.encoder[6].out_channels
+            t_d, noise_d = self._draw(B, lat, xs.shape[1] // 8, xs.shape[2] // 8)
+            t = t_d if t is None else t
+            noise = noise_d if noise is None else noise
         t = t.to(device=dev, dtype=torch.int64).contiguous()
 
         # ================= forward (LDM.forward, model.py:355-379), intermediates kept =================
         z0 = model.encoder._forward_nhwc(xs)                                     # frozen; BatchNorm in train mode (train.py:212)
         _, h, w, c = z0.shape
         S = sty._forward_nhwc(ss)                                                # six post-ReLU maps
-        if noise is None:
-            noise = torch.randn((B, c, h, w), dtype=torch.float32, device=dev)
         noise_l = ops.nchw_to_nhwc(noise.to(dev).float().contiguous(), torch.float32)
         z_t, z_t_lp = ops.q_sample(z0, noise_l, ab, t, lp=lp)
         zin = z_t_lp if lp else z_t
@@ -503,9 +537,7 @@ class LDMTrainer:
         self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
                       eps=self.eps, step=self.step_dev, grad_scale=1.0 / self.world)
-        for m in model.modules():                       # parameters changed under the packed copies
-            if m is not fl:
-                m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(model, keep=(fl,))         # parameters changed under the packed copies / captured sampling graphs
         losses = torch.stack([comp, den, styl.squeeze(0), total])
         if self.world > 1:                              # report the GLOBAL batch's losses (equal shards: mean of the ranks' means)
             self.reducer.all_reduce_small(losses)
@@ -564,8 +596,7 @@ class AutoencoderTrainer:
         if not all(p.requires_grad for p in order):
             raise MstkError("AutoencoderTrainer: every encoder / decoder parameter must require grad (train.py:47)")
         self.arena = _Arena(order, self.device)
-        for m in list(self.encoder.modules()) + list(self.decoder.modules()):
-            m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(self.encoder); Mo.invalidate_packed(self.decoder)
 
     @property
     def lr(self) -> float:
@@ -607,8 +638,7 @@ class AutoencoderTrainer:
         ent["graph"].replay()
         self.step_count += 1
         ops._count(ent["launches"])
-        for m in list(self.encoder.modules()) + list(self.decoder.modules()):
-            m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(self.encoder); Mo.invalidate_packed(self.decoder)
         return ent["out"]
 
     def _step_impl(self, spectrogram) -> torch.Tensor:
@@ -676,8 +706,7 @@ class AutoencoderTrainer:
         self.step_dev.add_(1)
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
                       eps=self.eps, step=self.step_dev, weight_decay=self.weight_decay)
-        for m in list(enc.modules()) + list(dec.modules()):       # parameters changed under the packed copies
-            m.__dict__.pop("_mstk_cache", None)
+        Mo.invalidate_packed(enc); Mo.invalidate_packed(dec)      # parameters changed under the packed copies
         return loss
 
 

@@ -1,7 +1,8 @@
 """Functional fp32 CPU restatement of the reference's model / sampler / loss path.
 
 TEST INFRASTRUCTURE: imported only by tests/, __graft_entry__.smoke() and
-bench.py's CPU-baseline legs.  Never by the product package.
+bench.py's baseline legs (the CPU arm, and -- tensors moved to `cuda` -- the
+stock-PyTorch-on-this-GPU bar of SURVEY 8(d)).  Never by the product package.
 
 Every function takes a flat ``sd`` (an ``LDM.state_dict()``-shaped mapping, keys
 as in SURVEY.md Appendix A.1) so that the same weights can be pushed through
@@ -202,7 +203,7 @@ def style_encoder_fwd(sd: SD, s: Tensor, prefix: str = "style_encoder.") -> Dict
 def sinusoidal_embedding(t: Tensor, dim: int = 128) -> Tensor:
     """SinusoidalPositionEmbeddings.forward (model.py:239-246)."""
     half = dim // 2
-    freq = torch.exp(torch.arange(half) * -(math.log(10000) / (half - 1)))
+    freq = torch.exp(torch.arange(half, device=t.device) * -(math.log(10000) / (half - 1)))
     arg = t[:, None] * freq[None, :]
     return torch.cat((arg.sin(), arg.cos()), dim=-1)
 
@@ -302,7 +303,7 @@ def ddim_sample(sd: SD, z_t: Tensor, style: Dict[str, Tensor], times: List[int],
     B = z_t.shape[0]
     for i in range(len(times) - 1):
         t, t_next = times[i], times[i + 1]
-        tb = torch.full((B,), t, dtype=torch.long)
+        tb = torch.full((B,), t, dtype=torch.long, device=z_t.device)
         eps_hat = unet_fwd(sd, x, tb, style)
         x, x0 = ddim_update(sd, x, eps_hat, t, t_next, eta)
         if logs is not None:
@@ -318,7 +319,7 @@ def content_style_transfer(sd: SD, content: Tensor, style_spec: Tensor, eps: Ten
     mode of encoder/decoder (BatchNorm statistics): the reference's scripts leave the
     freshly built model in train mode.  Returns (decoded in [0,1], z_t_decoded in [-1,1])."""
     z0 = encoder_fwd(sd, content.float(), training)
-    t = torch.full((content.shape[0],), num_timesteps - 1, dtype=torch.long)
+    t = torch.full((content.shape[0],), num_timesteps - 1, dtype=torch.long, device=content.device)
     z_t = q_sample(sd, z0, t, eps)
     style = style_encoder_fwd(sd, style_spec.float())
     x = ddim_sample(sd, z_t, style, ddim_times(num_timesteps - 1, num_timesteps), eta)

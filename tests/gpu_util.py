@@ -30,6 +30,11 @@ def rel_l2(got: torch.Tensor, ref) -> float:
     return (got - ref).norm().item() / (den if den > 0 else 1.0)
 
 
+# every whole-model comparison is recorded here; tests/conftest.py prints the table in the terminal summary
+# (also with -q), so a test log shows BOTH norms of every case, not only pass / fail
+REPORT = []
+
+
 def assert_close(got, ref, tol, what=""):
     e = rel_err(got, ref)
     assert e <= tol, f"{what}: relative error {e:.3e} > {tol:.1e}"
@@ -37,9 +42,11 @@ def assert_close(got, ref, tol, what=""):
 
 def assert_close_mode(got, ref, precision, what=""):
     """the parity bar of a whole-model output in the given precision mode (see TOL above)"""
-    if precision == "fp32":
-        return assert_close(got, ref, TOL["fp32"], what)
     e2, em = rel_l2(got, ref), rel_err(got, ref)
+    REPORT.append((what, precision, e2, em))
+    if precision == "fp32":
+        assert em <= TOL["fp32"], f"{what}: relative error {em:.3e} > {TOL['fp32']:.1e}"
+        return
     assert e2 <= TOL["bf16"], f"{what}: relative L2 error {e2:.3e} > {TOL['bf16']:.1e} (max-norm {em:.3e})"
     assert em <= BF16_MAX_GUARD, f"{what}: max-norm relative error {em:.3e} > {BF16_MAX_GUARD:.1e}"
 
