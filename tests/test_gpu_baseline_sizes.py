@@ -1,0 +1,181 @@
+"""-m gpu: the CUDA path against the CPU oracle at the EXACT sizes of BASELINE.json's configs
+(the goldens under tests/golden/ are small; these close the gap at the benchmark sizes):
+
+  config 3  content_style_transfer_wrapper(num_timesteps=50, eta=0) at batch 64: decoded, z_t_decoded,
+            the final latent and the per-step eps_hat at steps 1 / 25 / 49 (error growth over the 49
+            recurrent steps), fp32 (1e-4 max norm) and bf16 (2e-2 L2 norm) -- models/model.py:468-559
+  config 2  decoder(encoder(x)) for x [16,1,128,1024], eval-mode AND train-mode BatchNorm, both
+            precisions -- models/model.py:10-49
+  config 4  LDMTrainer.train_step at GLOBAL batch 256 for 3 steps against tests/golden/train_curve_b256.npz
+            (oracle/train_oracle.py, pinned to the unmodified reference trainer): fp32 1e-4, bf16 1 %;
+            the run also crosses from the eager step into the CUDA-graph capture and replay -- models/train.py:163-208
+
+The oracle runs on the box's host cores (seconds per case).
+"""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import make_golden_curve256 as G256
+from gpu_util import TOL, assert_close, assert_close_mode
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+PRECISIONS = ["fp32", "bf16"]
+
+
+def _ldm(sd, precision, train=False):
+    import music_style_transfer_ldm_b200 as M
+    m = M.LDM(latent_dim=32, pretrained_path=None)
+    m.load_state_dict(sd, strict=True)
+    m.to(DEV).train(train)
+    m.set_precision(precision)
+    return m
+
+
+class _fixed_randn_like:
+    def __init__(self, eps):
+        self.eps = eps
+
+    def __enter__(self):
+        self._real = torch.randn_like
+        torch.randn_like = lambda x, **kw: self.eps.to(device=x.device, dtype=x.dtype)
+        return self
+
+    def __exit__(self, *exc):
+        torch.randn_like = self._real
+        return False
+
+
+@pytest.fixture(scope="module")
+def config3_oracle(sd):
+    """one oracle run of config 3 (batch 64, 49 UNet + DDIM steps, eval-mode BatchNorm), shared by both precisions"""
+    from oracle import ldm_oracle as O
+    x, s, eps = cases.spec(171, 64), cases.spec(172, 64), cases.latent(173, 64)
+    with torch.no_grad():
+        z0 = O.encoder_fwd(sd, x, False)
+        t = torch.full((64,), 49, dtype=torch.long)
+        z_t = O.q_sample(sd, z0, t, eps)
+        style = O.style_encoder_fwd(sd, s)
+        logs = {}
+        xf = O.ddim_sample(sd, z_t, style, O.ddim_times(49, 50), 0.0, logs=logs)
+        dec = (O.decoder_fwd(sd, xf, False) + 1) / 2
+        ztd = O.decoder_fwd(sd, z_t, False)
+    return dict(x=x, s=s, eps=eps, z_t=z_t, x_final=xf, decoded=dec, z_t_decoded=ztd, timesteps=logs["timesteps"],
+                eps_hat={i: logs["noise_pred"][i] for i in (0, 24, 48)}, x0={i: logs["pred_x0"][i] for i in (0, 24, 48)})
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_config3_batch64_50_steps_vs_oracle(sd, config3_oracle, precision):
+    o = config3_oracle
+    m = _ldm(sd, precision)
+    with torch.no_grad():
+        with _fixed_randn_like(o["eps"]):
+            dec, ztd = m.content_style_transfer_wrapper(o["x"].to(DEV), o["s"].to(DEV), num_timesteps=50, eta=0.0)
+        assert dec.shape == (64, 1, 128, 128) and ztd.shape == (64, 1, 128, 128)
+        assert_close_mode(dec, o["decoded"], precision, "config3 decoded")
+        assert_close_mode(ztd, o["z_t_decoded"], precision, "config3 z_t_decoded")
+        # the inner loop with the reference's per-step logs: eps_hat after 1, 25 and 49 recurrent steps
+        m.collect_sampling_logs = True
+        emb = m.style_encoder(o["s"].to(DEV))
+        xf, logs = m.content_style_ddim_sample(o["z_t"].to(DEV), emb, timesteps=50, eta=0.0)
+    assert logs["timesteps"] == o["timesteps"] == list(range(49, 0, -1))
+    assert len(logs["noise_pred"]) == 49
+    for i in (0, 24, 48):
+        assert_close_mode(logs["noise_pred"][i], o["eps_hat"][i], precision, f"config3 eps_hat step {i + 1}")
+        assert_close_mode(logs["pred_x0"][i], o["x0"][i], precision, f"config3 pred_x0 step {i + 1}")
+    assert_close_mode(xf, o["x_final"], precision, "config3 final latent")
+
+
+@pytest.mark.parametrize("training", [False, True], ids=["eval", "train"])
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_config2_vae_16x128x1024_vs_oracle(sd, precision, training):
+    import music_style_transfer_ldm_b200 as M
+    from oracle import ldm_oracle as O
+    enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
+    enc.to(DEV).set_precision(precision).train(training)
+    dec.to(DEV).set_precision(precision).train(training)
+    x = cases.spec(131, 16, 128, 1024)
+    with torch.no_grad():
+        upd = {}
+        z_ref = O.encoder_fwd(sd, x, training, update=upd)
+        y_ref = O.decoder_fwd(sd, z_ref, training, update=upd)
+        z = enc(x.to(DEV))
+        y = dec(z)
+    assert z.shape == (16, 32, 16, 128) and y.shape == (16, 1, 128, 1024)
+    mode = "train" if training else "eval"
+    assert_close_mode(z, z_ref, precision, f"config2 latent ({mode} BN)")
+    assert_close_mode(y, y_ref, precision, f"config2 decoded ({mode} BN)")
+    if training:
+        cur = {"encoder." + k: v for k, v in enc.state_dict().items()}
+        cur.update({"decoder." + k: v for k, v in dec.state_dict().items()})
+        for k, v in upd.items():
+            if k.endswith("num_batches_tracked"):
+                assert int(cur[k]) == int(v)
+            else:
+                assert_close(cur[k], v, 10 * TOL[precision], k)
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+def test_config4_global_batch_256_vs_oracle_curve(sd, precision):
+    from music_style_transfer_ldm_b200.train import LDMTrainer
+    g = cases.load("train_curve_b256")["losses"]
+    m = _ldm(sd, precision, train=True)
+    m._freeze_encoder()
+    tr = LDMTrainer(m, None, torch.device(DEV), lr=G256.LR, style_loss_weight=G256.W)
+    m.train()
+    tr.graph_warmup = 1                      # step 0 eager, step 1 captures, step 2 replays: both paths against the oracle
+    keys = ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")
+    tol = 1e-4 if precision == "fp32" else 1e-2
+    worst = 0.0
+    for i in range(G256.STEPS):
+        x, s, t, eps = G256.step_inputs(i)
+        out = tr.train_step_device(x.to(DEV), s.to(DEV), t=t.to(DEV), noise=eps.to(DEV))
+        got = np.array([float(out[k]) for k in keys])
+        rel = np.abs(got - g[i]) / np.abs(g[i])
+        worst = max(worst, rel.max())
+        assert rel.max() <= tol, f"[{precision}] step {i}: losses {got} vs oracle {g[i]} (rel {rel})"
+    assert tr._graph is not None
+    print(f"config4 B=256 [{precision}]: worst relative loss deviation over {G256.STEPS} steps {worst:.3e}")
+
+
+def test_train_then_sample_uses_fresh_weights(sd):
+    """a captured sampling graph must not outlive the weights it packed.  Sample (graph captured), train a few
+    steps (raw-pointer Adam, no version bump), sample again: must equal an eager run on the trained weights."""
+    from music_style_transfer_ldm_b200.train import LDMTrainer
+    m = _ldm(sd, "bf16", train=True)
+    m._freeze_encoder()
+    z, st = cases.latent(181, 2), cases.style_dict(182, 2)
+    zd, std = z.to(DEV), {k: v.to(DEV) for k, v in st.items()}
+    with torch.no_grad():
+        before, _ = m.content_style_ddim_sample(zd, std, timesteps=6, eta=0.0)       # captures a graph
+        before2, _ = m.content_style_ddim_sample(zd, std, timesteps=6, eta=0.0)      # replays it
+    assert torch.equal(before, before2)
+    tr = LDMTrainer(m, None, torch.device(DEV), lr=5e-3, style_loss_weight=3.0)
+    m.train()
+    for i in range(4):
+        x, s = cases.spec(190 + i, 4), cases.spec(290 + i, 4)
+        tr.train_step_device(x.to(DEV), s.to(DEV))
+    with torch.no_grad():
+        after, _ = m.content_style_ddim_sample(zd, std, timesteps=6, eta=0.0)
+        m.use_cuda_graphs = False
+        eager, _ = m.content_style_ddim_sample(zd, std, timesteps=6, eta=0.0)
+    assert (after - before).abs().max().item() > 1e-3, "training did not move the sampler's output"
+    assert_close(after, eager, 1e-5, "graph sampling after training vs eager on the trained weights")
+
+
+def test_rank_local_forward_never_all_reduces(sd):
+    """BatchNorm statistics are all-reduced only inside a trainer's step.  No process group is ever
+    initialised here: a train-mode module forward must not touch torch.distributed at all, and the scope restores
+    itself on exit."""
+    from music_style_transfer_ldm_b200 import model as Mo
+    m = _ldm(sd, "bf16", train=True)
+    with Mo.bn_sync_group(None, 2):
+        assert Mo._bn_world() == 2
+    assert Mo._bn_world() == 1
+    with torch.no_grad():
+        dec, _ = m.content_style_transfer_wrapper(cases.spec(1, 2).to(DEV), cases.spec(2, 2).to(DEV), num_timesteps=3, eta=0.0)
+    assert torch.isfinite(dec).all()
