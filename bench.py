@@ -130,6 +130,8 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------
 def conv_flops(rec):
     """algorithmic FLOPs of one recorded conv call: 2 * output pixels * cout * cin * taps-per-output"""
+    if "flops" in rec:
+        return rec["flops"]
     n, h, w, cin, cout, k, s, tr = rec["n"], rec["h"], rec["w"], rec["cin"], rec["cout"], rec["ksize"], rec["stride"], rec["transposed"]
     if tr:
         # every input pixel meets every kernel tap exactly once
@@ -177,6 +179,22 @@ def kernel_roofline(model, peaks, reps=20):
     fl, us = sum(r["gflop"] for r in tc) * 1e9, sum(r["us"] for r in tc)
     peak = peaks.get("bf16_tflops", 1590.0)
     achieved = fl / (us * 1e-6) / 1e12 if us > 0 else 0.0
+    # the same step as ONE graph (what the sampling loop replays): PDL overlap = 1 - step / sum of isolated launches
+    with torch.cuda.stream(stream):
+        for r in recs:
+            r["replay"]()
+        stream.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=stream):
+            for _ in range(reps):
+                for r in recs:
+                    r["replay"]()
+        gr.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream); gr.replay(); e1.record(stream)
+        stream.synchronize()
+        chain_us = 1e3 * e0.elapsed_time(e1) / reps
+    iso_us = sum(r["us"] for r in rows)
     traffic, traffic_src = None, None
     try:        # dram bytes per launch from the committed ncu --set full capture (tools/traffic_from_ncu.py)
         with open(os.path.join(ROOT, "profiles", "conv_tc_traffic.json")) as f:
@@ -187,6 +205,8 @@ def kernel_roofline(model, peaks, reps=20):
     roof = {"bound": "tensor", "kernel": "conv_tc_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_unet_step": len(tc),
             "flop_per_launch_avg": fl / max(1, len(tc)), "us_per_launch_avg": us / max(1, len(tc)),
+            "launches_per_unet_step_all_kernels": len(rows), "sum_isolated_us_all_kernels": iso_us, "chained_step_us": chain_us,
+            "pdl_overlap_frac": 1.0 - chain_us / iso_us if iso_us > 0 else None,
             "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks else "fallback 1590 (B200_PROFILING.md)",
             "note": "achieved = sum of algorithmic conv FLOPs of the tcgen05 launches of one batch-64 UNet step / sum of their "
                     "isolated launch durations (each layer replayed 20x in a CUDA graph, CUDA events)"}
@@ -206,8 +226,6 @@ def vae_leg(sd, dev, peaks, precision, reps=20):
     epilogue + one normalise pass).  achieved = SURVEY 8(d)'s minimal traffic / device time."""
     import torch
     import music_style_transfer_ldm_b200 as M
-    from music_style_transfer_ldm_b200 import model as Mo
-    Mo.set_bn_sync_group(None, 1)        # this leg runs on rank 0 alone: train-mode BatchNorm must not all-reduce its statistics
     enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
     enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
     dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
@@ -316,8 +334,6 @@ def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True
         extra = train_rooflines(model, per, dev)
     del tr, model
     torch.cuda.empty_cache()
-    from music_style_transfer_ldm_b200 import model as Mo
-    Mo.set_bn_sync_group(None, 1)        # the trainer switched BatchNorm to global-batch statistics; later legs are per rank
     return {"metric": "train_samples_per_s", "value": gb * steps / (ms * 1e-3), "unit": "samples/s",
             "ms_per_step": ms / steps, "steps": steps, "global_batch": gb, "batch_per_gpu": per,
             "scaling": "strong" if gb == TRAIN_GLOBAL_BATCH else "weak",
@@ -453,6 +469,222 @@ def train_rooflines(model, per, dev):
 
 
 # ------------------------------------------------------------------------------------------
+# the bar on the same box: stock PyTorch (cuDNN / cuBLAS) running the reference's algorithm on the B200
+# ------------------------------------------------------------------------------------------
+def gpu_baseline(sd, dev, quick=False):
+    """SURVEY 8(d) / BASELINE.md section 3: the reference ships no kernels of its own, so the existing-GPU-implementation
+    bar is stock PyTorch executing the same modules on this B200.  The functional restatement (oracle/ldm_oracle.py,
+    pinned to the reference) is run with its tensors on `cuda`: (i) eager fp32 with torch's TF32 defaults, (ii) under
+    torch.autocast(bfloat16), (iii) (ii) captured in one torch.cuda.CUDAGraph.  Same config-3 / config-4 / config-2
+    inputs as the product legs, CUDA events, rank 0 only.  This measures the bar; nothing here is product code."""
+    import torch
+    from oracle import ldm_oracle as O, train_oracle as T
+    sdc = {k: v.to(dev) for k, v in sd.items()}
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand((BATCH, 1, SPEC, SPEC), generator=g).to(dev)
+    s = torch.rand((BATCH, 1, SPEC, SPEC), generator=g).to(dev)
+    eps = torch.randn((BATCH, 32, SPEC // 8, SPEC // 8), generator=g).to(dev)
+    out = {"what": "oracle/ldm_oracle.py (functional torch restatement of models/model.py) on cuda: cuDNN / cuBLAS kernels of torch "
+                   + torch.__version__, "unit_sampling": UNIT, "unit_train": "samples/s"}
+
+    def time_ms(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    def call3():
+        return O.content_style_transfer(sdc, x, s, eps, num_timesteps=NSTEPS, eta=0.0, training=False)
+
+    def call3_bf16():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            return call3()
+
+    reps = 2 if quick else 5
+    with torch.no_grad():
+        ms = time_ms(call3, reps)
+        out["config3_eager_fp32_tf32"] = {"value": (NSTEPS - 1) / (ms * 1e-3), "ms_per_call": ms}
+        ms = time_ms(call3_bf16, reps)
+        out["config3_autocast_bf16"] = {"value": (NSTEPS - 1) / (ms * 1e-3), "ms_per_call": ms}
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                call3_bf16()
+                st.synchronize()
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=st):
+                    call3_bf16()
+                st.synchronize()
+            ms = time_ms(gr.replay, reps)
+            out["config3_autocast_bf16_cudagraph"] = {"value": (NSTEPS - 1) / (ms * 1e-3), "ms_per_call": ms}
+            del gr
+        except Exception as e:      # noqa: BLE001 -- a baseline that cannot be captured is reported, not fatal
+            out["config3_autocast_bf16_cudagraph"] = {"error": repr(e)[:200]}
+        # config 2: VAE round trip, eval-mode BatchNorm
+        xv = torch.rand((VAE_BATCH, 1, VAE_H, VAE_W), generator=torch.Generator().manual_seed(3)).to(dev)
+
+        def vae():
+            return O.decoder_fwd(sdc, O.encoder_fwd(sdc, xv, False), False)
+
+        def vae_bf16():
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                return vae()
+
+        out["config2_eval_eager_fp32_tf32"] = {"us_per_round_trip": 1e3 * time_ms(vae, reps)}
+        out["config2_eval_autocast_bf16"] = {"us_per_round_trip": 1e3 * time_ms(vae_bf16, reps)}
+    # config 4: one training step at global batch 256 (fwd + 4 losses + autograd backward + torch.optim.Adam)
+    gb = TRAIN_GLOBAL_BATCH
+    xt = torch.rand((gb, 1, SPEC, SPEC), generator=g).to(dev)
+    stl = torch.rand((gb, 1, SPEC, SPEC), generator=g).to(dev)
+    tt = torch.randint(0, 200, (gb,), generator=g).to(dev)
+    ee = torch.randn((gb, 32, SPEC // 8, SPEC // 8), generator=g).to(dev)
+    for name, ac in (("config4_eager_fp32_tf32", False), ("config4_autocast_bf16", True)):
+        try:
+            tr = T.OracleTrainer(sdc, lr=5e-4, style_loss_weight=3.0)
+
+            def step():
+                if ac:
+                    with torch.autocast("cuda", dtype=torch.bfloat16):
+                        tr.train_step(xt, stl, tt, ee)
+                else:
+                    tr.train_step(xt, stl, tt, ee)
+
+            ms = time_ms(step, 2 if quick else 3)
+            out[name] = {"value": gb / (ms * 1e-3), "ms_per_step": ms}
+            del tr
+        except Exception as e:      # noqa: BLE001
+            out[name] = {"error": repr(e)[:200]}
+        torch.cuda.empty_cache()
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+# config 5: waveforms -> mel front end -> 50-step transfer (per GPU: 64 content + 64 style clips of 10 s)
+# ------------------------------------------------------------------------------------------
+MEL_CLIPS, MEL_LEN, MEL_CROP = 64, 220500, 384
+MEL_BYTES_PER_CLIP = MEL_LEN * 4 + 128 * 431 * 4        # SURVEY 8(d): 882 KB in + 221 KB fp32 out = 1.10 MB
+
+
+def mel_leg(model, dev, peaks, rank, cpu_baseline=True, reps=10):
+    """BASELINE config 5 on this rank: 0.1*randn(64, 220500) content and style clips -> AudioPreprocessor.spectrogram_batch
+    (csrc/mel.cu, crop 128x384) -> content_style_transfer_wrapper(num_timesteps=50).  Reports the mel front end alone (HBM
+    roofline: 1.10 MB per clip) and the whole config-5 call (UNet denoise steps/s at latent 16x48), device time."""
+    import torch
+    from music_style_transfer_ldm_b200.audio_processor import AudioPreprocessor
+    g = torch.Generator().manual_seed(900 + rank)
+    wc = (0.1 * torch.randn((MEL_CLIPS, MEL_LEN), generator=g)).to(dev)
+    ws = (0.1 * torch.randn((MEL_CLIPS, MEL_LEN), generator=g)).to(dev)
+    ap = AudioPreprocessor()
+
+    def mel_only():
+        return ap.spectrogram_batch(wc, n_mels=128, crop_frames=MEL_CROP)
+
+    def full():
+        xc = ap.spectrogram_batch(wc, n_mels=128, crop_frames=MEL_CROP)
+        xs = ap.spectrogram_batch(ws, n_mels=128, crop_frames=MEL_CROP)
+        return model.content_style_transfer_wrapper(xc, xs, num_timesteps=NSTEPS, eta=0.0)
+
+    with torch.no_grad():
+        us_mel = _time_us(mel_only, reps)
+        us_full = _time_us(full, max(2, reps // 3))
+    peak = peaks.get("hbm_gbs", 6550.0)
+    gbs = MEL_CLIPS * MEL_BYTES_PER_CLIP / (us_mel * 1e-6) / 1e9
+    out = {"workload": "config5 (per GPU): 2 x 64 clips of 10 s @ 22.05 kHz -> mel 128x431 -> crop 128x384 -> [0,1] -> 50-step transfer "
+                       "(latent 32x16x48) -> decode",
+           "mel": {"kernel": "mel front end (csrc/mel.cu)", "clips": MEL_CLIPS, "us": us_mel, "clips_per_s": MEL_CLIPS / (us_mel * 1e-6),
+                   "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                                "algorithmic_bytes_per_clip": MEL_BYTES_PER_CLIP}},
+           "end_to_end": {"ms_per_call": us_full * 1e-3, "unet_denoise_steps_per_s": (NSTEPS - 1) / (us_full * 1e-6),
+                          "clips_per_s": MEL_CLIPS / (us_full * 1e-6)}}
+    if cpu_baseline:
+        from oracle import mel_oracle as MO
+        w = wc[:4].cpu().numpy()
+        t0 = time.perf_counter()
+        for i in range(w.shape[0]):
+            MO.waveform_to_unit_image(w[i], 22050, 128, MEL_CROP)
+        dt = time.perf_counter() - t0
+        out["mel"]["cpu_baseline"] = {"clips_per_s": w.shape[0] / dt, "kind": "port", "cores": 1,
+                                      "sample": f"{w.shape[0]} clips through oracle/mel_oracle.py (numpy restatement of librosa's defaults; librosa "
+                                                f"is not installable here), {dt:.2f} s"}
+    return out
+
+
+def fp32_leg(sd, dev, content_d, style_d, calls=3):
+    """the same config-3 call in fp32 mode (1e-4 parity mode): UNet denoise steps/s, device time"""
+    import torch
+    import music_style_transfer_ldm_b200 as M
+    m = M.LDM(latent_dim=32, pretrained_path=None)
+    m.load_state_dict(sd, strict=True)
+    m.to(dev).eval().set_precision("fp32")
+    with torch.no_grad():
+        us = _time_us(lambda: m.content_style_transfer_wrapper(content_d, style_d, num_timesteps=NSTEPS, eta=0.0), calls)
+    del m
+    torch.cuda.empty_cache()
+    return {"metric": METRIC, "value": (NSTEPS - 1) / (us * 1e-6), "unit": UNIT, "ms_per_call": us * 1e-3, "precision": "fp32",
+            "unet_step_us": us / (NSTEPS - 1)}
+
+
+# ------------------------------------------------------------------------------------------
+# data-parallel self-check (the driver's test box has one GPU: the N > 1 bench runs carry the evidence)
+# ------------------------------------------------------------------------------------------
+def ddp_parity(args, rank, world, dev):
+    """3 steps of the SHARDED training step at global batch 256 (graph warm-up 1: eager, capture, replay -- so the captured
+    DDP step with its in-graph NCCL all-reduces is covered) against (a) the same global batch run single-process on rank 0
+    and (b) the fp32 oracle curve tests/golden/train_curve_b256.npz.  Also the spread of the replicas' parameter checksums."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200.train import LDMTrainer
+    from oracle import ldm_oracle as O
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    import make_golden_curve256 as G256
+    keys = ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")
+    per = G256.B // world
+
+    def run(w, shard):
+        model = M.LDM(latent_dim=32, pretrained_path=None)
+        model.load_state_dict(O.make_state_dict(1234), strict=True)
+        model._freeze_encoder()
+        model.to(dev).set_precision(args.precision)
+        tr = LDMTrainer(model, None, dev, lr=G256.LR, style_loss_weight=G256.W, process_group=None, world_size=w)
+        tr.graph_warmup = 1
+        model.train()
+        rows = []
+        for i in range(G256.STEPS):
+            x, s, t, eps = (v[shard].to(dev) for v in G256.step_inputs(i))
+            out = tr.train_step_device(x, s, t=t, noise=eps)
+            rows.append([float(out[k]) for k in keys])
+        chk = tr.arena.p.double().sum().reshape(1)
+        del tr, model
+        torch.cuda.empty_cache()
+        return np.asarray(rows), chk
+
+    ddp, chk = run(world, slice(rank * per, (rank + 1) * per))
+    chks = [torch.zeros_like(chk) for _ in range(world)]
+    dist.all_gather(chks, chk)
+    res = None
+    if rank == 0:
+        single, _ = run(1, slice(0, G256.B))
+        gold = np.load(os.path.join(ROOT, "tests", "golden", "train_curve_b256.npz"))["losses"]
+        c = torch.cat(chks).cpu().numpy()
+        res = {"steps": int(G256.STEPS), "global_batch": int(G256.B), "path": "step 0 eager, step 1 graph capture, step 2 graph replay",
+               "max_rel_loss_dev": float(np.max(np.abs(ddp - single) / np.abs(single))),
+               "max_rel_loss_dev_vs_oracle_fixture": float(np.max(np.abs(ddp - gold) / np.abs(gold))),
+               "replica_checksum_spread": float((c.max() - c.min()) / max(1e-30, abs(c[0]))), "tolerance": 1e-2}
+        res["pass"] = bool(res["max_rel_loss_dev"] <= 1e-2 and res["max_rel_loss_dev_vs_oracle_fixture"] <= 1e-2
+                           and res["replica_checksum_spread"] <= 1e-6)
+    dist.barrier()
+    return res
+
+
+# ------------------------------------------------------------------------------------------
 # CUDA arm
 # ------------------------------------------------------------------------------------------
 def run_cuda(args):
@@ -533,7 +765,7 @@ def run_cuda(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = t.tolist()
-    train = train_weak = None
+    train = train_weak = parity = None
     if not args.no_train:
         del model
         torch.cuda.empty_cache()
@@ -541,9 +773,28 @@ def run_cuda(args):
         if world > 1:
             # supplementary: the same step with the PER-GPU batch held at 256 (weak scaling of the training step)
             train_weak = train_leg(args, rank, world, dev, barrier, global_batch=TRAIN_GLOBAL_BATCH * world, rooflines=False)
+            parity = ddp_parity(args, rank, world, dev)
         model = M.LDM(latent_dim=32, pretrained_path=None)          # fresh sampler model for the roofline leg
         model.load_state_dict(sd, strict=True)
         model.to(dev).eval().set_precision(args.precision)
+    # config 5 (mel front end + transfer at 128x384) on every rank: batch-sharded like config 3, no collective
+    mel = None
+    if not args.no_mel:
+        peaks_all = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks_all = json.load(f)
+        except OSError:
+            pass
+        barrier()
+        mel = mel_leg(model, dev, peaks_all, rank, cpu_baseline=(rank == 0 and world == 1 and not args.no_cpu_baseline))
+        tm = torch.tensor([mel["mel"]["us"], mel["end_to_end"]["ms_per_call"]], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        us_mel, ms_c5 = tm.tolist()
+        mel["aggregate"] = {"n_gpus": world, "clips": MEL_CLIPS * world, "mel_clips_per_s": MEL_CLIPS * world / (us_mel * 1e-6),
+                            "config5_unet_denoise_steps_per_s": (NSTEPS - 1) * world / (ms_c5 * 1e-3),
+                            "config5_clips_per_s": MEL_CLIPS * world / (ms_c5 * 1e-3), "timing": "max over ranks"}
     unet_steps = (NSTEPS - 1) * args.steps * world
     value = unet_steps / (ms * 1e-3)
     e2e_value = unet_steps / (ms_e2e * 1e-3)
@@ -559,28 +810,86 @@ def run_cuda(args):
             roof, rows = kernel_roofline(model, peaks)
         # single-GPU measurements (config 2 and the autoencoder stage do not shard): skipped in the N > 1 scaling runs
         vae = None if (args.no_vae or world > 1) else vae_leg(sd, dev, peaks, args.precision)
+        vae32 = None if (args.no_vae or world > 1 or args.precision == "fp32") else vae_leg(sd, dev, peaks, "fp32", reps=5)
         ae = None if (args.no_train or world > 1) else ae_leg(sd, dev, args.precision)
+        fp32 = None if (world > 1 or args.precision == "fp32" or args.no_fp32) else fp32_leg(sd, dev, content_d, style_d)
+        base = None if (world > 1 or args.no_gpu_baseline) else gpu_baseline(sd, dev)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             v, threads, dt = cpu_transfer_timing(10)
             cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                    "sample": f"10 full config-3 calls (batch 64, 49 UNet+DDIM steps + VAE/style passes) of the oracle port, fp32, {dt:.1f} s"}
+        unet_step_us = 1e3 * ms / args.steps / (NSTEPS - 1)
+
+        def pick(d, *path):
+            for p in path:
+                if not isinstance(d, dict) or p not in d:
+                    return None
+                d = d[p]
+            return d
+
+        def r3(v):
+            return None if v is None else float(f"{v:.4g}")
+
+        def best(d, ks):
+            vs = [v for v in (pick(d, k, "value") for k in ks) if v]
+            return max(vs) if vs else None
+
+        c3k = ("config3_eager_fp32_tf32", "config3_autocast_bf16", "config3_autocast_bf16_cudagraph")
+        c4k = ("config4_eager_fp32_tf32", "config4_autocast_bf16")
+        tv = pick(train, "value")
+        # compact block, LAST in the line (the driver stores tails): everything BASELINE's metric names, with the bar beside it
+        summary = {
+            "sampling": {"steps_per_s": r3(value), "e2e_steps_per_s": r3(e2e_value), "unet_step_us": r3(unet_step_us),
+                         "sum_isolated_kernel_us": r3(roof.get("sum_isolated_us_all_kernels")), "pdl_overlap_frac": r3(roof.get("pdl_overlap_frac")),
+                         "launches_per_unet_step": roof.get("launches_per_unet_step_all_kernels"), "roofline_frac": r3(roof["frac"]),
+                         "fp32_mode_steps_per_s": r3(pick(fp32, "value"))},
+            "train_strong": {"global_batch": pick(train, "global_batch"), "samples_per_s": r3(tv), "ms_per_step": r3(pick(train, "ms_per_step")),
+                             "e2e_samples_per_s": r3(pick(train, "e2e", "value")), "vggish_conv_roofline_frac": r3(pick(train, "roofline", "frac")),
+                             "algorithmic_frac_of_bf16_peak": r3(19.6e9 * tv / 1e12 / peaks.get("bf16_tflops", 1590.0)) if tv else None},
+            "train_weak": {"global_batch": pick(train_weak, "global_batch"), "samples_per_s": r3(pick(train_weak, "value")),
+                           "ms_per_step": r3(pick(train_weak, "ms_per_step")), "e2e_samples_per_s": r3(pick(train_weak, "e2e", "value"))},
+            "ddp_parity": parity,
+            "vae": {"eval_us": r3(pick(vae, "eval", "us_per_round_trip")), "eval_frac": r3(pick(vae, "eval", "frac")),
+                    "train_us": r3(pick(vae, "train", "us_per_round_trip")), "train_frac": r3(pick(vae, "train", "frac")),
+                    "fp32_eval_us": r3(pick(vae32, "eval", "us_per_round_trip")), "fp32_eval_frac": r3(pick(vae32, "eval", "frac")),
+                    "fp32_train_us": r3(pick(vae32, "train", "us_per_round_trip")), "fp32_train_frac": r3(pick(vae32, "train", "frac"))},
+            "config5": {"mel_us_64_clips": r3(pick(mel, "mel", "us")), "mel_hbm_frac": r3(pick(mel, "mel", "roofline", "frac")),
+                        "mel_clips_per_s": r3(pick(mel, "aggregate", "mel_clips_per_s")),
+                        "unet_denoise_steps_per_s": r3(pick(mel, "aggregate", "config5_unet_denoise_steps_per_s")),
+                        "clips_per_s": r3(pick(mel, "aggregate", "config5_clips_per_s")),
+                        "mel_cpu_clips_per_s": r3(pick(mel, "mel", "cpu_baseline", "clips_per_s"))},
+            "autoencoder_samples_per_s": r3(pick(ae, "value")),
+            "gpu_baseline": None if base is None else {
+                "what": "stock PyTorch (cuDNN/cuBLAS) on this B200, same inputs: eager fp32+TF32 / autocast bf16 / autocast bf16 in one CUDA graph",
+                "config3_steps_per_s": [r3(pick(base, k, "value")) for k in c3k],
+                "config3_speedup_vs_best": r3(value / best(base, c3k)) if best(base, c3k) else None,
+                "config4_samples_per_s": [r3(pick(base, k, "value")) for k in c4k],
+                "config4_speedup_vs_best": r3(tv / best(base, c4k)) if (tv and best(base, c4k)) else None,
+                "config2_eval_us": [r3(pick(base, k, "us_per_round_trip")) for k in ("config2_eval_eager_fp32_tf32", "config2_eval_autocast_bf16")]},
+            "cpu_steps_per_s": r3(pick(cpu, "value")), "n_gpus": world,
+        }
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
             "config": workload_config({"precision": args.precision, "sharding": f"batch-sharded x{world}, no collective on the data path"}),
+            "layers": rows,
+            "train": train, "train_weak": train_weak, "vae": vae, "vae_fp32": vae32, "train_autoencoder": ae, "config5": mel, "fp32_mode": fp32,
+            "gpu_baseline": base,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
-            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks, "train": train, "train_weak": train_weak, "vae": vae, "train_autoencoder": ae,
+            "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
             "samples_steps_per_s": value * BATCH,
-            "unet_step_us": 1e3 * ms / args.steps / (NSTEPS - 1),
-            "layers": rows,
+            "unet_step_us": unet_step_us,
+            "summary": summary,
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity["pass"]:
+        raise SystemExit(f"bench.py: data-parallel self-check failed: {parity}")
 
 
 def main():
@@ -593,6 +902,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg")
     ap.add_argument("--no-vae", action="store_true", help="skip the config-2 VAE round-trip leg")
+    ap.add_argument("--no-mel", action="store_true", help="skip the config-5 mel front end + transfer leg")
+    ap.add_argument("--no-fp32", action="store_true", help="skip the fp32-mode sampling leg")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the stock-PyTorch-on-this-GPU baseline legs")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps is None:
