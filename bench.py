@@ -155,6 +155,7 @@ def kernel_roofline(model, peaks, reps=20):
     with torch.no_grad():
         model.content_style_ddim_sample(z, st, timesteps=2, eta=0.0)     # exactly one UNet step
     recs, ops.RECORD = ops.RECORD, None
+    recs = [r for r in recs if r.get("note") != "hoisted"]      # the style-side projections run once per loop, not per step
     model.use_cuda_graphs = True
     torch.cuda.synchronize()
     rows = []

@@ -173,6 +173,28 @@ typedef struct mstk_attn_args {
 int mstk_attention_fwd(const mstk_attn_args* a, void* stream);
 
 /* ------------------------------------------------------------------------------
+ * Style cross-attention with the projections composed into the style side (same layer:
+ * CrossAttention.forward, models/model.py:126-160; algebra in csrc/xattn.cu).  The style map
+ * is projected ONCE per sampling loop by a k1 mstk_conv2d_fwd with the composed weight
+ *   mstk_xattn_compose: in_proj_weight [3e,e], in_proj_bias [3e], out_proj.weight [e,e] (fp32)
+ *                       -> w_packed [ctot, e] (`dtype`), bias [ctot] fp32,  ctot = mstk_xattn_ctot(e, heads)
+ * and every evaluation of the layer is one launch:
+ *   x: [b, l, e] features; kvp: [b, s, ctot] projected style tokens; bias: out_proj.bias [e] fp32; out: [b, l, e].
+ *   kv_static != 0: kvp was produced at least two launches earlier on the stream (it may then be staged before the
+ *   programmatic grid dependency resolves).  e in {256, 512}.
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_xattn_args {
+    const void* x; const void* kvp; const float* bias; void* out;
+    int32_t b, l, s, e, heads, ctot;
+    int32_t kv_static;
+    int32_t dtype;
+} mstk_xattn_args;
+int mstk_xattn_ctot(int e, int heads);
+int mstk_xattn_compose(const float* in_proj_weight, const float* in_proj_bias, const float* out_proj_weight, void* w_packed,
+                       float* bias, int e, int heads, int dtype, void* stream);
+int mstk_xattn_fwd(const mstk_xattn_args* a, void* stream);
+
+/* ------------------------------------------------------------------------------
  * Scheduler arithmetic (ForwardDiffusion, model.py:102-124), NHWC or NCHW agnostic:
  * `inner` = elements per sample.
  *   q_sample:   z_t = sqrt(ab[t_b])*x0 + sqrt(1-ab[t_b])*eps

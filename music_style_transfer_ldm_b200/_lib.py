@@ -52,6 +52,12 @@ class AttnArgs(C.Structure):
                 ("dtype", c_int)]
 
 
+class XattnArgs(C.Structure):
+    _fields_ = [("x", c_void_p), ("kvp", c_void_p), ("bias", c_void_p), ("out", c_void_p),
+                ("b", c_int), ("l", c_int), ("s", c_int), ("e", c_int), ("heads", c_int), ("ctot", c_int),
+                ("kv_static", c_int), ("dtype", c_int)]
+
+
 class MelArgs(C.Structure):
     _fields_ = [("wave", c_void_p), ("out", c_void_p), ("db_out", c_void_p), ("mel_fb", c_void_p),
                 ("work", c_void_p), ("work_bytes", c_size_t),
@@ -99,6 +105,9 @@ SIGNATURES = {
     "mstk_bn_apply": (c_int, [C.POINTER(BnArgs), c_void_p]),
     "mstk_time_embed": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "mstk_attention_fwd": (c_int, [C.POINTER(AttnArgs), c_void_p]),
+    "mstk_xattn_ctot": (c_int, [c_int, c_int]),
+    "mstk_xattn_compose": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "mstk_xattn_fwd": (c_int, [C.POINTER(XattnArgs), c_void_p]),
     "mstk_q_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "mstk_predict_x0": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "mstk_ddim_step": (c_int, [C.POINTER(DdimArgs), c_void_p, c_size_t, c_void_p]),

@@ -345,9 +345,28 @@ class CrossAttention(_Kernelised):
         self.embed_dim = embed_dim
         self.num_heads = num_heads
 
+    # Two executions of the same layer (csrc/xattn.cu has the algebra):
+    #  * composed (inference: module forward, UNet.forward, both sampling loops; E in {256, 512}): the style map goes
+    #    through ONE k1 conv whose weight composes Wq^T Wk, Wo Wv and bq^T Wk per head -- once per sampling loop -- and
+    #    every evaluation of the layer is a single `xattn` launch;
+    #  * plain (the trainers, which need q / k / v for the parameter gradients; other E): K|V projection, q projection,
+    #    attention core, out projection.
+    def _composed_ok(self) -> bool:
+        return self.embed_dim in (256, 512) and self.num_heads <= 16 and self.embed_dim % self.num_heads == 0
+
     def _project_style(self, style_nhwc: torch.Tensor) -> torch.Tensor:
-        """K and V projections of the style map in ONE GEMM: [B,h,w,E] -> [B,h,w,2E].  Depends
-        only on the style, so the sampling loop hoists it out of the 49 steps."""
+        """The style side of the layer: [B,h,w,E] -> [B,h,w,ctot] (composed) or [B,h,w,2E] (K|V).  Depends only on
+        the style, so the sampling loop hoists it out of the 49 steps."""
+        e = self.embed_dim
+        m = self.multihead_attn
+        adt = style_nhwc.dtype
+        if self._composed_ok():
+            wp, bias = self._cached(("wcomp", adt), (m.in_proj_weight, m.in_proj_bias, m.out_proj.weight),
+                                    lambda: ops.xattn_compose(m.in_proj_weight, m.in_proj_bias, m.out_proj.weight, self.num_heads, adt))
+            return ops.conv(style_nhwc, wp, bias, ksize=1)
+        return self._project_style_kv(style_nhwc)
+
+    def _project_style_kv(self, style_nhwc: torch.Tensor) -> torch.Tensor:
         e = self.embed_dim
         m = self.multihead_attn
         adt = style_nhwc.dtype
@@ -355,15 +374,19 @@ class CrossAttention(_Kernelised):
         bkv = self._cached(("bkv",), (m.in_proj_bias,), lambda: m.in_proj_bias.detach()[e:].float().contiguous())
         return ops.conv(style_nhwc, wkv, bkv, ksize=1)
 
-    def _forward_nhwc(self, feat: torch.Tensor, kv: torch.Tensor) -> torch.Tensor:
+    def _forward_nhwc(self, feat: torch.Tensor, kv: torch.Tensor, kv_static: bool = False) -> torch.Tensor:
         e = self.embed_dim
         m = self.multihead_attn
         adt = feat.dtype
         b, h, w, _ = feat.shape
+        s_tok = kv.shape[1] * kv.shape[2]
+        if kv.shape[3] != 2 * e:          # composed projection
+            o = ops.xattn(feat.view(b, h * w, e), kv.view(b, s_tok, kv.shape[3]), self._f32("bo", m.out_proj.bias), self.num_heads,
+                          kv_static=kv_static)
+            return o.view(b, h, w, e)
         wq = self._cached(("wq", adt), (m.in_proj_weight,), lambda: ops.pack_weight(m.in_proj_weight.detach()[:e], adt))
         bq = self._cached(("bq",), (m.in_proj_bias,), lambda: m.in_proj_bias.detach()[:e].float().contiguous())
         q = ops.conv(feat, wq, bq, ksize=1)
-        s_tok = kv.shape[1] * kv.shape[2]
         kv2 = kv.view(b, s_tok, 2 * e)
         o = ops.attention(q.view(b, h * w, e), kv2[:, :, :e], kv2[:, :, e:], self.num_heads)
         wo = self._packed("wo", m.out_proj.weight, adt)
@@ -447,9 +470,9 @@ class UNet(_Kernelised):
         z1 = self._conv("enc1", z, act=ACT_RELU)
         z2 = self._conv("enc2", z1, act=ACT_RELU, add_nc=temb)
         z3 = self._conv("enc3", z2, act=ACT_RELU)
-        a3 = self.cross_attention2._forward_nhwc(z3, kv2)
+        a3 = self.cross_attention2._forward_nhwc(z3, kv2, kv_static=True)      # the projections precede enc1..enc3
         z4 = self._conv("enc4", a3, act=ACT_RELU)
-        a4 = self.cross_attention1._forward_nhwc(z4, kv1)
+        a4 = self.cross_attention1._forward_nhwc(z4, kv1, kv_static=True)
         bt = self._conv("bottleneck", a4, act=ACT_RELU)
         d4 = self._conv("dec4", bt, act=ACT_RELU, add=z3)
         d3 = self._conv("dec3", d4, act=ACT_RELU, add=z2)
@@ -599,7 +622,9 @@ class LDM(_Kernelised):
         b = x.shape[0]
         nsteps = len(times) - 1
         sab, s1m = self._schedule_host()
+        ops.RECORD_NOTE = "hoisted"
         kv2, kv1 = self.unet._project_style(s5, s6)
+        ops.RECORD_NOTE = ""
         temb = self.unet._time_embedding(tt).view(nsteps, b, -1)
         x_lp = ops.cast(x, adt) if adt != torch.float32 else None
         self._loop_steps(x, x_lp, temb, kv2, kv1, times, eta, logs)

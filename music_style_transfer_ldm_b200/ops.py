@@ -51,6 +51,7 @@ WORKSPACE_BYTES = 32 << 20
 # the caller that replays them) and, when RECORD is a list, a replayable record of conv calls
 LAUNCHES = 0
 RECORD = None
+RECORD_NOTE = ""        # free-form tag copied into the records made while it is set (bench.py: "hoisted" = once per loop)
 
 
 def _count(n: int = 1) -> None:
@@ -150,7 +151,7 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
         def replay(a=a, keep=keep):
             check(lib.mstk_conv2d_fwd(C.byref(a), _stream()), "mstk_conv2d_fwd(replay)")
 
-        RECORD.append(dict(n=n, h=h, w=w, cin=cin, cout=cout, ksize=ksize, stride=stride, transposed=transposed,
+        RECORD.append(dict(n=n, h=h, w=w, cin=cin, cout=cout, ksize=ksize, stride=stride, transposed=transposed, note=RECORD_NOTE,
                            kernel="conv_tc_kernel" if use_tc else "conv_simt_kernel", replay=replay,
                            tag=f"{'convT' if transposed else 'conv'}k{ksize}s{stride} {cin}->{cout} @{h}x{w} n{n}"))
     return y
@@ -259,8 +260,48 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
         def replay(a=a, keep=keep):
             check(lib.mstk_attention_fwd(C.byref(a), _stream()), "mstk_attention_fwd(replay)")
 
-        RECORD.append(dict(kernel="attention_block_kernel", replay=replay, flops=4.0 * b * l * s * e,
+        RECORD.append(dict(kernel="attention_block_kernel", replay=replay, flops=4.0 * b * l * s * e, note=RECORD_NOTE,
                            tag=f"attention core b{b} l{l} s{s} e{e} h{heads}"))
+    return out
+
+
+def xattn_compose(in_proj_weight: torch.Tensor, in_proj_bias: torch.Tensor, out_proj_weight: torch.Tensor, heads: int,
+                  dtype: torch.dtype):
+    """Composed projection of the style side of a cross-attention layer (csrc/xattn.cu): packed k1 conv weight
+    [1, ctot, e] in ``dtype`` and fp32 bias [ctot]."""
+    lib = _lib.load()
+    w_in, b_in, w_out = (_dev(t.detach(), "xattn_compose") for t in (in_proj_weight, in_proj_bias, out_proj_weight))
+    if any(t.dtype != torch.float32 for t in (w_in, b_in, w_out)):
+        raise MstkError("xattn_compose: parameters must be fp32")
+    e = w_out.shape[0]
+    ctot = lib.mstk_xattn_ctot(e, heads)
+    wp = torch.empty((1, ctot, e), dtype=dtype, device=w_in.device)
+    bias = torch.empty(ctot, dtype=torch.float32, device=w_in.device)
+    check(lib.mstk_xattn_compose(_p(w_in), _p(b_in), _p(w_out), _p(wp), _p(bias), e, heads, dtype_code(dtype), _stream()), "mstk_xattn_compose")
+    return wp, bias
+
+
+def xattn(x: torch.Tensor, kvp: torch.Tensor, bias: Optional[torch.Tensor], heads: int, kv_static: bool = False) -> torch.Tensor:
+    """x [b,l,e], kvp [b,s,ctot] (style tokens through the composed projection) -> [b,l,e]: the whole cross-attention layer."""
+    lib = _lib.load()
+    _dev(x, "xattn.x"); _dev(kvp, "xattn.kvp")
+    b, l, e = x.shape
+    s, ctot = kvp.shape[1], kvp.shape[2]
+    if kvp.shape[0] != b or kvp.dtype != x.dtype:
+        raise MstkError("xattn: kvp must match x in batch and dtype")
+    out = torch.empty((b, l, e), dtype=x.dtype, device=x.device)
+    a = _lib.XattnArgs(_p(x), _p(kvp), _p(bias), _p(out), b, l, s, e, heads, ctot, 1 if kv_static else 0, dtype_code(x))
+    check(lib.mstk_xattn_fwd(C.byref(a), _stream()), "mstk_xattn_fwd")
+    _count(1)
+    if RECORD is not None:
+        keep = (x, kvp, bias, out)
+
+        def replay(a=a, keep=keep):
+            check(lib.mstk_xattn_fwd(C.byref(a), _stream()), "mstk_xattn_fwd(replay)")
+
+        # algorithmic work of the layer as the reference states it: q and out projections + the attention core
+        RECORD.append(dict(kernel="xattn_kernel", replay=replay, flops=4.0 * b * l * e * e + 4.0 * b * l * s * e, note=RECORD_NOTE,
+                           tag=f"cross-attention (composed) b{b} l{l} s{s} e{e} h{heads}"))
     return out
 
 

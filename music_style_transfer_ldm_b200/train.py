@@ -307,7 +307,7 @@ class LDMTrainer:
     def _attn_fwd(self, ca, feat, style):
         e, m, adt = ca.embed_dim, ca.multihead_attn, feat.dtype
         b, h, w, _ = feat.shape
-        kv = ca._project_style(style)
+        kv = ca._project_style_kv(style)
         wq = ca._cached(("wq", adt), (m.in_proj_weight,), lambda: ops.pack_weight(m.in_proj_weight.detach()[:e], adt))
         bq = ca._cached(("bq",), (m.in_proj_bias,), lambda: m.in_proj_bias.detach()[:e].float().contiguous())
         q = ops.conv(feat, wq, bq, ksize=1)
