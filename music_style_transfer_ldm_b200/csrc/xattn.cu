@@ -24,9 +24,12 @@
 // xattn_kernel: one CTA (256 threads) per (sample, tile of LT query tokens).  fp32 accumulation on CUDA cores: per
 // sample the B operand is private (J x E values used by LT <= 16 rows), so there is no M = 128 tcgen05 tile to fill;
 // the kernel is bound by the latency of staging 2 x J x E values from L2, not by its 1 MFLOP.
-//   pass 1  K' rows staged chunk-wise in shared memory (16-byte loads), scores[l][j] with x broadcast from smem
+//   staging K' / V' rows chunk-wise into shared memory with cp.async (every 16-byte request of a chunk in flight at once:
+//           a chunk costs one L2 round trip); the first chunk of both is requested BEFORE the grid dependency resolves
+//           when the style side is loop-invariant (kv_static)
+//   pass 1  scores[l][j] with x broadcast from smem
 //   softmax per (l, head) over the S style tokens, 4 threads per row
-//   pass 2  V' rows staged chunk-wise, out[l][e] accumulated in registers (thread = channel), + bo, stored
+//   pass 2  out[l][e] accumulated in registers (thread = channel), + bo, stored
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -59,18 +62,24 @@ template <> __device__ __forceinline__ void xa_unpack<__nv_bfloat16>(const uint4
     }
 }
 
-// stage rows [j0, j0 + n) of the composed K' (off = 0) or V' (off = heads*E) block of sample `bi` into ch[n][E + PAD]
+__device__ __forceinline__ void xa_cp16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void xa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void xa_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Asynchronous staging (cp.async, 16 bytes per request, all requests of a chunk in flight together: the kernel is bound
+// by L2 round trips, so a chunk must cost ONE of them) of rows [j0, j0 + n) of the composed K' (off = 0) or V'
+// (off = heads*E) block of sample `bi` into buf[n][pitch].  rowoff[j] = s*ctot + h*E for composed row j = h*S + s.
 template <typename T>
-__device__ __forceinline__ void xa_stage(const XattnP& p, const int bi, const int off, const int j0, const int n, T* ch, const int pitch) {
+__device__ __forceinline__ void xa_stage(const XattnP& p, const int bi, const int off, const int j0, const int n, T* buf, const int pitch,
+                                         const int* rowoff, const int vshift) {
     constexpr int V = XaVec<T>::N;
-    const int vpr = p.e / V;                       // 16-byte vectors per row
-    const T* base = reinterpret_cast<const T*>(p.kvp);
-    for (int i = threadIdx.x; i < n * vpr; i += XA_THREADS) {
-        const int jl = i / vpr, v = i - jl * vpr;
-        const int j = j0 + jl;
-        const int h = j / p.s, s = j - h * p.s;
-        const uint4 q = *reinterpret_cast<const uint4*>(base + ((size_t)bi * p.s + s) * p.ctot + off + h * p.e + v * V);
-        *reinterpret_cast<uint4*>(ch + (size_t)jl * pitch + v * V) = q;
+    const T* base = reinterpret_cast<const T*>(p.kvp) + (size_t)bi * p.s * p.ctot + off;
+    const int vmask = (1 << vshift) - 1;
+    for (int i = threadIdx.x; i < (n << vshift); i += XA_THREADS) {
+        const int jl = i >> vshift, v = i & vmask;
+        xa_cp16(smem_u32(buf + (size_t)jl * pitch + v * V), base + rowoff[j0 + jl] + v * V);
     }
 }
 
@@ -80,40 +89,57 @@ __global__ void __launch_bounds__(XA_THREADS) xattn_kernel(const XattnP p) {
     extern __shared__ __align__(16) uint8_t xa_smem[];
     const int E = p.e, S = p.s, J = p.heads * p.s;
     const int pitch = E + V;                                   // 16 bytes of padding per staged row: conflict-free 16-byte row reads
-    float* xs = reinterpret_cast<float*>(xa_smem);             // [LT][E]
+    const int vshift = 31 - __clz(E / V);                      // E / V is a power of two (E in {256, 512})
+    float* xs = reinterpret_cast<float*>(xa_smem);             // [LT][E] queries, fp32
     float* ps = xs + LT * E;                                   // [J][LT] scores, then probabilities
     float* cs = ps + (size_t)J * LT;                           // [J] score bias c_h[s]
-    T* ch = reinterpret_cast<T*>(cs + ((J + 3) & ~3));         // [jc][pitch]
+    int* rowoff = reinterpret_cast<int*>(cs + ((J + 3) & ~3)); // [J]
+    T* xraw = reinterpret_cast<T*>(rowoff + ((J + 3) & ~3));   // [LT][E] queries as stored
+    T* bufk = xraw + LT * E;                                   // [jc][pitch] K' chunk
+    T* bufv = bufk + (size_t)p.jc * pitch;                     // [jc][pitch] V' chunk
     const int tid = threadIdx.x;
     const int tiles = (p.l + LT - 1) / LT;
     const int bi = blockIdx.x / tiles, l0 = (blockIdx.x - bi * tiles) * LT;
     const int lvalid = min(LT, p.l - l0);
-
     const int n0 = min(p.jc, J);
-    if (p.kv_static) xa_stage<T>(p, bi, 0, 0, n0, ch, pitch);
+
+    for (int j = tid; j < J; j += XA_THREADS) {
+        const int h = j / S, s = j - h * S;
+        rowoff[j] = s * p.ctot + h * E;
+    }
+    __syncthreads();
+    if (p.kv_static) {      // the style side does not depend on the preceding launch: both first chunks fly before the grid dependency
+        xa_stage<T>(p, bi, 0, 0, n0, bufk, pitch, rowoff, vshift);
+        xa_stage<T>(p, bi, p.heads * E, 0, n0, bufv, pitch, rowoff, vshift);
+    }
     pdl_wait();
     if (tid == 0) pdl_launch_dependents();
-    if (!p.kv_static) xa_stage<T>(p, bi, 0, 0, n0, ch, pitch);
-    {   // queries of this tile -> fp32 smem (rows past the end of the sample are zero), score biases
+    if (!p.kv_static) {
+        xa_stage<T>(p, bi, 0, 0, n0, bufk, pitch, rowoff, vshift);
+        xa_stage<T>(p, bi, p.heads * E, 0, n0, bufv, pitch, rowoff, vshift);
+    }
+    {
         const T* xg = reinterpret_cast<const T*>(p.x) + ((size_t)bi * p.l + l0) * E;
-        const int vpr = E / V;
-        for (int i = tid; i < LT * vpr; i += XA_THREADS) {
-            const int l = i / vpr, v = i - l * vpr;
-            float f[V];
-            if (l < lvalid) {
-                xa_unpack<T>(*reinterpret_cast<const uint4*>(xg + (size_t)l * E + v * V), f);
-            } else {
-#pragma unroll
-                for (int k = 0; k < V; ++k) f[k] = 0.f;
-            }
-#pragma unroll
-            for (int k = 0; k < V; k += 4) *reinterpret_cast<float4*>(xs + l * E + v * V + k) = make_float4(f[k], f[k + 1], f[k + 2], f[k + 3]);
-        }
+        for (int i = tid; i < (lvalid << vshift); i += XA_THREADS) xa_cp16(smem_u32(xraw + (size_t)i * V), xg + (size_t)i * V);
+        xa_commit();
         const T* cg = reinterpret_cast<const T*>(p.kvp) + (size_t)bi * S * p.ctot + 2 * p.heads * E;
         for (int j = tid; j < J; j += XA_THREADS) {
             const int h = j / S, s = j - h * S;
             cs[j] = to_f(cg[(size_t)s * p.ctot + h]);
         }
+    }
+    xa_wait_all();
+    __syncthreads();
+    for (int i = tid; i < (LT << vshift); i += XA_THREADS) {   // queries -> fp32 (rows past the end of the sample are zero)
+        float f[V];
+        if (i < (lvalid << vshift)) {
+            xa_unpack<T>(*reinterpret_cast<const uint4*>(xraw + (size_t)i * V), f);
+        } else {
+#pragma unroll
+            for (int k = 0; k < V; ++k) f[k] = 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < V; k += 4) *reinterpret_cast<float4*>(xs + (size_t)i * V + k) = make_float4(f[k], f[k + 1], f[k + 2], f[k + 3]);
     }
     __syncthreads();
 
@@ -124,12 +150,14 @@ __global__ void __launch_bounds__(XA_THREADS) xattn_kernel(const XattnP p) {
             const int n = min(p.jc, J - j0);
             if (j0 > 0) {
                 __syncthreads();
-                xa_stage<T>(p, bi, 0, j0, n, ch, pitch);
+                xa_stage<T>(p, bi, 0, j0, n, bufk, pitch, rowoff, vshift);
+                xa_commit();
+                xa_wait_all();
                 __syncthreads();
             }
             if (jl < n) {
                 float acc[4] = {0.f, 0.f, 0.f, 0.f};
-                const T* kr = ch + (size_t)jl * pitch;
+                const T* kr = bufk + (size_t)jl * pitch;
                 for (int e0 = 0; e0 < E; e0 += V) {
                     float kf[V];
                     xa_unpack<T>(*reinterpret_cast<const uint4*>(kr + e0), kf);
@@ -157,8 +185,6 @@ __global__ void __launch_bounds__(XA_THREADS) xattn_kernel(const XattnP p) {
         }
     }
     __syncthreads();
-    // V' chunk 0 can land while the softmax runs (ch is free: every pass-1 read is behind the barrier above)
-    xa_stage<T>(p, bi, p.heads * E, 0, n0, ch, pitch);
 
     // ---- softmax over the S style tokens of each (query, head): 4 threads per row ----
     {
@@ -196,13 +222,15 @@ __global__ void __launch_bounds__(XA_THREADS) xattn_kernel(const XattnP p) {
         const int n = min(p.jc, J - j0);
         if (j0 > 0) {
             __syncthreads();
-            xa_stage<T>(p, bi, p.heads * E, j0, n, ch, pitch);
+            xa_stage<T>(p, bi, p.heads * E, j0, n, bufv, pitch, rowoff, vshift);
+            xa_commit();
+            xa_wait_all();
             __syncthreads();
         }
         for (int jl = 0; jl < n; ++jl) {
             float v[EPT];
 #pragma unroll
-            for (int k = 0; k < EPT; ++k) v[k] = to_f(ch[(size_t)jl * pitch + tid + k * XA_THREADS]);
+            for (int k = 0; k < EPT; ++k) v[k] = to_f(bufv[(size_t)jl * pitch + tid + k * XA_THREADS]);
             const float* pj = ps + (size_t)(j0 + jl) * LT;
 #pragma unroll
             for (int l4 = 0; l4 < LT; l4 += 4) {
@@ -226,6 +254,241 @@ __global__ void __launch_bounds__(XA_THREADS) xattn_kernel(const XattnP p) {
         for (int l = 0; l < LT; ++l)
             if (l < lvalid) og[(size_t)l * E + e] = from_f<T>(acc[l][k] + bo);
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// bf16 execution on the tensor cores (mma.sync.m16n8k16, fp32 accumulate).  Per CTA M = one tile of 16 queries, so the
+// tcgen05 tile (M >= 64, one B operand for all rows) does not apply: every sample brings its own K' / V'.  The CUDA-core
+// kernel above spends ~5 k instructions per warp with two warps per scheduler (ncu: issue slots 25-34 % busy, stalled
+// on shared-memory latency): 14-18 us.  Here the two contractions are 2 x 128 MMAs per CTA.
+//   GEMM1  scores[16 x J]  = X[16 x E] K'^T : A = queries (row-major, ldmatrix), B = K' rows as staged ([j][e] = "col")
+//          work unit = (8-column tile of the chunk, K split) so that all 8 warps have MMAs even at J = 16; partial sums
+//          meet in shared memory (red.shared.add.f32 onto the score bias c).
+//   softmax per (query, head), probabilities written as the bf16 A operand of GEMM2.
+//   GEMM2  out[16 x E] = P[16 x J] V' : B = V' rows as staged ([j][e], e contiguous = "row") through ldmatrix.trans;
+//          warp w owns output channels [w*E/8, (w+1)*E/8), accumulators stay in registers across chunks.
+//   out + bo -> bf16 -> shared memory -> 16-byte coalesced stores.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2(uint32_t (&r)[2], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// stage rows [j0, j0+n) of K' / V' as in xa_stage and zero the rows up to the next multiple of 16 (MMA padding)
+__device__ __forceinline__ void xm_stage(const XattnP& p, const int bi, const int off, const int j0, const int n, __nv_bfloat16* buf,
+                                         const int pitch, const int* rowoff, const int vshift) {
+    xa_stage<__nv_bfloat16>(p, bi, off, j0, n, buf, pitch, rowoff, vshift);
+    const int npad = (n + 15) & ~15;
+    for (int i = threadIdx.x; i < ((npad - n) << vshift); i += XA_THREADS) {
+        const int jl = n + (i >> vshift), v = i & ((1 << vshift) - 1);
+        *reinterpret_cast<uint4*>(buf + (size_t)jl * pitch + v * 8) = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+template <int NT>       // NT = E / 64: 8-channel output tiles per warp in GEMM2
+__global__ void __launch_bounds__(XA_THREADS) xattn_mma_kernel(const XattnP p) {
+    using T = __nv_bfloat16;
+    extern __shared__ __align__(16) uint8_t xa_smem[];
+    const int E = p.e, S = p.s, J = p.heads * p.s;
+    const int pitch = E + 8;                                   // bf16 elements; 16-byte row skew: conflict-free ldmatrix
+    const int vshift = 31 - __clz(E / 8);
+    const int Jp = (J + 15) & ~15;                             // K extent of GEMM2 (padded probabilities are zero)
+    const int pspitch = Jp + 4, papitch = Jp + 8;
+    float* ps = reinterpret_cast<float*>(xa_smem);             // [16][pspitch] scores
+    float* cs = ps + 16 * pspitch;                             // [Jp] score bias
+    int* rowoff = reinterpret_cast<int*>(cs + Jp);             // [Jp]
+    T* pa = reinterpret_cast<T*>(rowoff + Jp);                 // [16][papitch] probabilities (A operand of GEMM2)
+    T* xq = pa + 16 * papitch;                                 // [16][pitch] queries (A operand of GEMM1), later the output tile
+    T* bufk = xq + 16 * pitch;                                 // [jc][pitch]
+    T* bufv = bufk + (size_t)p.jc * pitch;                     // [jc][pitch]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tiles = (p.l + 15) >> 4;
+    const int bi = blockIdx.x / tiles, l0 = (blockIdx.x - bi * tiles) << 4;
+    const int lvalid = min(16, p.l - l0);
+    const int n0 = min(p.jc, J);
+
+    for (int j = tid; j < J; j += XA_THREADS) {
+        const int h = j / S, s = j - h * S;
+        rowoff[j] = s * p.ctot + h * E;
+    }
+    __syncthreads();
+    if (p.kv_static) {
+        xm_stage(p, bi, 0, 0, n0, bufk, pitch, rowoff, vshift);
+        xm_stage(p, bi, p.heads * E, 0, n0, bufv, pitch, rowoff, vshift);
+    }
+    pdl_wait();
+    if (tid == 0) pdl_launch_dependents();
+    if (!p.kv_static) {
+        xm_stage(p, bi, 0, 0, n0, bufk, pitch, rowoff, vshift);
+        xm_stage(p, bi, p.heads * E, 0, n0, bufv, pitch, rowoff, vshift);
+    }
+    {
+        const T* xg = reinterpret_cast<const T*>(p.x) + ((size_t)bi * p.l + l0) * E;
+        for (int i = tid; i < (16 << vshift); i += XA_THREADS) {
+            const int l = i >> vshift, v = i & ((1 << vshift) - 1);
+            if (l < lvalid) xa_cp16(smem_u32(xq + (size_t)l * pitch + v * 8), xg + (size_t)l * E + v * 8);
+            else *reinterpret_cast<uint4*>(xq + (size_t)l * pitch + v * 8) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        xa_commit();
+        const T* cg = reinterpret_cast<const T*>(p.kvp) + (size_t)bi * S * p.ctot + 2 * p.heads * E;
+        for (int j = tid; j < Jp; j += XA_THREADS) {
+            float c = 0.f;
+            if (j < J) { const int h = j / S, s = j - h * S; c = to_f(cg[(size_t)s * p.ctot + h]); }
+            cs[j] = c;
+        }
+    }
+    __syncthreads();                                           // cs visible
+    for (int i = tid; i < 16 * Jp; i += XA_THREADS) {          // scores start at the bias
+        const int l = i / Jp, j = i - l * Jp;
+        ps[l * pspitch + j] = cs[j];
+    }
+    xa_wait_all();
+    __syncthreads();
+
+    // ---- GEMM1 ----
+    const int ksteps = E >> 4;
+    for (int j0 = 0; j0 < J; j0 += p.jc) {
+        const int n = min(p.jc, J - j0);
+        if (j0 > 0) {
+            __syncthreads();
+            xm_stage(p, bi, 0, j0, n, bufk, pitch, rowoff, vshift);
+            xa_commit();
+            xa_wait_all();
+            __syncthreads();
+        }
+        const int nt = (n + 7) >> 3;                           // 8-column tiles of this chunk
+        int ksplit = 1;
+        while (nt * ksplit < 8 && ksplit < 8) ksplit <<= 1;    // spread over the 8 warps
+        const int kper = ksteps / ksplit;                      // ksteps is 16 or 32
+        for (int unit = warp; unit < nt * ksplit; unit += 8) {
+            const int tile = unit % nt, kq = unit / nt;
+            float c[4] = {0.f, 0.f, 0.f, 0.f};
+            const uint32_t a_addr = smem_u32(xq + (size_t)(lane & 15) * pitch + ((lane >> 4) << 3));
+            const uint32_t b_addr = smem_u32(bufk + (size_t)(tile * 8 + (lane & 7)) * pitch + (((lane >> 3) & 1) << 3));
+            for (int ks = kq * kper; ks < (kq + 1) * kper; ++ks) {
+                uint32_t a[4], b[2];
+                ldsm_x4(a, a_addr + (uint32_t)ks * 32u);
+                ldsm_x2(b, b_addr + (uint32_t)ks * 32u);
+                mma_bf16_16816(c, a, b[0], b[1]);
+            }
+            const int row = lane >> 2, col = j0 + tile * 8 + ((lane & 3) << 1);
+            atomicAdd(ps + row * pspitch + col, c[0]);
+            atomicAdd(ps + row * pspitch + col + 1, c[1]);
+            atomicAdd(ps + (row + 8) * pspitch + col, c[2]);
+            atomicAdd(ps + (row + 8) * pspitch + col + 1, c[3]);
+        }
+    }
+    __syncthreads();
+
+    // ---- softmax per (query, head) over S, 4 threads per row; probabilities -> bf16 A operand ----
+    {
+        const int nrows = 16 * p.heads, sub = tid & 3;
+        for (int r0 = 0; r0 < nrows; r0 += XA_THREADS / 4) {
+            const int row = r0 + (tid >> 2);
+            const bool ok = row < nrows;
+            const int l = ok ? row / p.heads : 0, h = ok ? row - l * p.heads : 0;
+            const float* pr = ps + l * pspitch + h * S;
+            T* po = pa + l * papitch + h * S;
+            float mx = -INFINITY;
+            if (ok) for (int s = sub; s < S; s += 4) mx = fmaxf(mx, pr[s]);
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            float sum = 0.f;
+            if (ok) for (int s = sub; s < S; s += 4) sum += expf(pr[s] - mx);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            const float inv = 1.f / sum;
+            if (ok) for (int s = sub; s < S; s += 4) po[s] = __float2bfloat16_rn(expf(pr[s] - mx) * inv);
+        }
+        for (int i = tid; i < 16 * (Jp - J); i += XA_THREADS) {            // K padding of GEMM2
+            const int l = i / (Jp - J), j = J + i - l * (Jp - J);
+            pa[l * papitch + j] = __float2bfloat16_rn(0.f);
+        }
+    }
+    __syncthreads();
+
+    // ---- GEMM2: warp w -> output channels [w*NT*8, (w+1)*NT*8) ----
+    float acc[NT][4];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) { acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f; }
+    const int e_w = warp * NT * 8;
+    for (int j0 = 0; j0 < J; j0 += p.jc) {
+        const int n = min(p.jc, J - j0);
+        if (j0 > 0) {
+            __syncthreads();
+            xm_stage(p, bi, p.heads * E, j0, n, bufv, pitch, rowoff, vshift);
+            xa_commit();
+            xa_wait_all();
+            __syncthreads();
+        }
+        const int kk_n = (n + 15) >> 4;
+        for (int kk = 0; kk < kk_n; ++kk) {
+            uint32_t a[4];
+            ldsm_x4(a, smem_u32(pa + (size_t)(lane & 15) * papitch + j0 + kk * 16 + ((lane >> 4) << 3)));
+            // x4.trans: matrices (k 0-7, n 0-7), (k 8-15, n 0-7), (k 0-7, n 8-15), (k 8-15, n 8-15) of a 16 x 16 block of V'
+            const uint32_t v_addr = smem_u32(bufv + (size_t)(kk * 16 + (lane & 15)) * pitch + e_w + ((lane >> 4) << 3));
+#pragma unroll
+            for (int t = 0; t < NT; t += 2) {
+                uint32_t b[4];
+                ldsm_x4_trans(b, v_addr + (uint32_t)t * 16u);
+                mma_bf16_16816(acc[t], a, b[0], b[1]);
+                mma_bf16_16816(acc[t + 1], a, b[2], b[3]);
+            }
+        }
+    }
+    // ---- + bo, bf16, through shared memory (the query tile is dead: every GEMM1 read is behind two barriers) ----
+    {
+        const int row = lane >> 2;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+            const int e = e_w + t * 8 + ((lane & 3) << 1);
+            const float b0 = p.bias ? __ldg(p.bias + e) : 0.f, b1 = p.bias ? __ldg(p.bias + e + 1) : 0.f;
+            *reinterpret_cast<__nv_bfloat162*>(xq + (size_t)row * pitch + e) = __floats2bfloat162_rn(acc[t][0] + b0, acc[t][1] + b1);
+            *reinterpret_cast<__nv_bfloat162*>(xq + (size_t)(row + 8) * pitch + e) = __floats2bfloat162_rn(acc[t][2] + b0, acc[t][3] + b1);
+        }
+    }
+    __syncthreads();
+    T* og = reinterpret_cast<T*>(p.out) + ((size_t)bi * p.l + l0) * E;
+    for (int i = tid; i < (lvalid << vshift); i += XA_THREADS) {
+        const int l = i >> vshift, v = i & ((1 << vshift) - 1);
+        *reinterpret_cast<uint4*>(og + (size_t)l * E + v * 8) = *reinterpret_cast<const uint4*>(xq + (size_t)l * pitch + v * 8);
+    }
+}
+
+template <int NT>
+static int xattn_mma_launch(const XattnP& p, size_t smem, int grid, cudaStream_t st) {
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(xattn_mma_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "xattn_mma smem attr");
+        smem_set = 200 * 1024;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(XA_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, xattn_mma_kernel<NT>, p);
+    if (le != cudaSuccess) return cuda_fail(le, "xattn_mma launch");
+    return MSTK_OK;
 }
 
 // Composition of the projection weights (once per parameter version; fp32 accumulation).  Packed conv weight
@@ -335,15 +598,34 @@ int mstk_xattn_fwd(const mstk_xattn_args* a, void* stream) {
     p.x = a->x; p.kvp = a->kvp; p.bias = a->bias; p.out = a->out;
     p.b = a->b; p.l = a->l; p.s = a->s; p.e = a->e; p.heads = a->heads; p.ctot = a->ctot; p.kv_static = a->kv_static;
     const int J = a->heads * a->s;
+    if (a->dtype == MSTK_BF16) {
+        // tensor-core execution: query tiles of 16, chunks of at most 64 composed rows (multiples of 16)
+        const int Jp = (J + 15) & ~15;
+        const size_t fixed_m = (size_t)16 * (Jp + 4) * 4 + (size_t)Jp * 8 + (size_t)16 * (Jp + 8) * 2 + (size_t)16 * (a->e + 8) * 2;
+        const size_t row_m = (size_t)(a->e + 8) * 2;
+        MSTK_REQUIRE(fixed_m + 2 * 16 * row_m <= 200 * 1024, "xattn: %d style tokens x %d heads do not fit shared memory", a->s, a->heads);
+        int jcm = 64;
+        while (jcm > 16 && fixed_m + 2 * (size_t)jcm * row_m > 160 * 1024) jcm >>= 1;
+        p.jc = Jp < jcm ? Jp : jcm;  // the kernel stages min(jc, J - j0) rows and pads to 16 inside the buffer
+        p.jcw = 0;
+        const size_t smem_m = fixed_m + 2 * (size_t)p.jc * row_m;
+        const int grid_m = a->b * ((a->l + 15) / 16);
+        return a->e == 256 ? xattn_mma_launch<4>(p, smem_m, grid_m, (cudaStream_t)stream)
+                           : xattn_mma_launch<8>(p, smem_m, grid_m, (cudaStream_t)stream);
+    }
     const int esz = a->dtype == MSTK_F32 ? 4 : 2, vec = 16 / esz;
     const int lt = a->l <= 4 ? 4 : 16;
-    const int jc_max = a->dtype == MSTK_F32 ? 32 : 64;
-    p.jc = J < jc_max ? J : jc_max;
+    // rows per staged chunk: as many as fit next to the query tile and the score matrix (two chunk buffers), at most 64
+    const size_t fixed = ((size_t)lt * a->e + (size_t)J * lt + 2 * ((J + 3) & ~3)) * sizeof(float) + (size_t)lt * a->e * esz;
+    const size_t row = (size_t)(a->e + vec) * esz;
+    MSTK_REQUIRE(fixed + 2 * 16 * row <= 200 * 1024, "xattn: %d style tokens x %d heads do not fit shared memory", a->s, a->heads);
+    int jc = 64;
+    while (jc > 16 && fixed + 2 * (size_t)jc * row > 160 * 1024) jc >>= 1;
+    p.jc = J < jc ? J : jc;
     int jcw = 16;
     while (jcw < p.jc) jcw <<= 1;
     p.jcw = jcw;
-    const size_t smem = ((size_t)lt * a->e + (size_t)J * lt + ((J + 3) & ~3)) * sizeof(float) + (size_t)p.jc * (a->e + vec) * esz;
-    MSTK_REQUIRE(smem <= 200 * 1024, "xattn: %d style tokens x %d heads do not fit shared memory (%zu bytes)", a->s, a->heads, smem);
+    const size_t smem = fixed + 2 * (size_t)p.jc * row;
     const int tiles = (a->l + lt - 1) / lt;
     const int grid = a->b * tiles;
     return a->dtype == MSTK_F32 ? xattn_dispatch<float>(p, smem, lt, grid, (cudaStream_t)stream)
