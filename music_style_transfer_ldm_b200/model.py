@@ -612,8 +612,19 @@ class LDM(_Kernelised):
         return self._cached(("sched_host",), (ab,), build)
 
     def _step_times(self, times: List[int], b: int, device) -> torch.Tensor:
-        """fp32 timestep per (step, sample); built outside any graph capture (H2D copy)."""
-        return torch.tensor(times[:-1], dtype=torch.float32).repeat_interleave(b).to(device)
+        """fp32 timestep per (step, sample).  Cached per (schedule, batch, device): the H2D copy must happen outside
+        any graph capture (the whole-call graphs look it up while capturing; their eager warm-up fills the cache)."""
+        cache = self.__dict__.setdefault("_tt_cache", {})
+        key = (tuple(times), int(b), str(device))
+        tt = cache.get(key)
+        if tt is None:
+            if torch.cuda.is_current_stream_capturing():
+                raise MstkError("internal: step-time table requested for the first time inside a graph capture")
+            tt = torch.tensor(times[:-1], dtype=torch.float32).repeat_interleave(b).to(device)
+            if len(cache) >= 16:
+                cache.clear()
+            cache[key] = tt
+        return tt
 
     def _loop_body(self, x: torch.Tensor, s5: torch.Tensor, s6: torch.Tensor, times: List[int], eta: float, logs,
                    tt: torch.Tensor):
@@ -641,6 +652,64 @@ class LDM(_Kernelised):
 
     def _weights_sig(self):
         return tuple((p.data_ptr(), p._version) for p in list(self.unet.parameters()) + [self.noise_scheduler.alpha_bar_t])
+
+    def _weights_sig_full(self):
+        mods = (self.encoder, self.decoder, self.unet, self.style_encoder)
+        return tuple((p.data_ptr(), p._version) for m in mods for p in m.parameters()) + \
+            ((self.noise_scheduler.alpha_bar_t.data_ptr(), self.noise_scheduler.alpha_bar_t._version),)
+
+    def _bn_training(self) -> bool:
+        return any(isinstance(m, nn.BatchNorm2d) and m.training for m in list(self.encoder.modules()) + list(self.decoder.modules()))
+
+    def _graph_call(self, key, inputs, body, warm):
+        """A whole public call (VAE encode, style encoder, q-sample, the N-1 step loop, decode) as ONE CUDA graph per
+        (shapes, schedule, precision, module modes): ``inputs`` are copied into static buffers, the graph is replayed,
+        the outputs are cloned.  ``body(*static_inputs)`` is captured; ``warm(*static_inputs)`` is a short eager run that
+        fills the packed-weight caches and the split-K workspace first (BatchNorm buffers it moves are restored)."""
+        graphs = self.__dict__.setdefault("_graphs", {})
+        sig = self._weights_sig_full()
+        ent = graphs.get(key)
+        if ent is None or ent["sig"] != sig:
+            ent = {"sig": sig, "in": tuple(t.clone() for t in inputs)}
+            bn_train = self._bn_training()
+            bufs = [b for m in (self.encoder, self.decoder) for b in m.buffers()] if bn_train else []
+            snap = [b.clone() for b in bufs]
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            self.use_cuda_graphs = False           # the warm-up runs its short loop eagerly
+            try:
+                with torch.cuda.stream(side):
+                    warm(*ent["in"])
+            finally:
+                self.use_cuda_graphs = True
+            torch.cuda.current_stream().wait_stream(side)
+            for b, s0 in zip(bufs, snap):          # train-mode BatchNorm: the warm-up must not count as a forward pass
+                b.copy_(s0)
+            g = torch.cuda.CUDAGraph()
+            n0 = ops.LAUNCHES
+            with torch.cuda.graph(g):
+                ent["out"] = body(*ent["in"])
+            ent["graph"] = g
+            ent["launches"], ops.LAUNCHES = ops.LAUNCHES - n0, n0      # capture enqueues nothing
+            # the graph holds raw pointers to the packed weights: keep them alive with it
+            ent["keep"] = [dict(m.__dict__.get("_mstk_cache", {})) for m in self.modules()]
+            if len(graphs) >= 8:
+                graphs.clear()
+            graphs[key] = ent
+        for dst, src in zip(ent["in"], inputs):
+            dst.copy_(src)
+        ent["graph"].replay()
+        ops._count(ent["launches"])
+        if self._bn_training():                    # running buffers moved behind the version counters: eval folds are stale
+            for m in (self.encoder, self.decoder):
+                cache = m.__dict__.get("_mstk_cache")
+                if cache:
+                    for k in [k for k in cache if isinstance(k, tuple) and len(k) == 3 and k[1] == "fold"]:
+                        del cache[k]
+        return tuple(o.clone() for o in ent["out"])
+
+    def _whole_call_graph_ok(self) -> bool:
+        return self.use_cuda_graphs and not torch.cuda.is_current_stream_capturing() and not self.collect_sampling_logs
 
     def _run_loop(self, z_t: torch.Tensor, s5: torch.Tensor, s6: torch.Tensor, times: List[int], eta: float):
         """z_t [B,h,w,C] fp32 NHWC -> (x [B,h,w,C] fp32, logs-or-None).  Eager, or one CUDA graph
@@ -726,11 +795,19 @@ class LDM(_Kernelised):
     def style_ddim_sample_wrapper(self, z_shape, style_spec, timesteps=100, eta=0.0):
         """model.py:382-407.  Returns decoded spectrograms in [0,1]."""
         ss = self._spec_nhwc(style_spec, "style_ddim_sample_wrapper")
-        z_t = torch.randn(z_shape).to(ss.device)                       # CPU draw then move, as model.py:395
-        styles = self.style_encoder._forward_nhwc(ss)
-        x, _ = self._sample(ops.nchw_to_nhwc(z_t.float().contiguous(), torch.float32), styles[4], styles[5],
-                            self._times(self.num_timesteps - 1, timesteps), eta)
-        dec = self.decoder._forward_nhwc(x, unit_range=True)
+        z_t = torch.randn(z_shape).to(ss.device).float().contiguous()  # CPU draw then move, as model.py:395
+
+        def body(ss_, z_t_, n=timesteps):
+            styles = self.style_encoder._forward_nhwc(ss_)
+            x, _ = self._sample(ops.nchw_to_nhwc(z_t_, torch.float32), styles[4], styles[5], self._times(self.num_timesteps - 1, n), eta)
+            return (self.decoder._forward_nhwc(x, unit_range=True),)
+
+        if self._whole_call_graph_ok() and timesteps >= 2:
+            self._step_times(self._times(self.num_timesteps - 1, timesteps), ss.shape[0], ss.device)
+            key = ("style_only", tuple(ss.shape), tuple(z_t.shape), int(timesteps), float(eta), self._precision(), self._bn_training())
+            (dec,) = self._graph_call(key, (ss, z_t), body, lambda a, b: body(a, b, n=2))
+        else:
+            (dec,) = body(ss, z_t)
         return dec.view(dec.shape[0], 1, dec.shape[1], dec.shape[2])
 
     def content_style_transfer_wrapper(self, content_spec, style_spec, num_timesteps=250, eta=0.0):
@@ -738,13 +815,23 @@ class LDM(_Kernelised):
         cs = self._spec_nhwc(content_spec, "content_style_transfer_wrapper")
         ss = self._spec_nhwc(style_spec, "content_style_transfer_wrapper")
         dev = cs.device
-        z0 = self.encoder._forward_nhwc(cs)
-        b, h, w, c = z0.shape
-        t = torch.full((b,), num_timesteps - 1, dtype=torch.int64, device=dev)
-        noise = torch.randn_like(torch.empty((b, c, h, w), dtype=torch.float32, device=dev))
-        z_t, _ = ops.q_sample(z0, ops.nchw_to_nhwc(noise, torch.float32), self.noise_scheduler.alpha_bar_t, t)
-        styles = self.style_encoder._forward_nhwc(ss)
-        x, _ = self._sample(z_t, styles[4], styles[5], self._times(num_timesteps - 1, num_timesteps), eta)
-        dec = self.decoder._forward_nhwc(x, unit_range=True)
-        ztd = self.decoder._forward_nhwc(z_t)
+        b, hh, ww = cs.shape[0], cs.shape[1] // 8, cs.shape[2] // 8
+        c = self.encoder.encoder[6].out_channels
+        # the q-sample noise is drawn with torch's generator as the reference does (model.py:110, the only draw of the call)
+        noise = torch.randn_like(torch.empty((b, c, hh, ww), dtype=torch.float32, device=dev))
+
+        def body(cs_, ss_, noise_, n=num_timesteps):
+            z0 = self.encoder._forward_nhwc(cs_)
+            t = torch.full((b,), n - 1, dtype=torch.int64, device=dev)
+            z_t, _ = ops.q_sample(z0, ops.nchw_to_nhwc(noise_, torch.float32), self.noise_scheduler.alpha_bar_t, t)
+            styles = self.style_encoder._forward_nhwc(ss_)
+            x, _ = self._sample(z_t, styles[4], styles[5], self._times(n - 1, n), eta)
+            return self.decoder._forward_nhwc(x, unit_range=True), self.decoder._forward_nhwc(z_t)
+
+        if self._whole_call_graph_ok() and num_timesteps >= 2:
+            self._step_times(self._times(num_timesteps - 1, num_timesteps), b, dev)
+            key = ("transfer", tuple(cs.shape), int(num_timesteps), float(eta), self._precision(), self._bn_training())
+            dec, ztd = self._graph_call(key, (cs, ss, noise), body, lambda a, s_, e_: body(a, s_, e_, n=2))
+        else:
+            dec, ztd = body(cs, ss, noise)
         return dec.view(b, 1, dec.shape[1], dec.shape[2]), ztd.view(b, 1, ztd.shape[1], ztd.shape[2])
