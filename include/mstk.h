@@ -173,6 +173,14 @@ typedef struct mstk_attn_args {
 int mstk_attention_fwd(const mstk_attn_args* a, void* stream);
 
 /* ------------------------------------------------------------------------------
+ * fp32 mode on the tensor cores (csrc/split_f32.cu): [rows, c] fp32 -> [rows, 3c] bf16 with every value carried as
+ * hi + lo; weights == 0: [hi | lo | hi] (activations, NHWC rows = pixels), weights != 0: [hi | hi | lo] (packed
+ * conv weights, rows = taps * cout).  A bf16 mstk_conv2d_fwd over the 3c channels with fp32 output then equals the
+ * fp32 contraction to ~1e-5 relative.  c % 8 == 0.
+ * ---------------------------------------------------------------------------- */
+int mstk_split3(const float* src, void* dst, size_t rows, int c, int weights, void* stream);
+
+/* ------------------------------------------------------------------------------
  * Style cross-attention with the projections composed into the style side (same layer:
  * CrossAttention.forward, models/model.py:126-160; algebra in csrc/xattn.cu).  The style map
  * is projected ONCE per sampling loop by a k1 mstk_conv2d_fwd with the composed weight

@@ -105,6 +105,7 @@ SIGNATURES = {
     "mstk_bn_apply": (c_int, [C.POINTER(BnArgs), c_void_p]),
     "mstk_time_embed": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "mstk_attention_fwd": (c_int, [C.POINTER(AttnArgs), c_void_p]),
+    "mstk_split3": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_void_p]),
     "mstk_xattn_ctot": (c_int, [c_int, c_int]),
     "mstk_xattn_compose": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "mstk_xattn_fwd": (c_int, [C.POINTER(XattnArgs), c_void_p]),

@@ -104,6 +104,40 @@ def conv_out_hw(h, w, ksize, stride, transposed):
     return (h + 2 * pad - ksize) // stride + 1, (w + 2 * pad - ksize) // stride + 1
 
 
+# fp32 mode: contractions whose shapes fit the tcgen05 kernel run there on split (hi + lo) bf16 operands
+# (csrc/split_f32.cu); False sends every fp32 contraction to the CUDA-core kernel
+FP32_TC = True
+
+
+def split3(src: torch.Tensor, weights: bool = False) -> torch.Tensor:
+    """[..., c] fp32 -> [..., 3c] bf16: [hi | lo | hi] (activations) or [hi | hi | lo] (packed weights)"""
+    lib = _lib.load()
+    _dev(src, "split3.src")
+    c = src.shape[-1]
+    dst = torch.empty(tuple(src.shape[:-1]) + (3 * c,), dtype=torch.bfloat16, device=src.device)
+    check(lib.mstk_split3(_p(src), _p(dst), src.numel() // c, c, 1 if weights else 0, _stream()), "mstk_split3")
+    _count(1)
+    return dst
+
+
+def _conv_fp32_tc(x, wpacked, bias, *, ksize, stride, transposed, act, add, add_nc, stats, ddim, out_dtype, out_scale, out_shift, out, want_y):
+    """fp32 conv on the tensor cores: split operands, one bf16 tcgen05 launch with fp32 output, residual added after"""
+    w3 = getattr(wpacked, "_mstk_w3", None)
+    if w3 is None:
+        with torch.no_grad():
+            w3 = split3(wpacked, weights=True)
+        wpacked._mstk_w3 = w3                    # lives and dies with this packed copy of the parameter
+    x3 = split3(x)
+    y = conv(x3, w3, bias, ksize=ksize, stride=stride, transposed=transposed, act=act, add_nc=add_nc, stats=stats, ddim=ddim,
+             out_dtype=out_dtype or torch.float32, out_scale=out_scale, out_shift=out_shift, out=out, want_y=want_y, backend=BACKEND_TCGEN05)
+    if add is not None:
+        lib = _lib.load()
+        n, c = y.shape[0], y.shape[-1]
+        check(lib.mstk_add_bcast(_p(y), _p(add), None, _p(y), n, y.numel() // (n * c), c, dtype_code(y), _stream()), "mstk_add_bcast")
+        _count(1)
+    return y
+
+
 def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *, ksize: int, stride: int = 1,
          transposed: bool = False, act: int = ACT_NONE, add: Optional[torch.Tensor] = None,
          add_nc: Optional[torch.Tensor] = None, stats: Optional[torch.Tensor] = None, ddim: Optional[Ddim] = None,
@@ -118,6 +152,11 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
         raise MstkError(f"conv: packed weight {tuple(wpacked.shape)} does not match cin={cin} k={ksize}")
     if wpacked.dtype != x.dtype:
         raise MstkError(f"conv: weight dtype {wpacked.dtype} != activation dtype {x.dtype}")
+    if (FP32_TC and backend == BACKEND_AUTO and x.dtype == torch.float32 and cin % 32 == 0 and cout % 16 == 0
+            and (add is None or (want_y and add.dtype == torch.float32 and (out_dtype or x.dtype) == torch.float32))
+            and tc_eligible(torch.bfloat16, 3 * cin, cout, stride, transposed, h, w)):
+        return _conv_fp32_tc(x, wpacked, bias, ksize=ksize, stride=stride, transposed=transposed, act=act, add=add, add_nc=add_nc,
+                             stats=stats, ddim=ddim, out_dtype=out_dtype, out_scale=out_scale, out_shift=out_shift, out=out, want_y=want_y)
     ho, wo = conv_out_hw(h, w, ksize, stride, transposed)
     out_dtype = out_dtype or x.dtype
     y = None

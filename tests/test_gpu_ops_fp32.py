@@ -18,6 +18,16 @@ def _ops():
     return ops
 
 
+@pytest.fixture(autouse=True)
+def _cuda_core_fp32():
+    """this file pins the fp32 CUDA-core kernels; the split-operand tensor-core route of fp32 mode has its own
+    tests (test_gpu_fp32_tc.py)"""
+    ops = _ops()
+    old, ops.FP32_TC = ops.FP32_TC, False
+    yield
+    ops.FP32_TC = old
+
+
 CONV_CASES = [
     # n, h, w, cin, cout, k, stride, transposed
     (2, 16, 16, 32, 64, 3, 1, False),
