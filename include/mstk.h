@@ -268,8 +268,11 @@ typedef struct mstk_mel_args {
     const float* mel_fb;     /* [n_mels, 1025] filterbank (host builds it, fp32)   */
     void* work; size_t work_bytes;
     int32_t b, len, n_mels, crop_frames;
+    const int32_t* band_ranges;  /* optional [n_mels][2]: first / one-past-last non-zero bin of every band, from
+                                  * mstk_mel_band_ranges (once per filterbank); NULL = derived on every call */
 } mstk_mel_args;
 size_t mstk_mel_workspace_bytes(int b, int len, int n_mels);
+int mstk_mel_band_ranges(const float* mel_fb, int n_mels, int32_t* ranges, void* stream);
 int mstk_mel_frontend(const mstk_mel_args* a, void* stream);
 
 /* ==============================================================================

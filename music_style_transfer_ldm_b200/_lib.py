@@ -61,7 +61,7 @@ class XattnArgs(C.Structure):
 class MelArgs(C.Structure):
     _fields_ = [("wave", c_void_p), ("out", c_void_p), ("db_out", c_void_p), ("mel_fb", c_void_p),
                 ("work", c_void_p), ("work_bytes", c_size_t),
-                ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int)]
+                ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int), ("band_ranges", c_void_p)]
 
 
 class WgradArgs(C.Structure):
@@ -138,6 +138,7 @@ SIGNATURES = {
     "mstk_kl_grad": (c_int, [c_void_p, c_void_p, c_int, c_float, c_void_p, c_size_t, c_void_p]),
     "mstk_adam_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p]),
     "mstk_mel_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "mstk_mel_band_ranges": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),
 }
 

@@ -56,14 +56,15 @@ def slaney_filterbank(sr: int, n_mels: int, n_fft: int = N_FFT) -> np.ndarray:
 class AudioPreprocessor:
     def __init__(self, target_sr=22050):
         self.target_sr = target_sr
-        self._fb: Dict[Tuple[int, int, int], torch.Tensor] = {}
+        self._fb: Dict[Tuple[int, int, int], Tuple[torch.Tensor, torch.Tensor]] = {}
 
     # -- helpers ---------------------------------------------------------------------------
     def _filterbank(self, sr: int, n_mels: int, device) -> torch.Tensor:
         key = (int(sr), int(n_mels), torch.device(device).index or 0)
         fb = self._fb.get(key)
         if fb is None:
-            fb = torch.from_numpy(slaney_filterbank(int(sr), int(n_mels))).to(device).contiguous()
+            fbm = torch.from_numpy(slaney_filterbank(int(sr), int(n_mels))).to(device).contiguous()
+            fb = (fbm, ops.mel_band_ranges(fbm))          # the non-zero bin range of every band, once per filterbank
             self._fb[key] = fb
         return fb
 
@@ -88,7 +89,8 @@ class AudioPreprocessor:
         return CUDA tensors [b, n_mels, frames]."""
         w, single = self._device_waves(audio)
         frames = 1 + w.shape[1] // HOP_LENGTH
-        _, db = ops.mel_frontend(w, self._filterbank(sr, n_mels, w.device), crop_frames=frames, want_db=True)
+        fb, ranges = self._filterbank(sr, n_mels, w.device)
+        _, db = ops.mel_frontend(w, fb, crop_frames=frames, want_db=True, band_ranges=ranges)
         if isinstance(audio, torch.Tensor):
             return db[0] if single else db
         out = db.cpu().numpy()
@@ -118,5 +120,6 @@ class AudioPreprocessor:
             crop_frames = (frames // 64) * 64
         if crop_frames <= 0 or crop_frames > frames:
             raise MstkError(f"spectrogram_batch: crop_frames={crop_frames} outside 1..{frames}")
-        out, _ = ops.mel_frontend(w, self._filterbank(sr or self.target_sr, n_mels, w.device), crop_frames=crop_frames)
+        fb, ranges = self._filterbank(sr or self.target_sr, n_mels, w.device)
+        out, _ = ops.mel_frontend(w, fb, crop_frames=crop_frames, band_ranges=ranges)
         return out.view(out.shape[0], 1, n_mels, crop_frames)

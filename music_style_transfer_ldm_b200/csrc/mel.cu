@@ -3,17 +3,28 @@
 // the image scaling of data/audio_processor.py:44-73; the filterbank matrix
 // is passed in by the host (it is a constant of the configuration, not hot-path work).
 //
-// Kernel 1: one CTA per (frame, clip).  The 2048 real samples are packed as a 1024-point
-// complex sequence, transformed with an in-shared-memory radix-2 FFT (256 threads), split
-// back into the 1025-bin real spectrum, and reduced against each mel band's non-zero bin
-// range by one warp per band.  The clip maximum is kept with an integer atomicMax on the
-// (non-negative) float bit pattern.
-// Kernel 2: dB, floor at -80 dB, quantise, crop; 1 thread per output pixel.
+// Kernel 1 (mel_power_kernel): ONE WARP PER FRAME, the FFT in registers.  The 2048 windowed real samples are packed
+// as a 1024-point complex sequence z and transformed as 32 x 32 (n = 32a + b, k = k1 + 32 k2):
+//     Y[b][k1] = W_1024^(b k1) * DFT32_a(z[32a + b])      lane = b, 32 points in registers, fully unrolled radix-2 DIF
+//     Z[k1 + 32 k2] = DFT32_b(Y[b][k1])                   lane = k1, after one transposition through shared memory
+// with compile-time 32-point twiddles and a shared table e^{-2 pi i m / 2048} (m < 2048) for the inter-pass
+// twiddles, the Hann window (0.5 - 0.5 Re) and the real-spectrum split.  The partner Z[1024 - k] of the split lives
+// in lane 32 - k1 at a statically known register: one shuffle pair per bin, no second pass through memory.  Power
+// spectrum -> shared memory -> lane m of the warp reduces mel band m, m + 32, ... over its non-zero bin range
+// (ranges computed once per filterbank, mstk_mel_band_ranges).  A CTA = 8 warps x 2 frames = 16 consecutive frames
+// of one clip: the mel powers are staged as [band][16 frames] and written as 64-byte runs (the previous kernel wrote
+// one 4-byte value per 32-byte sector, recomputed sincospi in every butterfly and ran 10 block-wide barriers per
+// frame).  The clip maximum is kept with an integer atomicMax on the (non-negative) float bit pattern.
+// Kernel 2 (mel_db_kernel): dB, floor at -80 dB, quantise, crop; 1 thread per output pixel, frame-contiguous.
 #include "common.cuh"
 
 namespace mstk {
 
 constexpr int NFFT = 2048, HOP = 512, NBINS = NFFT / 2 + 1, NC = NFFT / 2;
+constexpr int MEL_WARPS = 8, MEL_FPW = 2, MEL_FPC = MEL_WARPS * MEL_FPW;     // frames per CTA
+constexpr int MEL_TW = NFFT + NFFT / 32;                                      // twiddle table, one pad slot per 32 entries
+constexpr int MEL_BUF = 32 * 33;                                              // transposition buffer (float2) per warp
+constexpr int MEL_PW = NBINS + 3;                                             // power spectrum (float) per warp
 
 __global__ void mel_ranges_kernel(const float* __restrict__ fb, int n_mels, int2* ranges) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
@@ -25,64 +36,146 @@ __global__ void mel_ranges_kernel(const float* __restrict__ fb, int n_mels, int2
     ranges[m] = make_int2(lo, hi);
 }
 
-__global__ void __launch_bounds__(256) mel_power_kernel(const float* __restrict__ wave, int len, int frames, const float* __restrict__ fb,
-                                                       const int2* __restrict__ ranges, int n_mels, float* __restrict__ melp,
-                                                       unsigned int* __restrict__ clipmax) {
-    __shared__ float2 z[NC];
-    __shared__ float pw[NBINS + 3];
-    const int frame = blockIdx.x, clip = blockIdx.y, tid = threadIdx.x;
-    const float* wv = wave + (size_t)clip * len;
-    const int start = frame * HOP - NFFT / 2;
-    // load, window (periodic Hann: 0.5 - 0.5 cos(2 pi n / N)), pack, bit-reverse
-    for (int i = tid; i < NC; i += 256) {
-        const int n0 = 2 * i, n1 = 2 * i + 1;
-        const int s0 = start + n0, s1 = start + n1;
-        const float x0 = (s0 >= 0 && s0 < len) ? wv[s0] : 0.f;
-        const float x1 = (s1 >= 0 && s1 < len) ? wv[s1] : 0.f;
-        const float w0 = 0.5f - 0.5f * cospif(2.0f * (float)n0 / (float)NFFT);
-        const float w1 = 0.5f - 0.5f * cospif(2.0f * (float)n1 / (float)NFFT);
-        const int r = (int)(__brev((unsigned)i) >> 22);   // 10-bit reversal
-        z[r] = make_float2(x0 * w0, x1 * w1);
+__device__ __forceinline__ float2 cmul(const float2 a, const float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__host__ __device__ constexpr int brev5(int r) { return ((r & 1) << 4) | ((r & 2) << 2) | (r & 4) | ((r & 8) >> 2) | ((r & 16) >> 4); }
+
+// e^{-2 pi i j / 32}, j = 0..15, folded to literals when j is a compile-time constant (every call site is unrolled)
+__device__ __forceinline__ float2 w32(const int j) {
+    switch (j) {
+        case 0: return make_float2(1.f, 0.f);
+        case 1: return make_float2(0.98078528040323043f, -0.19509032201612825f);
+        case 2: return make_float2(0.92387953251128674f, -0.38268343236508978f);
+        case 3: return make_float2(0.83146961230254524f, -0.55557023301960218f);
+        case 4: return make_float2(0.70710678118654757f, -0.70710678118654757f);
+        case 5: return make_float2(0.55557023301960229f, -0.83146961230254524f);
+        case 6: return make_float2(0.38268343236508984f, -0.92387953251128674f);
+        case 7: return make_float2(0.19509032201612833f, -0.98078528040323043f);
+        case 8: return make_float2(0.f, -1.f);
+        case 9: return make_float2(-0.19509032201612819f, -0.98078528040323043f);
+        case 10: return make_float2(-0.38268343236508973f, -0.92387953251128674f);
+        case 11: return make_float2(-0.55557023301960196f, -0.83146961230254535f);
+        case 12: return make_float2(-0.70710678118654746f, -0.70710678118654757f);
+        case 13: return make_float2(-0.83146961230254535f, -0.55557023301960218f);
+        case 14: return make_float2(-0.92387953251128674f, -0.38268343236508989f);
+        default: return make_float2(-0.98078528040323043f, -0.19509032201612861f);
     }
-    __syncthreads();
-    // 10 radix-2 DIT stages, 512 butterflies each
-    for (int s = 1; s <= 10; ++s) {
-        const int half = 1 << (s - 1);
-        for (int j = tid; j < NC / 2; j += 256) {
-            const int grp = j / half, pos = j - grp * half;
-            const int i0 = grp * 2 * half + pos, i1 = i0 + half;
-            float sn, cs;
-            sincospif(-(float)pos / (float)half, &sn, &cs);   // e^{-i pi pos/half}
-            const float2 a = z[i0], b = z[i1];
-            const float2 t = make_float2(b.x * cs - b.y * sn, b.x * sn + b.y * cs);
-            z[i0] = make_float2(a.x + t.x, a.y + t.y);
-            z[i1] = make_float2(a.x - t.x, a.y - t.y);
+}
+
+// 32-point DFT in registers, radix-2 decimation in frequency: on return v[r] holds X[brev5(r)]
+__device__ __forceinline__ void fft32(float2 (&v)[32]) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+#pragma unroll
+        for (int g = 0; g < 32; g += 2 * s) {
+#pragma unroll
+            for (int j = 0; j < s; ++j) {
+                const float2 a = v[g + j], b = v[g + j + s];
+                v[g + j] = make_float2(a.x + b.x, a.y + b.y);
+                const float2 d = make_float2(a.x - b.x, a.y - b.y);
+                const int tw = j * (16 / s);
+                if (tw == 0) v[g + j + s] = d;
+                else if (tw == 8) v[g + j + s] = make_float2(d.y, -d.x);          // * (-i)
+                else v[g + j + s] = cmul(d, w32(tw));
+            }
         }
-        __syncthreads();
     }
-    // split: X[k] = (Z[k] + conj(Z[NC-k]))/2 - (i/2) e^{-2 pi i k/NFFT} (Z[k] - conj(Z[NC-k]))
-    for (int k = tid; k <= NC; k += 256) {
-        const float2 zk = z[k & (NC - 1)];
-        const float2 zc = z[(NC - k) & (NC - 1)];
-        const float ex = 0.5f * (zk.x + zc.x), ey = 0.5f * (zk.y - zc.y);     // even part
-        const float ox = 0.5f * (zk.y + zc.y), oy = -0.5f * (zk.x - zc.x);    // odd part = -i/2 (Z[k] - conj(Z[NC-k]))
+}
+
+__device__ __forceinline__ int tw_slot(const int m) { return m + (m >> 5); }
+
+__global__ void __launch_bounds__(MEL_WARPS * 32) mel_power_kernel(const float* __restrict__ wave, int len, int frames,
+                                                                  const float* __restrict__ fb, const int2* __restrict__ ranges, int n_mels,
+                                                                  float* __restrict__ melp, unsigned int* __restrict__ clipmax) {
+    extern __shared__ __align__(16) uint8_t mel_smem[];
+    float2* tw = reinterpret_cast<float2*>(mel_smem);                         // [MEL_TW] e^{-2 pi i m / 2048}
+    float2* bufs = tw + MEL_TW;                                               // [MEL_WARPS][MEL_BUF]
+    float* pws = reinterpret_cast<float*>(bufs + MEL_WARPS * MEL_BUF);        // [MEL_WARPS][MEL_PW]
+    float* outs = pws + MEL_WARPS * MEL_PW;                                   // [n_mels][MEL_FPC]
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int clip = blockIdx.y, f0 = blockIdx.x * MEL_FPC;
+    for (int m = tid; m < NFFT; m += MEL_WARPS * 32) {
         float sn, cs;
-        sincospif(-2.0f * (float)k / (float)NFFT, &sn, &cs);
-        const float re = ex + (ox * cs - oy * sn);
-        const float im = ey + (ox * sn + oy * cs);
-        pw[k] = re * re + im * im;
+        sincospif(-(float)m * (2.0f / (float)NFFT), &sn, &cs);
+        tw[tw_slot(m)] = make_float2(cs, sn);
     }
     __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int m = warp; m < n_mels; m += 8) {
-        const int2 rg = ranges[m];
-        float acc = 0.f;
-        for (int k = rg.x + lane; k < rg.y; k += 32) acc = fmaf(fb[(size_t)m * NBINS + k], pw[k], acc);
-        acc = warp_sum(acc);
-        if (lane == 0) {
-            melp[((size_t)clip * n_mels + m) * frames + frame] = acc;
-            atomicMax(clipmax + clip, __float_as_uint(fmaxf(acc, 0.f)));
+    const float* wv = wave + (size_t)clip * len;
+    const bool vec_ok = ((len & 1) == 0) && ((reinterpret_cast<uintptr_t>(wave) & 7) == 0);
+    float2* buf = bufs + warp * MEL_BUF;
+    float* pw = pws + warp * MEL_PW;
+    float wmax = 0.f;
+    for (int fi = 0; fi < MEL_FPW; ++fi) {
+        const int fl = warp * MEL_FPW + fi, frame = f0 + fl;
+        if (frame >= frames) break;                                           // warp-uniform
+        const int start = frame * HOP - NFFT / 2;                             // even
+        float2 v[32];
+        // ---- pass 1: lane = b, v[a] = window * z[32a + b] ----
+#pragma unroll
+        for (int a = 0; a < 32; ++a) {
+            const int n = 32 * a + lane, s0 = start + 2 * n;
+            float x0, x1;
+            if (vec_ok && s0 >= 0 && s0 + 1 < len) {
+                const float2 t = __ldg(reinterpret_cast<const float2*>(wv + s0));
+                x0 = t.x; x1 = t.y;
+            } else {
+                x0 = (s0 >= 0 && s0 < len) ? __ldg(wv + s0) : 0.f;
+                x1 = (s0 + 1 >= 0 && s0 + 1 < len) ? __ldg(wv + s0 + 1) : 0.f;
+            }
+            // periodic Hann 0.5 - 0.5 cos(2 pi m / 2048), m = 2n and 2n + 1 (two consecutive table slots: 2n is even)
+            const float c0 = tw[tw_slot(2 * n)].x, c1 = tw[tw_slot(2 * n + 1)].x;
+            v[a] = make_float2(x0 * (0.5f - 0.5f * c0), x1 * (0.5f - 0.5f * c1));
         }
+        fft32(v);
+        __syncwarp();                                                          // previous frame's reads of buf are done
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const int k1 = brev5(r);
+            const float2 y = (k1 == 0) ? v[r] : cmul(v[r], tw[tw_slot(2 * lane * k1)]);   // W_1024^(b k1)
+            buf[k1 * 33 + lane] = y;
+        }
+        __syncwarp();
+        // ---- pass 2: lane = k1 ----
+#pragma unroll
+        for (int b = 0; b < 32; ++b) v[b] = buf[lane * 33 + b];
+        fft32(v);                                                              // v[r] = Z[lane + 32 brev5(r)]
+        // ---- real-spectrum split: X[k] = E[k] + e^{-2 pi i k / 2048} O[k], partner Z[1024 - k] by shuffle ----
+        const int src = (32 - lane) & 31;
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const int k2 = brev5(r);
+            const int k = lane + 32 * k2;
+            const float2 zk = v[r];
+            const float2 own = v[brev5((32 - k2) & 31)];                       // lane 0: Z[32 (32 - k2) mod 1024]
+            float2 zc = make_float2(__shfl_sync(0xffffffffu, v[31 - r].x, src), __shfl_sync(0xffffffffu, v[31 - r].y, src));
+            if (lane == 0) zc = own;
+            const float ex = 0.5f * (zk.x + zc.x), ey = 0.5f * (zk.y - zc.y);
+            const float ox = 0.5f * (zk.y + zc.y), oy = -0.5f * (zk.x - zc.x);
+            const float2 t = tw[tw_slot(k)];
+            const float re = ex + (ox * t.x - oy * t.y);
+            const float im = ey + (ox * t.y + oy * t.x);
+            pw[k] = re * re + im * im;
+        }
+        if (lane == 0) { const float d = v[0].x - v[0].y; pw[NC] = d * d; }    // Nyquist bin: Z[0] with e^{-i pi} = -1
+        __syncwarp();
+        // ---- mel bands: lane m, m + 32, ... ----
+        for (int m = lane; m < n_mels; m += 32) {
+            const int2 rg = ranges[m];
+            const float* fr = fb + (size_t)m * NBINS;
+            float acc = 0.f;
+            for (int k = rg.x; k < rg.y; ++k) acc = fmaf(__ldg(fr + k), pw[k], acc);
+            outs[m * MEL_FPC + fl] = acc;
+            wmax = fmaxf(wmax, acc);
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    if (lane == 0 && wmax > 0.f) atomicMax(clipmax + clip, __float_as_uint(wmax));
+    __syncthreads();
+    const int nf = min(MEL_FPC, frames - f0);
+    for (int i = tid; i < n_mels * MEL_FPC; i += MEL_WARPS * 32) {
+        const int m = i / MEL_FPC, j = i - m * MEL_FPC;
+        if (j < nf) melp[((size_t)clip * n_mels + m) * frames + f0 + j] = outs[i];
     }
 }
 
@@ -119,8 +212,15 @@ size_t mstk_mel_workspace_bytes(int b, int len, int n_mels) {
     size_t bytes = (size_t)b * n_mels * frames * sizeof(float);     // mel power
     bytes = (bytes + 255) & ~(size_t)255;
     bytes += ((size_t)b * sizeof(unsigned int) + 255) & ~(size_t)255;   // clip max
-    bytes += ((size_t)n_mels * sizeof(int2) + 255) & ~(size_t)255;      // band ranges
+    bytes += ((size_t)n_mels * sizeof(int2) + 255) & ~(size_t)255;      // band ranges (when the caller passes none)
     return bytes;
+}
+
+int mstk_mel_band_ranges(const float* mel_fb, int n_mels, int32_t* ranges, void* stream) {
+    MSTK_REQUIRE(mel_fb && ranges && n_mels > 0, "mel_band_ranges: bad args");
+    mel_ranges_kernel<<<(n_mels + 127) / 128, 128, 0, (cudaStream_t)stream>>>(mel_fb, n_mels, reinterpret_cast<int2*>(ranges));
+    MSTK_CHECK_LAUNCH("mel_ranges");
+    return MSTK_OK;
 }
 
 int mstk_mel_frontend(const mstk_mel_args* a, void* stream) {
@@ -135,12 +235,26 @@ int mstk_mel_frontend(const mstk_mel_args* a, void* stream) {
     size_t off = (((size_t)a->b * a->n_mels * frames * sizeof(float)) + 255) & ~(size_t)255;
     unsigned int* clipmax = reinterpret_cast<unsigned int*>(w + off);
     off += ((size_t)a->b * sizeof(unsigned int) + 255) & ~(size_t)255;
-    int2* ranges = reinterpret_cast<int2*>(w + off);
+    const int2* ranges = reinterpret_cast<const int2*>(a->band_ranges);
     cudaError_t e = cudaMemsetAsync(clipmax, 0, (size_t)a->b * sizeof(unsigned int), st);
     if (e != cudaSuccess) return cuda_fail(e, "mel memset");
-    mel_ranges_kernel<<<(a->n_mels + 127) / 128, 128, 0, st>>>(a->mel_fb, a->n_mels, ranges);
-    MSTK_CHECK_LAUNCH("mel_ranges");
-    mel_power_kernel<<<dim3(frames, a->b), 256, 0, st>>>(a->wave, a->len, frames, a->mel_fb, ranges, a->n_mels, melp, clipmax);
+    if (!ranges) {      // one-off callers: derive the non-zero bin range of every band here (mstk_mel_band_ranges caches it)
+        int2* r = reinterpret_cast<int2*>(w + off);
+        mel_ranges_kernel<<<(a->n_mels + 127) / 128, 128, 0, st>>>(a->mel_fb, a->n_mels, r);
+        MSTK_CHECK_LAUNCH("mel_ranges");
+        ranges = r;
+    }
+    const size_t smem = (size_t)MEL_TW * sizeof(float2) + (size_t)MEL_WARPS * MEL_BUF * sizeof(float2) +
+                        (size_t)MEL_WARPS * MEL_PW * sizeof(float) + (size_t)a->n_mels * MEL_FPC * sizeof(float);
+    MSTK_REQUIRE(smem <= 200 * 1024, "mel: n_mels %d does not fit the staging tile", a->n_mels);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        e = cudaFuncSetAttribute(mel_power_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "mel smem attr");
+        smem_set = 200 * 1024;
+    }
+    mel_power_kernel<<<dim3((frames + MEL_FPC - 1) / MEL_FPC, a->b), MEL_WARPS * 32, smem, st>>>(a->wave, a->len, frames, a->mel_fb, ranges,
+                                                                                             a->n_mels, melp, clipmax);
     MSTK_CHECK_LAUNCH("mel_power");
     const size_t total = (size_t)a->b * a->n_mels * frames;
     size_t blocks = (total + 255) / 256;

@@ -465,7 +465,16 @@ def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
-def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, want_db: bool = False):
+def mel_band_ranges(mel_fb: torch.Tensor) -> torch.Tensor:
+    """[n_mels, 2] int32: first / one-past-last non-zero bin of every band of a filterbank (once per filterbank)"""
+    lib = _lib.load()
+    _dev(mel_fb, "mel.fb")
+    r = torch.empty((mel_fb.shape[0], 2), dtype=torch.int32, device=mel_fb.device)
+    check(lib.mstk_mel_band_ranges(_p(mel_fb), mel_fb.shape[0], _p(r), _stream()), "mstk_mel_band_ranges")
+    return r
+
+
+def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, want_db: bool = False, band_ranges: Optional[torch.Tensor] = None):
     lib = _lib.load()
     _dev(wave, "mel.wave"); _dev(mel_fb, "mel.fb")
     b, ln = wave.shape
@@ -475,9 +484,9 @@ def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, wan
     db = torch.empty((b, n_mels, frames), dtype=torch.float32, device=wave.device) if want_db else None
     nbytes = lib.mstk_mel_workspace_bytes(b, ln, n_mels)
     work = torch.empty(nbytes, dtype=torch.uint8, device=wave.device)
-    a = _lib.MelArgs(_p(wave), _p(out), _p(db), _p(mel_fb), _p(work), nbytes, b, ln, n_mels, crop_frames)
+    a = _lib.MelArgs(_p(wave), _p(out), _p(db), _p(mel_fb), _p(work), nbytes, b, ln, n_mels, crop_frames, _p(band_ranges))
     check(lib.mstk_mel_frontend(C.byref(a), _stream()), "mstk_mel_frontend")
-    _count(3)
+    _count(2 if band_ranges is not None else 3)
     return out, db
 
 

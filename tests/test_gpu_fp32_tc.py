@@ -55,7 +55,8 @@ def test_conv_fp32_on_tensor_cores(case):
     assert_close(nchw(y), ref, 3e-5, "fp32 conv on tcgen05")
     n0 = ops.LAUNCHES
     y2 = ops.conv(xd, wp, b.to(DEV), ksize=k, stride=s, transposed=tr)
-    assert ops.LAUNCHES - n0 == 2 and torch.equal(y, y2)              # the split weight is cached with the packed weight
+    assert ops.LAUNCHES - n0 == 2                                     # the split weight is cached with the packed weight
+    assert_close(y2, y, 1e-6, "repeat (split-K partials meet in any order)")
     y_simt = ops.conv(xd, wp, b.to(DEV), ksize=k, stride=s, transposed=tr, backend=ops.BACKEND_SIMT)
     assert_close(y, y_simt, 3e-5, "vs the CUDA-core fp32 kernel")
 
