@@ -23,8 +23,8 @@ namespace mstk {
 constexpr int NFFT = 2048, HOP = 512, NBINS = NFFT / 2 + 1, NC = NFFT / 2;
 constexpr int MEL_WARPS = 8, MEL_FPW = 2, MEL_FPC = MEL_WARPS * MEL_FPW;     // frames per CTA
 constexpr int MEL_TW = NFFT + NFFT / 32;                                      // twiddle table, one pad slot per 32 entries
-constexpr int MEL_BUF = 32 * 33;                                              // transposition buffer (float2) per warp
-constexpr int MEL_PW = NBINS + 3;                                             // power spectrum (float) per warp
+constexpr int MEL_BUF = 32 * 33;                                              // per warp: transposition buffer (float2), then reused
+                                                                              // for the power spectrum (1025 floats)
 
 __global__ void mel_ranges_kernel(const float* __restrict__ fb, int n_mels, int2* ranges) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,14 +83,13 @@ __device__ __forceinline__ void fft32(float2 (&v)[32]) {
 
 __device__ __forceinline__ int tw_slot(const int m) { return m + (m >> 5); }
 
-__global__ void __launch_bounds__(MEL_WARPS * 32) mel_power_kernel(const float* __restrict__ wave, int len, int frames,
+__global__ void __launch_bounds__(MEL_WARPS * 32, 2) mel_power_kernel(const float* __restrict__ wave, int len, int frames,
                                                                   const float* __restrict__ fb, const int2* __restrict__ ranges, int n_mels,
                                                                   float* __restrict__ melp, unsigned int* __restrict__ clipmax) {
     extern __shared__ __align__(16) uint8_t mel_smem[];
     float2* tw = reinterpret_cast<float2*>(mel_smem);                         // [MEL_TW] e^{-2 pi i m / 2048}
     float2* bufs = tw + MEL_TW;                                               // [MEL_WARPS][MEL_BUF]
-    float* pws = reinterpret_cast<float*>(bufs + MEL_WARPS * MEL_BUF);        // [MEL_WARPS][MEL_PW]
-    float* outs = pws + MEL_WARPS * MEL_PW;                                   // [n_mels][MEL_FPC]
+    float* outs = reinterpret_cast<float*>(bufs + MEL_WARPS * MEL_BUF);       // [n_mels][MEL_FPC]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int clip = blockIdx.y, f0 = blockIdx.x * MEL_FPC;
     for (int m = tid; m < NFFT; m += MEL_WARPS * 32) {
@@ -102,28 +101,37 @@ __global__ void __launch_bounds__(MEL_WARPS * 32) mel_power_kernel(const float* 
     const float* wv = wave + (size_t)clip * len;
     const bool vec_ok = ((len & 1) == 0) && ((reinterpret_cast<uintptr_t>(wave) & 7) == 0);
     float2* buf = bufs + warp * MEL_BUF;
-    float* pw = pws + warp * MEL_PW;
+    float* pw = reinterpret_cast<float*>(buf);                                // the power spectrum overwrites the transposed tile
     float wmax = 0.f;
+#pragma unroll 1
     for (int fi = 0; fi < MEL_FPW; ++fi) {
         const int fl = warp * MEL_FPW + fi, frame = f0 + fl;
         if (frame >= frames) break;                                           // warp-uniform
         const int start = frame * HOP - NFFT / 2;                             // even
         float2 v[32];
         // ---- pass 1: lane = b, v[a] = window * z[32a + b] ----
+        if (vec_ok && start >= 0 && start + NFFT <= len) {                     // interior frame (warp-uniform): 8-byte loads, no predicates
+#pragma unroll
+            for (int a = 0; a < 32; ++a) {
+                const float2 t = __ldg(reinterpret_cast<const float2*>(wv + start) + 32 * a + lane);
+                v[a] = t;
+            }
+        } else {                                                               // the two frames at either end of a clip: zero padding
+#pragma unroll
+            for (int a = 0; a < 32; ++a) {
+                const int s0 = start + 2 * (32 * a + lane);
+                float x0 = 0.f, x1 = 0.f;
+                if (s0 >= 0 && s0 < len) x0 = __ldg(wv + s0);
+                if (s0 + 1 >= 0 && s0 + 1 < len) x1 = __ldg(wv + s0 + 1);
+                v[a] = make_float2(x0, x1);
+            }
+        }
 #pragma unroll
         for (int a = 0; a < 32; ++a) {
-            const int n = 32 * a + lane, s0 = start + 2 * n;
-            float x0, x1;
-            if (vec_ok && s0 >= 0 && s0 + 1 < len) {
-                const float2 t = __ldg(reinterpret_cast<const float2*>(wv + s0));
-                x0 = t.x; x1 = t.y;
-            } else {
-                x0 = (s0 >= 0 && s0 < len) ? __ldg(wv + s0) : 0.f;
-                x1 = (s0 + 1 >= 0 && s0 + 1 < len) ? __ldg(wv + s0 + 1) : 0.f;
-            }
-            // periodic Hann 0.5 - 0.5 cos(2 pi m / 2048), m = 2n and 2n + 1 (two consecutive table slots: 2n is even)
+            // periodic Hann 0.5 - 0.5 cos(2 pi m / 2048), m = 2n and 2n + 1, n = 32a + lane
+            const int n = 32 * a + lane;
             const float c0 = tw[tw_slot(2 * n)].x, c1 = tw[tw_slot(2 * n + 1)].x;
-            v[a] = make_float2(x0 * (0.5f - 0.5f * c0), x1 * (0.5f - 0.5f * c1));
+            v[a] = make_float2(v[a].x * (0.5f - 0.5f * c0), v[a].y * (0.5f - 0.5f * c1));
         }
         fft32(v);
         __syncwarp();                                                          // previous frame's reads of buf are done
@@ -137,6 +145,7 @@ __global__ void __launch_bounds__(MEL_WARPS * 32) mel_power_kernel(const float* 
         // ---- pass 2: lane = k1 ----
 #pragma unroll
         for (int b = 0; b < 32; ++b) v[b] = buf[lane * 33 + b];
+        __syncwarp();                                                          // the tile is dead: pw may overwrite it
         fft32(v);                                                              // v[r] = Z[lane + 32 brev5(r)]
         // ---- real-spectrum split: X[k] = E[k] + e^{-2 pi i k / 2048} O[k], partner Z[1024 - k] by shuffle ----
         const int src = (32 - lane) & 31;
@@ -245,7 +254,7 @@ int mstk_mel_frontend(const mstk_mel_args* a, void* stream) {
         ranges = r;
     }
     const size_t smem = (size_t)MEL_TW * sizeof(float2) + (size_t)MEL_WARPS * MEL_BUF * sizeof(float2) +
-                        (size_t)MEL_WARPS * MEL_PW * sizeof(float) + (size_t)a->n_mels * MEL_FPC * sizeof(float);
+                        (size_t)a->n_mels * MEL_FPC * sizeof(float);
     MSTK_REQUIRE(smem <= 200 * 1024, "mel: n_mels %d does not fit the staging tile", a->n_mels);
     static size_t smem_set = 0;
     if (smem > smem_set) {
