@@ -106,6 +106,7 @@ bool wgrad_tc_supported(const ConvP& p, int x_dtype, int dy_dtype);
 int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, cudaStream_t st);
 void tc_set_debug(long long* p);
 void tc_set_force(int bn, int sk, int stages, int pdl);
+void tc_set_persist(int on);
 const int* tc_last_config();
 
 // ---------------------------------------------------------------------------

@@ -102,6 +102,8 @@ int mstk_debug_tc_timeline(long long* dev_buf) { mstk::tc_set_debug(dev_buf); re
  * {BN, splitk, stages, smem, grid.x, grid.y, grid.z, KC} of the most recent tcgen05 launch */
 int mstk_debug_tc_force(int bn, int sk, int stages, int pdl) { mstk::tc_set_force(bn, sk, stages, pdl); return MSTK_OK; }
 const int* mstk_debug_tc_last_config(void) { return mstk::tc_last_config(); }
+/* 0: never take the persistent tile loop (conv_tcp_body.cuh); last_config()[1] == -1 marks a persistent launch */
+int mstk_debug_tc_persist(int on) { mstk::tc_set_persist(on); return MSTK_OK; }
 
 int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     mstk::ConvP p;

@@ -34,8 +34,17 @@
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include "conv_tc_body.cuh"
+#include "conv_tcp_body.cuh"
 
 namespace mstk {
+
+// persistent form (conv_tcp_body.cuh): one CTA per SM looping over tiles, double-buffered TMEM accumulators
+template <uint32_t F>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+conv_tcp_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcParams q, const __grid_constant__ TcpExtra x) {
+    extern __shared__ uint8_t smem_raw[];
+    conv_tcp_body<F>(maps, q, x, smem_raw);
+}
 
 template <uint32_t F>
 __global__ void __launch_bounds__(TC_THREADS, (F & F_DDIM) ? 1 : TC_MIN_CTAS)
@@ -63,6 +72,21 @@ static const TcVariant kVariants[] = {
 };
 static const int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 
+typedef void (*TcpKernel)(const TcMaps, const TcParams, const TcpExtra);
+struct TcpVariant { uint32_t flags; TcpKernel fn; };
+#define TCPV(f) {(f), conv_tcp_kernel<(f)>}
+static const TcpVariant kTcpVariants[] = {TCPV(F_STORE), TCPV(F_STORE | F_STATS), TCPV(F_STORE | F_ACTGEN), TCPV(F_STORE | F_STATS | F_ACTGEN)};
+static bool tcp_set_attrs() {
+    for (const TcpVariant& v : kTcpVariants) {
+        cudaError_t ea = cudaFuncSetAttribute(v.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        if (ea != cudaSuccess) {
+            cuda_fail(ea, "cudaFuncSetAttribute(conv_tcp_kernel)");
+            return false;
+        }
+    }
+    return true;
+}
+
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 static int g_tc_state = 0;   // 0 unknown, 1 ok, -1 failed
 static int g_num_sms = 148;
@@ -73,6 +97,7 @@ static int g_force_group = 0, g_trace = 0;
 // steps/s): a cluster needs 4-8 free SMs of one GPC at once, which stalls the programmatic-dependent-launch overlap
 // of consecutive layers.  Off by default.
 static int g_cluster = 0;
+static int g_persist = 1;     // MSTK_TC_PERSIST=0: never use the persistent tile loop (A/B comparisons)
 static int g_direct = 0;      // MSTK_TC_DIRECT=1: register -> global output stores instead of staging + TMA store
 static double g_split_cost = 1800.0;   // cost-model cycles charged to a split-K tile (MSTK_TC_SPLIT_COST)
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
@@ -82,6 +107,7 @@ void tc_set_force(int bn, int sk, int stages, int pdl) {
     g_force_bn = bn; g_force_sk = sk; g_force_stages = stages;
     if (pdl >= 0) g_pdl = pdl;
 }
+void tc_set_persist(int on) { g_persist = on; }
 static int g_last_cfg[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 const int* tc_last_config() { return g_last_cfg; }
 
@@ -106,6 +132,7 @@ bool tc_init() {
     if (const char* s = getenv("MSTK_TC_TRACE")) g_trace = atoi(s);
     if (const char* s = getenv("MSTK_TC_CLUSTER")) g_cluster = atoi(s);
     if (const char* s = getenv("MSTK_TC_DIRECT")) g_direct = atoi(s);
+    if (const char* s = getenv("MSTK_TC_PERSIST")) g_persist = atoi(s);
     if (const char* s = getenv("MSTK_TC_SPLIT_COST")) g_split_cost = atof(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
@@ -116,6 +143,10 @@ bool tc_init() {
             g_tc_state = -1;
             return false;
         }
+    }
+    if (!tcp_set_attrs()) {
+        g_tc_state = -1;
+        return false;
     }
     g_tc_state = 1;
     return true;
@@ -312,9 +343,67 @@ static int encode_out_maps(const ConvP& p, const TcConfig& c, const void* base, 
     return MSTK_OK;
 }
 
+// Persistent tile loop: throughput-bound grids only (several tiles per SM), plain bias / activation / BatchNorm-sum
+// epilogues.  BN = the widest tile that divides Cout (<= 128: two accumulators fit 256 TMEM columns), the smem ring as
+// deep as 200 KB allow next to the separate output staging tile.
+static bool choose_config_persistent(const ConvP& p, TcConfig& c, TcpExtra& x) {
+    if (!g_persist || !p.y || p.add || p.add_nc || p.has_ddim) return false;
+    memset(&c, 0, sizeof(c));
+    c.Wt = pow2_divisor(p.Wg, TILE_M);
+    c.Ht = pow2_divisor(p.Hg, TILE_M / c.Wt);
+    c.Nt = TILE_M / (c.Wt * c.Ht);
+    c.tiles_w = p.Wg / c.Wt;
+    c.tiles_h = p.Hg / c.Ht;
+    c.tiles_n = (p.N + c.Nt - 1) / c.Nt;
+    c.KC = (p.Cin % 64 == 0) ? 64 : 32;
+    c.kb_per_tap = p.Cin / c.KC;
+    c.BN = 0;
+    for (int bn = 128; bn >= 16; bn >>= 1)
+        if (p.Cout % bn == 0) { c.BN = bn; break; }
+    if (!c.BN) return false;
+    c.splitk = 1;
+    const long long mtiles = (long long)c.tiles_w * c.tiles_h * c.tiles_n;
+    const long long ntiles = mtiles * (p.Cout / c.BN) * p.nphases;
+    if (ntiles < 3ll * g_num_sms || ntiles > 0x7fffffffll) return false;
+    int min_kb = 1 << 30;
+    for (int i = 0; i < p.nphases; ++i) {
+        const int kb = p.ph[i].ntaps * c.kb_per_tap;
+        if (kb < min_kb) min_kb = kb;
+    }
+    c.out_esz = p.out_dtype == MSTK_F32 ? 4 : 2;
+    c.out_rowbytes = c.BN * c.out_esz >= 128 ? 128 : c.BN * c.out_esz;
+    c.out_chunks = c.BN * c.out_esz / c.out_rowbytes;
+    c.add_rowbytes = c.out_rowbytes; c.add_chunks = 0;
+    const size_t a_bytes = (size_t)TILE_M * c.KC * 2;
+    const size_t b_bytes = (((size_t)c.BN * c.KC * 2) + 1023) & ~(size_t)1023;
+    const size_t sub = a_bytes + b_bytes;
+    const size_t outb = ((size_t)TILE_M * c.BN * c.out_esz + 1023) & ~(size_t)1023;
+    const size_t budget = 200 * 1024 - outb - (size_t)c.BN * 12 - 1024;
+    // k-blocks per ring stage: up to 8 MMAs behind one barrier round trip, but at least 3 stages in flight
+    int grp = 8 / (c.KC / 16);
+    if (grp > min_kb) grp = min_kb;
+    while (grp > 1 && budget / (sub * grp) < 3) --grp;
+    int stages = (int)(budget / (sub * grp));
+    if (stages > MAX_STAGES) stages = MAX_STAGES;
+    while (stages * grp > 30) --stages;
+    if (stages < 2) return false;
+    c.kgroup = grp; c.stages = stages;
+    int cols = 32;
+    while (cols < 2 * c.BN) cols <<= 1;
+    c.tmem_cols = cols;
+    x.ntiles = (int)ntiles; x.mtiles = (int)mtiles; x.ny = p.Cout / c.BN;
+    x.off_out = (uint32_t)(sub * grp * stages);
+    x.off_bias = (uint32_t)(x.off_out + outb);
+    c.smem_bytes = x.off_bias + (size_t)c.BN * 12 + 1024;
+    return true;
+}
+
 int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cudaStream_t st) {
     if (!tc_init()) return MSTK_EUNSUPPORTED;
-    TcConfig c = choose_config(p);
+    TcConfig c;
+    TcpExtra px;
+    const bool persistent = choose_config_persistent(p, c, px);
+    if (!persistent) c = choose_config(p);
     TcParams q;
     memset(&q, 0, sizeof(q));
     q.p = p;
@@ -394,6 +483,33 @@ int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cuda
         for (int i = 0; i < 4; ++i) maps.add[i] = maps.a[0];
     }
 
+    if (persistent) {
+        uint32_t need = F_STORE;
+        if (p.stats) need |= F_STATS;
+        if (p.affine || (p.act != MSTK_ACT_NONE && p.act != MSTK_ACT_RELU)) need |= F_ACTGEN;
+        TcpKernel pfn = nullptr;
+        for (const TcpVariant& v : kTcpVariants)
+            if (v.flags == need) pfn = v.fn;
+        cudaLaunchConfig_t pc;
+        memset(&pc, 0, sizeof(pc));
+        pc.gridDim = dim3((unsigned)(px.ntiles < g_num_sms ? px.ntiles : g_num_sms), 1, 1);
+        pc.blockDim = dim3(TC_THREADS, 1, 1);
+        pc.dynamicSmemBytes = c.smem_bytes;
+        pc.stream = st;
+        cudaLaunchAttribute pattr[1];
+        pattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        pattr[0].val.programmaticStreamSerializationAllowed = 1;
+        pc.attrs = pattr;
+        pc.numAttrs = g_pdl ? 1 : 0;
+        g_last_cfg[0] = c.BN; g_last_cfg[1] = -1; g_last_cfg[2] = c.stages; g_last_cfg[3] = (int)c.smem_bytes;
+        g_last_cfg[4] = px.mtiles; g_last_cfg[5] = px.ny; g_last_cfg[6] = p.nphases; g_last_cfg[7] = c.KC;
+        if (g_trace)
+            fprintf(stderr, "[mstk conv_tcp] persistent: %d tiles on %u CTAs, BN %d KC %d stages %d kgroup %d smem %zu\n", px.ntiles, pc.gridDim.x,
+                    c.BN, c.KC, c.stages, c.kgroup, c.smem_bytes);
+        cudaError_t pe = cudaLaunchKernelEx(&pc, pfn, maps, q, px);
+        if (pe != cudaSuccess) return cuda_fail(pe, "conv_tcp launch");
+        return MSTK_OK;
+    }
     g_last_cfg[0] = c.BN; g_last_cfg[1] = c.splitk; g_last_cfg[2] = c.stages; g_last_cfg[3] = (int)c.smem_bytes;
     g_last_cfg[4] = c.tiles_w * c.tiles_h * c.tiles_n; g_last_cfg[5] = p.Cout / c.BN; g_last_cfg[6] = p.nphases * c.splitk; g_last_cfg[7] = c.KC;
     cudaLaunchConfig_t cfg;
