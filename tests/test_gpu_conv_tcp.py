@@ -31,7 +31,7 @@ CASES = [
     (16, 64, 512, 64, 128, 3, 2, False),     # config 2 encoder
     (48, 64, 64, 64, 128, 3, 1, False),      # VGGish conv2
     (50, 32, 32, 128, 256, 3, 1, False),     # VGGish conv3: two output-channel tiles per pixel tile; 50 images: ragged tail
-    (21, 16, 16, 256, 512, 3, 1, False),     # VGGish conv5: K = 2304, 4 channel tiles
+    (117, 16, 16, 256, 512, 3, 1, False),    # VGGish conv5: K = 2304, 4 channel tiles per pixel tile, ragged tail
     (70, 16, 16, 64, 32, 3, 2, True),        # convT k3: phases with 1 / 2 / 2 / 4 taps (different K per tile), BN = 32
 ]
 
@@ -65,7 +65,7 @@ def test_persistent_matches_one_tile_kernel(case):
         lib.mstk_debug_tc_persist(1)
     assert torch.equal(y_p, y_o), "bf16 output of the two kernels differs"
     assert torch.equal(y_ps, y_os)
-    assert_close(stats_p, stats_o, 1e-9, "BatchNorm sums")
+    assert_close(stats_p, stats_o, 1e-6, "BatchNorm sums (fp32 per-CTA partials meet in any order)")
     ref = conv_ref(x.float(), wt[:, :, 0, 0] if k == 1 else wt, b, k, s, tr)
     assert_close(nchw(y_ps), ref, 2e-5, "vs torch fp32 on the same bf16 operands")
     assert_close(nchw(y_pt), torch.tanh(ref) * 0.5 + 0.5, 2e-5, "tanh + affine epilogue")
