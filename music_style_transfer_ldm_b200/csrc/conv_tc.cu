@@ -97,6 +97,7 @@ static int g_force_group = 0, g_trace = 0;
 // steps/s): a cluster needs 4-8 free SMs of one GPC at once, which stalls the programmatic-dependent-launch overlap
 // of consecutive layers.  Off by default.
 static int g_cluster = 0;
+static int g_tcp_grp = 0, g_tcp_stages = 0, g_tcp_bn = 0;   // MSTK_TCP_FORCE="kgroup,stages,BN" (tuning sweeps)
 static int g_persist = 1;     // MSTK_TC_PERSIST=0: never use the persistent tile loop (A/B comparisons)
 static int g_direct = 0;      // MSTK_TC_DIRECT=1: register -> global output stores instead of staging + TMA store
 static double g_split_cost = 1800.0;   // cost-model cycles charged to a split-K tile (MSTK_TC_SPLIT_COST)
@@ -133,6 +134,7 @@ bool tc_init() {
     if (const char* s = getenv("MSTK_TC_CLUSTER")) g_cluster = atoi(s);
     if (const char* s = getenv("MSTK_TC_DIRECT")) g_direct = atoi(s);
     if (const char* s = getenv("MSTK_TC_PERSIST")) g_persist = atoi(s);
+    if (const char* s = getenv("MSTK_TCP_FORCE")) sscanf(s, "%d,%d,%d", &g_tcp_grp, &g_tcp_stages, &g_tcp_bn);
     if (const char* s = getenv("MSTK_TC_SPLIT_COST")) g_split_cost = atof(s);
     if (const char* s = getenv("MSTK_PDL")) g_pdl = atoi(s) != 0;
     if (const char* s = getenv("MSTK_TC_FORCE")) sscanf(s, "%d,%d,%d,%d", &g_force_bn, &g_force_sk, &g_force_stages, &g_force_group);
@@ -358,8 +360,8 @@ static bool choose_config_persistent(const ConvP& p, TcConfig& c, TcpExtra& x) {
     c.KC = (p.Cin % 64 == 0) ? 64 : 32;
     c.kb_per_tap = p.Cin / c.KC;
     c.BN = 0;
-    for (int bn = 128; bn >= 16; bn >>= 1)
-        if (p.Cout % bn == 0) { c.BN = bn; break; }
+    for (int bn = 256; bn >= 16; bn >>= 1)
+        if (p.Cout % bn == 0 && (!g_tcp_bn || bn <= g_tcp_bn)) { c.BN = bn; break; }
     if (!c.BN) return false;
     c.splitk = 1;
     const long long mtiles = (long long)c.tiles_w * c.tiles_h * c.tiles_n;
@@ -377,13 +379,15 @@ static bool choose_config_persistent(const ConvP& p, TcConfig& c, TcpExtra& x) {
     const size_t a_bytes = (size_t)TILE_M * c.KC * 2;
     const size_t b_bytes = (((size_t)c.BN * c.KC * 2) + 1023) & ~(size_t)1023;
     const size_t sub = a_bytes + b_bytes;
-    const size_t outb = ((size_t)TILE_M * c.BN * c.out_esz + 1023) & ~(size_t)1023;
+    const size_t outb = ((size_t)TILE_M * (c.BN < 128 ? c.BN : 128) * c.out_esz + 1023) & ~(size_t)1023;   // one column block of <= 128
     const size_t budget = 200 * 1024 - outb - (size_t)c.BN * 12 - 1024;
     // k-blocks per ring stage: up to 8 MMAs behind one barrier round trip, but at least 3 stages in flight
     int grp = 8 / (c.KC / 16);
     if (grp > min_kb) grp = min_kb;
     while (grp > 1 && budget / (sub * grp) < 3) --grp;
+    if (g_tcp_grp > 0 && g_tcp_grp <= min_kb) grp = g_tcp_grp;
     int stages = (int)(budget / (sub * grp));
+    if (g_tcp_stages > 0 && g_tcp_stages <= stages) stages = g_tcp_stages;
     if (stages > MAX_STAGES) stages = MAX_STAGES;
     while (stages * grp > 30) --stages;
     if (stages < 2) return false;

@@ -87,9 +87,12 @@ __device__ __forceinline__ void conv_tcp_body(const TcMaps& maps, const TcParams
                 if (first < 0) first += S;
                 for (int grp = first; grp < ngroups; grp += S) {
                     const int cnt = total_kb - grp * G < G ? total_kb - grp * G : G;
-                    if (g >= cnt) continue;
                     const int use = (gcount + grp) / S;               // earlier uses of this stage
+                    // EVERY lane of the stage observes EVERY release of it, also when a short group leaves it nothing to
+                    // load: a lane that skipped a use could not tell release #u from release #u+2 by parity and would
+                    // overwrite operands the MMAs have not read yet
                     if (use > 0) mbar_wait(&empty_bar[s], (uint32_t)((use - 1) & 1));
+                    if (g >= cnt) continue;
                     const int kb = grp * G + g;
                     const int tap_i = kb / q.kb_per_tap, cb = kb - tap_i * q.kb_per_tap;
                     const Tap tp = ph.taps[tap_i];
@@ -166,14 +169,19 @@ __device__ __forceinline__ void conv_tcp_body(const TcMaps& maps, const TcParams
         const int n_l = row >> (q.wt_shift + q.ht_shift);
         const int half = warp >= 7 ? 1 : 0;
         const int et = half ? (int)threadIdx.x - 96 : (int)threadIdx.x - 64;         // 0..255
-        const int cbeg = BN >= 32 ? half * (BN >> 1) : 0;
-        const int cend = BN >= 32 ? cbeg + (BN >> 1) : (half ? 0 : BN);
+        // the tile's columns are processed in blocks of CB <= 128 (one staging tile of 128 rows x CB columns, reused per
+        // block; BN = 256 tiles have two); within a block the two warps of a TMEM lane quarter take half the columns each
+        const int CB = BN < 128 ? BN : 128, nblk = BN / CB;
+        const int cb_lo = CB >= 32 ? half * (CB >> 1) : 0;
+        const int cb_hi = CB >= 32 ? cb_lo + (CB >> 1) : (half ? 0 : CB);
+        const int blk_chunks = CB * q.out_esz / q.out_rowbytes;
         float* sstat = sbias + BN;
         const int out_cpr = q.out_rowbytes / q.out_esz;
         const int out_sh = 31 - __clz(out_cpr);
         const int out_esz = q.out_esz, out_rowbytes = q.out_rowbytes;
         uint8_t* const out_stage = smem + x.off_out;
         const int act = p.act;
+        if (f_stats) { for (int i = et; i < 2 * BN; i += EPI_THREADS) sstat[i] = 0.f; }
         int it = 0;
         for (int t = blockIdx.x; t < x.ntiles; t += gridDim.x, ++it) {
             const int by = t % x.ny, r = t / x.ny;
@@ -184,12 +192,14 @@ __device__ __forceinline__ void conv_tcp_body(const TcMaps& maps, const TcParams
             const bool row_ok = n0 + n_l < p.N;
             (void)h_l; (void)w_l;
             if (et < BN) sbias[et] = p.bias ? __ldg(p.bias + co0 + et) : 0.f;
-            if (f_stats) { for (int i = et; i < 2 * BN; i += EPI_THREADS) sstat[i] = 0.f; }
             epi_bar();            // bias visible; also: the previous tile's TMA store has finished reading the staging tile
             const int buf = it & 1;
             mbar_wait(&tfull_bar[buf], (uint32_t)((it >> 1) & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(qd * 32) << 16);
+            for (int blk = 0; blk < nblk; ++blk) {
+            const int cbeg = blk * CB + cb_lo, cend = blk * CB + cb_hi;
+            if (blk > 0) epi_bar();                 // the previous block's TMA store has finished reading the staging tile
             float vnext[16];
             if (cbeg < cend) tmem_ld16_issue(taddr + (uint32_t)cbeg, vnext);
             for (int c = cbeg; c < cend; c += 16) {
@@ -225,7 +235,7 @@ __device__ __forceinline__ void conv_tcp_body(const TcMaps& maps, const TcParams
                     }
                     v[jj] = xv;
                 }
-                uint8_t* ob = out_stage + (size_t)(c >> out_sh) * TILE_M * out_rowbytes;
+                uint8_t* ob = out_stage + (size_t)((c - blk * CB) >> out_sh) * TILE_M * out_rowbytes;
                 const int j0 = ((c & (out_cpr - 1)) * out_esz) >> 4;
                 if (out_esz == 4) {
 #pragma unroll
@@ -241,23 +251,28 @@ __device__ __forceinline__ void conv_tcp_body(const TcMaps& maps, const TcParams
                     *reinterpret_cast<uint4*>(ob + swz_off(row, j0 + 1, out_rowbytes)) = pk[1];
                 }
             }
-            // this thread's TMEM reads are complete (tcgen05.wait::ld above): hand the accumulator buffer back
-            tc_fence_before();
-            mbar_arrive(&tempty_bar[buf]);
-            if (f_stats) {
-                epi_bar();
-                if (et < BN) {
-                    atomicAdd(p.stats + co0 + et, (double)sstat[et]);
-                    atomicAdd(p.stats + p.Cout + co0 + et, (double)sstat[BN + et]);
-                }
+            if (blk == nblk - 1) {
+                // this thread's TMEM reads are complete (tcgen05.wait::ld above): hand the accumulator buffer back
+                tc_fence_before();
+                mbar_arrive(&tempty_bar[buf]);
             }
             fence_async_smem();
             epi_bar();
             if (et == 0) {
-                for (int ch = 0; ch < q.out_chunks; ++ch)
-                    tma_store_4d(&maps.out[phase_idx], smem_base + x.off_out + (uint32_t)(ch * TILE_M * out_rowbytes), co0 + ch * out_cpr, w0, h0, n0);
+                for (int ch = 0; ch < blk_chunks; ++ch)
+                    tma_store_4d(&maps.out[phase_idx], smem_base + x.off_out + (uint32_t)(ch * TILE_M * out_rowbytes),
+                                 co0 + blk * CB + ch * out_cpr, w0, h0, n0);
                 bulk_commit();
                 bulk_wait_read();
+            }
+            }
+            if (f_stats) {      // the per-CTA column sums are complete behind the last block's barrier
+                if (et < BN) {
+                    atomicAdd(p.stats + co0 + et, (double)sstat[et]);
+                    atomicAdd(p.stats + p.Cout + co0 + et, (double)sstat[BN + et]);
+                    sstat[et] = 0.f;                 // ready for the next tile (its first atomics are behind a barrier)
+                    sstat[BN + et] = 0.f;
+                }
             }
         }
         tc_fence_before();
