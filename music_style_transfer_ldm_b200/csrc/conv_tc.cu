@@ -98,7 +98,12 @@ static int g_force_group = 0, g_trace = 0;
 // of consecutive layers.  Off by default.
 static int g_cluster = 0;
 static int g_tcp_grp = 0, g_tcp_stages = 0, g_tcp_bn = 0;   // MSTK_TCP_FORCE="kgroup,stages,BN" (tuning sweeps)
-static int g_persist = 1;     // MSTK_TC_PERSIST=0: never use the persistent tile loop (A/B comparisons)
+// Persistent tile loop (conv_tcp_body.cuh), OFF by default.  Measured on B200 (tools/tcp_tune.py, round 2): with one
+// CTA per SM the smem ring (<= 160 KB in flight) and the single MMA issuer bound it at 640-1080 TFLOP/s on the VGGish
+// stack against 690-1184 for two resident one-tile CTAs (two issuers, ~200 KB in flight), and the config-2 VAE layers do
+// not move (92 us for the K = 512 convT either way: they are bound by the 16x re-read of the activation tile through
+// L2, not by per-tile prologues).  MSTK_TC_PERSIST=1 / mstk_debug_tc_persist(1) select it; the tests keep it correct.
+static int g_persist = 0;
 static int g_direct = 0;      // MSTK_TC_DIRECT=1: register -> global output stores instead of staging + TMA store
 static double g_split_cost = 1800.0;   // cost-model cycles charged to a split-K tile (MSTK_TC_SPLIT_COST)
 static int g_force_bn = 0, g_force_sk = 0, g_force_stages = 0;
