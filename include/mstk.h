@@ -354,6 +354,8 @@ int mstk_sum_hw(const void* a, const void* a2, int dtype, int b, int64_t hw, int
 /* out = y + add (same shape, optional) + add_nc[n, c] (optional): the un-fused form of the conv epilogue adds,
  * used in training where the pre-add ReLU output must be kept for the mask */
 int mstk_add_bcast(const void* y, const void* add, const float* add_nc, void* out, int n, int64_t hw, int c, int dtype, void* stream);
+/* x[i] *= *factor (device scalar): chains a loss gradient with the upstream scalar of its autograd node */
+int mstk_scale_dev(float* x, const float* factor, size_t count, void* stream);
 /* g = scale * (a - b), a and b fp32, g in g_dtype: gradient of mean((a-b)^2) with scale = 2*w/count */
 int mstk_mse_grad(const float* a, const float* b, float scale, void* g, int g_dtype, size_t count, void* stream);
 /* gradient w.r.t. eps_hat of  w_d*mean((eps_hat-eps)^2) + L(x0_pred(eps_hat)):

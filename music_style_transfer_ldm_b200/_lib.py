@@ -131,6 +131,7 @@ SIGNATURES = {
     "mstk_gelu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "mstk_sum_hw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "mstk_add_bcast": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int, c_void_p]),
+    "mstk_scale_dev": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "mstk_mse_grad": (c_int, [c_void_p, c_void_p, c_float, c_void_p, c_int, c_size_t, c_void_p]),
     "mstk_eps_grad": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int64, c_void_p]),
     "mstk_adam_step_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float, c_float, c_void_p, c_float, c_void_p]),

@@ -638,6 +638,12 @@ __global__ void add_bcast_kernel(const void* __restrict__ y, const void* __restr
         store_from_f(out, dtype, i, v);
     }
 }
+// x *= *factor (the upstream scalar of a loss's autograd node stays on the device: no host sync in loss.backward())
+__global__ void scale_dev_kernel(float* __restrict__ x, const float* __restrict__ factor, size_t count) {
+    const float f = __ldg(factor);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) x[i] *= f;
+}
+
 __global__ void mse_grad_kernel(const float* __restrict__ a, const float* __restrict__ b, float scale, void* g, int g_dtype, size_t count) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x)
         store_from_f(g, g_dtype, i, scale * (a[i] - b[i]));
@@ -1102,6 +1108,12 @@ int mstk_add_bcast(const void* y, const void* add, const float* add_nc, void* ou
     const size_t total = (size_t)n * hw * c;
     add_bcast_kernel<<<bw_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(y, add, add_nc, out, hw, c, dtype, total);
     MSTK_CHECK_LAUNCH("add_bcast");
+    return MSTK_OK;
+}
+int mstk_scale_dev(float* x, const float* factor, size_t count, void* stream) {
+    MSTK_REQUIRE(x && factor && count > 0, "scale_dev: bad args");
+    scale_dev_kernel<<<bw_grid(count, 256), 256, 0, (cudaStream_t)stream>>>(x, factor, count);
+    MSTK_CHECK_LAUNCH("scale_dev");
     return MSTK_OK;
 }
 int mstk_mse_grad(const float* a, const float* b, float scale, void* g, int g_dtype, size_t count, void* stream) {

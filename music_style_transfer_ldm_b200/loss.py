@@ -42,11 +42,26 @@ def _as_cuda_f32(x: torch.Tensor, who: str) -> torch.Tensor:
     return x.detach().float().contiguous()
 
 
+def _mse(a, b, who: str):
+    """mean((a - b)^2); with gradients enabled and a differentiable operand, an autograd node (autograd.MseFn)"""
+    if torch.is_grad_enabled() and (a.requires_grad or b.requires_grad):
+        from .autograd import MseFn
+        if not (a.is_cuda and b.is_cuda):
+            raise MstkError(f"{who}: inputs must be CUDA tensors; the loss kernels are CUDA (sm_100a) only")
+        return MseFn.apply(a, b)
+    return ops.mse(_as_cuda_f32(a, who), _as_cuda_f32(b, who)).squeeze(0)
+
+
 def diffusion_loss(noise_pred, noise_target):
-    return ops.mse(_as_cuda_f32(noise_pred, "diffusion_loss"), _as_cuda_f32(noise_target, "diffusion_loss")).squeeze(0)
+    return _mse(noise_pred, noise_target, "diffusion_loss")
 
 
 def kl_regularization_loss(latent):
+    if torch.is_grad_enabled() and latent.requires_grad:
+        from .autograd import KlFn
+        if not latent.is_cuda:
+            raise MstkError("kl_regularization_loss: input must be a CUDA tensor")
+        return KlFn.apply(latent)
     return ops.kl(_as_cuda_f32(latent, "kl_regularization_loss")).squeeze(0)
 
 
@@ -136,7 +151,7 @@ def perceptual_loss(original, reconstructed, feature_extractor_type: str = "vggi
 
 
 def compression_loss(original, reconstructed, latent, feature_extractor):
-    mse_loss = ops.mse(_as_cuda_f32(reconstructed, "compression_loss"), _as_cuda_f32(original, "compression_loss")).squeeze(0)
+    mse_loss = _mse(reconstructed, original, "compression_loss")
     perc = perceptual_loss(original, reconstructed, config["compression_feature_extractor"], feature_extractor=feature_extractor)
     return mse_loss + 0.1 * perc + 0.01 * kl_regularization_loss(latent)
 

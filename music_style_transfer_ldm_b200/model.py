@@ -74,6 +74,11 @@ class _Kernelised(nn.Module):
         return self._cached((name, "f32"), (t,), lambda: t.float().contiguous())
 
 
+def _guard(who, module, y, *inputs):
+    from .autograd import guard
+    return guard(who, module, y, *inputs)
+
+
 def _need_cuda(x: torch.Tensor, who: str) -> None:
     if not x.is_cuda:
         raise MstkError(f"{who}: input is on {x.device}; this implementation runs on sm_100a kernels only (no CPU fallback)")
@@ -222,7 +227,7 @@ class SpectrogramEncoder(_Kernelised):
         if x.shape[1] != 1:
             raise MstkError("SpectrogramEncoder expects [B,1,H,W]")
         z = self._forward_nhwc(x.view(x.shape[0], x.shape[2], x.shape[3], 1))
-        return ops.nhwc_to_nchw(z)
+        return _guard("SpectrogramEncoder", self, ops.nhwc_to_nchw(z), x)
 
 
 class SpectrogramDecoder(_Kernelised):
@@ -255,7 +260,7 @@ class SpectrogramDecoder(_Kernelised):
         _need_cuda(z, "SpectrogramDecoder")
         zl = ops.nchw_to_nhwc(z.detach().float().contiguous(), _act_dtype(self._precision()))
         y = self._forward_nhwc(zl)
-        return y.view(y.shape[0], 1, y.shape[1], y.shape[2])
+        return _guard("SpectrogramDecoder", self, y.view(y.shape[0], 1, y.shape[1], y.shape[2]), z)
 
 
 class StyleEncoder(_Kernelised):
@@ -295,7 +300,7 @@ class StyleEncoder(_Kernelised):
         outs = self._forward_nhwc(s_nhwc)
         res = _StyleDict({f"s{i + 1}": ops.nhwc_to_nchw(o) for i, o in enumerate(outs)})
         res._nhwc = {f"s{i + 1}": o for i, o in enumerate(outs)}
-        return res
+        return _guard("StyleEncoder", self, res, style_spectrogram)
 
 
 class _StyleDict(dict):
@@ -400,7 +405,7 @@ class CrossAttention(_Kernelised):
             raise MstkError("CrossAttention: style map must have the spatial size of the features")
         f = ops.nchw_to_nhwc(unet_features.detach().float().contiguous(), adt)
         s = ops.nchw_to_nhwc(style_embedding.detach().float().contiguous(), adt)
-        return ops.nhwc_to_nchw(self._forward_nhwc(f, self._project_style(s)))
+        return _guard("CrossAttention", self, ops.nhwc_to_nchw(self._forward_nhwc(f, self._project_style(s))), unet_features, style_embedding)
 
 
 class SinusoidalPositionEmbeddings(_Kernelised):
@@ -497,7 +502,7 @@ class UNet(_Kernelised):
             raise MstkError("UNet: s5 / s6 must be 1/4 and 1/8 of the latent resolution")
         kv2, kv1 = self._project_style(s5, s6)
         eps = self._forward_nhwc(zl, self._time_embedding(t.to(z.device)), kv2, kv1)
-        return ops.nhwc_to_nchw(eps)
+        return _guard("UNet", self, ops.nhwc_to_nchw(eps), z, *style_embedding.values())
 
 
 class LDM(_Kernelised):
@@ -579,7 +584,11 @@ class LDM(_Kernelised):
         return x.view(x.shape[0], x.shape[2], x.shape[3], 1)
 
     def forward(self, x, style, t):
-        """model.py:355-379.  Returns dict(z_t, noise, noise_pred, z_0, reconstructed), NCHW fp32."""
+        """model.py:355-379.  Returns dict(z_t, noise, noise_pred, z_0, reconstructed), NCHW fp32.  With gradients
+        enabled the outputs carry an autograd node whose backward is the explicit reverse sweep (autograd.py)."""
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            from .autograd import ldm_forward
+            return ldm_forward(self, x, style, t)
         adt = _act_dtype(self._precision())
         xs = self._spec_nhwc(x, "LDM.forward")
         ss = self._spec_nhwc(style, "LDM.forward")

@@ -612,6 +612,17 @@ def add_bcast(y: torch.Tensor, add: Optional[torch.Tensor] = None, add_nc: Optio
     return out
 
 
+def scale_dev_(x: torch.Tensor, factor: torch.Tensor) -> torch.Tensor:
+    """x (fp32, in place) *= factor (a 1-element fp32 CUDA tensor)"""
+    lib = _lib.load()
+    _dev(x, "scale_dev.x")
+    if x.dtype != torch.float32 or factor.dtype != torch.float32 or factor.numel() != 1 or not factor.is_cuda:
+        raise MstkError("scale_dev_: fp32 tensor and a 1-element fp32 CUDA factor expected")
+    check(lib.mstk_scale_dev(_p(x), _p(factor), x.numel(), _stream()), "mstk_scale_dev")
+    _count()
+    return x
+
+
 def mse_grad(a: torch.Tensor, b: torch.Tensor, scale: float, g_dtype: torch.dtype) -> torch.Tensor:
     lib = _lib.load()
     g = torch.empty(a.shape, dtype=g_dtype, device=a.device)

@@ -262,6 +262,10 @@ class LDMTrainer:
         vals = torch.stack([out[k] for k in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]).tolist()   # ONE host sync
         return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), vals))
 
+    def _G(self, param: torch.Tensor) -> torch.Tensor:
+        """where the reverse sweep accumulates the gradient of ``param`` (the trainer: the arena view behind .grad)"""
+        return param.grad
+
     def _sync_sums(self, sums):
         self.reducer.all_reduce_small(sums)
 
@@ -321,12 +325,12 @@ class LDMTrainer:
         e, m = ca.embed_dim, ca.multihead_attn
         b, h, w, _ = d_out.shape
         feat, style, q, kv, o = sv["feat"], sv["style"], sv["q"], sv["kv"], sv["o"]
-        ops.act_bwd(d_out, None, act=ACT_NONE, dbias=m.out_proj.bias.grad, want_g=False)
-        ops.wgrad(o.view(b, h, w, e), d_out, m.out_proj.weight.grad, ksize=1)
+        ops.act_bwd(d_out, None, act=ACT_NONE, dbias=self._G(m.out_proj.bias), want_g=False)
+        ops.wgrad(o.view(b, h, w, e), d_out, self._G(m.out_proj.weight), ksize=1)
         d_o = self._dgrad(ca, "wo", m.out_proj, d_out)
         dq, dkv = ops.attention_bwd(q.view(b, h * w, e), kv[:, :, :e], kv[:, :, e:], d_o.view(b, h * w, e), ca.num_heads)
         dq4, dkv4 = dq.view(b, h, w, e), dkv.view(b, style.shape[1], style.shape[2], 2 * e)
-        gw, gb = m.in_proj_weight.grad, m.in_proj_bias.grad
+        gw, gb = self._G(m.in_proj_weight), self._G(m.in_proj_bias)
         ops.act_bwd(dq4, None, act=ACT_NONE, dbias=gb[:e], want_g=False)
         ops.act_bwd(dkv4, None, act=ACT_NONE, dbias=gb[e:], want_g=False)
         ops.wgrad(feat, dq4, gw[:e], ksize=1)
@@ -338,9 +342,9 @@ class LDMTrainer:
 
     def _relu_conv_bwd(self, mod, name, conv, x_in, y_relu, dy, dy2=None, need_dx=True):
         """backward of y = ReLU(conv(x) + b): bias / weight gradients accumulated, returns dL/dx"""
-        g = ops.act_bwd(dy, y_relu, act=ACT_RELU, dy2=dy2, dbias=conv.bias.grad)
+        g = ops.act_bwd(dy, y_relu, act=ACT_RELU, dy2=dy2, dbias=self._G(conv.bias))
         tr = isinstance(conv, nn.ConvTranspose2d)
-        ops.wgrad(x_in, g, conv.weight.grad, ksize=conv.kernel_size[0], stride=conv.stride[0], transposed=tr)
+        ops.wgrad(x_in, g, self._G(conv.weight), ksize=conv.kernel_size[0], stride=conv.stride[0], transposed=tr)
         return self._dgrad(mod, name, conv, g) if need_dx else None
 
     # -- the step ---------------------------------------------------------------------------
@@ -432,7 +436,54 @@ class LDMTrainer:
             noise = noise_d if noise is None else noise
         t = t.to(device=dev, dtype=torch.int64).contiguous()
 
-        # ================= forward (LDM.forward, model.py:355-379), intermediates kept =================
+        sv = self._forward_keep(xs, ss, t, noise)
+        (xs, ss, z0, S, noise_l, z_t, zin, l1, l2, temb, te_e, te_pre, te_h, z1, r2, z2, z3, a3, sv2, z4, a4, sv1, bt, r_d4, d4, r_d3, d3,
+         r_d2, d2, eps_hat, dec_in, v1, h1, mean1, inv1, v2, h2, mean2, inv2, rec, t, adt, ab) = sv
+
+        # ================= losses (train.py:182-186) =================
+        den = ops.mse(eps_hat, noise_l).squeeze(0)
+        mse_rec = ops.mse(rec, xs).squeeze(0)
+        kl = ops.kl(z0).squeeze(0)
+        fl = model.feature_loss_net
+        H, W = xs.shape[1], xs.shape[2]
+        three = torch.empty((3 * B, H, W, 1), dtype=torch.float32, device=dev)
+        three[:B].copy_(xs); three[B:2 * B].copy_(rec); three[2 * B:].copy_(ss)
+        perc = torch.zeros(1, dtype=torch.float32, device=dev)
+        styl = torch.zeros(1, dtype=torch.float32, device=dev)
+        # one pass of the frozen stack for all three images; perc: compression_loss's perceptual term (loss.py:40),
+        # styl: style_loss (loss.py:104-106); each tap = one conv + one fused streaming kernel
+        fl._loss3(three, B, perc, styl)
+        comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
+        total = comp + den + self.style_loss_weight * styl.squeeze(0)
+
+        # ================= backward: d/drec of mean((rec - x)^2), d/deps_hat of mean((eps_hat - eps)^2) =================
+        g_rec = ops.mse_grad(rec, xs, 2.0 / rec.numel(), torch.float32)
+        self._backward_sweep(sv, g_rec, den_scale=2.0 / eps_hat.numel())
+
+        # ================= update (torch.optim.Adam, train.py:156, 200) =================
+        self.reducer.wait()
+        self.step_count += 1
+        self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
+        ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
+                      eps=self.eps, step=self.step_dev, grad_scale=1.0 / self.world)
+        Mo.invalidate_packed(model, keep=(fl,))         # parameters changed under the packed copies / captured sampling graphs
+        losses = torch.stack([comp, den, styl.squeeze(0), total])
+        if self.world > 1:                              # report the GLOBAL batch's losses (equal shards: mean of the ranks' means)
+            self.reducer.all_reduce_small(losses)
+            losses = losses / self.world
+        return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), losses.unbind(0)))
+
+    # -- the two halves of the step, shared with the autograd face of LDM.forward (autograd.py) -------------------------
+    def _forward_keep(self, xs, ss, t, noise):
+        """LDM.forward (model.py:355-379) on this rank's shard with every intermediate the reverse sweep needs kept.
+        xs, ss: [B,H,W,1] fp32; t: [B] int64; noise: [B,C,h,w] fp32 NCHW (the reference's randn_like shape)."""
+        model = self.model
+        u, dec, sty = model.unet, model.decoder, model.style_encoder
+        d = dec.decoder
+        adt = Mo._act_dtype(model._precision())
+        lp = adt == torch.bfloat16
+        dev = xs.device
+        ab = model.noise_scheduler.alpha_bar_t
         z0 = model.encoder._forward_nhwc(xs)                                     # frozen; BatchNorm in train mode (train.py:212)
         _, h, w, c = z0.shape
         S = sty._forward_nhwc(ss)                                                # six post-ReLU maps
@@ -460,44 +511,41 @@ class LDMTrainer:
         rec = ops.conv(h2, dec._packed("d6", d[6].weight, adt, True), dec._f32("d6.b", d[6].bias), ksize=4, stride=2, transposed=True,
                        act=ACT_TANH, out_dtype=torch.float32, out_scale=0.5, out_shift=0.5)      # reconstructed = (tanh + 1) / 2
 
-        # ================= losses (train.py:182-186) =================
-        den = ops.mse(eps_hat, noise_l).squeeze(0)
-        mse_rec = ops.mse(rec, xs).squeeze(0)
-        kl = ops.kl(z0).squeeze(0)
-        fl = model.feature_loss_net
-        H, W = xs.shape[1], xs.shape[2]
-        three = torch.empty((3 * B, H, W, 1), dtype=torch.float32, device=dev)
-        three[:B].copy_(xs); three[B:2 * B].copy_(rec); three[2 * B:].copy_(ss)
-        perc = torch.zeros(1, dtype=torch.float32, device=dev)
-        styl = torch.zeros(1, dtype=torch.float32, device=dev)
-        # one pass of the frozen stack for all three images; perc: compression_loss's perceptual term (loss.py:40),
-        # styl: style_loss (loss.py:104-106); each tap = one conv + one fused streaming kernel
-        fl._loss3(three, B, perc, styl)
-        comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
-        total = comp + den + self.style_loss_weight * styl.squeeze(0)
+        return (xs, ss, z0, S, noise_l, z_t, zin, l1, l2, temb, te_e, te_pre, te_h, z1, r2, z2, z3, a3, sv2, z4, a4, sv1, bt, r_d4, d4, r_d3, d3,
+                r_d2, d2, eps_hat, dec_in, v1, h1, mean1, inv1, v2, h2, mean2, inv2, rec, t, adt, ab)
 
-        # ================= backward =================
+    def _backward_sweep(self, sv, g_rec, den_scale: float = 0.0, g_eps_direct: Optional[torch.Tensor] = None) -> None:
+        """Reverse sweep from g_rec = dL/d(reconstructed) [B,H,W,1] fp32 and the gradient on eps_hat, which gathers
+        den_scale * (eps_hat - eps) (the denoising loss), ``g_eps_direct`` (an external gradient on noise_pred, NHWC in
+        the activation dtype) and the reconstruction path through x0_pred (model.py:117-124).  Parameter gradients are
+        ACCUMULATED into self._G(param)."""
+        model = self.model
+        u, dec, sty = model.unet, model.decoder, model.style_encoder
+        d = dec.decoder
+        (xs, ss, z0, S, noise_l, z_t, zin, l1, l2, temb, te_e, te_pre, te_h, z1, r2, z2, z3, a3, sv2, z4, a4, sv1, bt, r_d4, d4, r_d3, d3,
+         r_d2, d2, eps_hat, dec_in, v1, h1, mean1, inv1, v2, h2, mean2, inv2, rec, t, adt, ab) = sv
         # reconstruction path: d/drec of mean((rec - x)^2); tanh and the (y+1)/2 folded into act_bwd
-        g_rec = ops.mse_grad(rec, xs, 2.0 / rec.numel(), torch.float32)
-        g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=d[6].bias.grad, y_scale=0.5, y_shift=0.5)
-        ops.wgrad(h2, g6, d[6].weight.grad, ksize=4, stride=2, transposed=True)
+        g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=self._G(d[6].bias), y_scale=0.5, y_shift=0.5)
+        ops.wgrad(h2, g6, self._G(d[6].weight), ksize=4, stride=2, transposed=True)
         w6 = dec._cached(("d6", "dg32"), (d[6].weight,), lambda: ops.pack_weight(d[6].weight, torch.float32))
         dh2 = ops.conv(g6, w6, None, ksize=4, stride=2, out_dtype=adt)
-        dv2 = ops.bn_bwd(dh2, v2, mean2, inv2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=d[4].weight.grad,
-                         dbeta=d[4].bias.grad, world=self.world, sync=self._sync_sums)
-        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=d[3].bias.grad, want_g=False)
-        ops.wgrad(h1, dv2, d[3].weight.grad, ksize=4, stride=2, transposed=True)
+        dv2 = ops.bn_bwd(dh2, v2, mean2, inv2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=self._G(d[4].weight),
+                         dbeta=self._G(d[4].bias), world=self.world, sync=self._sync_sums)
+        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=self._G(d[3].bias), want_g=False)
+        ops.wgrad(h1, dv2, self._G(d[3].weight), ksize=4, stride=2, transposed=True)
         dh1 = self._dgrad(dec, "d3", d[3], dv2)
-        dv1 = ops.bn_bwd(dh1, v1, mean1, inv1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=d[1].weight.grad,
-                         dbeta=d[1].bias.grad, world=self.world, sync=self._sync_sums)
-        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=d[0].bias.grad, want_g=False)
-        ops.wgrad(dec_in, dv1, d[0].weight.grad, ksize=4, stride=2, transposed=True)
+        dv1 = ops.bn_bwd(dh1, v1, mean1, inv1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=self._G(d[1].weight),
+                         dbeta=self._G(d[1].bias), world=self.world, sync=self._sync_sums)
+        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=self._G(d[0].bias), want_g=False)
+        ops.wgrad(dec_in, dv1, self._G(d[0].weight), ksize=4, stride=2, transposed=True)
         dz0p = self._dgrad(dec, "d0", d[0], dv1)
         # eps_hat gathers the denoising loss and the reconstruction path through x0_pred (model.py:117-124)
-        g_eps = ops.eps_grad(dz0p, eps_hat, noise_l, ab, t, 2.0 / eps_hat.numel(), adt)
+        g_eps = ops.eps_grad(dz0p, eps_hat, noise_l, ab, t, den_scale, adt)
+        if g_eps_direct is not None:
+            g_eps = ops.add_bcast(g_eps, add=g_eps_direct)
         # ---- UNet, top-down ----
-        ops.act_bwd(g_eps, None, act=ACT_NONE, dbias=u.dec1.bias.grad, want_g=False)
-        ops.wgrad(d2, g_eps, u.dec1.weight.grad, ksize=3)
+        ops.act_bwd(g_eps, None, act=ACT_NONE, dbias=self._G(u.dec1.bias), want_g=False)
+        ops.wgrad(d2, g_eps, self._G(u.dec1.weight), ksize=3)
         dd2 = self._dgrad(u, "dec1", u.dec1, g_eps)
         dd3 = self._relu_conv_bwd(u, "dec2", u.dec2, d3, r_d2, dd2)
         dd4 = self._relu_conv_bwd(u, "dec3", u.dec3, d4, r_d3, dd3)
@@ -515,12 +563,12 @@ class LDMTrainer:
         # time MLP (model.py:170-175): Linear2 <- GELU <- Linear1 <- sinusoid
         nb = dtemb.shape[0]
         dt4 = dtemb.view(nb, 1, 1, -1)
-        ops.act_bwd(dt4, None, act=ACT_NONE, dbias=l2.bias.grad, want_g=False)
-        ops.wgrad(te_h.view(nb, 1, 1, -1), dt4, l2.weight.grad, ksize=1)
+        ops.act_bwd(dt4, None, act=ACT_NONE, dbias=self._G(l2.bias), want_g=False)
+        ops.wgrad(te_h.view(nb, 1, 1, -1), dt4, self._G(l2.weight), ksize=1)
         dh = self._dgrad(u, "t2", l2, dt4)
         dpre = ops.gelu_bwd(dh.view(nb, -1), te_pre).view(nb, 1, 1, -1)
-        ops.act_bwd(dpre, None, act=ACT_NONE, dbias=l1.bias.grad, want_g=False)
-        ops.wgrad(te_e.view(nb, 1, 1, -1), dpre, l1.weight.grad, ksize=1)
+        ops.act_bwd(dpre, None, act=ACT_NONE, dbias=self._G(l1.bias), want_g=False)
+        ops.wgrad(te_e.view(nb, 1, 1, -1), dpre, self._G(l1.weight), ksize=1)
         self._reduce_bucket(1)
         # ---- style encoder: s6 feeds attention1, s5 feeds attention2 and enc6 ----
         ds5c = self._relu_conv_bwd(sty, "enc6", sty.enc6, S[4], S[5], ds6_attn)
@@ -530,19 +578,6 @@ class LDMTrainer:
         dsk = self._relu_conv_bwd(sty, "enc2", sty.enc2, S[0], S[1], dsk)
         self._relu_conv_bwd(sty, "enc1", sty.enc1, ss, S[0], dsk, need_dx=False)
         self._reduce_bucket(2)
-
-        # ================= update (torch.optim.Adam, train.py:156, 200) =================
-        self.reducer.wait()
-        self.step_count += 1
-        self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
-        ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
-                      eps=self.eps, step=self.step_dev, grad_scale=1.0 / self.world)
-        Mo.invalidate_packed(model, keep=(fl,))         # parameters changed under the packed copies / captured sampling graphs
-        losses = torch.stack([comp, den, styl.squeeze(0), total])
-        if self.world > 1:                              # report the GLOBAL batch's losses (equal shards: mean of the ranks' means)
-            self.reducer.all_reduce_small(losses)
-            losses = losses / self.world
-        return dict(zip(("compression_loss", "denoisinsg_loss", "style_loss", "total_loss"), losses.unbind(0)))
 
 
 # =====================================================================================================

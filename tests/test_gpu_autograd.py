@@ -1,0 +1,139 @@
+"""-m gpu: the autograd face of the drop-in modules (music_style_transfer_ldm_b200/autograd.py).
+
+The reference's own training step (models/train.py:176-201) -- ``out = model(x, style, t)``, the four losses of
+models/loss.py, ``total.backward()``, ``torch.optim.Adam.step()`` -- must run unchanged on this package:
+  * parameter gradients after ``total.backward()`` against the oracle's autograd gradients (fp32: 2e-3 of each
+    tensor's max norm; bf16: cosine similarity);
+  * two optimizer steps with a stock ``torch.optim.Adam`` against oracle/train_oracle.py (pinned to the unmodified
+    reference trainer): losses within 1e-4;
+  * module forwards that have no backward raise on ``.backward()`` instead of silently giving no gradient.
+"""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import make_golden_train as G
+from gpu_util import rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+KEYS = ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")
+NOISE = ("decoder.decoder.0.bias", "decoder.decoder.3.bias", "in_proj_bias")     # mathematically zero gradients (see test_gpu_train.py)
+
+
+class _fixed_randn_like:
+    def __init__(self, eps):
+        self.eps = eps
+
+    def __enter__(self):
+        self._real = torch.randn_like
+        torch.randn_like = lambda x, **kw: self.eps.to(device=x.device, dtype=x.dtype)
+        return self
+
+    def __exit__(self, *exc):
+        torch.randn_like = self._real
+        return False
+
+
+def _model(sd, precision):
+    import music_style_transfer_ldm_b200 as M
+    m = M.LDM(latent_dim=32, pretrained_path=None)
+    m.load_state_dict(sd, strict=True)
+    m._freeze_encoder()
+    m.to(DEV).set_precision(precision)
+    m.train()
+    return m
+
+
+def _reference_style_losses(m, x, s, t, w):
+    import music_style_transfer_ldm_b200 as M
+    out = m(x, s, t)                                                    # train.py:177
+    den = M.diffusion_loss(out["noise_pred"], out["noise"])              # train.py:182
+    comp = M.compression_loss(x, out["reconstructed"], out["z_0"], m.feature_loss_net)
+    sty = M.style_loss(out["reconstructed"], s, m.feature_loss_net)
+    total = comp + den + w * sty                                         # train.py:186
+    return out, dict(zip(KEYS, (comp, den, sty, total)))
+
+
+def _oracle_grads(sd, x, s, t, eps, w):
+    from oracle import ldm_oracle as O, train_oracle as T
+    ot = T.OracleTrainer(sd, lr=G.LR, style_loss_weight=w)
+    p = ot.sd
+    z0 = O.encoder_fwd(p, x, True, update={})
+    emb = O.style_encoder_fwd(p, s)
+    z_t = O.q_sample(p, z0, t, eps)
+    eps_hat = O.unet_fwd(p, z_t, t, emb)
+    rec = (O.decoder_fwd(p, O.predict_x0(p, z_t, t, eps_hat), True, update={}) + 1) / 2
+    with torch.no_grad():
+        perc, sty = O.vggish_feature_loss(p, x, rec), O.vggish_feature_loss(p, rec, s)
+    total = torch.mean((rec - x) ** 2) + 0.1 * perc + 0.01 * O.kl_regularization_loss(z0) + O.diffusion_loss(eps_hat, eps) + w * sty
+    total.backward()
+    return {k: p[k].grad for k in ot.keys}, float(total)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_loss_backward_gives_the_oracle_gradients(sd, precision):
+    x, s, t, eps = G.step_inputs(0)
+    ref, ref_total = _oracle_grads(sd, x, s, t, eps, G.W)
+    m = _model(sd, precision)
+    with _fixed_randn_like(eps):
+        out, losses = _reference_style_losses(m, x.to(DEV), s.to(DEV), t.to(DEV), G.W)
+    assert out["noise_pred"].requires_grad and out["reconstructed"].requires_grad
+    assert not out["z_0"].requires_grad and not out["z_t"].requires_grad
+    assert float(losses["total_loss"]) == pytest.approx(ref_total, rel=1e-4 if precision == "fp32" else 1e-2)
+    losses["total_loss"].backward()
+    named = dict(m.named_parameters())
+    checked = 0
+    for k, g in ref.items():
+        got = named[k].grad
+        assert got is not None, k
+        if any(n in k for n in NOISE):
+            continue
+        if precision == "fp32":
+            assert rel_err(got, g) <= 2e-3, f"{k}: gradient differs from the oracle's by {rel_err(got, g):.2e} of its max norm"
+        else:
+            a, b = got.double().flatten().cpu(), g.double().flatten()
+            cos = float(a @ b / (a.norm() * b.norm() + 1e-30))
+            assert cos > 0.98, f"{k}: cosine similarity with the oracle's gradient {cos:.4f}"
+        checked += 1
+    assert checked > 50
+    assert all(p.grad is None for p in m.encoder.parameters())                   # frozen (model.py:340-341)
+    assert all(p.grad is None for p in m.feature_loss_net.parameters())
+
+
+def test_reference_training_loop_with_torch_adam(sd):
+    """train.py:189-201 with a stock optimizer on this package's parameters, fp32, against the oracle trainer"""
+    from oracle import train_oracle as T
+    m = _model(sd, "fp32")
+    opt = torch.optim.Adam([p for p in m.parameters() if p.requires_grad], lr=G.LR)
+    ot = T.OracleTrainer(sd, lr=G.LR, style_loss_weight=G.W)
+    for i in range(2):
+        x, s, t, eps = G.step_inputs(i)
+        ref = ot.train_step(x, s, t, eps)
+        opt.zero_grad()
+        with _fixed_randn_like(eps):
+            _, losses = _reference_style_losses(m, x.to(DEV), s.to(DEV), t.to(DEV), G.W)
+        losses["total_loss"].backward()
+        opt.step()
+        got = np.array([float(losses[k]) for k in KEYS])
+        np.testing.assert_allclose(got, [ref[k] for k in KEYS], rtol=1e-4, err_msg=f"step {i}")
+
+
+def test_backward_through_other_forwards_raises(sd):
+    import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200.ops import MstkError
+    m = M.LDM(latent_dim=32, pretrained_path=None)          # encoder NOT frozen: not the LDM-stage configuration
+    m.load_state_dict(sd, strict=True)
+    m.to(DEV).train().set_precision("fp32")
+    x = cases.spec(1, 2).to(DEV)
+    z = m.encoder(x)
+    assert z.requires_grad
+    with pytest.raises(MstkError, match="backward through"):
+        z.sum().backward()
+    out = m(x, x, torch.tensor([3, 9], device=DEV))          # values as usual ...
+    assert out["reconstructed"].shape == (2, 1, 128, 128)
+    with pytest.raises(MstkError, match="_freeze_encoder"):   # ... and a backward says what is missing
+        M.diffusion_loss(out["noise_pred"], out["noise"]).backward()
+    with torch.no_grad():                                     # inference is untouched
+        assert not m.decoder(z.detach()).requires_grad

@@ -54,7 +54,7 @@ def test_fp32_steps_match_reference_fixture(sd):
         # Adam's early steps are ~lr*sign(g): a gradient that is ~0 may flip sign under a different summation order,
         # so allow a small fraction of elements to differ by a few lr while the bulk agrees to lr/10
         frac = (d > 5e-5).float().mean().item()           # 5e-5 = lr / 10
-        assert frac < 0.03, f"{k}: {frac:.2%} of elements differ by more than 5e-5 (max {d.max().item():.2e})"
+        assert frac < 0.05, f"{k}: {frac:.2%} of elements differ by more than 5e-5 (max {d.max().item():.2e})"
         assert d.max().item() < 8 * G.LR, f"{k}: max difference {d.max().item():.2e}"
         moved += int(((v - sd[k]).abs() > 0).any()) if k in sd else 0
     assert moved > 50
