@@ -33,7 +33,28 @@ def _trainer(sd, precision, lr, w):
     return m, tr
 
 
-def test_fp32_steps_match_reference_fixture(sd):
+@pytest.fixture
+def cuda_core_fp32():
+    """fp32 contractions on the exact CUDA-core kernels (ops.FP32_TC = False) for the element-wise parameter comparison:
+    Adam normalises every element's step, so the ~1e-5 operand rounding of the split-bf16 tensor-core route (and the ReLU
+    masks it flips) moves many near-zero-gradient elements by a visible fraction of lr although the losses agree"""
+    from music_style_transfer_ldm_b200 import ops
+    old, ops.FP32_TC = ops.FP32_TC, False
+    yield
+    ops.FP32_TC = old
+
+
+def test_fp32_tensor_core_steps_match_reference_losses(sd):
+    """the default fp32 mode (split-bf16 operands on tcgen05): losses of 3 consecutive steps vs the reference fixture"""
+    g = cases.load("train_steps")
+    m, tr = _trainer(sd, "fp32", G.LR, G.W)
+    for i in range(G.STEPS):
+        x, s, t, eps = G.step_inputs(i)
+        out = tr.train_step_device(x.to(DEV), s.to(DEV), t=t.to(DEV), noise=eps.to(DEV))
+        np.testing.assert_allclose([float(out[k]) for k in KEYS], g["losses"][i], rtol=1e-4, err_msg=f"step {i} losses vs reference LDMTrainer")
+
+
+def test_fp32_steps_match_reference_fixture(sd, cuda_core_fp32):
     from oracle import train_oracle as T
     g = cases.load("train_steps")
     m, tr = _trainer(sd, "fp32", G.LR, G.W)
@@ -54,7 +75,7 @@ def test_fp32_steps_match_reference_fixture(sd):
         # Adam's early steps are ~lr*sign(g): a gradient that is ~0 may flip sign under a different summation order,
         # so allow a small fraction of elements to differ by a few lr while the bulk agrees to lr/10
         frac = (d > 5e-5).float().mean().item()           # 5e-5 = lr / 10
-        assert frac < 0.05, f"{k}: {frac:.2%} of elements differ by more than 5e-5 (max {d.max().item():.2e})"
+        assert frac < 0.03, f"{k}: {frac:.2%} of elements differ by more than 5e-5 (max {d.max().item():.2e})"
         assert d.max().item() < 8 * G.LR, f"{k}: max difference {d.max().item():.2e}"
         moved += int(((v - sd[k]).abs() > 0).any()) if k in sd else 0
     assert moved > 50
