@@ -255,6 +255,14 @@ int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, in
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------
+ * Packed uint8 spectrogram cache -> batch (models/dataset.py:28-53, 206-260: PNG -> crop (0,0,128,128) -> grayscale
+ * -> ToTensor): pool [n, h, w] uint8 images as stored (128 x 130 for the reference's 3 s chunks), index [b] int64
+ * image numbers; out [b, 1, crop_h, crop_w] fp32 = top-left crop / 255.  Indices are not range-checked.
+ * ---------------------------------------------------------------------------- */
+int mstk_u8_gather_crop(const uint8_t* pool, const int64_t* index, float* out, int b, int h, int w, int crop_h, int crop_w,
+                        void* stream);
+
+/* ------------------------------------------------------------------------------
  * Mel front end (data/audio_processor.py:44-73 -> librosa.feature.melspectrogram +
  * power_to_db(ref=np.max) + the uint8 image quantisation):
  * wave [b, len] fp32 -> frames (n_fft 2048, hop 512, periodic Hann, centre zero pad)

@@ -6,6 +6,8 @@ Public surface mirrors the reference's modules:
     loss   (diffusion_loss, kl_regularization_loss, compression_loss, perceptual_loss,
             VGGishFeatureLoss, style_loss)
     config (config dict)
+    train  (LDMTrainer, AutoencoderTrainer, train_autoencoder), audio_processor (AudioPreprocessor),
+    dataset (SpectrogramPairDataset, SpectrogramDataset, PackedSpectrograms), autograd (the backward face)
 Kernels live in libmstk.so (csrc/, C ABI in include/mstk.h) and are reached through ops.
 """
 from . import _lib, ops                      # noqa: F401

@@ -101,6 +101,7 @@ SIGNATURES = {
     "mstk_pack_convt_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_nchw_to_nhwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_nhwc_to_nchw": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_u8_gather_crop": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_cast": (c_int, [c_void_p, c_int, c_void_p, c_int, c_size_t, c_void_p]),
     "mstk_bn_apply": (c_int, [C.POINTER(BnArgs), c_void_p]),
     "mstk_time_embed": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -80,6 +80,19 @@ __global__ void nhwc_to_nchw_kernel(const void* __restrict__ src, float* dst, in
     }
 }
 
+// Packed uint8 spectrogram cache -> training batch: out[i] = crop(pool[index[i]], crop_h x crop_w, top-left) / 255
+// (models/dataset.py:51-53: img.crop((0, 0, 128, 128)), Grayscale, ToTensor).  One thread per output pixel; a warp reads
+// 32 consecutive bytes of one image row and writes 128 consecutive bytes.
+__global__ void u8_gather_crop_kernel(const uint8_t* __restrict__ pool, const long long* __restrict__ index, float* __restrict__ out,
+                                      const int h, const int w, const int crop_h, const int crop_w, const size_t total) {
+    const size_t per = (size_t)crop_h * crop_w;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t s = i / per, r = i - s * per;
+        const int y = (int)(r / crop_w), x = (int)(r - (size_t)y * crop_w);
+        out[i] = (float)pool[((size_t)index[s] * h + y) * w + x] * (1.0f / 255.0f);
+    }
+}
+
 __global__ void cast_kernel(const void* __restrict__ src, int sd, void* dst, int dd, size_t count) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x)
         store_from_f(dst, dd, i, load_as_f(src, sd, i));
@@ -571,6 +584,15 @@ int mstk_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w, i
     dim3 grid((hw + 31) / 32, (c + 31) / 32, n);
     nhwc_to_nchw_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(src, dst, c, hw, src_dtype);
     MSTK_CHECK_LAUNCH("nhwc_to_nchw");
+    return MSTK_OK;
+}
+int mstk_u8_gather_crop(const uint8_t* pool, const int64_t* index, float* out, int b, int h, int w, int crop_h, int crop_w, void* stream) {
+    MSTK_REQUIRE(pool && index && out && b > 0 && h > 0 && w > 0, "u8_gather_crop: bad args");
+    MSTK_REQUIRE(crop_h > 0 && crop_w > 0 && crop_h <= h && crop_w <= w, "u8_gather_crop: crop %dx%d outside the stored %dx%d image", crop_h,
+                 crop_w, h, w);
+    const size_t total = (size_t)b * crop_h * crop_w;
+    u8_gather_crop_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(pool, (const long long*)index, out, h, w, crop_h, crop_w, total);
+    MSTK_CHECK_LAUNCH("u8_gather_crop");
     return MSTK_OK;
 }
 int mstk_cast(const void* src, int sd, void* dst, int dd, size_t count, void* stream) {

@@ -240,6 +240,19 @@ def nhwc_to_nchw(x: torch.Tensor) -> torch.Tensor:
     return dst
 
 
+def u8_gather_crop(pool: torch.Tensor, index: torch.Tensor, crop_h: int, crop_w: int) -> torch.Tensor:
+    """pool [n,h,w] uint8 (CUDA), index [b] int64 (CUDA) -> [b,1,crop_h,crop_w] fp32 in [0,1] (top-left crop / 255)"""
+    lib = _lib.load()
+    _dev(pool, "u8_gather_crop.pool"); _dev(index, "u8_gather_crop.index")
+    if pool.dtype != torch.uint8 or pool.dim() != 3 or index.dtype != torch.int64:
+        raise MstkError("u8_gather_crop: pool must be uint8 [n,h,w] and index int64 [b]")
+    b = index.numel()
+    out = torch.empty((b, 1, crop_h, crop_w), dtype=torch.float32, device=pool.device)
+    check(lib.mstk_u8_gather_crop(_p(pool), _p(index), _p(out), b, pool.shape[1], pool.shape[2], crop_h, crop_w, _stream()), "mstk_u8_gather_crop")
+    _count(1)
+    return out
+
+
 def cast(x: torch.Tensor, dtype: torch.dtype, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     lib = _lib.load()
     x = _dev(x, "cast.x")
