@@ -89,7 +89,7 @@ __global__ void u8_gather_crop_kernel(const uint8_t* __restrict__ pool, const lo
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         const size_t s = i / per, r = i - s * per;
         const int y = (int)(r / crop_w), x = (int)(r - (size_t)y * crop_w);
-        out[i] = (float)pool[((size_t)index[s] * h + y) * w + x] * (1.0f / 255.0f);
+        out[i] = (float)pool[((size_t)index[s] * h + y) * w + x] / 255.0f;      // IEEE division, as ToTensor's .div(255)
     }
 }
 
