@@ -333,6 +333,7 @@ def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True
     extra = {}
     if rank == 0 and rooflines:
         extra = train_rooflines(model, per, dev)
+    tr.close()
     del tr, model
     torch.cuda.empty_cache()
     return {"metric": "train_samples_per_s", "value": gb * steps / (ms * 1e-3), "unit": "samples/s",
@@ -663,6 +664,7 @@ def ddp_parity(args, rank, world, dev):
             out = tr.train_step_device(x, s, t=t, noise=eps)
             rows.append([float(out[k]) for k in keys])
         chk = tr.arena.p.double().sum().reshape(1)
+        tr.close()
         del tr, model
         torch.cuda.empty_cache()
         return np.asarray(rows), chk

@@ -206,6 +206,15 @@ class LDMTrainer:
                 if b.dtype.is_floating_point:
                     dist.broadcast(b, src=0, group=self.group)
 
+    def close(self) -> None:
+        """Drop the captured step.  A CUDA graph that holds NCCL kernels keeps the communicator busy:
+        ``torch.distributed.destroy_process_group()`` blocks until every such graph is gone, so data-parallel callers
+        close their trainers first."""
+        self._graph = None
+        self._eager_steps = 0
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+
     @property
     def lr(self) -> float:
         return self._lr

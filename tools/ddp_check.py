@@ -45,6 +45,7 @@ for i in range(steps):
 chk = tr.arena.p.double().sum().reshape(1)
 lo, hi = chk.clone(), chk.clone()
 dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+tr.close()          # the captured step holds NCCL kernels: it must go before the process group does
 ok = worst <= 1e-2 and float(hi - lo) == 0.0
 if rank == 0:
     print(f"ddp_check world={world} steps={steps}: worst loss deviation vs single-process oracle {worst:.3e}; "
