@@ -636,16 +636,23 @@ class LDM(_Kernelised):
         return tt
 
     def _loop_body(self, x: torch.Tensor, s5: torch.Tensor, s6: torch.Tensor, times: List[int], eta: float, logs,
-                   tt: torch.Tensor):
-        """N-1 UNet evaluations, each ending in the fused DDIM update (in place on ``x``)."""
+                   tt: torch.Tensor, kv=None):
+        """N-1 UNet evaluations, each ending in the fused DDIM update (in place on ``x``).  ``kv``: the projected
+        style maps when the caller has them already (computed on a concurrent branch)."""
         adt = _act_dtype(self._precision())
         b = x.shape[0]
         nsteps = len(times) - 1
         sab, s1m = self._schedule_host()
-        ops.RECORD_NOTE = "hoisted"
-        kv2, kv1 = self.unet._project_style(s5, s6)
-        ops.RECORD_NOTE = ""
-        temb = self.unet._time_embedding(tt).view(nsteps, b, -1)
+        if kv is None:
+            ops.RECORD_NOTE = "hoisted"
+            kv2, kv1 = self.unet._project_style(s5, s6)
+            ops.RECORD_NOTE = ""
+        else:
+            kv2, kv1 = kv
+        # every sample of a step shares its timestep: the time MLP runs on the N-1 distinct values, one broadcast
+        # kernel lays the rows out per (step, sample) for the conv epilogue's add_nc
+        tu = self.unet._time_embedding(tt.view(nsteps, b)[:, 0].contiguous())
+        temb = ops.add_bcast(torch.zeros((nsteps, b, tu.shape[1]), dtype=torch.float32, device=x.device), add_nc=tu)
         x_lp = ops.cast(x, adt) if adt != torch.float32 else None
         self._loop_steps(x, x_lp, temb, kv2, kv1, times, eta, logs)
         return x
@@ -716,6 +723,13 @@ class LDM(_Kernelised):
                     for k in [k for k in cache if isinstance(k, tuple) and len(k) == 3 and k[1] == "fold"]:
                         del cache[k]
         return tuple(o.clone() for o in ent["out"])
+
+    def _side_streams(self, device):
+        ss = self.__dict__.get("_side")
+        if ss is None or ss[0].device != torch.device(device):
+            ss = (torch.cuda.Stream(device=device), torch.cuda.Stream(device=device))
+            self.__dict__["_side"] = ss
+        return ss
 
     def _whole_call_graph_ok(self) -> bool:
         return self.use_cuda_graphs and not torch.cuda.is_current_stream_capturing() and not self.collect_sampling_logs
@@ -830,12 +844,33 @@ class LDM(_Kernelised):
         noise = torch.randn_like(torch.empty((b, c, hh, ww), dtype=torch.float32, device=dev))
 
         def body(cs_, ss_, noise_, n=num_timesteps):
+            times = self._times(n - 1, n)
+            # Inside the whole-call graph the call forks: the style side (style encoder + composed projections) runs
+            # beside the VAE encoder, and the decode of z_t (which the loop does not need) beside the N-1 latency-bound
+            # steps.  Not with train-mode BatchNorm: the two decoder passes update the running buffers in call order.
+            fork = torch.cuda.is_current_stream_capturing() and not self._bn_training()
+            main = torch.cuda.current_stream()
+            if fork:
+                s_a, s_b = self._side_streams(dev)
+                s_a.wait_stream(main)
+                with torch.cuda.stream(s_a), ops.workspace_slot(1):
+                    styles = self.style_encoder._forward_nhwc(ss_)
+                    kv = self.unet._project_style(styles[4], styles[5])
             z0 = self.encoder._forward_nhwc(cs_)
             t = torch.full((b,), n - 1, dtype=torch.int64, device=dev)
             z_t, _ = ops.q_sample(z0, ops.nchw_to_nhwc(noise_, torch.float32), self.noise_scheduler.alpha_bar_t, t)
-            styles = self.style_encoder._forward_nhwc(ss_)
-            x, _ = self._sample(z_t, styles[4], styles[5], self._times(n - 1, n), eta)
-            return self.decoder._forward_nhwc(x, unit_range=True), self.decoder._forward_nhwc(z_t)
+            if not fork:
+                styles = self.style_encoder._forward_nhwc(ss_)
+                x, _ = self._sample(z_t, styles[4], styles[5], times, eta)
+                return self.decoder._forward_nhwc(x, unit_range=True), self.decoder._forward_nhwc(z_t)
+            s_b.wait_stream(main)
+            with torch.cuda.stream(s_b), ops.workspace_slot(2):
+                ztd_ = self.decoder._forward_nhwc(z_t)
+            main.wait_stream(s_a)
+            x = self._loop_body(z_t.clone(), styles[4], styles[5], times, eta, None, self._step_times(times, b, dev), kv=kv)
+            dec_ = self.decoder._forward_nhwc(x, unit_range=True)
+            main.wait_stream(s_b)
+            return dec_, ztd_
 
         if self._whole_call_graph_ok() and num_timesteps >= 2:
             self._step_times(self._times(num_timesteps - 1, num_timesteps), b, dev)

@@ -68,10 +68,32 @@ def tc_eligible(dtype, cin: int, cout: int, stride: int, transposed: bool, h: in
     return True
 
 
+_WS_SLOT = 0
+
+
+class workspace_slot:
+    """Convolutions enqueued inside ``with workspace_slot(k)`` use their own split-K scratch: branches of one call that
+    run CONCURRENTLY on different streams (the style encoder beside the VAE encoder, the z_t decode beside the sampling
+    loop) must not share the scratch that ordered launches of one stream share."""
+
+    def __init__(self, slot: int):
+        self.slot = int(slot)
+
+    def __enter__(self):
+        global _WS_SLOT
+        self.old, _WS_SLOT = _WS_SLOT, self.slot
+        return self
+
+    def __exit__(self, *exc):
+        global _WS_SLOT
+        _WS_SLOT = self.old
+        return False
+
+
 def workspace(device) -> torch.Tensor:
-    """Zero-initialised split-K scratch shared by all conv calls of a device (kernels
+    """Zero-initialised split-K scratch shared by all conv calls of a device and workspace slot (kernels
     leave it zeroed; launches on one stream are ordered)."""
-    key = torch.device(device).index or 0
+    key = (torch.device(device).index or 0, _WS_SLOT)
     ws = _workspaces.get(key)
     if ws is None:
         ws = torch.zeros(WORKSPACE_BYTES, dtype=torch.uint8, device=device)
