@@ -251,6 +251,12 @@ int mstk_feature_mse3(const void* f0, const void* f1, const void* f2, int dtype,
  * acc: [8*b] doubles, scratch: 1 double; zeroed by the caller once, left zeroed. */
 int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc,
                         double* scratch, float weight, float* out_a, float* out_c, void* stream);
+/* The FIRST tap of the same training-step form without materialising it: img [3b, h, w] fp32 single-channel images
+ * (x; recon; style), wpacked [9][64] / bias [64] fp32 = features.0 (vggish.py:108-118, Conv2d(1, 64, 3, padding=1) + ReLU).
+ * Accumulates the tap's two loss terms into out_a / out_c exactly as mstk_feature_fused3 does and writes ONLY the 2x2
+ * max-pooled map [3b, h/2, w/2, 64] (`pooled_dtype`).  acc / scratch: as mstk_feature_fused3. */
+int mstk_feature_first3(const float* img, const float* wpacked, const float* bias, void* pooled, int pooled_dtype, int b, int h, int w,
+                        double* acc, double* scratch, float weight, float* out_a, float* out_c, void* stream);
 /* 2x2/2 max pool on NHWC (vggish.py:113) */
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream);
 

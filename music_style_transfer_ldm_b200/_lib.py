@@ -121,6 +121,8 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p]),
     "mstk_feature_fused3": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p, c_void_p,
                                     c_void_p]),
+    "mstk_feature_first3": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p,
+                                    c_void_p, c_void_p]),
     "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_pack_conv_weight_dgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),

@@ -100,6 +100,8 @@ int launch_feat_mse3(const void* f0, const void* f1, const void* f2, int dtype, 
                      double* st2, double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st);
 int launch_feat_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc, double* scratch, float weight,
                        float* out_a, float* out_c, cudaStream_t st);
+int launch_feat_first3(const float* img, const float* wgt, const float* bias, void* pooled, int dtype, int b, int h, int w, double* acc,
+                       double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st);
 int launch_maxpool_vec(const void* x, void* y, int n, int h, int w, int c, int dtype, cudaStream_t st);
 // tcgen05 weight gradient (wgrad_tc.cu); `p` = forward plan with p.x = input, p.y = dy
 bool wgrad_tc_supported(const ConvP& p, int x_dtype, int dy_dtype);

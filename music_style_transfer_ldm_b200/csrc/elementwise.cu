@@ -785,6 +785,14 @@ int mstk_feature_fused3(const void* f, void* pooled, int dtype, int b, int h, in
     MSTK_REQUIRE(!pooled || (!(h & 1) && !(w & 1)), "feature_fused3: pooling needs even h, w");
     return launch_feat_fused3(f, pooled, dtype, b, h, w, c, acc, scratch, weight, out_a, out_c, (cudaStream_t)stream);
 }
+int mstk_feature_first3(const float* img, const float* wpacked, const float* bias, void* pooled, int pooled_dtype, int b, int h, int w,
+                        double* acc, double* scratch, float weight, float* out_a, float* out_c, void* stream) {
+    MSTK_REQUIRE(img && wpacked && pooled && acc && scratch && out_a && out_c && b > 0 && b <= 65535, "feature_first3: bad args");
+    MSTK_REQUIRE(pooled_dtype == MSTK_BF16 || pooled_dtype == MSTK_F32, "feature_first3: bad dtype");
+    MSTK_REQUIRE(h > 1 && w > 1 && !(h & 1) && !(w & 1) && (long long)(h / 2) * (w / 2) * 8 < (1ll << 31), "feature_first3: h, w must be even");
+    MSTK_REQUIRE(!(reinterpret_cast<uintptr_t>(pooled) & 15), "feature_first3: 16-byte alignment");
+    return launch_feat_first3(img, wpacked, bias, pooled, pooled_dtype, b, h, w, acc, scratch, weight, out_a, out_c, (cudaStream_t)stream);
+}
 int mstk_maxpool2x2(const void* x, void* y, int n, int h, int w, int c, int dtype, void* stream) {
     MSTK_REQUIRE(x && y && n > 0 && h > 1 && w > 1 && c > 0, "maxpool: bad args");
     {

@@ -203,6 +203,55 @@ static unsigned fl_grid_x(long long nvec, int samples) {
 // The last CTA to finish evaluates them for every sample, adds weight * mean into out_a / out_c and re-zeroes
 // acc and the counter.  Traffic: one read of f (+ a quarter-size write) instead of three reads (+ the write).
 // ---------------------------------------------------------------------------
+// Common end of the one-pass tap kernels: block-reduce the eight per-sample sums (l: fp32 run, d: double), add them to
+// acc[b], and let the last CTA of the grid turn the sums into the two loss terms (see feat_fused3_kernel).
+__device__ __forceinline__ void fused3_finish(float (&l)[8], double (&d)[8], double* red, const int b, const int nb, const int h, const int w,
+                                              const int c, double* acc, double* scratch, const float weight, float* out_a, float* out_c) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        d[k] += l[k];
+        d[k] = block_sum_d(d[k], red);
+    }
+    __shared__ unsigned int s_last;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) atomicAdd(acc + (size_t)b * 8 + k, d[k]);
+        __threadfence();
+        unsigned int* ctr = reinterpret_cast<unsigned int*>(scratch);
+        s_last = (atomicAdd(ctr, 1u) == gridDim.x * gridDim.y - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        const double n = (double)h * w * c;
+        double ta = 0.0, tc = 0.0;
+        for (int s = threadIdx.x; s < nb; s += 256) {
+            double* a = acc + (size_t)s * 8;
+            double v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v[k] = __ldcg(a + k); a[k] = 0.0; }
+            double r3[3];
+#pragma unroll
+            for (int im = 0; im < 3; ++im) {
+                const double mean = v[2 * im] / n;
+                double var = (v[2 * im + 1] - n * mean * mean) / (n - 1.0);
+                if (var < 0) var = 0;
+                r3[im] = 1.0 / ((double)((float)sqrt(var)) + 1e-8);
+            }
+            ta += r3[0] * r3[0] * v[1] - 2.0 * r3[0] * r3[1] * v[6] + r3[1] * r3[1] * v[3];
+            tc += r3[1] * r3[1] * v[3] - 2.0 * r3[1] * r3[2] * v[7] + r3[2] * r3[2] * v[5];
+        }
+        ta = block_sum_d(ta, red);
+        tc = block_sum_d(tc, red);
+        if (threadIdx.x == 0) {
+            const double den = (double)nb * n;
+            atomicAdd(out_a, weight * (float)(ta / den));
+            atomicAdd(out_c, weight * (float)(tc / den));
+            *reinterpret_cast<unsigned int*>(scratch) = 0u;
+        }
+    }
+}
+
 template <int DT, bool POOL>
 __global__ void __launch_bounds__(256) feat_fused3_kernel(const void* __restrict__ f, void* pooled, int nb, int h, int w, int c, double* acc,
                                                          double* scratch, float weight, float* out_a, float* out_c) {
@@ -285,49 +334,113 @@ __global__ void __launch_bounds__(256) feat_fused3_kernel(const void* __restrict
             }
         }
     }
+    fused3_finish(l, d, red, b, nb, h, w, c, acc, scratch, weight, out_a, out_c);
+}
+
+// ---------------------------------------------------------------------------
+// First VGGish tap of the training step WITHOUT materialising it: conv3x3(1 -> 64) + bias + ReLU of the three stacked
+// image batches (x, recon, style) is recomputed on the fly from the single-channel images (9 FMAs per value), the eight
+// per-sample sums of the tap and its 2x2 max-pool come out of the same pass.  The stand-alone form wrote the
+// [3b,128,128,64] map (1.6 GB bf16 at batch 256, 499 us at ~50 % of the HBM peak) and read it back once for the
+// statistics; here only the pooled quarter-size map is written.  The statistics are taken on the fp32 values (the
+// materialised form took them on the bf16-rounded map); the pooled map is identical (rounding is monotonic).
+// Thread = 8 consecutive channels (weights + bias in 80 registers) of one pooled pixel; the 4x4 image patches are
+// shared by the 8 threads of a pixel through L1.
+// ---------------------------------------------------------------------------
+template <int DT>
+__global__ void __launch_bounds__(256) feat_first3_kernel(const float* __restrict__ img, const float* __restrict__ wgt,
+                                                         const float* __restrict__ bias, void* pooled, int nb, int h, int w, double* acc,
+                                                         double* scratch, float weight, float* out_a, float* out_c) {
+    __shared__ double red[32];
+    constexpr int C = 64, CV = 8;                       // 8 channel vectors of 8
+    const int b = blockIdx.y;
+    const int ch = threadIdx.x & (CV - 1);              // constant per thread: the item stride is a multiple of 256
+    float wr[9][8], br[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        d[k] += l[k];
-        d[k] = block_sum_d(d[k], red);
-    }
-    __shared__ unsigned int s_last;
-    if (threadIdx.x == 0) {
+    for (int t = 0; t < 9; ++t)
 #pragma unroll
-        for (int k = 0; k < 8; ++k) atomicAdd(acc + (size_t)b * 8 + k, d[k]);
-        __threadfence();
-        unsigned int* ctr = reinterpret_cast<unsigned int*>(scratch);
-        s_last = (atomicAdd(ctr, 1u) == gridDim.x * gridDim.y - 1) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (s_last) {
-        __threadfence();
-        const double n = (double)h * w * c;
-        double ta = 0.0, tc = 0.0;
-        for (int s = threadIdx.x; s < nb; s += 256) {
-            double* a = acc + (size_t)s * 8;
-            double v[8];
+        for (int j = 0; j < 8; ++j) wr[t][j] = __ldg(wgt + t * C + ch * 8 + j);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) { v[k] = __ldcg(a + k); a[k] = 0.0; }
-            double r3[3];
+    for (int j = 0; j < 8; ++j) br[j] = bias ? __ldg(bias + ch * 8 + j) : 0.f;
+    float l[8];
+    double d[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { l[k] = 0.f; d[k] = 0.0; }
+    const int ho = h / 2, wo = w / 2;
+    const unsigned items = (unsigned)ho * wo * CV;
+    const size_t plane = (size_t)h * w, out_img = (size_t)ho * wo * CV;
+    int run = 0;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < items; i += gridDim.x * 256u) {
+        const unsigned r = i / CV;
+        const int ox = (int)(r % wo), oy = (int)(r / wo);
+        float m[3][8];
+#pragma unroll
+        for (int im = 0; im < 3; ++im)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m[im][j] = 0.f;             // post-ReLU values are >= 0
+#pragma unroll 1
+        for (int p4 = 0; p4 < 4; ++p4) {
+            const int y = 2 * oy + (p4 >> 1), x = 2 * ox + (p4 & 1);
+            float v[3][8];
 #pragma unroll
             for (int im = 0; im < 3; ++im) {
-                const double mean = v[2 * im] / n;
-                double var = (v[2 * im + 1] - n * mean * mean) / (n - 1.0);
-                if (var < 0) var = 0;
-                r3[im] = 1.0 / ((double)((float)sqrt(var)) + 1e-8);
+                const float* pl = img + (size_t)(im * nb + b) * plane;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[im][j] = br[j];
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+                    float px = 0.f;
+                    if (yy >= 0 && yy < h && xx >= 0 && xx < w) px = __ldg(pl + (size_t)yy * w + xx);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[im][j] = fmaf(px, wr[t][j], v[im][j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    v[im][j] = fmaxf(v[im][j], 0.f);
+                    m[im][j] = fmaxf(m[im][j], v[im][j]);
+                }
             }
-            ta += r3[0] * r3[0] * v[1] - 2.0 * r3[0] * r3[1] * v[6] + r3[1] * r3[1] * v[3];
-            tc += r3[1] * r3[1] * v[3] - 2.0 * r3[1] * r3[2] * v[7] + r3[2] * r3[2] * v[5];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float xv = v[0][j], rv = v[1][j], sv = v[2][j];
+                l[0] += xv; l[1] = fmaf(xv, xv, l[1]);
+                l[2] += rv; l[3] = fmaf(rv, rv, l[3]);
+                l[4] += sv; l[5] = fmaf(sv, sv, l[5]);
+                l[6] = fmaf(xv, rv, l[6]); l[7] = fmaf(rv, sv, l[7]);
+            }
         }
-        ta = block_sum_d(ta, red);
-        tc = block_sum_d(tc, red);
-        if (threadIdx.x == 0) {
-            const double den = (double)nb * n;
-            atomicAdd(out_a, weight * (float)(ta / den));
-            atomicAdd(out_c, weight * (float)(tc / den));
-            *reinterpret_cast<unsigned int*>(scratch) = 0u;
+#pragma unroll
+        for (int im = 0; im < 3; ++im) {
+            if (DT == MSTK_BF16) {
+                uint4 o;
+                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(m[im][2 * j], m[im][2 * j + 1]);
+                reinterpret_cast<uint4*>(pooled)[(size_t)(im * nb + b) * out_img + i] = o;
+            } else {
+                float4* o = reinterpret_cast<float4*>(pooled) + ((size_t)(im * nb + b) * out_img + i) * 2;
+                o[0] = make_float4(m[im][0], m[im][1], m[im][2], m[im][3]);
+                o[1] = make_float4(m[im][4], m[im][5], m[im][6], m[im][7]);
+            }
+        }
+        if (++run == 4) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { d[k] += l[k]; l[k] = 0.f; }
+            run = 0;
         }
     }
+    fused3_finish(l, d, red, b, nb, h, w, C, acc, scratch, weight, out_a, out_c);
+}
+
+int launch_feat_first3(const float* img, const float* wgt, const float* bias, void* pooled, int dtype, int b, int h, int w, double* acc,
+                       double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st) {
+    const long long items = (long long)(h / 2) * (w / 2) * 8;
+    dim3 grid(fl_grid_x(items, b), (unsigned)b);
+    if (dtype == MSTK_BF16) feat_first3_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
+    else feat_first3_kernel<MSTK_F32><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
+    MSTK_CHECK_LAUNCH("feature_first3");
+    return MSTK_OK;
 }
 
 int launch_feat_fused3(const void* f, void* pooled, int dtype, int b, int h, int w, int c, double* acc, double* scratch, float weight,

@@ -114,6 +114,12 @@ class VGGishFeatureLoss(nn.Module):
         for ci, idx in enumerate(convs):
             layer = layers[idx]
             first = layer.in_channels == 1
+            if (first and ci == 0 and layer.out_channels == 64 and h.shape[1] % 2 == 0 and h.shape[2] % 2 == 0
+                    and idx + 2 < len(layers) and isinstance(layers[idx + 2], nn.MaxPool2d)):
+                # the first tap is never materialised: conv(1 -> 64) + ReLU recomputed inside the statistics pass
+                wp, bias = self._packed(idx, torch.float32)
+                h = ops.feature_first3(h, wp, bias, b, 1.0 / len(convs), out_a, out_c, adt)
+                continue
             wp, bias = self._packed(idx, torch.float32 if first else adt)
             h = ops.conv(h, wp, bias, ksize=3, stride=1, act=ACT_RELU, out_dtype=adt)
             last = ci == len(convs) - 1

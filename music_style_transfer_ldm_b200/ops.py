@@ -490,6 +490,24 @@ def feature_fused3(f_all: torch.Tensor, b: int, weight: float, out_a: torch.Tens
     return pooled
 
 
+def feature_first3(three: torch.Tensor, wpacked: torch.Tensor, bias: torch.Tensor, b: int, weight: float, out_a: torch.Tensor,
+                   out_c: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """First VGGish tap of the training-step loss without materialising it: three [3b,h,w,1] fp32 images (x; recon; style),
+    features.0's packed fp32 weight [9,64,1] and bias -> accumulates the tap terms into out_a / out_c and returns the 2x2
+    max-pooled map [3b,h/2,w/2,64] in ``dtype`` (the next conv's input)."""
+    lib = _lib.load()
+    _dev(three, "feature_first3.x"); _dev(wpacked, "feature_first3.w")
+    n3, h, w, c1 = three.shape
+    if n3 != 3 * b or c1 != 1 or three.dtype != torch.float32 or tuple(wpacked.shape) != (9, 64, 1) or wpacked.dtype != torch.float32:
+        raise MstkError("feature_first3: expected [3b,h,w,1] fp32 images and a packed fp32 [9,64,1] weight")
+    pooled = torch.empty((n3, h // 2, w // 2, 64), dtype=dtype, device=three.device)
+    tmp = _loss_scratch(three.device, 8 * b + 2)
+    check(lib.mstk_feature_first3(_p(three), _p(wpacked), _p(bias), _p(pooled), dtype_code(dtype), b, h, w, tmp.data_ptr(), tmp.data_ptr() + 64 * b,
+                                  weight, _p(out_a), _p(out_c), _stream()), "mstk_feature_first3")
+    _count(1)
+    return pooled
+
+
 def maxpool2x2(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     _dev(x, "maxpool.x")

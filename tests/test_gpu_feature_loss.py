@@ -77,3 +77,28 @@ def test_feature_fused3(shape, pool, dt):
             assert torch.equal(nchw(pooled).cpu(), want)
         else:
             assert pooled is None
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("b,h,w", [(2, 128, 128), (3, 16, 24)])
+def test_feature_first3_never_materialises_the_first_tap(b, h, w, dt):
+    """conv(1 -> 64) + ReLU recomputed inside the statistics pass: the two loss terms of the tap against the reference
+    formula on the fp32 tap, the pooled map against max_pool2d of the tap"""
+    from music_style_transfer_ldm_b200 import ops
+    g = gen(b + h)
+    imgs = [torch.rand((b, 1, h, w), generator=g) for _ in range(3)]
+    imgs[1] = (imgs[0] * 0.9 + 0.1 * imgs[1]).contiguous()
+    wt = torch.randn((64, 1, 3, 3), generator=g) * 0.3
+    bias = torch.randn((64,), generator=g) * 0.1
+    taps = [F.relu(F.conv2d(im, wt, bias, padding=1)) for im in imgs]
+    ref_a, ref_c = _term(taps[0], taps[1]), _term(taps[1], taps[2])
+    three = torch.cat(imgs, dim=0).view(3 * b, h, w, 1).to(DEV)
+    wp = ops.pack_weight(wt.to(DEV), torch.float32)
+    for _ in range(2):
+        out_a, out_c = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+        pooled = ops.feature_first3(three, wp, bias.to(DEV), b, 1.0, out_a, out_c, dt)
+        assert_close(out_a, ref_a, 1e-4, "first tap, pair (x, recon)")
+        assert_close(out_c, ref_c, 1e-4, "first tap, pair (recon, style)")
+        want = F.max_pool2d(torch.cat(taps, dim=0), 2, 2)
+        assert pooled.dtype == dt
+        assert_close(nchw(pooled), want.to(dt).float(), 1e-6 if dt == torch.float32 else 4e-3, "pooled first tap")
