@@ -789,7 +789,7 @@ int mstk_feature_first3(const float* img, const float* wpacked, const float* bia
                         double* acc, double* scratch, float weight, float* out_a, float* out_c, void* stream) {
     MSTK_REQUIRE(img && wpacked && pooled && acc && scratch && out_a && out_c && b > 0 && b <= 65535, "feature_first3: bad args");
     MSTK_REQUIRE(pooled_dtype == MSTK_BF16 || pooled_dtype == MSTK_F32, "feature_first3: bad dtype");
-    MSTK_REQUIRE(h > 1 && w > 1 && !(h & 1) && !(w & 1) && (long long)(h / 2) * (w / 2) * 8 < (1ll << 31), "feature_first3: h, w must be even");
+    MSTK_REQUIRE(h > 1 && w > 1 && !(h & 1) && !(w & 1) && (long long)(h / 2) * (w / 2) * 16 < (1ll << 31), "feature_first3: h, w must be even");
     MSTK_REQUIRE(!(reinterpret_cast<uintptr_t>(pooled) & 15), "feature_first3: 16-byte alignment");
     return launch_feat_first3(img, wpacked, bias, pooled, pooled_dtype, b, h, w, acc, scratch, weight, out_a, out_c, (cudaStream_t)stream);
 }

@@ -344,24 +344,24 @@ __global__ void __launch_bounds__(256) feat_fused3_kernel(const void* __restrict
 // [3b,128,128,64] map (1.6 GB bf16 at batch 256, 499 us at ~50 % of the HBM peak) and read it back once for the
 // statistics; here only the pooled quarter-size map is written.  The statistics are taken on the fp32 values (the
 // materialised form took them on the bf16-rounded map); the pooled map is identical (rounding is monotonic).
-// Thread = 8 consecutive channels (weights + bias in 80 registers) of one pooled pixel; the 4x4 image patches are
-// shared by the 8 threads of a pixel through L1.
+// Thread = 4 consecutive channels (weights + bias in 40 registers, two CTAs per SM) of one pooled pixel; its 4x4 input
+// patch per image is loaded once (unpredicated in the interior) and shared by the 16 threads of a pixel through L1.
 // ---------------------------------------------------------------------------
 template <int DT>
-__global__ void __launch_bounds__(256) feat_first3_kernel(const float* __restrict__ img, const float* __restrict__ wgt,
-                                                         const float* __restrict__ bias, void* pooled, int nb, int h, int w, double* acc,
-                                                         double* scratch, float weight, float* out_a, float* out_c) {
+__global__ void __launch_bounds__(256, 2) feat_first3_kernel(const float* __restrict__ img, const float* __restrict__ wgt,
+                                                            const float* __restrict__ bias, void* pooled, int nb, int h, int w, double* acc,
+                                                            double* scratch, float weight, float* out_a, float* out_c) {
     __shared__ double red[32];
-    constexpr int C = 64, CV = 8;                       // 8 channel vectors of 8
+    constexpr int C = 64, NC = 4, CV = C / NC;          // thread = 4 consecutive channels; 16 threads per pooled pixel
     const int b = blockIdx.y;
     const int ch = threadIdx.x & (CV - 1);              // constant per thread: the item stride is a multiple of 256
-    float wr[9][8], br[8];
+    float wr[9][NC], br[NC];
 #pragma unroll
     for (int t = 0; t < 9; ++t)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) wr[t][j] = __ldg(wgt + t * C + ch * 8 + j);
+        for (int j = 0; j < NC; ++j) wr[t][j] = __ldg(wgt + t * C + ch * NC + j);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) br[j] = bias ? __ldg(bias + ch * 8 + j) : 0.f;
+    for (int j = 0; j < NC; ++j) br[j] = bias ? __ldg(bias + ch * NC + j) : 0.f;
     float l[8];
     double d[8];
 #pragma unroll
@@ -373,55 +373,65 @@ __global__ void __launch_bounds__(256) feat_first3_kernel(const float* __restric
     for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < items; i += gridDim.x * 256u) {
         const unsigned r = i / CV;
         const int ox = (int)(r % wo), oy = (int)(r / wo);
-        float m[3][8];
+        const int y0 = 2 * oy - 1, x0 = 2 * ox - 1;      // top-left of the 4x4 input patch of this 2x2 output block
+        const bool interior = y0 >= 0 && x0 >= 0 && y0 + 3 < h && x0 + 3 < w;
+        float v[3][4][NC];                               // [image][pixel of the 2x2 block][channel]
 #pragma unroll
-        for (int im = 0; im < 3; ++im)
+        for (int im = 0; im < 3; ++im) {
+            const float* pl = img + (size_t)(im * nb + b) * plane;
+            float pt[4][4];
+            if (interior) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) m[im][j] = 0.f;             // post-ReLU values are >= 0
-#pragma unroll 1
-        for (int p4 = 0; p4 < 4; ++p4) {
-            const int y = 2 * oy + (p4 >> 1), x = 2 * ox + (p4 & 1);
-            float v[3][8];
-#pragma unroll
-            for (int im = 0; im < 3; ++im) {
-                const float* pl = img + (size_t)(im * nb + b) * plane;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) v[im][j] = br[j];
-#pragma unroll
-                for (int t = 0; t < 9; ++t) {
-                    const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
-                    float px = 0.f;
-                    if (yy >= 0 && yy < h && xx >= 0 && xx < w) px = __ldg(pl + (size_t)yy * w + xx);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) v[im][j] = fmaf(px, wr[t][j], v[im][j]);
+                for (int yy = 0; yy < 4; ++yy) {
+                    const float* rowp = pl + (size_t)(y0 + yy) * w + x0;
+                    pt[yy][0] = __ldg(rowp); pt[yy][1] = __ldg(rowp + 1); pt[yy][2] = __ldg(rowp + 2); pt[yy][3] = __ldg(rowp + 3);
                 }
+            } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    v[im][j] = fmaxf(v[im][j], 0.f);
-                    m[im][j] = fmaxf(m[im][j], v[im][j]);
-                }
+                for (int yy = 0; yy < 4; ++yy)
+#pragma unroll
+                    for (int xx = 0; xx < 4; ++xx) {
+                        const int gy = y0 + yy, gx = x0 + xx;
+                        pt[yy][xx] = (gy >= 0 && gy < h && gx >= 0 && gx < w) ? __ldg(pl + (size_t)gy * w + gx) : 0.f;
+                    }
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float xv = v[0][j], rv = v[1][j], sv = v[2][j];
+            for (int p4 = 0; p4 < 4; ++p4) {
+                const int py = p4 >> 1, px = p4 & 1;
+#pragma unroll
+                for (int j = 0; j < NC; ++j) v[im][p4][j] = br[j];
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    const float pv = pt[py + t / 3][px + t % 3];
+#pragma unroll
+                    for (int j = 0; j < NC; ++j) v[im][p4][j] = fmaf(pv, wr[t][j], v[im][p4][j]);
+                }
+#pragma unroll
+                for (int j = 0; j < NC; ++j) v[im][p4][j] = fmaxf(v[im][p4][j], 0.f);
+            }
+        }
+#pragma unroll
+        for (int p4 = 0; p4 < 4; ++p4)
+#pragma unroll
+            for (int j = 0; j < NC; ++j) {
+                const float xv = v[0][p4][j], rv = v[1][p4][j], sv = v[2][p4][j];
                 l[0] += xv; l[1] = fmaf(xv, xv, l[1]);
                 l[2] += rv; l[3] = fmaf(rv, rv, l[3]);
                 l[4] += sv; l[5] = fmaf(sv, sv, l[5]);
                 l[6] = fmaf(xv, rv, l[6]); l[7] = fmaf(rv, sv, l[7]);
             }
-        }
 #pragma unroll
         for (int im = 0; im < 3; ++im) {
-            if (DT == MSTK_BF16) {
-                uint4 o;
-                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+            float m[NC];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(m[im][2 * j], m[im][2 * j + 1]);
-                reinterpret_cast<uint4*>(pooled)[(size_t)(im * nb + b) * out_img + i] = o;
+            for (int j = 0; j < NC; ++j) m[j] = fmaxf(fmaxf(v[im][0][j], v[im][1][j]), fmaxf(v[im][2][j], v[im][3][j]));
+            if (DT == MSTK_BF16) {
+                uint2 o;
+                __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+                hh[0] = __floats2bfloat162_rn(m[0], m[1]); hh[1] = __floats2bfloat162_rn(m[2], m[3]);
+                reinterpret_cast<uint2*>(pooled)[(size_t)(im * nb + b) * out_img + i] = o;
             } else {
-                float4* o = reinterpret_cast<float4*>(pooled) + ((size_t)(im * nb + b) * out_img + i) * 2;
-                o[0] = make_float4(m[im][0], m[im][1], m[im][2], m[im][3]);
-                o[1] = make_float4(m[im][4], m[im][5], m[im][6], m[im][7]);
+                reinterpret_cast<float4*>(pooled)[(size_t)(im * nb + b) * out_img + i] = make_float4(m[0], m[1], m[2], m[3]);
             }
         }
         if (++run == 4) {
@@ -435,7 +445,7 @@ __global__ void __launch_bounds__(256) feat_first3_kernel(const float* __restric
 
 int launch_feat_first3(const float* img, const float* wgt, const float* bias, void* pooled, int dtype, int b, int h, int w, double* acc,
                        double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st) {
-    const long long items = (long long)(h / 2) * (w / 2) * 8;
+    const long long items = (long long)(h / 2) * (w / 2) * 16;
     dim3 grid(fl_grid_x(items, b), (unsigned)b);
     if (dtype == MSTK_BF16) feat_first3_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
     else feat_first3_kernel<MSTK_F32><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
