@@ -288,6 +288,17 @@ typedef struct mstk_mel_args {
 size_t mstk_mel_workspace_bytes(int b, int len, int n_mels);
 int mstk_mel_band_ranges(const float* mel_fb, int n_mels, int32_t* ranges, void* stream);
 int mstk_mel_frontend(const mstk_mel_args* a, void* stream);
+/* Allocation-free variant of mstk_mel_frontend.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as mstk_mel_frontend; a->work / a->work_bytes are IGNORED: the scratch (mel power,
+ * clip maxima, band ranges) is a file-scope `static __device__` array of mstk_mel_static_scratch_bytes() = 8 MiB that
+ * every GPU loading the library holds until exit.  Problems with mstk_mel_workspace_bytes(b, len, n_mels) above that
+ * limit are rejected with MSTK_EINVAL and a message (64 clips x 128 bands x 3 s at 22.05 kHz need 4.1 MiB).  Calls no
+ * cudaMalloc / cudaFree / allocating library routine.  All calls on a device share the one array: calls that overlap on
+ * the GPU (different streams, no ordering) race; calls on one stream, or ordered by events, are safe -- everything read
+ * is cleared or overwritten first by the call itself. */
+size_t mstk_mel_static_scratch_bytes(void);
+int mstk_mel_frontend_static(const mstk_mel_args* a, void* stream);
 
 /* ==============================================================================
  * Backward pass and optimizer of the training step (models/train.py:163-208).  The

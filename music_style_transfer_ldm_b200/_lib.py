@@ -144,6 +144,8 @@ SIGNATURES = {
     "mstk_mel_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "mstk_mel_band_ranges": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),
+    "mstk_mel_static_scratch_bytes": (c_size_t, []),
+    "mstk_mel_frontend_static": (c_int, [C.POINTER(MelArgs), c_void_p]),
 }
 
 _lib = None

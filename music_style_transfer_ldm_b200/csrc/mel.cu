@@ -18,6 +18,8 @@
 // Kernel 2 (mel_db_kernel): dB, floor at -80 dB, quantise, crop; 1 thread per output pixel, frame-contiguous.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace mstk {
 
 constexpr int NFFT = 2048, HOP = 512, NBINS = NFFT / 2 + 1, NC = NFFT / 2;
@@ -271,6 +273,63 @@ int mstk_mel_frontend(const mstk_mel_args* a, void* stream) {
     mel_db_kernel<<<(unsigned)blocks, 256, 0, st>>>(melp, clipmax, a->b, a->n_mels, frames, a->crop_frames, a->out, a->db_out);
     MSTK_CHECK_LAUNCH("mel_db");
     return MSTK_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA-graph capture, tight serving loops, harnesses that forbid it).  The front end's
+// scratch (mel power, per-clip maximum, band ranges) lives in ONE file-scope device array instead of a caller buffer.
+// Every GPU that loads the library holds MEL_STATIC_BYTES until exit.  In host code `g_mel_scratch` is only a host-side
+// stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------------------------
+namespace mstk {
+constexpr size_t MEL_STATIC_BYTES = (size_t)8 << 20;      // 8 MiB: e.g. 64 clips x 128 bands x 130 frames (3 s at 22.05 kHz) = 4.1 MiB
+static __device__ __align__(256) unsigned char g_mel_scratch[MEL_STATIC_BYTES];
+
+constexpr int MEL_MAX_DEVICES = 64;
+static void* g_mel_scratch_ptr[MEL_MAX_DEVICES];            // device address of g_mel_scratch on device i (0 = not looked up yet)
+static std::mutex g_mel_scratch_mu;
+
+static int mel_static_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "mel_static: cudaGetDevice");
+    MSTK_REQUIRE(dev >= 0 && dev < MEL_MAX_DEVICES, "mel_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_mel_scratch_mu);
+    if (!g_mel_scratch_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_mel_scratch);       // the current device's copy of the array
+        if (e != cudaSuccess) return cuda_fail(e, "mel_static: cudaGetSymbolAddress");
+        MSTK_REQUIRE(p != nullptr, "mel_static: cudaGetSymbolAddress returned a null address");
+        g_mel_scratch_ptr[dev] = p;
+    }
+    *out = g_mel_scratch_ptr[dev];
+    return MSTK_OK;
+}
+}  // namespace mstk
+
+extern "C" {
+
+size_t mstk_mel_static_scratch_bytes(void) { return MEL_STATIC_BYTES; }
+
+int mstk_mel_frontend_static(const mstk_mel_args* a, void* stream) {
+    MSTK_REQUIRE(a != nullptr, "mel_static: null");
+    const size_t need = mstk_mel_workspace_bytes(a->b, a->len, a->n_mels);
+    MSTK_REQUIRE(need > 0, "mel_static: bad dims");
+    MSTK_REQUIRE(need <= MEL_STATIC_BYTES,
+                 "mel_static: b %d x n_mels %d x frames %d needs %zu bytes of scratch, the built-in array holds %zu; "
+                 "use mstk_mel_frontend with a caller workspace", a->b, a->n_mels, 1 + a->len / HOP, need, MEL_STATIC_BYTES);
+    void* scratch = nullptr;
+    const int rc = mel_static_scratch(&scratch);
+    if (rc != MSTK_OK) return rc;
+    mstk_mel_args b = *a;              // a->work / a->work_bytes are ignored
+    b.work = scratch;
+    b.work_bytes = MEL_STATIC_BYTES;
+    // same launches as the caller-workspace entry point: it clears the per-clip maxima (the only scratch that must start at
+    // zero) on `stream` and overwrites everything else it reads, so the previous call's contents never leak into this one
+    return mstk_mel_frontend(&b, stream);
 }
 
 }  // extern "C"
