@@ -300,6 +300,45 @@ int mstk_mel_frontend(const mstk_mel_args* a, void* stream);
 size_t mstk_mel_static_scratch_bytes(void);
 int mstk_mel_frontend_static(const mstk_mel_args* a, void* stream);
 
+/* ------------------------------------------------------------------------------
+ * Inverse audio path (data/audio_processor.py:81-100: librosa.db_to_power + librosa.feature.inverse.mel_to_audio;
+ * :137-162: librosa.db_to_amplitude + librosa.griffinlim).  SURVEY 8(f) rank 2.  Every spectrogram-shaped array on this
+ * side of the ABI is FRAME-MAJOR: [b, frames, 1025].
+ *
+ * mstk_mel_to_stft = audio_processor.py:93-97 + librosa.feature.inverse.mel_to_stft: image [b, n_mels, frames] uint8
+ * (row 0 = lowest band) -> dB = u8 * max_db / 255 - max_db -> power 10^(dB/10) -> x = clip(pinv(mel_fb) @ power, 0)
+ * (librosa.util.nnls's starting point, and its result whenever L-BFGS-B's projected-gradient test passes there: always
+ * for a dB image, whose power is <= 1) -> mag = sqrt(x).  pinv: [1025, n_mels] fp32 (host: numpy.linalg.pinv of the
+ * filterbank, a constant of (sr, n_mels)).  pg_norm (optional, [b]) receives the L-BFGS-B projected-gradient norm
+ * max |proj(A^T (A x - B) / B.size)| of every clip's result: the caller compares it with scipy's pgtol = 1e-5.  pg_iters > 0
+ * runs that many projected-gradient steps x <- max(x - pg_step * A^T (A x - B), 0) after the initialisation (a stand-in
+ * for the L-BFGS-B iterations the reference would run on an input outside the dB-image domain; not the same iterates).
+ *
+ * mstk_db_image_to_mag = audio_processor.py:150-155: image [b, bins, frames] uint8 -> mag [b, frames, bins] amplitude.
+ *
+ * mstk_griffinlim = librosa.griffinlim(S, n_iter, hop 512, Hann, center, pad_mode constant, momentum, init random):
+ * mag [b, frames, 1025]; phase_u [b, frames, 1025] uniform draws in [0,1) (the caller's RNG: initial phase 2 pi u);
+ * audio [b, 512 * (frames - 1)] fp32.  n_fft = 2048 only.  2 launches per iteration (inverse STFT; forward STFT fused
+ * with the overlap-add read, the momentum update and the magnitude projection).
+ * ---------------------------------------------------------------------------- */
+typedef struct mstk_mel_to_stft_args {
+    const uint8_t* image; const float* pinv; const float* mel_fb; const int32_t* band_ranges;
+    float* mag; float* pg_norm;
+    int32_t b, n_mels, frames;
+    float max_db;
+    int32_t pg_iters; float pg_step;
+} mstk_mel_to_stft_args;
+int mstk_mel_to_stft(const mstk_mel_to_stft_args* a, void* stream);
+int mstk_db_image_to_mag(const uint8_t* image, float* mag, int b, int bins, int frames, float max_db, void* stream);
+typedef struct mstk_griffinlim_args {
+    const float* mag; const float* phase_u; float* audio;
+    void* work; size_t work_bytes;
+    int32_t b, frames, n_iter;
+    float momentum;
+} mstk_griffinlim_args;
+size_t mstk_griffinlim_workspace_bytes(int b, int frames);
+int mstk_griffinlim(const mstk_griffinlim_args* a, void* stream);
+
 /* ==============================================================================
  * Backward pass and optimizer of the training step (models/train.py:163-208).  The
  * reference gets these from autograd + torch.optim.Adam; here every gradient op is an

@@ -64,6 +64,17 @@ class MelArgs(C.Structure):
                 ("b", c_int), ("len", c_int), ("n_mels", c_int), ("crop_frames", c_int), ("band_ranges", c_void_p)]
 
 
+class MelToStftArgs(C.Structure):
+    _fields_ = [("image", c_void_p), ("pinv", c_void_p), ("mel_fb", c_void_p), ("band_ranges", c_void_p),
+                ("mag", c_void_p), ("pg_norm", c_void_p),
+                ("b", c_int), ("n_mels", c_int), ("frames", c_int), ("max_db", c_float), ("pg_iters", c_int), ("pg_step", c_float)]
+
+
+class GriffinLimArgs(C.Structure):
+    _fields_ = [("mag", c_void_p), ("phase_u", c_void_p), ("audio", c_void_p), ("work", c_void_p), ("work_bytes", c_size_t),
+                ("b", c_int), ("frames", c_int), ("n_iter", c_int), ("momentum", c_float)]
+
+
 class WgradArgs(C.Structure):
     _fields_ = [("x", c_void_p), ("dy", c_void_p), ("dw", c_void_p),
                 ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int), ("ksize", c_int),
@@ -146,6 +157,10 @@ SIGNATURES = {
     "mstk_mel_frontend": (c_int, [C.POINTER(MelArgs), c_void_p]),
     "mstk_mel_static_scratch_bytes": (c_size_t, []),
     "mstk_mel_frontend_static": (c_int, [C.POINTER(MelArgs), c_void_p]),
+    "mstk_mel_to_stft": (c_int, [C.POINTER(MelToStftArgs), c_void_p]),
+    "mstk_db_image_to_mag": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p]),
+    "mstk_griffinlim_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "mstk_griffinlim": (c_int, [C.POINTER(GriffinLimArgs), c_void_p]),
 }
 
 _lib = None

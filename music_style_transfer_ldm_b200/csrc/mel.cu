@@ -17,14 +17,14 @@
 // frame).  The clip maximum is kept with an integer atomicMax on the (non-negative) float bit pattern.
 // Kernel 2 (mel_db_kernel): dB, floor at -80 dB, quantise, crop; 1 thread per output pixel, frame-contiguous.
 #include "common.cuh"
+#include "fft_warp.cuh"
 
 #include <mutex>
 
 namespace mstk {
 
-constexpr int NFFT = 2048, HOP = 512, NBINS = NFFT / 2 + 1, NC = NFFT / 2;
 constexpr int MEL_WARPS = 8, MEL_FPW = 2, MEL_FPC = MEL_WARPS * MEL_FPW;     // frames per CTA
-constexpr int MEL_TW = NFFT + NFFT / 32;                                      // twiddle table, one pad slot per 32 entries
+constexpr int MEL_TW = FFT_TW;                                                // twiddle table, one pad slot per 32 entries
 constexpr int MEL_BUF = 32 * 33;                                              // per warp: transposition buffer (float2), then reused
                                                                               // for the power spectrum (1025 floats)
 
@@ -37,53 +37,6 @@ __global__ void mel_ranges_kernel(const float* __restrict__ fb, int n_mels, int2
     if (lo > hi) lo = hi = 0;
     ranges[m] = make_int2(lo, hi);
 }
-
-__device__ __forceinline__ float2 cmul(const float2 a, const float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
-__host__ __device__ constexpr int brev5(int r) { return ((r & 1) << 4) | ((r & 2) << 2) | (r & 4) | ((r & 8) >> 2) | ((r & 16) >> 4); }
-
-// e^{-2 pi i j / 32}, j = 0..15, folded to literals when j is a compile-time constant (every call site is unrolled)
-__device__ __forceinline__ float2 w32(const int j) {
-    switch (j) {
-        case 0: return make_float2(1.f, 0.f);
-        case 1: return make_float2(0.98078528040323043f, -0.19509032201612825f);
-        case 2: return make_float2(0.92387953251128674f, -0.38268343236508978f);
-        case 3: return make_float2(0.83146961230254524f, -0.55557023301960218f);
-        case 4: return make_float2(0.70710678118654757f, -0.70710678118654757f);
-        case 5: return make_float2(0.55557023301960229f, -0.83146961230254524f);
-        case 6: return make_float2(0.38268343236508984f, -0.92387953251128674f);
-        case 7: return make_float2(0.19509032201612833f, -0.98078528040323043f);
-        case 8: return make_float2(0.f, -1.f);
-        case 9: return make_float2(-0.19509032201612819f, -0.98078528040323043f);
-        case 10: return make_float2(-0.38268343236508973f, -0.92387953251128674f);
-        case 11: return make_float2(-0.55557023301960196f, -0.83146961230254535f);
-        case 12: return make_float2(-0.70710678118654746f, -0.70710678118654757f);
-        case 13: return make_float2(-0.83146961230254535f, -0.55557023301960218f);
-        case 14: return make_float2(-0.92387953251128674f, -0.38268343236508989f);
-        default: return make_float2(-0.98078528040323043f, -0.19509032201612861f);
-    }
-}
-
-// 32-point DFT in registers, radix-2 decimation in frequency: on return v[r] holds X[brev5(r)]
-__device__ __forceinline__ void fft32(float2 (&v)[32]) {
-#pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
-#pragma unroll
-        for (int g = 0; g < 32; g += 2 * s) {
-#pragma unroll
-            for (int j = 0; j < s; ++j) {
-                const float2 a = v[g + j], b = v[g + j + s];
-                v[g + j] = make_float2(a.x + b.x, a.y + b.y);
-                const float2 d = make_float2(a.x - b.x, a.y - b.y);
-                const int tw = j * (16 / s);
-                if (tw == 0) v[g + j + s] = d;
-                else if (tw == 8) v[g + j + s] = make_float2(d.y, -d.x);          // * (-i)
-                else v[g + j + s] = cmul(d, w32(tw));
-            }
-        }
-    }
-}
-
-__device__ __forceinline__ int tw_slot(const int m) { return m + (m >> 5); }
 
 __global__ void __launch_bounds__(MEL_WARPS * 32, 2) mel_power_kernel(const float* __restrict__ wave, int len, int frames,
                                                                   const float* __restrict__ fb, const int2* __restrict__ ranges, int n_mels,

@@ -543,6 +543,57 @@ def mel_frontend(wave: torch.Tensor, mel_fb: torch.Tensor, crop_frames: int, wan
     return out, db
 
 
+def mel_to_stft(image_u8: torch.Tensor, pinv: torch.Tensor, mel_fb: torch.Tensor, band_ranges: torch.Tensor, *, max_db: float = 80.0,
+                pg_iters: int = 0, pg_step: float = 0.0):
+    """image [b, n_mels, frames] uint8 -> (mag [b, frames, 1025] fp32, pg_norm [b] fp32): librosa.feature.inverse.mel_to_stft at
+    the NNLS starting point (audio_processor.py:93-97 + mel_to_audio's first half)."""
+    lib = _lib.load()
+    _dev(image_u8, "mel_to_stft.image"); _dev(pinv, "mel_to_stft.pinv"); _dev(mel_fb, "mel_to_stft.fb"); _dev(band_ranges, "mel_to_stft.ranges")
+    if image_u8.dtype != torch.uint8 or image_u8.dim() != 3:
+        raise MstkError(f"mel_to_stft: image must be uint8 [b, n_mels, frames], got {image_u8.dtype} {tuple(image_u8.shape)}")
+    b, n_mels, frames = image_u8.shape
+    if tuple(pinv.shape) != (1025, n_mels) or tuple(mel_fb.shape) != (n_mels, 1025):
+        raise MstkError("mel_to_stft: pinv must be [1025, n_mels] and mel_fb [n_mels, 1025]")
+    mag = torch.empty((b, frames, 1025), dtype=torch.float32, device=image_u8.device)
+    pg = torch.empty((b,), dtype=torch.float32, device=image_u8.device)
+    a = _lib.MelToStftArgs(_p(image_u8), _p(pinv), _p(mel_fb), _p(band_ranges), _p(mag), _p(pg), b, n_mels, frames, float(max_db),
+                           int(pg_iters), float(pg_step))
+    check(lib.mstk_mel_to_stft(C.byref(a), _stream()), "mstk_mel_to_stft")
+    _count(1)
+    return mag, pg
+
+
+def db_image_to_mag(image_u8: torch.Tensor, *, max_db: float = 80.0) -> torch.Tensor:
+    """image [b, bins, frames] uint8 dB -> amplitude [b, frames, bins] fp32 (audio_processor.py:150-155)."""
+    lib = _lib.load()
+    _dev(image_u8, "db_image_to_mag.image")
+    if image_u8.dtype != torch.uint8 or image_u8.dim() != 3:
+        raise MstkError(f"db_image_to_mag: image must be uint8 [b, bins, frames], got {image_u8.dtype} {tuple(image_u8.shape)}")
+    b, bins, frames = image_u8.shape
+    mag = torch.empty((b, frames, bins), dtype=torch.float32, device=image_u8.device)
+    check(lib.mstk_db_image_to_mag(_p(image_u8), _p(mag), b, bins, frames, float(max_db), _stream()), "mstk_db_image_to_mag")
+    _count(1)
+    return mag
+
+
+def griffinlim(mag: torch.Tensor, phase_u: torch.Tensor, *, n_iter: int = 32, momentum: float = 0.99) -> torch.Tensor:
+    """mag, phase_u [b, frames, 1025] fp32 -> audio [b, 512 * (frames - 1)] fp32 (librosa.griffinlim, n_fft 2048, hop 512)."""
+    lib = _lib.load()
+    _dev(mag, "griffinlim.mag"); _dev(phase_u, "griffinlim.phase_u")
+    if mag.dim() != 3 or mag.shape[2] != 1025 or mag.shape != phase_u.shape or mag.dtype != torch.float32 or phase_u.dtype != torch.float32:
+        raise MstkError(f"griffinlim: mag / phase_u must be fp32 [b, frames, 1025], got {tuple(mag.shape)} / {tuple(phase_u.shape)}")
+    b, frames, _ = mag.shape
+    if frames < 2:
+        raise MstkError("griffinlim: at least 2 frames")
+    audio = torch.empty((b, 512 * (frames - 1)), dtype=torch.float32, device=mag.device)
+    nbytes = lib.mstk_griffinlim_workspace_bytes(b, frames)
+    work = torch.empty(nbytes, dtype=torch.uint8, device=mag.device)
+    a = _lib.GriffinLimArgs(_p(mag), _p(phase_u), _p(audio), _p(work), nbytes, b, frames, int(n_iter), float(momentum))
+    check(lib.mstk_griffinlim(C.byref(a), _stream()), "mstk_griffinlim")
+    _count(4 + 2 * int(n_iter))
+    return audio
+
+
 # ------------------------------------------------------------------------------------------
 # backward pass / optimizer (include/mstk.h, "Backward pass and optimizer" section)
 # ------------------------------------------------------------------------------------------
