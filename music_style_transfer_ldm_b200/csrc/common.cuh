@@ -91,6 +91,9 @@ int launch_conv_edge(const ConvP& p, cudaStream_t st);
 // returns MSTK_EUNSUPPORTED when the shape is outside the tcgen05 kernel's domain
 int launch_conv_tc(const ConvP& p, void* workspace, size_t workspace_bytes, cudaStream_t st);
 bool conv_tc_supported(const ConvP& p);
+// halo-resident persistent kernel for the throughput-bound 3x3 stride-1 layers (conv_halo.cu)
+bool conv_halo_supported(const ConvP& p);
+int launch_conv_halo(const ConvP& p, cudaStream_t st);
 size_t conv_tc_workspace_bytes(const ConvP& p);
 bool tc_init();
 // vectorised feature-loss kernels (feature_loss.cu)

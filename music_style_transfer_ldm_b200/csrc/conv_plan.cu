@@ -121,6 +121,7 @@ int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
                             p.dtype, p.Cin, p.Cout, p.Hg, p.Wg);
             return MSTK_EUNSUPPORTED;
         }
+        if (mstk::tc_init() && mstk::conv_halo_supported(p)) return mstk::launch_conv_halo(p, st);
         return mstk::launch_conv_tc(p, a->workspace, a->workspace_bytes, st);
     }
     if (backend == MSTK_BACKEND_SIMT) return mstk::launch_conv_simt(p, st);

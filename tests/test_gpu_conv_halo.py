@@ -1,0 +1,69 @@
+"""-m gpu: the halo-resident persistent tcgen05 kernel (csrc/conv_halo.cu) for the throughput-bound 3x3 stride-1 layers
+against a plain PyTorch fp32 reference on the bf16-rounded operands, and against the one-tile kernel it replaces."""
+import math
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from gpu_util import assert_close, conv_ref, gen, nchw, nhwc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+# n, h, w, cin, cout: all take the halo kernel (>= 4 x 148 items of a 16 x 16 pixel block x 128 output channels)
+CASES = [
+    (160, 16, 16, 64, 512),      # one block per image, 4 output blocks, single channel block
+    (40, 32, 64, 128, 256),      # non-square image, 2 channel blocks
+    (10, 64, 64, 64, 512),       # VGGish conv2 geometry
+    (150, 16, 32, 192, 128),     # 3 channel blocks (odd), one output block
+    (64, 16, 16, 512, 1280),     # 8 channel blocks, 10 output blocks: long K loop, many accumulator hand-overs
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "x".join(map(str, c)))
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_conv_halo_vs_torch(case, out_dtype):
+    from music_style_transfer_ldm_b200 import ops
+    n, h, w, cin, cout = case
+    g = gen(hash(case) % 1000)
+    x = torch.randn((n, cin, h, w), generator=g).bfloat16()
+    wt = (torch.randn((cout, cin, 3, 3), generator=g) / math.sqrt(cin * 9)).bfloat16()
+    b = torch.randn((cout,), generator=g)
+    xd = nhwc(x, torch.bfloat16).to(DEV)
+    wp = ops.pack_weight(wt.float().to(DEV), torch.bfloat16)
+    bd = b.to(DEV)
+    y = ops.conv(xd, wp, bd, ksize=3, act=ops.ACT_RELU, out_dtype=out_dtype, backend=ops.BACKEND_TCGEN05)
+    torch.cuda.synchronize()
+    ref = torch.relu(torch.nn.functional.conv2d(x.float().to(DEV), wt.float().to(DEV), bd, padding=1))
+    assert_close(nchw(y), ref.cpu(), 1e-5 if out_dtype == torch.float32 else 8e-3, "halo vs torch")
+    # second launch (fresh barriers / TMEM) and no activation
+    y2 = ops.conv(xd, wp, None, ksize=3, act=ops.ACT_NONE, out_dtype=torch.float32, backend=ops.BACKEND_TCGEN05)
+    ref2 = torch.nn.functional.conv2d(x.float().to(DEV), wt.float().to(DEV), None, padding=1)
+    assert_close(nchw(y2), ref2.cpu(), 1e-5, "halo vs torch (no bias, no act)")
+
+
+def test_halo_kernel_is_the_one_that_runs_and_matches_the_one_tile_kernel():
+    """a child interpreter with MSTK_CONV_HALO=0 gives the one-tile kernel's result for the same seeded operands"""
+    code = r'''
+import sys, torch, math
+sys.path.insert(0, %r)
+from music_style_transfer_ldm_b200 import ops
+g = torch.Generator().manual_seed(5)
+x = torch.randn((96, 32, 32, 64), generator=g).bfloat16().cuda()
+wp = (torch.randn((9, 128, 64), generator=g) / 24).bfloat16().cuda()
+b = torch.randn((128,), generator=g).cuda()
+y = ops.conv(x, wp, b, ksize=3, act=ops.ACT_RELU, out_dtype=torch.float32)
+torch.save(y.cpu(), sys.argv[1])
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for flag in ("1", "0"):
+        path = f"/tmp/halo_cmp_{flag}.pt"
+        r = subprocess.run([sys.executable, "-c", code % root, path], env=dict(os.environ, MSTK_CONV_HALO=flag), capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(torch.load(path))
+    assert_close(outs[0], outs[1], 1e-5, "halo vs one-tile kernel")

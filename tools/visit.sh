@@ -1,5 +1,5 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_audio_inverse.py tests/test_gpu_mel.py tests/test_zz_no_alloc.py -q -m gpu -x -s --timeout 600 > gpurun_out/t_inv.log 2>&1; echo "pytest rc=$?"; tail -n 40 gpurun_out/t_inv.log
-timeout 300 python tools/bench_inverse.py > gpurun_out/inv_bench.json 2>gpurun_out/inv_bench.err; echo "inv bench rc=$?"; cat gpurun_out/inv_bench.json; tail -3 gpurun_out/inv_bench.err
-timeout 300 python tools/profile_train.py 256 5 > gpurun_out/pt_plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/train_launches.csv python tools/profile_train.py 256 3 > gpurun_out/pt_ncu.log 2>&1; echo "ncu train rc=$?"
-python tools/summarize_launches.py gpurun_out/train_launches.csv > gpurun_out/train_launches.md 2>&1; head -50 gpurun_out/train_launches.md
+( timeout 1200 python -m pytest tests/test_gpu_conv_halo.py tests/test_gpu_conv_tc.py tests/test_gpu_feature_loss.py tests/test_gpu_train.py tests/test_gpu_fp32_tc.py -q -m gpu -x --timeout 600 2>&1 | tail -8
+bash tools/bench_train.sh 2>&1
+echo "--- halo off"; MSTK_CONV_HALO=0 bash tools/bench_train.sh 2>&1 ) > gpurun_out/halo_train.log 2>&1
+cat gpurun_out/halo_train.log | cut -c 1-400
