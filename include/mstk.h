@@ -351,6 +351,18 @@ int mstk_griffinlim(const mstk_griffinlim_args* a, void* stream);
  * the packed weight of the stride-1 convolution (k3 p1, or k1) that maps dL/dy to dL/dx. */
 int mstk_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int cout, int cin, int k, int dtype, void* stream);
 
+/* All packed copies of a step's trainable weights in ONE launch: entry i re-does mstk_pack_conv_weight (mode 0),
+ * mstk_pack_convt_weight (mode 1) or mstk_pack_conv_weight_dgrad (mode 2) without a scale, kk = k * k.  The table lives in
+ * DEVICE memory; first_block = running sum of mstk_pack_blocks(cout, cin, kk) over the entries before it, total_blocks the
+ * sum over all.  (The reference re-reads nn.Parameter storage in every cuDNN call; here the trainer refreshes the packed
+ * copies once per optimizer step, models/train.py:200.) */
+typedef struct mstk_pack_entry {
+    const float* src; void* dst;
+    int32_t cout, cin, kk, mode, dtype, first_block;
+} mstk_pack_entry;
+int mstk_pack_blocks(int cout, int cin, int kk);
+int mstk_pack_multi(const mstk_pack_entry* entries_dev, int n_entries, int total_blocks, void* stream);
+
 /* Weight gradient of the convolution family: for every kernel tap,
  *   dW[tap][co][ci] += sum over pixels of dy[out pixel, co] * x[in pixel shifted by tap, ci],
  * accumulated (atomically, fp32) straight into the gradient tensor in the PARAMETER's own

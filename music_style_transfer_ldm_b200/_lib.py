@@ -75,6 +75,11 @@ class GriffinLimArgs(C.Structure):
                 ("b", c_int), ("frames", c_int), ("n_iter", c_int), ("momentum", c_float)]
 
 
+class PackEntry(C.Structure):
+    _fields_ = [("src", c_void_p), ("dst", c_void_p), ("cout", c_int), ("cin", c_int), ("kk", c_int), ("mode", c_int),
+                ("dtype", c_int), ("first_block", c_int)]
+
+
 class WgradArgs(C.Structure):
     _fields_ = [("x", c_void_p), ("dy", c_void_p), ("dw", c_void_p),
                 ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int), ("ksize", c_int),
@@ -136,6 +141,8 @@ SIGNATURES = {
                                     c_void_p, c_void_p]),
     "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_pack_conv_weight_dgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "mstk_pack_blocks": (c_int, [c_int, c_int, c_int]),
+    "mstk_pack_multi": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "mstk_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
     "mstk_act_bwd": (c_int, [C.POINTER(ActBwdArgs), c_void_p]),
     "mstk_bn_bwd_reduce": (c_int, [C.POINTER(BnBwdArgs), c_void_p]),

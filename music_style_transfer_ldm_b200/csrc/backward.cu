@@ -714,6 +714,41 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ src, void* dst, int 
     }
 }
 
+// Every packed copy of the trainable weights of a training step in ONE launch (the step re-packed each weight with its
+// own 3-5 us kernel right in front of the convolution that reads it: 52 launches, and a weight prefetch ahead of
+// griddepcontrol.wait that relied on the pack kernel's exit).  Table in device memory; block b serves the entry whose
+// [first_block, first_block + blocks) range holds it, PACK_PER_BLOCK elements each.
+constexpr int PACK_PER_BLOCK = 2048;
+__global__ void __launch_bounds__(256) pack_multi_kernel(const mstk_pack_entry* __restrict__ tab, int n) {
+    __shared__ int s_e;
+    if (threadIdx.x == 0) {
+        int e = 0;
+        while (e + 1 < n && (int)blockIdx.x >= tab[e + 1].first_block) ++e;
+        s_e = e;
+    }
+    __syncthreads();
+    const mstk_pack_entry t = tab[s_e];
+    const size_t total = (size_t)t.kk * t.cout * t.cin;
+    const size_t i0 = (size_t)((int)blockIdx.x - t.first_block) * PACK_PER_BLOCK;
+    const size_t i1 = i0 + PACK_PER_BLOCK < total ? i0 + PACK_PER_BLOCK : total;
+    const float* __restrict__ src = t.src;
+    for (size_t i = i0 + threadIdx.x; i < i1; i += 256) {
+        size_t si;
+        if (t.mode == 2) {              // dgrad: dst [kk][cin][cout], taps flipped
+            const int co = (int)(i % t.cout);
+            const int ci = (int)((i / t.cout) % t.cin);
+            const int sl = (int)(i / ((size_t)t.cin * t.cout));
+            si = ((size_t)co * t.cin + ci) * t.kk + (t.kk - 1 - sl);
+        } else {                        // dst [kk][cout][cin]; src [cout][cin][kk] (0) or [cin][cout][kk] (1)
+            const int ci = (int)(i % t.cin);
+            const int co = (int)((i / t.cin) % t.cout);
+            const int sl = (int)(i / ((size_t)t.cin * t.cout));
+            si = t.mode == 1 ? ((size_t)ci * t.cout + co) * t.kk + sl : ((size_t)co * t.cin + ci) * t.kk + sl;
+        }
+        store_from_f(t.dst, t.dtype, i, src[si]);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // weight gradient of the single-channel edge layers (HBM-streaming, CUDA cores):
 //   Conv2d(1, C, k3, stride s, p1):          V = dy [N,Hv,Wv,C], S = x  [N,Hs,Ws]
@@ -971,6 +1006,18 @@ int mstk_pack_conv_weight_dgrad(const float* w, void* dst, int cout, int cin, in
     const size_t total = (size_t)k * k * cout * cin;
     pack_dgrad_kernel<<<bw_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(w, dst, cout, cin, k, dtype);
     MSTK_CHECK_LAUNCH("pack_conv_weight_dgrad");
+    return MSTK_OK;
+}
+
+int mstk_pack_blocks(int cout, int cin, int kk) {
+    if (cout <= 0 || cin <= 0 || kk <= 0) return 0;
+    return (int)(((size_t)kk * cout * cin + PACK_PER_BLOCK - 1) / PACK_PER_BLOCK);
+}
+
+int mstk_pack_multi(const mstk_pack_entry* entries_dev, int n_entries, int total_blocks, void* stream) {
+    MSTK_REQUIRE(entries_dev && n_entries > 0 && total_blocks > 0, "pack_multi: bad args");
+    pack_multi_kernel<<<(unsigned)total_blocks, 256, 0, (cudaStream_t)stream>>>(entries_dev, n_entries);
+    MSTK_CHECK_LAUNCH("pack_multi");
     return MSTK_OK;
 }
 

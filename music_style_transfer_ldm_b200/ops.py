@@ -218,6 +218,38 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
     return y
 
 
+# When a list, every un-scaled pack_weight / pack_weight_dgrad call appends what it did (source view, destination, geometry):
+# the trainers turn the record of their first step into a PackPlan and refresh all packed copies with one launch per step.
+PACK_RECORDER: Optional[list] = None
+
+
+class PackPlan:
+    """One-launch refresh of a set of packed weight copies (mstk_pack_multi).  Holds the source views and the destination
+    tensors alive; the destinations keep their addresses, so module caches that hand them out stay valid."""
+
+    def __init__(self, entries):
+        lib = _lib.load()
+        self.entries = list(entries)
+        arr = (_lib.PackEntry * len(self.entries))()
+        blocks = 0
+        for i, e in enumerate(self.entries):
+            arr[i] = _lib.PackEntry(_p(e["src"]), _p(e["dst"]), e["cout"], e["cin"], e["kk"], e["mode"], e["dtype"], blocks)
+            blocks += lib.mstk_pack_blocks(e["cout"], e["cin"], e["kk"])
+        self.blocks = blocks
+        dev = self.entries[0]["dst"].device
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone()
+        self.table = raw.to(dev)
+        self.dst_ids = {id(e["dst"]) for e in self.entries}
+
+    def __len__(self):
+        return len(self.entries)
+
+    def run(self) -> None:
+        lib = _lib.load()
+        check(lib.mstk_pack_multi(_p(self.table), len(self.entries), self.blocks, _stream()), "mstk_pack_multi")
+        _count(1)
+
+
 def pack_weight(w: torch.Tensor, dtype: torch.dtype, *, transposed: bool = False,
                 scale: Optional[torch.Tensor] = None) -> torch.Tensor:
     """nn.Conv2d [co,ci,k,k] / nn.ConvTranspose2d [ci,co,k,k] / nn.Linear [co,ci] fp32 -> [k*k, co, ci]."""
@@ -232,6 +264,9 @@ def pack_weight(w: torch.Tensor, dtype: torch.dtype, *, transposed: bool = False
     else:
         co, ci, k = w.shape[0], w.shape[1], w.shape[2]
     dst = torch.empty((k * k, co, ci), dtype=dtype, device=w.device)
+    if PACK_RECORDER is not None and scale is None:
+        PACK_RECORDER.append(dict(src=w, dst=dst, cout=co, cin=ci, kk=k * k, mode=1 if (transposed and w.dim() == 4) else 0,
+                                  dtype=dtype_code(dtype)))
     fn = lib.mstk_pack_convt_weight if (transposed and w.dim() == 4) else lib.mstk_pack_conv_weight
     if transposed and w.dim() == 4:
         check(fn(_p(w), _p(scale), _p(dst), ci, co, k, dtype_code(dtype), _stream()), "mstk_pack_convt_weight")
@@ -605,6 +640,8 @@ def pack_weight_dgrad(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     co, ci = w.shape[0], w.shape[1]
     k = 1 if w.dim() == 2 else w.shape[2]
     dst = torch.empty((k * k, ci, co), dtype=dtype, device=w.device)
+    if PACK_RECORDER is not None:
+        PACK_RECORDER.append(dict(src=w, dst=dst, cout=co, cin=ci, kk=k * k, mode=2, dtype=dtype_code(dtype)))
     check(lib.mstk_pack_conv_weight_dgrad(_p(w), _p(dst), co, ci, k, dtype_code(dtype), _stream()), "mstk_pack_conv_weight_dgrad")
     return dst
 

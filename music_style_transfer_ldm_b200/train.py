@@ -87,6 +87,66 @@ def _backward_order(model) -> List[nn.Parameter]:
     return out
 
 
+class _PackRefresher:
+    """Keeps the packed copies of the trainable weights valid across raw-pointer optimizer steps with ONE launch per step.
+
+    The step's first run records every un-scaled pack (ops.PACK_RECORDER); afterwards, right behind the fused Adam / AdamW
+    launch, `refresh()` re-packs all recorded copies of arena parameters in place (ops.PackPlan -> mstk_pack_multi) and drops
+    only what it cannot refresh (BatchNorm folds, composed attention weights, captured sampling graphs), instead of
+    dropping every cache entry and paying one pack launch in front of every convolution of the next step (52 of the 145
+    launches of the config-4 step, and a weight prefetch that raced the pack kernel in front of it)."""
+
+    def __init__(self, roots, arena_p: torch.Tensor, skip=()):
+        self.roots, self.skip = list(roots), tuple(skip)
+        self.lo = arena_p.data_ptr()
+        self.hi = self.lo + arena_p.numel() * arena_p.element_size()
+        self.entries, self.plan, self.keep_ids = [], None, set()
+        self._saved, self._active, self._keepalive = None, False, []
+
+    def begin(self) -> None:
+        if self._active:                       # a step that raised between begin() and refresh()
+            ops.PACK_RECORDER = self._saved
+        self._saved, self._active = ops.PACK_RECORDER, True
+        ops.PACK_RECORDER = []
+
+    def _modules(self):
+        for root in self.roots:
+            for m in root.modules():
+                if not any(m is k for k in self.skip):
+                    yield m
+
+    def refresh(self) -> None:
+        new, ops.PACK_RECORDER, self._active = ops.PACK_RECORDER or [], self._saved, False
+        if new and not torch.cuda.is_current_stream_capturing():
+            cached = set()
+            for m in self._modules():
+                for _, val in m.__dict__.get("_mstk_cache", {}).values():
+                    if isinstance(val, torch.Tensor):
+                        cached.add(id(val))
+            new = [e for e in new if id(e["dst"]) in cached]          # packs of skipped (frozen, kept) modules are not ours
+            self.keep_ids |= {id(e["dst"]) for e in new}
+            self._keepalive += [e["dst"] for e in new]
+            mine = [e for e in new if self.lo <= e["src"].data_ptr() < self.hi]   # frozen weights need no refresh, only keeping
+            if mine:
+                self.entries += mine
+                self.plan = ops.PackPlan(self.entries)
+        if self.plan is not None:
+            self.plan.run()
+            for e in self.entries:             # fp32 mode hangs the hi/lo split of a packed copy on the copy itself (ops._conv_fp32_tc)
+                if hasattr(e["dst"], "_mstk_w3"):
+                    del e["dst"]._mstk_w3
+        self.drop_stale()
+
+    def drop_stale(self) -> None:
+        """everything derived from the parameters that the plan does not refresh"""
+        for m in self._modules():
+            m.__dict__.pop("_graphs", None)
+            cache = m.__dict__.get("_mstk_cache")
+            if cache:
+                for key in [k for k, (_, val) in cache.items() if not (isinstance(val, torch.Tensor) and id(val) in self.keep_ids)]:
+                    del cache[key]
+
+
 class GradReducer:
     """Data-parallel exchange of the training step: bucketed all-reduce (sum) of the flat gradient arena, issued per
     bucket behind the backward kernels that fill it and overlapped with the rest of the sweep on a side stream, plus
@@ -196,6 +256,7 @@ class LDMTrainer:
                             "encoder, model.py:340-341, and VGGishFeatureLoss is frozen); call model._freeze_encoder() first")
         self.arena = _Arena(order, self.device)
         Mo.invalidate_packed(self.model)                      # packed-weight caches point at the old storages
+        self.packs = _PackRefresher([self.model], self.arena.p, skip=(self.model.feature_loss_net,))
         # gradient buckets for the data-parallel all-reduce, in backward-completion order
         self.buckets = bucket_spans(self.model, self.arena, num_buckets)
         self.reducer = GradReducer(self.arena.g, self.buckets, self.group, self.world)
@@ -398,7 +459,7 @@ class LDMTrainer:
         ent["graph"].replay()
         self.step_count += 1
         ops._count(ent["launches"])
-        Mo.invalidate_packed(self.model, keep=(self.model.feature_loss_net,))   # parameters changed under packed copies / captured sampling graphs
+        self.packs.drop_stale()                         # the replay refreshed the packed copies; folds / sampling graphs are stale
         return ent["out"]
 
     def _step_impl(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
@@ -438,6 +499,7 @@ class LDMTrainer:
         dev, B = xs.device, xs.shape[0]
         ab = model.noise_scheduler.alpha_bar_t
         self.arena.g.zero_()                                                     # optimizer.zero_grad()
+        self.packs.begin()
         if t is None or noise is None:
             lat = model.encoder.encoder[6].out_channels
             t_d, noise_d = self._draw(B, lat, xs.shape[1] // 8, xs.shape[2] // 8)
@@ -475,7 +537,7 @@ class LDMTrainer:
         self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
                       eps=self.eps, step=self.step_dev, grad_scale=1.0 / self.world)
-        Mo.invalidate_packed(model, keep=(fl,))         # parameters changed under the packed copies / captured sampling graphs
+        self.packs.refresh()                            # parameters changed under the packed copies / captured sampling graphs
         losses = torch.stack([comp, den, styl.squeeze(0), total])
         if self.world > 1:                              # report the GLOBAL batch's losses (equal shards: mean of the ranks' means)
             self.reducer.all_reduce_small(losses)
@@ -641,6 +703,7 @@ class AutoencoderTrainer:
             raise MstkError("AutoencoderTrainer: every encoder / decoder parameter must require grad (train.py:47)")
         self.arena = _Arena(order, self.device)
         Mo.invalidate_packed(self.encoder); Mo.invalidate_packed(self.decoder)
+        self.packs = _PackRefresher([self.encoder, self.decoder], self.arena.p)
 
     @property
     def lr(self) -> float:
@@ -682,7 +745,7 @@ class AutoencoderTrainer:
         ent["graph"].replay()
         self.step_count += 1
         ops._count(ent["launches"])
-        Mo.invalidate_packed(self.encoder); Mo.invalidate_packed(self.decoder)
+        self.packs.drop_stale()
         return ent["out"]
 
     def _step_impl(self, spectrogram) -> torch.Tensor:
@@ -698,6 +761,7 @@ class AutoencoderTrainer:
         xs = x.view(B, H, W, 1)
         adt = Mo._act_dtype(enc._precision())
         self.arena.g.zero_()                                                     # optimizer.zero_grad()
+        self.packs.begin()
 
         # ---- forward (model.py:16-28, 37-49), intermediates kept ----
         v0, h0, m0, i0 = _conv_bn_train(enc, "c0", e[0], e[1], xs, transposed=False, ksize=3, act=ACT_RELU, mid_dtype=adt, out_dtype=adt, first=True)
@@ -750,7 +814,7 @@ class AutoencoderTrainer:
         self.step_dev.add_(1)
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
                       eps=self.eps, step=self.step_dev, weight_decay=self.weight_decay)
-        Mo.invalidate_packed(enc); Mo.invalidate_packed(dec)      # parameters changed under the packed copies
+        self.packs.refresh()                                      # parameters changed under the packed copies
         return loss
 
 
