@@ -604,6 +604,31 @@ def mel_leg(model, dev, peaks, rank, cpu_baseline=True, reps=10):
                                 "algorithmic_bytes_per_clip": MEL_BYTES_PER_CLIP}},
            "end_to_end": {"ms_per_call": us_full * 1e-3, "unet_denoise_steps_per_s": (NSTEPS - 1) / (us_full * 1e-6),
                           "clips_per_s": MEL_CLIPS / (us_full * 1e-6)}}
+    # the step after the path: 64 decoded 128 x 128 images -> NNLS magnitude -> 32 Griffin-Lim iterations -> waveforms
+    from music_style_transfer_ldm_b200 import ops as _ops
+    img = (torch.rand((MEL_CLIPS, 128, 128), generator=g) * 255).to(torch.uint8).to(dev)
+    u = torch.rand((MEL_CLIPS, 128, 1025), generator=g).to(dev)
+    mag = ap.mel_images_to_magnitude(img)
+    with torch.no_grad():
+        us_inv = _time_us(lambda: ap.audio_batch(img, phase_u=u), max(2, reps // 3))
+        us_gl0 = _time_us(lambda: _ops.griffinlim(mag, u, n_iter=0), max(2, reps // 3))
+        us_gl32 = _time_us(lambda: _ops.griffinlim(mag, u, n_iter=32), max(2, reps // 3))
+    us_it = (us_gl32 - us_gl0) / 32.0
+    # per frame and iteration: angles read + written, tprev read + written (complex64), S read, windowed frame written + read (2048 fp32)
+    gl_bytes_it = MEL_CLIPS * 128 * (1025 * (4 * 8 + 4) + 2 * 2048 * 4)
+    out["inverse"] = {"workload": "64 uint8 mel images 128 x 128 -> mel_to_stft (clipped pseudo-inverse = librosa's NNLS result on a dB image) -> "
+                                  "32 Griffin-Lim iterations (n_fft 2048, hop 512) -> 64 x 65 024 samples (audio_processor.py:81-100)",
+                      "kernel": "gl_istft_kernel + gl_stft_kernel (csrc/griffinlim.cu)", "us_per_call": us_inv, "clips_per_s": MEL_CLIPS / (us_inv * 1e-6),
+                      "us_per_iteration": us_it,
+                      "roofline": {"bound": "hbm", "achieved": gl_bytes_it / (us_it * 1e-6) / 1e9, "peak": peak, "unit": "GB/s",
+                                   "frac": gl_bytes_it / (us_it * 1e-6) / 1e9 / peak, "algorithmic_bytes_per_iteration": gl_bytes_it}}
+    if cpu_baseline:
+        from oracle import audio_inverse_oracle as AO
+        t0 = time.perf_counter()
+        AO.grayscale_mel_spectogram_image_to_audio(img[0].cpu().numpy(), u[0].cpu().numpy().T.astype("float64"), use_lbfgs=False)
+        dt = time.perf_counter() - t0
+        out["inverse"]["cpu_baseline"] = {"clips_per_s": 1.0 / dt, "kind": "port", "cores": 1,
+                                          "sample": f"1 clip through oracle/audio_inverse_oracle.py (numpy restatement of librosa's mel_to_audio), {dt:.2f} s"}
     if cpu_baseline:
         from oracle import mel_oracle as MO
         w = wc[:4].cpu().numpy()
@@ -861,7 +886,10 @@ def run_cuda(args):
                         "mel_clips_per_s": r3(pick(mel, "aggregate", "mel_clips_per_s")),
                         "unet_denoise_steps_per_s": r3(pick(mel, "aggregate", "config5_unet_denoise_steps_per_s")),
                         "clips_per_s": r3(pick(mel, "aggregate", "config5_clips_per_s")),
-                        "mel_cpu_clips_per_s": r3(pick(mel, "mel", "cpu_baseline", "clips_per_s"))},
+                        "mel_cpu_clips_per_s": r3(pick(mel, "mel", "cpu_baseline", "clips_per_s")),
+                        "inverse_clips_per_s": r3(pick(mel, "inverse", "clips_per_s")), "griffinlim_us_per_iteration": r3(pick(mel, "inverse", "us_per_iteration")),
+                        "griffinlim_hbm_frac": r3(pick(mel, "inverse", "roofline", "frac")),
+                        "inverse_cpu_clips_per_s": r3(pick(mel, "inverse", "cpu_baseline", "clips_per_s"))},
             "autoencoder_samples_per_s": r3(pick(ae, "value")),
             "gpu_baseline": None if base is None else {
                 "what": "stock PyTorch (cuDNN/cuBLAS) on this B200, same inputs: eager fp32+TF32 / autocast bf16 / autocast bf16 in one CUDA graph",

@@ -22,10 +22,8 @@
 namespace mstk {
 
 constexpr int CH_THREADS = 320;
-constexpr int CH_BW = 16, CH_BH = 16;                         // pixel block of one item
-constexpr int CH_HW = CH_BW + 2, CH_HH = CH_BH + 2;           // with halo
-constexpr uint32_t CH_A_BYTES = CH_HW * CH_HH * 128;          // 41 472
-constexpr uint32_t CH_A_STAGE = (CH_A_BYTES + 1023u) & ~1023u;
+constexpr int CH_BH = 16;                                     // pixel rows of one item (its width: 8 per MMA tile)
+constexpr int CH_HH = CH_BH + 2;                              // with halo
 constexpr uint32_t CH_B_BYTES = 128 * 128;                    // one tap, 128 output channels x 64 input channels
 constexpr int CH_MAX_SUB = 6;                                 // B sub-slots (stages x taps per stage)
 constexpr int CH_BN = 128;
@@ -43,7 +41,13 @@ struct HaloParams {
     float out_scale, out_shift;
     uint32_t inv_nblocks, inv_bw, inv_bwh;
     int32_t dbg;                       // development: 1 = no output stores, 2 = no TMEM reads either
+    // conv-transpose k4 s2 (CONVT kernel): 16 (phase, tap) operations per channel block, all on the SAME 18 x 18 halo box
+    int16_t op_aoff[16];               // halo row of the operation's A start: (dy + 1) * (halo width) + (dx + 1)
+    int16_t op_slice[16];              // weight slice ky * 4 + kx
+    uint32_t off_stg;                  // byte offset of the epilogue warps' staging tiles
 };
+
+struct HaloOutMaps { CUtensorMap m[4]; };   // output tensor map(s): [0] for the convolution, one per output parity for conv-transpose
 
 struct HaloShared {
     uint64_t a_full[2], a_empty[2];
@@ -54,22 +58,37 @@ struct HaloShared {
 
 __device__ __forceinline__ int hdiv(int n, uint32_t inv) { return inv ? (int)__umulhi((uint32_t)n, inv) : n; }
 
+// CONVT = false: 3x3 stride-1 convolution, 9 taps, BN = 128 output channels per item, two accumulator buffers of 2 x 128 columns.
+// CONVT = true : ConvTranspose2d(k4, s2, p1) with Cout = 64: the four output parities are four accumulators per tile
+//                (2 tiles x 4 x 64 = all 512 columns, single-buffered), 16 operations of N = 64 per channel block; each
+//                epilogue warp stores (tile, parity) boxes through the parity's strided output map.
+template <bool CONVT, int TILES>
 __global__ void __launch_bounds__(CH_THREADS, 1)
-conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_o,
+conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ HaloOutMaps maps_o,
                  const __grid_constant__ HaloParams q) {
+    constexpr int NOPS = CONVT ? 16 : 9;
+    constexpr int BN = CONVT ? 64 : 128;                    // MMA N
+    constexpr uint32_t B_BYTES = (uint32_t)BN * 128u;       // one operation's weight box
+    constexpr uint32_t TILE_COLS = CONVT ? 256u : 128u;     // TMEM columns of one tile's accumulator(s)
+    constexpr int NBUF = 512 / (TILES * (int)TILE_COLS);   // accumulator buffers: all 512 TMEM columns are used
+    constexpr int BW = 8 * TILES;                           // pixel columns of one item
+    constexpr int HW = BW + 2;                              // with halo
+    constexpr uint32_t A_BYTES = (uint32_t)(HW * CH_HH * 128);
+    constexpr uint32_t A_STAGE = (A_BYTES + 1023u) & ~1023u;
+    static_assert(NBUF >= 1 && NBUF <= 2, "accumulator budget");
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) HaloShared sh;
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
-    const uint32_t off_b = 2u * CH_A_STAGE;
+    const uint32_t off_b = 2u * A_STAGE;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = q.G, S = q.S;
-    const int R = (9 + G - 1) / G;                  // B rounds per channel block
+    const int R = (NOPS + G - 1) / G;               // B rounds per channel block
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&map_a);
         prefetch_tmap(&map_b);
-        prefetch_tmap(&map_o);
+        prefetch_tmap(&maps_o.m[0]);
         for (int s = 0; s < 2; ++s) { mbar_init(&sh.a_full[s], 1); mbar_init(&sh.a_empty[s], 1); }
         for (int s = 0; s < CH_MAX_SUB; ++s) { mbar_init(&sh.b_full[s], (uint32_t)q.G); mbar_init(&sh.b_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&sh.acc_full[s], 1); mbar_init(&sh.acc_empty[s], 8); }
@@ -95,18 +114,18 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const int n = hdiv(blk, q.inv_bwh);
                 const int rem = blk - n * (q.blocks_w * q.blocks_h);
                 const int bh = hdiv(rem, q.inv_bw), bw = rem - bh * q.blocks_w;
-                const int w0 = bw * CH_BW - 1, h0 = bh * CH_BH - 1;
+                const int w0 = bw * BW - 1, h0 = bh * CH_BH - 1;
                 for (int kb = 0; kb < q.KB; ++kb, ++ka) {
                     const int s = ka & 1;
                     if (ka >= 2) mbar_wait(&sh.a_empty[s], (uint32_t)(((ka >> 1) - 1) & 1));
-                    mbar_expect_tx(&sh.a_full[s], CH_A_BYTES);
-                    tma_load_4d(&map_a, &sh.a_full[s], smem_base + (uint32_t)s * CH_A_STAGE, kb * 64, w0, h0, n);
+                    mbar_expect_tx(&sh.a_full[s], A_BYTES);
+                    tma_load_4d(&map_a, &sh.a_full[s], smem_base + (uint32_t)s * A_STAGE, kb * 64, w0, h0, n);
                 }
             }
         } else if (lane <= S * G) {
             const int j = lane - 1;
             const int s = j / G, g = j - s * G;
-            const uint32_t dst = smem_base + off_b + (uint32_t)j * CH_B_BYTES;
+            const uint32_t dst = smem_base + off_b + (uint32_t)j * B_BYTES;
             int rr = 0;                              // global round counter (all items, all channel blocks)
             for (int it = first; it < q.nitems; it += step) {
                 const int blk = hdiv(it, q.inv_nblocks);
@@ -115,57 +134,68 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     for (int r = 0; r < R; ++r, ++rr) {
                         if (rr % S != s) continue;
                         const int use = rr / S;
-                        const int cnt = min(G, 9 - r * G);
+                        const int cnt = min(G, NOPS - r * G);
                         // EVERY lane of the stage observes EVERY release and arrives on the full barrier (count = G), also
                         // in a short round it does not load for: a lane that skipped a release could not tell release #u
                         // from #u+2 by parity, and a round that could complete without one of its lanes could run two
                         // releases ahead of it -- the same aliasing from the other side.
                         if (use > 0) mbar_wait(&sh.b_empty[s], (uint32_t)((use - 1) & 1));
-                        if (g == 0) mbar_expect_tx(&sh.b_full[s], CH_B_BYTES * (uint32_t)cnt);
+                        if (g == 0) mbar_expect_tx(&sh.b_full[s], B_BYTES * (uint32_t)cnt);
                         else mbar_arrive(&sh.b_full[s]);
                         if (g >= cnt) continue;
-                        tma_load_2d(&map_b, &sh.b_full[s], dst, kb * 64, (r * G + g) * q.Cout + nb * CH_BN);
+                        const int slice = CONVT ? (int)q.op_slice[r * G + g] : r * G + g;
+                        tma_load_2d(&map_b, &sh.b_full[s], dst, kb * 64, slice * q.Cout + nb * BN);
                     }
                 }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        const uint32_t idesc = keep_reg(make_idesc(CH_BN));
+        const uint32_t idesc = keep_reg(make_idesc(BN));
         const uint32_t a_full0 = keep_reg(smem_u32(&sh.a_full[0])), a_empty0 = keep_reg(smem_u32(&sh.a_empty[0]));
         const uint32_t b_full0 = keep_reg(smem_u32(&sh.b_full[0])), b_empty0 = keep_reg(smem_u32(&sh.b_empty[0]));
         const uint32_t acc_full0 = keep_reg(smem_u32(&sh.acc_full[0])), acc_empty0 = keep_reg(smem_u32(&sh.acc_empty[0]));
         // descriptor high words: SBO = one halo row (A) / 1024 (B), version 1, SWIZZLE_128B
-        const uint32_t ahi = keep_reg((uint32_t)((((uint64_t)((CH_HW * 128) >> 4)) | (1ull << 14) | (2ull << 29))));
+        const uint32_t ahi = keep_reg((uint32_t)((((uint64_t)((HW * 128) >> 4)) | (1ull << 14) | (2ull << 29))));
         const uint32_t bhi = keep_reg((uint32_t)((((uint64_t)(1024 >> 4)) | (1ull << 14) | (2ull << 29))));
         const uint32_t a_lo0 = keep_reg((smem_base & 0x3FFFFu) >> 4);
         const uint32_t b_lo0 = keep_reg(((smem_base + off_b) & 0x3FFFFu) >> 4);
         int ka = 0, rr = 0, ia = 0;
         for (int it = first; it < q.nitems; it += step, ++ia) {
-            const int buf = ia & 1;
-            if (ia >= 2) mbar_wait_addr(acc_empty0 + 8u * (uint32_t)buf, (uint32_t)(((ia >> 1) - 1) & 1));
+            const int buf = ia % NBUF, use = ia / NBUF;
+            if (use >= 1) mbar_wait_addr(acc_empty0 + 8u * (uint32_t)buf, (uint32_t)((use - 1) & 1));
             tc_fence_after();
-            const uint32_t d0 = tmem_base + (uint32_t)buf * 256u;
+            const uint32_t d0 = tmem_base + (uint32_t)buf * (uint32_t)(TILES * TILE_COLS);
             uint32_t accf = 0;
             for (int kb = 0; kb < q.KB; ++kb, ++ka) {
                 const int sa = ka & 1;
                 mbar_wait_addr(a_full0 + 8u * (uint32_t)sa, (uint32_t)((ka >> 1) & 1));
-                const uint32_t a_lo = a_lo0 + (uint32_t)sa * (CH_A_STAGE >> 4);
+                const uint32_t a_lo = a_lo0 + (uint32_t)sa * (A_STAGE >> 4);
                 for (int r = 0; r < R; ++r, ++rr) {
                     const int s = rr % S;
                     mbar_wait_addr(b_full0 + 8u * (uint32_t)s, (uint32_t)((rr / S) & 1));
                     tc_fence_after();
-                    const int cnt = min(G, 9 - r * G);
+                    const int cnt = min(G, NOPS - r * G);
                     if (elect_one()) {
                         for (int g = 0; g < cnt; ++g) {
-                            const int tap = r * G + g;
-                            const int dy = tap / 3, dx = tap - dy * 3;
-                            const uint32_t at = a_lo + (uint32_t)(dy * CH_HW + dx) * 8u;            // 128 B per halo row = 8 units of 16 B
-                            const uint32_t bt = b_lo0 + (uint32_t)(s * G + g) * (CH_B_BYTES >> 4);
+                            const int op = r * G + g;
+                            uint32_t aoff, dcol;
+                            if (CONVT) {
+                                aoff = (uint32_t)q.op_aoff[op];
+                                dcol = (uint32_t)(op >> 2) * 64u;                                  // parity's accumulator
+                                if (kb == 0 && (op & 3) == 0) accf = 0u;                            // its first operation
+                            } else {
+                                const int dy = op / 3, dx = op - dy * 3;
+                                aoff = (uint32_t)(dy * HW + dx);
+                                dcol = 0u;
+                            }
+                            const uint32_t at = a_lo + aoff * 8u;                                   // 128 B per halo row = 8 units of 16 B
+                            const uint32_t bt = b_lo0 + (uint32_t)(s * G + g) * (B_BYTES >> 4);
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
-                                umma_bf16(d0, ((uint64_t)ahi << 32) | (at + 2u * k), ((uint64_t)bhi << 32) | (bt + 2u * k), idesc, accf);
-                                umma_bf16(d0 + 128u, ((uint64_t)ahi << 32) | (at + 64u + 2u * k), ((uint64_t)bhi << 32) | (bt + 2u * k), idesc, accf);
+                                umma_bf16(d0 + dcol, ((uint64_t)ahi << 32) | (at + 2u * k), ((uint64_t)bhi << 32) | (bt + 2u * k), idesc, accf);
+                                if (TILES == 2)
+                                    umma_bf16(d0 + TILE_COLS + dcol, ((uint64_t)ahi << 32) | (at + 64u + 2u * k), ((uint64_t)bhi << 32) | (bt + 2u * k), idesc, accf);
                                 accf = 1u;
                             }
                         }
@@ -188,84 +218,98 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int half = ew >> 2;                   // column half: [0,64) or [64,128)
         const int row = qd * 32 + lane;             // GEMM row of the tile = pixel (row >> 3, row & 7) of the tile
         const int esz = q.out_f32 ? 4 : 2;
-        uint8_t* const stg = smem + off_b + (uint32_t)CH_MAX_SUB * CH_B_BYTES + (uint32_t)ew * 4096u;      // this warp's staging tile
+        uint8_t* const stg = smem + q.off_stg + (uint32_t)ew * 4096u;      // this warp's staging tile
         pdl_wait();
         int ia = 0;
         for (int it = first; it < q.nitems; it += step, ++ia) {
-            const int buf = ia & 1;
+            const int buf = ia % NBUF, use = ia / NBUF;
             const int blk = hdiv(it, q.inv_nblocks);
             const int nb = it - blk * q.nblocks;
             const int n = hdiv(blk, q.inv_bwh);
             const int rem = blk - n * (q.blocks_w * q.blocks_h);
             const int bh = hdiv(rem, q.inv_bw), bw = rem - bh * q.blocks_w;
-            const int co0 = nb * CH_BN + half * 64;
+            const int co0 = CONVT ? 0 : nb * BN + half * 64;
             const float* bias = q.bias ? q.bias + co0 : nullptr;
-            mbar_wait(&sh.acc_full[buf], (uint32_t)((ia >> 1) & 1));
+            mbar_wait(&sh.acc_full[buf], (uint32_t)(use & 1));
             tc_fence_after();
-            // Both tiles' 64 columns are fetched with ONE tcgen05.ld each, both in flight before the first is used: with
-            // 16-column loads issued one at a time the epilogue of the 64-channel layer (one channel block per item) took
-            // 15 k cycles per item under the concurrent MMAs and bounded the kernel (727 -> 1426 TFLOP/s without it).
-            const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(buf * 256 + half * 64);
-            float va[64], vb[64];
-            if (!(q.dbg & 2)) {
-                tmem_ld64_issue(taddr, va);
-                tmem_ld64_issue(taddr + 128u, vb);
-            }
-            if (!(q.dbg & 2)) { tmem_ld64_wait(va); tmem_ld64_wait(vb); }
-            // both tiles are in registers: hand the accumulator buffer back before the arithmetic and the stores
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sh.acc_empty[buf]);
-#pragma unroll
-            for (int tile = 0; tile < 2; ++tile) {
-                if (q.dbg & 2) continue;
-                float* v = tile ? vb : va;
-                const int h = bh * CH_BH + (row >> 3), w = bw * CH_BW + tile * 8 + (row & 7);
-                uint8_t* orow = reinterpret_cast<uint8_t*>(q.y) + ((((size_t)n * q.H + h) * q.W + w) * (size_t)q.Cout + (size_t)co0) * esz;
-                if (!q.out_f32) {
-                    // the previous TMA store of this warp has finished READING the staging tile
-                    if (lane == 0) bulk_wait_read();
+            // 64 accumulator columns per tcgen05.ld, two loads in flight before the first is used: with 16-column loads issued
+            // one at a time the epilogue of the 64-channel layer (one channel block per item) took 15 k cycles per item under
+            // the concurrent MMAs and bounded the kernel (727 -> 1426 TFLOP/s without it).
+            // Convolution: warp = (lane quarter, column half); the pair is (tile 0, tile 1).
+            // Conv-transpose: warp = (lane quarter, output row parity py); pair p = tile p, its two members the column parities.
+            constexpr int NPAIR = CONVT ? TILES : 1;
+#pragma unroll 1
+            for (int pair = 0; pair < NPAIR; ++pair) {
+                const uint32_t col0 = (uint32_t)buf * (uint32_t)(TILES * TILE_COLS);
+                const uint32_t col_a = col0 + (CONVT ? (uint32_t)(pair * 256 + half * 128) : (uint32_t)(half * 64));
+                const uint32_t col_b = col_a + (CONVT ? 64u : 128u);
+                const uint32_t tlane = tmem_base + ((uint32_t)(qd * 32) << 16);
+                float va[64], vb[64];
+                if (!(q.dbg & 2)) {
+                    tmem_ld64_issue(tlane + col_a, va);
+                    tmem_ld64_issue(tlane + col_b, vb);
+                    tmem_ld64_wait(va); tmem_ld64_wait(vb);
+                }
+                if (pair == NPAIR - 1) {
+                    // everything this warp needs is in registers: hand the accumulators back before the arithmetic and the stores
+                    tc_fence_before();
                     __syncwarp();
+                    if (lane == 0) mbar_arrive(&sh.acc_empty[buf]);
                 }
 #pragma unroll
-                for (int c = 0; c < 64; c += 16) {
+                for (int sub = 0; sub < 2; ++sub) {
+                    if (q.dbg & 2) continue;
+                    float* v = sub ? vb : va;
+                    const int tile = CONVT ? pair : sub;
+                    const int h = bh * CH_BH + (row >> 3), w = bw * BW + tile * 8 + (row & 7);
+                    uint8_t* orow = reinterpret_cast<uint8_t*>(q.y) + ((((size_t)n * q.H + h) * q.W + w) * (size_t)q.Cout + (size_t)co0) * esz;
+                    const bool direct = !CONVT && q.out_f32;
+                    if (!direct) {
+                        // the previous TMA store of this warp has finished READING the staging tile
+                        if (lane == 0) bulk_wait_read();
+                        __syncwarp();
+                    }
 #pragma unroll
-                    for (int j4 = 0; j4 < 16; j4 += 4) {
-                        const float4 bq = bias ? __ldg(reinterpret_cast<const float4*>(bias + c + j4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                        const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
+                    for (int c = 0; c < 64; c += 16) {
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            float x = v[c + j4 + e] + bb[e];
-                            if (q.act == MSTK_ACT_RELU) x = fmaxf(x, 0.f);
-                            else if (q.act != MSTK_ACT_NONE) x = apply_act(x, q.act);
-                            if (q.affine) x = x * q.out_scale + q.out_shift;
-                            v[c + j4 + e] = x;
+                        for (int j4 = 0; j4 < 16; j4 += 4) {
+                            const float4 bq = bias ? __ldg(reinterpret_cast<const float4*>(bias + c + j4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float x = v[c + j4 + e] + bb[e];
+                                if (q.act == MSTK_ACT_RELU) x = fmaxf(x, 0.f);
+                                else if (q.act != MSTK_ACT_NONE) x = apply_act(x, q.act);
+                                if (q.affine) x = x * q.out_scale + q.out_shift;
+                                v[c + j4 + e] = x;
+                            }
+                        }
+                        if (q.dbg & 1) { if (v[c + 3] == 123.456f) reinterpret_cast<float*>(orow)[0] = v[c + 5]; continue; }
+                        if (direct) {
+                            float4* o4 = reinterpret_cast<float4*>(orow + (size_t)c * 4);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) o4[j] = make_float4(v[c + 4 * j], v[c + 4 * j + 1], v[c + 4 * j + 2], v[c + 4 * j + 3]);
+                        } else {
+                            // bf16: this warp's 32 pixels x 64 channels go through its own 4 KB staging tile (128-byte rows in the
+                            // TMA swizzle: conflict-free 16-byte stores) and leave as ONE TMA box store; 32-byte register stores to
+                            // 32 different pixels per instruction cost the 64-channel layer 195 us of 581
+                            uint4 pk[2];
+                            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[c + 2 * e], v[c + 2 * e + 1]);
+                            const int ch = c >> 3;                                  // 16-byte chunk index of the row
+                            *reinterpret_cast<uint4*>(stg + lane * 128 + (((ch) ^ (lane & 7)) << 4)) = pk[0];
+                            *reinterpret_cast<uint4*>(stg + lane * 128 + (((ch + 1) ^ (lane & 7)) << 4)) = pk[1];
                         }
                     }
-                    if (q.dbg & 1) { if (v[c + 3] == 123.456f) reinterpret_cast<float*>(orow)[0] = v[c + 5]; continue; }
-                    if (q.out_f32) {
-                        float4* o4 = reinterpret_cast<float4*>(orow + (size_t)c * 4);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) o4[j] = make_float4(v[c + 4 * j], v[c + 4 * j + 1], v[c + 4 * j + 2], v[c + 4 * j + 3]);
-                    } else {
-                        // bf16: this warp's 32 pixels x 64 channels go through its own 4 KB staging tile (128-byte rows in the
-                        // TMA swizzle: conflict-free 16-byte stores) and leave as ONE TMA box store; 32-byte register stores to
-                        // 32 different pixels per instruction cost the 64-channel layer 195 us of 581
-                        uint4 pk[2];
-                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(pk);
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) hh[e] = __floats2bfloat162_rn(v[c + 2 * e], v[c + 2 * e + 1]);
-                        const int ch = c >> 3;                                  // 16-byte chunk index of the row
-                        *reinterpret_cast<uint4*>(stg + lane * 128 + (((ch) ^ (lane & 7)) << 4)) = pk[0];
-                        *reinterpret_cast<uint4*>(stg + lane * 128 + (((ch + 1) ^ (lane & 7)) << 4)) = pk[1];
-                    }
-                }
-                if (!q.out_f32 && !(q.dbg & 1)) {
-                    fence_async_smem();
-                    __syncwarp();
-                    if (lane == 0) {
-                        tma_store_4d(&map_o, smem_u32(stg), co0, bw * CH_BW + tile * 8, bh * CH_BH + qd * 4, n);
-                        bulk_commit();
+                    if (!direct && !(q.dbg & 1)) {
+                        fence_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            // conv-transpose: the parity's map is the output seen with doubled strides, indexed by INPUT pixel
+                            tma_store_4d(&maps_o.m[CONVT ? half * 2 + sub : 0], smem_u32(stg), co0, bw * BW + tile * 8, bh * CH_BH + qd * 4, n);
+                            bulk_commit();
+                        }
                     }
                 }
             }
@@ -285,44 +329,79 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // ---------------------------------------------------------------------------
 static int g_halo = -1, g_halo_g = 3, g_halo_s = 2, g_halo_dbg = 0;
 static bool g_halo_attr = false;
+static long long g_halo_count[3] = {0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
 
-bool conv_halo_supported(const ConvP& p) {
-    if (g_halo < 0) {
-        g_halo = 1;
-        if (const char* s = getenv("MSTK_CONV_HALO")) g_halo = atoi(s);
-        if (const char* s = getenv("MSTK_HALO_DBG")) g_halo_dbg = atoi(s);
-        if (const char* s = getenv("MSTK_HALO_GS")) sscanf(s, "%d,%d", &g_halo_g, &g_halo_s);
-        if (g_halo_g < 1 || g_halo_s < 2 || g_halo_g * g_halo_s > CH_MAX_SUB) { g_halo_g = 3; g_halo_s = 2; }
-    }
-    if (!g_halo) return false;
-    if (p.dtype != MSTK_BF16 || !p.y || p.add || p.add_nc || p.has_ddim || p.stats) return false;
-    if (p.nphases != 1 || p.ph[0].ntaps != 9 || p.s_in != 1 || p.s_out != 1) return false;
-    for (int t = 0; t < 9; ++t) {
-        const Tap& tp = p.ph[0].taps[t];
-        if (tp.dy != t / 3 - 1 || tp.dx != t % 3 - 1 || tp.slice != t) return false;
-    }
-    if (p.Cin % 64 != 0 || p.Cout % CH_BN != 0) return false;
-    if (p.Hg % CH_BH != 0 || p.Wg % CH_BW != 0 || p.Hg != p.H || p.Wg != p.W) return false;
-    if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return false;
-    if (p.bias && (reinterpret_cast<uintptr_t>(p.bias) & 15)) return false;
-    const long long items = (long long)p.N * (p.H / CH_BH) * (p.W / CH_BW) * (p.Cout / CH_BN);
-    // throughput-bound grids only: several items per SM, otherwise the one-tile kernel's finer grid wins
-    return items >= 4ll * tc_num_sms() && items < 0x7fffffffll;
+static void halo_env() {
+    if (g_halo >= 0) return;
+    g_halo = 1;
+    if (const char* s = getenv("MSTK_CONV_HALO")) g_halo = atoi(s);
+    if (const char* s = getenv("MSTK_HALO_DBG")) g_halo_dbg = atoi(s);
+    if (const char* s = getenv("MSTK_HALO_GS")) sscanf(s, "%d,%d", &g_halo_g, &g_halo_s);
+    if (g_halo_g < 1 || g_halo_s < 2 || g_halo_g * g_halo_s > CH_MAX_SUB) { g_halo_g = 3; g_halo_s = 2; }
 }
+
+// 0 = not eligible, 1 = 3x3 stride-1 convolution, 2 = ConvTranspose2d(k4, s2, p1) with 64 output channels
+static int halo_kind(const ConvP& p) {
+    halo_env();
+    if (!g_halo) return 0;
+    if (p.dtype != MSTK_BF16 || !p.y || p.add || p.add_nc || p.has_ddim || p.stats) return 0;
+    if (p.Cin % 64 != 0 || p.s_in != 1) return 0;
+    if (p.Hg % CH_BH != 0 || p.Wg % 16 != 0 || p.Hg != p.H || p.Wg != p.W) return 0;
+    if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return 0;
+    if (p.bias && (reinterpret_cast<uintptr_t>(p.bias) & 15)) return 0;
+    const long long blocks = (long long)p.N * (p.H / CH_BH) * (p.W / 16);      // 16 x 16 pixel blocks
+    if (p.nphases == 1 && p.s_out == 1 && p.ph[0].ntaps == 9 && p.Cout % CH_BN == 0) {
+        for (int t = 0; t < 9; ++t) {
+            const Tap& tp = p.ph[0].taps[t];
+            if (tp.dy != t / 3 - 1 || tp.dx != t % 3 - 1 || tp.slice != t) return 0;
+        }
+        const long long items = blocks * (p.Cout / CH_BN);
+        // throughput-bound grids only: several items per SM, otherwise the one-tile kernel's finer grid wins
+        return (items >= 4ll * tc_num_sms() && items < 0x7fffffffll) ? 1 : 0;
+    }
+    if (p.nphases == 4 && p.s_out == 2 && p.Cout == 64 && p.out_dtype == MSTK_BF16 && !(g_halo & 2)) {
+        for (int ph = 0; ph < 4; ++ph) {
+            if (p.ph[ph].ntaps != 4 || p.ph[ph].oy != (ph >> 1) || p.ph[ph].ox != (ph & 1)) return 0;
+            for (int t = 0; t < 4; ++t) {
+                const Tap& tp = p.ph[ph].taps[t];
+                if (tp.dy < -1 || tp.dy > 1 || tp.dx < -1 || tp.dx > 1 || tp.slice < 0 || tp.slice >= 16) return 0;
+            }
+        }
+        return (2 * blocks >= 4ll * tc_num_sms() && blocks < 0x3fffffffll) ? 2 : 0;     // items are 16 x 8 pixel tiles
+    }
+    return 0;
+}
+
+bool conv_halo_supported(const ConvP& p) { return halo_kind(p) != 0; }
 
 int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     if (!tc_init()) return MSTK_EUNSUPPORTED;
+    const int kind = halo_kind(p);
+    if (!kind) return MSTK_EUNSUPPORTED;
+    const bool convt = kind == 2;
+    const int bn = convt ? 64 : CH_BN;
     HaloParams q;
     memset(&q, 0, sizeof(q));
     q.bias = p.bias; q.y = p.y;
     q.N = p.N; q.H = p.H; q.W = p.W; q.Cin = p.Cin; q.Cout = p.Cout;
-    q.blocks_w = p.W / CH_BW; q.blocks_h = p.H / CH_BH;
-    q.nblocks = p.Cout / CH_BN;
+    const int tiles = convt ? 1 : 2, hw = 8 * tiles + 2;
+    q.blocks_w = p.W / (8 * tiles); q.blocks_h = p.H / CH_BH;
+    q.nblocks = convt ? 1 : p.Cout / CH_BN;
     q.nitems = p.N * q.blocks_w * q.blocks_h * q.nblocks;
     q.KB = p.Cin / 64;
-    q.G = g_halo_g; q.S = g_halo_s; q.dbg = g_halo_dbg;
+    q.G = convt ? 4 : g_halo_g; q.S = convt ? 4 : g_halo_s; q.dbg = g_halo_dbg;      // conv-transpose: 8 KB boxes, 4 per stage, 4 stages
     q.act = p.act; q.affine = p.affine; q.out_f32 = p.out_dtype == MSTK_F32 ? 1 : 0;
     q.out_scale = p.out_scale; q.out_shift = p.out_shift;
+    int nslices = 9;
+    if (convt) {
+        nslices = 16;
+        for (int ph = 0; ph < 4; ++ph)
+            for (int t = 0; t < 4; ++t) {
+                const Tap& tp = p.ph[ph].taps[t];
+                q.op_aoff[ph * 4 + t] = (int16_t)((tp.dy + 1) * hw + (tp.dx + 1));
+                q.op_slice[ph * 4 + t] = (int16_t)tp.slice;
+            }
+    }
     auto inv = [](int d) -> uint32_t { return d <= 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); };
     q.inv_nblocks = inv(q.nblocks); q.inv_bw = inv(q.blocks_w); q.inv_bwh = inv(q.blocks_w * q.blocks_h);
     MSTK_REQUIRE((long long)q.nitems * (q.blocks_w * q.blocks_h > q.nblocks ? q.blocks_w * q.blocks_h : q.nblocks) < (1ll << 32),
@@ -331,28 +410,44 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     {
         const uint64_t dims[4] = {(uint64_t)p.Cin, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)p.N};
         const uint64_t strides[3] = {(uint64_t)p.Cin * 2, (uint64_t)p.W * p.Cin * 2, (uint64_t)p.H * p.W * p.Cin * 2};
-        const uint32_t box[4] = {64u, (uint32_t)CH_HW, (uint32_t)CH_HH, 1u};
+        const uint32_t box[4] = {64u, (uint32_t)hw, (uint32_t)CH_HH, 1u};
         int rc = tc_encode_map(&map_a, 0, p.x, 4, dims, strides, box, 128);
         if (rc != MSTK_OK) return rc;
     }
     {
-        const uint64_t dims[2] = {(uint64_t)p.Cin, (uint64_t)9 * p.Cout};
+        const uint64_t dims[2] = {(uint64_t)p.Cin, (uint64_t)nslices * p.Cout};
         const uint64_t strides[1] = {(uint64_t)p.Cin * 2};
-        const uint32_t box[2] = {64u, (uint32_t)CH_BN};
+        const uint32_t box[2] = {64u, (uint32_t)bn};
         int rc = tc_encode_map(&map_b, 0, p.w, 2, dims, strides, box, 128);
         if (rc != MSTK_OK) return rc;
     }
-    CUtensorMap map_o = map_a;
-    if (!q.out_f32) {
+    HaloOutMaps maps_o;
+    for (int i = 0; i < 4; ++i) maps_o.m[i] = map_a;
+    if (convt) {
+        // one map per output parity: the output [N, 2H, 2W, 64] seen with doubled pixel strides from (py, px), indexed by input pixel
+        for (int ph = 0; ph < 4; ++ph) {
+            const int py = ph >> 1, px = ph & 1;
+            const uint8_t* base = reinterpret_cast<const uint8_t*>(p.y) + ((size_t)py * p.Wo + px) * p.Cout * 2;
+            const uint64_t dims[4] = {(uint64_t)p.Cout, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)p.N};
+            const uint64_t strides[3] = {(uint64_t)2 * p.Cout * 2, (uint64_t)2 * p.Wo * p.Cout * 2, (uint64_t)p.Ho * p.Wo * p.Cout * 2};
+            const uint32_t box[4] = {64u, 8u, 4u, 1u};
+            int rc = tc_encode_map(&maps_o.m[ph], 0, base, 4, dims, strides, box, 128);
+            if (rc != MSTK_OK) return rc;
+        }
+    } else if (!q.out_f32) {
         const uint64_t dims[4] = {(uint64_t)p.Cout, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)p.N};
         const uint64_t strides[3] = {(uint64_t)p.Cout * 2, (uint64_t)p.W * p.Cout * 2, (uint64_t)p.H * p.W * p.Cout * 2};
         const uint32_t box[4] = {64u, 8u, 4u, 1u};
-        int rc = tc_encode_map(&map_o, 0, p.y, 4, dims, strides, box, 128);
+        int rc = tc_encode_map(&maps_o.m[0], 0, p.y, 4, dims, strides, box, 128);
         if (rc != MSTK_OK) return rc;
     }
-    const size_t smem = 2 * (size_t)CH_A_STAGE + (size_t)CH_MAX_SUB * CH_B_BYTES + 8 * 4096 + 1024;
+    const size_t a_stage = ((size_t)hw * CH_HH * 128 + 1023) & ~(size_t)1023;
+    q.off_stg = (uint32_t)(2 * a_stage + (size_t)q.G * q.S * bn * 128);
+    const size_t smem = (size_t)q.off_stg + 8 * 4096 + 1024;
+    MSTK_REQUIRE(smem <= 224 * 1024 && q.S <= CH_MAX_SUB, "conv(halo): shared-memory budget");
     if (!g_halo_attr) {
-        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
         if (ea != cudaSuccess) return cuda_fail(ea, "cudaFuncSetAttribute(conv_halo_kernel)");
         g_halo_attr = true;
     }
@@ -368,9 +463,16 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_halo_kernel, map_a, map_b, map_o, q);
+    cudaError_t e = convt ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1>, map_a, map_b, maps_o, q)
+                          : cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2>, map_a, map_b, maps_o, q);
     if (e != cudaSuccess) return cuda_fail(e, "conv_halo launch");
+    ++g_halo_count[kind];
     return MSTK_OK;
 }
 
+long long halo_count(int kind) { return kind >= 1 && kind <= 2 ? g_halo_count[kind] : 0; }
+
 }  // namespace mstk
+
+/* development aid (not in mstk.h): how many launches took the halo-resident kernel (1 = 3x3 convolution, 2 = conv-transpose k4) */
+extern "C" long long mstk_debug_halo_count(int kind) { return mstk::halo_count(kind); }

@@ -67,3 +67,52 @@ torch.save(y.cpu(), sys.argv[1])
         assert r.returncode == 0, r.stderr[-2000:]
         outs.append(torch.load(path))
     assert_close(outs[0], outs[1], 1e-5, "halo vs one-tile kernel")
+
+
+def _halo_count(kind):
+    import ctypes
+    from music_style_transfer_ldm_b200 import _lib
+    fn = _lib.load().mstk_debug_halo_count
+    fn.restype, fn.argtypes = ctypes.c_longlong, [ctypes.c_int]
+    return fn(kind)
+
+
+# n, h, w, cin: ConvTranspose2d(cin, 64, k4, s2, p1) shapes that take the halo kernel (>= 2 x 148 blocks of 16 x 16 input pixels)
+CONVT_CASES = [
+    (16, 32, 256, 128),      # config-2 decoder layer (128 -> 64 @ 32 x 256 -> 64 x 512)
+    (100, 16, 48, 64),       # one channel block, non-square
+    (80, 32, 32, 192),       # three channel blocks
+]
+
+
+@pytest.mark.parametrize("case", CONVT_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_convt_halo_vs_torch(case):
+    from music_style_transfer_ldm_b200 import ops
+    n, h, w, cin = case
+    cout = 64
+    g = gen(hash(case) % 1000)
+    x = torch.randn((n, cin, h, w), generator=g).bfloat16()
+    wt = (torch.randn((cin, cout, 4, 4), generator=g) / math.sqrt(cin * 4)).bfloat16()
+    b = torch.randn((cout,), generator=g)
+    xd = nhwc(x, torch.bfloat16).to(DEV)
+    wp = ops.pack_weight(wt.float().to(DEV), torch.bfloat16, transposed=True)
+    before = _halo_count(2)
+    y = ops.conv(xd, wp, b.to(DEV), ksize=4, stride=2, transposed=True, act=ops.ACT_RELU, out_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert _halo_count(2) == before + 1, "the conv-transpose did not take the halo kernel"
+    assert tuple(y.shape) == (n, 2 * h, 2 * w, cout)
+    ref = torch.relu(torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), b.to(DEV), stride=2, padding=1))
+    assert_close(nchw(y), ref.cpu(), 8e-3, "convT halo vs torch")
+    # no bias / no activation, second launch
+    y2 = ops.conv(xd, wp, None, ksize=4, stride=2, transposed=True, act=ops.ACT_NONE, out_dtype=torch.bfloat16)
+    ref2 = torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), None, stride=2, padding=1)
+    assert_close(nchw(y2), ref2.cpu(), 8e-3, "convT halo vs torch (no bias, no act)")
+
+
+def test_conv_halo_counter():
+    from music_style_transfer_ldm_b200 import ops
+    x = torch.randn((640, 16, 16, 64), device=DEV).bfloat16()
+    wp = (torch.randn((9, 128, 64), device=DEV) / 24).bfloat16()
+    before = _halo_count(1)
+    ops.conv(x, wp, None, ksize=3)
+    assert _halo_count(1) == before + 1
