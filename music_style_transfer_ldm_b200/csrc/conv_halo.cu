@@ -18,6 +18,7 @@
 #include <cudaTypedefs.h>
 #include "common.cuh"
 #include "tc_ptx.cuh"
+#include "conv_tc_body.cuh"      // colsum16 / colsum_index (BatchNorm column sums)
 
 namespace mstk {
 
@@ -31,6 +32,7 @@ constexpr int CH_BN = 128;
 struct HaloParams {
     const float* bias;
     void* y;
+    double* stats;                     // optional [2 * Cout] BatchNorm sums of (conv + bias), conv-transpose kernel only
     int32_t N, H, W, Cin, Cout;
     int32_t blocks_w, blocks_h;        // pixel blocks per image
     int32_t nblocks;                   // Cout / 128
@@ -54,6 +56,7 @@ struct HaloShared {
     uint64_t b_full[CH_MAX_SUB], b_empty[CH_MAX_SUB];
     uint64_t acc_full[2], acc_empty[2];
     uint32_t tmem_base;
+    float sstat[2 * 64];               // conv-transpose + BatchNorm statistics: per-CTA column sums (sum, sum of squares)
 };
 
 __device__ __forceinline__ int hdiv(int n, uint32_t inv) { return inv ? (int)__umulhi((uint32_t)n, inv) : n; }
@@ -62,7 +65,7 @@ __device__ __forceinline__ int hdiv(int n, uint32_t inv) { return inv ? (int)__u
 // CONVT = true : ConvTranspose2d(k4, s2, p1) with Cout = 64: the four output parities are four accumulators per tile
 //                (2 tiles x 4 x 64 = all 512 columns, single-buffered), 16 operations of N = 64 per channel block; each
 //                epilogue warp stores (tile, parity) boxes through the parity's strided output map.
-template <bool CONVT, int TILES>
+template <bool CONVT, int TILES, bool STATS>
 __global__ void __launch_bounds__(CH_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ HaloOutMaps maps_o,
                  const __grid_constant__ HaloParams q) {
@@ -94,6 +97,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int s = 0; s < 2; ++s) { mbar_init(&sh.acc_full[s], 1); mbar_init(&sh.acc_empty[s], 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (threadIdx.x >= 64 && threadIdx.x < 64 + 128) sh.sstat[threadIdx.x - 64] = 0.f;
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sh.tmem_base)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -271,6 +275,24 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     }
 #pragma unroll
                     for (int c = 0; c < 64; c += 16) {
+                        if (CONVT && STATS) {
+                            // BatchNorm batch statistics of (conv + bias), before the activation: column sums over this warp's 32
+                            // pixels (halving butterfly), then shared-memory atomics; flushed once per CTA after the item loop
+                            float a1[16], a2[16];
+#pragma unroll
+                            for (int j4 = 0; j4 < 16; j4 += 4) {
+                                const float4 bq = bias ? __ldg(reinterpret_cast<const float4*>(bias + c + j4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                                const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) { const float x = v[c + j4 + e] + bb[e]; a1[j4 + e] = x; a2[j4 + e] = x * x; }
+                            }
+                            const float s1 = colsum16(a1, lane), s2 = colsum16(a2, lane);
+                            if (!(lane & 1)) {
+                                const int ci = c + colsum_index(lane);
+                                atomicAdd(&sh.sstat[ci], s1);
+                                atomicAdd(&sh.sstat[64 + ci], s2);
+                            }
+                        }
 #pragma unroll
                         for (int j4 = 0; j4 < 16; j4 += 4) {
                             const float4 bq = bias ? __ldg(reinterpret_cast<const float4*>(bias + c + j4)) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -315,6 +337,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
         }
         if (lane == 0) bulk_wait_read();          // the staging tile must outlive the last store's read
+        if (CONVT && STATS) {
+            epi_bar();
+            const int et = (int)threadIdx.x - 64;
+            if (et < 64) {
+                atomicAdd(q.stats + et, (double)sh.sstat[et]);
+                atomicAdd(q.stats + q.Cout + et, (double)sh.sstat[64 + et]);
+            }
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -344,13 +374,13 @@ static void halo_env() {
 static int halo_kind(const ConvP& p) {
     halo_env();
     if (!g_halo) return 0;
-    if (p.dtype != MSTK_BF16 || !p.y || p.add || p.add_nc || p.has_ddim || p.stats) return 0;
+    if (p.dtype != MSTK_BF16 || !p.y || p.add || p.add_nc || p.has_ddim) return 0;
     if (p.Cin % 64 != 0 || p.s_in != 1) return 0;
     if (p.Hg % CH_BH != 0 || p.Wg % 16 != 0 || p.Hg != p.H || p.Wg != p.W) return 0;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return 0;
     if (p.bias && (reinterpret_cast<uintptr_t>(p.bias) & 15)) return 0;
     const long long blocks = (long long)p.N * (p.H / CH_BH) * (p.W / 16);      // 16 x 16 pixel blocks
-    if (p.nphases == 1 && p.s_out == 1 && p.ph[0].ntaps == 9 && p.Cout % CH_BN == 0) {
+    if (p.nphases == 1 && p.s_out == 1 && p.ph[0].ntaps == 9 && p.Cout % CH_BN == 0 && !p.stats) {
         for (int t = 0; t < 9; ++t) {
             const Tap& tp = p.ph[0].taps[t];
             if (tp.dy != t / 3 - 1 || tp.dx != t % 3 - 1 || tp.slice != t) return 0;
@@ -382,7 +412,7 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     const int bn = convt ? 64 : CH_BN;
     HaloParams q;
     memset(&q, 0, sizeof(q));
-    q.bias = p.bias; q.y = p.y;
+    q.bias = p.bias; q.y = p.y; q.stats = p.stats;
     q.N = p.N; q.H = p.H; q.W = p.W; q.Cin = p.Cin; q.Cout = p.Cout;
     const int tiles = convt ? 1 : 2, hw = 8 * tiles + 2;
     q.blocks_w = p.W / (8 * tiles); q.blocks_h = p.H / CH_BH;
@@ -446,8 +476,9 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     const size_t smem = (size_t)q.off_stg + 8 * 4096 + 1024;
     MSTK_REQUIRE(smem <= 224 * 1024 && q.S <= CH_MAX_SUB, "conv(halo): shared-memory budget");
     if (!g_halo_attr) {
-        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
         if (ea != cudaSuccess) return cuda_fail(ea, "cudaFuncSetAttribute(conv_halo_kernel)");
         g_halo_attr = true;
     }
@@ -463,8 +494,9 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = convt ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1>, map_a, map_b, maps_o, q)
-                          : cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2>, map_a, map_b, maps_o, q);
+    cudaError_t e = !convt    ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2, false>, map_a, map_b, maps_o, q)
+                    : q.stats ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, true>, map_a, map_b, maps_o, q)
+                              : cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, false>, map_a, map_b, maps_o, q);
     if (e != cudaSuccess) return cuda_fail(e, "conv_halo launch");
     ++g_halo_count[kind];
     return MSTK_OK;

@@ -116,3 +116,24 @@ def test_conv_halo_counter():
     before = _halo_count(1)
     ops.conv(x, wp, None, ksize=3)
     assert _halo_count(1) == before + 1
+
+
+def test_convt_halo_batchnorm_statistics():
+    """train-mode decoder layer: per-channel sum / sum of squares of (conv + bias) gathered in the halo kernel's epilogue"""
+    from music_style_transfer_ldm_b200 import ops
+    n, h, w, cin, cout = 96, 32, 32, 128, 64
+    g = gen(21)
+    x = torch.randn((n, cin, h, w), generator=g).bfloat16()
+    wt = (torch.randn((cin, cout, 4, 4), generator=g) / math.sqrt(cin * 4)).bfloat16()
+    b = torch.randn((cout,), generator=g)
+    wp = ops.pack_weight(wt.float().to(DEV), torch.bfloat16, transposed=True)
+    stats = torch.zeros(2 * cout, dtype=torch.float64, device=DEV)
+    before = _halo_count(2)
+    y = ops.conv(nhwc(x, torch.bfloat16).to(DEV), wp, b.to(DEV), ksize=4, stride=2, transposed=True, act=ops.ACT_NONE, stats=stats,
+                 out_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert _halo_count(2) == before + 1
+    pre = torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), b.to(DEV), stride=2, padding=1).double()
+    assert_close(nchw(y), pre.float().cpu(), 8e-3, "convT halo (stats variant) output")
+    assert_close(stats[:cout], pre.sum(dim=(0, 2, 3)), 1e-4, "stats sum")
+    assert_close(stats[cout:], (pre ** 2).sum(dim=(0, 2, 3)), 1e-4, "stats sumsq")
