@@ -351,6 +351,28 @@ int mstk_griffinlim(const mstk_griffinlim_args* a, void* stream);
  * the packed weight of the stride-1 convolution (k3 p1, or k1) that maps dL/dy to dL/dx. */
 int mstk_pack_conv_weight_dgrad(const float* w_oihw, void* dst, int cout, int cin, int k, int dtype, void* stream);
 
+/* One-shot all-reduce (sum) of a small fp64 vector over peer-mapped memory, for the BatchNorm statistic exchanges of the
+ * data-parallel step (models/train.py:163-208 run under DDP with global-batch statistics; the reference is
+ * single-process and has no exchange).  One process per GPU: every rank allocates one exchange buffer
+ * (mstk_peer_alloc -> device pointer + 64-byte CUDA IPC handle), gathers the world's handles with its own plumbing,
+ * maps the others (mstk_peer_open) and fills mstk_peer_ctx.  mstk_peer_allreduce_f64 then replaces data[0..n) by the sum
+ * over ranks with ONE single-CTA launch per rank: push to every peer, system fence, epoch flag, spin on the own flags,
+ * sum in rank order (replicas stay bit-identical).  Every rank must issue the same sequence of (slot, n) calls; a slot may
+ * be reused once per step (32 slots, n <= 512).  Graph-capturable (the epoch lives in device memory).  A peer that never
+ * arrives makes the launch fail after ~2 s instead of hanging. */
+#define MSTK_PEER_MAX_WORLD 8
+#define MSTK_PEER_HANDLE_BYTES 64
+typedef struct mstk_peer_ctx {
+    void* bufs[MSTK_PEER_MAX_WORLD];   /* exchange buffer of every rank as mapped in THIS process (bufs[rank] = own) */
+    int32_t rank, world;
+} mstk_peer_ctx;
+size_t mstk_peer_buffer_bytes(void);
+int mstk_peer_alloc(void** dev_ptr, void* ipc_handle_out);
+int mstk_peer_open(const void* ipc_handle, void** dev_ptr);
+int mstk_peer_close(void* dev_ptr);
+int mstk_peer_free(void* dev_ptr);
+int mstk_peer_allreduce_f64(double* data, int n, int slot, const mstk_peer_ctx* ctx, void* stream);
+
 /* All packed copies of a step's trainable weights in ONE launch: entry i re-does mstk_pack_conv_weight (mode 0),
  * mstk_pack_convt_weight (mode 1) or mstk_pack_conv_weight_dgrad (mode 2) without a scale, kk = k * k.  The table lives in
  * DEVICE memory; first_block = running sum of mstk_pack_blocks(cout, cin, kk) over the entries before it, total_blocks the

@@ -80,6 +80,10 @@ class PackEntry(C.Structure):
                 ("dtype", c_int), ("first_block", c_int)]
 
 
+class PeerCtx(C.Structure):
+    _fields_ = [("bufs", c_void_p * 8), ("rank", c_int), ("world", c_int)]
+
+
 class WgradArgs(C.Structure):
     _fields_ = [("x", c_void_p), ("dy", c_void_p), ("dw", c_void_p),
                 ("n", c_int), ("h", c_int), ("w", c_int), ("cin", c_int), ("cout", c_int), ("ksize", c_int),
@@ -142,6 +146,12 @@ SIGNATURES = {
     "mstk_maxpool2x2": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_pack_conv_weight_dgrad": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "mstk_pack_blocks": (c_int, [c_int, c_int, c_int]),
+    "mstk_peer_buffer_bytes": (c_size_t, []),
+    "mstk_peer_alloc": (c_int, [C.POINTER(c_void_p), c_void_p]),
+    "mstk_peer_open": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "mstk_peer_close": (c_int, [c_void_p]),
+    "mstk_peer_free": (c_int, [c_void_p]),
+    "mstk_peer_allreduce_f64": (c_int, [c_void_p, c_int, c_int, C.POINTER(PeerCtx), c_void_p]),
     "mstk_pack_multi": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "mstk_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
     "mstk_act_bwd": (c_int, [C.POINTER(ActBwdArgs), c_void_p]),

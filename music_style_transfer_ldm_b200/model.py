@@ -148,20 +148,23 @@ def _conv_bn(mod: _Kernelised, name: str, conv, bn: nn.BatchNorm2d, x: torch.Ten
 # train-mode BatchNorm are all-reduced so that each rank normalises with the GLOBAL batch statistics
 # (SURVEY 8e).  The trainers open the scope around their own step only: a module forward outside a
 # training step (a rank-0-only sample or validation pass) never issues a collective.
-_BN_GROUP = {"group": None, "world": 1}
+_BN_GROUP = {"group": None, "world": 1, "reduce": None}
 
 
 class bn_sync_group:
-    def __init__(self, group, world_size: int):
-        self.new = (group, int(world_size))
+    """``reduce``: optional callable that sums a [2C] fp64 statistics vector over the ranks in place (the trainer passes its
+    peer-memory exchange); default: torch.distributed.all_reduce on ``group``."""
+
+    def __init__(self, group, world_size: int, reduce=None):
+        self.new = (group, int(world_size), reduce)
 
     def __enter__(self):
-        self.old = (_BN_GROUP["group"], _BN_GROUP["world"])
-        _BN_GROUP["group"], _BN_GROUP["world"] = self.new
+        self.old = (_BN_GROUP["group"], _BN_GROUP["world"], _BN_GROUP["reduce"])
+        _BN_GROUP["group"], _BN_GROUP["world"], _BN_GROUP["reduce"] = self.new
         return self
 
     def __exit__(self, *exc):
-        _BN_GROUP["group"], _BN_GROUP["world"] = self.old
+        _BN_GROUP["group"], _BN_GROUP["world"], _BN_GROUP["reduce"] = self.old
         return False
 
 
@@ -182,8 +185,11 @@ def _bn_world() -> int:
 
 def _sync_bn_stats(stats: torch.Tensor) -> torch.Tensor:
     if _BN_GROUP["world"] > 1:
-        import torch.distributed as dist
-        dist.all_reduce(stats, group=_BN_GROUP["group"])
+        if _BN_GROUP["reduce"] is not None:
+            _BN_GROUP["reduce"](stats)
+        else:
+            import torch.distributed as dist
+            dist.all_reduce(stats, group=_BN_GROUP["group"])
     return stats
 
 

@@ -33,6 +33,8 @@ Plotting (matplotlib) and tqdm are outside the hot path.
 """
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional
 
 import torch
@@ -147,13 +149,69 @@ class _PackRefresher:
                     del cache[key]
 
 
+class PeerExchange:
+    """The small fp64 all-reduces of the data-parallel step (BatchNorm statistics forward and backward) over peer-mapped
+    memory: one single-CTA launch per rank instead of an NCCL collective (csrc/peer.cu).  One process per GPU; the exchange
+    buffers are shared as CUDA IPC handles gathered over the process group.  `begin_step()` restarts the slot sequence: every
+    rank must issue the same sequence of all_reduce_() calls per step."""
+
+    MAXN, SLOTS = 512, 32
+
+    def __init__(self, group, world_size: int, device):
+        import ctypes as C
+        import torch.distributed as dist
+        from . import _lib
+        self.lib = _lib.load()
+        self.world, self.rank = int(world_size), dist.get_rank(group)
+        if self.world > 8:
+            raise MstkError("PeerExchange: at most 8 ranks (one NVSwitch domain)")
+        own, handle = C.c_void_p(), (C.c_char * 64)()
+        ops.check(self.lib.mstk_peer_alloc(C.byref(own), handle), "mstk_peer_alloc")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self.own, self.mapped = own, []
+        self.ctx = _lib.PeerCtx()
+        self.ctx.rank, self.ctx.world = self.rank, self.world
+        for r in range(self.world):
+            if r == self.rank:
+                self.ctx.bufs[r] = own.value
+                continue
+            p = C.c_void_p()
+            ops.check(self.lib.mstk_peer_open(handles[r], C.byref(p)), "mstk_peer_open")
+            self.mapped.append(p)
+            self.ctx.bufs[r] = p.value
+        self.slot = 0
+        dist.barrier(group=group)                      # every rank has mapped every buffer before the first push
+
+    def begin_step(self) -> None:
+        self.slot = 0
+
+    def fits(self, t: torch.Tensor) -> bool:
+        return t.is_cuda and t.dtype == torch.float64 and t.is_contiguous() and 0 < t.numel() <= self.MAXN and self.slot < self.SLOTS
+
+    def all_reduce_(self, t: torch.Tensor) -> None:
+        import ctypes as C
+        ops.check(self.lib.mstk_peer_allreduce_f64(t.data_ptr(), t.numel(), self.slot, C.byref(self.ctx), ops._stream()), "mstk_peer_allreduce_f64")
+        self.slot += 1
+        ops._count(1)
+
+    def close(self) -> None:
+        for p in self.mapped:
+            self.lib.mstk_peer_close(p)
+        self.mapped = []
+        if self.own is not None:
+            self.lib.mstk_peer_free(self.own)
+            self.own = None
+
+
 class GradReducer:
     """Data-parallel exchange of the training step: bucketed all-reduce (sum) of the flat gradient arena, issued per
     bucket behind the backward kernels that fill it and overlapped with the rest of the sweep on a side stream, plus
     the small all-reduces of BatchNorm statistics.  Works on CPU tensors too (gloo, synchronous) for the host-logic tests."""
 
-    def __init__(self, grads: torch.Tensor, buckets, group=None, world_size: int = 1):
+    def __init__(self, grads: torch.Tensor, buckets, group=None, world_size: int = 1, peer: Optional["PeerExchange"] = None):
         self.g, self.buckets, self.group, self.world = grads, list(buckets), group, int(world_size)
+        self.peer = peer
         self.stream = torch.cuda.Stream(device=grads.device) if (self.world > 1 and grads.is_cuda) else None
         lo = 0
         for a, b in self.buckets:
@@ -165,6 +223,9 @@ class GradReducer:
 
     def all_reduce_small(self, t: torch.Tensor) -> None:
         if self.world > 1:
+            if self.peer is not None and self.peer.fits(t):
+                self.peer.all_reduce_(t)              # one single-CTA launch over peer-mapped memory (csrc/peer.cu)
+                return
             import torch.distributed as dist
             dist.all_reduce(t, group=self.group)
 
@@ -259,7 +320,22 @@ class LDMTrainer:
         self.packs = _PackRefresher([self.model], self.arena.p, skip=(self.model.feature_loss_net,))
         # gradient buckets for the data-parallel all-reduce, in backward-completion order
         self.buckets = bucket_spans(self.model, self.arena, num_buckets)
-        self.reducer = GradReducer(self.arena.g, self.buckets, self.group, self.world)
+        # BatchNorm statistic exchanges over peer-mapped memory instead of NCCL (MSTK_PEER_BN=0 keeps NCCL); falls back when the
+        # ranks cannot map each other's memory (no peer access / IPC)
+        self.peer = None
+        if self.world > 1 and os.environ.get("MSTK_PEER_BN", "1") != "0":
+            import torch.distributed as dist
+            ok = torch.ones(1, dtype=torch.int32, device=self.device)
+            try:
+                self.peer = PeerExchange(self.group, self.world, self.device)
+            except Exception as e:      # noqa: BLE001
+                print(f"[mstk] peer-memory BatchNorm exchange unavailable ({e}); using NCCL", flush=True)
+                ok.zero_()
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            if int(ok) == 0 and self.peer is not None:
+                self.peer.close()
+                self.peer = None
+        self.reducer = GradReducer(self.arena.g, self.buckets, self.group, self.world, peer=self.peer)
         if self.world > 1:
             import torch.distributed as dist
             dist.broadcast(self.arena.p, src=0, group=self.group)        # identical replicas
@@ -275,6 +351,10 @@ class LDMTrainer:
         self._eager_steps = 0
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
+        if getattr(self, "peer", None) is not None:
+            self.reducer.peer = None
+            self.peer.close()
+            self.peer = None
 
     @property
     def lr(self) -> float:
@@ -465,7 +545,9 @@ class LDMTrainer:
     def _step_impl(self, content_spec, style_spec, t: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         # BatchNorm statistics are global-batch statistics INSIDE the step only (Mo.bn_sync_group): module forwards
         # outside a training step never all-reduce
-        with Mo.bn_sync_group(self.group, self.world):
+        if self.peer is not None:
+            self.peer.begin_step()
+        with Mo.bn_sync_group(self.group, self.world, reduce=self.reducer.all_reduce_small):
             return self._step_body(content_spec, style_spec, t, noise)
 
     def _draw(self, B: int, c: int, h: int, w: int):

@@ -40,7 +40,7 @@ def test_struct_sizes_match_the_header_layout(tmp_path):
              ("mstk_attn_args", _lib.AttnArgs), ("mstk_mel_args", _lib.MelArgs), ("mstk_wgrad_args", _lib.WgradArgs),
              ("mstk_act_bwd_args", _lib.ActBwdArgs), ("mstk_bn_bwd_args", _lib.BnBwdArgs), ("mstk_attn_bwd_args", _lib.AttnBwdArgs),
              ("mstk_mel_to_stft_args", _lib.MelToStftArgs), ("mstk_griffinlim_args", _lib.GriffinLimArgs),
-             ("mstk_pack_entry", _lib.PackEntry)]
+             ("mstk_pack_entry", _lib.PackEntry), ("mstk_peer_ctx", _lib.PeerCtx)]
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "mstk.h"\nint main(void){' +
                    "".join(f'printf("%zu\\n", sizeof({c}));' for c, _ in pairs) + "return 0;}\n")
