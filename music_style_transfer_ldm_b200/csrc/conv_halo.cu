@@ -503,8 +503,11 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
 }
 
 long long halo_count(int kind) { return kind >= 1 && kind <= 2 ? g_halo_count[kind] : 0; }
+void halo_set(int on) { halo_env(); g_halo = on; }
 
 }  // namespace mstk
 
 /* development aid (not in mstk.h): how many launches took the halo-resident kernel (1 = 3x3 convolution, 2 = conv-transpose k4) */
 extern "C" long long mstk_debug_halo_count(int kind) { return mstk::halo_count(kind); }
+/* development aid (not in mstk.h): 0 sends every shape back to the one-tile / persistent kernels of conv_tc.cu (1 = default) */
+extern "C" int mstk_debug_halo(int on) { mstk::halo_set(on); return 0; }

@@ -24,6 +24,17 @@ def _lib():
     return lib
 
 
+@pytest.fixture(autouse=True)
+def _no_halo_kernel():
+    """these tests compare the two tile loops of conv_tc.cu: keep the halo-resident kernel (conv_halo.cu, which takes the
+    VGGish-sized and config-2 decoder shapes by default) out of the way"""
+    lib = _lib()
+    lib.mstk_debug_halo.argtypes = [C.c_int]
+    lib.mstk_debug_halo(0)
+    yield
+    lib.mstk_debug_halo(1)
+
+
 CASES = [
     # n, h, w, cin, cout, k, stride, transposed
     (16, 32, 256, 128, 64, 4, 2, True),      # config 2 decoder: 4 phases x 1024 tiles
