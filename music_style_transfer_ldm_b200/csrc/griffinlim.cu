@@ -236,13 +236,42 @@ __global__ void __launch_bounds__(GL_WARPS * 32, 2) gl_stft_kernel(const float* 
     for (int fi = 0; fi < GL_FPW; ++fi) {
         const int frame = f0 + warp * GL_FPW + fi;
         if (frame >= frames) break;
+        // Sample m = frame * 512 + i of the padded signal, i = 2 (32 a + lane): its hop quarter q = i / 512 = a / 8 is the same for
+        // the whole warp, so the covering frames f' = frame + q - j (j = 0..3), their validity and the centre-trim test
+        // (2 <= frame + q <= frames) are warp-uniform and hoisted out of the 8 loads of a (q, j) pair (the per-sample
+        // form with its predicates and 64-bit address arithmetic made this kernel 5x slower than the inverse transform).
         float2 v[32];
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+            const int fq = frame + q4;
+            const bool inside = fq >= 2 && fq <= frames;
+#pragma unroll
+            for (int a8 = 0; a8 < 8; ++a8) v[8 * q4 + a8] = make_float2(0.f, 0.f);
+            if (inside) {
+#pragma unroll
+                for (int j = 3; j >= 0; --j) {               // ascending frame order, as the reference's overlap-add
+                    const int f = fq - j;
+                    if (f < 0 || f >= frames) continue;
+                    const float2* src = reinterpret_cast<const float2*>(frc + (size_t)f * NFFT + 512 * j) + lane;
+#pragma unroll
+                    for (int a8 = 0; a8 < 8; ++a8) {
+                        const float2 t = src[32 * a8];
+                        v[8 * q4 + a8].x += t.x; v[8 * q4 + a8].y += t.y;
+                    }
+                }
+                const float2* wsp = reinterpret_cast<const float2*>(inv_wss + (size_t)fq * HOP) + lane;
+#pragma unroll
+                for (int a8 = 0; a8 < 8; ++a8) {
+                    const float2 w = __ldg(wsp + 32 * a8);
+                    v[8 * q4 + a8].x *= w.x; v[8 * q4 + a8].y *= w.y;
+                }
+            }
+        }
 #pragma unroll
         for (int a = 0; a < 32; ++a) {
             const int n = 32 * a + lane;
-            const float2 t = gl_sample_pair(frc, inv_wss, frames, len, frame * HOP + 2 * n);
             const float c0 = tw[tw_slot(2 * n)].x, c1 = tw[tw_slot(2 * n + 1)].x;
-            v[a] = make_float2(t.x * (0.5f - 0.5f * c0), t.y * (0.5f - 0.5f * c1));
+            v[a] = make_float2(v[a].x * (0.5f - 0.5f * c0), v[a].y * (0.5f - 0.5f * c1));
         }
         fft1024_warp(v, tw, buf, lane);                  // v[r] = Z[lane + 32 brev5(r)]
         const size_t base = ((size_t)clip * frames + frame) * NBINS;
