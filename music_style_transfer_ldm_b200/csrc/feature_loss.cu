@@ -12,6 +12,7 @@
 // runs and fold them into doubles, use 32-bit index arithmetic inside a sample, and end in one double
 // atomic per CTA and quantity.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace mstk {
 
@@ -443,10 +444,158 @@ __global__ void __launch_bounds__(256, 2) feat_first3_kernel(const float* __rest
     fused3_finish(l, d, red, b, nb, h, w, C, acc, scratch, weight, out_a, out_c);
 }
 
+// ---------------------------------------------------------------------------
+// The same first tap on the tensor cores (bf16 mode).  feat_first3_kernel is bound by the FMA pipe: 816 FMA-class
+// instructions per thread item (432 of them the 9-tap convolution) at one per two cycles and scheduler = the measured
+// 734 us.  Here a warp owns a 2 x 8 pixel patch and computes its 16 pixels x 64 channels as eight mma.sync.m16n8k16 tiles
+// per image (K = 9 taps padded to 16): the im2col fragment is built from <= 6 pixel loads per lane; pixels AND weights are
+// carried as bf16 hi + lo (three MMAs: hi*hi + lo*hi + hi*lo, ~16 mantissa bits), so the statistics keep the accuracy of the
+// fp32 kernel (tests hold the two loss terms to 1e-4).  Accumulator layout: a thread holds pixel (y, x0 + g) in c0/c1 and (y + 1, x0 + g) in c2/c3
+// (g = lane / 4), so the vertical half of the 2x2 max-pool is in-thread and the horizontal half one shuffle (lane ^ 4);
+// the pooled 4 pixels x 64 channels of a patch are 512 contiguous bytes: staged per warp, written as 16 bytes per lane.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], const uint32_t b0, const uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(const float lo, const float hi) {
+    const __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&t);
+}
+__device__ __forceinline__ void split_pack(const float x0, const float x1, uint32_t& hi, uint32_t& lo) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+    const __nv_bfloat162 hh = __halves2bfloat162(h0, h1);
+    hi = *reinterpret_cast<const uint32_t*>(&hh);
+    lo = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
+}
+
+__global__ void __launch_bounds__(256, 2) feat_first3_mma_kernel(const float* __restrict__ img, const float* __restrict__ wgt,
+                                                                const float* __restrict__ bias, __nv_bfloat16* __restrict__ pooled, int nb, int h,
+                                                                int w, double* acc, double* scratch, float weight, float* out_a, float* out_c) {
+    __shared__ double red[32];
+    __shared__ __align__(16) uint8_t stage[8][3][512];       // per warp and image: pooled 4 pixels x 64 channels bf16
+    constexpr int C = 64;
+    const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // B fragments (weights as bf16 hi + lo, so that the statistics keep fp32-level accuracy): tile j = channels 8j..8j+7;
+    // b0 = taps (2t, 2t+1), b1 = taps (2t+8, 2t+9) of channel 8j + g.  Kept in shared memory (one word per lane and
+    // fragment: conflict-free), not in 48 registers.
+    __shared__ uint32_t sbw[4][8][32];                       // [hi b0, hi b1, lo b0, lo b1][tile][lane]
+    __shared__ __align__(8) float sbias[64];
+    if (warp == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int ch = 8 * j + g;
+            uint32_t h0, l0, h1 = 0u, l1 = 0u;
+            split_pack(__ldg(wgt + (2 * t) * C + ch), __ldg(wgt + (2 * t + 1) * C + ch), h0, l0);
+            if (t == 0) split_pack(__ldg(wgt + 8 * C + ch), 0.f, h1, l1);
+            sbw[0][j][lane] = h0; sbw[1][j][lane] = h1; sbw[2][j][lane] = l0; sbw[3][j][lane] = l1;
+        }
+    }
+    if (threadIdx.x < 64) sbias[threadIdx.x] = bias ? __ldg(bias + threadIdx.x) : 0.f;
+    __syncthreads();
+    float l[8];
+    double d[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { l[k] = 0.f; d[k] = 0.0; }
+    const int ho = h / 2, wo = w / 2, ux = w / 8;
+    const int units = ho * ux;
+    const size_t plane = (size_t)h * w;
+    // taps of this lane: k0 = 2t, k1 = 2t + 1 (and k = 8 for t == 0)
+    const int ky0 = (2 * t) / 3, kx0 = (2 * t) % 3, ky1 = (2 * t + 1) / 3, kx1 = (2 * t + 1) % 3;
+    int run = 0;
+    for (int u = blockIdx.x * 8 + warp; u < units; u += gridDim.x * 8) {
+        const int ry = u / ux, cx = u - ry * ux;
+        const int y0 = 2 * ry, x = 8 * cx + g;
+        uint32_t ah[3][4], al[3][4];
+#pragma unroll
+        for (int im = 0; im < 3; ++im) {
+            const float* pl = img + (size_t)(im * nb + b) * plane;
+            auto px = [&](int yy, int xx) -> float { return (yy >= 0 && yy < h && xx >= 0 && xx < w) ? __ldg(pl + (size_t)yy * w + xx) : 0.f; };
+            // rows of the fragment: g -> pixel (y0, x), g + 8 -> pixel (y0 + 1, x); input of tap (ky, kx) = (y + ky - 1, x + kx - 1)
+            const float p00 = px(y0 + ky0 - 1, x + kx0 - 1), p01 = px(y0 + ky1 - 1, x + kx1 - 1);
+            const float p10 = px(y0 + ky0, x + kx0 - 1), p11 = px(y0 + ky1, x + kx1 - 1);
+            split_pack(p00, p01, ah[im][0], al[im][0]);
+            split_pack(p10, p11, ah[im][1], al[im][1]);
+            if (t == 0) {                                    // tap 8 = (2, 2)
+                split_pack(px(y0 + 1, x + 1), 0.f, ah[im][2], al[im][2]);
+                split_pack(px(y0 + 2, x + 1), 0.f, ah[im][3], al[im][3]);
+            } else {
+                ah[im][2] = ah[im][3] = al[im][2] = al[im][3] = 0u;
+            }
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            float v[3][4][4];                                // [image][tile of this half][c0..c3]
+#pragma unroll
+            for (int im = 0; im < 3; ++im)
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const int j = 4 * half + jj;
+                    const float2 bj = *reinterpret_cast<const float2*>(&sbias[8 * j + 2 * t]);
+                    float c[4] = {bj.x, bj.y, bj.x, bj.y};
+                    const uint32_t wh0 = sbw[0][j][lane], wh1 = sbw[1][j][lane];
+                    mma_bf16_16816(c, ah[im], wh0, wh1);
+                    mma_bf16_16816(c, al[im], wh0, wh1);
+                    mma_bf16_16816(c, ah[im], sbw[2][j][lane], sbw[3][j][lane]);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) v[im][jj][e] = fmaxf(c[e], 0.f);
+                }
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float xv = v[0][jj][e], rv = v[1][jj][e], sv = v[2][jj][e];
+                    l[0] += xv; l[1] = fmaf(xv, xv, l[1]);
+                    l[2] += rv; l[3] = fmaf(rv, rv, l[3]);
+                    l[4] += sv; l[5] = fmaf(sv, sv, l[5]);
+                    l[6] = fmaf(xv, rv, l[6]); l[7] = fmaf(rv, sv, l[7]);
+                }
+            // 2x2 max-pool: rows g / g + 8 are the vertical pair, lane ^ 4 holds the horizontal neighbour
+#pragma unroll
+            for (int im = 0; im < 3; ++im) {
+                __syncwarp();
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    float m0 = fmaxf(v[im][jj][0], v[im][jj][2]), m1 = fmaxf(v[im][jj][1], v[im][jj][3]);
+                    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 4));
+                    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 4));
+                    if (!(g & 1)) {
+                        const int ch = 8 * (4 * half + jj) + 2 * t;
+                        *reinterpret_cast<uint32_t*>(&stage[warp][im][(g >> 1) * 128 + ch * 2]) = pack_bf16x2(m0, m1);
+                    }
+                }
+                if (half == 1) {
+                    // both halves of the 64 channels are staged: 4 pooled pixels x 128 bytes, contiguous in the pooled map
+                    __syncwarp();
+                    const uint4 o = *reinterpret_cast<const uint4*>(&stage[warp][im][lane * 16]);
+                    uint8_t* dst = reinterpret_cast<uint8_t*>(pooled + (((size_t)(im * nb + b) * ho + ry) * wo + 4 * cx) * C);
+                    *reinterpret_cast<uint4*>(dst + lane * 16) = o;
+                }
+            }
+        }
+        if (++run == 4) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { d[k] += l[k]; l[k] = 0.f; }
+            run = 0;
+        }
+    }
+    fused3_finish(l, d, red, b, nb, h, w, C, acc, scratch, weight, out_a, out_c);
+}
+
 int launch_feat_first3(const float* img, const float* wgt, const float* bias, void* pooled, int dtype, int b, int h, int w, double* acc,
                        double* scratch, float weight, float* out_a, float* out_c, cudaStream_t st) {
     const long long items = (long long)(h / 2) * (w / 2) * 16;
     dim3 grid(fl_grid_x(items, b), (unsigned)b);
+    static int use_mma = -1;
+    if (use_mma < 0) { const char* e = getenv("MSTK_FIRST3_MMA"); use_mma = e ? atoi(e) : 1; }
+    if (dtype == MSTK_BF16 && use_mma && (w % 8) == 0 && (h % 2) == 0 && (reinterpret_cast<uintptr_t>(pooled) & 15) == 0) {
+        const long long units = (long long)(h / 2) * (w / 8);
+        dim3 g2(fl_grid_x(units * 32, b), (unsigned)b);
+        feat_first3_mma_kernel<<<g2, 256, 0, st>>>(img, wgt, bias, reinterpret_cast<__nv_bfloat16*>(pooled), b, h, w, acc, scratch, weight, out_a, out_c);
+        MSTK_CHECK_LAUNCH("feature_first3(mma)");
+        return MSTK_OK;
+    }
     if (dtype == MSTK_BF16) feat_first3_kernel<MSTK_BF16><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
     else feat_first3_kernel<MSTK_F32><<<grid, 256, 0, st>>>(img, wgt, bias, pooled, b, h, w, acc, scratch, weight, out_a, out_c);
     MSTK_CHECK_LAUNCH("feature_first3");

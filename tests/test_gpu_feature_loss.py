@@ -101,4 +101,9 @@ def test_feature_first3_never_materialises_the_first_tap(b, h, w, dt):
         assert_close(out_c, ref_c, 1e-4, "first tap, pair (recon, style)")
         want = F.max_pool2d(torch.cat(taps, dim=0), 2, 2)
         assert pooled.dtype == dt
-        assert_close(nchw(pooled), want.to(dt).float(), 1e-6 if dt == torch.float32 else 4e-3, "pooled first tap")
+        # bf16 map: the tensor-core kernel carries pixels and weights as bf16 hi + lo (~1e-5 relative before rounding), so a value
+        # on a bf16 rounding boundary may land one ulp (2^-7 of the value) away from the rounded fp32 tap -- on very few elements
+        assert_close(nchw(pooled), want.to(dt).float(), 1e-6 if dt == torch.float32 else 8e-3, "pooled first tap")
+        if dt == torch.bfloat16:
+            frac = (nchw(pooled).cpu() != want.to(dt).float()).float().mean().item()
+            assert frac < 5e-3, f"{frac:.3%} of the pooled bf16 values differ from the rounded fp32 tap"

@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-( timeout 900 python -m pytest tests/test_gpu_audio_inverse.py tests/test_gpu_mel.py -q -m gpu -x --timeout 600 2>&1 | tail -3
-timeout 300 python tools/bench_inverse.py 64 128 5 ) > gpurun_out/gl2.log 2>&1
-cat gpurun_out/gl2.log | cut -c 1-400
+( timeout 1200 python -m pytest tests/test_gpu_feature_loss.py tests/test_gpu_train.py tests/test_gpu_train_autoencoder.py tests/test_gpu_baseline_sizes.py tests/test_gpu_autograd.py -q -m gpu -x --timeout 600 2>&1 | tail -4 ) > gpurun_out/f3.log 2>&1
+cat gpurun_out/f3.log | cut -c 1-300
