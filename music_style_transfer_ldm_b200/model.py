@@ -128,7 +128,7 @@ def _conv_bn(mod: _Kernelised, name: str, conv, bn: nn.BatchNorm2d, x: torch.Ten
         return ops.conv(x, wp, bias, ksize=ksize, stride=2, transposed=transposed, act=act, out_dtype=out_dtype)
     cout = bn.num_features
     _drop_fold(mod, name)
-    stats = torch.zeros(2 * cout, dtype=torch.float64, device=x.device)
+    stats = ops.zeros_f64(2 * cout, x.device)
     wp = mod._packed(name, conv.weight, w_dtype, transposed)
     y = ops.conv(x, wp, mod._f32(name + ".b", conv.bias), ksize=ksize, stride=2, transposed=transposed, act=ACT_NONE,
                  stats=stats, out_dtype=mid_dtype)
@@ -210,7 +210,7 @@ class SpectrogramEncoder(_Kernelised):
         if e[1].training:
             cout = e[1].num_features
             _drop_fold(self, "c0")
-            stats = torch.zeros(2 * cout, dtype=torch.float64, device=x.device)
+            stats = ops.zeros_f64(2 * cout, x.device)
             y = _first_layer_conv(self, "c0", e[0], x, adt, ACT_NONE, stats=stats)
             stats = _sync_bn_stats(stats)
             bn = e[1]

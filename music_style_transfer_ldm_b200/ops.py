@@ -218,6 +218,40 @@ def conv(x: torch.Tensor, wpacked: torch.Tensor, bias: Optional[torch.Tensor], *
     return y
 
 
+class ZeroPool:
+    """Step-scoped pool of zeroed fp64 scratch (BatchNorm sums): ONE memset per training step instead of one fill launch per
+    BatchNorm layer and direction.  The trainers activate it around their step (ZERO_POOL); slices keep their addresses
+    across steps, so the captured step replays."""
+
+    def __init__(self, device, doubles: int = 8192):
+        self.buf = torch.zeros(doubles, dtype=torch.float64, device=device)
+        self.off = 0
+
+    def begin(self) -> None:
+        self.buf.zero_()
+        self.off = 0
+
+    def take(self, n: int):
+        span = (n + 31) // 32 * 32
+        if self.off + span > self.buf.numel():
+            return None
+        v = self.buf[self.off:self.off + n]
+        self.off += span
+        return v
+
+
+ZERO_POOL: Optional[ZeroPool] = None
+
+
+def zeros_f64(n: int, device) -> torch.Tensor:
+    """n zeroed doubles: a slice of the active step pool, else a fresh tensor"""
+    if ZERO_POOL is not None and ZERO_POOL.buf.device == torch.device(device):
+        v = ZERO_POOL.take(n)
+        if v is not None:
+            return v
+    return torch.zeros(n, dtype=torch.float64, device=device)
+
+
 # When a list, every un-scaled pack_weight / pack_weight_dgrad call appends what it did (source view, destination, geometry):
 # the trainers turn the record of their first step into a PackPlan and refresh all packed copies with one launch per step.
 PACK_RECORDER: Optional[list] = None
@@ -687,7 +721,7 @@ def bn_bwd(dy: torch.Tensor, v: torch.Tensor, mean, invstd, gamma, beta, *, act:
     lib = _lib.load()
     c = v.shape[-1]
     rows = v.numel() // c
-    sums = torch.zeros(2 * c, dtype=torch.float64, device=v.device)
+    sums = zeros_f64(2 * c, v.device)
     dv = torch.empty(v.shape, dtype=dv_dtype or dy.dtype, device=v.device)
     a = _lib.BnBwdArgs(_p(dy), _p(v), _p(dv), _p(mean), _p(invstd), _p(gamma), _p(beta), _p(sums), _p(dgamma), _p(dbeta),
                        rows, rows * world, c, act, dtype_code(dy), dtype_code(v), dtype_code(dv))

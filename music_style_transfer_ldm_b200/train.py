@@ -286,7 +286,44 @@ class PlateauScheduler:
             self.num_bad_epochs = 0
 
 
-class LDMTrainer:
+class _SideStream:
+    """mixin of the trainers"""
+
+    # -- side stream for the parameter-gradient kernels -----------------------------------------------------------
+    # Weight gradients and bias sums are leaves of the reverse sweep: nothing downstream reads them before the bucket
+    # all-reduce / the optimizer.  On their own stream they run beside the data-gradient chain (the UNet's kernels are
+    # 30-130 CTAs on 148 SMs); inside the captured step that is a parallel branch of the graph.
+    def _side_begin(self):
+        side = getattr(self, "_side", None)
+        if side is not None:
+            side.wait_stream(torch.cuda.current_stream())
+        return side
+
+    def _side_join(self) -> None:
+        side = getattr(self, "_side", None)
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)
+
+    def _wgrad(self, x, g, dw, **kw) -> None:
+        side = self._side_begin()
+        if side is None:
+            ops.wgrad(x, g, dw, **kw)
+            return
+        with torch.cuda.stream(side):
+            ops.wgrad(x, g, dw, **kw)
+        x.record_stream(side); g.record_stream(side)
+
+    def _dbias(self, g, dbias) -> None:
+        side = self._side_begin()
+        if side is None:
+            ops.act_bwd(g, None, act=ACT_NONE, dbias=dbias, want_g=False)
+            return
+        with torch.cuda.stream(side):
+            ops.act_bwd(g, None, act=ACT_NONE, dbias=dbias, want_g=False)
+        g.record_stream(side)
+
+
+class LDMTrainer(_SideStream):
     def __init__(self, model, train_loader, device, lr=1e-4, style_loss_weight=0.1, process_group=None, world_size: int = 1,
                  num_buckets: int = 3):
         self.model = model.to(device)
@@ -318,6 +355,8 @@ class LDMTrainer:
         self.arena = _Arena(order, self.device)
         Mo.invalidate_packed(self.model)                      # packed-weight caches point at the old storages
         self.packs = _PackRefresher([self.model], self.arena.p, skip=(self.model.feature_loss_net,))
+        # parameter-gradient kernels on a side stream (MSTK_WGRAD_STREAM=0: in line)
+        self._side = torch.cuda.Stream(device=self.device) if os.environ.get("MSTK_WGRAD_STREAM", "1") != "0" else None
         # gradient buckets for the data-parallel all-reduce, in backward-completion order
         self.buckets = bucket_spans(self.model, self.arena, num_buckets)
         # BatchNorm statistic exchanges over peer-mapped memory instead of NCCL (MSTK_PEER_BN=0 keeps NCCL); falls back when the
@@ -422,6 +461,7 @@ class LDMTrainer:
     def _reduce_bucket(self, stage: int):
         """the backward sweep finished stage 0 (decoder + UNet decoder half), 1 (rest of the UNet) or 2 (style encoder):
         launch the all-reduce of every bucket that is complete now (the last bucket always ends with stage 2)"""
+        self._side_join()                       # the bucket's weight gradients run on the side stream
         n = len(self.buckets)
         for b in range(n):
             if (b if b < n - 1 else 2) == stage:
@@ -446,7 +486,7 @@ class LDMTrainer:
     def _dec_layer(self, name, conv, bn, x, adt):
         dec = self.model.decoder
         c = bn.num_features
-        stats = torch.zeros(2 * c, dtype=torch.float64, device=x.device)
+        stats = ops.zeros_f64(2 * c, x.device)
         v = ops.conv(x, dec._packed(name, conv.weight, adt, True), dec._f32(name + ".b", conv.bias), ksize=4, stride=2, transposed=True,
                      act=ACT_NONE, stats=stats, out_dtype=adt)
         Mo._sync_bn_stats(stats)
@@ -475,16 +515,16 @@ class LDMTrainer:
         e, m = ca.embed_dim, ca.multihead_attn
         b, h, w, _ = d_out.shape
         feat, style, q, kv, o = sv["feat"], sv["style"], sv["q"], sv["kv"], sv["o"]
-        ops.act_bwd(d_out, None, act=ACT_NONE, dbias=self._G(m.out_proj.bias), want_g=False)
-        ops.wgrad(o.view(b, h, w, e), d_out, self._G(m.out_proj.weight), ksize=1)
+        self._dbias(d_out, self._G(m.out_proj.bias))
+        self._wgrad(o.view(b, h, w, e), d_out, self._G(m.out_proj.weight), ksize=1)
         d_o = self._dgrad(ca, "wo", m.out_proj, d_out)
         dq, dkv = ops.attention_bwd(q.view(b, h * w, e), kv[:, :, :e], kv[:, :, e:], d_o.view(b, h * w, e), ca.num_heads)
         dq4, dkv4 = dq.view(b, h, w, e), dkv.view(b, style.shape[1], style.shape[2], 2 * e)
         gw, gb = self._G(m.in_proj_weight), self._G(m.in_proj_bias)
-        ops.act_bwd(dq4, None, act=ACT_NONE, dbias=gb[:e], want_g=False)
-        ops.act_bwd(dkv4, None, act=ACT_NONE, dbias=gb[e:], want_g=False)
-        ops.wgrad(feat, dq4, gw[:e], ksize=1)
-        ops.wgrad(style, dkv4, gw[e:], ksize=1)
+        self._dbias(dq4, gb[:e])
+        self._dbias(dkv4, gb[e:])
+        self._wgrad(feat, dq4, gw[:e], ksize=1)
+        self._wgrad(style, dkv4, gw[e:], ksize=1)
         wq_, wkv_ = m.in_proj_weight.detach()[:e], m.in_proj_weight.detach()[e:]
         d_feat = ops.conv(dq4, ca._cached(("wq", "dg", dq.dtype), (m.in_proj_weight,), lambda: ops.pack_weight_dgrad(wq_, dq.dtype)), None, ksize=1)
         d_style = ops.conv(dkv4, ca._cached(("wkv", "dg", dq.dtype), (m.in_proj_weight,), lambda: ops.pack_weight_dgrad(wkv_, dq.dtype)), None, ksize=1)
@@ -494,7 +534,7 @@ class LDMTrainer:
         """backward of y = ReLU(conv(x) + b): bias / weight gradients accumulated, returns dL/dx"""
         g = ops.act_bwd(dy, y_relu, act=ACT_RELU, dy2=dy2, dbias=self._G(conv.bias))
         tr = isinstance(conv, nn.ConvTranspose2d)
-        ops.wgrad(x_in, g, self._G(conv.weight), ksize=conv.kernel_size[0], stride=conv.stride[0], transposed=tr)
+        self._wgrad(x_in, g, self._G(conv.weight), ksize=conv.kernel_size[0], stride=conv.stride[0], transposed=tr)
         return self._dgrad(mod, name, conv, g) if need_dx else None
 
     # -- the step ---------------------------------------------------------------------------
@@ -547,8 +587,15 @@ class LDMTrainer:
         # outside a training step never all-reduce
         if self.peer is not None:
             self.peer.begin_step()
-        with Mo.bn_sync_group(self.group, self.world, reduce=self.reducer.all_reduce_small):
-            return self._step_body(content_spec, style_spec, t, noise)
+        if getattr(self, "_zpool", None) is None:
+            self._zpool = ops.ZeroPool(self.device)
+        saved, ops.ZERO_POOL = ops.ZERO_POOL, self._zpool
+        self._zpool.begin()
+        try:
+            with Mo.bn_sync_group(self.group, self.world, reduce=self.reducer.all_reduce_small):
+                return self._step_body(content_spec, style_spec, t, noise)
+        finally:
+            ops.ZERO_POOL = saved
 
     def _draw(self, B: int, c: int, h: int, w: int):
         """t ~ randint(0, T) (train.py:172) and eps ~ randn (model.py:110) for this rank's shard.  Single process: torch's
@@ -614,6 +661,7 @@ class LDMTrainer:
         self._backward_sweep(sv, g_rec, den_scale=2.0 / eps_hat.numel())
 
         # ================= update (torch.optim.Adam, train.py:156, 200) =================
+        self._side_join()
         self.reducer.wait()
         self.step_count += 1
         self.step_dev.add_(1)                           # device-side copy of the step count: the update is graph-replayable
@@ -679,26 +727,26 @@ class LDMTrainer:
          r_d2, d2, eps_hat, dec_in, v1, h1, mean1, inv1, v2, h2, mean2, inv2, rec, t, adt, ab) = sv
         # reconstruction path: d/drec of mean((rec - x)^2); tanh and the (y+1)/2 folded into act_bwd
         g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=self._G(d[6].bias), y_scale=0.5, y_shift=0.5)
-        ops.wgrad(h2, g6, self._G(d[6].weight), ksize=4, stride=2, transposed=True)
+        self._wgrad(h2, g6, self._G(d[6].weight), ksize=4, stride=2, transposed=True)
         w6 = dec._cached(("d6", "dg32"), (d[6].weight,), lambda: ops.pack_weight(d[6].weight, torch.float32))
         dh2 = ops.conv(g6, w6, None, ksize=4, stride=2, out_dtype=adt)
         dv2 = ops.bn_bwd(dh2, v2, mean2, inv2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=self._G(d[4].weight),
                          dbeta=self._G(d[4].bias), world=self.world, sync=self._sync_sums)
-        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=self._G(d[3].bias), want_g=False)
-        ops.wgrad(h1, dv2, self._G(d[3].weight), ksize=4, stride=2, transposed=True)
+        self._dbias(dv2, self._G(d[3].bias))
+        self._wgrad(h1, dv2, self._G(d[3].weight), ksize=4, stride=2, transposed=True)
         dh1 = self._dgrad(dec, "d3", d[3], dv2)
         dv1 = ops.bn_bwd(dh1, v1, mean1, inv1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=self._G(d[1].weight),
                          dbeta=self._G(d[1].bias), world=self.world, sync=self._sync_sums)
-        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=self._G(d[0].bias), want_g=False)
-        ops.wgrad(dec_in, dv1, self._G(d[0].weight), ksize=4, stride=2, transposed=True)
+        self._dbias(dv1, self._G(d[0].bias))
+        self._wgrad(dec_in, dv1, self._G(d[0].weight), ksize=4, stride=2, transposed=True)
         dz0p = self._dgrad(dec, "d0", d[0], dv1)
         # eps_hat gathers the denoising loss and the reconstruction path through x0_pred (model.py:117-124)
         g_eps = ops.eps_grad(dz0p, eps_hat, noise_l, ab, t, den_scale, adt)
         if g_eps_direct is not None:
             g_eps = ops.add_bcast(g_eps, add=g_eps_direct)
         # ---- UNet, top-down ----
-        ops.act_bwd(g_eps, None, act=ACT_NONE, dbias=self._G(u.dec1.bias), want_g=False)
-        ops.wgrad(d2, g_eps, self._G(u.dec1.weight), ksize=3)
+        self._dbias(g_eps, self._G(u.dec1.bias))
+        self._wgrad(d2, g_eps, self._G(u.dec1.weight), ksize=3)
         dd2 = self._dgrad(u, "dec1", u.dec1, g_eps)
         dd3 = self._relu_conv_bwd(u, "dec2", u.dec2, d3, r_d2, dd2)
         dd4 = self._relu_conv_bwd(u, "dec3", u.dec3, d4, r_d3, dd3)
@@ -716,12 +764,12 @@ class LDMTrainer:
         # time MLP (model.py:170-175): Linear2 <- GELU <- Linear1 <- sinusoid
         nb = dtemb.shape[0]
         dt4 = dtemb.view(nb, 1, 1, -1)
-        ops.act_bwd(dt4, None, act=ACT_NONE, dbias=self._G(l2.bias), want_g=False)
-        ops.wgrad(te_h.view(nb, 1, 1, -1), dt4, self._G(l2.weight), ksize=1)
+        self._dbias(dt4, self._G(l2.bias))
+        self._wgrad(te_h.view(nb, 1, 1, -1), dt4, self._G(l2.weight), ksize=1)
         dh = self._dgrad(u, "t2", l2, dt4)
         dpre = ops.gelu_bwd(dh.view(nb, -1), te_pre).view(nb, 1, 1, -1)
-        ops.act_bwd(dpre, None, act=ACT_NONE, dbias=self._G(l1.bias), want_g=False)
-        ops.wgrad(te_e.view(nb, 1, 1, -1), dpre, self._G(l1.weight), ksize=1)
+        self._dbias(dpre, self._G(l1.bias))
+        self._wgrad(te_e.view(nb, 1, 1, -1), dpre, self._G(l1.weight), ksize=1)
         self._reduce_bucket(1)
         # ---- style encoder: s6 feeds attention1, s5 feeds attention2 and enc6 ----
         ds5c = self._relu_conv_bwd(sty, "enc6", sty.enc6, S[4], S[5], ds6_attn)
@@ -740,7 +788,7 @@ def _conv_bn_train(mod, name, conv, bn, x, *, transposed: bool, ksize: int, act:
     """conv / convT (stride 2) with the batch sums in its epilogue, then the normalise(+ReLU) pass; keeps what the
     backward sweep needs: the pre-BatchNorm map v and the batch mean / inverse std."""
     c = bn.num_features
-    stats = torch.zeros(2 * c, dtype=torch.float64, device=x.device)
+    stats = ops.zeros_f64(2 * c, x.device)
     wp = mod._packed(name, conv.weight, torch.float32 if first else x.dtype, transposed)
     v = ops.conv(x, wp, mod._f32(name + ".b", conv.bias), ksize=ksize, stride=2, transposed=transposed, act=ACT_NONE, stats=stats,
                  out_dtype=mid_dtype)
@@ -752,7 +800,7 @@ def _conv_bn_train(mod, name, conv, bn, x, *, transposed: bool, ksize: int, act:
     return v, h, mean, invstd
 
 
-class AutoencoderTrainer:
+class AutoencoderTrainer(_SideStream):
     """One optimisation step of the reference's autoencoder stage (train.py:47, 68-83) on libmstk kernels:
     latent = encoder(x); recon = decoder(latent) (tanh range, NOT rescaled -- train.py:71-75 compares it with the
     spectrogram directly); loss = compression_loss(x, recon, latent, feature_extractor); AdamW over encoder + decoder.
@@ -786,6 +834,7 @@ class AutoencoderTrainer:
         self.arena = _Arena(order, self.device)
         Mo.invalidate_packed(self.encoder); Mo.invalidate_packed(self.decoder)
         self.packs = _PackRefresher([self.encoder, self.decoder], self.arena.p)
+        self._side = torch.cuda.Stream(device=self.device) if os.environ.get("MSTK_WGRAD_STREAM", "1") != "0" else None
 
     @property
     def lr(self) -> float:
@@ -865,33 +914,34 @@ class AutoencoderTrainer:
         # ---- backward: decoder ----
         g_rec = ops.mse_grad(rec, xs, 2.0 / rec.numel(), torch.float32)
         g6 = ops.act_bwd(g_rec, rec, act=ACT_TANH, dbias=d[6].bias.grad)
-        ops.wgrad(g2, g6, d[6].weight.grad, ksize=4, stride=2, transposed=True)
+        self._wgrad(g2, g6, d[6].weight.grad, ksize=4, stride=2, transposed=True)
         w6 = dec._cached(("d6", "dg32"), (d[6].weight,), lambda: ops.pack_weight(d[6].weight, torch.float32))
         dg2 = ops.conv(g6, w6, None, ksize=4, stride=2, out_dtype=adt)
         du2 = ops.bn_bwd(dg2, u2, n2, j2, d[4].weight.detach(), d[4].bias.detach(), act=ACT_RELU, dgamma=d[4].weight.grad, dbeta=d[4].bias.grad)
-        ops.act_bwd(du2, None, act=ACT_NONE, dbias=d[3].bias.grad, want_g=False)
-        ops.wgrad(g1, du2, d[3].weight.grad, ksize=4, stride=2, transposed=True)
+        self._dbias(du2, d[3].bias.grad)
+        self._wgrad(g1, du2, d[3].weight.grad, ksize=4, stride=2, transposed=True)
         dg1 = LDMTrainer._dgrad(dec, "d3", d[3], du2)
         du1 = ops.bn_bwd(dg1, u1, n1, j1, d[1].weight.detach(), d[1].bias.detach(), act=ACT_RELU, dgamma=d[1].weight.grad, dbeta=d[1].bias.grad)
-        ops.act_bwd(du1, None, act=ACT_NONE, dbias=d[0].bias.grad, want_g=False)
-        ops.wgrad(dec_in, du1, d[0].weight.grad, ksize=4, stride=2, transposed=True)
+        self._dbias(du1, d[0].bias.grad)
+        self._wgrad(dec_in, du1, d[0].weight.grad, ksize=4, stride=2, transposed=True)
         dz = LDMTrainer._dgrad(dec, "d0", d[0], du1)
         # ---- backward: encoder; the latent also carries 0.01 * KL ----
         gz = ops.kl_grad(z, dz, 0.01 / z.numel())
         dv2 = ops.bn_bwd(gz, v2, m2, i2, e[7].weight.detach(), e[7].bias.detach(), act=ACT_NONE, dgamma=e[7].weight.grad, dbeta=e[7].bias.grad,
                          dv_dtype=adt)
-        ops.act_bwd(dv2, None, act=ACT_NONE, dbias=e[6].bias.grad, want_g=False)
-        ops.wgrad(h1, dv2, e[6].weight.grad, ksize=3, stride=2)
+        self._dbias(dv2, e[6].bias.grad)
+        self._wgrad(h1, dv2, e[6].weight.grad, ksize=3, stride=2)
         dh1 = LDMTrainer._dgrad(enc, "c6", e[6], dv2)
         dv1 = ops.bn_bwd(dh1, v1, m1, i1, e[4].weight.detach(), e[4].bias.detach(), act=ACT_RELU, dgamma=e[4].weight.grad, dbeta=e[4].bias.grad)
-        ops.act_bwd(dv1, None, act=ACT_NONE, dbias=e[3].bias.grad, want_g=False)
-        ops.wgrad(h0, dv1, e[3].weight.grad, ksize=3, stride=2)
+        self._dbias(dv1, e[3].bias.grad)
+        self._wgrad(h0, dv1, e[3].weight.grad, ksize=3, stride=2)
         dh0 = LDMTrainer._dgrad(enc, "c3", e[3], dv1)
         dv0 = ops.bn_bwd(dh0, v0, m0, i0, e[1].weight.detach(), e[1].bias.detach(), act=ACT_RELU, dgamma=e[1].weight.grad, dbeta=e[1].bias.grad)
-        ops.act_bwd(dv0, None, act=ACT_NONE, dbias=e[0].bias.grad, want_g=False)
-        ops.wgrad(xs, dv0, e[0].weight.grad, ksize=3, stride=2)
+        self._dbias(dv0, e[0].bias.grad)
+        self._wgrad(xs, dv0, e[0].weight.grad, ksize=3, stride=2)
 
         # ---- update (torch.optim.AdamW, train.py:47, 81-83) ----
+        self._side_join()
         self.step_count += 1
         self.step_dev.add_(1)
         ops.adam_step(self.arena.p, self.arena.g, self.arena.m, self.arena.v, lr=self.lr, beta1=self.betas[0], beta2=self.betas[1],
