@@ -685,16 +685,30 @@ class LDMTrainer(_SideStream):
         lp = adt == torch.bfloat16
         dev = xs.device
         ab = model.noise_scheduler.alpha_bar_t
+        # the style encoder and the time MLP do not depend on the content path: they run on the side stream beside the
+        # encoder, q-sample and the first two UNet layers, and join where the time embedding is added
+        l1, l2 = u.time_mlp[1], u.time_mlp[3]
+        side = self._side_begin()
+        if side is not None:
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(side), ops.workspace_slot(1):                 # own split-K scratch: the branches run concurrently
+                S = sty._forward_nhwc(ss)                                        # six post-ReLU maps
+                temb, te_e, te_pre, te_h = ops.time_embed_train(t.to(torch.float32), l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach())
+            for tt in list(S) + [temb, te_e, te_pre, te_h]:
+                tt.record_stream(main)
+            ss.record_stream(side)
         z0 = model.encoder._forward_nhwc(xs)                                     # frozen; BatchNorm in train mode (train.py:212)
         _, h, w, c = z0.shape
-        S = sty._forward_nhwc(ss)                                                # six post-ReLU maps
+        if side is None:
+            S = sty._forward_nhwc(ss)
         noise_l = ops.nchw_to_nhwc(noise.to(dev).float().contiguous(), torch.float32)
         z_t, z_t_lp = ops.q_sample(z0, noise_l, ab, t, lp=lp)
         zin = z_t_lp if lp else z_t
-        l1, l2 = u.time_mlp[1], u.time_mlp[3]
-        temb, te_e, te_pre, te_h = ops.time_embed_train(t.to(torch.float32), l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach())
+        if side is None:
+            temb, te_e, te_pre, te_h = ops.time_embed_train(t.to(torch.float32), l1.weight.detach(), l1.bias.detach(), l2.weight.detach(), l2.bias.detach())
         z1 = u._conv("enc1", zin, act=ACT_RELU)
         r2 = u._conv("enc2", z1, act=ACT_RELU)
+        self._side_join()
         z2 = ops.add_bcast(r2, add_nc=temb)
         z3 = u._conv("enc3", z2, act=ACT_RELU)
         a3, sv2 = self._attn_fwd(u.cross_attention2, z3, S[4])

@@ -189,3 +189,29 @@ def test_adam_matches_torch():
         ref.grad = gr.clone(); opt.step()
         ops.adam_step(p, gr.to(DEV), m, v, lr=5e-4, beta1=0.9, beta2=0.999, eps=1e-8, step=i + 1)
     assert_close(p, ref.detach(), 1e-6, "adam params after 5 steps")
+
+
+def test_pack_multi_matches_the_single_packs():
+    """ops.PackPlan (one launch for every packed copy) against pack_weight / pack_weight_dgrad, all three modes, ragged tiles"""
+    from music_style_transfer_ldm_b200 import ops
+    g = torch.Generator().manual_seed(9)
+    ws = {"conv": torch.randn((70, 33, 3, 3), generator=g).cuda(), "lin": torch.randn((130, 96), generator=g).cuda(),
+          "convt": torch.randn((40, 65, 4, 4), generator=g).cuda(), "dg": torch.randn((64, 48, 3, 3), generator=g).cuda(),
+          "k1": torch.randn((256, 512, 1, 1), generator=g).cuda()}
+    ops.PACK_RECORDER = []
+    try:
+        outs = [ops.pack_weight(ws["conv"], torch.bfloat16), ops.pack_weight(ws["lin"], torch.float32),
+                ops.pack_weight(ws["convt"], torch.bfloat16, transposed=True), ops.pack_weight_dgrad(ws["dg"], torch.bfloat16),
+                ops.pack_weight(ws["k1"], torch.bfloat16), ops.pack_weight_dgrad(ws["lin"], torch.float32)]
+        rec = ops.PACK_RECORDER
+    finally:
+        ops.PACK_RECORDER = None
+    assert len(rec) == len(outs)
+    want = [o.clone() for o in outs]
+    for o in outs:
+        o.zero_()
+    plan = ops.PackPlan(rec)
+    plan.run()
+    torch.cuda.synchronize()
+    for o, w_ in zip(outs, want):
+        assert torch.equal(o, w_)
