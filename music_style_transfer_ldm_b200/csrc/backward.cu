@@ -718,50 +718,40 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ src, void* dst, int 
 // own 3-5 us kernel right in front of the convolution that reads it: 52 launches, and a weight prefetch ahead of
 // griddepcontrol.wait that relied on the pack kernel's exit).  Table in device memory; block b serves the entry whose
 // [first_block, first_block + blocks) range holds it, PACK_PER_BLOCK elements each.
-// A block owns a 32 x 32 tile of the two channel dimensions of one entry with all its taps: the source rows
-// [a][b0..b0+31][kk] are contiguous runs (coalesced reads into shared memory), the destination rows 32 consecutive
-// channels of the fastest dimension (64 / 128-byte runs).  (The first form walked the destination linearly: two 64-bit
-// divisions per element and reads strided by kk floats -- 96 us per step for the 14.5 M packed elements.)
-constexpr int PACK_T = 32;
+constexpr int PACK_PER_BLOCK = 2048;
 __global__ void __launch_bounds__(256) pack_multi_kernel(const mstk_pack_entry* __restrict__ tab, int n) {
-    extern __shared__ float ptile[];                 // [32][32 * kk + 1]
     __shared__ int s_e;
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {
+        // entry of this block = the last one whose first_block <= blockIdx.x: one coalesced probe of the table per 32 entries
+        // (a serial scan by one thread was ~25 dependent global loads per block)
         int e = 0;
-        while (e + 1 < n && (int)blockIdx.x >= tab[e + 1].first_block) ++e;
-        s_e = e;
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + (int)threadIdx.x;
+            const bool le = i < n && tab[i].first_block <= (int)blockIdx.x;
+            e += __popc(__ballot_sync(0xffffffffu, le));
+        }
+        if (threadIdx.x == 0) s_e = e - 1;
     }
     __syncthreads();
     const mstk_pack_entry t = tab[s_e];
-    const int kk = t.kk;
-    // source dims [NA][NB][kk]: (cout, cin) for conv / dgrad packs, (cin, cout) for conv-transpose
-    const int NA = t.mode == 1 ? t.cin : t.cout, NB = t.mode == 1 ? t.cout : t.cin;
-    const int tiles_b = (NB + PACK_T - 1) / PACK_T;
-    const int blk = (int)blockIdx.x - t.first_block;
-    const int a0 = (blk / tiles_b) * PACK_T, b0 = (blk % tiles_b) * PACK_T;
-    const int na = min(PACK_T, NA - a0), nbv = min(PACK_T, NB - b0);
-    const int row = PACK_T * kk + 1;
+    const uint32_t total = (uint32_t)t.kk * (uint32_t)t.cout * (uint32_t)t.cin;
+    const uint32_t i0 = (uint32_t)((int)blockIdx.x - t.first_block) * PACK_PER_BLOCK;
+    const uint32_t i1 = i0 + PACK_PER_BLOCK < total ? i0 + PACK_PER_BLOCK : total;
     const float* __restrict__ src = t.src;
-    for (int ar = 0; ar < na; ++ar) {
-        const float* sr = src + ((size_t)(a0 + ar) * NB + b0) * kk;
-        for (int i = threadIdx.x; i < nbv * kk; i += 256) ptile[ar * row + i] = sr[i];
-    }
-    __syncthreads();
-    // destination [kk][cout][cin] (modes 0, 1) or [kk][cin][cout] with flipped taps (mode 2); fastest index f, middle index m
-    //   mode 0: f = cin = b, m = cout = a;  mode 1: f = cin = a, m = cout = b;  mode 2: f = cout = a, m = cin = b
-    const bool f_is_a = t.mode != 0;
-    const int nf = f_is_a ? na : nbv, nm = f_is_a ? nbv : na;
-    const int f0 = f_is_a ? a0 : b0, m0 = f_is_a ? b0 : a0;
-    const int NF = t.mode == 2 ? t.cout : t.cin, NM = t.mode == 2 ? t.cin : t.cout;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int r = w; r < kk * nm; r += 8) {            // one warp per destination row (tap, middle index)
-        const int sl = r / nm, mi = r - sl * nm;
-        if (lane < nf) {
-            const int ai = f_is_a ? lane : mi, bi = f_is_a ? mi : lane;
-            const float v = ptile[ai * row + bi * kk + sl];
-            const int ds = t.mode == 2 ? kk - 1 - sl : sl;
-            store_from_f(t.dst, t.dtype, ((size_t)ds * NM + (m0 + mi)) * NF + f0 + lane, v);
+    const uint32_t kk = (uint32_t)t.kk, cin = (uint32_t)t.cin, cout = (uint32_t)t.cout;
+#pragma unroll 4
+    for (uint32_t i = i0 + threadIdx.x; i < i1; i += 256) {
+        uint32_t si;
+        if (t.mode == 2) {              // dgrad: dst [kk][cin][cout], taps flipped
+            const uint32_t co = i % cout, r = i / cout;
+            const uint32_t ci = r % cin, sl = r / cin;
+            si = (co * cin + ci) * kk + (kk - 1 - sl);
+        } else {                        // dst [kk][cout][cin]; src [cout][cin][kk] (0) or [cin][cout][kk] (1)
+            const uint32_t ci = i % cin, r = i / cin;
+            const uint32_t co = r % cout, sl = r / cout;
+            si = t.mode == 1 ? (ci * cout + co) * kk + sl : (co * cin + ci) * kk + sl;
         }
+        store_from_f(t.dst, t.dtype, i, __ldg(src + si));
     }
 }
 
@@ -1026,20 +1016,13 @@ int mstk_pack_conv_weight_dgrad(const float* w, void* dst, int cout, int cin, in
 }
 
 int mstk_pack_blocks(int cout, int cin, int kk) {
-    if (cout <= 0 || cin <= 0 || kk <= 0 || kk > 16) return 0;
-    return ((cout + PACK_T - 1) / PACK_T) * ((cin + PACK_T - 1) / PACK_T);
+    if (cout <= 0 || cin <= 0 || kk <= 0 || (long long)kk * cout * cin >= (1ll << 31)) return 0;
+    return (int)(((size_t)kk * cout * cin + PACK_PER_BLOCK - 1) / PACK_PER_BLOCK);
 }
 
 int mstk_pack_multi(const mstk_pack_entry* entries_dev, int n_entries, int total_blocks, void* stream) {
     MSTK_REQUIRE(entries_dev && n_entries > 0 && total_blocks > 0, "pack_multi: bad args");
-    const size_t smem = (size_t)PACK_T * (PACK_T * 16 + 1) * sizeof(float);          // kk <= 16
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pack_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return cuda_fail(e, "pack_multi smem attr");
-        attr_set = true;
-    }
-    pack_multi_kernel<<<(unsigned)total_blocks, 256, smem, (cudaStream_t)stream>>>(entries_dev, n_entries);
+    pack_multi_kernel<<<(unsigned)total_blocks, 256, 0, (cudaStream_t)stream>>>(entries_dev, n_entries);
     MSTK_CHECK_LAUNCH("pack_multi");
     return MSTK_OK;
 }

@@ -484,7 +484,7 @@ _scratch = {}
 
 
 def _loss_scratch(device, n_doubles: int) -> torch.Tensor:
-    key = (torch.device(device).index or 0, n_doubles)
+    key = (torch.device(device).index or 0, n_doubles, _WS_SLOT)        # concurrent branches (workspace_slot) get their own
     s = _scratch.get(key)
     if s is None:
         s = torch.zeros(n_doubles, dtype=torch.float64, device=device)

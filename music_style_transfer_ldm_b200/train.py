@@ -641,9 +641,21 @@ class LDMTrainer(_SideStream):
          r_d2, d2, eps_hat, dec_in, v1, h1, mean1, inv1, v2, h2, mean2, inv2, rec, t, adt, ab) = sv
 
         # ================= losses (train.py:182-186) =================
-        den = ops.mse(eps_hat, noise_l).squeeze(0)
-        mse_rec = ops.mse(rec, xs).squeeze(0)
-        kl = ops.kl(z0).squeeze(0)
+        side = self._side_begin()                   # three small reductions: beside the feature stack, joined before the sums
+        if side is not None:
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(side), ops.workspace_slot(1):
+                den = ops.mse(eps_hat, noise_l).squeeze(0)
+                mse_rec = ops.mse(rec, xs).squeeze(0)
+                kl = ops.kl(z0).squeeze(0)
+            for tt in (den, mse_rec, kl):
+                tt.record_stream(main)
+            for tt in (eps_hat, noise_l, rec, xs, z0):
+                tt.record_stream(side)
+        else:
+            den = ops.mse(eps_hat, noise_l).squeeze(0)
+            mse_rec = ops.mse(rec, xs).squeeze(0)
+            kl = ops.kl(z0).squeeze(0)
         fl = model.feature_loss_net
         H, W = xs.shape[1], xs.shape[2]
         three = torch.empty((3 * B, H, W, 1), dtype=torch.float32, device=dev)
@@ -653,6 +665,7 @@ class LDMTrainer(_SideStream):
         # one pass of the frozen stack for all three images; perc: compression_loss's perceptual term (loss.py:40),
         # styl: style_loss (loss.py:104-106); each tap = one conv + one fused streaming kernel
         fl._loss3(three, B, perc, styl)
+        self._side_join()
         comp = mse_rec + 0.1 * perc.squeeze(0) + 0.01 * kl
         total = comp + den + self.style_loss_weight * styl.squeeze(0)
 
