@@ -44,8 +44,14 @@ struct HaloParams {
     uint32_t inv_nblocks, inv_bw, inv_bwh;
     int32_t dbg;                       // development: 1 = no output stores, 2 = no TMEM reads either
     // conv-transpose k4 s2 (CONVT kernel): 16 (phase, tap) operations per channel block, all on the SAME 18 x 18 halo box
-    int16_t op_aoff[16];               // halo row of the operation's A start: (dy + 1) * (halo width) + (dx + 1)
-    int16_t op_slice[16];              // weight slice ky * 4 + kx
+    // Four rounds of four 8 KB weight boxes per channel block (op_slice[round * 4 + slot]); parities that read the SAME input offset
+    // sit in adjacent boxes and adjacent accumulator columns ([P00 | P01 | P11 | P10]), so one MMA serves them together:
+    // 10 operations per channel block (1 x N = 256, 3 x N = 128, 6 x N = 64) instead of 16 of N = 64 -- the kernel was bound by
+    // the MMA issue rate (~110 cycles per MMA whatever its N).
+    int16_t op_slice[16];              // weight slice ky * 4 + kx of box (round, slot)
+    int16_t t_aoff[10];                // halo row of the operation's A start: (dy + 1) * (halo width) + (dx + 1)
+    int8_t t_slot[10], t_nsel[10], t_dcol[10];   // first box of the round, N = 64 << nsel, first accumulator column / 64
+    int8_t t_first[5];                 // operations of round r: [t_first[r], t_first[r + 1])
     uint32_t off_stg;                  // byte offset of the epilogue warps' staging tiles
 };
 
@@ -156,6 +162,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         const uint32_t idesc = keep_reg(make_idesc(BN));
+        const uint32_t idesc_n[3] = {make_idesc(64), make_idesc(128), make_idesc(256)};
         const uint32_t a_full0 = keep_reg(smem_u32(&sh.a_full[0])), a_empty0 = keep_reg(smem_u32(&sh.a_empty[0]));
         const uint32_t b_full0 = keep_reg(smem_u32(&sh.b_full[0])), b_empty0 = keep_reg(smem_u32(&sh.b_empty[0]));
         const uint32_t acc_full0 = keep_reg(smem_u32(&sh.acc_full[0])), acc_empty0 = keep_reg(smem_u32(&sh.acc_empty[0]));
@@ -181,18 +188,23 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     tc_fence_after();
                     const int cnt = min(G, NOPS - r * G);
                     if (elect_one()) {
-                        for (int g = 0; g < cnt; ++g) {
-                            const int op = r * G + g;
-                            uint32_t aoff, dcol;
-                            if (CONVT) {
-                                aoff = (uint32_t)q.op_aoff[op];
-                                dcol = (uint32_t)(op >> 2) * 64u;                                  // parity's accumulator
-                                if (kb == 0 && (op & 3) == 0) accf = 0u;                            // its first operation
-                            } else {
-                                const int dy = op / 3, dx = op - dy * 3;
-                                aoff = (uint32_t)(dy * HW + dx);
-                                dcol = 0u;
+                        if (CONVT) {
+                            // round 0 is the one N = 256 operation on the centre offset: it opens all four parity accumulators
+                            for (int o = q.t_first[r]; o < q.t_first[r + 1]; ++o) {
+                                const uint32_t at = a_lo + (uint32_t)q.t_aoff[o] * 8u;
+                                const uint32_t bt = b_lo0 + (uint32_t)(s * G + q.t_slot[o]) * (B_BYTES >> 4);
+                                const uint32_t dcol = (uint32_t)q.t_dcol[o] * 64u, ide = idesc_n[q.t_nsel[o]];
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    umma_bf16(d0 + dcol, ((uint64_t)ahi << 32) | (at + 2u * k), ((uint64_t)bhi << 32) | (bt + 2u * k), ide, accf);
+                                    accf = 1u;
+                                }
                             }
+                        }
+                        for (int g = 0; g < (CONVT ? 0 : cnt); ++g) {
+                            const int op = r * G + g;
+                            const int dy = op / 3, dx = op - dy * 3;
+                            const uint32_t aoff = (uint32_t)(dy * HW + dx), dcol = 0u;
                             const uint32_t at = a_lo + aoff * 8u;                                   // 128 B per halo row = 8 units of 16 B
                             const uint32_t bt = b_lo0 + (uint32_t)(s * G + g) * (B_BYTES >> 4);
 #pragma unroll
@@ -245,8 +257,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll 1
             for (int pair = 0; pair < NPAIR; ++pair) {
                 const uint32_t col0 = (uint32_t)buf * (uint32_t)(TILES * TILE_COLS);
-                const uint32_t col_a = col0 + (CONVT ? (uint32_t)(pair * 256 + half * 128) : (uint32_t)(half * 64));
-                const uint32_t col_b = col_a + (CONVT ? 64u : 128u);
+                // conv-transpose accumulator columns: [P00 | P01 | P11 | P10] (row parity = half, column parity = pair member)
+                const uint32_t col_a = col0 + (CONVT ? (uint32_t)(pair * 256 + (half ? 192 : 0)) : (uint32_t)(half * 64));
+                const uint32_t col_b = CONVT ? col0 + (uint32_t)(pair * 256 + (half ? 128 : 64)) : col_a + 128u;
                 const uint32_t tlane = tmem_base + ((uint32_t)(qd * 32) << 16);
                 float va[64], vb[64];
                 if (!(q.dbg & 2)) {
@@ -419,18 +432,46 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     q.nblocks = convt ? 1 : p.Cout / CH_BN;
     q.nitems = p.N * q.blocks_w * q.blocks_h * q.nblocks;
     q.KB = p.Cin / 64;
-    q.G = convt ? 4 : g_halo_g; q.S = convt ? 4 : g_halo_s; q.dbg = g_halo_dbg;      // conv-transpose: 8 KB boxes, 4 per stage, 4 stages
+    // conv-transpose: 8 KB boxes; 8 per stage (two rounds of the box table = 20 MMAs per issuer round trip), 2 stages
+    static int ct_g = 0;
+    if (!ct_g) { const char* e = getenv("MSTK_HALO_CTG"); ct_g = e ? atoi(e) : 8; if (ct_g != 4 && ct_g != 8 && ct_g != 16) ct_g = 8; }
+    q.G = convt ? ct_g : g_halo_g; q.S = convt ? 16 / ct_g : g_halo_s; q.dbg = g_halo_dbg;
     q.act = p.act; q.affine = p.affine; q.out_f32 = p.out_dtype == MSTK_F32 ? 1 : 0;
     q.out_scale = p.out_scale; q.out_shift = p.out_shift;
     int nslices = 9;
     if (convt) {
         nslices = 16;
-        for (int ph = 0; ph < 4; ++ph)
+        int slice_of[4][3][3];                           // [parity py * 2 + px][dy + 1][dx + 1] -> weight slice, -1 = not a tap
+        for (int ph = 0; ph < 4; ++ph) {
+            for (int i = 0; i < 9; ++i) slice_of[ph][i / 3][i % 3] = -1;
             for (int t = 0; t < 4; ++t) {
                 const Tap& tp = p.ph[ph].taps[t];
-                q.op_aoff[ph * 4 + t] = (int16_t)((tp.dy + 1) * hw + (tp.dx + 1));
-                q.op_slice[ph * 4 + t] = (int16_t)tp.slice;
+                slice_of[ph][tp.dy + 1][tp.dx + 1] = tp.slice;
             }
+        }
+        // boxes of the four rounds: {parity, dy, dx}; accumulator column order P00, P01, P11, P10 = parities 0, 1, 3, 2
+        static const int box[16][3] = {{0, 0, 0}, {1, 0, 0}, {3, 0, 0}, {2, 0, 0},          // round 0: centre, all four
+                                       {0, -1, 0}, {1, -1, 0}, {1, 0, 1}, {3, 0, 1},        // round 1: row above (py = 0), column right (px = 1)
+                                       {3, 1, 0}, {2, 1, 0}, {0, 0, -1}, {2, 0, -1},        // round 2: row below (py = 1), column left (px = 0)
+                                       {0, -1, -1}, {1, -1, 1}, {3, 1, 1}, {2, 1, -1}};     // round 3: the four corners
+        for (int i = 0; i < 16; ++i) {
+            const int sl = slice_of[box[i][0]][box[i][1] + 1][box[i][2] + 1];
+            MSTK_REQUIRE(sl >= 0, "conv(halo): conv-transpose plan does not have the k4 s2 p1 tap structure");
+            q.op_slice[i] = (int16_t)sl;
+        }
+        // operations: {round, first box, nsel, first column / 64, dy, dx}
+        static const int ops[10][6] = {{0, 0, 2, 0, 0, 0},
+                                       {1, 0, 1, 0, -1, 0}, {1, 2, 1, 1, 0, 1},
+                                       {2, 0, 1, 2, 1, 0}, {2, 2, 0, 0, 0, -1}, {2, 3, 0, 3, 0, -1},
+                                       {3, 0, 0, 0, -1, -1}, {3, 1, 0, 1, -1, 1}, {3, 2, 0, 2, 1, 1}, {3, 3, 0, 3, 1, -1}};
+        // a stage holds G / 4 rounds of the box table: the issuer's round = those rounds' operations
+        const int rps = q.G / 4;
+        for (int r = 0; r <= 4; ++r) q.t_first[r] = 10;
+        for (int o = 9; o >= 0; --o) {
+            q.t_slot[o] = (int8_t)(ops[o][1] + 4 * (ops[o][0] % rps)); q.t_nsel[o] = (int8_t)ops[o][2]; q.t_dcol[o] = (int8_t)ops[o][3];
+            q.t_aoff[o] = (int16_t)((ops[o][4] + 1) * hw + (ops[o][5] + 1));
+            q.t_first[ops[o][0] / rps] = (int8_t)o;
+        }
     }
     auto inv = [](int d) -> uint32_t { return d <= 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); };
     q.inv_nblocks = inv(q.nblocks); q.inv_bw = inv(q.blocks_w); q.inv_bwh = inv(q.blocks_w * q.blocks_h);
@@ -474,7 +515,7 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     const size_t a_stage = ((size_t)hw * CH_HH * 128 + 1023) & ~(size_t)1023;
     q.off_stg = (uint32_t)(2 * a_stage + (size_t)q.G * q.S * bn * 128);
     const size_t smem = (size_t)q.off_stg + 8 * 4096 + 1024;
-    MSTK_REQUIRE(smem <= 224 * 1024 && q.S <= CH_MAX_SUB, "conv(halo): shared-memory budget");
+    MSTK_REQUIRE(smem <= 224 * 1024 && q.S <= CH_MAX_SUB && q.S >= 1, "conv(halo): shared-memory budget");
     if (!g_halo_attr) {
         cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
         if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
