@@ -370,7 +370,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
-static int g_halo = -1, g_halo_g = 3, g_halo_s = 2, g_halo_dbg = 0;
+static int g_halo = -1, g_halo_g = 3, g_halo_s = 2, g_halo_dbg = 0, g_halo_min = 2;   // g_halo_min: items per SM from which the kernel is taken (never slower than conv_tc from 1; tools/halo_tune.py 96)
 static bool g_halo_attr = false;
 static long long g_halo_count[3] = {0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
 
@@ -379,6 +379,7 @@ static void halo_env() {
     g_halo = 1;
     if (const char* s = getenv("MSTK_CONV_HALO")) g_halo = atoi(s);
     if (const char* s = getenv("MSTK_HALO_DBG")) g_halo_dbg = atoi(s);
+    if (const char* s = getenv("MSTK_HALO_MIN")) g_halo_min = atoi(s) > 0 ? atoi(s) : 2;
     if (const char* s = getenv("MSTK_HALO_GS")) sscanf(s, "%d,%d", &g_halo_g, &g_halo_s);
     if (g_halo_g < 1 || g_halo_s < 2 || g_halo_g * g_halo_s > CH_MAX_SUB) { g_halo_g = 3; g_halo_s = 2; }
 }
@@ -399,8 +400,8 @@ static int halo_kind(const ConvP& p) {
             if (tp.dy != t / 3 - 1 || tp.dx != t % 3 - 1 || tp.slice != t) return 0;
         }
         const long long items = blocks * (p.Cout / CH_BN);
-        // throughput-bound grids only: several items per SM, otherwise the one-tile kernel's finer grid wins
-        return (items >= 4ll * tc_num_sms() && items < 0x7fffffffll) ? 1 : 0;
+        // throughput-bound grids only (at least g_halo_min items per SM)
+        return (items >= (long long)g_halo_min * tc_num_sms() && items < 0x7fffffffll) ? 1 : 0;
     }
     if (p.nphases == 4 && p.s_out == 2 && p.Cout == 64 && p.out_dtype == MSTK_BF16 && !(g_halo & 2)) {
         for (int ph = 0; ph < 4; ++ph) {

@@ -13,7 +13,7 @@ from gpu_util import assert_close, conv_ref, gen, nchw, nhwc
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
-# n, h, w, cin, cout: all take the halo kernel (>= 4 x 148 items of a 16 x 16 pixel block x 128 output channels)
+# n, h, w, cin, cout: all take the halo kernel (>= 2 x 148 items of a 16 x 16 pixel block x 128 output channels)
 CASES = [
     (160, 16, 16, 64, 512),      # one block per image, 4 output blocks, single channel block
     (40, 32, 64, 128, 256),      # non-square image, 2 channel blocks

@@ -5,7 +5,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from music_style_transfer_ldm_b200 import ops
 
-LAYERS = [(768, 64, 64, 64, 128), (768, 32, 32, 128, 256), (768, 32, 32, 256, 256), (768, 16, 16, 256, 512), (768, 16, 16, 512, 512)]
+NIMG = int(sys.argv[1]) if len(sys.argv) > 1 else 768
+LAYERS = [(NIMG, 64, 64, 64, 128), (NIMG, 32, 32, 128, 256), (NIMG, 32, 32, 256, 256), (NIMG, 16, 16, 256, 512), (NIMG, 16, 16, 512, 512)]
 tot = 0.0
 for n, h, w, cin, cout in LAYERS:
     x = torch.randn((n, h, w, cin), device="cuda").bfloat16()
