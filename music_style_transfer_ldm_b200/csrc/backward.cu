@@ -292,9 +292,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdP a) {
     for (int i = threadIdx.x; i < 2 * a.c; i += blockDim.x) sm[i] = 0.f;
     __syncthreads();
     const size_t nvec = ((size_t)a.rows * a.c) >> 3;
-    float p0[8], p1[8];
+    float p0[8], p1[8], pm[8], pis[8], pg[8], pb[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { p0[k] = 0.f; p1[k] = 0.f; }
+    for (int k = 0; k < 8; ++k) { p0[k] = 0.f; p1[k] = 0.f; pm[k] = 0.f; pis[k] = 0.f; pg[k] = 0.f; pb[k] = 0.f; }
     int ch_prev = -1;
     ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
@@ -303,15 +303,21 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdP a) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) { atomicAdd(&s0[ch_prev + k], p0[k]); atomicAdd(&s1[ch_prev + k], p1[k]); p0[k] = 0.f; p1[k] = 0.f; }
         }
+        if (ch != ch_prev) {
+            // per-channel parameters in registers: the grid stride is a multiple of c whenever c divides 2048 * gridDim, so a
+            // thread normally keeps its 8 channels for the whole pass (the loop did 4 global loads per ELEMENT)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { pm[k] = a.mean[ch + k]; pis[k] = a.invstd[ch + k]; pg[k] = a.gamma[ch + k]; pb[k] = a.beta[ch + k]; }
+        }
         ch_prev = ch;
         float d[8], v[8];
         load8_rt(a.dy, a.dy_dtype, i, d);
         load8_rt(a.v, a.v_dtype, i, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float xh = (v[k] - a.mean[ch + k]) * a.invstd[ch + k];
+            const float xh = (v[k] - pm[k]) * pis[k];
             float g = d[k];
-            if (a.act == MSTK_ACT_RELU && !(a.gamma[ch + k] * xh + a.beta[ch + k] > 0.f)) g = 0.f;
+            if (a.act == MSTK_ACT_RELU && !(pg[k] * xh + pb[k] > 0.f)) g = 0.f;
             p0[k] += g; p1[k] = fmaf(g, xh, p1[k]);
         }
     }
@@ -338,19 +344,28 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdP a) {
     }
     __syncthreads();
     const size_t nvec = ((size_t)a.rows * a.c) >> 3;
+    float pm[8], pis[8], pg[8], pb[8], q0[8], q1[8];
+    int chc = -1;
     ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
         const int ch = cw.ch;
+        if (ch != chc) {                     // this thread's per-channel parameters in registers (normally loaded once)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                pm[k] = a.mean[ch + k]; pis[k] = a.invstd[ch + k]; pg[k] = a.gamma[ch + k]; pb[k] = a.beta[ch + k];
+                q0[k] = m0[ch + k]; q1[k] = m1[ch + k];
+            }
+            chc = ch;
+        }
         float d[8], v[8];
         load8_rt(a.dy, a.dy_dtype, i, d);
         load8_rt(a.v, a.v_dtype, i, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float is = a.invstd[ch + k];
-            const float xh = (v[k] - a.mean[ch + k]) * is;
+            const float xh = (v[k] - pm[k]) * pis[k];
             float g = d[k];
-            if (a.act == MSTK_ACT_RELU && !(a.gamma[ch + k] * xh + a.beta[ch + k] > 0.f)) g = 0.f;
-            d[k] = a.gamma[ch + k] * is * (g - m0[ch + k] - xh * m1[ch + k]);
+            if (a.act == MSTK_ACT_RELU && !(pg[k] * xh + pb[k] > 0.f)) g = 0.f;
+            d[k] = pg[k] * pis[k] * (g - q0[k] - xh * q1[k]);
         }
         store8_rt(a.dv, a.dv_dtype, i, d);
     }
