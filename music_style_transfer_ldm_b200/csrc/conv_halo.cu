@@ -52,6 +52,7 @@ struct HaloParams {
     int16_t t_aoff[10];                // halo row of the operation's A start: (dy + 1) * (halo width) + (dx + 1)
     int8_t t_slot[10], t_nsel[10], t_dcol[10];   // first box of the round, N = 64 << nsel, first accumulator column / 64
     int8_t t_first[5];                 // operations of round r: [t_first[r], t_first[r + 1])
+    int32_t nboxes;                    // 16 (k4) or 9 (k3)
     uint32_t off_stg;                  // byte offset of the epilogue warps' staging tiles
 };
 
@@ -68,14 +69,16 @@ struct HaloShared {
 __device__ __forceinline__ int hdiv(int n, uint32_t inv) { return inv ? (int)__umulhi((uint32_t)n, inv) : n; }
 
 // CONVT = false: 3x3 stride-1 convolution, 9 taps, BN = 128 output channels per item, two accumulator buffers of 2 x 128 columns.
-// CONVT = true : ConvTranspose2d(k4, s2, p1) with Cout = 64: the four output parities are four accumulators per tile
-//                (2 tiles x 4 x 64 = all 512 columns, single-buffered), 16 operations of N = 64 per channel block; each
-//                epilogue warp stores (tile, parity) boxes through the parity's strided output map.
+// CONVT = true : ConvTranspose2d(k4, s2, p1) with Cout = 64, or (k3, s2, p1, output_padding 1) with Cout % 64 == 0 (the data
+//                gradient of the stride-2 convolutions): ONE 16 x 8 tile per item, its four output parities four accumulators
+//                of 64 columns ([P00 | P01 | P11 | P10], double-buffered); parities that read the same input offset share one
+//                MMA (N = 256 / 128 / 64, host-built operation table); each epilogue warp stores (parity) boxes through the
+//                parity's strided output map.
 template <bool CONVT, int TILES, bool STATS>
 __global__ void __launch_bounds__(CH_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ HaloOutMaps maps_o,
                  const __grid_constant__ HaloParams q) {
-    constexpr int NOPS = CONVT ? 16 : 9;
+    const int NOPS = CONVT ? q.nboxes : 9;                  // weight boxes per channel block
     constexpr int BN = CONVT ? 64 : 128;                    // MMA N
     constexpr uint32_t B_BYTES = (uint32_t)BN * 128u;       // one operation's weight box
     constexpr uint32_t TILE_COLS = CONVT ? 256u : 128u;     // TMEM columns of one tile's accumulator(s)
@@ -244,7 +247,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const int n = hdiv(blk, q.inv_bwh);
             const int rem = blk - n * (q.blocks_w * q.blocks_h);
             const int bh = hdiv(rem, q.inv_bw), bw = rem - bh * q.blocks_w;
-            const int co0 = CONVT ? 0 : nb * BN + half * 64;
+            const int co0 = CONVT ? nb * 64 : nb * BN + half * 64;
             const float* bias = q.bias ? q.bias + co0 : nullptr;
             mbar_wait(&sh.acc_full[buf], (uint32_t)(use & 1));
             tc_fence_after();
@@ -372,7 +375,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // ---------------------------------------------------------------------------
 static int g_halo = -1, g_halo_g = 3, g_halo_s = 2, g_halo_dbg = 0, g_halo_min = 2;   // g_halo_min: items per SM from which the kernel is taken (never slower than conv_tc from 1; tools/halo_tune.py 96)
 static bool g_halo_attr = false;
-static long long g_halo_count[3] = {0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
+static long long g_halo_count[4] = {0, 0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
 
 static void halo_env() {
     if (g_halo >= 0) return;
@@ -403,15 +406,28 @@ static int halo_kind(const ConvP& p) {
         // throughput-bound grids only (at least g_halo_min items per SM)
         return (items >= (long long)g_halo_min * tc_num_sms() && items < 0x7fffffffll) ? 1 : 0;
     }
-    if (p.nphases == 4 && p.s_out == 2 && p.Cout == 64 && p.out_dtype == MSTK_BF16 && !(g_halo & 2)) {
+    if (p.nphases == 4 && p.s_out == 2 && p.Cout % 64 == 0 && p.out_dtype == MSTK_BF16 && !(g_halo & 2)) {
+        // conv-transpose: k4 s2 p1 (four taps per output parity, offsets -1..1) or k3 s2 p1 op1 (1 / 2 / 2 / 4 taps, offsets 0..1:
+        // the data gradient of the stride-2 convolutions)
+        int ntaps = 0;
+        bool k3 = true, k4 = true;
         for (int ph = 0; ph < 4; ++ph) {
-            if (p.ph[ph].ntaps != 4 || p.ph[ph].oy != (ph >> 1) || p.ph[ph].ox != (ph & 1)) return 0;
-            for (int t = 0; t < 4; ++t) {
+            if (p.ph[ph].oy != (ph >> 1) || p.ph[ph].ox != (ph & 1)) return 0;
+            const int py = ph >> 1, px = ph & 1;
+            if (p.ph[ph].ntaps != 4) k4 = false;
+            if (p.ph[ph].ntaps != (1 + py) * (1 + px)) k3 = false;
+            ntaps += p.ph[ph].ntaps;
+            for (int t = 0; t < p.ph[ph].ntaps; ++t) {
                 const Tap& tp = p.ph[ph].taps[t];
                 if (tp.dy < -1 || tp.dy > 1 || tp.dx < -1 || tp.dx > 1 || tp.slice < 0 || tp.slice >= 16) return 0;
+                if (tp.dy < 0 || tp.dx < 0 || tp.dy > py || tp.dx > px) k3 = false;
             }
         }
-        return (2 * blocks >= 4ll * tc_num_sms() && blocks < 0x3fffffffll) ? 2 : 0;     // items are 16 x 8 pixel tiles
+        const long long items = 2 * blocks * (p.Cout / 64);                             // 16 x 8 pixel tiles x 64-channel blocks
+        if (items < (long long)g_halo_min * tc_num_sms() || items >= 0x7fffffffll) return 0;
+        if (k4 && ntaps == 16 && p.Cout == 64) return 2;
+        if (k3 && ntaps == 9 && !p.stats) return 3;
+        return 0;
     }
     return 0;
 }
@@ -422,7 +438,7 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     if (!tc_init()) return MSTK_EUNSUPPORTED;
     const int kind = halo_kind(p);
     if (!kind) return MSTK_EUNSUPPORTED;
-    const bool convt = kind == 2;
+    const bool convt = kind >= 2, k3 = kind == 3;
     const int bn = convt ? 64 : CH_BN;
     HaloParams q;
     memset(&q, 0, sizeof(q));
@@ -430,26 +446,29 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     q.N = p.N; q.H = p.H; q.W = p.W; q.Cin = p.Cin; q.Cout = p.Cout;
     const int tiles = convt ? 1 : 2, hw = 8 * tiles + 2;
     q.blocks_w = p.W / (8 * tiles); q.blocks_h = p.H / CH_BH;
-    q.nblocks = convt ? 1 : p.Cout / CH_BN;
+    q.nblocks = convt ? p.Cout / 64 : p.Cout / CH_BN;
     q.nitems = p.N * q.blocks_w * q.blocks_h * q.nblocks;
     q.KB = p.Cin / 64;
-    // conv-transpose: 8 KB boxes; 8 per stage (two rounds of the box table = 20 MMAs per issuer round trip), 2 stages
+    // conv-transpose: 8 KB boxes.  k4: 8 per stage (two rounds of the box table = 20 MMAs per issuer round trip), 2 stages.
+    // k3: 5 per stage (rounds of 5 and 4 boxes), 3 stages.
     static int ct_g = 0;
     if (!ct_g) { const char* e = getenv("MSTK_HALO_CTG"); ct_g = e ? atoi(e) : 8; if (ct_g != 4 && ct_g != 8 && ct_g != 16) ct_g = 8; }
-    q.G = convt ? ct_g : g_halo_g; q.S = convt ? 16 / ct_g : g_halo_s; q.dbg = g_halo_dbg;
+    q.G = !convt ? g_halo_g : k3 ? 5 : ct_g; q.S = !convt ? g_halo_s : k3 ? 3 : 16 / ct_g; q.dbg = g_halo_dbg;
+    q.nboxes = k3 ? 9 : 16;
     q.act = p.act; q.affine = p.affine; q.out_f32 = p.out_dtype == MSTK_F32 ? 1 : 0;
     q.out_scale = p.out_scale; q.out_shift = p.out_shift;
     int nslices = 9;
     if (convt) {
-        nslices = 16;
+        nslices = k3 ? 9 : 16;
         int slice_of[4][3][3];                           // [parity py * 2 + px][dy + 1][dx + 1] -> weight slice, -1 = not a tap
         for (int ph = 0; ph < 4; ++ph) {
             for (int i = 0; i < 9; ++i) slice_of[ph][i / 3][i % 3] = -1;
-            for (int t = 0; t < 4; ++t) {
+            for (int t = 0; t < p.ph[ph].ntaps; ++t) {
                 const Tap& tp = p.ph[ph].taps[t];
                 slice_of[ph][tp.dy + 1][tp.dx + 1] = tp.slice;
             }
         }
+        if (!k3) {
         // boxes of the four rounds: {parity, dy, dx}; accumulator column order P00, P01, P11, P10 = parities 0, 1, 3, 2
         static const int box[16][3] = {{0, 0, 0}, {1, 0, 0}, {3, 0, 0}, {2, 0, 0},          // round 0: centre, all four
                                        {0, -1, 0}, {1, -1, 0}, {1, 0, 1}, {3, 0, 1},        // round 1: row above (py = 0), column right (px = 1)
@@ -472,6 +491,24 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
             q.t_slot[o] = (int8_t)(ops[o][1] + 4 * (ops[o][0] % rps)); q.t_nsel[o] = (int8_t)ops[o][2]; q.t_dcol[o] = (int8_t)ops[o][3];
             q.t_aoff[o] = (int16_t)((ops[o][4] + 1) * hw + (ops[o][5] + 1));
             q.t_first[ops[o][0] / rps] = (int8_t)o;
+        }
+        } else {
+            // k3 s2 p1 op1: offsets 0..1.  Round 0 (5 boxes): the centre offset for all four parities (one N = 256 operation) and
+            // the (+1, +1) corner of P11; round 1 (4 boxes): (0, +1) for P01 | P11 and (+1, 0) for P11 | P10 (N = 128 each).
+            static const int box3[9][3] = {{0, 0, 0}, {1, 0, 0}, {3, 0, 0}, {2, 0, 0}, {3, 1, 1}, {1, 0, 1}, {3, 0, 1}, {3, 1, 0}, {2, 1, 0}};
+            for (int i = 0; i < 9; ++i) {
+                const int sl = slice_of[box3[i][0]][box3[i][1] + 1][box3[i][2] + 1];
+                MSTK_REQUIRE(sl >= 0, "conv(halo): conv-transpose plan does not have the k3 s2 p1 op1 tap structure");
+                q.op_slice[i] = (int16_t)sl;
+            }
+            // {round, first box of the round, nsel, first column / 64, dy, dx}
+            static const int ops3[4][6] = {{0, 0, 2, 0, 0, 0}, {0, 4, 0, 2, 1, 1}, {1, 0, 1, 1, 0, 1}, {1, 2, 1, 2, 1, 0}};
+            for (int r = 0; r <= 4; ++r) q.t_first[r] = 4;
+            for (int o = 3; o >= 0; --o) {
+                q.t_slot[o] = (int8_t)ops3[o][1]; q.t_nsel[o] = (int8_t)ops3[o][2]; q.t_dcol[o] = (int8_t)ops3[o][3];
+                q.t_aoff[o] = (int16_t)((ops3[o][4] + 1) * hw + (ops3[o][5] + 1));
+                q.t_first[ops3[o][0]] = (int8_t)o;
+            }
         }
     }
     auto inv = [](int d) -> uint32_t { return d <= 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); };
@@ -544,7 +581,7 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     return MSTK_OK;
 }
 
-long long halo_count(int kind) { return kind >= 1 && kind <= 2 ? g_halo_count[kind] : 0; }
+long long halo_count(int kind) { return kind >= 1 && kind <= 3 ? g_halo_count[kind] : 0; }
 void halo_set(int on) { halo_env(); g_halo = on; }
 
 }  // namespace mstk

@@ -137,3 +137,33 @@ def test_convt_halo_batchnorm_statistics():
     assert_close(nchw(y), pre.float().cpu(), 8e-3, "convT halo (stats variant) output")
     assert_close(stats[:cout], pre.sum(dim=(0, 2, 3)), 1e-4, "stats sum")
     assert_close(stats[cout:], (pre ** 2).sum(dim=(0, 2, 3)), 1e-4, "stats sumsq")
+
+
+# n, h, w, cin, cout: ConvTranspose2d(cin, cout, k3, s2, p1, output_padding 1) = the data gradient of the stride-2 convolutions
+CONVT3_CASES = [
+    (64, 32, 32, 128, 64),       # style encoder enc2's data gradient geometry
+    (40, 16, 32, 256, 128),      # two 64-channel output blocks, four channel blocks, non-square
+    (100, 16, 16, 64, 192),      # three output blocks, one channel block
+]
+
+
+@pytest.mark.parametrize("case", CONVT3_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_convt3_halo_vs_torch(case):
+    from music_style_transfer_ldm_b200 import ops
+    n, h, w, cin, cout = case
+    g = gen(hash(case) % 1000)
+    x = torch.randn((n, cin, h, w), generator=g).bfloat16()
+    wt = (torch.randn((cin, cout, 3, 3), generator=g) / math.sqrt(cin * 2.25)).bfloat16()
+    b = torch.randn((cout,), generator=g)
+    xd = nhwc(x, torch.bfloat16).to(DEV)
+    wp = ops.pack_weight(wt.float().to(DEV), torch.bfloat16, transposed=True)
+    before = _halo_count(3)
+    y = ops.conv(xd, wp, None, ksize=3, stride=2, transposed=True, act=ops.ACT_NONE, out_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    assert _halo_count(3) == before + 1, "the k3 conv-transpose did not take the halo kernel"
+    assert tuple(y.shape) == (n, 2 * h, 2 * w, cout)
+    ref = torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), None, stride=2, padding=1, output_padding=1)
+    assert_close(nchw(y), ref.cpu(), 8e-3, "convT k3 halo vs torch")
+    y2 = ops.conv(xd, wp, b.to(DEV), ksize=3, stride=2, transposed=True, act=ops.ACT_RELU, out_dtype=torch.bfloat16)
+    ref2 = torch.relu(torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), b.to(DEV), stride=2, padding=1, output_padding=1))
+    assert_close(nchw(y2), ref2.cpu(), 8e-3, "convT k3 halo vs torch (bias, ReLU)")
