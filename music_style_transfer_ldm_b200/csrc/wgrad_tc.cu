@@ -369,6 +369,11 @@ int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, c
     if (ks > ks_max) ks = ks_max;
     if (ks < 1) ks = 1;
     if (ks > 65535) ks = 65535;
+    {
+        static int ks_cap = -1;                               // development: MSTK_WG_KSMAX caps the pixel split
+        if (ks_cap < 0) { const char* e = getenv("MSTK_WG_KSMAX"); ks_cap = e ? atoi(e) : 0; }
+        if (ks_cap > 0 && ks > ks_cap) ks = ks_cap;
+    }
     q.ksplit = (int)ks;
 
     WgMaps maps;
