@@ -53,10 +53,17 @@ struct HaloParams {
     int8_t t_slot[10], t_nsel[10], t_dcol[10];   // first box of the round, N = 64 << nsel, first accumulator column / 64
     int8_t t_first[5];                 // operations of round r: [t_first[r], t_first[r + 1])
     int32_t nboxes;                    // 16 (k4) or 9 (k3)
+    // stride-2 3x3 convolution (S2 kernel): a stride-1 2x2 convolution over the four parity planes of the input, one plane per
+    // "channel block": plane (py, px) contributes (1 + py) * (1 + px) taps, all on the plane's own 18 x 18 halo box
+    int32_t KBC;                       // channel blocks per plane (Cin / 64)
+    int8_t s2_ntaps[4];                // taps of plane py * 2 + px
+    int8_t s2_slice[4][4];             // weight slice ky * 3 + kx of the plane's tap
+    int16_t s2_aoff[4][4];             // halo row of its A start
     uint32_t off_stg;                  // byte offset of the epilogue warps' staging tiles
 };
 
-struct HaloOutMaps { CUtensorMap m[4]; };   // output tensor map(s): [0] for the convolution, one per output parity for conv-transpose
+struct HaloOutMaps { CUtensorMap m[4]; };
+struct HaloInMaps { CUtensorMap m[4]; };    // input tensor map(s): [0], or one per parity plane for the stride-2 convolution   // output tensor map(s): [0] for the convolution, one per output parity for conv-transpose
 
 struct HaloShared {
     uint64_t a_full[2], a_empty[2];
@@ -74,10 +81,11 @@ __device__ __forceinline__ int hdiv(int n, uint32_t inv) { return inv ? (int)__u
 //                of 64 columns ([P00 | P01 | P11 | P10], double-buffered); parities that read the same input offset share one
 //                MMA (N = 256 / 128 / 64, host-built operation table); each epilogue warp stores (parity) boxes through the
 //                parity's strided output map.
-template <bool CONVT, int TILES, bool STATS>
+template <bool CONVT, int TILES, bool STATS, bool S2>
 __global__ void __launch_bounds__(CH_THREADS, 1)
-conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ HaloOutMaps maps_o,
+conv_halo_kernel(const __grid_constant__ HaloInMaps maps_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ HaloOutMaps maps_o,
                  const __grid_constant__ HaloParams q) {
+    const CUtensorMap& map_a = maps_a.m[0];
     const int NOPS = CONVT ? q.nboxes : 9;                  // weight boxes per channel block
     constexpr int BN = CONVT ? 64 : 128;                    // MMA N
     constexpr uint32_t B_BYTES = (uint32_t)BN * 128u;       // one operation's weight box
@@ -95,7 +103,6 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const uint32_t off_b = 2u * A_STAGE;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = q.G, S = q.S;
-    const int R = (NOPS + G - 1) / G;               // B rounds per channel block
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&map_a);
@@ -132,7 +139,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                     const int s = ka & 1;
                     if (ka >= 2) mbar_wait(&sh.a_empty[s], (uint32_t)(((ka >> 1) - 1) & 1));
                     mbar_expect_tx(&sh.a_full[s], A_BYTES);
-                    tma_load_4d(&map_a, &sh.a_full[s], smem_base + (uint32_t)s * A_STAGE, kb * 64, w0, h0, n);
+                    const int plane = S2 ? kb / q.KBC : 0, cb = S2 ? kb - plane * q.KBC : kb;
+                    tma_load_4d(&maps_a.m[plane], &sh.a_full[s], smem_base + (uint32_t)s * A_STAGE, cb * 64, w0, h0, n);
                 }
             }
         } else if (lane <= S * G) {
@@ -144,10 +152,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const int blk = hdiv(it, q.inv_nblocks);
                 const int nb = it - blk * q.nblocks;
                 for (int kb = 0; kb < q.KB; ++kb) {
+                    const int plane = S2 ? kb / q.KBC : 0, cb = S2 ? kb - plane * q.KBC : kb;
+                    const int nops = S2 ? (int)q.s2_ntaps[plane] : NOPS, R = (nops + G - 1) / G;      // B rounds of this channel block
                     for (int r = 0; r < R; ++r, ++rr) {
                         if (rr % S != s) continue;
                         const int use = rr / S;
-                        const int cnt = min(G, NOPS - r * G);
+                        const int cnt = min(G, nops - r * G);
                         // EVERY lane of the stage observes EVERY release and arrives on the full barrier (count = G), also
                         // in a short round it does not load for: a lane that skipped a release could not tell release #u
                         // from #u+2 by parity, and a round that could complete without one of its lanes could run two
@@ -156,8 +166,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                         if (g == 0) mbar_expect_tx(&sh.b_full[s], B_BYTES * (uint32_t)cnt);
                         else mbar_arrive(&sh.b_full[s]);
                         if (g >= cnt) continue;
-                        const int slice = CONVT ? (int)q.op_slice[r * G + g] : r * G + g;
-                        tma_load_2d(&map_b, &sh.b_full[s], dst, kb * 64, slice * q.Cout + nb * BN);
+                        const int slice = CONVT ? (int)q.op_slice[r * G + g] : S2 ? (int)q.s2_slice[plane][r * G + g] : r * G + g;
+                        tma_load_2d(&map_b, &sh.b_full[s], dst, cb * 64, slice * q.Cout + nb * BN);
                     }
                 }
             }
@@ -185,11 +195,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 const int sa = ka & 1;
                 mbar_wait_addr(a_full0 + 8u * (uint32_t)sa, (uint32_t)((ka >> 1) & 1));
                 const uint32_t a_lo = a_lo0 + (uint32_t)sa * (A_STAGE >> 4);
+                const int plane = S2 ? kb / q.KBC : 0;
+                const int nops = S2 ? (int)q.s2_ntaps[plane] : NOPS, R = (nops + G - 1) / G;
                 for (int r = 0; r < R; ++r, ++rr) {
                     const int s = rr % S;
                     mbar_wait_addr(b_full0 + 8u * (uint32_t)s, (uint32_t)((rr / S) & 1));
                     tc_fence_after();
-                    const int cnt = min(G, NOPS - r * G);
+                    const int cnt = min(G, nops - r * G);
                     if (elect_one()) {
                         if (CONVT) {
                             // round 0 is the one N = 256 operation on the centre offset: it opens all four parity accumulators
@@ -207,7 +219,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                         for (int g = 0; g < (CONVT ? 0 : cnt); ++g) {
                             const int op = r * G + g;
                             const int dy = op / 3, dx = op - dy * 3;
-                            const uint32_t aoff = (uint32_t)(dy * HW + dx), dcol = 0u;
+                            const uint32_t aoff = S2 ? (uint32_t)q.s2_aoff[plane][op] : (uint32_t)(dy * HW + dx), dcol = 0u;
                             const uint32_t at = a_lo + aoff * 8u;                                   // 128 B per halo row = 8 units of 16 B
                             const uint32_t bt = b_lo0 + (uint32_t)(s * G + g) * (B_BYTES >> 4);
 #pragma unroll
@@ -375,7 +387,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // ---------------------------------------------------------------------------
 static int g_halo = -1, g_halo_g = 3, g_halo_s = 2, g_halo_dbg = 0, g_halo_min = 2;   // g_halo_min: items per SM from which the kernel is taken (never slower than conv_tc from 1; tools/halo_tune.py 96)
 static bool g_halo_attr = false;
-static long long g_halo_count[4] = {0, 0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
+static long long g_halo_count[5] = {0, 0, 0, 0, 0};   // launches per kind (development aid, mstk_debug_halo_count)
 
 static void halo_env() {
     if (g_halo >= 0) return;
@@ -392,11 +404,26 @@ static int halo_kind(const ConvP& p) {
     halo_env();
     if (!g_halo) return 0;
     if (p.dtype != MSTK_BF16 || !p.y || p.add || p.add_nc || p.has_ddim) return 0;
-    if (p.Cin % 64 != 0 || p.s_in != 1) return 0;
-    if (p.Hg % CH_BH != 0 || p.Wg % 16 != 0 || p.Hg != p.H || p.Wg != p.W) return 0;
+    if (p.Cin % 64 != 0) return 0;
+    if (p.Hg % CH_BH != 0 || p.Wg % 16 != 0) return 0;
+    if (p.s_in == 2) {
+        // 3x3 stride-2 convolution = a 2x2 stride-1 convolution over the four parity planes of the input (kind 4)
+        if (p.nphases != 1 || p.s_out != 1 || p.ph[0].ntaps != 9 || p.Cout % CH_BN != 0 || p.stats || (p.H & 1) || (p.W & 1)) return 0;
+        // OPT-IN (MSTK_CONV_HALO=9 / mstk_debug_halo(9)): measured neutral against conv_tc (config-2 encoder layer 40.6 us both ways,
+        // training step 6.86 vs 6.89 ms) -- with one plane per channel block an item loads four 41 KB boxes for the 72 MMAs that
+        // the stride-1 layers get from one, and the A loads, not the weights, bound it
+        if (p.Hg * 2 != p.H || p.Wg * 2 != p.W || !(g_halo & 8)) return 0;
+        for (int t = 0; t < 9; ++t) {
+            const Tap& tp = p.ph[0].taps[t];
+            if (tp.dy != t / 3 - 1 || tp.dx != t % 3 - 1 || tp.slice != t) return 0;
+        }
+        const long long items = (long long)p.N * (p.Hg / CH_BH) * (p.Wg / 16) * (p.Cout / CH_BN);
+        return (items >= (long long)g_halo_min * tc_num_sms() && items < 0x7fffffffll) ? 4 : 0;
+    }
+    if (p.s_in != 1 || p.Hg != p.H || p.Wg != p.W) return 0;
     if ((reinterpret_cast<uintptr_t>(p.x) & 15) || (reinterpret_cast<uintptr_t>(p.w) & 15) || (reinterpret_cast<uintptr_t>(p.y) & 15)) return 0;
     if (p.bias && (reinterpret_cast<uintptr_t>(p.bias) & 15)) return 0;
-    const long long blocks = (long long)p.N * (p.H / CH_BH) * (p.W / 16);      // 16 x 16 pixel blocks
+    const long long blocks = (long long)p.N * (p.Hg / CH_BH) * (p.Wg / 16);    // 16 x 16 pixel blocks
     if (p.nphases == 1 && p.s_out == 1 && p.ph[0].ntaps == 9 && p.Cout % CH_BN == 0 && !p.stats) {
         for (int t = 0; t < 9; ++t) {
             const Tap& tp = p.ph[0].taps[t];
@@ -438,22 +465,34 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     if (!tc_init()) return MSTK_EUNSUPPORTED;
     const int kind = halo_kind(p);
     if (!kind) return MSTK_EUNSUPPORTED;
-    const bool convt = kind >= 2, k3 = kind == 3;
+    const bool convt = kind == 2 || kind == 3, k3 = kind == 3, s2 = kind == 4;
     const int bn = convt ? 64 : CH_BN;
     HaloParams q;
     memset(&q, 0, sizeof(q));
     q.bias = p.bias; q.y = p.y; q.stats = p.stats;
-    q.N = p.N; q.H = p.H; q.W = p.W; q.Cin = p.Cin; q.Cout = p.Cout;
+    q.N = p.N; q.H = p.Hg; q.W = p.Wg; q.Cin = p.Cin; q.Cout = p.Cout;      // the pixel grid of the items: output (= input for stride 1 / conv-transpose input)
     const int tiles = convt ? 1 : 2, hw = 8 * tiles + 2;
-    q.blocks_w = p.W / (8 * tiles); q.blocks_h = p.H / CH_BH;
+    q.blocks_w = p.Wg / (8 * tiles); q.blocks_h = p.Hg / CH_BH;
     q.nblocks = convt ? p.Cout / 64 : p.Cout / CH_BN;
     q.nitems = p.N * q.blocks_w * q.blocks_h * q.nblocks;
-    q.KB = p.Cin / 64;
+    q.KBC = p.Cin / 64;
+    q.KB = s2 ? 4 * q.KBC : q.KBC;
+    if (s2) {
+        // parity plane of a tap: input row 2 ho + ky - 1 -> plane py = (ky - 1) & 1, plane row ho + (ky - 1 - py) / 2 (same in x)
+        for (int pl = 0; pl < 4; ++pl) q.s2_ntaps[pl] = 0;
+        for (int t = 0; t < 9; ++t) {
+            const int dy = t / 3 - 1, dx = t % 3 - 1;
+            const int py = dy & 1, px = dx & 1, oy = (dy - py) / 2, ox = (dx - px) / 2, pl = py * 2 + px;
+            const int i = q.s2_ntaps[pl]++;
+            q.s2_slice[pl][i] = (int8_t)t;
+            q.s2_aoff[pl][i] = (int16_t)((oy + 1) * (8 * 2 + 2) + (ox + 1));
+        }
+    }
     // conv-transpose: 8 KB boxes.  k4: 8 per stage (two rounds of the box table = 20 MMAs per issuer round trip), 2 stages.
     // k3: 5 per stage (rounds of 5 and 4 boxes), 3 stages.
     static int ct_g = 0;
     if (!ct_g) { const char* e = getenv("MSTK_HALO_CTG"); ct_g = e ? atoi(e) : 8; if (ct_g != 4 && ct_g != 8 && ct_g != 16) ct_g = 8; }
-    q.G = !convt ? g_halo_g : k3 ? 5 : ct_g; q.S = !convt ? g_halo_s : k3 ? 3 : 16 / ct_g; q.dbg = g_halo_dbg;
+    q.G = s2 ? 2 : !convt ? g_halo_g : k3 ? 5 : ct_g; q.S = s2 ? 3 : !convt ? g_halo_s : k3 ? 3 : 16 / ct_g; q.dbg = g_halo_dbg;
     q.nboxes = k3 ? 9 : 16;
     q.act = p.act; q.affine = p.affine; q.out_f32 = p.out_dtype == MSTK_F32 ? 1 : 0;
     q.out_scale = p.out_scale; q.out_shift = p.out_shift;
@@ -516,12 +555,26 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     MSTK_REQUIRE((long long)q.nitems * (q.blocks_w * q.blocks_h > q.nblocks ? q.blocks_w * q.blocks_h : q.nblocks) < (1ll << 32),
                  "conv(halo): item grid outside the range of the division-free index math");
     CUtensorMap map_a, map_b;
+    HaloInMaps maps_a;
     {
         const uint64_t dims[4] = {(uint64_t)p.Cin, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)p.N};
         const uint64_t strides[3] = {(uint64_t)p.Cin * 2, (uint64_t)p.W * p.Cin * 2, (uint64_t)p.H * p.W * p.Cin * 2};
         const uint32_t box[4] = {64u, (uint32_t)hw, (uint32_t)CH_HH, 1u};
         int rc = tc_encode_map(&map_a, 0, p.x, 4, dims, strides, box, 128);
         if (rc != MSTK_OK) return rc;
+        for (int i = 0; i < 4; ++i) maps_a.m[i] = map_a;
+    }
+    if (s2) {
+        // one map per parity plane: the input seen with doubled pixel strides from (py, px)
+        for (int pl = 0; pl < 4; ++pl) {
+            const int py = pl >> 1, px = pl & 1;
+            const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(p.x) + ((size_t)py * p.W + px) * p.Cin;
+            const uint64_t dims[4] = {(uint64_t)p.Cin, (uint64_t)(p.W / 2), (uint64_t)(p.H / 2), (uint64_t)p.N};
+            const uint64_t strides[3] = {(uint64_t)p.Cin * 2 * 2, (uint64_t)p.W * p.Cin * 2 * 2, (uint64_t)p.H * p.W * p.Cin * 2};
+            const uint32_t box[4] = {64u, (uint32_t)hw, (uint32_t)CH_HH, 1u};
+            int rc = tc_encode_map(&maps_a.m[pl], 0, base, 4, dims, strides, box, 128);
+            if (rc != MSTK_OK) return rc;
+        }
     }
     {
         const uint64_t dims[2] = {(uint64_t)p.Cin, (uint64_t)nslices * p.Cout};
@@ -544,8 +597,8 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
             if (rc != MSTK_OK) return rc;
         }
     } else if (!q.out_f32) {
-        const uint64_t dims[4] = {(uint64_t)p.Cout, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)p.N};
-        const uint64_t strides[3] = {(uint64_t)p.Cout * 2, (uint64_t)p.W * p.Cout * 2, (uint64_t)p.H * p.W * p.Cout * 2};
+        const uint64_t dims[4] = {(uint64_t)p.Cout, (uint64_t)p.Wg, (uint64_t)p.Hg, (uint64_t)p.N};
+        const uint64_t strides[3] = {(uint64_t)p.Cout * 2, (uint64_t)p.Wg * p.Cout * 2, (uint64_t)p.Hg * p.Wg * p.Cout * 2};
         const uint32_t box[4] = {64u, 8u, 4u, 1u};
         int rc = tc_encode_map(&maps_o.m[0], 0, p.y, 4, dims, strides, box, 128);
         if (rc != MSTK_OK) return rc;
@@ -555,9 +608,10 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     const size_t smem = (size_t)q.off_stg + 8 * 4096 + 1024;
     MSTK_REQUIRE(smem <= 224 * 1024 && q.S <= CH_MAX_SUB && q.S >= 1, "conv(halo): shared-memory budget");
     if (!g_halo_attr) {
-        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        cudaError_t ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<false, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(conv_halo_kernel<true, 1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
         if (ea != cudaSuccess) return cuda_fail(ea, "cudaFuncSetAttribute(conv_halo_kernel)");
         g_halo_attr = true;
     }
@@ -573,15 +627,16 @@ int launch_conv_halo(const ConvP& p, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = !convt    ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2, false>, map_a, map_b, maps_o, q)
-                    : q.stats ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, true>, map_a, map_b, maps_o, q)
-                              : cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, false>, map_a, map_b, maps_o, q);
+    cudaError_t e = s2        ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2, false, true>, maps_a, map_b, maps_o, q)
+                    : !convt  ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<false, 2, false, false>, maps_a, map_b, maps_o, q)
+                    : q.stats ? cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, true, false>, maps_a, map_b, maps_o, q)
+                              : cudaLaunchKernelEx(&cfg, conv_halo_kernel<true, 1, false, false>, maps_a, map_b, maps_o, q);
     if (e != cudaSuccess) return cuda_fail(e, "conv_halo launch");
     ++g_halo_count[kind];
     return MSTK_OK;
 }
 
-long long halo_count(int kind) { return kind >= 1 && kind <= 3 ? g_halo_count[kind] : 0; }
+long long halo_count(int kind) { return kind >= 1 && kind <= 4 ? g_halo_count[kind] : 0; }
 void halo_set(int on) { halo_env(); g_halo = on; }
 
 }  // namespace mstk

@@ -167,3 +167,39 @@ def test_convt3_halo_vs_torch(case):
     y2 = ops.conv(xd, wp, b.to(DEV), ksize=3, stride=2, transposed=True, act=ops.ACT_RELU, out_dtype=torch.bfloat16)
     ref2 = torch.relu(torch.nn.functional.conv_transpose2d(x.float().to(DEV), wt.float().to(DEV), b.to(DEV), stride=2, padding=1, output_padding=1))
     assert_close(nchw(y2), ref2.cpu(), 8e-3, "convT k3 halo vs torch (bias, ReLU)")
+
+
+# n, h, w (input), cin, cout: Conv2d(cin, cout, k3, s2, p1) on the halo kernel (a 2x2 stride-1 convolution over the four parity planes)
+S2_CASES = [
+    (16, 64, 512, 64, 128),      # config-2 encoder layer (64 -> 128 @ 64 x 512 -> 32 x 256)
+    (80, 64, 64, 128, 256),      # style encoder enc3 geometry: two channel blocks per plane, two output blocks
+    (300, 32, 32, 64, 128),      # one 16 x 16 output block per image
+]
+
+
+@pytest.mark.parametrize("case", S2_CASES, ids=lambda c: "x".join(map(str, c)))
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_conv_s2_halo_vs_torch(case, out_dtype):
+    from music_style_transfer_ldm_b200 import ops
+    n, h, w, cin, cout = case
+    g = gen(hash(case) % 1000)
+    x = torch.randn((n, cin, h, w), generator=g).bfloat16()
+    wt = (torch.randn((cout, cin, 3, 3), generator=g) / math.sqrt(cin * 9)).bfloat16()
+    b = torch.randn((cout,), generator=g)
+    xd = nhwc(x, torch.bfloat16).to(DEV)
+    wp = ops.pack_weight(wt.float().to(DEV), torch.bfloat16)
+    before = _halo_count(4)
+    import ctypes
+    from music_style_transfer_ldm_b200 import _lib
+    sw = _lib.load().mstk_debug_halo
+    sw.argtypes = [ctypes.c_int]
+    sw(9)                                   # the stride-2 form is opt-in (measured neutral against conv_tc, see conv_halo.cu)
+    try:
+        y = ops.conv(xd, wp, b.to(DEV), ksize=3, stride=2, act=ops.ACT_RELU, out_dtype=out_dtype)
+        torch.cuda.synchronize()
+    finally:
+        sw(1)
+    assert _halo_count(4) == before + 1, "the stride-2 convolution did not take the halo kernel"
+    assert tuple(y.shape) == (n, h // 2, w // 2, cout)
+    ref = torch.relu(torch.nn.functional.conv2d(x.float().to(DEV), wt.float().to(DEV), b.to(DEV), stride=2, padding=1))
+    assert_close(nchw(y), ref.cpu(), 1e-5 if out_dtype == torch.float32 else 8e-3, "conv s2 halo vs torch")
