@@ -48,6 +48,7 @@ struct WgParams {
     int32_t m_tiles, n_tiles, ngroups, tpc;
     int32_t Wt, Ht, Nt, tiles_w, tiles_h, ptiles;
     int32_t ksplit, stages, tmem_cols;
+    int32_t tpm;                   // taps served by one MMA (their B tiles are one MN-major operand): 1 when swapped
     uint32_t m_tile_bytes, n_tile_bytes, stage_bytes;
     WgGroup groups[WG_MAX_GROUPS];
 };
@@ -192,6 +193,9 @@ wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgP
         // whole warp converged, one elected lane issues (see conv_tc_body.cuh); invariants pinned in registers
         if (nkb > 0) {
             const uint32_t idesc = keep_reg(make_idesc_mn(q.BNt));
+            const int tpm = keep_reg(q.tpm);                                   // taps per MMA (1 when swapped)
+            const uint32_t idesc_m[3] = {make_idesc_mn(2 * q.BNt <= 256 ? 2 * q.BNt : q.BNt), make_idesc_mn(3 * q.BNt <= 256 ? 3 * q.BNt : q.BNt),
+                                         make_idesc_mn(4 * q.BNt <= 256 ? 4 * q.BNt : q.BNt)};
             const uint32_t kstep_a = (uint32_t)(16 * 128) >> 4;            // 16 pixels further along K
             const uint32_t kstep_b = keep_reg((uint32_t)(16 * n_rowbytes) >> 4);
             const int stages = keep_reg(q.stages), nk = keep_reg(nkb), nt_ = keep_reg(ntaps);
@@ -211,12 +215,18 @@ wgrad_tc_kernel(const __grid_constant__ WgMaps maps, const __grid_constant__ WgP
                 tc_fence_after();
                 if (elect_one()) {
                     uint32_t alo = alo0 + soff, blo = blo0 + soff, tacc = tm;
-                    for (int t = 0; t < nt_; ++t) {
+                    // Not swapped: the taps' x tiles follow each other in the stage exactly one channel-chunk stride apart, so
+                    // `tpm` taps are ONE MN-major B operand of N = tpm * BNt (<= 256) and their accumulators adjacent TMEM
+                    // columns: one MMA instead of tpm (an MMA costs ~110 cycles to issue whatever its N; with N = 64 per tap the
+                    // K loop was bound by that, tools/wgrad_tune.py)
+                    for (int t = 0; t < nt_; t += tpm) {
+                        const int nn = nt_ - t < tpm ? nt_ - t : tpm;
+                        const uint32_t ide = nn == 1 ? idesc : idesc_m[nn - 2];
 #pragma unroll
                         for (int k = 0; k < WG_KP / 16; ++k)
-                            umma_bf16(tacc, ((uint64_t)ahi << 32) | (alo + k * kstep_a), ((uint64_t)bhi << 32) | (blo + k * kstep_b), idesc,
+                            umma_bf16(tacc, ((uint64_t)ahi << 32) | (alo + k * kstep_a), ((uint64_t)bhi << 32) | (blo + k * kstep_b), ide,
                                       (acc | (uint32_t)k) ? 1u : 0u);
-                        alo += a_tap; blo += b_tap; tacc += bnt;
+                        alo += a_tap * (uint32_t)nn; blo += b_tap * (uint32_t)nn; tacc += bnt * (uint32_t)nn;
                     }
                     umma_commit_addr(empty0 + 8u * (uint32_t)s);
                     if (it == nk - 1) umma_commit_addr(accum_a);
@@ -375,6 +385,13 @@ int launch_wgrad_tc(const ConvP& p, float* dw, long long s_co, long long s_ci, c
         if (ks_cap > 0 && ks > ks_cap) ks = ks_cap;
     }
     q.ksplit = (int)ks;
+    {
+        static int merge = -1;                                // MSTK_WG_MERGE=0: one MMA per tap (development)
+        if (merge < 0) { const char* e = getenv("MSTK_WG_MERGE"); merge = e ? atoi(e) : 1; }
+        q.tpm = (!q.swap && merge) ? 256 / q.BNt : 1;
+        if (q.tpm < 1) q.tpm = 1;
+        if (q.tpm > 4) q.tpm = 4;
+    }
 
     WgMaps maps;
     memset(&maps, 0, sizeof(maps));

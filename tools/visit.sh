@@ -1,2 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_conv_halo.py tests/test_gpu_conv_tcp.py tests/test_gpu_conv_tc.py -q -m gpu --timeout 300 2>&1 | tail -3 > gpurun_out/s2.log; cat gpurun_out/s2.log
+( timeout 1200 python -m pytest tests/test_gpu_train.py tests/test_gpu_train_autoencoder.py tests/test_gpu_autograd.py -q -m gpu -x --timeout 600 2>&1 | tail -2
+bash tools/bench_train.sh 2>&1 | tail -2 ) > gpurun_out/wg3.log 2>&1
+cat gpurun_out/wg3.log | cut -c 1-300
