@@ -166,7 +166,7 @@ def kernel_roofline(model, peaks, reps=20):
                 rec["replay"]()
             stream.synchronize()
             gr = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gr, stream=stream):
+            with ops.graph_capture(gr, stream=stream):
                 for _ in range(reps):
                     rec["replay"]()
             gr.replay()
@@ -186,7 +186,7 @@ def kernel_roofline(model, peaks, reps=20):
             r["replay"]()
         stream.synchronize()
         gr = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(gr, stream=stream):
+        with ops.graph_capture(gr, stream=stream):
             for _ in range(reps):
                 for r in recs:
                     r["replay"]()
@@ -227,6 +227,7 @@ def vae_leg(sd, dev, peaks, precision, reps=20):
     epilogue + one normalise pass).  achieved = SURVEY 8(d)'s minimal traffic / device time."""
     import torch
     import music_style_transfer_ldm_b200 as M
+    from music_style_transfer_ldm_b200 import ops
     enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
     enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
     dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
@@ -247,7 +248,7 @@ def vae_leg(sd, dev, peaks, precision, reps=20):
                     y = dec(enc(x))
                 stream.synchronize()
                 gr = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(gr, stream=stream):
+                with ops.graph_capture(gr, stream=stream):
                     y = dec(enc(x))
                 gr.replay()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

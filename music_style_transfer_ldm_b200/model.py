@@ -709,7 +709,7 @@ class LDM(_Kernelised):
                 b.copy_(s0)
             g = torch.cuda.CUDAGraph()
             n0 = ops.LAUNCHES
-            with torch.cuda.graph(g):
+            with ops.graph_capture(g):
                 ent["out"] = body(*ent["in"])
             ent["graph"] = g
             ent["launches"], ops.LAUNCHES = ops.LAUNCHES - n0, n0      # capture enqueues nothing
@@ -768,7 +768,7 @@ class LDM(_Kernelised):
             torch.cuda.current_stream().wait_stream(side)
             g = torch.cuda.CUDAGraph()
             n0 = ops.LAUNCHES
-            with torch.cuda.graph(g):
+            with ops.graph_capture(g):
                 self._loop_body(ent["x"], ent["s5"], ent["s6"], times, eta, logs, ent["tt"])
             ent["graph"] = g
             ent["launches"], ops.LAUNCHES = ops.LAUNCHES - n0, n0      # capture enqueues nothing

@@ -68,6 +68,40 @@ def tc_eligible(dtype, cin: int, cout: int, stride: int, transposed: bool, h: in
     return True
 
 
+class graph_capture:
+    """``torch.cuda.graph`` with the cyclic garbage collector held off for the duration of the capture.
+
+    Destroying a CUDA graph (cudaGraphExecDestroy / cudaGraphDestroy) is not permitted while a stream of the process is
+    capturing in the default "global" error mode.  A dead reference cycle that still owns a ``torch.cuda.CUDAGraph`` (an
+    earlier trainer or model with captured steps) is finalised whenever the cyclic collector happens to run; when that is
+    in the middle of a capture the capture is invalidated and the next launch reports "operation failed due to a previous
+    error during capture".  So: collect BEFORE the capture begins (torch >= 2.9 no longer does), keep the collector off
+    while capturing, restore it afterwards."""
+
+    def __init__(self, graph, **kw):
+        self.ctx = torch.cuda.graph(graph, **kw)
+
+    def __enter__(self):
+        import gc
+        gc.collect()
+        self.was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            return self.ctx.__enter__()
+        except BaseException:
+            if self.was_enabled:
+                gc.enable()
+            raise
+
+    def __exit__(self, *exc):
+        import gc
+        try:
+            return self.ctx.__exit__(*exc)
+        finally:
+            if self.was_enabled:
+                gc.enable()
+
+
 _WS_SLOT = 0
 
 

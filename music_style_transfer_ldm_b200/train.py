@@ -561,7 +561,7 @@ class LDMTrainer(_SideStream):
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             n0, c0 = ops.LAUNCHES, self.step_count
-            with torch.cuda.graph(g):
+            with ops.graph_capture(g):
                 ent["out"] = self._step_impl(ent["x"], ent["s"], ent["t"], ent["noise"])
             ent["launches"] = ops.LAUNCHES - n0
             ops.LAUNCHES, self.step_count = n0, c0          # capture enqueued nothing
@@ -892,7 +892,7 @@ class AutoencoderTrainer(_SideStream):
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             n0, c0 = ops.LAUNCHES, self.step_count
-            with torch.cuda.graph(g):
+            with ops.graph_capture(g):
                 ent["out"] = self._step_impl(ent["x"])
             ent["launches"] = ops.LAUNCHES - n0
             ops.LAUNCHES, self.step_count = n0, c0          # capture enqueued nothing

@@ -168,3 +168,35 @@ def test_train_epoch_and_train_follow_reference_contract(sd, tmp_path, capsys):
     back = torch.load(tmp_path / "ldm_0.pth", map_location="cpu")
     assert set(back) == set(sd)
     assert "Epoch 1: Train Loss" in capsys.readouterr().out
+
+
+def test_capture_is_not_invalidated_by_a_dead_cycle_that_owns_a_graph():
+    """ops.graph_capture: a dead reference cycle owning a CUDAGraph (an earlier trainer) used to be finalised by the cyclic
+    collector in the middle of a later capture -- cudaGraphExecDestroy is not permitted then, the capture was invalidated and
+    the next launch failed with "operation failed due to a previous error during capture" (seen when two trainers were
+    captured in one process, depending on when the collector happened to run)."""
+    import gc
+    from music_style_transfer_ldm_b200 import ops
+
+    class Holder:
+        pass
+
+    x = torch.zeros(8, device=DEV)
+    g0 = torch.cuda.CUDAGraph()
+    with ops.graph_capture(g0):
+        x += 1
+    h = Holder()
+    h.me, h.graph = h, g0
+    del h, g0                                   # dead cycle; only the cyclic collector can finalise the graph now
+    assert gc.isenabled()
+    g = torch.cuda.CUDAGraph()
+    with ops.graph_capture(g):
+        assert not gc.isenabled()
+        x += 1
+        junk = [[i] for i in range(200000)]     # enough container allocations for several automatic collections
+        x += 1
+    assert gc.isenabled() and len(junk) == 200000
+    x.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    assert x.tolist() == [2.0] * 8
