@@ -19,6 +19,12 @@
  *     all work is enqueued on `stream` and is CUDA-graph capturable.
  *   - activations are NHWC ("channels last"), dtype MSTK_F32 or MSTK_BF16;
  *     parameters are packed once by the mstk_pack_* calls.
+ *   - alignment: tensor base addresses should be 16-byte aligned (any cudaMalloc / framework allocation is; a view that
+ *     starts part-way into one may not be).  The tensor-core, convolution, weight-gradient, attention, split, BatchNorm
+ *     backward, feature-loss and optimizer entry points move data as 128-bit vectors or TMA boxes and REFUSE a misaligned
+ *     tensor (MSTK_EINVAL, message naming the alignment); the remaining element-wise / reduction / layout calls accept
+ *     any naturally aligned pointer and any element count (scalar path).  No call faults on a misaligned pointer
+ *     (tests/test_gpu_ops_fuzz.py).
  */
 #ifndef MSTK_H_
 #define MSTK_H_

@@ -171,13 +171,14 @@ __device__ __forceinline__ void store8_rt(void* p, int dtype, size_t i8, const f
 struct ActBwdP {
     const void* dy; const void* dy2; const void* y; void* g; float* dbias;
     long long rows; int c, act; float y_scale, y_shift; int dy_dtype, y_dtype, g_dtype;
+    int vec;            // 8 / 4: the 128-bit paths (c % 8 == 0 / single channel) are usable -- sizes AND base addresses allow them; 0: scalar
 };
 __device__ __forceinline__ float act_deriv(float y, int act, float y_scale, float y_shift) {
     if (act == MSTK_ACT_RELU) return y > 0.f ? y_scale : 0.f;
     if (act == MSTK_ACT_TANH) { const float t = (y - y_shift) / y_scale; return (1.f - t * t) * y_scale; }
     return y_scale;
 }
-// vector path: c % 8 == 0; per-thread column sums are flushed through shared memory
+// vector path (a.vec == 8): c % 8 == 0 and 16-byte aligned tensors; per-thread column sums are flushed through shared memory
 __global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
     extern __shared__ float scol[];     // [c] when dbias
     if (a.dbias) {
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
         __syncthreads();
     }
     const size_t total = (size_t)a.rows * a.c;
-    if ((a.c & 7) == 0) {
+    if (a.vec == 8) {
         const size_t nvec = total >> 3;
         float s[8];
 #pragma unroll
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const ActBwdP a) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) atomicAdd(&scol[ch_prev + k], s[k]);
         }
-    } else if (a.c == 1 && (total & 3) == 0) {
+    } else if (a.vec == 4) {
         // single channel (the decoder's output layer): 4 elements per thread, the bias gradient is ONE sum --
         // registers -> warp shuffle -> one shared-memory atomic per warp (the generic path below would issue one
         // shared-memory atomic per ELEMENT on the same address)
@@ -1044,6 +1045,7 @@ int mstk_pack_multi(const mstk_pack_entry* entries_dev, int n_entries, int total
 
 int mstk_conv2d_wgrad(const mstk_wgrad_args* a, void* stream) {
     MSTK_REQUIRE(a && a->x && a->dy && a->dw, "wgrad: null");
+    MSTK_REQUIRE(aligned16({a->x, a->dy, a->dw}), "wgrad: x / dy / dw must be 16-byte aligned (TMA boxes, 128-bit loads)");
     // build the FORWARD plan (taps / phases); x stays the input, "y" is dy
     mstk_conv_args f;
     memset(&f, 0, sizeof(f));
@@ -1089,7 +1091,9 @@ int mstk_act_bwd(const mstk_act_bwd_args* a, void* stream) {
     p.dy = a->dy; p.dy2 = a->dy2; p.y = a->y; p.g = a->g; p.dbias = a->dbias; p.rows = a->rows; p.c = a->c; p.act = a->act;
     p.y_scale = a->y_scale; p.y_shift = a->y_shift; p.dy_dtype = a->dy_dtype; p.y_dtype = a->y_dtype; p.g_dtype = a->g_dtype;
     const size_t total = (size_t)a->rows * a->c;
-    const size_t items = (a->c & 7) == 0 ? total / 8 : total;
+    const bool al = aligned16({a->dy, a->dy2, a->y, a->g});
+    p.vec = !al ? 0 : (a->c & 7) == 0 ? 8 : (a->c == 1 && (total & 3) == 0) ? 4 : 0;
+    const size_t items = p.vec ? total / p.vec : total;
     act_bwd_kernel<<<bw_grid(items, 256, 4), 256, a->dbias ? a->c * sizeof(float) : 0, (cudaStream_t)stream>>>(p);
     MSTK_CHECK_LAUNCH("act_bwd");
     return MSTK_OK;
@@ -1098,6 +1102,7 @@ int mstk_act_bwd(const mstk_act_bwd_args* a, void* stream) {
 static int bn_bwd_common(const mstk_bn_bwd_args* a, BnBwdP* p) {
     MSTK_REQUIRE(a && a->dy && a->v && a->mean && a->invstd && a->gamma && a->beta && a->sums, "bn_bwd: null");
     MSTK_REQUIRE(a->c > 0 && (a->c & 7) == 0 && a->c <= 4096 && a->rows > 0 && a->count >= a->rows, "bn_bwd: bad dims (c must be a multiple of 8)");
+    MSTK_REQUIRE(aligned16({a->dy, a->v, a->dv}), "bn_bwd: dy / v / dv must be 16-byte aligned (128-bit loads and stores)");
     p->dy = a->dy; p->v = a->v; p->dv = a->dv; p->mean = a->mean; p->invstd = a->invstd; p->gamma = a->gamma; p->beta = a->beta;
     p->sums = a->sums; p->dgamma = a->dgamma; p->dbeta = a->dbeta; p->rows = a->rows; p->count = a->count; p->c = a->c; p->act = a->act;
     p->dy_dtype = a->dy_dtype; p->v_dtype = a->v_dtype; p->dv_dtype = a->dv_dtype;

@@ -1,5 +1,7 @@
 // Shared device/host definitions for libmstk (sm_100a only).
 #pragma once
+#include <initializer_list>
+#include <cstdint>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -22,6 +24,13 @@ int cuda_fail(cudaError_t e, const char* what);
             return MSTK_EINVAL;                          \
         }                                                \
     } while (0)
+
+// true when every pointer is 16-byte aligned (null counts as aligned): the gate of the kernels' 128-bit load / store paths
+inline bool aligned16(std::initializer_list<const void*> ps) {
+    for (const void* q : ps)
+        if (reinterpret_cast<uintptr_t>(q) & 15) return false;
+    return true;
+}
 
 #define MSTK_CHECK_LAUNCH(what)                                         \
     do {                                                                \

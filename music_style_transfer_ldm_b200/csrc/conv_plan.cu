@@ -109,6 +109,11 @@ int mstk_conv2d_fwd(const mstk_conv_args* a, void* stream) {
     mstk::ConvP p;
     int rc = mstk::build_conv_plan(a, &p);
     if (rc != MSTK_OK) return rc;
+    // every kernel behind this entry point moves its tensors with 128-bit accesses or TMA boxes
+    MSTK_REQUIRE(mstk::aligned16({a->x, a->wpacked, a->y, a->add, a->add_nc, a->bias, a->stats}), "conv: tensor pointers must be 16-byte aligned");
+    if (a->ddim)
+        MSTK_REQUIRE(mstk::aligned16({a->ddim->x_cur, a->ddim->x_next, a->ddim->x_next_lp, a->ddim->x0_pred}),
+                     "conv: the tensors of the ddim epilogue must be 16-byte aligned");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     int backend = a->backend;
     if (backend == MSTK_BACKEND_AUTO) {

@@ -105,6 +105,7 @@ struct BnP {
     const void* x; void* y; const double* stats; const float* gamma; const float* beta;
     float* running_mean; float* running_var; float* save_mean; float* save_invstd;
     long long count, rows; int c; float eps, momentum; int act, dtype, out_dtype;
+    int vec;            // 1: c % 8 == 0 and x / y 16-byte aligned -> 8 channels per thread with 128-bit accesses
 };
 
 // one thread handles 8 consecutive channels of one row (requires c % 8 == 0) or falls
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnP a) {
     }
     __syncthreads();
     const size_t total = (size_t)a.rows * a.c;
-    if ((a.c & 7) == 0) {
+    if (a.vec) {
         const size_t nvec = total >> 3;
         ChanWalk cw((blockIdx.x * (size_t)blockDim.x + threadIdx.x) << 3, ((size_t)gridDim.x * blockDim.x) << 3, a.c);
         for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x, cw.next()) {
@@ -611,7 +612,8 @@ int mstk_bn_apply(const mstk_bn_args* a, void* stream) {
     p.running_mean = a->running_mean; p.running_var = a->running_var; p.save_mean = a->save_mean; p.save_invstd = a->save_invstd;
     p.count = a->count; p.rows = a->rows > 0 ? a->rows : a->count; p.c = a->c; p.eps = a->eps; p.momentum = a->momentum; p.act = a->act; p.dtype = a->dtype; p.out_dtype = a->out_dtype;
     const size_t total = (size_t)p.rows * a->c;
-    const size_t items = (a->c & 7) == 0 ? total / 8 : total;
+    p.vec = ((a->c & 7) == 0 && aligned16({a->x, a->y})) ? 1 : 0;
+    const size_t items = p.vec ? total / 8 : total;
     bn_apply_kernel<<<grid_for(items, 256), 256, 2 * a->c * sizeof(float), (cudaStream_t)stream>>>(p);
     MSTK_CHECK_LAUNCH("bn_apply");
     return MSTK_OK;
