@@ -1,0 +1,115 @@
+"""-m gpu: the drop-in modules on seeded random spectrogram SIZES and batch sizes, against the CPU oracle (oracle/ldm_oracle.py,
+pinned to the unmodified reference by tests/test_oracle_golden.py).  The golden fixtures and the BASELINE-size tests fix the map
+at 128 x 128, 128 x 384 and 128 x 1024; the reference's modules accept any height / width the UNet's three stride-2 levels
+divide (models/model.py:196-231: the skip concatenations need latent sides that are multiples of 8, i.e. spectrogram sides that
+are multiples of 64), the VAE alone any size at all (models/model.py:10-49).  Every size changes which kernel a layer
+dispatches to (halo / tcgen05 / edge / CUDA-core, split-K factors, tile shapes), so the same comparison is repeated here over
+non-square maps, small and prime batches, both precisions, eager and CUDA-graph paths."""
+import random
+
+import pytest
+import torch
+
+from gpu_util import assert_close_mode
+from oracle import ldm_oracle as O
+from test_gpu_model import fixed_randn_like
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+PRECISIONS = ["fp32", "bf16"]
+
+
+@pytest.fixture(scope="module")
+def ldm_by_precision(sd):
+    import music_style_transfer_ldm_b200 as M
+    out = {}
+    for p in PRECISIONS:
+        m = M.LDM(latent_dim=32, pretrained_path=None)
+        m.load_state_dict(sd, strict=True)
+        m.to(DEV).eval()
+        m.set_precision(p)
+        out[p] = m
+    return out
+
+
+def _spec(gen, b, h, w):
+    return torch.rand((b, 1, h, w), generator=gen)
+
+
+def _sizes(seed, count, step, hmax, wmax):
+    rng = random.Random(seed)
+    return [(rng.choice([1, 2, 3, 5, 7]), step * rng.randint(1, hmax), step * rng.randint(1, wmax), rng.randrange(1 << 20)) for _ in range(count)]
+
+
+def _down3(n):
+    for _ in range(3):
+        n = (n + 1) // 2
+    return n
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("b,h,w,seed", _sizes(11, 6, 64, 3, 5), ids=lambda v: str(v))
+def test_transfer_random_sizes(ldm_by_precision, sd, precision, b, h, w, seed):
+    """content_style_transfer_wrapper (VAE encode, style encoder, q-sample, DDIM loop, both decodes; model.py:468-559)"""
+    m = ldm_by_precision[precision]
+    g = torch.Generator().manual_seed(seed)
+    x, s = _spec(g, b, h, w), _spec(g, b, h, w)
+    eps = torch.randn((b, 32, h // 8, w // 8), generator=g)
+    steps, eta = 4, 0.3
+    ref_dec, ref_ztd = O.content_style_transfer(sd, x, s, eps, num_timesteps=steps, eta=eta, training=False)
+    for _ in range(2):                         # the second call replays the graph captured by the first
+        with fixed_randn_like(eps):
+            dec, ztd = m.content_style_transfer_wrapper(x.to(DEV), s.to(DEV), num_timesteps=steps, eta=eta)
+        assert dec.shape == (b, 1, h, w) and ztd.shape == (b, 1, h, w)
+        assert_close_mode(dec, ref_dec, precision, f"decoded {b}x{h}x{w}")
+        assert_close_mode(ztd, ref_ztd, precision, f"z_t_decoded {b}x{h}x{w}")
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("b,h,w,seed", _sizes(12, 8, 1, 71, 97) + [(2, 1, 1, 5), (1, 2, 3, 6), (3, 4, 4, 7), (1, 8, 8, 8)], ids=lambda v: str(v))
+def test_vae_any_size(sd, precision, b, h, w, seed):
+    """SpectrogramEncoder / SpectrogramDecoder on arbitrary (odd, tiny) maps, eval and train-mode BatchNorm: Conv2d(s2, p1) halves
+    with rounding up (three times), ConvTranspose2d doubles (three times)"""
+    import music_style_transfer_ldm_b200 as M
+    g = torch.Generator().manual_seed(seed)
+    x = _spec(g, b, h, w)
+    enc, dec = M.SpectrogramEncoder(32), M.SpectrogramDecoder(32)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")})
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")})
+    enc.to(DEV); dec.to(DEV)
+    enc.set_precision(precision); dec.set_precision(precision)
+    for training in (False, True):
+        if training and b * _down3(h) * _down3(w) < 2:
+            continue                                  # one value per channel: torch's BatchNorm refuses it in training mode
+        enc.train(training); dec.train(training)
+        z_ref = O.encoder_fwd(sd, x, training)
+        y_ref = O.decoder_fwd(sd, z_ref, training)
+        z = enc(x.to(DEV))
+        y = dec(z)
+        assert z.shape == z_ref.shape == (b, 32, _down3(h), _down3(w)) and y.shape == y_ref.shape == (b, 1, 8 * _down3(h), 8 * _down3(w))
+        if precision == "bf16" and training and z_ref.numel() // 32 < 64:
+            continue    # a batch statistic over a handful of bf16 values: shapes checked, numbers left to the larger cases
+        assert_close_mode(z, z_ref, precision, f"latent {b}x{h}x{w} train={training}")
+        assert_close_mode(y, y_ref, precision, f"decoded {b}x{h}x{w} train={training}")
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("b,h,w,seed", _sizes(13, 4, 64, 3, 4), ids=lambda v: str(v))
+def test_training_forward_random_sizes(sd, precision, b, h, w, seed):
+    """LDM.forward in train mode (batch-statistics BatchNorm; models/model.py:351-380) -- z_t, eps_hat, z_0, reconstruction"""
+    import music_style_transfer_ldm_b200 as M
+    if b == 1:
+        b = 2
+    m = M.LDM(latent_dim=32, pretrained_path=None)
+    m.load_state_dict(sd, strict=True)
+    m.to(DEV).train()
+    m.set_precision(precision)
+    g = torch.Generator().manual_seed(seed)
+    x, s = _spec(g, b, h, w), _spec(g, b, h, w)
+    eps = torch.randn((b, 32, h // 8, w // 8), generator=g)
+    t = torch.randint(0, 200, (b,), generator=g)
+    ref = O.ldm_forward(sd, x, s, t, eps, training=True)
+    with fixed_randn_like(eps):
+        out = m(x.to(DEV), s.to(DEV), t.to(DEV))
+    for k in ("z_t", "noise_pred", "z_0", "reconstructed"):
+        assert_close_mode(out[k], ref[k], precision, f"{k} {b}x{h}x{w}")
