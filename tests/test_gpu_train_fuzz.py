@@ -1,0 +1,37 @@
+"""-m gpu: LDMTrainer.train_step on batch sizes and spectrogram sizes other than the fixtures' (4 x 128 x 128, 256 x 128 x 128),
+against oracle/train_oracle.py (pinned to the unmodified reference trainer by tests/test_oracle_golden_train.py): four
+consecutive steps -- two eager, the capture, one replay -- so every size also goes through its own CUDA graph.  Sizes pick
+different kernels for the same layers (weight-gradient split-K factors, halo / tcgen05 / edge dispatch, BatchNorm row counts,
+the VGGish statistics kernels' tile walks), batch 1 and prime batches leave tiles ragged.
+fp32 mode: losses within 1e-4 (north_star); bf16 mode: within 1 %."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+KEYS = ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")
+SIZES = [(1, 64, 64), (3, 64, 192), (5, 128, 64), (2, 192, 128), (7, 64, 64)]
+
+
+def _inputs(i, b, h, w):
+    g = torch.Generator().manual_seed(9100 + 17 * i + b + h + w)
+    return (torch.rand((b, 1, h, w), generator=g), torch.rand((b, 1, h, w), generator=g),
+            torch.randint(0, 200, (b,), generator=g), torch.randn((b, 32, h // 8, w // 8), generator=g))
+
+
+@pytest.mark.parametrize("precision,rtol", [("fp32", 1e-4), ("bf16", 1e-2)])
+@pytest.mark.parametrize("b,h,w", SIZES, ids=lambda v: str(v))
+def test_train_steps_at_other_sizes(sd, b, h, w, precision, rtol):
+    from oracle import train_oracle as T
+    from test_gpu_train import _trainer
+    m, tr = _trainer(sd, precision, 1e-4, 3.0)
+    ot = T.OracleTrainer(sd, lr=1e-4, style_loss_weight=3.0)
+    for i in range(4):
+        x, s, t, eps = _inputs(i, b, h, w)
+        out = tr.train_step_device(x.to(DEV), s.to(DEV), t=t.to(DEV), noise=eps.to(DEV))
+        want = ot.train_step(x, s, t, eps)
+        np.testing.assert_allclose([float(out[k]) for k in KEYS], [want[k] for k in KEYS], rtol=rtol,
+                                   err_msg=f"step {i} of batch {b} x {h} x {w} ({precision})")
+    assert tr._graph is not None and tr.step_count == 4
+    tr.close()
