@@ -406,9 +406,10 @@ class CrossAttention(_Kernelised):
     def forward(self, unet_features, style_embedding):
         _need_cuda(unet_features, "CrossAttention")
         adt = _act_dtype(self._precision())
-        if unet_features.shape[2:] != style_embedding.shape[2:]:
-            # the reference reshapes the style map with the feature map's h*w (model.py:150)
-            raise MstkError("CrossAttention: style map must have the spatial size of the features")
+        if unet_features.shape[:2] != style_embedding.shape[:2] or unet_features[0, 0].numel() != style_embedding[0, 0].numel():
+            # the reference reshapes the style map with the feature map's h*w (model.py:149-150): any map with that many
+            # tokens passes there (tokens in row-major order), anything else is a reshape error
+            raise MstkError("CrossAttention: the style map must hold as many tokens (h*w) as the feature map, same batch and channels")
         f = ops.nchw_to_nhwc(unet_features.detach().float().contiguous(), adt)
         s = ops.nchw_to_nhwc(style_embedding.detach().float().contiguous(), adt)
         return _guard("CrossAttention", self, ops.nhwc_to_nchw(self._forward_nhwc(f, self._project_style(s))), unet_features, style_embedding)
