@@ -149,6 +149,47 @@ class _PackRefresher:
                     del cache[key]
 
 
+def device_prefetch(loader, device, pick=lambda element: element):
+    """Iterates ``loader`` one element ahead: yields ``pick(element)`` (a tensor or a tuple / list of tensors) on ``device``
+    with the upload of the NEXT element already enqueued on a copy stream, so the host-to-device copy of step i+1 runs under
+    the kernels of step i (33.5 MB per config-4 step: 0.6 ms of PCIe time beside a 6.9 ms step).  Pinned source tensors copy
+    asynchronously; pageable ones work too (the copy then blocks the host, as ``.to(device)`` always does).  Tensors cross
+    from the copy stream to the caller's stream through an event and ``record_stream``."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        for element in loader:
+            item = pick(element)
+            yield item.to(device) if isinstance(item, torch.Tensor) else tuple(t.to(device) for t in item)
+        return
+    copy = torch.cuda.Stream(device)
+
+    def upload(element):
+        item = pick(element)
+        single = isinstance(item, torch.Tensor)
+        with torch.cuda.stream(copy):
+            moved = tuple(t.to(device, non_blocking=True) for t in ((item,) if single else item))
+            done = torch.cuda.Event()
+            done.record(copy)
+        return moved, done, single
+
+    it = iter(loader)
+    try:
+        ahead = upload(next(it))
+    except StopIteration:
+        return
+    while ahead is not None:
+        moved, done, single = ahead
+        try:
+            ahead = upload(next(it))              # enqueued before the consumer launches the step that uses `moved`
+        except StopIteration:
+            ahead = None
+        main = torch.cuda.current_stream(device)
+        main.wait_event(done)
+        for t in moved:
+            t.record_stream(main)
+        yield moved[0] if single else moved
+
+
 class PeerExchange:
     """The small fp64 all-reduces of the data-parallel step (BatchNorm statistics forward and backward) over peer-mapped
     memory: one single-CTA launch per rank instead of an NCCL collective (csrc/peer.cu).  One process per GPU; the exchange
@@ -416,9 +457,8 @@ class LDMTrainer(_SideStream):
         self.model.train()
         num_batches = len(self.train_loader)
         acc = torch.zeros(4, dtype=torch.float64, device=self.device)
-        for element in self.train_loader:
-            (content_spec, _), (style_spec, _) = element
-            out = self.train_step_device(content_spec.to(self.device, non_blocking=True), style_spec.to(self.device, non_blocking=True))
+        for content_spec, style_spec in device_prefetch(self.train_loader, self.device, pick=lambda el: (el[0][0], el[1][0])):
+            out = self.train_step_device(content_spec, style_spec)
             acc += torch.stack([out["total_loss"], out["compression_loss"], out["denoisinsg_loss"], out["style_loss"]]).double()
         k = config["training_iteration_noise"]
         return tuple(v / num_batches * k for v in acc.tolist())                  # ONE host sync per epoch
@@ -1005,14 +1045,13 @@ def train_autoencoder(config, train_loader=None, test_loader=None, checkpoint_di
     for epoch in range(config["num_epochs"]):
         encoder.train(); decoder.train()
         acc = torch.zeros((), dtype=torch.float64, device=device)
-        for element in train_loader:
-            acc += tr.train_step_device(element[0].to(device, non_blocking=True)).double()
+        for spec in device_prefetch(train_loader, device, pick=lambda el: el[0]):
+            acc += tr.train_step_device(spec).double()
         train_losses.append(float(acc) / len(train_loader))
         encoder.eval(); decoder.eval()
         acc = torch.zeros((), dtype=torch.float64, device=device)
         with torch.no_grad():
-            for element in test_loader:
-                spec = element[0].to(device, non_blocking=True)
+            for spec in device_prefetch(test_loader, device, pick=lambda el: el[0]):
                 latent = encoder(spec)
                 acc += L.compression_loss(spec, decoder(latent), latent, feature_extractor).double()
         val_losses.append(float(acc) / len(test_loader))

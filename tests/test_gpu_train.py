@@ -200,3 +200,19 @@ def test_capture_is_not_invalidated_by_a_dead_cycle_that_owns_a_graph():
     g.replay()
     torch.cuda.synchronize()
     assert x.tolist() == [2.0] * 8
+
+
+def test_device_prefetch_uploads_ahead_and_in_order():
+    """train.device_prefetch: pinned and pageable sources, one element ahead on a copy stream; values and order survive, and the
+    consumer's stream may use the tensors at once (event + record_stream)"""
+    from music_style_transfer_ldm_b200.train import device_prefetch
+    g = torch.Generator().manual_seed(3)
+    host = [torch.rand((4, 1, 64, 64), generator=g) for _ in range(5)]
+    loader = [((h.pin_memory() if i % 2 else h, 0), (h.flip(0).contiguous().pin_memory(), 1)) for i, h in enumerate(host)]
+    sums = []
+    for c, s in device_prefetch(loader, torch.device(DEV), pick=lambda el: (el[0][0], el[1][0])):
+        assert c.is_cuda and s.is_cuda
+        sums.append((c.double().sum() + 2 * s[0].double().sum()))       # enqueued immediately on the current stream
+    want = [float(h.double().sum() + 2 * h[-1].double().sum()) for h in host]
+    np.testing.assert_allclose([float(v) for v in sums], want, rtol=1e-12)
+    assert list(device_prefetch([], torch.device(DEV))) == []

@@ -40,3 +40,14 @@ def test_zero_pool_hands_out_aligned_zeroed_slices_and_falls_back():
     finally:
         ops.ZERO_POOL = old
     assert ops.zeros_f64(4, "cpu").numel() == 4                  # no pool active
+
+
+def test_device_prefetch_cpu_path_keeps_order_and_structure():
+    """train.device_prefetch on a CPU device: a plain pass-through (the CUDA path is exercised by tests/test_gpu_train.py)"""
+    import torch
+    from music_style_transfer_ldm_b200.train import device_prefetch
+    loader = [((torch.full((2,), float(i)), "label"), (torch.full((3,), float(-i)), "label")) for i in range(4)]
+    got = list(device_prefetch(loader, "cpu", pick=lambda el: (el[0][0], el[1][0])))
+    assert [float(c[0]) for c, _ in got] == [0.0, 1.0, 2.0, 3.0] and [float(s[0]) for _, s in got] == [0.0, -1.0, -2.0, -3.0]
+    single = list(device_prefetch([(torch.ones(2) * i, 0) for i in range(3)], torch.device("cpu"), pick=lambda el: el[0]))
+    assert [float(t[0]) for t in single] == [0.0, 1.0, 2.0] and list(device_prefetch([], "cpu")) == []
