@@ -791,10 +791,25 @@ def run_cuda(args):
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in evs)        # ms on the device
 
+    def loop_e2e(k):
+        """k calls through LDM.transfer_batches: pinned host batches in, pinned host images out, the upload of call i+1 and
+        the download of call i-1 on copy streams under call i.  One event pair around the whole loop (first upload and last
+        download unoverlapped, included); the host waits for the last download before the closing event is recorded."""
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for dec, ztd in model.transfer_batches([(content_h, style_h)] * k, num_timesteps=NSTEPS, eta=0.0):
+            out_h[0], out_h[1] = dec, ztd
+            flush.fill_(1)                                   # L2 flush between calls, INSIDE the timed region here (~40 us per call)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
     with torch.no_grad():
         for _ in range(max(3, args.warmup)):
             step_device()
         step_e2e()
+        loop_e2e(2)
         torch.cuda.synchronize()
         ops.LAUNCHES = 0
         step_device()
@@ -807,14 +822,16 @@ def run_cuda(args):
         barrier()
         ms = timed(step_device, args.steps)
         barrier()
-        ms_e2e = timed(step_e2e, args.steps)
+        ms_serial = timed(step_e2e, args.steps)
+        barrier()
+        ms_e2e = loop_e2e(args.steps)
         barrier()
         clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, ms_e2e, ms_serial], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = t.tolist()
+    ms, ms_e2e, ms_serial = t.tolist()
     train = train_weak = parity = None
     if not args.no_train:
         del model
@@ -931,7 +948,10 @@ def run_cuda(args):
             "train": train, "train_weak": train_weak, "vae": vae, "vae_fp32": vae32, "train_autoencoder": ae, "config5": mel, "fp32_mode": fp32,
             "gpu_baseline": base,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
-                    "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps},
+                    "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps,
+                    "how": "LDM.transfer_batches: pinned host batches in, pinned host images out; upload of call i+1 and download of "
+                           "call i-1 on copy streams under call i; one event pair around all calls, the L2 flush between calls inside it",
+                    "serial_value": unet_steps / (ms_serial * 1e-3), "serial_ms_per_step": ms_serial / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
             "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
             "samples_steps_per_s": value * BATCH,

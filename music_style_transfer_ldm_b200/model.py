@@ -840,6 +840,37 @@ class LDM(_Kernelised):
             (dec,) = body(ss, z_t)
         return dec.view(dec.shape[0], 1, dec.shape[1], dec.shape[2])
 
+    def transfer_batches(self, batches, num_timesteps=250, eta=0.0):
+        """Serving loop over HOST batches (no reference counterpart: the reference's scripts call the wrapper once per batch and
+        copy around it).  ``batches`` yields (content, style) CPU tensors, pinned for asynchronous copies; for each one, in
+        order, this yields the wrapper's (decoded, z_t_decoded) as pinned CPU tensors.  The upload of batch i+1 and the
+        download of batch i-1 run on copy streams under the kernels of batch i (ops.device_prefetch; the wrapper's outputs
+        are clones, so the next replay does not touch what the download reads); each result is handed out one call late,
+        after its download event."""
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise MstkError("transfer_batches: the model must be on a CUDA device (the kernels have no CPU path)")
+        down = torch.cuda.Stream(dev)
+        pending = None
+        for c, s in ops.device_prefetch(batches, dev):
+            dec, ztd = self.content_style_transfer_wrapper(c, s, num_timesteps=num_timesteps, eta=eta)
+            main = torch.cuda.current_stream(dev)
+            ready = torch.cuda.Event()
+            ready.record(main)
+            with torch.cuda.stream(down):
+                down.wait_event(ready)
+                outs = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t, non_blocking=True) for t in (dec, ztd))
+                done = torch.cuda.Event()
+                done.record(down)
+            dec.record_stream(down); ztd.record_stream(down)
+            if pending is not None:
+                pending[1].synchronize()
+                yield pending[0]
+            pending = (outs, done)
+        if pending is not None:
+            pending[1].synchronize()
+            yield pending[0]
+
     def content_style_transfer_wrapper(self, content_spec, style_spec, num_timesteps=250, eta=0.0):
         """model.py:468-501.  Returns (decoded in [0,1], z_t_decoded in [-1,1])."""
         cs = self._spec_nhwc(content_spec, "content_style_transfer_wrapper")

@@ -242,3 +242,26 @@ def test_full_size_properties(ldm_by_precision, sd):
         m.use_cuda_graphs = True
         m.train()
         _reset(m, sd)
+
+
+def test_transfer_batches_equals_the_wrapper_call_by_call(ldm_by_precision, sd):
+    """LDM.transfer_batches (uploads / downloads pipelined on copy streams around the whole-call graph): every yielded pair equals
+    the wrapper called on the same batch with the same generator state, in order, as pinned CPU tensors (fp32 mode, 1e-5:
+    split-K partial sums are reduced in arrival order, so two runs of the SAME call already differ in the last bits)"""
+    m = ldm_by_precision["fp32"]
+    m.eval()
+    try:
+        g = torch.Generator().manual_seed(81)
+        batches = [(torch.rand((3, 1, 128, 128), generator=g).pin_memory(), torch.rand((3, 1, 128, 128), generator=g)) for _ in range(4)]
+        torch.manual_seed(5); torch.cuda.manual_seed(5)
+        want = [tuple(t.cpu() for t in m.content_style_transfer_wrapper(c.to(DEV), s.to(DEV), num_timesteps=6, eta=0.0)) for c, s in batches]
+        torch.manual_seed(5); torch.cuda.manual_seed(5)
+        got = list(m.transfer_batches(iter(batches), num_timesteps=6, eta=0.0))
+        assert len(got) == 4
+        for (d, z), (dw, zw) in zip(got, want):
+            assert not d.is_cuda and d.is_pinned() and d.shape == (3, 1, 128, 128)
+            assert rel_err(d, dw) <= 1e-5 and rel_err(z, zw) <= 1e-5, (rel_err(d, dw), rel_err(z, zw))
+        assert list(m.transfer_batches([], num_timesteps=6)) == []
+    finally:
+        m.train()
+        _reset(m, sd)
