@@ -111,3 +111,30 @@ def test_batch_loader_one_kernel_per_side(png_root, tmp_path):
     sd_ = SpectrogramDataset({"processed_spectograms_dataset_folderpath": ds.store})
     xb, cb = next(iter(sd_.loader(8)))
     assert xb.shape == (8, 1, 128, 128) and torch.equal(xb[3].cpu(), sd_[3][0]) and int(cb[3]) == sd_[3][1]
+
+
+@pytest.mark.gpu
+def test_pair_loader_feeds_train_epoch(png_root, tmp_path, sd):
+    """§8(f) rank 3 end to end: the GPU-resident pair loader (elements already on the device) through LDMTrainer.train_epoch
+    (train.py:209-243; ops.device_prefetch passes device tensors through) against a hand-written loop of train_step over the
+    same batches -- four epoch averages, the ragged last batch of 2 included"""
+    import numpy as np
+    from music_style_transfer_ldm_b200.config import config
+    from music_style_transfer_ldm_b200.dataset import SpectrogramPairDataset
+    from test_gpu_train import _trainer
+    csv_path = str(tmp_path / "pairs.csv")
+    SpectrogramPairDataset.generate_pairings(png_root, csv_path, num_pairs=10)
+    ds = _ds(png_root, csv_path)
+    _, tr1 = _trainer(sd, "fp32", 1e-4, 3.0)
+    tr1.train_loader = ds.loader(batch_size=4, shuffle=False)
+    torch.manual_seed(3); torch.cuda.manual_seed(3)
+    avg = tr1.train_epoch(0)
+    _, tr2 = _trainer(sd, "fp32", 1e-4, 3.0)
+    torch.manual_seed(3); torch.cuda.manual_seed(3)
+    tot, n = np.zeros(4), 0
+    for (c, _), (s, _) in ds.loader(batch_size=4, shuffle=False):
+        out = tr2.train_step(c, s)
+        tot += [out["total_loss"], out["compression_loss"], out["denoisinsg_loss"], out["style_loss"]]
+        n += 1
+    assert n == 3 and tr1.step_count == 3
+    np.testing.assert_allclose(avg, tot / n * config["training_iteration_noise"], rtol=1e-4)
