@@ -1,6 +1,5 @@
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --no-train --no-vae --no-mel --no-fp32 --no-gpu-baseline --no-cpu-baseline"
-timeout 300 $CMD > gpurun_out/bl_plain.log 2> gpurun_out/bl_plain.err; echo "plain rc=$?"
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/bench_launches.csv $CMD > gpurun_out/bl_ncu.log 2> gpurun_out/bl_ncu.err; echo "ncu rc=$?"
-wc -l gpurun_out/bench_launches.csv
-python tools/summarize_launches.py gpurun_out/bench_launches.csv --md > gpurun_out/bench_launches.md; head -25 gpurun_out/bench_launches.md | cut -c 1-200
+run() { timeout 600 env $1 python bench.py --steps 20 --no-train --no-vae --no-mel --no-fp32 --no-gpu-baseline --no-cpu-baseline > gpurun_out/bk.log 2> gpurun_out/bk.err
+python -c "
+import json; d=json.loads(open('gpurun_out/bk.log').read().strip().splitlines()[-1]); e=d['e2e']; print('$1', round(d['ms_per_step'],3), [round(v,3) for v in e['runs_ms_per_step']], round(e['serial_ms_per_step'],3))"; }
+for i in 1 2 3 4; do run A=1; run MSTK_BENCH_NOSAMPLER=1; done
