@@ -687,6 +687,26 @@ def fp32_leg(sd, dev, content_d, style_d, calls=3):
             "unet_step_us": us / (NSTEPS - 1)}
 
 
+def batch_sweep(model, dev, peaks, flop_per_sample_step, batches=(64, 128, 256, 512), calls=3):
+    """Not a BASELINE config: the config-3 call at larger batches on the same kernels and graph -- how much of the 0.06 is the
+    batch size of the config (11 dependent launches of 0.1-0.9 waves per step at batch 64) and how much the kernels.  Device
+    time of the whole call per UNet step, sample-steps/s, fraction of the measured bf16 peak on the algorithmic conv FLOPs."""
+    import torch
+    peak = float(peaks.get("bf16_tflops", 1590.0))
+    out = []
+    for b in batches:
+        g = torch.Generator().manual_seed(900 + b)
+        c, s_ = torch.rand((b, 1, SPEC, SPEC), generator=g).to(dev), torch.rand((b, 1, SPEC, SPEC), generator=g).to(dev)
+        with torch.no_grad():
+            us = _time_us(lambda: model.content_style_transfer_wrapper(c, s_, num_timesteps=NSTEPS, eta=0.0), calls)
+        step_us = us / (NSTEPS - 1)
+        tf = flop_per_sample_step * b / (step_us * 1e-6) / 1e12
+        out.append({"batch": b, "unet_step_us": step_us, "sample_steps_per_s": b * (NSTEPS - 1) / (us * 1e-6), "tflops": tf, "frac_of_bf16_peak": tf / peak})
+        del c, s_
+    torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------------------
 # data-parallel self-check (the driver's test box has one GPU: the N > 1 bench runs carry the evidence)
 # ------------------------------------------------------------------------------------------
@@ -902,6 +922,9 @@ def run_cuda(args):
         vae32 = None if (args.no_vae or world > 1 or args.precision == "fp32") else vae_leg(sd, dev, peaks, "fp32", reps=5)
         ae = None if (args.no_train or world > 1) else ae_leg(sd, dev, args.precision)
         fp32 = None if (world > 1 or args.precision == "fp32" or args.no_fp32) else fp32_leg(sd, dev, content_d, style_d)
+        sweep = None
+        if world == 1 and not args.no_fp32 and roof and roof.get("flop_per_launch_avg"):
+            sweep = batch_sweep(model, dev, peaks, roof["flop_per_launch_avg"] * roof["launches_per_unet_step"] / BATCH)
         base = None if (world > 1 or args.no_gpu_baseline) else gpu_baseline(sd, dev)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -932,7 +955,9 @@ def run_cuda(args):
             "sampling": {"steps_per_s": r3(value), "e2e_steps_per_s": r3(e2e_value), "unet_step_us": r3(unet_step_us),
                          "sum_isolated_kernel_us": r3(roof.get("sum_isolated_us_all_kernels")), "pdl_overlap_frac": r3(roof.get("pdl_overlap_frac")),
                          "launches_per_unet_step": roof.get("launches_per_unet_step_all_kernels"), "roofline_frac": r3(roof["frac"]),
-                         "fp32_mode_steps_per_s": r3(pick(fp32, "value"))},
+                         "fp32_mode_steps_per_s": r3(pick(fp32, "value")),
+                         "batch_sweep_frac_of_bf16_peak": None if not sweep else {str(r["batch"]): r3(r["frac_of_bf16_peak"]) for r in sweep},
+                         "batch_sweep_unet_step_us": None if not sweep else {str(r["batch"]): r3(r["unet_step_us"]) for r in sweep}},
             "train_strong": {"global_batch": pick(train, "global_batch"), "samples_per_s": r3(tv), "ms_per_step": r3(pick(train, "ms_per_step")),
                              "e2e_samples_per_s": r3(pick(train, "e2e", "value")), "vggish_conv_roofline_frac": r3(pick(train, "roofline", "frac")),
                              "algorithmic_frac_of_bf16_peak": r3(19.6e9 * tv / 1e12 / peaks.get("bf16_tflops", 1590.0)) if tv else None},
@@ -967,7 +992,7 @@ def run_cuda(args):
             "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
             "config": workload_config({"precision": args.precision, "sharding": f"batch-sharded x{world}, no collective on the data path"}),
             "layers": rows,
-            "train": train, "train_weak": train_weak, "vae": vae, "vae_fp32": vae32, "train_autoencoder": ae, "config5": mel, "fp32_mode": fp32,
+            "train": train, "train_weak": train_weak, "vae": vae, "vae_fp32": vae32, "train_autoencoder": ae, "config5": mel, "fp32_mode": fp32, "batch_sweep": sweep,
             "gpu_baseline": base,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * content_h.numel() * 4,
                     "d2h_bytes_per_step": 2 * out_h[0].numel() * 4, "ms_per_step": ms_e2e / args.steps,
