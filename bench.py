@@ -960,7 +960,7 @@ def run_cuda(args):
                          "batch_sweep_unet_step_us": None if not sweep else {str(r["batch"]): r3(r["unet_step_us"]) for r in sweep}},
             "train_strong": {"global_batch": pick(train, "global_batch"), "samples_per_s": r3(tv), "ms_per_step": r3(pick(train, "ms_per_step")),
                              "e2e_samples_per_s": r3(pick(train, "e2e", "value")), "vggish_conv_roofline_frac": r3(pick(train, "roofline", "frac")),
-                             "algorithmic_frac_of_bf16_peak": r3(19.6e9 * tv / 1e12 / peaks.get("bf16_tflops", 1590.0)) if tv else None},
+                             "algorithmic_frac_of_bf16_peak": r3(19.6e9 * tv / 1e12 / (world * peaks.get("bf16_tflops", 1590.0))) if tv else None},
             "train_weak": {"global_batch": pick(train_weak, "global_batch"), "samples_per_s": r3(pick(train_weak, "value")),
                            "ms_per_step": r3(pick(train_weak, "ms_per_step")), "e2e_samples_per_s": r3(pick(train_weak, "e2e", "value"))},
             "ddp_parity": parity,
