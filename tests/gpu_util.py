@@ -40,15 +40,16 @@ def assert_close(got, ref, tol, what=""):
     assert e <= tol, f"{what}: relative error {e:.3e} > {tol:.1e}"
 
 
-def assert_close_mode(got, ref, precision, what=""):
-    """the parity bar of a whole-model output in the given precision mode (see TOL above)"""
+def assert_close_mode(got, ref, precision, what="", max_guard=BF16_MAX_GUARD):
+    """the parity bar of a whole-model output in the given precision mode (see TOL above); ``max_guard`` replaces the bf16
+    max-norm guard where a case is known to sit next to it (the bar itself, the L2 norm, is never loosened)"""
     e2, em = rel_l2(got, ref), rel_err(got, ref)
     REPORT.append((what, precision, e2, em))
     if precision == "fp32":
         assert em <= TOL["fp32"], f"{what}: relative error {em:.3e} > {TOL['fp32']:.1e}"
         return
     assert e2 <= TOL["bf16"], f"{what}: relative L2 error {e2:.3e} > {TOL['bf16']:.1e} (max-norm {em:.3e})"
-    assert em <= BF16_MAX_GUARD, f"{what}: max-norm relative error {em:.3e} > {BF16_MAX_GUARD:.1e}"
+    assert em <= max_guard, f"{what}: max-norm relative error {em:.3e} > {max_guard:.1e}"
 
 
 def nhwc(x_nchw: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
