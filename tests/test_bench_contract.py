@@ -1,0 +1,37 @@
+"""CPU: the two things the driver's bench contract needs that can be checked without a GPU --
+  * `bench.py --impl reference` (the reference arm: the oracle port of the reference's CPU path on the host cores) prints ONE JSON
+    line with the contract's keys, the product arm's metric / unit / config, `"impl": "reference"`, a `cpu_baseline` describing the
+    run and an `e2e` that repeats the line's own value with zero copy bytes;
+  * the product arm refuses to run without a CUDA device (no CPU fallback, no silent routing through the oracle)."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(*args, timeout=600):
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")          # also on a GPU box: this file is about the CPU behaviour
+    return subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
+
+
+def test_reference_arm_prints_the_contract_line():
+    r = _run("--impl", "reference", "--steps", "1", "--warmup", "1")
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")]
+    assert len(lines) == 1, r.stdout[-2000:]
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "unet_denoise_steps_per_s" and d["unit"] == "steps/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] == 1 and d["value"] > 0
+    assert d["data"] == "synthetic" and d["vs_baseline"] is None and "workload" in d["config"]
+    cb, e2e = d["cpu_baseline"], d["e2e"]
+    assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    assert e2e["value"] == d["value"] and e2e["unit"] == d["unit"] and e2e["h2d_bytes_per_step"] == 0 and e2e["d2h_bytes_per_step"] == 0
+
+
+def test_product_arm_fails_loudly_without_a_gpu():
+    r = _run("--steps", "1", timeout=300)
+    assert r.returncode != 0
+    assert "no CUDA device" in (r.stderr + r.stdout) and "no CPU fallback" in (r.stderr + r.stdout)
+    assert not [ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")]          # and prints no number
